@@ -1,0 +1,156 @@
+/* m2f_b200.h -- C ABI of the B200-native M2FNet hot path (libm2f_b200.so).
+ *
+ * The reference (iosonopersia/Multimodal-Emotion-Recognition) has no FFI of its own: the
+ * boundary the hot path sits behind is the Python class `M2FNet` in src/model.py.  Every
+ * entry point below cites the reference arithmetic it replaces (paths relative to the
+ * reference repo; "torch/" = the PyTorch the reference executes through).  INTEGRATION.md
+ * shows the ctypes binding a maintainer of the reference would add.
+ *
+ * Conventions
+ *  - plain C types only; every pointer is a DEVICE pointer unless named host_*;
+ *  - every function returns 0 (M2F_OK) or a negative error code; the message is available
+ *    from m2f_last_error() (thread-local).  No C++ exception crosses the boundary;
+ *  - all work is enqueued on `stream` (a cudaStream_t passed as void*), never synchronises,
+ *    never allocates or frees device memory: the caller owns every buffer;
+ *  - unsupported shapes are errors, never silent fallbacks.  There is no CPU path.
+ *
+ * "planes": a matrix stored as P in {1,2,3} bf16 planes whose sum is the value
+ * (P = 1: bf16 throughput mode; P = 3: ~24 mantissa bits, the fp32-parity mode in which each
+ * tensor-core GEMM runs the 6 significant plane products with fp32 accumulation).
+ */
+#ifndef M2F_B200_H
+#define M2F_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define M2F_ABI_VERSION 1
+
+#define M2F_OK 0
+#define M2F_ERR_ARG (-1)         /* bad argument / shape */
+#define M2F_ERR_UNSUPPORTED (-2) /* valid request outside the kernels' limits */
+#define M2F_ERR_CUDA (-3)        /* CUDA runtime / driver error */
+#define M2F_ERR_ALIGN (-4)       /* pointer or stride alignment */
+
+/* dropout call sites (src/model.py:57,61,73,85,97,111-131).  mod: 0 audio, 1 text */
+#define M2F_SITE_ENC(mod, t, l, k) (0x1000u * ((mod) + 1u) + 0x100u * (t) + 0x10u * (l) + (k))
+#define M2F_SITE_MOD(mod, k) (0x1000u * ((mod) + 1u) + 0xF00u + (k))
+#define M2F_SITE_FAM(i, k) (0x3000u + 0x10u * (i) + (k))
+#define M2F_SITE_CLS 0x4000u
+
+typedef struct {
+    void* ptr;            /* bf16, plane 0 */
+    int64_t rows, cols;   /* logical extent */
+    int64_t ld;           /* row stride in elements; multiple of 8 */
+    int64_t plane_stride; /* elements between consecutive planes */
+    int32_t planes;       /* 1..3 */
+    int32_t _pad;
+} m2f_planes_t;
+
+typedef struct {
+    int32_t a_k0, b_k0, klen; /* contraction segment: A[:, a_k0:a_k0+klen] . B[:, b_k0:b_k0+klen]^T */
+} m2f_kseg_t;
+
+/* Epilogue applied to each accumulator element v = sum_k A[m,k] B[n,k], in this order:
+ *   v += bias[n]; if relu: v = max(v,0); if gate: v = gate[m,n] > 0 ? v*gate_scale : 0;
+ *   if drop_p > 0: v = keep(seed,step,site, m*drop_ld+n) ? v/(1-p) : 0; v += resid[m,n];
+ *   if accumulate: v += out_f32[m,n];  then stored to out_f32 and/or out_planes. */
+typedef struct {
+    const float* bias;
+    int32_t relu;
+    int32_t accumulate;
+    const void* gate; /* bf16 plane 0 of a saved activation */
+    int64_t gate_ld;
+    float gate_scale;
+    float drop_p;
+    uint64_t seed, step;
+    uint32_t site;
+    int32_t _pad;
+    int64_t drop_ld;
+    const float* resid;
+    int64_t resid_ld;
+    float* out_f32;
+    int64_t out_f32_ld;
+    m2f_planes_t out_planes; /* ptr == NULL: none */
+} m2f_epilogue_t;
+
+int m2f_abi_version(void);
+const char* m2f_last_error(void);
+
+/* Device capability check: returns M2F_OK only on an sm_100 device. */
+int m2f_check_device(void);
+
+/* ---- K1: tcgen05 GEMM.  D[M,N] = sum over segments and plane products of A . B^T.
+ * Replaces every nn.Linear / in-projection of the model (src/model.py:9,68,80,90-98;
+ * torch/nn/functional.py:5833-5873; torch/nn/modules/transformer.py:980-982) and, with
+ * a_mn_major / b_mn_major, their autograd backward (dgrad: B = W stored [N_contract, K_out];
+ * wgrad: A = dY stored [M_contract, N_out], B = X stored [M_contract, K_out]).
+ * x_mn_major = 0: operand stored [rows = M or N, cols = K]; 1: stored [rows = K, cols = M or N]. */
+int m2f_gemm(const m2f_planes_t* A, int a_mn_major, const m2f_planes_t* B, int b_mn_major,
+             const m2f_kseg_t* segs, int nsegs, int64_t M, int64_t N,
+             const m2f_epilogue_t* epi, void* stream);
+
+/* fp32 [rows, cols] (row stride src_ld) -> bf16 planes (weights shadow copy, model inputs). */
+int m2f_split_planes(const float* src, int64_t src_ld, const m2f_planes_t* dst, void* stream);
+/* dst = relu(src) on planes (first fusion layer's concat operand, src/model.py:16-17) */
+int m2f_relu_planes(const m2f_planes_t* src, const m2f_planes_t* dst, void* stream);
+/* out[n] += sum_m src[m,n]  (bias gradients) */
+int m2f_colsum_planes(const m2f_planes_t* src, float* out, void* stream);
+
+/* ---- K3: LayerNorm (+ residual / outer skip).  nn.LayerNorm eps 1e-5, biased variance
+ * (torch/nn/modules/transformer.py:977-982 norm1/norm2; :550-551 final norm; src/model.py:107,119).
+ *   y = LN(x) * gamma + beta (+ skip);  stats[2*m] = mean, stats[2*m+1] = rstd.
+ *   y_f32 (nullable) and y_planes (nullable ptr) receive y; the planes copy optionally gets
+ *   dropout (site, p) applied -- the model-level dropout before the projection (src/model.py:111,123). */
+int m2f_ln_fwd(const float* x, int64_t x_ld, const float* gamma, const float* beta,
+               const float* skip, int64_t skip_ld, int64_t M, int64_t D,
+               float* y_f32, int64_t y_ld, const m2f_planes_t* y_planes,
+               float drop_p, uint64_t seed, uint64_t step, uint32_t site,
+               float* stats, void* stream);
+
+/* LayerNorm backward.  g = dL/dy [M,D] fp32;  x, stats from the forward.
+ *   dx = rstd * (gamma*g - mean(gamma*g) - xhat * mean(gamma*g*xhat));
+ *   dgamma += sum_m g*xhat; dbeta += sum_m g;
+ *   dx_f32 (nullable) receives dx; dx_planes (nullable ptr) receives dropmask(dx) (the mask of the
+ *   dropout that sat between the producing Linear and the residual add, regenerated from
+ *   (seed, step, site)); dbias (nullable) += column sums of dropmask(dx). */
+int m2f_ln_bwd(const float* g, int64_t g_ld, const float* x, int64_t x_ld, const float* gamma,
+               const float* stats, int64_t M, int64_t D,
+               float* dx_f32, int64_t dx_ld, const m2f_planes_t* dx_planes,
+               float drop_p, uint64_t seed, uint64_t step, uint32_t site,
+               float* dgamma, float* dbeta, float* dbias, void* stream);
+
+/* ---- K2: masked multi-head attention, one CTA per (dialogue, head).
+ * P = softmax(q k^T / sqrt(hd) with -inf on padded KEYS), O = dropout(P) v
+ * (torch/nn/functional.py:6607-6690; fusion layers: q,v from text, k from audio, src/model.py:14).
+ * q,k,v,o: planes views of [B*S, H*hd] (cols = H*hd; they may alias one packed buffer through
+ * different base pointers and a common ld).  key_pad: uint8 [B,S], 1 = padded. */
+int m2f_attn_fwd(const m2f_planes_t* q, const m2f_planes_t* k, const m2f_planes_t* v,
+                 const uint8_t* key_pad, int64_t B, int64_t S, int32_t H,
+                 float drop_p, uint64_t seed, uint64_t step, uint32_t site,
+                 const m2f_planes_t* o, void* stream);
+/* backward: recomputes P; d_o planes in, dq/dk/dv planes out. */
+int m2f_attn_bwd(const m2f_planes_t* q, const m2f_planes_t* k, const m2f_planes_t* v,
+                 const m2f_planes_t* d_o, const uint8_t* key_pad, int64_t B, int64_t S, int32_t H,
+                 float drop_p, uint64_t seed, uint64_t step, uint32_t site,
+                 const m2f_planes_t* dq, const m2f_planes_t* dk, const m2f_planes_t* dv, void* stream);
+
+/* ---- K4: cross entropy, ignore_index = -1, label smoothing eps, optional class weights
+ * (src/train.py:48-50,229).  logits fp32 [M,C] (row stride ld), target int64 [M].
+ * loss_out[0] = loss, loss_out[1] = sum of weights over valid rows (scratch: 4 floats, zeroed inside).
+ * dlogits (nullable) fp32 [M, dl_ld] receives grad_scale * dL/dlogits; dl_planes likewise. */
+int m2f_ce_fwd_bwd(const float* logits, int64_t ld, const int64_t* target, const float* class_w,
+                   int64_t M, int32_t C, float eps, float grad_scale, float* loss_out,
+                   float* dlogits, int64_t dl_ld, const m2f_planes_t* dl_planes, void* stream);
+
+/* test helper: mask[i] = 1 if element i of `site` is kept, for i in [0, n) */
+int m2f_dropout_mask(float p, uint64_t seed, uint64_t step, uint32_t site, int64_t n, uint8_t* mask,
+                     void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* M2F_B200_H */

@@ -1,0 +1,85 @@
+"""ctypes binding of libm2f_b200.so (the C ABI declared in include/m2f_b200.h).
+
+The library is the only compute path: if it cannot be loaded, or a call fails, a RuntimeError is
+raised -- there is no eager / CPU fallback anywhere in this package.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import threading
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "libm2f_b200.so")
+
+M2F_OK = 0
+
+
+class Planes(C.Structure):
+    """m2f_planes_t"""
+    _fields_ = [("ptr", C.c_void_p), ("rows", C.c_int64), ("cols", C.c_int64), ("ld", C.c_int64),
+                ("plane_stride", C.c_int64), ("planes", C.c_int32), ("_pad", C.c_int32)]
+
+
+class KSeg(C.Structure):
+    """m2f_kseg_t"""
+    _fields_ = [("a_k0", C.c_int32), ("b_k0", C.c_int32), ("klen", C.c_int32)]
+
+
+class Epilogue(C.Structure):
+    """m2f_epilogue_t"""
+    _fields_ = [("bias", C.c_void_p), ("relu", C.c_int32), ("accumulate", C.c_int32),
+                ("gate", C.c_void_p), ("gate_ld", C.c_int64), ("gate_scale", C.c_float), ("drop_p", C.c_float),
+                ("seed", C.c_uint64), ("step", C.c_uint64), ("site", C.c_uint32), ("_pad", C.c_int32),
+                ("drop_ld", C.c_int64), ("resid", C.c_void_p), ("resid_ld", C.c_int64),
+                ("out_f32", C.c_void_p), ("out_f32_ld", C.c_int64), ("out_planes", Planes)]
+
+
+PP = C.POINTER(Planes)
+_i64, _i32, _u64, _u32, _f32, _vp = C.c_int64, C.c_int32, C.c_uint64, C.c_uint32, C.c_float, C.c_void_p
+
+# name -> argtypes; must list every symbol include/m2f_b200.h declares (tests/test_abi_symbols.py checks)
+PROTOTYPES = {
+    "m2f_abi_version": [],
+    "m2f_last_error": [],
+    "m2f_check_device": [],
+    "m2f_gemm": [PP, C.c_int, PP, C.c_int, C.POINTER(KSeg), C.c_int, _i64, _i64, C.POINTER(Epilogue), _vp],
+    "m2f_split_planes": [_vp, _i64, PP, _vp],
+    "m2f_relu_planes": [PP, PP, _vp],
+    "m2f_colsum_planes": [PP, _vp, _vp],
+    "m2f_ln_fwd": [_vp, _i64, _vp, _vp, _vp, _i64, _i64, _i64, _vp, _i64, PP, _f32, _u64, _u64, _u32, _vp, _vp],
+    "m2f_ln_bwd": [_vp, _i64, _vp, _i64, _vp, _vp, _i64, _i64, _vp, _i64, PP, _f32, _u64, _u64, _u32, _vp, _vp, _vp, _vp],
+    "m2f_attn_fwd": [PP, PP, PP, _vp, _i64, _i64, _i32, _f32, _u64, _u64, _u32, PP, _vp],
+    "m2f_attn_bwd": [PP, PP, PP, PP, _vp, _i64, _i64, _i32, _f32, _u64, _u64, _u32, PP, PP, PP, _vp],
+    "m2f_ce_fwd_bwd": [_vp, _i64, _vp, _vp, _i64, _i32, _f32, _f32, _vp, _vp, _i64, PP, _vp],
+    "m2f_dropout_mask": [_f32, _u64, _u64, _u32, _i64, _vp, _vp],
+}
+
+_lock = threading.Lock()
+_lib = None
+
+
+def lib() -> C.CDLL:
+    """Load (once) and return the shared library; raises if it is missing."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    with _lock:
+        if _lib is None:
+            if not os.path.exists(LIB_PATH):
+                raise RuntimeError(
+                    f"{LIB_PATH} is missing: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+                    "(nvcc, sm_100a).  This package has no CPU or eager fallback.")
+            L = C.CDLL(LIB_PATH)
+            for name, args in PROTOTYPES.items():
+                fn = getattr(L, name)  # AttributeError if the symbol is missing
+                fn.argtypes = args
+                fn.restype = C.c_char_p if name == "m2f_last_error" else C.c_int
+            _lib = L
+    return _lib
+
+
+def check(rc: int, what: str = "") -> None:
+    if rc != M2F_OK:
+        msg = lib().m2f_last_error()
+        raise RuntimeError(f"libm2f_b200 {what} failed (code {rc}): {msg.decode() if msg else '?'}")

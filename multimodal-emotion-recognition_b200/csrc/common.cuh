@@ -1,0 +1,187 @@
+// Shared device/host helpers for the M2FNet sm_100a kernels.
+#pragma once
+#include <cuda.h>
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../../include/m2f_b200.h"
+
+namespace m2f {
+
+// ------------------------------------------------------------------ error plumbing (host)
+void set_error(const char* fmt, ...);
+int cuda_fail(cudaError_t e, const char* what, const char* file, int line);
+
+#define M2F_CUDA(expr)                                                              \
+    do {                                                                            \
+        cudaError_t _e = (expr);                                                    \
+        if (_e != cudaSuccess) return ::m2f::cuda_fail(_e, #expr, __FILE__, __LINE__); \
+    } while (0)
+
+#define M2F_REQUIRE(cond, code, ...)              \
+    do {                                          \
+        if (!(cond)) {                            \
+            ::m2f::set_error(__VA_ARGS__);        \
+            return (code);                        \
+        }                                         \
+    } while (0)
+
+#define M2F_TRY(expr)               \
+    do {                            \
+        int _r = (expr);            \
+        if (_r != M2F_OK) return _r; \
+    } while (0)
+
+// after a kernel launch: catches bad launch configurations without synchronising
+#define M2F_LAUNCH_CHECK() M2F_CUDA(cudaPeekAtLastError())
+
+int check_planes(const m2f_planes_t* t, const char* name, int vec);
+
+static inline int ceil_div(int a, int b) { return (a + b - 1) / b; }
+static inline int64_t round_up(int64_t a, int64_t b) { return (a + b - 1) / b * b; }
+
+// ------------------------------------------------------------------ Philox4x32-10
+// Counter layout: (idx4_lo, idx4_hi, site, step_lo) ; key: (seed_lo, seed_hi ^ step_hi).
+// One call yields the four keep/drop decisions of elements 4*idx4 .. 4*idx4+3 of a site.
+struct Philox {
+    uint32_t k0, k1, site, step;
+};
+
+__host__ __device__ __forceinline__ Philox philox_make(uint64_t seed, uint64_t step, uint32_t site) {
+    Philox p;
+    p.k0 = (uint32_t)seed;
+    p.k1 = (uint32_t)(seed >> 32) ^ (uint32_t)(step >> 32);
+    p.site = site;
+    p.step = (uint32_t)step;
+    return p;
+}
+
+__host__ __device__ __forceinline__ void philox4(const Philox& p, uint64_t idx4, uint32_t out[4]) {
+    uint32_t c0 = (uint32_t)idx4, c1 = (uint32_t)(idx4 >> 32), c2 = p.site, c3 = p.step;
+    uint32_t k0 = p.k0, k1 = p.k1;
+#pragma unroll
+    for (int r = 0; r < 10; ++r) {
+        const uint64_t p0 = (uint64_t)0xD2511F53u * c0;
+        const uint64_t p1 = (uint64_t)0xCD9E8D57u * c2;
+        const uint32_t n0 = (uint32_t)(p1 >> 32) ^ c1 ^ k0;
+        const uint32_t n2 = (uint32_t)(p0 >> 32) ^ c3 ^ k1;
+        c1 = (uint32_t)p1;
+        c3 = (uint32_t)p0;
+        c0 = n0;
+        c2 = n2;
+        k0 += 0x9E3779B9u;
+        k1 += 0xBB67AE85u;
+    }
+    out[0] = c0; out[1] = c1; out[2] = c2; out[3] = c3;
+}
+
+// keep iff r >= thresh where thresh = round(p * 2^32)  (P(keep) = 1 - p)
+__host__ __device__ __forceinline__ uint32_t drop_threshold(float p) {
+    double t = (double)p * 4294967296.0;
+    if (t <= 0.0) return 0u;
+    if (t >= 4294967295.0) return 0xFFFFFFFFu;
+    return (uint32_t)t;
+}
+
+// Dropout descriptor passed by value into kernels.  p == 0 => disabled.
+struct Drop {
+    Philox ph;
+    uint32_t thresh;
+    float scale;  // 1 / (1 - p)
+    int enabled;
+};
+
+__host__ __device__ __forceinline__ Drop drop_make(float p, uint64_t seed, uint64_t step, uint32_t site) {
+    Drop d;
+    d.ph = philox_make(seed, step, site);
+    d.thresh = drop_threshold(p);
+    d.scale = p < 1.f ? 1.f / (1.f - p) : 0.f;
+    d.enabled = p > 0.f;
+    return d;
+}
+
+// multiplier (0 or scale) for the single element `idx` (slow path: one Philox per element)
+__device__ __forceinline__ float drop_mult1(const Drop& d, uint64_t idx) {
+    uint32_t r[4];
+    philox4(d.ph, idx >> 2, r);
+    return r[idx & 3] >= d.thresh ? d.scale : 0.f;
+}
+
+// multipliers for the aligned group of four elements 4*idx4 .. 4*idx4+3
+__device__ __forceinline__ void drop_mult4(const Drop& d, uint64_t idx4, float m[4]) {
+    uint32_t r[4];
+    philox4(d.ph, idx4, r);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) m[i] = r[i] >= d.thresh ? d.scale : 0.f;
+}
+
+// ------------------------------------------------------------------ bf16 planes
+// A value v is stored as P bf16 planes hi, mid, lo with hi + mid + lo ~= v (P = 1: plain bf16,
+// P = 3: ~24 mantissa bits, the fp32-accurate mode).  Plane p lives at base + p * plane_stride.
+__device__ __forceinline__ void split_planes(float v, int P, __nv_bfloat16 out[3]) {
+    out[0] = __float2bfloat16_rn(v);
+    if (P > 1) {
+        float r = v - __bfloat162float(out[0]);
+        out[1] = __float2bfloat16_rn(r);
+        if (P > 2) {
+            r -= __bfloat162float(out[1]);
+            out[2] = __float2bfloat16_rn(r);
+        }
+    }
+}
+
+__device__ __forceinline__ void store_planes(__nv_bfloat16* base, int64_t plane_stride, int P, int64_t idx, float v) {
+    __nv_bfloat16 h[3];
+    split_planes(v, P, h);
+    base[idx] = h[0];
+    if (P > 1) base[plane_stride + idx] = h[1];
+    if (P > 2) base[2 * plane_stride + idx] = h[2];
+}
+
+__device__ __forceinline__ float load_planes(const __nv_bfloat16* base, int64_t plane_stride, int P, int64_t idx) {
+    float v = __bfloat162float(base[idx]);
+    if (P > 1) v += __bfloat162float(base[plane_stride + idx]);
+    if (P > 2) v += __bfloat162float(base[2 * plane_stride + idx]);
+    return v;
+}
+
+// four consecutive elements (idx multiple of 4, 8-byte aligned rows)
+__device__ __forceinline__ void load_planes4(const __nv_bfloat16* base, int64_t plane_stride, int P, int64_t idx, float v[4]) {
+    v[0] = v[1] = v[2] = v[3] = 0.f;
+    for (int p = P - 1; p >= 0; --p) {  // small terms first
+        const uint2 raw = *reinterpret_cast<const uint2*>(base + p * plane_stride + idx);
+        const __nv_bfloat162 a = *reinterpret_cast<const __nv_bfloat162*>(&raw.x);
+        const __nv_bfloat162 b = *reinterpret_cast<const __nv_bfloat162*>(&raw.y);
+        v[0] += __low2float(a); v[1] += __high2float(a);
+        v[2] += __low2float(b); v[3] += __high2float(b);
+    }
+}
+
+__device__ __forceinline__ void store_planes4(__nv_bfloat16* base, int64_t plane_stride, int P, int64_t idx, const float v[4]) {
+    __nv_bfloat16 h[4][3];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) split_planes(v[i], P, h[i]);
+    for (int p = 0; p < P; ++p) {
+        __nv_bfloat162 a = __halves2bfloat162(h[0][p], h[1][p]);
+        __nv_bfloat162 b = __halves2bfloat162(h[2][p], h[3][p]);
+        uint2 raw;
+        raw.x = *reinterpret_cast<uint32_t*>(&a);
+        raw.y = *reinterpret_cast<uint32_t*>(&b);
+        *reinterpret_cast<uint2*>(base + p * plane_stride + idx) = raw;
+    }
+}
+
+// ------------------------------------------------------------------ warp helpers
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+__device__ __forceinline__ float warp_max(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+    return v;
+}
+
+}  // namespace m2f

@@ -1,0 +1,245 @@
+// K3: LayerNorm forward / backward with fused residual (outer skip), dropout-mask regeneration,
+// bf16-plane operand copies and bias / gamma / beta gradient column sums.
+// Reference arithmetic: nn.LayerNorm(eps=1e-5, biased variance) as used by
+// nn.TransformerEncoderLayer norm1/norm2 (torch/nn/modules/transformer.py:977-982), the shared final norm
+// of nn.TransformerEncoder (:550-551) and the outer skip of src/model.py:107,119.
+// One warp per row; a row of D <= 1024 fp32 lives in registers (NCH float4 chunks per lane).
+#include "common.cuh"
+
+namespace m2f {
+
+constexpr float LN_EPS = 1e-5f;
+constexpr int LN_THREADS = 128;
+constexpr int LN_WARPS = LN_THREADS / 32;
+
+template <int NCH>
+__global__ void __launch_bounds__(LN_THREADS)
+ln_fwd_kernel(const float* __restrict__ x, int64_t x_ld, const float* __restrict__ gamma, const float* __restrict__ beta,
+              const float* __restrict__ skip, int64_t skip_ld, int64_t M, int D, float* __restrict__ y, int64_t y_ld,
+              __nv_bfloat16* __restrict__ ypl, int64_t ypl_ld, int64_t ypl_stride, int P, Drop drop, float* __restrict__ stats) {
+    const int lane = threadIdx.x & 31;
+    const int64_t warp0 = (int64_t)blockIdx.x * LN_WARPS + (threadIdx.x >> 5);
+    const int64_t nwarps = (int64_t)gridDim.x * LN_WARPS;
+    const float invD = 1.f / (float)D;
+    for (int64_t m = warp0; m < M; m += nwarps) {
+        float4 v[NCH];
+        float s = 0.f;
+#pragma unroll
+        for (int c = 0; c < NCH; ++c) {
+            const int col = (c * 32 + lane) * 4;
+            v[c] = col < D ? *reinterpret_cast<const float4*>(x + m * x_ld + col) : make_float4(0.f, 0.f, 0.f, 0.f);
+            s += v[c].x + v[c].y + v[c].z + v[c].w;
+        }
+        const float mean = warp_sum(s) * invD;
+        float q = 0.f;
+#pragma unroll
+        for (int c = 0; c < NCH; ++c) {
+            const int col = (c * 32 + lane) * 4;
+            if (col < D) {
+                const float a = v[c].x - mean, b = v[c].y - mean, cc = v[c].z - mean, d = v[c].w - mean;
+                q += a * a + b * b + cc * cc + d * d;
+            }
+        }
+        const float rstd = rsqrtf(warp_sum(q) * invD + LN_EPS);
+        if (lane == 0 && stats) {
+            stats[2 * m] = mean;
+            stats[2 * m + 1] = rstd;
+        }
+#pragma unroll
+        for (int c = 0; c < NCH; ++c) {
+            const int col = (c * 32 + lane) * 4;
+            if (col < D) {
+                const float4 g = *reinterpret_cast<const float4*>(gamma + col);
+                const float4 b = *reinterpret_cast<const float4*>(beta + col);
+                float o[4] = {(v[c].x - mean) * rstd * g.x + b.x, (v[c].y - mean) * rstd * g.y + b.y,
+                              (v[c].z - mean) * rstd * g.z + b.z, (v[c].w - mean) * rstd * g.w + b.w};
+                if (skip) {
+                    const float4 k = *reinterpret_cast<const float4*>(skip + m * skip_ld + col);
+                    o[0] += k.x; o[1] += k.y; o[2] += k.z; o[3] += k.w;
+                }
+                if (y) *reinterpret_cast<float4*>(y + m * y_ld + col) = make_float4(o[0], o[1], o[2], o[3]);
+                if (ypl) {
+                    if (drop.enabled) {
+                        float dm[4];
+                        drop_mult4(drop, (uint64_t)(m * D + col) >> 2, dm);
+#pragma unroll
+                        for (int i = 0; i < 4; ++i) o[i] *= dm[i];
+                    }
+                    store_planes4(ypl, ypl_stride, P, m * ypl_ld + col, o);
+                }
+            }
+        }
+    }
+}
+
+// Backward.  Per-warp register partials of dgamma / dbeta / dbias over the rows the warp owns, reduced
+// across the block's warps in shared memory, then one atomicAdd per column per block.
+template <int NCH>
+__global__ void __launch_bounds__(LN_THREADS)
+ln_bwd_kernel(const float* __restrict__ g, int64_t g_ld, const float* __restrict__ x, int64_t x_ld,
+              const float* __restrict__ gamma, const float* __restrict__ stats, int64_t M, int D, float* __restrict__ dx,
+              int64_t dx_ld, __nv_bfloat16* __restrict__ dxpl, int64_t dxpl_ld, int64_t dxpl_stride, int P, Drop drop,
+              float* __restrict__ dgamma, float* __restrict__ dbeta, float* __restrict__ dbias) {
+    __shared__ float red[LN_WARPS][3][32 * 4 + 4];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int64_t warp0 = (int64_t)blockIdx.x * LN_WARPS + warp;
+    const int64_t nwarps = (int64_t)gridDim.x * LN_WARPS;
+    const float invD = 1.f / (float)D;
+    float4 gm[NCH], pg[NCH], pb[NCH], pbias[NCH];
+#pragma unroll
+    for (int c = 0; c < NCH; ++c) {
+        const int col = (c * 32 + lane) * 4;
+        gm[c] = col < D ? *reinterpret_cast<const float4*>(gamma + col) : make_float4(0.f, 0.f, 0.f, 0.f);
+        pg[c] = pb[c] = pbias[c] = make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+    for (int64_t m = warp0; m < M; m += nwarps) {
+        const float mean = stats[2 * m], rstd = stats[2 * m + 1];
+        float4 xh[NCH], a[NCH];
+        float s1 = 0.f, s2 = 0.f;
+#pragma unroll
+        for (int c = 0; c < NCH; ++c) {
+            const int col = (c * 32 + lane) * 4;
+            if (col < D) {
+                const float4 xv = *reinterpret_cast<const float4*>(x + m * x_ld + col);
+                const float4 gv = *reinterpret_cast<const float4*>(g + m * g_ld + col);
+                xh[c] = make_float4((xv.x - mean) * rstd, (xv.y - mean) * rstd, (xv.z - mean) * rstd, (xv.w - mean) * rstd);
+                a[c] = make_float4(gv.x * gm[c].x, gv.y * gm[c].y, gv.z * gm[c].z, gv.w * gm[c].w);
+                s1 += a[c].x + a[c].y + a[c].z + a[c].w;
+                s2 += a[c].x * xh[c].x + a[c].y * xh[c].y + a[c].z * xh[c].z + a[c].w * xh[c].w;
+                pg[c].x += gv.x * xh[c].x; pg[c].y += gv.y * xh[c].y; pg[c].z += gv.z * xh[c].z; pg[c].w += gv.w * xh[c].w;
+                pb[c].x += gv.x; pb[c].y += gv.y; pb[c].z += gv.z; pb[c].w += gv.w;
+            } else {
+                xh[c] = a[c] = make_float4(0.f, 0.f, 0.f, 0.f);
+            }
+        }
+        const float c1 = warp_sum(s1) * invD, c2 = warp_sum(s2) * invD;
+#pragma unroll
+        for (int c = 0; c < NCH; ++c) {
+            const int col = (c * 32 + lane) * 4;
+            if (col < D) {
+                float o[4] = {rstd * (a[c].x - c1 - xh[c].x * c2), rstd * (a[c].y - c1 - xh[c].y * c2),
+                              rstd * (a[c].z - c1 - xh[c].z * c2), rstd * (a[c].w - c1 - xh[c].w * c2)};
+                if (dx) *reinterpret_cast<float4*>(dx + m * dx_ld + col) = make_float4(o[0], o[1], o[2], o[3]);
+                if (drop.enabled) {
+                    float dm[4];
+                    drop_mult4(drop, (uint64_t)(m * D + col) >> 2, dm);
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) o[i] *= dm[i];
+                }
+                if (dxpl) store_planes4(dxpl, dxpl_stride, P, m * dxpl_ld + col, o);
+                pbias[c].x += o[0]; pbias[c].y += o[1]; pbias[c].z += o[2]; pbias[c].w += o[3];
+            }
+        }
+    }
+    // block reduction, one 128-column chunk at a time
+#pragma unroll
+    for (int c = 0; c < NCH; ++c) {
+        if (c * 128 >= D) break;
+        __syncthreads();
+        *reinterpret_cast<float4*>(&red[warp][0][lane * 4]) = pg[c];
+        *reinterpret_cast<float4*>(&red[warp][1][lane * 4]) = pb[c];
+        *reinterpret_cast<float4*>(&red[warp][2][lane * 4]) = pbias[c];
+        __syncthreads();
+        for (int i = threadIdx.x; i < 3 * 128; i += LN_THREADS) {
+            const int which = i / 128, j = i - which * 128;
+            const int col = c * 128 + j;
+            float* dst = which == 0 ? dgamma : (which == 1 ? dbeta : dbias);
+            if (col < D && dst) {
+                float s = 0.f;
+#pragma unroll
+                for (int w = 0; w < LN_WARPS; ++w) s += red[w][which][j];
+                atomicAdd(dst + col, s);
+            }
+        }
+    }
+}
+
+static int ln_grid(int64_t M, int rows_per_warp) {
+    int64_t blocks = (M + LN_WARPS * rows_per_warp - 1) / (LN_WARPS * rows_per_warp);
+    if (blocks > 148 * 4) blocks = 148 * 4;
+    return blocks < 1 ? 1 : (int)blocks;
+}
+
+static int ln_check(const void* x, int64_t x_ld, int64_t M, int64_t D, const char* who) {
+    M2F_REQUIRE(x != nullptr && M > 0 && D > 0, M2F_ERR_ARG, "%s: bad argument", who);
+    M2F_REQUIRE(D <= 1024 && (D % 4) == 0, M2F_ERR_UNSUPPORTED, "%s: D = %lld unsupported (need D %% 4 == 0 and D <= 1024)", who, (long long)D);
+    M2F_REQUIRE((x_ld % 4) == 0 && (reinterpret_cast<uintptr_t>(x) % 16) == 0, M2F_ERR_ALIGN, "%s: rows must be 16-byte aligned", who);
+    return M2F_OK;
+}
+
+#define M2F_LN_DISPATCH(D, CALL)                              \
+    do {                                                      \
+        const int nch_ = (int)((D + 127) / 128);              \
+        switch (nch_) {                                       \
+            case 1: { constexpr int NCH = 1; CALL; } break;   \
+            case 2: { constexpr int NCH = 2; CALL; } break;   \
+            case 3: { constexpr int NCH = 3; CALL; } break;   \
+            case 4: { constexpr int NCH = 4; CALL; } break;   \
+            case 5: { constexpr int NCH = 5; CALL; } break;   \
+            case 6: { constexpr int NCH = 6; CALL; } break;   \
+            case 7: { constexpr int NCH = 7; CALL; } break;   \
+            default: { constexpr int NCH = 8; CALL; } break;  \
+        }                                                     \
+    } while (0)
+
+}  // namespace m2f
+
+using namespace m2f;
+
+extern "C" int m2f_ln_fwd(const float* x, int64_t x_ld, const float* gamma, const float* beta, const float* skip, int64_t skip_ld,
+                          int64_t M, int64_t D, float* y_f32, int64_t y_ld, const m2f_planes_t* y_planes, float drop_p, uint64_t seed,
+                          uint64_t step, uint32_t site, float* stats, void* stream) {
+    M2F_TRY(ln_check(x, x_ld, M, D, "ln_fwd"));
+    M2F_REQUIRE(gamma && beta, M2F_ERR_ARG, "ln_fwd: null gamma/beta");
+    M2F_REQUIRE((reinterpret_cast<uintptr_t>(gamma) % 16) == 0 && (reinterpret_cast<uintptr_t>(beta) % 16) == 0, M2F_ERR_ALIGN,
+                "ln_fwd: gamma/beta must be 16-byte aligned");
+    M2F_REQUIRE(!skip || ((skip_ld % 4) == 0 && (reinterpret_cast<uintptr_t>(skip) % 16) == 0), M2F_ERR_ALIGN, "ln_fwd: skip alignment");
+    M2F_REQUIRE(!y_f32 || ((y_ld % 4) == 0 && (reinterpret_cast<uintptr_t>(y_f32) % 16) == 0), M2F_ERR_ALIGN, "ln_fwd: y alignment");
+    M2F_REQUIRE(drop_p >= 0.f && drop_p < 1.f, M2F_ERR_ARG, "ln_fwd: dropout p must be in [0,1)");
+    __nv_bfloat16* ypl = nullptr;
+    int64_t ypl_ld = 0, ypl_stride = 0;
+    int P = 1;
+    if (y_planes && y_planes->ptr) {
+        M2F_TRY(check_planes(y_planes, "ln_fwd y_planes", 4));
+        M2F_REQUIRE(y_planes->rows >= M && y_planes->cols == D, M2F_ERR_ARG, "ln_fwd: y_planes extent mismatch");
+        ypl = reinterpret_cast<__nv_bfloat16*>(y_planes->ptr);
+        ypl_ld = y_planes->ld;
+        ypl_stride = y_planes->plane_stride;
+        P = y_planes->planes;
+    }
+    M2F_REQUIRE(y_f32 || ypl, M2F_ERR_ARG, "ln_fwd: no output given");
+    const Drop drop = drop_make(drop_p, seed, step, site);
+    auto st = reinterpret_cast<cudaStream_t>(stream);
+    M2F_LN_DISPATCH(D, (ln_fwd_kernel<NCH><<<ln_grid(M, 1), LN_THREADS, 0, st>>>(x, x_ld, gamma, beta, skip, skip_ld, M, (int)D, y_f32, y_ld,
+                                                                                  ypl, ypl_ld, ypl_stride, P, drop, stats)));
+    M2F_LAUNCH_CHECK();
+    return M2F_OK;
+}
+
+extern "C" int m2f_ln_bwd(const float* g, int64_t g_ld, const float* x, int64_t x_ld, const float* gamma, const float* stats, int64_t M,
+                          int64_t D, float* dx_f32, int64_t dx_ld, const m2f_planes_t* dx_planes, float drop_p, uint64_t seed, uint64_t step,
+                          uint32_t site, float* dgamma, float* dbeta, float* dbias, void* stream) {
+    M2F_TRY(ln_check(x, x_ld, M, D, "ln_bwd"));
+    M2F_TRY(ln_check(g, g_ld, M, D, "ln_bwd"));
+    M2F_REQUIRE(gamma && stats, M2F_ERR_ARG, "ln_bwd: null gamma/stats");
+    M2F_REQUIRE((reinterpret_cast<uintptr_t>(gamma) % 16) == 0, M2F_ERR_ALIGN, "ln_bwd: gamma must be 16-byte aligned");
+    M2F_REQUIRE(!dx_f32 || ((dx_ld % 4) == 0 && (reinterpret_cast<uintptr_t>(dx_f32) % 16) == 0), M2F_ERR_ALIGN, "ln_bwd: dx alignment");
+    M2F_REQUIRE(drop_p >= 0.f && drop_p < 1.f, M2F_ERR_ARG, "ln_bwd: dropout p must be in [0,1)");
+    __nv_bfloat16* dpl = nullptr;
+    int64_t dpl_ld = 0, dpl_stride = 0;
+    int P = 1;
+    if (dx_planes && dx_planes->ptr) {
+        M2F_TRY(check_planes(dx_planes, "ln_bwd dx_planes", 4));
+        M2F_REQUIRE(dx_planes->rows >= M && dx_planes->cols == D, M2F_ERR_ARG, "ln_bwd: dx_planes extent mismatch");
+        dpl = reinterpret_cast<__nv_bfloat16*>(dx_planes->ptr);
+        dpl_ld = dx_planes->ld;
+        dpl_stride = dx_planes->plane_stride;
+        P = dx_planes->planes;
+    }
+    const Drop drop = drop_make(drop_p, seed, step, site);
+    auto st = reinterpret_cast<cudaStream_t>(stream);
+    M2F_LN_DISPATCH(D, (ln_bwd_kernel<NCH><<<ln_grid(M, 4), LN_THREADS, 0, st>>>(g, g_ld, x, x_ld, gamma, stats, M, (int)D, dx_f32, dx_ld, dpl,
+                                                                                  dpl_ld, dpl_stride, P, drop, dgamma, dbeta, dbias)));
+    M2F_LAUNCH_CHECK();
+    return M2F_OK;
+}
