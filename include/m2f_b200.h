@@ -146,6 +146,66 @@ int m2f_ce_fwd_bwd(const float* logits, int64_t ld, const int64_t* target, const
                    int64_t M, int32_t C, float eps, float grad_scale, float* loss_out,
                    float* dlogits, int64_t dl_ld, const m2f_planes_t* dl_planes, void* stream);
 
+
+/* ---- model-level API: the whole M2FNet forward / backward as one call each ------------------------------
+ * m2f_model_cfg_t mirrors the `model:` block of src/config.yaml:31-56 (what M2FNet.__init__ reads,
+ * src/model.py:24-56) plus the build-side knobs (planes, ffn_dim = nn.TransformerEncoderLayer's default 2048). */
+typedef struct {
+    int32_t enabled, dim, n_head, n_transformers, n_layers;
+} m2f_modality_cfg_t;
+
+typedef struct {
+    m2f_modality_cfg_t audio, text;
+    int32_t fam_enabled, fam_dim, fam_heads, fam_layers;
+    int32_t cls_hidden, cls_out, cls_layers;
+    float dropout;
+    int32_t ffn_dim;
+    int32_t planes; /* 1 = bf16 throughput mode, 3 = fp32-parity mode (2 = 16-bit mantissa) */
+} m2f_model_cfg_t;
+
+typedef struct m2f_model m2f_model_t;
+typedef struct m2f_plan m2f_plan_t;
+
+/* Parameter layout (host only; works without a GPU).  All parameters live in ONE fp32 arena: 2-D weights
+ * first, then every 1-D tensor from m2f_model_arena_1d_offset() on.  Names are the reference state_dict
+ * names; the shared final norm appears once, as `{m}_encoders.0.norm.*`.
+ * Invalid enable-flag combinations return M2F_ERR_ARG with the reference's message (src/model.py:32-35). */
+int m2f_model_create(const m2f_model_cfg_t* cfg, m2f_model_t** out);
+int m2f_model_destroy(m2f_model_t* m);
+int64_t m2f_model_num_params(const m2f_model_t* m);
+/* cols == 0: 1-D tensor of length rows.  offset in floats from the arena base. */
+int m2f_model_param_info(const m2f_model_t* m, int64_t i, char* name_buf, int32_t name_buf_len, int64_t* offset,
+                         int64_t* rows, int64_t* cols);
+int64_t m2f_model_arena_floats(const m2f_model_t* m);
+int64_t m2f_model_arena_1d_offset(const m2f_model_t* m);
+/* bf16-plane shadow copy of the 2-D weights (GEMM B operands, TMA-readable) + fused bias copies */
+int64_t m2f_model_shadow_bytes(const m2f_model_t* m);
+int m2f_model_refresh_shadow(const m2f_model_t* m, const float* params, void* shadow, void* stream);
+
+/* A plan fixes the batch geometry (B dialogues x S padded utterances) and owns the workspace layout and the
+ * cached TMA descriptors.  training_plan = 1 keeps every activation the backward needs. */
+int m2f_plan_create(m2f_model_t* m, int64_t B, int64_t S, int32_t training_plan, m2f_plan_t** out);
+int m2f_plan_destroy(m2f_plan_t* p);
+int64_t m2f_plan_workspace_bytes(const m2f_plan_t* p);
+/* M2FNet.forward (src/model.py:102-145).  text [B,S,Dt] / audio [B,S,Da] fp32 contiguous, key_pad uint8 [B,S]
+ * (1 = padding), logits fp32 [B,S,C] contiguous.  dropout_on = model.training (p from the config). */
+int m2f_plan_forward(m2f_plan_t* p, const float* params, const void* shadow, void* workspace, const float* text,
+                     const float* audio, const uint8_t* key_pad, int32_t dropout_on, uint64_t seed, uint64_t step,
+                     float* logits, void* stream);
+/* Fused criterion on the logits of the last forward (src/train.py:48-50,229): writes loss_out[0..3] and keeps
+ * grad_scale * dL/dlogits in the workspace for m2f_plan_backward(dlogits = NULL). */
+int m2f_plan_loss(m2f_plan_t* p, void* workspace, const float* logits, const int64_t* target, const float* class_w,
+                  float eps, float grad_scale, float* loss_out, void* stream);
+/* Backward of the last forward.  dlogits fp32 [B,S,C] (from autograd) or NULL (use m2f_plan_loss's).
+ * Every parameter gradient is WRITTEN (not accumulated) into the fp32 arena `grads` (same layout as params). */
+int m2f_plan_backward(m2f_plan_t* p, const float* params, const void* shadow, void* workspace, const float* dlogits,
+                      float* grads, void* stream);
+
+/* Adam with L2 weight decay folded into the gradient (torch.optim.Adam semantics, src/train.py:56,231), one
+ * launch over the arena; `t` is the 1-based step count.  grad_scale multiplies g first (DDP averaging). */
+int m2f_adam_step(float* params, const float* grads, float* exp_avg, float* exp_avg_sq, int64_t n, float lr,
+                  float beta1, float beta2, float eps, float weight_decay, int64_t t, float grad_scale, void* stream);
+
 /* test helper: mask[i] = 1 if element i of `site` is kept, for i in [0, n) */
 int m2f_dropout_mask(float p, uint64_t seed, uint64_t step, uint32_t site, int64_t n, uint8_t* mask,
                      void* stream);

@@ -14,41 +14,10 @@
 #include <mutex>
 
 #include "common.cuh"
+#include "gemm.cuh"
 #include "ptx.cuh"
 
 namespace m2f {
-
-constexpr int BLOCK_M = 128;
-constexpr int BLOCK_K = 64;  // one 128-byte swizzle atom of bf16
-constexpr int UMMA_K = 16;
-constexpr int MAX_SEGS = 4;
-constexpr int MAX_PROD = 6;
-constexpr int GEMM_THREADS = 192;
-
-struct GemmParams {
-    int M, N;
-    int nsegs;
-    int seg_a_k0[MAX_SEGS], seg_b_k0[MAX_SEGS], seg_nkb[MAX_SEGS];
-    int nprod;
-    int prod_a[MAX_PROD], prod_b[MAX_PROD];
-    int total_kb;
-    // epilogue
-    const float* bias;
-    int relu;
-    int accumulate;
-    const __nv_bfloat16* gate;
-    int64_t gate_ld;
-    float gate_scale;
-    Drop drop;
-    int64_t drop_ld;
-    const float* resid;
-    int64_t resid_ld;
-    float* out_f32;
-    int64_t out_f32_ld;
-    __nv_bfloat16* out_pl;
-    int64_t out_pl_ld, out_pl_stride;
-    int out_pl_n;
-};
 
 template <int BLOCK_N>
 struct GemmCfg {

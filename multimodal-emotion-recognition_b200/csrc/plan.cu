@@ -1,0 +1,991 @@
+// Model-level executor: the whole M2FNet forward (src/model.py:102-145) and its backward as one C call each.
+//
+// Host-side only (no kernels here except the shadow refresh): it owns the parameter-arena layout, the
+// bf16-plane shadow copy of the weights, the per-(B,S) workspace layout and a cache of TMA descriptors,
+// and enqueues the kernels of gemm_sm100.cu / attention.cu / layernorm.cu / loss.cu on the caller's stream.
+//
+// Data flow (M = B*S rows, kept [B,S,D] row-major end to end -- the reference's permutes,
+// head split/merge copies and torch.cat calls never materialise):
+//   * the residual stream, LayerNorm inputs and every gradient w.r.t. the residual stream stay fp32;
+//   * everything a GEMM reads (activations and the weight shadow) is bf16 planes (P = 1 or 3);
+//   * concat operands are column halves of one buffer (fusion `u_i`, classifier input `zc`).
+#include <string>
+#include <unordered_map>
+#include <vector>
+
+#include "common.cuh"
+#include "gemm.cuh"
+
+namespace m2f {
+
+// ------------------------------------------------------------------------------------------ layout types
+enum Base { WS = 0, SHADOW = 1 };
+
+struct Buf {  // a matrix inside the workspace or the shadow, by byte offset
+    int64_t off = -1;
+    int64_t rows = 0, cols = 0, ld = 0, stride = 0;
+    int planes = 0;  // 0: fp32
+    Base base = WS;
+};
+
+struct ParamInfo {
+    std::string name;
+    int64_t off, rows, cols;
+};
+
+struct Lin {       // one nn.Linear (or a fused group of in-projection rows)
+    Buf w;         // shadow planes [out, in]
+    int64_t w_off; // arena offset of the fp32 weight (gradient destination)
+    int64_t b_off; // arena offset of the fp32 bias
+    int out, in;
+};
+
+struct EncLayer {
+    Lin qkv, wo, w1, w2;
+    int64_t g1, be1, g2, be2;  // LayerNorm weight / bias arena offsets
+    // saved activations
+    Buf qkv_pl, o_pl, y1, st1, x1, x1_pl, h_pl, y2, st2, x2, x2_pl;
+};
+
+struct Modality {
+    int enabled = 0, idx = 0, D = 0, H = 0, T = 0, L = 0;
+    std::vector<EncLayer> layers;  // T * L
+    int64_t gf = 0, bef = 0;       // shared final norm
+    Lin proj;
+    Buf in_pl;                     // planes of the raw input
+    std::vector<Buf> xout, xout_pl, stf;  // per transformer: x_t (fp32), its planes, final-norm stats
+};
+
+struct FusionLayer {
+    Lin qv, wo, lin;  // qv: rows [Wq; Wv] of in_proj_weight fused in the shadow
+    int64_t inw_off, inb_off;  // arena offsets of in_proj_weight / in_proj_bias
+    Buf bqv;                   // fp32 shadow copy [bq; bv]
+    Buf qv_pl, xo_pl, u_pl;    // saved: [q | v], attention output, relu([x | t])
+};
+
+struct SEntry {  // shadow refresh work item
+    int64_t src_off;
+    int rows, cols, src_ld;
+    int64_t dst_off;
+    int dst_ld;
+    int64_t stride;
+    int planes;  // 0: fp32 copy
+};
+
+}  // namespace m2f
+
+using namespace m2f;
+
+struct m2f_model {
+    m2f_model_cfg_t cfg;
+    std::vector<ParamInfo> params;
+    int64_t arena_floats = 0, off_1d = 0;
+    int64_t shadow_bytes = 0;
+    std::vector<SEntry> sentries;
+    Modality mod[2];
+    std::vector<FusionLayer> fam;
+    Lin wk_all;   // fused K projections of all fusion layers [F*Df, Df]
+    Buf bk_all;   // fp32 shadow copy of their biases
+    std::vector<Lin> cls;
+    int Df = 0, cls_in = 0;
+    bool both = false;
+
+    int64_t add_param(const std::string& name, int64_t rows, int64_t cols, int64_t& cursor) {
+        cursor = round_up(cursor, 4);
+        params.push_back({name, cursor, rows, cols});
+        const int64_t off = cursor;
+        cursor += rows * (cols ? cols : 1);
+        return off;
+    }
+    Buf add_shadow_planes(int64_t src_off, int rows, int cols, int src_ld) {
+        Buf b;
+        b.base = SHADOW;
+        b.rows = rows;
+        b.cols = cols;
+        b.ld = round_up(cols, 8);
+        b.stride = round_up((int64_t)rows * b.ld, 8);
+        b.planes = cfg.planes;
+        shadow_bytes = round_up(shadow_bytes, 256);
+        b.off = shadow_bytes;
+        shadow_bytes += b.stride * 2 * cfg.planes;
+        sentries.push_back({src_off, rows, cols, src_ld, b.off, (int)b.ld, b.stride, cfg.planes});
+        return b;
+    }
+    // rows appended to an existing shadow matrix (fused projections)
+    void add_shadow_rows(const Buf& dst, int row0, int64_t src_off, int rows, int cols, int src_ld) {
+        sentries.push_back({src_off, rows, cols, src_ld, dst.off + (int64_t)row0 * dst.ld * 2, (int)dst.ld, dst.stride, cfg.planes});
+    }
+    Buf alloc_shadow_planes(int rows, int cols) {
+        Buf b;
+        b.base = SHADOW;
+        b.rows = rows;
+        b.cols = cols;
+        b.ld = round_up(cols, 8);
+        b.stride = round_up((int64_t)rows * b.ld, 8);
+        b.planes = cfg.planes;
+        shadow_bytes = round_up(shadow_bytes, 256);
+        b.off = shadow_bytes;
+        shadow_bytes += b.stride * 2 * cfg.planes;
+        return b;
+    }
+    Buf alloc_shadow_f32(int n) {
+        Buf b;
+        b.base = SHADOW;
+        b.rows = 1;
+        b.cols = n;
+        b.ld = n;
+        b.planes = 0;
+        shadow_bytes = round_up(shadow_bytes, 256);
+        b.off = shadow_bytes;
+        shadow_bytes += (int64_t)n * 4;
+        return b;
+    }
+    void add_shadow_f32(const Buf& dst, int col0, int64_t src_off, int n) {
+        sentries.push_back({src_off, 1, n, n, dst.off + (int64_t)col0 * 4, n, 0, 0});
+    }
+};
+
+struct TmapKey {
+    const void* ptr;
+    int64_t rows, cols, ld, stride;
+    int planes, box_rows;
+    bool operator==(const TmapKey& o) const {
+        return ptr == o.ptr && rows == o.rows && cols == o.cols && ld == o.ld && stride == o.stride && planes == o.planes &&
+               box_rows == o.box_rows;
+    }
+};
+struct TmapKeyHash {
+    size_t operator()(const TmapKey& k) const {
+        size_t h = reinterpret_cast<size_t>(k.ptr);
+        h = h * 1000003u ^ (size_t)k.rows;
+        h = h * 1000003u ^ (size_t)k.cols;
+        h = h * 1000003u ^ (size_t)k.ld;
+        h = h * 1000003u ^ (size_t)(k.planes * 1024 + k.box_rows);
+        return h;
+    }
+};
+
+struct m2f_plan {
+    m2f_model* m;
+    int64_t B, S, M;
+    int training;
+    int64_t ws_bytes = 0;
+    // per-plan copies of the model's layer tables (their activation Bufs are plan-specific)
+    Modality mod[2];
+    std::vector<FusionLayer> fam;
+    // workspace buffers that are not per-layer
+    Buf key_pad;                            // uint8 [M] copy of the padding mask (re-read by the backward)
+    Buf zc_pl, t0_pl, kall_pl;
+    std::vector<Buf> cls_h;                 // classifier hidden activations
+    Buf dl_pl;                              // dlogits planes [M, 8-padded]
+    Buf logits_copy;                        // unused placeholder
+    // backward scratch
+    Buf gG, gA, gB;                         // fp32 [M, Dmax]
+    Buf dx_pl, dh_pl, do_pl, dqkv_pl;       // encoder backward operands
+    Buf dcls_a, dcls_b;                     // classifier hidden gradients (ping-pong)
+    Buf dz_pl, dz2_pl, dxo_pl, dattn_pl, dqv_pl, dkall_pl, dproj_pl, dprojt_pl, gt_f32, ga_f32;
+    // state of the last forward
+    float p_used = 0.f;
+    uint64_t seed = 0, step = 0;
+    bool have_loss_grad = false;
+    // descriptor cache
+    const void* bound_ws = nullptr;
+    const void* bound_shadow = nullptr;
+    std::unordered_map<TmapKey, CUtensorMap, TmapKeyHash> tmaps;
+
+    Buf alloc_pl(int64_t rows, int64_t cols, int planes) {
+        Buf b;
+        b.rows = rows;
+        b.cols = cols;
+        b.ld = round_up(cols, 8);
+        b.stride = round_up(rows * b.ld, 8);
+        b.planes = planes;
+        ws_bytes = round_up(ws_bytes, 256);
+        b.off = ws_bytes;
+        ws_bytes += b.stride * 2 * planes;
+        return b;
+    }
+    Buf alloc_f32(int64_t rows, int64_t cols) {
+        Buf b;
+        b.rows = rows;
+        b.cols = cols;
+        b.ld = round_up(cols, 4);
+        b.planes = 0;
+        ws_bytes = round_up(ws_bytes, 256);
+        b.off = ws_bytes;
+        ws_bytes += rows * b.ld * 4;
+        return b;
+    }
+};
+
+namespace m2f {
+
+// ------------------------------------------------------------------------------------------ model layout
+static std::string enc_prefix(const char* m, int t, int l) {
+    return std::string(m) + "_encoders." + std::to_string(t) + ".layers." + std::to_string(l) + ".";
+}
+
+static int build_model(m2f_model* md) {
+    const m2f_model_cfg_t& c = md->cfg;
+    // the reference's constructor checks (src/model.py:32-35), same messages
+    M2F_REQUIRE(c.audio.enabled || c.text.enabled, M2F_ERR_ARG, "At least one of audio and text must be enabled!");
+    M2F_REQUIRE(!c.fam_enabled || (c.audio.enabled && c.text.enabled), M2F_ERR_ARG,
+                "Fusion Attention Module can only be used with both audio and text enabled!");
+    M2F_REQUIRE(c.planes >= 1 && c.planes <= 3, M2F_ERR_ARG, "planes must be 1, 2 or 3");
+    M2F_REQUIRE(c.dropout >= 0.f && c.dropout < 1.f, M2F_ERR_ARG, "dropout must be in [0, 1)");
+    M2F_REQUIRE(c.ffn_dim > 0 && c.ffn_dim % 8 == 0, M2F_ERR_ARG, "ffn_dim must be a positive multiple of 8");
+    M2F_REQUIRE(c.fam_dim > 0 && c.fam_dim % 8 == 0, M2F_ERR_UNSUPPORTED, "FAM.embedding_size must be a positive multiple of 8");
+    M2F_REQUIRE(c.cls_hidden > 0 && c.cls_hidden % 8 == 0 && c.cls_out >= 1 && c.cls_out <= 32, M2F_ERR_UNSUPPORTED,
+                "CLASSIFIER: hidden_size must be a multiple of 8 and output_size in 1..32");
+    const m2f_modality_cfg_t* mc[2] = {&c.audio, &c.text};
+    const char* mname[2] = {"audio", "text"};
+    for (int i = 0; i < 2; ++i) {
+        if (!mc[i]->enabled) continue;
+        M2F_REQUIRE(mc[i]->dim > 0 && mc[i]->n_head > 0 && mc[i]->dim % mc[i]->n_head == 0, M2F_ERR_ARG,
+                    "embed_dim must be divisible by num_heads");  // torch's assertion text
+        M2F_REQUIRE(mc[i]->dim % 4 == 0 && mc[i]->dim <= 1024, M2F_ERR_UNSUPPORTED, "%s embedding_size must be a multiple of 4 and <= 1024",
+                    mname[i]);
+        M2F_REQUIRE(mc[i]->n_transformers >= 1 && mc[i]->n_transformers <= 15 && mc[i]->n_layers >= 1 && mc[i]->n_layers <= 16,
+                    M2F_ERR_UNSUPPORTED, "%s: n_transformers must be 1..15 and n_encoder_layers 1..16", mname[i]);
+    }
+    if (c.fam_enabled) {
+        M2F_REQUIRE(c.fam_heads > 0 && c.fam_dim % c.fam_heads == 0, M2F_ERR_ARG, "embed_dim must be divisible by num_heads");
+        M2F_REQUIRE(c.fam_layers >= 1 && c.fam_layers <= 255, M2F_ERR_UNSUPPORTED, "FAM.n_layers must be 1..255");
+        M2F_REQUIRE(c.fam_dim % 64 == 0, M2F_ERR_UNSUPPORTED, "FAM.embedding_size must be a multiple of 64 (concat K-segments)");
+    }
+    md->Df = c.fam_dim;
+    md->both = c.audio.enabled && c.text.enabled;
+    md->cls_in = md->both ? 2 * md->Df : md->Df;
+    const int FF = c.ffn_dim, Df = md->Df;
+
+    // ---- pass 1: 2-D weights
+    int64_t cur = 0;
+    for (int i = 0; i < 2; ++i) {
+        Modality& mo = md->mod[i];
+        mo.enabled = mc[i]->enabled;
+        mo.idx = i;
+        if (!mo.enabled) continue;
+        mo.D = mc[i]->dim; mo.H = mc[i]->n_head; mo.T = mc[i]->n_transformers; mo.L = mc[i]->n_layers;
+        const int D = mo.D;
+        mo.layers.resize((size_t)mo.T * mo.L);
+        for (int t = 0; t < mo.T; ++t)
+            for (int l = 0; l < mo.L; ++l) {
+                EncLayer& e = mo.layers[(size_t)t * mo.L + l];
+                const std::string P = enc_prefix(mname[i], t, l);
+                e.qkv.w_off = md->add_param(P + "self_attn.in_proj_weight", 3 * D, D, cur); e.qkv.out = 3 * D; e.qkv.in = D;
+                e.wo.w_off = md->add_param(P + "self_attn.out_proj.weight", D, D, cur);     e.wo.out = D; e.wo.in = D;
+                e.w1.w_off = md->add_param(P + "linear1.weight", FF, D, cur);               e.w1.out = FF; e.w1.in = D;
+                e.w2.w_off = md->add_param(P + "linear2.weight", D, FF, cur);               e.w2.out = D; e.w2.in = FF;
+            }
+        mo.proj.w_off = md->add_param(std::string(mname[i]) + "_proj.weight", Df, D, cur); mo.proj.out = Df; mo.proj.in = D;
+    }
+    if (c.fam_enabled) {
+        md->fam.resize(c.fam_layers);
+        for (int f = 0; f < c.fam_layers; ++f) {
+            FusionLayer& fl = md->fam[f];
+            const std::string P = "fusion_layers." + std::to_string(f) + ".";
+            fl.inw_off = md->add_param(P + "multihead_attention.in_proj_weight", 3 * Df, Df, cur);
+            fl.wo.w_off = md->add_param(P + "multihead_attention.out_proj.weight", Df, Df, cur); fl.wo.out = Df; fl.wo.in = Df;
+            fl.lin.w_off = md->add_param(P + "linear.weight", Df, 2 * Df, cur);                  fl.lin.out = Df; fl.lin.in = 2 * Df;
+            fl.qv.out = 2 * Df; fl.qv.in = Df; fl.qv.w_off = fl.inw_off;
+        }
+    }
+    {   // classifier: Linear, (ReLU, Linear) x (n-2), ReLU, Dropout, Linear  (src/model.py:89-100)
+        const int n_lin = c.cls_layers > 2 ? c.cls_layers : 2;
+        md->cls.resize(n_lin);
+        int k = 0, in = md->cls_in;
+        for (int j = 0; j < n_lin; ++j) {
+            const int idx = (j == 0) ? 0 : (j < n_lin - 1 ? k + 1 : k + 2);
+            const int out = (j == n_lin - 1) ? c.cls_out : c.cls_hidden;
+            md->cls[j].w_off = md->add_param("output_layer." + std::to_string(idx) + ".weight", out, in, cur);
+            md->cls[j].out = out; md->cls[j].in = in;
+            md->cls[j].b_off = idx;  // temporarily the Sequential index
+            k = (j == 0) ? 1 : k + 2;
+            in = out;
+        }
+    }
+    // ---- pass 2: 1-D tensors
+    cur = round_up(cur, 64);
+    md->off_1d = cur;
+    for (int i = 0; i < 2; ++i) {
+        Modality& mo = md->mod[i];
+        if (!mo.enabled) continue;
+        const int D = mo.D;
+        for (int t = 0; t < mo.T; ++t)
+            for (int l = 0; l < mo.L; ++l) {
+                EncLayer& e = mo.layers[(size_t)t * mo.L + l];
+                const std::string P = enc_prefix(mname[i], t, l);
+                e.qkv.b_off = md->add_param(P + "self_attn.in_proj_bias", 3 * D, 0, cur);
+                e.wo.b_off = md->add_param(P + "self_attn.out_proj.bias", D, 0, cur);
+                e.w1.b_off = md->add_param(P + "linear1.bias", FF, 0, cur);
+                e.w2.b_off = md->add_param(P + "linear2.bias", D, 0, cur);
+                e.g1 = md->add_param(P + "norm1.weight", D, 0, cur);
+                e.be1 = md->add_param(P + "norm1.bias", D, 0, cur);
+                e.g2 = md->add_param(P + "norm2.weight", D, 0, cur);
+                e.be2 = md->add_param(P + "norm2.bias", D, 0, cur);
+            }
+        mo.gf = md->add_param(std::string(mname[i]) + "_encoders.0.norm.weight", D, 0, cur);
+        mo.bef = md->add_param(std::string(mname[i]) + "_encoders.0.norm.bias", D, 0, cur);
+        mo.proj.b_off = md->add_param(std::string(mname[i]) + "_proj.bias", Df, 0, cur);
+    }
+    for (int f = 0; f < (int)md->fam.size(); ++f) {
+        FusionLayer& fl = md->fam[f];
+        const std::string P = "fusion_layers." + std::to_string(f) + ".";
+        fl.inb_off = md->add_param(P + "multihead_attention.in_proj_bias", 3 * Df, 0, cur);
+        fl.wo.b_off = md->add_param(P + "multihead_attention.out_proj.bias", Df, 0, cur);
+        fl.lin.b_off = md->add_param(P + "linear.bias", Df, 0, cur);
+    }
+    for (auto& L : md->cls) {
+        const int idx = (int)L.b_off;
+        L.b_off = md->add_param("output_layer." + std::to_string(idx) + ".bias", L.out, 0, cur);
+    }
+    md->arena_floats = round_up(cur, 64);
+
+    // ---- shadow layout
+    for (int i = 0; i < 2; ++i) {
+        Modality& mo = md->mod[i];
+        if (!mo.enabled) continue;
+        for (auto& e : mo.layers) {
+            for (Lin* L : {&e.qkv, &e.wo, &e.w1, &e.w2}) L->w = md->add_shadow_planes(L->w_off, L->out, L->in, L->in);
+        }
+        mo.proj.w = md->add_shadow_planes(mo.proj.w_off, mo.proj.out, mo.proj.in, mo.proj.in);
+    }
+    if (!md->fam.empty()) {
+        const int F = (int)md->fam.size();
+        md->wk_all.out = F * Df; md->wk_all.in = Df; md->wk_all.w_off = -1; md->wk_all.b_off = -1;
+        md->wk_all.w = md->alloc_shadow_planes(F * Df, Df);
+        md->bk_all = md->alloc_shadow_f32(F * Df);
+        for (int f = 0; f < F; ++f) {
+            FusionLayer& fl = md->fam[f];
+            fl.qv.w = md->alloc_shadow_planes(2 * Df, Df);
+            md->add_shadow_rows(fl.qv.w, 0, fl.inw_off, Df, Df, Df);                            // Wq
+            md->add_shadow_rows(fl.qv.w, Df, fl.inw_off + (int64_t)2 * Df * Df, Df, Df, Df);    // Wv
+            md->add_shadow_rows(md->wk_all.w, f * Df, fl.inw_off + (int64_t)Df * Df, Df, Df, Df);  // Wk
+            fl.bqv = md->alloc_shadow_f32(2 * Df);
+            md->add_shadow_f32(fl.bqv, 0, fl.inb_off, Df);
+            md->add_shadow_f32(fl.bqv, Df, fl.inb_off + 2 * Df, Df);
+            md->add_shadow_f32(md->bk_all, f * Df, fl.inb_off + Df, Df);
+            fl.wo.w = md->add_shadow_planes(fl.wo.w_off, Df, Df, Df);
+            fl.lin.w = md->add_shadow_planes(fl.lin.w_off, Df, 2 * Df, 2 * Df);
+        }
+    }
+    for (auto& L : md->cls) L.w = md->add_shadow_planes(L.w_off, L.out, L.in, L.in);
+    md->shadow_bytes = round_up(md->shadow_bytes, 256);
+    return M2F_OK;
+}
+
+// ------------------------------------------------------------------------------------------ shadow refresh
+constexpr int SHADOW_CHUNK = 48;
+struct ShadowBatch {
+    SEntry e[SHADOW_CHUNK];
+    int n;
+};
+
+__global__ void __launch_bounds__(256)
+shadow_refresh_kernel(const float* __restrict__ params, uint8_t* __restrict__ shadow, const ShadowBatch batch) {
+    const SEntry& e = batch.e[blockIdx.y];
+    const float* src = params + e.src_off;
+    if (e.planes == 0) {
+        float* dst = reinterpret_cast<float*>(shadow + e.dst_off);
+        for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < e.cols; i += gridDim.x * blockDim.x) dst[i] = src[i];
+        return;
+    }
+    __nv_bfloat16* dst = reinterpret_cast<__nv_bfloat16*>(shadow + e.dst_off);
+    if ((e.cols & 3) == 0 && (e.src_ld & 3) == 0) {
+        const int c4 = e.cols >> 2;
+        const int64_t total = (int64_t)e.rows * c4;
+        for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+            const int64_t r = i / c4;
+            const int cc = (int)(i - r * c4) * 4;
+            const float4 q = *reinterpret_cast<const float4*>(src + r * e.src_ld + cc);
+            const float v[4] = {q.x, q.y, q.z, q.w};
+            store_planes4(dst, e.stride, e.planes, r * e.dst_ld + cc, v);
+        }
+    } else {
+        const int64_t total = (int64_t)e.rows * e.cols;
+        for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+            const int64_t r = i / e.cols;
+            const int cc = (int)(i - r * e.cols);
+            store_planes(dst, e.stride, e.planes, r * e.dst_ld + cc, src[r * e.src_ld + cc]);
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------ execution context
+struct Ctx {
+    m2f_plan* p;
+    const float* params;
+    float* grads;
+    uint8_t* shadow;
+    uint8_t* ws;
+    cudaStream_t st;
+    int P;
+
+    m2f_planes_t pv(const Buf& b) const {
+        m2f_planes_t t;
+        t.ptr = (b.base == WS ? ws : shadow) + b.off;
+        t.rows = b.rows; t.cols = b.cols; t.ld = b.ld; t.plane_stride = b.stride; t.planes = b.planes; t._pad = 0;
+        return t;
+    }
+    static m2f_planes_t cols(m2f_planes_t t, int64_t c0, int64_t n) {
+        t.ptr = reinterpret_cast<uint8_t*>(t.ptr) + c0 * 2;
+        t.cols = n;
+        return t;
+    }
+    float* f32(const Buf& b) const { return reinterpret_cast<float*>((b.base == WS ? ws : shadow) + b.off); }
+    const float* prm(int64_t off) const { return params + off; }
+    float* grd(int64_t off) const { return grads + off; }
+
+    int tmap(const m2f_planes_t& t, int box_rows, const CUtensorMap** out) {
+        TmapKey k{t.ptr, t.rows, t.cols, t.ld, t.plane_stride, t.planes, box_rows};
+        auto it = p->tmaps.find(k);
+        if (it == p->tmaps.end()) {
+            CUtensorMap m;
+            M2F_TRY(make_planes_tmap(&m, &t, box_rows));
+            it = p->tmaps.emplace(k, m).first;
+        }
+        *out = &it->second;
+        return M2F_OK;
+    }
+
+    int gemm(const m2f_planes_t& A, bool a_mn, const m2f_planes_t& B, bool b_mn, int64_t M, int64_t N, const m2f_epilogue_t& e,
+             const m2f_kseg_t* segs = nullptr, int nsegs = 0) {
+        m2f_kseg_t one;
+        if (!segs) {
+            const int64_t ka = a_mn ? A.rows : A.cols, kb = b_mn ? B.rows : B.cols;
+            M2F_REQUIRE(ka == kb, M2F_ERR_ARG, "plan gemm: contraction extents differ (%lld vs %lld)", (long long)ka, (long long)kb);
+            one = {0, 0, (int32_t)ka};
+            segs = &one;
+            nsegs = 1;
+        }
+        GemmParams gp;
+        M2F_TRY(gemm_fill_params(gp, &A, a_mn, &B, b_mn, segs, nsegs, M, N, &e));
+        const int bn = gemm_block_n(M, N);
+        const CUtensorMap *ta, *tb;
+        M2F_TRY(tmap(A, a_mn ? BLOCK_K : BLOCK_M, &ta));
+        M2F_TRY(tmap(B, b_mn ? BLOCK_K : bn, &tb));
+        return gemm_launch(*ta, *tb, gp, bn, a_mn, b_mn, st);
+    }
+};
+
+struct Epi {
+    m2f_epilogue_t e;
+    Epi() { memset(&e, 0, sizeof(e)); e.gate_scale = 1.f; }
+    Epi& bias(const float* b) { e.bias = b; return *this; }
+    Epi& relu() { e.relu = 1; return *this; }
+    Epi& gate(const m2f_planes_t& g, float scale) { e.gate = g.ptr; e.gate_ld = g.ld; e.gate_scale = scale; return *this; }
+    Epi& drop(float p, uint64_t seed, uint64_t step, uint32_t site, int64_t ld) {
+        e.drop_p = p; e.seed = seed; e.step = step; e.site = site; e.drop_ld = ld; return *this;
+    }
+    Epi& resid(const float* r, int64_t ld) { e.resid = r; e.resid_ld = ld; return *this; }
+    Epi& f32(float* o, int64_t ld, bool acc = false) { e.out_f32 = o; e.out_f32_ld = ld; e.accumulate = acc ? 1 : 0; return *this; }
+    Epi& pl(const m2f_planes_t& o) { e.out_planes = o; return *this; }
+    operator const m2f_epilogue_t&() const { return e; }
+};
+
+static inline float inv_keep(float p) { return 1.f / (1.f - p); }
+
+// ------------------------------------------------------------------------------------------ forward
+static int forward_modality(Ctx& c, Modality& mo, const float* input, const uint8_t* key_pad, const m2f_planes_t& proj_dst) {
+    m2f_plan* p = c.p;
+    const int64_t M = p->M;
+    const int D = mo.D;
+    const float pd = p->p_used;
+    const uint64_t seed = p->seed, step = p->step;
+    m2f_planes_t in_pl = c.pv(mo.in_pl);
+    M2F_TRY(m2f_split_planes(input, D, &in_pl, c.st));
+    const float* x_f32 = input;
+    int64_t x_ld = D;
+    m2f_planes_t x_pl = in_pl;
+    for (int t = 0; t < mo.T; ++t) {
+        const float* cur = x_f32;
+        int64_t cur_ld = x_ld;
+        m2f_planes_t cur_pl = x_pl;
+        for (int l = 0; l < mo.L; ++l) {
+            EncLayer& e = mo.layers[(size_t)t * mo.L + l];
+            m2f_planes_t qkv = c.pv(e.qkv_pl), o = c.pv(e.o_pl), x1p = c.pv(e.x1_pl), h = c.pv(e.h_pl), x2p = c.pv(e.x2_pl);
+            // packed QKV projection (torch/nn/functional.py:5833-5846)
+            M2F_TRY(c.gemm(cur_pl, false, c.pv(e.qkv.w), false, M, 3 * D, Epi().bias(c.prm(e.qkv.b_off)).pl(qkv)));
+            m2f_planes_t q = Ctx::cols(qkv, 0, D), k = Ctx::cols(qkv, D, D), v = Ctx::cols(qkv, 2 * D, D);
+            M2F_TRY(m2f_attn_fwd(&q, &k, &v, key_pad, p->B, p->S, mo.H, pd, seed, step, M2F_SITE_ENC(mo.idx, t, l, 0), &o, c.st));
+            // x = norm1(x + dropout1(out_proj(attn)))   (transformer.py:951-977)
+            M2F_TRY(c.gemm(o, false, c.pv(e.wo.w), false, M, D,
+                           Epi().bias(c.prm(e.wo.b_off)).drop(pd, seed, step, M2F_SITE_ENC(mo.idx, t, l, 1), D).resid(cur, cur_ld).f32(c.f32(e.y1), e.y1.ld)));
+            M2F_TRY(m2f_ln_fwd(c.f32(e.y1), e.y1.ld, c.prm(e.g1), c.prm(e.be1), nullptr, 0, M, D, c.f32(e.x1), e.x1.ld, &x1p, 0.f, 0, 0, 0,
+                               c.f32(e.st1), c.st));
+            // x = norm2(x + dropout2(linear2(dropout(relu(linear1(x))))))   (transformer.py:980-982)
+            M2F_TRY(c.gemm(x1p, false, c.pv(e.w1.w), false, M, e.w1.out,
+                           Epi().bias(c.prm(e.w1.b_off)).relu().drop(pd, seed, step, M2F_SITE_ENC(mo.idx, t, l, 2), e.w1.out).pl(h)));
+            M2F_TRY(c.gemm(h, false, c.pv(e.w2.w), false, M, D,
+                           Epi().bias(c.prm(e.w2.b_off)).drop(pd, seed, step, M2F_SITE_ENC(mo.idx, t, l, 3), D).resid(c.f32(e.x1), e.x1.ld).f32(c.f32(e.y2), e.y2.ld)));
+            M2F_TRY(m2f_ln_fwd(c.f32(e.y2), e.y2.ld, c.prm(e.g2), c.prm(e.be2), nullptr, 0, M, D, c.f32(e.x2), e.x2.ld, &x2p, 0.f, 0, 0, 0,
+                               c.f32(e.st2), c.st));
+            cur = c.f32(e.x2);
+            cur_ld = e.x2.ld;
+            cur_pl = x2p;
+        }
+        // x = x + norm(encoder(x))  (src/model.py:107,119; the norm is shared across t); the last one
+        // also applies the dropout in front of the projection (src/model.py:111,123) to its operand copy
+        const bool last = (t == mo.T - 1);
+        m2f_planes_t outp = c.pv(mo.xout_pl[t]);
+        M2F_TRY(m2f_ln_fwd(cur, cur_ld, c.prm(mo.gf), c.prm(mo.bef), x_f32, x_ld, M, D, last ? nullptr : c.f32(mo.xout[t]), mo.xout[t].ld, &outp,
+                           last ? pd : 0.f, seed, step, M2F_SITE_MOD(mo.idx, 0), c.f32(mo.stf[t]), c.st));
+        x_f32 = c.f32(mo.xout[t]);
+        x_ld = mo.xout[t].ld;
+        x_pl = outp;
+    }
+    // projection to the fusion width + dropout (src/model.py:112-113,124-125)
+    M2F_TRY(c.gemm(x_pl, false, c.pv(mo.proj.w), false, M, mo.proj.out,
+                   Epi().bias(c.prm(mo.proj.b_off)).drop(pd, seed, step, M2F_SITE_MOD(mo.idx, 1), mo.proj.out).pl(proj_dst)));
+    return M2F_OK;
+}
+
+static int forward_all(Ctx& c, const float* text, const float* audio, const uint8_t* key_pad, float* logits) {
+    m2f_plan* p = c.p;
+    m2f_model* md = p->m;
+    const int64_t M = p->M;
+    const int Df = md->Df;
+    const float pd = p->p_used;
+    const uint64_t seed = p->seed, step = p->step;
+    m2f_planes_t zc = c.pv(p->zc_pl);
+    const bool fam = !p->fam.empty();
+    if (p->mod[0].enabled) M2F_TRY(forward_modality(c, p->mod[0], audio, key_pad, md->both ? Ctx::cols(zc, 0, Df) : zc));
+    if (p->mod[1].enabled) {
+        m2f_planes_t dst = fam ? c.pv(p->t0_pl) : (md->both ? Ctx::cols(zc, Df, Df) : zc);
+        M2F_TRY(forward_modality(c, p->mod[1], text, key_pad, dst));
+    }
+    if (fam) {
+        const int F = (int)p->fam.size();
+        m2f_planes_t a = Ctx::cols(zc, 0, Df);
+        m2f_planes_t kall = c.pv(p->kall_pl);
+        // K projections of every fusion layer read the same audio features: one GEMM
+        M2F_TRY(c.gemm(a, false, c.pv(md->wk_all.w), false, M, (int64_t)F * Df, Epi().bias(c.f32(md->bk_all)).pl(kall)));
+        m2f_planes_t t_cur = c.pv(p->t0_pl);
+        {   // relu(text) half of the first concat operand (src/model.py:16-17); later layers' text is already >= 0
+            m2f_planes_t u0r = Ctx::cols(c.pv(p->fam[0].u_pl), Df, Df);
+            M2F_TRY(m2f_relu_planes(&t_cur, &u0r, c.st));
+        }
+        for (int f = 0; f < F; ++f) {
+            FusionLayer& fl = p->fam[f];
+            m2f_planes_t qv = c.pv(fl.qv_pl), xo = c.pv(fl.xo_pl), u = c.pv(fl.u_pl);
+            M2F_TRY(c.gemm(t_cur, false, c.pv(fl.qv.w), false, M, 2 * Df, Epi().bias(c.f32(fl.bqv)).pl(qv)));
+            // query = text, key = audio, value = text  (src/model.py:14)
+            m2f_planes_t q = Ctx::cols(qv, 0, Df), v = Ctx::cols(qv, Df, Df), k = Ctx::cols(kall, (int64_t)f * Df, Df);
+            M2F_TRY(m2f_attn_fwd(&q, &k, &v, key_pad, p->B, p->S, md->cfg.fam_heads, pd, seed, step, M2F_SITE_FAM(f, 0), &xo, c.st));
+            M2F_TRY(c.gemm(xo, false, c.pv(fl.wo.w), false, M, Df, Epi().bias(c.prm(fl.wo.b_off)).relu().pl(Ctx::cols(u, 0, Df))));
+            m2f_planes_t t_next = (f < F - 1) ? Ctx::cols(c.pv(p->fam[f + 1].u_pl), Df, Df) : Ctx::cols(zc, Df, Df);
+            // relu(linear(relu(cat(x, text)))) then the model-level dropout (src/model.py:16-19,131)
+            M2F_TRY(c.gemm(u, false, c.pv(fl.lin.w), false, M, Df,
+                           Epi().bias(c.prm(fl.lin.b_off)).relu().drop(pd, seed, step, M2F_SITE_FAM(f, 1), Df).pl(t_next)));
+            t_cur = t_next;
+        }
+    }
+    // classifier (src/model.py:89-100,143)
+    const int n_lin = (int)md->cls.size();
+    m2f_planes_t in = zc;
+    for (int j = 0; j < n_lin; ++j) {
+        Lin& L = md->cls[j];
+        if (j < n_lin - 1) {
+            m2f_planes_t hj = c.pv(p->cls_h[j]);
+            Epi e;
+            e.bias(c.prm(L.b_off)).relu().pl(hj);
+            if (j == n_lin - 2) e.drop(pd, seed, step, M2F_SITE_CLS, L.out);
+            M2F_TRY(c.gemm(in, false, c.pv(L.w), false, M, L.out, e));
+            in = hj;
+        } else {
+            M2F_TRY(c.gemm(in, false, c.pv(L.w), false, M, L.out, Epi().bias(c.prm(L.b_off)).f32(logits, L.out)));
+        }
+    }
+    return M2F_OK;
+}
+
+// ------------------------------------------------------------------------------------------ backward
+// wgrad + bias grad of one Linear: dW[out,in] = dY^T X, db = colsum(dY)
+static int lin_wgrad(Ctx& c, const m2f_planes_t& dY, const m2f_planes_t& X, float* dW, int64_t dW_ld, float* db, int64_t out, int64_t in) {
+    M2F_TRY(c.gemm(dY, true, X, true, out, in, Epi().f32(dW, dW_ld)));
+    if (db) M2F_TRY(m2f_colsum_planes(&dY, db, c.st));
+    return M2F_OK;
+}
+
+static int backward_modality(Ctx& c, Modality& mo, const uint8_t* key_pad, const m2f_planes_t& dproj) {
+    m2f_plan* p = c.p;
+    const int64_t M = p->M;
+    const int D = mo.D;
+    const float pd = p->p_used;
+    const uint64_t seed = p->seed, step = p->step;
+    float* G = c.f32(p->gG);
+    float* A = c.f32(p->gA);
+    float* Bq = c.f32(p->gB);
+    const int64_t gld = p->gG.ld;
+    // projection: dW, db, and g = dropmask0(dproj . Wp)
+    m2f_planes_t xp = c.pv(mo.xout_pl[mo.T - 1]);
+    M2F_TRY(lin_wgrad(c, dproj, xp, c.grd(mo.proj.w_off), mo.proj.in, c.grd(mo.proj.b_off), mo.proj.out, mo.proj.in));
+    M2F_TRY(c.gemm(dproj, false, c.pv(mo.proj.w), true, M, D, Epi().drop(pd, seed, step, M2F_SITE_MOD(mo.idx, 0), D).f32(G, gld)));
+    m2f_planes_t dxp = c.pv(p->dx_pl), dhp = c.pv(p->dh_pl), dop = c.pv(p->do_pl), dqkvp = c.pv(p->dqkv_pl);
+    dxp.cols = D; dop.cols = D; dqkvp.cols = 3 * D;  // scratch buffers are sized for the wider modality
+    for (int t = mo.T - 1; t >= 0; --t) {
+        const EncLayer& lastl = mo.layers[(size_t)t * mo.L + mo.L - 1];
+        // x_out = x_in + LN_f(x2_last): G is d x_out; A <- d x2_last; G stays as the skip gradient
+        M2F_TRY(m2f_ln_bwd(G, gld, c.f32(lastl.x2), lastl.x2.ld, c.prm(mo.gf), c.f32(mo.stf[t]), M, D, A, gld, nullptr, 0.f, 0, 0, 0,
+                           c.grd(mo.gf), c.grd(mo.bef), nullptr, c.st));
+        for (int l = mo.L - 1; l >= 0; --l) {
+            EncLayer& e = mo.layers[(size_t)t * mo.L + l];
+            const bool first = (t == 0 && l == 0);
+            m2f_planes_t in_pl = (l > 0) ? c.pv(mo.layers[(size_t)t * mo.L + l - 1].x2_pl) : (t > 0 ? c.pv(mo.xout_pl[t - 1]) : c.pv(mo.in_pl));
+            m2f_planes_t h = c.pv(e.h_pl), x1p = c.pv(e.x1_pl), o = c.pv(e.o_pl), qkv = c.pv(e.qkv_pl);
+            // LN2: A = d x2 -> Bq = d y2 (fp32), dxp = dropmask3(d y2), db2 += colsum
+            M2F_TRY(m2f_ln_bwd(A, gld, c.f32(e.y2), e.y2.ld, c.prm(e.g2), c.f32(e.st2), M, D, Bq, gld, &dxp, pd, seed, step,
+                               M2F_SITE_ENC(mo.idx, t, l, 3), c.grd(e.g2), c.grd(e.be2), c.grd(e.w2.b_off), c.st));
+            M2F_TRY(lin_wgrad(c, dxp, h, c.grd(e.w2.w_off), e.w2.in, nullptr, e.w2.out, e.w2.in));
+            // dh = (d y2 . W2) * [h > 0] / (1-p)   (relu + dropout backward from the saved output)
+            M2F_TRY(c.gemm(dxp, false, c.pv(e.w2.w), true, M, e.w2.in, Epi().gate(h, inv_keep(pd)).pl(dhp)));
+            M2F_TRY(lin_wgrad(c, dhp, x1p, c.grd(e.w1.w_off), e.w1.in, c.grd(e.w1.b_off), e.w1.out, e.w1.in));
+            // A = d x1 = dh . W1 + d y2
+            M2F_TRY(c.gemm(dhp, false, c.pv(e.w1.w), true, M, D, Epi().resid(Bq, gld).f32(A, gld)));
+            // LN1: A -> Bq = d y1, dxp = dropmask1(d y1), dbo += colsum
+            M2F_TRY(m2f_ln_bwd(A, gld, c.f32(e.y1), e.y1.ld, c.prm(e.g1), c.f32(e.st1), M, D, Bq, gld, &dxp, pd, seed, step,
+                               M2F_SITE_ENC(mo.idx, t, l, 1), c.grd(e.g1), c.grd(e.be1), c.grd(e.wo.b_off), c.st));
+            M2F_TRY(lin_wgrad(c, dxp, o, c.grd(e.wo.w_off), e.wo.in, nullptr, e.wo.out, e.wo.in));
+            M2F_TRY(c.gemm(dxp, false, c.pv(e.wo.w), true, M, D, Epi().pl(dop)));
+            m2f_planes_t q = Ctx::cols(qkv, 0, D), k = Ctx::cols(qkv, D, D), v = Ctx::cols(qkv, 2 * D, D);
+            m2f_planes_t dq = Ctx::cols(dqkvp, 0, D), dk = Ctx::cols(dqkvp, D, D), dv = Ctx::cols(dqkvp, 2 * D, D);
+            M2F_TRY(m2f_attn_bwd(&q, &k, &v, &dop, key_pad, p->B, p->S, mo.H, pd, seed, step, M2F_SITE_ENC(mo.idx, t, l, 0), &dq, &dk, &dv, c.st));
+            M2F_TRY(lin_wgrad(c, dqkvp, in_pl, c.grd(e.qkv.w_off), e.qkv.in, c.grd(e.qkv.b_off), e.qkv.out, e.qkv.in));
+            if (!first) {
+                // gradient w.r.t. the layer input = dqkv . Wqkv + d y1 ; at l == 0 it also joins the skip gradient in G
+                if (l > 0) M2F_TRY(c.gemm(dqkvp, false, c.pv(e.qkv.w), true, M, D, Epi().resid(Bq, gld).f32(A, gld)));
+                else       M2F_TRY(c.gemm(dqkvp, false, c.pv(e.qkv.w), true, M, D, Epi().resid(Bq, gld).f32(G, gld, true)));
+            }
+        }
+    }
+    return M2F_OK;
+}
+
+static int backward_all(Ctx& c, const uint8_t* key_pad, const float* dlogits) {
+    m2f_plan* p = c.p;
+    m2f_model* md = p->m;
+    const int64_t M = p->M;
+    const int Df = md->Df;
+    const float pd = p->p_used;
+    const uint64_t seed = p->seed, step = p->step;
+    const bool fam = !p->fam.empty();
+    // 1-D gradients are accumulated with atomics: zero that region of the arena
+    M2F_CUDA(cudaMemsetAsync(c.grads + md->off_1d, 0, (size_t)(md->arena_floats - md->off_1d) * 4, c.st));
+    m2f_planes_t dl = c.pv(p->dl_pl);
+    if (dlogits) {
+        m2f_planes_t dlc = dl;
+        dlc.cols = md->cfg.cls_out;
+        M2F_TRY(m2f_split_planes(dlogits, md->cfg.cls_out, &dlc, c.st));
+    } else {
+        M2F_REQUIRE(p->have_loss_grad, M2F_ERR_ARG, "plan_backward: dlogits is NULL but m2f_plan_loss was not called after the forward");
+    }
+    dl.cols = md->cfg.cls_out;
+    m2f_planes_t zc = c.pv(p->zc_pl);
+    // ---- classifier
+    const int n_lin = (int)md->cls.size();
+    m2f_planes_t d_cur = dl;
+    m2f_planes_t dproj[2];
+    dproj[0] = c.pv(p->dproj_pl);
+    dproj[1] = c.pv(p->dprojt_pl);
+    m2f_planes_t dz = c.pv(p->dz_pl);
+    for (int j = n_lin - 1; j >= 0; --j) {
+        Lin& L = md->cls[j];
+        m2f_planes_t in = (j == 0) ? zc : c.pv(p->cls_h[j - 1]);
+        M2F_TRY(lin_wgrad(c, d_cur, in, c.grd(L.w_off), L.in, c.grd(L.b_off), L.out, L.in));
+        if (j > 0) {
+            m2f_planes_t dn = c.pv((j & 1) ? p->dcls_a : p->dcls_b);
+            const float sc = (j == n_lin - 1) ? inv_keep(pd) : 1.f;  // only the last hidden layer has dropout
+            M2F_TRY(c.gemm(d_cur, false, c.pv(L.w), true, M, L.in, Epi().gate(in, sc).pl(dn)));
+            d_cur = dn;
+        } else if (md->both) {
+            m2f_planes_t w = c.pv(L.w);
+            // audio half of the concat: gradient w.r.t. the projection's pre-dropout output (mask regenerated)
+            if (fam) {
+                M2F_TRY(c.gemm(d_cur, false, Ctx::cols(w, 0, Df), true, M, Df,
+                               Epi().drop(pd, seed, step, M2F_SITE_MOD(0, 1), Df).f32(c.f32(p->ga_f32), p->ga_f32.ld)));
+                // text half: gradient w.r.t. the last fusion linear's pre-activation
+                M2F_TRY(c.gemm(d_cur, false, Ctx::cols(w, Df, Df), true, M, Df, Epi().gate(Ctx::cols(zc, Df, Df), inv_keep(pd)).pl(dz)));
+            } else {
+                M2F_TRY(c.gemm(d_cur, false, Ctx::cols(w, 0, Df), true, M, Df, Epi().drop(pd, seed, step, M2F_SITE_MOD(0, 1), Df).pl(dproj[0])));
+                M2F_TRY(c.gemm(d_cur, false, Ctx::cols(w, Df, Df), true, M, Df, Epi().drop(pd, seed, step, M2F_SITE_MOD(1, 1), Df).pl(dproj[1])));
+            }
+        } else {
+            const int mi = p->mod[0].enabled ? 0 : 1;
+            M2F_TRY(c.gemm(d_cur, false, c.pv(L.w), true, M, Df, Epi().drop(pd, seed, step, M2F_SITE_MOD(mi, 1), Df).pl(dproj[mi])));
+        }
+    }
+    // ---- fusion stack, last layer first
+    if (fam) {
+        const int F = (int)p->fam.size();
+        m2f_planes_t a = Ctx::cols(zc, 0, Df);
+        m2f_planes_t dxo = c.pv(p->dxo_pl), dattn = c.pv(p->dattn_pl), dqv = c.pv(p->dqv_pl), dkall = c.pv(p->dkall_pl), kall = c.pv(p->kall_pl);
+        m2f_planes_t dz_cur = dz, dz_other = c.pv(p->dz2_pl);
+        float* gt = c.f32(p->gt_f32);
+        const int64_t gt_ld = p->gt_f32.ld;
+        for (int f = F - 1; f >= 0; --f) {
+            FusionLayer& fl = p->fam[f];
+            m2f_planes_t u = c.pv(fl.u_pl), qv = c.pv(fl.qv_pl), xo = c.pv(fl.xo_pl);
+            m2f_planes_t t_in = (f == 0) ? c.pv(p->t0_pl) : Ctx::cols(u, Df, Df);  // the layer's text input
+            m2f_planes_t wl = c.pv(fl.lin.w);
+            // linear on the concat
+            M2F_TRY(lin_wgrad(c, dz_cur, u, c.grd(fl.lin.w_off), fl.lin.in, c.grd(fl.lin.b_off), fl.lin.out, fl.lin.in));
+            // left half of d u -> gradient w.r.t. the out-proj output (gate: relu(x) > 0)
+            M2F_TRY(c.gemm(dz_cur, false, Ctx::cols(wl, 0, Df), true, M, Df, Epi().gate(Ctx::cols(u, 0, Df), 1.f).pl(dxo)));
+            // right half of d u -> first contribution to the gradient of this layer's text input, already in the
+            // pre-activation space of its producer: previous fusion linear (relu + dropout: gate [t > 0] / (1-p))
+            // or the text projection (cat-relu gate [t0 > 0], then the regenerated projection dropout mask)
+            if (f > 0) {
+                M2F_TRY(c.gemm(dz_cur, false, Ctx::cols(wl, Df, Df), true, M, Df, Epi().gate(t_in, inv_keep(pd)).f32(gt, gt_ld)));
+            } else {
+                M2F_TRY(c.gemm(dz_cur, false, Ctx::cols(wl, Df, Df), true, M, Df,
+                               Epi().gate(t_in, 1.f).drop(pd, seed, step, M2F_SITE_MOD(1, 1), Df).f32(gt, gt_ld)));
+            }
+            // attention out-proj
+            M2F_TRY(lin_wgrad(c, dxo, xo, c.grd(fl.wo.w_off), fl.wo.in, c.grd(fl.wo.b_off), fl.wo.out, fl.wo.in));
+            M2F_TRY(c.gemm(dxo, false, c.pv(fl.wo.w), true, M, Df, Epi().pl(dattn)));
+            m2f_planes_t q = Ctx::cols(qv, 0, Df), v = Ctx::cols(qv, Df, Df), k = Ctx::cols(kall, (int64_t)f * Df, Df);
+            m2f_planes_t dq = Ctx::cols(dqv, 0, Df), dv = Ctx::cols(dqv, Df, Df), dk = Ctx::cols(dkall, (int64_t)f * Df, Df);
+            M2F_TRY(m2f_attn_bwd(&q, &k, &v, &dattn, key_pad, p->B, p->S, md->cfg.fam_heads, pd, seed, step, M2F_SITE_FAM(f, 0), &dq, &dk, &dv, c.st));
+            // in-projection weight / bias gradients: rows [0,E) = q, [E,2E) = k, [2E,3E) = v of in_proj_weight
+            float* dWin = c.grd(fl.inw_off);
+            float* dbin = c.grd(fl.inb_off);
+            M2F_TRY(lin_wgrad(c, dq, t_in, dWin, Df, dbin, Df, Df));
+            M2F_TRY(lin_wgrad(c, dv, t_in, dWin + (int64_t)2 * Df * Df, Df, dbin + 2 * Df, Df, Df));
+            M2F_TRY(lin_wgrad(c, dk, a, dWin + (int64_t)Df * Df, Df, dbin + Df, Df, Df));
+            // second + third contributions to the text-input gradient: [dq | dv] . [Wq; Wv], same gate, summed with gt
+            if (f > 0) {
+                M2F_TRY(c.gemm(dqv, false, c.pv(fl.qv.w), true, M, Df, Epi().gate(t_in, inv_keep(pd)).resid(gt, gt_ld).pl(dz_other)));
+                std::swap(dz_cur, dz_other);
+            } else {
+                M2F_TRY(c.gemm(dqv, false, c.pv(fl.qv.w), true, M, Df,
+                               Epi().drop(pd, seed, step, M2F_SITE_MOD(1, 1), Df).resid(gt, gt_ld).pl(dproj[1])));
+            }
+        }
+        // audio: every layer's K projection + the classifier half, through the projection dropout mask
+        M2F_TRY(c.gemm(dkall, false, c.pv(md->wk_all.w), true, M, Df,
+                       Epi().drop(pd, seed, step, M2F_SITE_MOD(0, 1), Df).resid(c.f32(p->ga_f32), p->ga_f32.ld).pl(dproj[0])));
+    }
+    // NOTE on the f == 0 text contribution through q/v: q and v read t0 itself (no cat-relu on that path), so only the
+    // projection dropout mask applies -- handled above by not gating the [dq | dv] GEMM at f == 0.
+    for (int i = 0; i < 2; ++i)
+        if (p->mod[i].enabled) M2F_TRY(backward_modality(c, p->mod[i], key_pad, dproj[i]));
+    return M2F_OK;
+}
+
+}  // namespace m2f
+
+// ------------------------------------------------------------------------------------------ C ABI
+extern "C" int m2f_model_create(const m2f_model_cfg_t* cfg, m2f_model_t** out) {
+    M2F_REQUIRE(cfg && out, M2F_ERR_ARG, "model_create: null argument");
+    m2f_model* md = new m2f_model();
+    md->cfg = *cfg;
+    const int rc = build_model(md);
+    if (rc != M2F_OK) {
+        delete md;
+        return rc;
+    }
+    *out = md;
+    return M2F_OK;
+}
+extern "C" int m2f_model_destroy(m2f_model_t* m) {
+    delete m;
+    return M2F_OK;
+}
+extern "C" int64_t m2f_model_num_params(const m2f_model_t* m) { return m ? (int64_t)m->params.size() : 0; }
+extern "C" int m2f_model_param_info(const m2f_model_t* m, int64_t i, char* name_buf, int32_t name_buf_len, int64_t* offset, int64_t* rows,
+                                    int64_t* cols) {
+    M2F_REQUIRE(m && i >= 0 && i < (int64_t)m->params.size(), M2F_ERR_ARG, "param_info: index out of range");
+    const ParamInfo& pi = m->params[(size_t)i];
+    if (name_buf && name_buf_len > 0) snprintf(name_buf, (size_t)name_buf_len, "%s", pi.name.c_str());
+    if (offset) *offset = pi.off;
+    if (rows) *rows = pi.rows;
+    if (cols) *cols = pi.cols;
+    return M2F_OK;
+}
+extern "C" int64_t m2f_model_arena_floats(const m2f_model_t* m) { return m ? m->arena_floats : 0; }
+extern "C" int64_t m2f_model_arena_1d_offset(const m2f_model_t* m) { return m ? m->off_1d : 0; }
+extern "C" int64_t m2f_model_shadow_bytes(const m2f_model_t* m) { return m ? m->shadow_bytes : 0; }
+
+extern "C" int m2f_model_refresh_shadow(const m2f_model_t* m, const float* params, void* shadow, void* stream) {
+    M2F_REQUIRE(m && params && shadow, M2F_ERR_ARG, "refresh_shadow: null argument");
+    M2F_REQUIRE((reinterpret_cast<uintptr_t>(params) % 16) == 0 && (reinterpret_cast<uintptr_t>(shadow) % 256) == 0, M2F_ERR_ALIGN,
+                "refresh_shadow: params must be 16-byte and shadow 256-byte aligned");
+    auto st = reinterpret_cast<cudaStream_t>(stream);
+    for (size_t i = 0; i < m->sentries.size(); i += SHADOW_CHUNK) {
+        ShadowBatch b;
+        b.n = (int)std::min<size_t>(SHADOW_CHUNK, m->sentries.size() - i);
+        for (int j = 0; j < b.n; ++j) b.e[j] = m->sentries[i + j];
+        shadow_refresh_kernel<<<dim3(64, b.n), 256, 0, st>>>(params, reinterpret_cast<uint8_t*>(shadow), b);
+        M2F_LAUNCH_CHECK();
+    }
+    return M2F_OK;
+}
+
+extern "C" int m2f_plan_create(m2f_model_t* m, int64_t B, int64_t S, int32_t training_plan, m2f_plan_t** out) {
+    M2F_REQUIRE(m && out && B > 0 && S > 0, M2F_ERR_ARG, "plan_create: bad argument");
+    M2F_REQUIRE(B * S < (1ll << 30), M2F_ERR_UNSUPPORTED, "plan_create: B*S too large");
+    m2f_plan* p = new m2f_plan();
+    p->m = m;
+    p->B = B; p->S = S; p->M = B * S;
+    p->training = training_plan;
+    const int64_t M = p->M;
+    const int P = m->cfg.planes, FF = m->cfg.ffn_dim, Df = m->Df;
+    int Dmax = 0;
+    p->mod[0] = m->mod[0];
+    p->mod[1] = m->mod[1];
+    p->fam = m->fam;
+    {
+        Buf kb;
+        kb.rows = 1; kb.cols = M; kb.ld = M; kb.planes = 0;
+        kb.off = p->ws_bytes;
+        p->ws_bytes += round_up(M, 256);
+        p->key_pad = kb;
+    }
+    for (int i = 0; i < 2; ++i) {
+        Modality& mo = p->mod[i];
+        if (!mo.enabled) continue;
+        const int D = mo.D;
+        Dmax = std::max(Dmax, D);
+        mo.in_pl = p->alloc_pl(M, D, P);
+        EncLayer shared;  // inference plans alias one set of per-layer buffers
+        bool have_shared = false;
+        for (auto& e : mo.layers) {
+            if (training_plan || !have_shared) {
+                e.qkv_pl = p->alloc_pl(M, 3 * D, P);
+                e.o_pl = p->alloc_pl(M, D, P);
+                e.y1 = p->alloc_f32(M, D);
+                e.st1 = p->alloc_f32(M, 2);
+                e.x1 = p->alloc_f32(M, D);
+                e.x1_pl = p->alloc_pl(M, D, P);
+                e.h_pl = p->alloc_pl(M, FF, P);
+                e.y2 = p->alloc_f32(M, D);
+                e.st2 = p->alloc_f32(M, 2);
+                if (!training_plan) { shared = e; have_shared = true; }
+            } else {
+                e.qkv_pl = shared.qkv_pl; e.o_pl = shared.o_pl; e.y1 = shared.y1; e.st1 = shared.st1; e.x1 = shared.x1;
+                e.x1_pl = shared.x1_pl; e.h_pl = shared.h_pl; e.y2 = shared.y2; e.st2 = shared.st2;
+            }
+            // the layer output feeds the next layer while this layer's buffers are being reused: never aliased per layer pair
+            e.x2 = p->alloc_f32(M, D);
+            e.x2_pl = p->alloc_pl(M, D, P);
+        }
+        if (!training_plan) {  // two alternating output slots are enough for inference
+            Buf x2a = mo.layers[0].x2, x2pa = mo.layers[0].x2_pl;
+            Buf x2b = x2a, x2pb = x2pa;
+            if (mo.layers.size() > 1) { x2b = mo.layers[1].x2; x2pb = mo.layers[1].x2_pl; }
+            for (size_t j = 2; j < mo.layers.size(); ++j) {
+                mo.layers[j].x2 = (j & 1) ? x2b : x2a;
+                mo.layers[j].x2_pl = (j & 1) ? x2pb : x2pa;
+            }
+        }
+        mo.xout.resize(mo.T); mo.xout_pl.resize(mo.T); mo.stf.resize(mo.T);
+        for (int t = 0; t < mo.T; ++t) {
+            mo.xout[t] = p->alloc_f32(M, D);
+            mo.xout_pl[t] = p->alloc_pl(M, D, P);
+            mo.stf[t] = p->alloc_f32(M, 2);
+        }
+    }
+    p->zc_pl = p->alloc_pl(M, m->cls_in, P);
+    if (!m->fam.empty()) {
+        const int F = (int)m->fam.size();
+        p->t0_pl = p->alloc_pl(M, Df, P);
+        p->kall_pl = p->alloc_pl(M, (int64_t)F * Df, P);
+        for (auto& fl : p->fam) {
+            fl.qv_pl = p->alloc_pl(M, 2 * Df, P);
+            fl.xo_pl = p->alloc_pl(M, Df, P);
+            fl.u_pl = p->alloc_pl(M, 2 * Df, P);
+        }
+    }
+    p->cls_h.resize(m->cls.size() - 1);
+    for (size_t j = 0; j + 1 < m->cls.size(); ++j) p->cls_h[j] = p->alloc_pl(M, m->cls[j].out, P);
+    if (training_plan) {
+        p->dl_pl = p->alloc_pl(M, 8 * ((m->cfg.cls_out + 7) / 8), P);
+        const int Dg = std::max(Dmax, Df);
+        p->gG = p->alloc_f32(M, Dg);
+        p->gA = p->alloc_f32(M, Dg);
+        p->gB = p->alloc_f32(M, Dg);
+        // every backward scratch matrix gets ld = its own width; views narrow `cols` only
+        p->dx_pl = p->alloc_pl(M, Dg, P);
+        p->dh_pl = p->alloc_pl(M, FF, P);
+        p->do_pl = p->alloc_pl(M, Dg, P);
+        p->dqkv_pl = p->alloc_pl(M, 3 * Dmax, P);
+        p->dcls_a = p->alloc_pl(M, m->cfg.cls_hidden, P);
+        p->dcls_b = p->alloc_pl(M, m->cfg.cls_hidden, P);
+        p->dz_pl = p->alloc_pl(M, Df, P);
+        p->dz2_pl = p->alloc_pl(M, Df, P);
+        p->dproj_pl = p->alloc_pl(M, Df, P);
+        p->dprojt_pl = p->alloc_pl(M, Df, P);
+        if (!m->fam.empty()) {
+            p->dxo_pl = p->alloc_pl(M, Df, P);
+            p->dattn_pl = p->alloc_pl(M, Df, P);
+            p->dqv_pl = p->alloc_pl(M, 2 * Df, P);
+            p->dkall_pl = p->alloc_pl(M, (int64_t)m->fam.size() * Df, P);
+            p->gt_f32 = p->alloc_f32(M, Df);
+            p->ga_f32 = p->alloc_f32(M, Df);
+        }
+    }
+    p->ws_bytes = round_up(p->ws_bytes, 256);
+    *out = p;
+    return M2F_OK;
+}
+extern "C" int m2f_plan_destroy(m2f_plan_t* p) {
+    delete p;
+    return M2F_OK;
+}
+extern "C" int64_t m2f_plan_workspace_bytes(const m2f_plan_t* p) { return p ? p->ws_bytes : 0; }
+
+static int bind(m2f_plan* p, const void* shadow, void* ws) {
+    M2F_REQUIRE((reinterpret_cast<uintptr_t>(ws) % 256) == 0 && (reinterpret_cast<uintptr_t>(shadow) % 256) == 0, M2F_ERR_ALIGN,
+                "plan: workspace and shadow must be 256-byte aligned");
+    if (p->bound_ws != ws || p->bound_shadow != shadow) {
+        p->tmaps.clear();
+        p->bound_ws = ws;
+        p->bound_shadow = shadow;
+    }
+    return M2F_OK;
+}
+
+extern "C" int m2f_plan_forward(m2f_plan_t* p, const float* params, const void* shadow, void* workspace, const float* text,
+                                const float* audio, const uint8_t* key_pad, int32_t dropout_on, uint64_t seed, uint64_t step, float* logits,
+                                void* stream) {
+    M2F_REQUIRE(p && params && shadow && workspace && key_pad && logits, M2F_ERR_ARG, "plan_forward: null argument");
+    m2f_model* md = p->m;
+    M2F_REQUIRE(!md->mod[0].enabled || audio, M2F_ERR_ARG, "plan_forward: audio is enabled but the audio pointer is NULL");
+    M2F_REQUIRE(!md->mod[1].enabled || text, M2F_ERR_ARG, "plan_forward: text is enabled but the text pointer is NULL");
+    M2F_REQUIRE((!audio || (reinterpret_cast<uintptr_t>(audio) % 16) == 0) && (!text || (reinterpret_cast<uintptr_t>(text) % 16) == 0) &&
+                    (reinterpret_cast<uintptr_t>(logits) % 16) == 0 && (reinterpret_cast<uintptr_t>(params) % 16) == 0,
+                M2F_ERR_ALIGN, "plan_forward: text / audio / logits / params must be 16-byte aligned");
+    M2F_TRY(bind(p, shadow, workspace));
+    p->p_used = dropout_on ? md->cfg.dropout : 0.f;
+    p->seed = seed;
+    p->step = step;
+    p->have_loss_grad = false;
+    Ctx c{p, params, nullptr, reinterpret_cast<uint8_t*>(const_cast<void*>(shadow)), reinterpret_cast<uint8_t*>(workspace),
+          reinterpret_cast<cudaStream_t>(stream), md->cfg.planes};
+    uint8_t* kp = c.ws + p->key_pad.off;
+    M2F_CUDA(cudaMemcpyAsync(kp, key_pad, (size_t)p->M, cudaMemcpyDeviceToDevice, c.st));
+    return forward_all(c, text, audio, kp, logits);
+}
+
+extern "C" int m2f_plan_loss(m2f_plan_t* p, void* workspace, const float* logits, const int64_t* target, const float* class_w, float eps,
+                             float grad_scale, float* loss_out, void* stream) {
+    M2F_REQUIRE(p && workspace && logits && target && loss_out, M2F_ERR_ARG, "plan_loss: null argument");
+    M2F_REQUIRE(p->training, M2F_ERR_ARG, "plan_loss: needs a training plan");
+    Ctx c{p, nullptr, nullptr, nullptr, reinterpret_cast<uint8_t*>(workspace), reinterpret_cast<cudaStream_t>(stream), p->m->cfg.planes};
+    m2f_planes_t dl = c.pv(p->dl_pl);
+    M2F_TRY(m2f_ce_fwd_bwd(logits, p->m->cfg.cls_out, target, class_w, p->M, p->m->cfg.cls_out, eps, grad_scale, loss_out, nullptr, 0, &dl,
+                           stream));
+    p->have_loss_grad = true;
+    return M2F_OK;
+}
+
+extern "C" int m2f_plan_backward(m2f_plan_t* p, const float* params, const void* shadow, void* workspace, const float* dlogits,
+                                 float* grads, void* stream) {
+    M2F_REQUIRE(p && params && shadow && workspace && grads, M2F_ERR_ARG, "plan_backward: null argument");
+    M2F_REQUIRE(p->training, M2F_ERR_ARG, "plan_backward: this plan was created for inference (training_plan = 0)");
+    M2F_REQUIRE((reinterpret_cast<uintptr_t>(grads) % 16) == 0, M2F_ERR_ALIGN, "plan_backward: grads must be 16-byte aligned");
+    M2F_TRY(bind(p, shadow, workspace));
+    Ctx c{p, params, grads, reinterpret_cast<uint8_t*>(const_cast<void*>(shadow)), reinterpret_cast<uint8_t*>(workspace),
+          reinterpret_cast<cudaStream_t>(stream), p->m->cfg.planes};
+    return backward_all(c, c.ws + p->key_pad.off, dlogits);
+}
