@@ -4,5 +4,6 @@ Host side: Python / PyTorch (device memory, streams, torch.distributed).  Comput
 libm2f_b200.so behind the C ABI of include/m2f_b200.h.  No Triton, no multi-backend dispatch, no CPU fallback.
 """
 from . import _lib, ops  # noqa: F401
+from .model import FusedCrossEntropyLoss, FusionAttentionModule, M2FNet  # noqa: F401
 
-__all__ = ["_lib", "ops"]
+__all__ = ["_lib", "ops", "M2FNet", "FusionAttentionModule", "FusedCrossEntropyLoss"]

@@ -35,6 +35,19 @@ class Epilogue(C.Structure):
                 ("out_f32", C.c_void_p), ("out_f32_ld", C.c_int64), ("out_planes", Planes)]
 
 
+class ModalityCfg(C.Structure):
+    """m2f_modality_cfg_t"""
+    _fields_ = [("enabled", C.c_int32), ("dim", C.c_int32), ("n_head", C.c_int32), ("n_transformers", C.c_int32),
+                ("n_layers", C.c_int32)]
+
+
+class ModelCfg(C.Structure):
+    """m2f_model_cfg_t"""
+    _fields_ = [("audio", ModalityCfg), ("text", ModalityCfg), ("fam_enabled", C.c_int32), ("fam_dim", C.c_int32),
+                ("fam_heads", C.c_int32), ("fam_layers", C.c_int32), ("cls_hidden", C.c_int32), ("cls_out", C.c_int32),
+                ("cls_layers", C.c_int32), ("dropout", C.c_float), ("ffn_dim", C.c_int32), ("planes", C.c_int32)]
+
+
 PP = C.POINTER(Planes)
 _i64, _i32, _u64, _u32, _f32, _vp = C.c_int64, C.c_int32, C.c_uint64, C.c_uint32, C.c_float, C.c_void_p
 
@@ -53,7 +66,26 @@ PROTOTYPES = {
     "m2f_attn_bwd": [PP, PP, PP, PP, _vp, _i64, _i64, _i32, _f32, _u64, _u64, _u32, PP, PP, PP, _vp],
     "m2f_ce_fwd_bwd": [_vp, _i64, _vp, _vp, _i64, _i32, _f32, _f32, _vp, _vp, _i64, PP, _vp],
     "m2f_dropout_mask": [_f32, _u64, _u64, _u32, _i64, _vp, _vp],
+    "m2f_model_create": [C.POINTER(ModelCfg), C.POINTER(_vp)],
+    "m2f_model_destroy": [_vp],
+    "m2f_model_num_params": [_vp],
+    "m2f_model_param_info": [_vp, _i64, C.c_char_p, _i32, C.POINTER(_i64), C.POINTER(_i64), C.POINTER(_i64)],
+    "m2f_model_arena_floats": [_vp],
+    "m2f_model_arena_1d_offset": [_vp],
+    "m2f_model_shadow_bytes": [_vp],
+    "m2f_model_refresh_shadow": [_vp, _vp, _vp, _vp],
+    "m2f_plan_create": [_vp, _i64, _i64, _i32, C.POINTER(_vp)],
+    "m2f_plan_destroy": [_vp],
+    "m2f_plan_workspace_bytes": [_vp],
+    "m2f_plan_forward": [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _i32, _u64, _u64, _vp, _vp],
+    "m2f_plan_loss": [_vp, _vp, _vp, _vp, _vp, _f32, _f32, _vp, _vp],
+    "m2f_plan_backward": [_vp, _vp, _vp, _vp, _vp, _vp, _vp],
+    "m2f_adam_step": [_vp, _vp, _vp, _vp, _i64, _f32, _f32, _f32, _f32, _f32, _i64, _f32, _vp],
 }
+
+# functions that return a 64-bit count instead of an error code
+_RET_I64 = {"m2f_model_num_params", "m2f_model_arena_floats", "m2f_model_arena_1d_offset", "m2f_model_shadow_bytes",
+            "m2f_plan_workspace_bytes"}
 
 _lock = threading.Lock()
 _lib = None
@@ -74,7 +106,7 @@ def lib() -> C.CDLL:
             for name, args in PROTOTYPES.items():
                 fn = getattr(L, name)  # AttributeError if the symbol is missing
                 fn.argtypes = args
-                fn.restype = C.c_char_p if name == "m2f_last_error" else C.c_int
+                fn.restype = C.c_char_p if name == "m2f_last_error" else (C.c_int64 if name in _RET_I64 else C.c_int)
             _lib = L
     return _lib
 

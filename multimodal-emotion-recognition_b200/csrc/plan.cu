@@ -251,7 +251,6 @@ static int build_model(m2f_model* md) {
     if (c.fam_enabled) {
         M2F_REQUIRE(c.fam_heads > 0 && c.fam_dim % c.fam_heads == 0, M2F_ERR_ARG, "embed_dim must be divisible by num_heads");
         M2F_REQUIRE(c.fam_layers >= 1 && c.fam_layers <= 255, M2F_ERR_UNSUPPORTED, "FAM.n_layers must be 1..255");
-        M2F_REQUIRE(c.fam_dim % 64 == 0, M2F_ERR_UNSUPPORTED, "FAM.embedding_size must be a multiple of 64 (concat K-segments)");
     }
     md->Df = c.fam_dim;
     md->both = c.audio.enabled && c.text.enabled;

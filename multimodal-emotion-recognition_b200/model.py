@@ -1,0 +1,385 @@
+"""Host-side mirror of the reference's `model` module: `M2FNet` and `FusionAttentionModule`.
+
+Same constructor (`M2FNet(config.model)`), same `forward(text, audio, mask)` signature, same `state_dict()` names
+and shapes (incl. the shared final LayerNorm aliases) as /root/reference/src/model.py:5-145, so the
+reference's `train.py` / `test.py` run unchanged with this module on `sys.path` as `model`.
+
+What differs is what executes: every parameter is a view into ONE fp32 arena laid out by libm2f_b200
+(`m2f_model_*`), the forward is ONE C call (`m2f_plan_forward`) and the backward is ONE C call
+(`m2f_plan_backward`) into hand-written sm_100a kernels.  There is no eager / CPU fallback: CPU tensors raise.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import math
+from typing import Dict, List, Optional, Tuple
+
+import torch
+from torch import nn
+
+from . import _lib
+from ._lib import ModalityCfg, ModelCfg
+
+FFN_DIM = 2048  # nn.TransformerEncoderLayer's default dim_feedforward (src/model.py:61,73 pass none)
+
+
+def _stream() -> int:
+    return torch.cuda.current_stream().cuda_stream
+
+
+class _Node(nn.Module):
+    """Name-space node: gives parameters the dotted names of the reference state_dict."""
+
+    def forward(self, *a, **k):  # pragma: no cover - never called
+        raise RuntimeError("structural node of M2FNet; call the model itself")
+
+
+class FusionAttentionModule(_Node):
+    """Name-space twin of src/model.py:5-20.  The arithmetic (MHA with query = text, key = audio, value = text,
+    concat, ReLU, Linear, ReLU) runs inside m2f_plan_forward; this class only carries the parameters."""
+
+
+def _cfg_get(c, key, default=None):
+    try:
+        return getattr(c, key)
+    except AttributeError:
+        if isinstance(c, dict) and key in c:
+            return c[key]
+        if default is not None:
+            return default
+        raise
+
+
+def _default_planes() -> int:
+    import os
+    mode = os.environ.get("M2F_PRECISION", "bf16").lower()
+    table = {"bf16": 1, "1": 1, "bf16x2": 2, "2": 2, "fp32": 3, "bf16x3": 3, "3": 3}
+    if mode not in table:
+        raise ValueError(f"M2F_PRECISION={mode!r}: expected one of {sorted(table)}")
+    return table[mode]
+
+
+class _Plan:
+    """One (B, S, training) geometry: the C plan handle plus its torch-owned workspace."""
+
+    def __init__(self, model: "M2FNet", B: int, S: int, training: bool):
+        L = _lib.lib()
+        h = C.c_void_p()
+        _lib.check(L.m2f_plan_create(model._handle, B, S, int(training), C.byref(h)), "plan_create")
+        self.handle = h
+        self.B, self.S, self.training = B, S, training
+        self.ws_bytes = int(L.m2f_plan_workspace_bytes(h))
+        self.ws = torch.empty(self.ws_bytes, dtype=torch.uint8, device=model._arena.device)
+        self.token = 0  # bumped by every forward; a backward must match the forward that filled the workspace
+
+    def destroy(self):
+        if self.handle:
+            _lib.lib().m2f_plan_destroy(self.handle)
+            self.handle = None
+
+
+class _M2FStep(torch.autograd.Function):
+    """forward = m2f_plan_forward, backward = m2f_plan_backward.  Parameter gradients are written by the C call
+    straight into the model's gradient arena and attached as `p.grad` views (no per-parameter autograd traffic);
+    `anchor` is only there so that autograd records a node."""
+
+    @staticmethod
+    def forward(ctx, model, plan, text, audio, mask_u8, dropout_on, anchor):
+        logits = model._launch_forward(plan, text, audio, mask_u8, dropout_on)
+        ctx.model, ctx.plan, ctx.token = model, plan, plan.token
+        return logits
+
+    @staticmethod
+    def backward(ctx, dlogits):
+        ctx.model._launch_backward(ctx.plan, ctx.token, dlogits)
+        return None, None, None, None, None, None, None
+
+
+class M2FNet(nn.Module):
+    """Drop-in for the reference `M2FNet` (src/model.py:22-145)."""
+
+    def __init__(self, config, planes: Optional[int] = None):
+        super().__init__()
+        self.config = config
+        # the reference's constructor checks, same messages (src/model.py:32-35)
+        a, t, f, c = config.AUDIO, config.TEXT, config.FAM, config.CLASSIFIER
+        if not a.enabled and not t.enabled:
+            raise ValueError("At least one of audio and text must be enabled!")
+        if f.enabled and not (a.enabled and t.enabled):
+            raise ValueError("Fusion Attention Module can only be used with both audio and text enabled!")
+        for mc in (a, t):
+            if mc.enabled:
+                assert mc.embedding_size % mc.n_head == 0, "embed_dim must be divisible by num_heads"
+        if f.enabled:
+            assert f.embedding_size % f.n_head == 0, "embed_dim must be divisible by num_heads"
+        self.planes = int(planes if planes is not None else _cfg_get(config, "planes", 0) or _default_planes())
+        cc = ModelCfg()
+        for dst, src in ((cc.audio, a), (cc.text, t)):
+            dst.enabled, dst.dim, dst.n_head = int(bool(src.enabled)), int(src.embedding_size), int(src.n_head)
+            dst.n_transformers, dst.n_layers = int(src.n_transformers), int(src.n_encoder_layers)
+        cc.fam_enabled, cc.fam_dim, cc.fam_heads, cc.fam_layers = int(bool(f.enabled)), int(f.embedding_size), int(f.n_head), int(f.n_layers)
+        cc.cls_hidden, cc.cls_out, cc.cls_layers = int(c.hidden_size), int(c.output_size), int(c.n_layers)
+        cc.dropout, cc.ffn_dim, cc.planes = float(config.dropout), FFN_DIM, self.planes
+        self._ccfg = cc
+        L = _lib.lib()
+        h = C.c_void_p()
+        _lib.check(L.m2f_model_create(C.byref(cc), C.byref(h)), "model_create")
+        self._handle = h
+        self._arena_floats = int(L.m2f_model_arena_floats(h))
+        self._off_1d = int(L.m2f_model_arena_1d_offset(h))
+        self._shadow_bytes = int(L.m2f_model_shadow_bytes(h))
+        self._layout: List[Tuple[str, int, Tuple[int, ...]]] = []
+        n = int(L.m2f_model_num_params(h))
+        buf = C.create_string_buffer(256)
+        off, rows, cols = C.c_int64(), C.c_int64(), C.c_int64()
+        for i in range(n):
+            _lib.check(L.m2f_model_param_info(h, i, buf, 256, C.byref(off), C.byref(rows), C.byref(cols)), "param_info")
+            shape = (rows.value, cols.value) if cols.value else (rows.value,)
+            self._layout.append((buf.value.decode(), off.value, shape))
+        # parameters = views into one arena, registered under the reference's dotted names
+        self._arena = torch.zeros(self._arena_floats, dtype=torch.float32)
+        self._flat: List[Tuple[nn.Parameter, int, int]] = []
+        for name, o, shape in self._layout:
+            p = nn.Parameter(self._arena[o:o + math.prod(shape)].view(shape))
+            self._register_dotted(name, p)
+            self._flat.append((p, o, math.prod(shape)))
+        for m_name, mc in (("audio", a), ("text", t)):  # shared final norm: one module object under every t (G5)
+            if mc.enabled:
+                encs = getattr(self, f"{m_name}_encoders")
+                for ti in range(1, mc.n_transformers):
+                    getattr(encs, str(ti)).add_module("norm", getattr(encs, "0").norm)
+        self.reset_parameters()
+        self._grad_arena: Optional[torch.Tensor] = None
+        self._shadow: Optional[torch.Tensor] = None
+        self._shadow_version = None
+        self._plans: Dict[Tuple[int, int, bool], _Plan] = {}
+        self._seed = int(torch.initial_seed()) & ((1 << 64) - 1)
+        self._step = 0
+        self.launches = 0  # C-ABI model-level calls issued (bench.py reports kernel launches separately)
+
+    # ------------------------------------------------------------------------------------------ structure
+    def _register_dotted(self, name: str, p: nn.Parameter):
+        parts = name.split(".")
+        node: nn.Module = self
+        for i, part in enumerate(parts[:-1]):
+            child = node._modules.get(part)
+            if child is None:
+                is_fam = len(parts) > 2 and parts[0] == "fusion_layers" and i == 1
+                child = FusionAttentionModule() if is_fam else _Node()
+                node.add_module(part, child)
+            node = child
+        node.register_parameter(parts[-1], p)
+
+    @torch.no_grad()
+    def reset_parameters(self):
+        """Same initial distributions as the reference's torch modules (SURVEY.md A.3 'Init'); the encoder layers of
+        one modality start as clones of one template layer (G6)."""
+        by_name = {n: p for n, p in self.named_parameters()}
+        template: Dict[str, torch.Tensor] = {}
+        for name, p in by_name.items():
+            parts = name.split(".")
+            key = None
+            if parts[0].endswith("_encoders") and parts[2] == "layers":
+                key = parts[0] + "." + ".".join(parts[4:])
+                if key in template:
+                    p.copy_(template[key])
+                    continue
+            if name.endswith("in_proj_weight"):
+                nn.init.xavier_uniform_(p)
+            elif name.endswith("in_proj_bias") or name.endswith("out_proj.bias"):
+                p.zero_()
+            elif ".norm" in name and p.dim() == 1:
+                p.fill_(1.0) if name.endswith("weight") else p.zero_()
+            elif p.dim() == 2:
+                nn.init.kaiming_uniform_(p, a=math.sqrt(5))
+            else:  # Linear bias: U(-1/sqrt(fan_in), 1/sqrt(fan_in))
+                w = by_name[name[:-4] + "weight"]
+                bound = 1.0 / math.sqrt(w.shape[1])
+                p.uniform_(-bound, bound)
+            if key is not None:
+                template[key] = p.detach().clone()
+
+    # ------------------------------------------------------------------------------------------ arena upkeep
+    def _apply(self, fn, recurse=True):
+        super()._apply(fn, recurse)
+        self._repack()
+        return self
+
+    @torch.no_grad()
+    def _repack(self):
+        """Make every parameter a view of one contiguous fp32 arena again (after .to(device) re-allocated them)."""
+        p0 = self._flat[0][0]
+        dev = p0.device
+        for p, _, _ in self._flat:
+            if p.dtype != torch.float32:
+                raise RuntimeError("M2FNet parameters must stay fp32 (master weights); precision is chosen with `planes`")
+        arena = torch.empty(self._arena_floats, dtype=torch.float32, device=dev)
+        arena.zero_()
+        for p, o, n in self._flat:
+            view = arena[o:o + n].view(p.shape)
+            view.copy_(p.data)
+            p.data = view
+            p.grad = None
+        self._arena = arena
+        self._grad_arena = None
+        self._shadow = None
+        self._shadow_version = None
+        for pl in self._plans.values():
+            pl.destroy()
+        self._plans.clear()
+
+    def _views_intact(self) -> bool:
+        base = self._arena.data_ptr()
+        for idx in (0, len(self._flat) // 2, len(self._flat) - 1):
+            p, o, _ = self._flat[idx]
+            if p.data_ptr() != base + 4 * o:
+                return False
+        return True
+
+    def _param_version(self) -> int:
+        return sum(p._version for p, _, _ in self._flat)
+
+    def _ensure_shadow(self):
+        if not self._views_intact():
+            self._repack()
+        ver = self._param_version()
+        if self._shadow is None:
+            self._shadow = torch.empty(self._shadow_bytes, dtype=torch.uint8, device=self._arena.device)
+            self._shadow_version = None
+        if self._shadow_version != ver:
+            _lib.check(_lib.lib().m2f_model_refresh_shadow(self._handle, self._arena.data_ptr(), self._shadow.data_ptr(), _stream()),
+                       "refresh_shadow")
+            self._shadow_version = ver
+
+    def _plan(self, B: int, S: int, training: bool) -> _Plan:
+        key = (B, S, training)
+        pl = self._plans.get(key)
+        if pl is None:
+            pl = _Plan(self, B, S, training)
+            self._plans[key] = pl
+        return pl
+
+    # ------------------------------------------------------------------------------------------ execution
+    def _launch_forward(self, plan: _Plan, text, audio, mask_u8, dropout_on: bool) -> torch.Tensor:
+        C_out = self._ccfg.cls_out
+        logits = torch.empty((plan.B, plan.S, C_out), dtype=torch.float32, device=self._arena.device)
+        self._step += 1
+        plan.token += 1
+        _lib.check(_lib.lib().m2f_plan_forward(plan.handle, self._arena.data_ptr(), self._shadow.data_ptr(), plan.ws.data_ptr(),
+                                               None if text is None else text.data_ptr(), None if audio is None else audio.data_ptr(),
+                                               mask_u8.data_ptr(), int(dropout_on), self._seed, self._step, logits.data_ptr(), _stream()),
+                   "plan_forward")
+        self.launches += 1
+        return logits
+
+    def _launch_backward(self, plan: _Plan, token: int, dlogits: torch.Tensor):
+        if token != plan.token:
+            raise RuntimeError("M2FNet backward: the workspace of this (B,S) plan was overwritten by a later forward; "
+                               "call backward before the next forward of the same shape")
+        dlogits = dlogits.contiguous().float()
+        fresh = all(p.grad is None for p, _, _ in self._flat)
+        if self._grad_arena is None:
+            self._grad_arena = torch.zeros(self._arena_floats, dtype=torch.float32, device=self._arena.device)
+        target = self._grad_arena if fresh else torch.empty_like(self._grad_arena)
+        _lib.check(_lib.lib().m2f_plan_backward(plan.handle, self._arena.data_ptr(), self._shadow.data_ptr(), plan.ws.data_ptr(),
+                                                dlogits.data_ptr(), target.data_ptr(), _stream()), "plan_backward")
+        self.launches += 1
+        if fresh:
+            for p, o, n in self._flat:
+                if p.requires_grad:
+                    p.grad = self._grad_arena[o:o + n].view(p.shape)
+        else:  # gradient accumulation (zero_grad(set_to_none=False) or several backwards per step)
+            for p, o, n in self._flat:
+                if not p.requires_grad:
+                    continue
+                g = target[o:o + n].view(p.shape)
+                if p.grad is None:
+                    p.grad = g.clone()
+                else:
+                    p.grad.add_(g)
+
+    def forward(self, text, audio, mask):
+        """text [B,S,Dt], audio [B,S,Da] fp32, mask [B,S] bool (True = padding) -> logits [B,S,C] fp32
+        (src/model.py:102-145).  A disabled modality's tensor is ignored, as in the reference."""
+        a_on, t_on = bool(self._ccfg.audio.enabled), bool(self._ccfg.text.enabled)
+        used = [x for x, on in ((text, t_on), (audio, a_on)) if on] + [mask]
+        for x in used:
+            if not isinstance(x, torch.Tensor) or not x.is_cuda:
+                raise RuntimeError("M2FNet (B200-native) runs on CUDA tensors only: there is no CPU path. "
+                                   "Move the model and the batch to a B200 (`.to('cuda')`).")
+        if not self._arena.is_cuda:
+            raise RuntimeError("M2FNet (B200-native): move the model to the GPU first (`model.to('cuda')`); there is no CPU path")
+        B, S = mask.shape
+        text = text.contiguous().float() if t_on else None
+        audio = audio.contiguous().float() if a_on else None
+        if t_on and tuple(text.shape) != (B, S, self._ccfg.text.dim):
+            raise RuntimeError(f"text must be [B,S,{self._ccfg.text.dim}], got {tuple(text.shape)}")
+        if a_on and tuple(audio.shape) != (B, S, self._ccfg.audio.dim):
+            raise RuntimeError(f"audio must be [B,S,{self._ccfg.audio.dim}], got {tuple(audio.shape)}")
+        mask_u8 = mask.contiguous()
+        mask_u8 = mask_u8.view(torch.uint8) if mask_u8.dtype == torch.bool else (mask_u8 != 0).view(torch.uint8)
+        with torch.cuda.device(self._arena.device):
+            self._ensure_shadow()
+            needs_grad = torch.is_grad_enabled() and any(p.requires_grad for p, _, _ in self._flat)
+            plan = self._plan(B, S, needs_grad)
+            dropout_on = self.training and float(self.config.dropout) > 0.0
+            if needs_grad:
+                anchor = next(p for p, _, _ in self._flat if p.requires_grad)
+                return _M2FStep.apply(self, plan, text, audio, mask_u8, dropout_on, anchor)
+            return self._launch_forward(plan, text, audio, mask_u8, dropout_on)
+
+    # ------------------------------------------------------------------------------------------ extras
+    def flat_parameters(self) -> torch.Tensor:
+        """The fp32 parameter arena (every parameter is a view of it) -- for fused Adam and NCCL buckets."""
+        return self._arena
+
+    def flat_grads(self) -> Optional[torch.Tensor]:
+        return self._grad_arena
+
+    def __del__(self):
+        try:
+            for pl in self._plans.values():
+                pl.destroy()
+            if getattr(self, "_handle", None):
+                _lib.lib().m2f_model_destroy(self._handle)
+                self._handle = None
+        except Exception:
+            pass
+
+
+class _CEFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, logits, target, weight, eps):
+        from . import ops
+        B, S, Cc = logits.shape
+        lg = logits.reshape(B * S, Cc)
+        dl = torch.empty_like(lg)
+        out = ops.ce_fwd_bwd(lg, target.reshape(-1).contiguous(), weight, eps=eps, grad_scale=1.0, dlogits=dl)
+        ctx.save_for_backward(dl)
+        ctx.shape = (B, S, Cc)
+        return out[0]
+
+    @staticmethod
+    def backward(ctx, g):
+        (dl,) = ctx.saved_tensors
+        return (dl * g).view(ctx.shape), None, None, None
+
+
+class FusedCrossEntropyLoss(nn.Module):
+    """CrossEntropyLoss(weight?, ignore_index=-1, label_smoothing=eps) as src/train.py:48-50 builds it, computed by
+    the K4 kernel (loss and dlogits in one pass).  Called like the reference's criterion: `criterion(outputs.permute(0,2,1), emotion)`."""
+
+    def __init__(self, weight: Optional[torch.Tensor] = None, ignore_index: int = -1, label_smoothing: float = 0.1):
+        super().__init__()
+        if ignore_index != -1:
+            raise ValueError("FusedCrossEntropyLoss supports ignore_index=-1 only (src/train.py:48-50)")
+        self.register_buffer("weight", weight.float() if weight is not None else None)
+        self.eps = float(label_smoothing)
+
+    def forward(self, outputs_bcs: torch.Tensor, target: torch.Tensor) -> torch.Tensor:
+        if not outputs_bcs.is_cuda:
+            raise RuntimeError("FusedCrossEntropyLoss runs on CUDA tensors only")
+        logits = outputs_bcs.permute(0, 2, 1)  # back to [B,S,C]; a no-copy view of the model's logits
+        if not logits.is_contiguous():
+            logits = logits.contiguous()
+        return _CEFn.apply(logits.float(), target, self.weight, self.eps)
