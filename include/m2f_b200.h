@@ -80,6 +80,9 @@ typedef struct {
 int m2f_abi_version(void);
 const char* m2f_last_error(void);
 
+/* Number of kernels this library has launched in this process so far (bench.py's `gpu_launches`). */
+int64_t m2f_launch_count(void);
+
 /* Device capability check: returns M2F_OK only on an sm_100 device. */
 int m2f_check_device(void);
 
@@ -200,6 +203,16 @@ int m2f_plan_loss(m2f_plan_t* p, void* workspace, const float* logits, const int
  * Every parameter gradient is WRITTEN (not accumulated) into the fp32 arena `grads` (same layout as params). */
 int m2f_plan_backward(m2f_plan_t* p, const float* params, const void* shadow, void* workspace, const float* dlogits,
                       float* grads, void* stream);
+
+/* Data-parallel variant: `cb(user, lo, hi)` is called on the host, in enqueue order, each time the gradients of the
+ * arena range [lo, hi) (floats) are final on `stream` and at least `bucket_floats` of them have accumulated -- the 2-D
+ * weights complete from the top of the arena downwards (classifier, fusion layers, text stack, audio stack), the 1-D
+ * region [m2f_model_arena_1d_offset, arena_floats) last.  The caller records an event / launches its NCCL all-reduce
+ * of that range from the callback, so the exchange overlaps the rest of the backward. */
+typedef void (*m2f_bucket_cb)(void* user, int64_t lo, int64_t hi);
+int m2f_plan_backward_bucketed(m2f_plan_t* p, const float* params, const void* shadow, void* workspace,
+                               const float* dlogits, float* grads, int64_t bucket_floats, m2f_bucket_cb cb, void* user,
+                               void* stream);
 
 /* Adam with L2 weight decay folded into the gradient (torch.optim.Adam semantics, src/train.py:56,231), one
  * launch over the arena; `t` is the 1-based step count.  grad_scale multiplies g first (DDP averaging). */

@@ -48,6 +48,8 @@ class ModelCfg(C.Structure):
                 ("cls_layers", C.c_int32), ("dropout", C.c_float), ("ffn_dim", C.c_int32), ("planes", C.c_int32)]
 
 
+BUCKET_CB = C.CFUNCTYPE(None, C.c_void_p, C.c_int64, C.c_int64)  # m2f_bucket_cb
+
 PP = C.POINTER(Planes)
 _i64, _i32, _u64, _u32, _f32, _vp = C.c_int64, C.c_int32, C.c_uint64, C.c_uint32, C.c_float, C.c_void_p
 
@@ -56,6 +58,7 @@ PROTOTYPES = {
     "m2f_abi_version": [],
     "m2f_last_error": [],
     "m2f_check_device": [],
+    "m2f_launch_count": [],
     "m2f_gemm": [PP, C.c_int, PP, C.c_int, C.POINTER(KSeg), C.c_int, _i64, _i64, C.POINTER(Epilogue), _vp],
     "m2f_split_planes": [_vp, _i64, PP, _vp],
     "m2f_relu_planes": [PP, PP, _vp],
@@ -80,11 +83,12 @@ PROTOTYPES = {
     "m2f_plan_forward": [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _i32, _u64, _u64, _vp, _vp],
     "m2f_plan_loss": [_vp, _vp, _vp, _vp, _vp, _f32, _f32, _vp, _vp],
     "m2f_plan_backward": [_vp, _vp, _vp, _vp, _vp, _vp, _vp],
+    "m2f_plan_backward_bucketed": [_vp, _vp, _vp, _vp, _vp, _vp, _i64, _vp, _vp, _vp],
     "m2f_adam_step": [_vp, _vp, _vp, _vp, _i64, _f32, _f32, _f32, _f32, _f32, _i64, _f32, _vp],
 }
 
 # functions that return a 64-bit count instead of an error code
-_RET_I64 = {"m2f_model_num_params", "m2f_model_arena_floats", "m2f_model_arena_1d_offset", "m2f_model_shadow_bytes",
+_RET_I64 = {"m2f_launch_count", "m2f_model_num_params", "m2f_model_arena_floats", "m2f_model_arena_1d_offset", "m2f_model_shadow_bytes",
             "m2f_plan_workspace_bytes"}
 
 _lock = threading.Lock()

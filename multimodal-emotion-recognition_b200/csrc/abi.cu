@@ -1,5 +1,7 @@
 // Error plumbing, version / device query and the small element-wise kernels of the C ABI.
 #include <stdarg.h>
+
+#include <atomic>
 #include <stdio.h>
 
 #include "common.cuh"
@@ -7,6 +9,9 @@
 namespace m2f {
 
 static thread_local char g_err[512] = "";
+static std::atomic<long long> g_launches{0};
+
+void note_launch() { g_launches.fetch_add(1, std::memory_order_relaxed); }
 
 void set_error(const char* fmt, ...) {
     va_list ap;
@@ -97,6 +102,8 @@ using namespace m2f;
 
 extern "C" int m2f_abi_version(void) { return M2F_ABI_VERSION; }
 extern "C" const char* m2f_last_error(void) { return g_err; }
+
+extern "C" int64_t m2f_launch_count(void) { return (int64_t)g_launches.load(std::memory_order_relaxed); }
 
 extern "C" int m2f_check_device(void) {
     int dev = 0;

@@ -34,7 +34,12 @@ int cuda_fail(cudaError_t e, const char* what, const char* file, int line);
     } while (0)
 
 // after a kernel launch: catches bad launch configurations without synchronising
-#define M2F_LAUNCH_CHECK() M2F_CUDA(cudaPeekAtLastError())
+void note_launch();
+#define M2F_LAUNCH_CHECK()                  \
+    do {                                    \
+        ::m2f::note_launch();               \
+        M2F_CUDA(cudaPeekAtLastError());    \
+    } while (0)
 
 int check_planes(const m2f_planes_t* t, const char* name, int vec);
 

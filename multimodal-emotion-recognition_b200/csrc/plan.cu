@@ -419,6 +419,20 @@ struct Ctx {
     uint8_t* ws;
     cudaStream_t st;
     int P;
+    // gradient-bucket notification (data-parallel overlap): the 2-D gradients complete top-down in the arena
+    int64_t bucket_floats = 0;
+    m2f_bucket_cb cb = nullptr;
+    void* cb_user = nullptr;
+    int64_t hi = 0;
+
+    // every 2-D gradient at arena offsets >= w is final (enqueued on the stream)
+    void done_down_to(int64_t w, bool flush = false) {
+        if (!cb) return;
+        if (hi - w >= bucket_floats || (flush && hi > w)) {
+            cb(cb_user, w, hi);
+            hi = w;
+        }
+    }
 
     m2f_planes_t pv(const Buf& b) const {
         m2f_planes_t t;
@@ -619,6 +633,7 @@ static int backward_modality(Ctx& c, Modality& mo, const uint8_t* key_pad, const
     // projection: dW, db, and g = dropmask0(dproj . Wp)
     m2f_planes_t xp = c.pv(mo.xout_pl[mo.T - 1]);
     M2F_TRY(lin_wgrad(c, dproj, xp, c.grd(mo.proj.w_off), mo.proj.in, c.grd(mo.proj.b_off), mo.proj.out, mo.proj.in));
+    c.done_down_to(mo.proj.w_off);
     M2F_TRY(c.gemm(dproj, false, c.pv(mo.proj.w), true, M, D, Epi().drop(pd, seed, step, M2F_SITE_MOD(mo.idx, 0), D).f32(G, gld)));
     m2f_planes_t dxp = c.pv(p->dx_pl), dhp = c.pv(p->dh_pl), dop = c.pv(p->do_pl), dqkvp = c.pv(p->dqkv_pl);
     dxp.cols = D; dop.cols = D; dqkvp.cols = 3 * D;  // scratch buffers are sized for the wider modality
@@ -650,6 +665,7 @@ static int backward_modality(Ctx& c, Modality& mo, const uint8_t* key_pad, const
             m2f_planes_t dq = Ctx::cols(dqkvp, 0, D), dk = Ctx::cols(dqkvp, D, D), dv = Ctx::cols(dqkvp, 2 * D, D);
             M2F_TRY(m2f_attn_bwd(&q, &k, &v, &dop, key_pad, p->B, p->S, mo.H, pd, seed, step, M2F_SITE_ENC(mo.idx, t, l, 0), &dq, &dk, &dv, c.st));
             M2F_TRY(lin_wgrad(c, dqkvp, in_pl, c.grd(e.qkv.w_off), e.qkv.in, c.grd(e.qkv.b_off), e.qkv.out, e.qkv.in));
+            c.done_down_to(e.qkv.w_off);
             if (!first) {
                 // gradient w.r.t. the layer input = dqkv . Wqkv + d y1 ; at l == 0 it also joins the skip gradient in G
                 if (l > 0) M2F_TRY(c.gemm(dqkvp, false, c.pv(e.qkv.w), true, M, D, Epi().resid(Bq, gld).f32(A, gld)));
@@ -713,6 +729,7 @@ static int backward_all(Ctx& c, const uint8_t* key_pad, const float* dlogits) {
             M2F_TRY(c.gemm(d_cur, false, c.pv(L.w), true, M, Df, Epi().drop(pd, seed, step, M2F_SITE_MOD(mi, 1), Df).pl(dproj[mi])));
         }
     }
+    c.done_down_to(md->cls[0].w_off);
     // ---- fusion stack, last layer first
     if (fam) {
         const int F = (int)p->fam.size();
@@ -751,6 +768,7 @@ static int backward_all(Ctx& c, const uint8_t* key_pad, const float* dlogits) {
             M2F_TRY(lin_wgrad(c, dq, t_in, dWin, Df, dbin, Df, Df));
             M2F_TRY(lin_wgrad(c, dv, t_in, dWin + (int64_t)2 * Df * Df, Df, dbin + 2 * Df, Df, Df));
             M2F_TRY(lin_wgrad(c, dk, a, dWin + (int64_t)Df * Df, Df, dbin + Df, Df, Df));
+            c.done_down_to(fl.inw_off);
             // second + third contributions to the text-input gradient: [dq | dv] . [Wq; Wv], same gate, summed with gt
             if (f > 0) {
                 M2F_TRY(c.gemm(dqv, false, c.pv(fl.qv.w), true, M, Df, Epi().gate(t_in, inv_keep(pd)).resid(gt, gt_ld).pl(dz_other)));
@@ -766,8 +784,11 @@ static int backward_all(Ctx& c, const uint8_t* key_pad, const float* dlogits) {
     }
     // NOTE on the f == 0 text contribution through q/v: q and v read t0 itself (no cat-relu on that path), so only the
     // projection dropout mask applies -- handled above by not gating the [dq | dv] GEMM at f == 0.
-    for (int i = 0; i < 2; ++i)
+    // text first, audio last: gradients then complete in exactly the reverse of the arena order
+    for (int i = 1; i >= 0; --i)
         if (p->mod[i].enabled) M2F_TRY(backward_modality(c, p->mod[i], key_pad, dproj[i]));
+    c.done_down_to(0, true);
+    if (c.cb) c.cb(c.cb_user, md->off_1d, md->arena_floats);  // biases / LayerNorm parameters (atomically accumulated)
     return M2F_OK;
 }
 
@@ -978,13 +999,23 @@ extern "C" int m2f_plan_loss(m2f_plan_t* p, void* workspace, const float* logits
     return M2F_OK;
 }
 
-extern "C" int m2f_plan_backward(m2f_plan_t* p, const float* params, const void* shadow, void* workspace, const float* dlogits,
-                                 float* grads, void* stream) {
+extern "C" int m2f_plan_backward_bucketed(m2f_plan_t* p, const float* params, const void* shadow, void* workspace,
+                                          const float* dlogits, float* grads, int64_t bucket_floats, m2f_bucket_cb cb, void* user,
+                                          void* stream) {
     M2F_REQUIRE(p && params && shadow && workspace && grads, M2F_ERR_ARG, "plan_backward: null argument");
     M2F_REQUIRE(p->training, M2F_ERR_ARG, "plan_backward: this plan was created for inference (training_plan = 0)");
     M2F_REQUIRE((reinterpret_cast<uintptr_t>(grads) % 16) == 0, M2F_ERR_ALIGN, "plan_backward: grads must be 16-byte aligned");
     M2F_TRY(bind(p, shadow, workspace));
     Ctx c{p, params, grads, reinterpret_cast<uint8_t*>(const_cast<void*>(shadow)), reinterpret_cast<uint8_t*>(workspace),
           reinterpret_cast<cudaStream_t>(stream), p->m->cfg.planes};
+    c.bucket_floats = bucket_floats > 0 ? bucket_floats : 1;
+    c.cb = cb;
+    c.cb_user = user;
+    c.hi = p->m->off_1d;
     return backward_all(c, c.ws + p->key_pad.off, dlogits);
+}
+
+extern "C" int m2f_plan_backward(m2f_plan_t* p, const float* params, const void* shadow, void* workspace, const float* dlogits,
+                                 float* grads, void* stream) {
+    return m2f_plan_backward_bucketed(p, params, shadow, workspace, dlogits, grads, 0, nullptr, nullptr, stream);
 }

@@ -156,6 +156,10 @@ class M2FNet(nn.Module):
         self._seed = int(torch.initial_seed()) & ((1 << 64) - 1)
         self._step = 0
         self.launches = 0  # C-ABI model-level calls issued (bench.py reports kernel launches separately)
+        # data-parallel hooks (parallel.GradBucketReducer): on_bucket(lo, hi) per finished gradient range, on_done()
+        self._bucket_hook = None
+        self._bucket_floats = 0
+        self._done_hook = None
 
     # ------------------------------------------------------------------------------------------ structure
     def _register_dotted(self, name: str, p: nn.Parameter):
@@ -281,8 +285,27 @@ class M2FNet(nn.Module):
         if self._grad_arena is None:
             self._grad_arena = torch.zeros(self._arena_floats, dtype=torch.float32, device=self._arena.device)
         target = self._grad_arena if fresh else torch.empty_like(self._grad_arena)
-        _lib.check(_lib.lib().m2f_plan_backward(plan.handle, self._arena.data_ptr(), self._shadow.data_ptr(), plan.ws.data_ptr(),
-                                                dlogits.data_ptr(), target.data_ptr(), _stream()), "plan_backward")
+        if self._bucket_hook is not None and fresh:
+            errors = []
+
+            def _cb(_user, lo, hi):
+                try:
+                    self._bucket_hook(int(lo), int(hi))
+                except BaseException as e:  # an exception cannot cross the C frame
+                    errors.append(e)
+
+            cb = _lib.BUCKET_CB(_cb)
+            _lib.check(_lib.lib().m2f_plan_backward_bucketed(plan.handle, self._arena.data_ptr(), self._shadow.data_ptr(),
+                                                             plan.ws.data_ptr(), dlogits.data_ptr(), target.data_ptr(),
+                                                             int(self._bucket_floats), cb, None, _stream()), "plan_backward_bucketed")
+            if errors:
+                raise errors[0]
+        else:
+            if self._bucket_hook is not None:
+                raise RuntimeError("data-parallel M2FNet needs zero_grad(set_to_none=True) (gradient accumulation across "
+                                   "backwards is not supported with bucketed all-reduce)")
+            _lib.check(_lib.lib().m2f_plan_backward(plan.handle, self._arena.data_ptr(), self._shadow.data_ptr(), plan.ws.data_ptr(),
+                                                    dlogits.data_ptr(), target.data_ptr(), _stream()), "plan_backward")
         self.launches += 1
         if fresh:
             for p, o, n in self._flat:
@@ -297,6 +320,13 @@ class M2FNet(nn.Module):
                     p.grad = g.clone()
                 else:
                     p.grad.add_(g)
+        if self._done_hook is not None:
+            self._done_hook()
+
+    def set_grad_hooks(self, on_bucket, bucket_floats: int, on_done=None):
+        """Data-parallel plumbing: `on_bucket(lo, hi)` is called (host side, in stream order) each time the gradient
+        arena range [lo, hi) is final; `on_done()` once the backward has been enqueued and `p.grad` views are attached."""
+        self._bucket_hook, self._bucket_floats, self._done_hook = on_bucket, int(bucket_floats), on_done
 
     def forward(self, text, audio, mask):
         """text [B,S,Dt], audio [B,S,Da] fp32, mask [B,S] bool (True = padding) -> logits [B,S,C] fp32

@@ -1,0 +1,63 @@
+"""Fused Adam over the model's flat parameter arena: one kernel per step instead of
+torch.optim.Adam's foreach launches over 186 tensors.  Same update rule as the reference's optimizer,
+`torch.optim.Adam(model.parameters(), lr, weight_decay=wd)` (src/train.py:56,231): L2 decay folded into the gradient,
+bias-corrected moments, eps 1e-8.  `state_dict()` has torch.optim.Adam's layout (step / exp_avg / exp_avg_sq per
+parameter), so checkpoints interchange with the reference's `optimizer_state_dict` (src/train.py:163-168)."""
+from __future__ import annotations
+
+import torch
+
+from . import _lib
+
+
+class FusedAdam(torch.optim.Optimizer):
+    def __init__(self, model, lr=1e-3, betas=(0.9, 0.999), eps=1e-8, weight_decay=0.0, grad_scale: float = 1.0):
+        self.model = getattr(model, "module", model)
+        params = [p for p, _, _ in self.model._flat]
+        super().__init__(params, dict(lr=lr, betas=betas, eps=eps, weight_decay=weight_decay))
+        self.grad_scale = float(grad_scale)
+        self._t = 0
+        self._bind()
+
+    def _bind(self):
+        arena = self.model.flat_parameters()
+        if not arena.is_cuda:
+            raise RuntimeError("FusedAdam needs the model on the GPU (there is no CPU path)")
+        self._m = torch.zeros_like(arena)
+        self._v = torch.zeros_like(arena)
+        for p, o, n in self.model._flat:
+            self.state[p] = {"step": torch.tensor(float(self._t)), "exp_avg": self._m[o:o + n].view(p.shape),
+                             "exp_avg_sq": self._v[o:o + n].view(p.shape)}
+
+    @torch.no_grad()
+    def step(self, closure=None):
+        loss = closure() if closure is not None else None
+        g = self.model.flat_grads()
+        if g is None:
+            raise RuntimeError("FusedAdam.step(): no gradients (call backward first)")
+        grp = self.param_groups[0]
+        self._t += 1
+        arena = self.model.flat_parameters()
+        _lib.check(_lib.lib().m2f_adam_step(arena.data_ptr(), g.data_ptr(), self._m.data_ptr(), self._v.data_ptr(), arena.numel(),
+                                            float(grp["lr"]), float(grp["betas"][0]), float(grp["betas"][1]), float(grp["eps"]),
+                                            float(grp["weight_decay"]), self._t, self.grad_scale,
+                                            torch.cuda.current_stream().cuda_stream), "adam_step")
+        self.model._shadow_version = None  # the kernel wrote through raw pointers: the bf16 weight shadow is stale
+        return loss
+
+    def state_dict(self):
+        for st in self.state.values():
+            st["step"] = torch.tensor(float(self._t))
+        return super().state_dict()
+
+    def load_state_dict(self, sd):
+        super().load_state_dict(sd)
+        first = True
+        for p, o, n in self.model._flat:
+            st = self.state[p]
+            if first:
+                self._t = int(float(st["step"]))
+                first = False
+            self._m[o:o + n].view(p.shape).copy_(st["exp_avg"])
+            self._v[o:o + n].view(p.shape).copy_(st["exp_avg_sq"])
+            st["exp_avg"], st["exp_avg_sq"] = self._m[o:o + n].view(p.shape), self._v[o:o + n].view(p.shape)

@@ -1,0 +1,41 @@
+"""The C-ABI library loads on a CPU-only box and exports every symbol include/m2f_b200.h declares; the ctypes binding
+lists a prototype for each of them (no compute calls here)."""
+import ctypes
+import os
+import re
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def declared():
+    src = open(os.path.join(ROOT, "include", "m2f_b200.h")).read()
+    src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+    return sorted(set(re.findall(r"\b(m2f_[a-z0-9_]+)\s*\(", src)) - {"m2f_bucket_cb"})
+
+
+def test_header_declares_the_expected_surface():
+    names = declared()
+    for must in ("m2f_gemm", "m2f_attn_fwd", "m2f_attn_bwd", "m2f_ln_fwd", "m2f_ln_bwd", "m2f_ce_fwd_bwd", "m2f_plan_forward",
+                 "m2f_plan_backward", "m2f_plan_backward_bucketed", "m2f_adam_step", "m2f_last_error"):
+        assert must in names
+
+
+def test_library_exports_every_declared_symbol(pkg):
+    lib = ctypes.CDLL(pkg._lib.LIB_PATH)
+    for n in declared():
+        assert hasattr(lib, n), n
+
+
+def test_binding_covers_every_declared_symbol(pkg):
+    assert sorted(pkg._lib.PROTOTYPES) == declared()
+    L = pkg._lib.lib()
+    assert L.m2f_abi_version() == 1
+    assert L.m2f_launch_count() == 0
+
+
+def test_errors_are_codes_with_messages(pkg):
+    L = pkg._lib.lib()
+    cfg = pkg._lib.ModelCfg()  # everything disabled
+    h = ctypes.c_void_p()
+    rc = L.m2f_model_create(ctypes.byref(cfg), ctypes.byref(h))
+    assert rc == -1 and b"At least one of audio and text must be enabled!" in L.m2f_last_error()
