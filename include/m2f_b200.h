@@ -57,7 +57,7 @@ typedef struct {
 /* Epilogue applied to each accumulator element v = sum_k A[m,k] B[n,k], in this order:
  *   v += bias[n]; if relu: v = max(v,0); if gate: v = gate[m,n] > 0 ? v*gate_scale : 0;
  *   if drop_p > 0: v = keep(seed,step,site, m*drop_ld+n) ? v/(1-p) : 0; v += resid[m,n];
- *   if accumulate: v += out_f32[m,n];  then stored to out_f32 and/or out_planes. */
+ *   if accumulate: v += out_f32[m,n];  then stored to out_f32 and/or out_planes; colsum[n] += v (atomic). */
 typedef struct {
     const float* bias;
     int32_t relu;
@@ -75,6 +75,7 @@ typedef struct {
     float* out_f32;
     int64_t out_f32_ld;
     m2f_planes_t out_planes; /* ptr == NULL: none */
+    float* colsum;           /* nullable: colsum[n] += sum over rows m < M of the stored value (bias gradients) */
 } m2f_epilogue_t;
 
 int m2f_abi_version(void);

@@ -32,7 +32,7 @@ class Epilogue(C.Structure):
                 ("gate", C.c_void_p), ("gate_ld", C.c_int64), ("gate_scale", C.c_float), ("drop_p", C.c_float),
                 ("seed", C.c_uint64), ("step", C.c_uint64), ("site", C.c_uint32), ("_pad", C.c_int32),
                 ("drop_ld", C.c_int64), ("resid", C.c_void_p), ("resid_ld", C.c_int64),
-                ("out_f32", C.c_void_p), ("out_f32_ld", C.c_int64), ("out_planes", Planes)]
+                ("out_f32", C.c_void_p), ("out_f32_ld", C.c_int64), ("out_planes", Planes), ("colsum", C.c_void_p)]
 
 
 class ModalityCfg(C.Structure):

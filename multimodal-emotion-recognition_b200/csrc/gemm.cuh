@@ -10,6 +10,8 @@ constexpr int UMMA_K = 16;
 constexpr int MAX_SEGS = 4;
 constexpr int MAX_PROD = 6;
 constexpr int GEMM_THREADS = 192;
+constexpr int EPI_STG_LD = 36;                    // floats per staged accumulator row (32 + 4: conflict-free float4 rows)
+constexpr int EPI_STG_FLOATS = 32 * EPI_STG_LD;   // one epilogue warp's staging tile
 
 struct GemmParams {
     int M, N;
@@ -31,6 +33,10 @@ struct GemmParams {
     int64_t resid_ld;
     float* out_f32;
     int64_t out_f32_ld;
+    float* colsum;
+    int vec4;
+    int dbg;
+    unsigned long long* trace;  // debug: 8 timestamps per CTA (nullptr in production)
     __nv_bfloat16* out_pl;
     int64_t out_pl_ld, out_pl_stride;
     int out_pl_n;

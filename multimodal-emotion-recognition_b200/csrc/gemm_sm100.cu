@@ -19,19 +19,203 @@
 
 namespace m2f {
 
+static unsigned long long* g_trace = nullptr;
+static int g_dbg = 0;  // experiment switches (m2f_debug_set_gemm_flags): 1 skip global stores, 2 skip tcgen05.ld, 4 skip staging  // set through m2f_debug_set_gemm_trace (profiling aid)
+
+__device__ __forceinline__ unsigned long long gtimer() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t)::"memory");
+    return t;
+}
+#define M2F_TRACE(slot)                                                                                          \
+    do {                                                                                                         \
+        if (p.trace) p.trace[(size_t)(blockIdx.y * gridDim.x + blockIdx.x) * 8 + (slot)] = gtimer();             \
+    } while (0)
+
 template <int BLOCK_N>
 struct GemmCfg {
     static constexpr int A_BYTES = BLOCK_M * BLOCK_K * 2;
     static constexpr int B_BYTES = BLOCK_N * BLOCK_K * 2;
     static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
-    static constexpr int STAGES = (BLOCK_N == 256) ? 4 : (BLOCK_N == 128 ? 6 : 8);
+    // 96 KB of operand ring per CTA, so that TWO CTAs are co-resident per SM: one CTA's epilogue overlaps the other's
+    // prologue / main loop (TMEM: 2 x BLOCK_N <= 512 columns)
+    static constexpr int STAGES = (96 * 1024) / STAGE_BYTES;
     static constexpr int BAR_BYTES = (2 * STAGES + 1) * 8 + 16;
     static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + BAR_BYTES + 1024;  // + alignment slack
     static constexpr int TMEM_COLS = BLOCK_N < 32 ? 32 : BLOCK_N;
+    static_assert(STAGES >= 2, "pipeline too shallow");
+    static_assert(4 * EPI_STG_FLOATS * 4 <= STAGES * STAGE_BYTES, "epilogue staging must fit in the operand ring");
 };
 
+__device__ __forceinline__ uint2 pack_bf16x4(const float v[4]) {
+    const __nv_bfloat162 a = __floats2bfloat162_rn(v[0], v[1]);
+    const __nv_bfloat162 b = __floats2bfloat162_rn(v[2], v[3]);
+    uint2 r;
+    r.x = *reinterpret_cast<const uint32_t*>(&a);
+    r.y = *reinterpret_cast<const uint32_t*>(&b);
+    return r;
+}
+__device__ __forceinline__ void unpack_sub(const uint2 h, float v[4]) {  // v -= float(h)
+    const __nv_bfloat162 a = *reinterpret_cast<const __nv_bfloat162*>(&h.x);
+    const __nv_bfloat162 b = *reinterpret_cast<const __nv_bfloat162*>(&h.y);
+    v[0] -= __low2float(a); v[1] -= __high2float(a); v[2] -= __low2float(b); v[3] -= __high2float(b);
+}
+
+// Epilogue parameters held in registers by the epilogue warps (loaded once, before the accumulator wait).
+struct EpiRegs {
+    const float* bias;
+    const __nv_bfloat16* gate;
+    const float* resid;
+    float* out_f32;
+    __nv_bfloat16* out_pl;
+    float* colsum;
+    int64_t gate_ld, resid_ld, out_f32_ld, out_pl_ld, out_pl_stride, drop_ld;
+    float gate_scale, floor_;
+    int M, N, out_pl_n, accumulate, vec4, drop_on;
+};
+
+__device__ __forceinline__ float4 lds128(uint32_t addr) {
+    float4 v;
+    asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(addr));
+    return v;
+}
+__device__ __forceinline__ void sts128(uint32_t addr, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
+    asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
+}
+
+// Epilogue of one 32-row x 32-column chunk.  `stg` (shared-space address) holds the raw accumulators
+// [32 rows][EPI_STG_LD floats]; lane l handles columns 4*(l%8)..+3 of rows it*4 + l/8, it = 0..7, so every global
+// access of the warp covers 4 full 128-byte rows.  Fast path in phases (all shared loads, all global loads, math,
+// all stores) so that the memory latencies of the 8 row groups overlap; the rare ragged path goes element by element.
+__device__ __forceinline__ void epilogue_chunk(const EpiRegs& e, const Drop& drop, uint32_t stg, int lane, int64_t m0, int n0) {
+    const int cg = (lane & 7) * 4;
+    const int n = n0 + cg;
+    const int r0 = lane >> 3;
+    const bool vec = e.vec4 && (n + 4 <= e.N);
+    float cs0 = 0.f, cs1 = 0.f, cs2 = 0.f, cs3 = 0.f;
+    if (vec) {
+        float4 v[8];
+#pragma unroll
+        for (int it = 0; it < 8; ++it) v[it] = lds128(stg + (uint32_t)(((it * 4 + r0) * EPI_STG_LD + cg) * 4));
+        bool ok[8];
+#pragma unroll
+        for (int it = 0; it < 8; ++it) ok[it] = (m0 + it * 4 + r0) < e.M;
+        if (e.bias) {
+            const float4 b = *reinterpret_cast<const float4*>(e.bias + n);
+#pragma unroll
+            for (int it = 0; it < 8; ++it) { v[it].x += b.x; v[it].y += b.y; v[it].z += b.z; v[it].w += b.w; }
+        }
+#pragma unroll
+        for (int it = 0; it < 8; ++it) {
+            v[it].x = fmaxf(v[it].x, e.floor_); v[it].y = fmaxf(v[it].y, e.floor_);
+            v[it].z = fmaxf(v[it].z, e.floor_); v[it].w = fmaxf(v[it].w, e.floor_);
+        }
+        if (e.gate) {
+            uint2 g[8];
+#pragma unroll
+            for (int it = 0; it < 8; ++it)
+                g[it] = ok[it] ? *reinterpret_cast<const uint2*>(e.gate + (m0 + it * 4 + r0) * e.gate_ld + n) : make_uint2(0u, 0u);
+#pragma unroll
+            for (int it = 0; it < 8; ++it) {
+                const __nv_bfloat162 g0 = *reinterpret_cast<const __nv_bfloat162*>(&g[it].x);
+                const __nv_bfloat162 g1 = *reinterpret_cast<const __nv_bfloat162*>(&g[it].y);
+                v[it].x = __low2float(g0) > 0.f ? v[it].x * e.gate_scale : 0.f;
+                v[it].y = __high2float(g0) > 0.f ? v[it].y * e.gate_scale : 0.f;
+                v[it].z = __low2float(g1) > 0.f ? v[it].z * e.gate_scale : 0.f;
+                v[it].w = __high2float(g1) > 0.f ? v[it].w * e.gate_scale : 0.f;
+            }
+        }
+        if (e.drop_on) {
+#pragma unroll
+            for (int it = 0; it < 8; ++it) {
+                float dm[4];
+                drop_mult4(drop, (uint64_t)((m0 + it * 4 + r0) * e.drop_ld + n) >> 2, dm);
+                v[it].x *= dm[0]; v[it].y *= dm[1]; v[it].z *= dm[2]; v[it].w *= dm[3];
+            }
+        }
+        if (e.resid) {
+            float4 q[8];
+#pragma unroll
+            for (int it = 0; it < 8; ++it)
+                q[it] = ok[it] ? *reinterpret_cast<const float4*>(e.resid + (m0 + it * 4 + r0) * e.resid_ld + n) : make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+            for (int it = 0; it < 8; ++it) { v[it].x += q[it].x; v[it].y += q[it].y; v[it].z += q[it].z; v[it].w += q[it].w; }
+        }
+        if (e.out_f32) {
+            if (e.accumulate) {
+                float4 q[8];
+#pragma unroll
+                for (int it = 0; it < 8; ++it)
+                    q[it] = ok[it] ? *reinterpret_cast<const float4*>(e.out_f32 + (m0 + it * 4 + r0) * e.out_f32_ld + n) : make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+                for (int it = 0; it < 8; ++it) { v[it].x += q[it].x; v[it].y += q[it].y; v[it].z += q[it].z; v[it].w += q[it].w; }
+            }
+#pragma unroll
+            for (int it = 0; it < 8; ++it)
+                if (ok[it]) *reinterpret_cast<float4*>(e.out_f32 + (m0 + it * 4 + r0) * e.out_f32_ld + n) = v[it];
+        }
+#pragma unroll
+        for (int it = 0; it < 8; ++it)
+            if (ok[it]) { cs0 += v[it].x; cs1 += v[it].y; cs2 += v[it].z; cs3 += v[it].w; }
+        if (e.out_pl) {  // hi / mid / lo bf16 planes, registers only
+            for (int pl = 0; pl < e.out_pl_n; ++pl) {
+                __nv_bfloat16* base = e.out_pl + pl * e.out_pl_stride + n;
+#pragma unroll
+                for (int it = 0; it < 8; ++it) {
+                    float t[4] = {v[it].x, v[it].y, v[it].z, v[it].w};
+                    const uint2 h = pack_bf16x4(t);
+                    if (ok[it]) *reinterpret_cast<uint2*>(base + (m0 + it * 4 + r0) * e.out_pl_ld) = h;
+                    unpack_sub(h, t);  // residual feeds the next plane
+                    v[it] = make_float4(t[0], t[1], t[2], t[3]);
+                }
+            }
+        }
+    } else if (n < e.N) {
+        // rare: ragged N or unaligned leading dimensions, element by element
+#pragma unroll 1
+        for (int it = 0; it < 8; ++it) {
+            const int64_t m = m0 + it * 4 + r0;
+            if (m >= e.M) continue;
+            const float4 acc = lds128(stg + (uint32_t)(((it * 4 + r0) * EPI_STG_LD + cg) * 4));
+            const float a4[4] = {acc.x, acc.y, acc.z, acc.w};
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                const int nn = n + i;
+                float x = 0.f;
+                if (nn < e.N) {
+                    x = a4[i];
+                    if (e.bias) x += e.bias[nn];
+                    x = fmaxf(x, e.floor_);
+                    if (e.gate) x = __bfloat162float(e.gate[m * e.gate_ld + nn]) > 0.f ? x * e.gate_scale : 0.f;
+                    if (e.drop_on) x *= drop_mult1(drop, (uint64_t)(m * e.drop_ld + nn));
+                    if (e.resid) x += e.resid[m * e.resid_ld + nn];
+                    if (e.out_f32) {
+                        float* o = e.out_f32 + m * e.out_f32_ld + nn;
+                        if (e.accumulate) x += *o;
+                        *o = x;
+                    }
+                    if (e.out_pl) store_planes(e.out_pl, e.out_pl_stride, e.out_pl_n, m * e.out_pl_ld + nn, x);
+                }
+                if (i == 0) cs0 += x; else if (i == 1) cs1 += x; else if (i == 2) cs2 += x; else cs3 += x;
+            }
+        }
+    }
+    if (e.colsum) {  // bias gradient: column sums of what was stored, 4 row-groups of the warp folded first
+        cs0 += __shfl_xor_sync(0xffffffffu, cs0, 8);  cs0 += __shfl_xor_sync(0xffffffffu, cs0, 16);
+        cs1 += __shfl_xor_sync(0xffffffffu, cs1, 8);  cs1 += __shfl_xor_sync(0xffffffffu, cs1, 16);
+        cs2 += __shfl_xor_sync(0xffffffffu, cs2, 8);  cs2 += __shfl_xor_sync(0xffffffffu, cs2, 16);
+        cs3 += __shfl_xor_sync(0xffffffffu, cs3, 8);  cs3 += __shfl_xor_sync(0xffffffffu, cs3, 16);
+        if (lane < 8) {
+            if (n < e.N) atomicAdd(e.colsum + n, cs0);
+            if (n + 1 < e.N) atomicAdd(e.colsum + n + 1, cs1);
+            if (n + 2 < e.N) atomicAdd(e.colsum + n + 2, cs2);
+            if (n + 3 < e.N) atomicAdd(e.colsum + n + 3, cs3);
+        }
+    }
+}
+
 template <int BLOCK_N, bool A_MN, bool B_MN>
-__global__ void __launch_bounds__(GEMM_THREADS, 1)
+__global__ void __launch_bounds__(GEMM_THREADS, 2)
 gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b, const GemmParams p) {
     using Cfg = GemmCfg<BLOCK_N>;
     constexpr int STAGES = Cfg::STAGES;
@@ -47,6 +231,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ C
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
     const int m_blk = blockIdx.x, n_blk = blockIdx.y;
+    if (threadIdx.x == 0) M2F_TRACE(0);
 
     if (warp == 0 && lane == 0) {
         ptx::prefetch_tensormap(&tma_a);
@@ -65,6 +250,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ C
     __syncthreads();
     ptx::tcgen05_fence_after();
     const uint32_t tmem_base = *tmem_slot;
+    if (threadIdx.x == 0) M2F_TRACE(1);
 
     if (warp == 0) {
         // ------------------------------------------------------------------ TMA producer
@@ -102,6 +288,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ C
                 }
             }
         }
+        __syncwarp();
     } else if (warp == 1) {
         // ------------------------------------------------------------------ MMA issuer
         if (ptx::elect_one()) {
@@ -116,6 +303,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ C
                 const int stage = it % STAGES;
                 const uint32_t phase = (it / STAGES) & 1;
                 ptx::mbar_wait(&full_bar[stage], phase);
+                if (it == 0) M2F_TRACE(2);
                 ptx::tcgen05_fence_after();
                 const uint32_t sa = ptx::smem_u32(smem_a + stage * Cfg::A_BYTES);
                 const uint32_t sb = ptx::smem_u32(smem_b + stage * Cfg::B_BYTES);
@@ -128,93 +316,54 @@ gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ C
                 ptx::umma_commit(&empty_bar[stage]);  // frees the smem slot once these MMAs retire
             }
             ptx::umma_commit(tmem_full_bar);
+            M2F_TRACE(3);
         }
+        __syncwarp();
     } else {
         // ------------------------------------------------------------------ epilogue
+        // TMEM -> registers (thread = row) -> shared (transpose) -> registers (lane = 4 columns) -> global, coalesced.
+        // The operand ring is free by now: the accumulator-ready commit fires after the last MMA has read it.
+        EpiRegs e;
+        e.bias = p.bias; e.gate = p.gate; e.resid = p.resid; e.out_f32 = p.out_f32; e.out_pl = p.out_pl; e.colsum = p.colsum;
+        e.gate_ld = p.gate_ld; e.resid_ld = p.resid_ld; e.out_f32_ld = p.out_f32_ld; e.out_pl_ld = p.out_pl_ld;
+        e.out_pl_stride = p.out_pl_stride; e.drop_ld = p.drop_ld; e.gate_scale = p.gate_scale; e.floor_ = p.relu ? 0.f : -INFINITY;
+        e.M = p.M; e.N = p.N; e.out_pl_n = p.out_pl_n; e.accumulate = p.accumulate; e.vec4 = p.vec4; e.drop_on = p.drop.enabled;
+        const Drop drop = p.drop;
         ptx::mbar_wait(tmem_full_bar, 0);
+        if (threadIdx.x == 64) M2F_TRACE(4);
         ptx::tcgen05_fence_after();
         const int lg = warp & 3;  // TMEM lane group this warp may access
-        const int64_t m = (int64_t)m_blk * BLOCK_M + lg * 32 + lane;
-        const bool row_ok = m < p.M;
-        const bool vec4 = (p.out_f32 == nullptr || (p.out_f32_ld & 3) == 0) && (p.resid == nullptr || (p.resid_ld & 3) == 0) &&
-                          ((p.drop_ld & 3) == 0);
+        const uint32_t stg = ptx::smem_u32(smem) + (uint32_t)(lg * EPI_STG_FLOATS * 4);
+        const int64_t m0 = (int64_t)m_blk * BLOCK_M + lg * 32;
+        if (m0 < p.M) {
 #pragma unroll 1
-        for (int c = 0; c < BLOCK_N / 32; ++c) {
-            const int n0 = n_blk * BLOCK_N + c * 32;
-            if (n0 >= p.N) break;  // warp-uniform
-            uint32_t r[32];
-            ptx::tmem_ld_32x32(tmem_base + ((uint32_t)(lg * 32) << 16) + (uint32_t)(c * 32), r);
-            ptx::tmem_ld_wait();
-            const bool full = (n0 + 32 <= p.N) && vec4;
-            if (row_ok) {
+            for (int c = 0; c < BLOCK_N / 32; ++c) {
+                const int n0 = n_blk * BLOCK_N + c * 32;
+                if (n0 >= p.N) break;  // warp-uniform
+                uint32_t r[32];
+                long long c0 = 0, c1 = 0, c2 = 0;
+                if (p.trace) c0 = clock64();
+                ptx::tmem_ld_32x32(tmem_base + ((uint32_t)(lg * 32) << 16) + (uint32_t)(c * 32), r);
+                ptx::tmem_ld_wait();
+                if (p.trace) c1 = clock64();
+                __syncwarp();
 #pragma unroll
-            for (int j = 0; j < 32; j += 4) {
-                float v[4];
-#pragma unroll
-                for (int i = 0; i < 4; ++i) v[i] = __uint_as_float(r[j + i]);
-                const int n = n0 + j;
-                if (full) {
-                    if (p.bias) {
-                        const float4 b = *reinterpret_cast<const float4*>(p.bias + n);
-                        v[0] += b.x; v[1] += b.y; v[2] += b.z; v[3] += b.w;
-                    }
-                    if (p.relu) {
-#pragma unroll
-                        for (int i = 0; i < 4; ++i) v[i] = fmaxf(v[i], 0.f);
-                    }
-                    if (p.gate) {
-                        const uint2 raw = *reinterpret_cast<const uint2*>(p.gate + m * p.gate_ld + n);
-                        const __nv_bfloat162 g0 = *reinterpret_cast<const __nv_bfloat162*>(&raw.x);
-                        const __nv_bfloat162 g1 = *reinterpret_cast<const __nv_bfloat162*>(&raw.y);
-                        v[0] = __low2float(g0) > 0.f ? v[0] * p.gate_scale : 0.f;
-                        v[1] = __high2float(g0) > 0.f ? v[1] * p.gate_scale : 0.f;
-                        v[2] = __low2float(g1) > 0.f ? v[2] * p.gate_scale : 0.f;
-                        v[3] = __high2float(g1) > 0.f ? v[3] * p.gate_scale : 0.f;
-                    }
-                    if (p.drop.enabled) {
-                        float dm[4];
-                        drop_mult4(p.drop, (uint64_t)(m * p.drop_ld + n) >> 2, dm);
-#pragma unroll
-                        for (int i = 0; i < 4; ++i) v[i] *= dm[i];
-                    }
-                    if (p.resid) {
-                        const float4 q = *reinterpret_cast<const float4*>(p.resid + m * p.resid_ld + n);
-                        v[0] += q.x; v[1] += q.y; v[2] += q.z; v[3] += q.w;
-                    }
-                    if (p.out_f32) {
-                        float4* o = reinterpret_cast<float4*>(p.out_f32 + m * p.out_f32_ld + n);
-                        if (p.accumulate) {
-                            const float4 q = *o;
-                            v[0] += q.x; v[1] += q.y; v[2] += q.z; v[3] += q.w;
-                        }
-                        *o = make_float4(v[0], v[1], v[2], v[3]);
-                    }
-                    if (p.out_pl) store_planes4(p.out_pl, p.out_pl_stride, p.out_pl_n, m * p.out_pl_ld + n, v);
-                } else {
-#pragma unroll
-                    for (int i = 0; i < 4; ++i) {
-                        const int nn = n + i;
-                        if (nn >= p.N) break;
-                        float x = v[i];
-                        if (p.bias) x += p.bias[nn];
-                        if (p.relu) x = fmaxf(x, 0.f);
-                        if (p.gate) x = __bfloat162float(p.gate[m * p.gate_ld + nn]) > 0.f ? x * p.gate_scale : 0.f;
-                        if (p.drop.enabled) x *= drop_mult1(p.drop, (uint64_t)(m * p.drop_ld + nn));
-                        if (p.resid) x += p.resid[m * p.resid_ld + nn];
-                        if (p.out_f32) {
-                            float* o = p.out_f32 + m * p.out_f32_ld + nn;
-                            if (p.accumulate) x += *o;
-                            *o = x;
-                        }
-                        if (p.out_pl) store_planes(p.out_pl, p.out_pl_stride, p.out_pl_n, m * p.out_pl_ld + nn, x);
-                    }
+                for (int j = 0; j < 8; ++j)
+                    sts128(stg + (uint32_t)((lane * EPI_STG_LD + j * 4) * 4), r[4 * j], r[4 * j + 1], r[4 * j + 2], r[4 * j + 3]);
+                __syncwarp();
+                if (p.trace) c2 = clock64();
+                epilogue_chunk(e, drop, stg, lane, m0, n0);
+                if (p.trace && threadIdx.x == 64 && c < 2) {
+                    unsigned long long* t2 = p.trace + (size_t)4096 * 8 + (size_t)(blockIdx.y * gridDim.x + blockIdx.x) * 8 + c * 4;
+                    t2[0] = c1 - c0; t2[1] = c2 - c1; t2[2] = clock64() - c2; t2[3] = c0;
                 }
             }
-            }  // row_ok
         }
         ptx::tcgen05_fence_before();
+        if (threadIdx.x == 64) M2F_TRACE(5);
     }
     __syncthreads();
+    if (threadIdx.x == 0) M2F_TRACE(6);
     if (warp == 2) {
         ptx::tcgen05_fence_after();
         ptx::tmem_dealloc(tmem_base, Cfg::TMEM_COLS);
@@ -341,6 +490,10 @@ int gemm_fill_params(GemmParams& p, const m2f_planes_t* A, int a_mn, const m2f_p
     p.out_pl_ld = e->out_planes.ld;
     p.out_pl_stride = e->out_planes.plane_stride;
     p.out_pl_n = e->out_planes.planes;
+    p.trace = g_trace;
+    p.dbg = g_dbg;
+    p.colsum = e->colsum;
+    p.vec4 = (p.out_f32 == nullptr || (p.out_f32_ld & 3) == 0) && (p.resid == nullptr || (p.resid_ld & 3) == 0) && ((p.drop_ld & 3) == 0);
     M2F_REQUIRE(p.out_f32 || p.out_pl, M2F_ERR_ARG, "gemm: no output given");
     M2F_REQUIRE(!p.out_pl || (p.out_pl_n >= 1 && p.out_pl_n <= 3 && (p.out_pl_ld % 4) == 0 &&
                               (reinterpret_cast<uintptr_t>(p.out_pl) & 7) == 0 && (p.out_pl_n == 1 || (p.out_pl_stride % 4) == 0)),
@@ -372,6 +525,10 @@ int gemm_launch(const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& 
 }
 
 }  // namespace m2f
+
+// profiling aid (not part of the public header): 8 x uint64 globaltimer stamps per CTA are written to `buf`
+extern "C" void m2f_debug_set_gemm_flags(int f) { m2f::g_dbg = f; }
+extern "C" void m2f_debug_set_gemm_trace(void* buf) { m2f::g_trace = reinterpret_cast<unsigned long long*>(buf); }
 
 extern "C" int m2f_gemm(const m2f_planes_t* A, int a_mn_major, const m2f_planes_t* B, int b_mn_major,
                         const m2f_kseg_t* segs, int nsegs, int64_t M, int64_t N, const m2f_epilogue_t* epi,

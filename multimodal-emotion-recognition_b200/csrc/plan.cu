@@ -493,6 +493,7 @@ struct Epi {
     Epi& resid(const float* r, int64_t ld) { e.resid = r; e.resid_ld = ld; return *this; }
     Epi& f32(float* o, int64_t ld, bool acc = false) { e.out_f32 = o; e.out_f32_ld = ld; e.accumulate = acc ? 1 : 0; return *this; }
     Epi& pl(const m2f_planes_t& o) { e.out_planes = o; return *this; }
+    Epi& colsum(float* cs) { e.colsum = cs; return *this; }
     operator const m2f_epilogue_t&() const { return e; }
 };
 
@@ -632,7 +633,7 @@ static int backward_modality(Ctx& c, Modality& mo, const uint8_t* key_pad, const
     const int64_t gld = p->gG.ld;
     // projection: dW, db, and g = dropmask0(dproj . Wp)
     m2f_planes_t xp = c.pv(mo.xout_pl[mo.T - 1]);
-    M2F_TRY(lin_wgrad(c, dproj, xp, c.grd(mo.proj.w_off), mo.proj.in, c.grd(mo.proj.b_off), mo.proj.out, mo.proj.in));
+    M2F_TRY(lin_wgrad(c, dproj, xp, c.grd(mo.proj.w_off), mo.proj.in, nullptr, mo.proj.out, mo.proj.in));  // db: by dproj's producer
     c.done_down_to(mo.proj.w_off);
     M2F_TRY(c.gemm(dproj, false, c.pv(mo.proj.w), true, M, D, Epi().drop(pd, seed, step, M2F_SITE_MOD(mo.idx, 0), D).f32(G, gld)));
     m2f_planes_t dxp = c.pv(p->dx_pl), dhp = c.pv(p->dh_pl), dop = c.pv(p->do_pl), dqkvp = c.pv(p->dqkv_pl);
@@ -652,8 +653,8 @@ static int backward_modality(Ctx& c, Modality& mo, const uint8_t* key_pad, const
                                M2F_SITE_ENC(mo.idx, t, l, 3), c.grd(e.g2), c.grd(e.be2), c.grd(e.w2.b_off), c.st));
             M2F_TRY(lin_wgrad(c, dxp, h, c.grd(e.w2.w_off), e.w2.in, nullptr, e.w2.out, e.w2.in));
             // dh = (d y2 . W2) * [h > 0] / (1-p)   (relu + dropout backward from the saved output)
-            M2F_TRY(c.gemm(dxp, false, c.pv(e.w2.w), true, M, e.w2.in, Epi().gate(h, inv_keep(pd)).pl(dhp)));
-            M2F_TRY(lin_wgrad(c, dhp, x1p, c.grd(e.w1.w_off), e.w1.in, c.grd(e.w1.b_off), e.w1.out, e.w1.in));
+            M2F_TRY(c.gemm(dxp, false, c.pv(e.w2.w), true, M, e.w2.in, Epi().gate(h, inv_keep(pd)).pl(dhp).colsum(c.grd(e.w1.b_off))));
+            M2F_TRY(lin_wgrad(c, dhp, x1p, c.grd(e.w1.w_off), e.w1.in, nullptr, e.w1.out, e.w1.in));
             // A = d x1 = dh . W1 + d y2
             M2F_TRY(c.gemm(dhp, false, c.pv(e.w1.w), true, M, D, Epi().resid(Bq, gld).f32(A, gld)));
             // LN1: A -> Bq = d y1, dxp = dropmask1(d y1), dbo += colsum
@@ -706,11 +707,12 @@ static int backward_all(Ctx& c, const uint8_t* key_pad, const float* dlogits) {
     for (int j = n_lin - 1; j >= 0; --j) {
         Lin& L = md->cls[j];
         m2f_planes_t in = (j == 0) ? zc : c.pv(p->cls_h[j - 1]);
-        M2F_TRY(lin_wgrad(c, d_cur, in, c.grd(L.w_off), L.in, c.grd(L.b_off), L.out, L.in));
+        // bias gradients ride in the epilogue of the GEMM that produces dY; only dlogits comes from elsewhere
+        M2F_TRY(lin_wgrad(c, d_cur, in, c.grd(L.w_off), L.in, j == n_lin - 1 ? c.grd(L.b_off) : nullptr, L.out, L.in));
         if (j > 0) {
             m2f_planes_t dn = c.pv((j & 1) ? p->dcls_a : p->dcls_b);
             const float sc = (j == n_lin - 1) ? inv_keep(pd) : 1.f;  // only the last hidden layer has dropout
-            M2F_TRY(c.gemm(d_cur, false, c.pv(L.w), true, M, L.in, Epi().gate(in, sc).pl(dn)));
+            M2F_TRY(c.gemm(d_cur, false, c.pv(L.w), true, M, L.in, Epi().gate(in, sc).pl(dn).colsum(c.grd(md->cls[j - 1].b_off))));
             d_cur = dn;
         } else if (md->both) {
             m2f_planes_t w = c.pv(L.w);
@@ -719,14 +721,18 @@ static int backward_all(Ctx& c, const uint8_t* key_pad, const float* dlogits) {
                 M2F_TRY(c.gemm(d_cur, false, Ctx::cols(w, 0, Df), true, M, Df,
                                Epi().drop(pd, seed, step, M2F_SITE_MOD(0, 1), Df).f32(c.f32(p->ga_f32), p->ga_f32.ld)));
                 // text half: gradient w.r.t. the last fusion linear's pre-activation
-                M2F_TRY(c.gemm(d_cur, false, Ctx::cols(w, Df, Df), true, M, Df, Epi().gate(Ctx::cols(zc, Df, Df), inv_keep(pd)).pl(dz)));
+                M2F_TRY(c.gemm(d_cur, false, Ctx::cols(w, Df, Df), true, M, Df,
+                               Epi().gate(Ctx::cols(zc, Df, Df), inv_keep(pd)).pl(dz).colsum(c.grd(p->fam.back().lin.b_off))));
             } else {
-                M2F_TRY(c.gemm(d_cur, false, Ctx::cols(w, 0, Df), true, M, Df, Epi().drop(pd, seed, step, M2F_SITE_MOD(0, 1), Df).pl(dproj[0])));
-                M2F_TRY(c.gemm(d_cur, false, Ctx::cols(w, Df, Df), true, M, Df, Epi().drop(pd, seed, step, M2F_SITE_MOD(1, 1), Df).pl(dproj[1])));
+                M2F_TRY(c.gemm(d_cur, false, Ctx::cols(w, 0, Df), true, M, Df,
+                               Epi().drop(pd, seed, step, M2F_SITE_MOD(0, 1), Df).pl(dproj[0]).colsum(c.grd(p->mod[0].proj.b_off))));
+                M2F_TRY(c.gemm(d_cur, false, Ctx::cols(w, Df, Df), true, M, Df,
+                               Epi().drop(pd, seed, step, M2F_SITE_MOD(1, 1), Df).pl(dproj[1]).colsum(c.grd(p->mod[1].proj.b_off))));
             }
         } else {
             const int mi = p->mod[0].enabled ? 0 : 1;
-            M2F_TRY(c.gemm(d_cur, false, c.pv(L.w), true, M, Df, Epi().drop(pd, seed, step, M2F_SITE_MOD(mi, 1), Df).pl(dproj[mi])));
+            M2F_TRY(c.gemm(d_cur, false, c.pv(L.w), true, M, Df,
+                           Epi().drop(pd, seed, step, M2F_SITE_MOD(mi, 1), Df).pl(dproj[mi]).colsum(c.grd(p->mod[mi].proj.b_off))));
         }
     }
     c.done_down_to(md->cls[0].w_off);
@@ -744,9 +750,9 @@ static int backward_all(Ctx& c, const uint8_t* key_pad, const float* dlogits) {
             m2f_planes_t t_in = (f == 0) ? c.pv(p->t0_pl) : Ctx::cols(u, Df, Df);  // the layer's text input
             m2f_planes_t wl = c.pv(fl.lin.w);
             // linear on the concat
-            M2F_TRY(lin_wgrad(c, dz_cur, u, c.grd(fl.lin.w_off), fl.lin.in, c.grd(fl.lin.b_off), fl.lin.out, fl.lin.in));
+            M2F_TRY(lin_wgrad(c, dz_cur, u, c.grd(fl.lin.w_off), fl.lin.in, nullptr, fl.lin.out, fl.lin.in));
             // left half of d u -> gradient w.r.t. the out-proj output (gate: relu(x) > 0)
-            M2F_TRY(c.gemm(dz_cur, false, Ctx::cols(wl, 0, Df), true, M, Df, Epi().gate(Ctx::cols(u, 0, Df), 1.f).pl(dxo)));
+            M2F_TRY(c.gemm(dz_cur, false, Ctx::cols(wl, 0, Df), true, M, Df, Epi().gate(Ctx::cols(u, 0, Df), 1.f).pl(dxo).colsum(c.grd(fl.wo.b_off))));
             // right half of d u -> first contribution to the gradient of this layer's text input, already in the
             // pre-activation space of its producer: previous fusion linear (relu + dropout: gate [t > 0] / (1-p))
             // or the text projection (cat-relu gate [t0 > 0], then the regenerated projection dropout mask)
@@ -757,7 +763,7 @@ static int backward_all(Ctx& c, const uint8_t* key_pad, const float* dlogits) {
                                Epi().gate(t_in, 1.f).drop(pd, seed, step, M2F_SITE_MOD(1, 1), Df).f32(gt, gt_ld)));
             }
             // attention out-proj
-            M2F_TRY(lin_wgrad(c, dxo, xo, c.grd(fl.wo.w_off), fl.wo.in, c.grd(fl.wo.b_off), fl.wo.out, fl.wo.in));
+            M2F_TRY(lin_wgrad(c, dxo, xo, c.grd(fl.wo.w_off), fl.wo.in, nullptr, fl.wo.out, fl.wo.in));
             M2F_TRY(c.gemm(dxo, false, c.pv(fl.wo.w), true, M, Df, Epi().pl(dattn)));
             m2f_planes_t q = Ctx::cols(qv, 0, Df), v = Ctx::cols(qv, Df, Df), k = Ctx::cols(kall, (int64_t)f * Df, Df);
             m2f_planes_t dq = Ctx::cols(dqv, 0, Df), dv = Ctx::cols(dqv, Df, Df), dk = Ctx::cols(dkall, (int64_t)f * Df, Df);
@@ -771,16 +777,17 @@ static int backward_all(Ctx& c, const uint8_t* key_pad, const float* dlogits) {
             c.done_down_to(fl.inw_off);
             // second + third contributions to the text-input gradient: [dq | dv] . [Wq; Wv], same gate, summed with gt
             if (f > 0) {
-                M2F_TRY(c.gemm(dqv, false, c.pv(fl.qv.w), true, M, Df, Epi().gate(t_in, inv_keep(pd)).resid(gt, gt_ld).pl(dz_other)));
+                M2F_TRY(c.gemm(dqv, false, c.pv(fl.qv.w), true, M, Df,
+                               Epi().gate(t_in, inv_keep(pd)).resid(gt, gt_ld).pl(dz_other).colsum(c.grd(p->fam[f - 1].lin.b_off))));
                 std::swap(dz_cur, dz_other);
             } else {
                 M2F_TRY(c.gemm(dqv, false, c.pv(fl.qv.w), true, M, Df,
-                               Epi().drop(pd, seed, step, M2F_SITE_MOD(1, 1), Df).resid(gt, gt_ld).pl(dproj[1])));
+                               Epi().drop(pd, seed, step, M2F_SITE_MOD(1, 1), Df).resid(gt, gt_ld).pl(dproj[1]).colsum(c.grd(p->mod[1].proj.b_off))));
             }
         }
         // audio: every layer's K projection + the classifier half, through the projection dropout mask
         M2F_TRY(c.gemm(dkall, false, c.pv(md->wk_all.w), true, M, Df,
-                       Epi().drop(pd, seed, step, M2F_SITE_MOD(0, 1), Df).resid(c.f32(p->ga_f32), p->ga_f32.ld).pl(dproj[0])));
+                       Epi().drop(pd, seed, step, M2F_SITE_MOD(0, 1), Df).resid(c.f32(p->ga_f32), p->ga_f32.ld).pl(dproj[0]).colsum(c.grd(p->mod[0].proj.b_off))));
     }
     // NOTE on the f == 0 text contribution through q/v: q and v read t0 itself (no cat-relu on that path), so only the
     // projection dropout mask applies -- handled above by not gating the [dq | dv] GEMM at f == 0.

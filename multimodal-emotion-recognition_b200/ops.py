@@ -73,7 +73,7 @@ def gemm(A: PlanesTensor, B: PlanesTensor, M: int, N: int, *, a_mn: bool = False
          segs: Optional[Sequence[Tuple[int, int, int]]] = None, bias: Optional[torch.Tensor] = None, relu: bool = False,
          gate: Optional[PlanesTensor] = None, gate_scale: float = 1.0, drop_p: float = 0.0, seed: int = 0, step: int = 0,
          site: int = 0, drop_ld: Optional[int] = None, resid: Optional[torch.Tensor] = None, out_f32: Optional[torch.Tensor] = None,
-         accumulate: bool = False, out_planes: Optional[PlanesTensor] = None):
+         accumulate: bool = False, out_planes: Optional[PlanesTensor] = None, colsum: Optional[torch.Tensor] = None):
     """D = A . B^T (+ fused epilogue), see m2f_gemm in include/m2f_b200.h."""
     _need_cuda(A.data, B.data, bias, resid, out_f32)
     if segs is None:
@@ -97,6 +97,7 @@ def gemm(A: PlanesTensor, B: PlanesTensor, M: int, N: int, *, a_mn: bool = False
         e.out_f32, e.out_f32_ld = out_f32.data_ptr(), out_f32.stride(0)
     if out_planes is not None:
         e.out_planes = out_planes.c()
+    e.colsum = _ptr(colsum)
     ca, cb = A.c(), B.c()
     _lib.check(_lib.lib().m2f_gemm(C.byref(ca), int(a_mn), C.byref(cb), int(b_mn), cs, len(segs), M, N, C.byref(e), _stream()), "gemm")
 

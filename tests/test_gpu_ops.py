@@ -88,6 +88,18 @@ def test_gemm_a_mn_b_k_major(ops):
     assert rel(out, A.float().double().T @ B.float().double().T) < 1e-5
 
 
+def test_gemm_colsum_ragged(ops):
+    M, N, K = 100, 136, 304
+    X, W = rnd(M, K, seed=21), rnd(N, K, seed=22)
+    A, B = ops.PlanesTensor.from_float(X, 1), ops.PlanesTensor.from_float(W, 1)
+    bias = rnd(N, seed=23)
+    outp = ops.PlanesTensor.empty(M, N, 3, "cuda", zero=True)
+    cs = torch.zeros(N, device="cuda")
+    ops.gemm(A, B, M, N, bias=bias, out_planes=outp, colsum=cs)
+    ref = A.float().double() @ B.float().double().T + bias.double()
+    assert rel(outp.float(), ref) < 1e-5 and rel(cs, ref.sum(0)) < 1e-5
+
+
 def test_gemm_two_k_segments(ops):
     """Fusion linear on cat(x, text) without materialising the concat (src/model.py:16-18)."""
     M, N, Df = 500, 256, 128
@@ -112,8 +124,9 @@ def test_gemm_epilogue_chain(ops, planes_out):
     gate = ops.PlanesTensor.from_float(gate_src, 1)
     out = prev.clone()
     outp = ops.PlanesTensor.empty(M, N, planes_out, "cuda", zero=True)
+    cs = torch.ones(N, device="cuda")
     ops.gemm(A, B, M, N, bias=bias, relu=True, gate=gate, gate_scale=1.25, drop_p=p, seed=77, step=3, site=0x1234,
-             resid=resid, out_f32=out, accumulate=True, out_planes=outp)
+             resid=resid, out_f32=out, accumulate=True, out_planes=outp, colsum=cs)
     keep = ops.dropout_mask(p, 77, 3, 0x1234, M * N, "cuda").reshape(M, N).double()
     v = A.float().double() @ B.float().double().T + bias.double()
     v = torch.relu(v)
@@ -121,6 +134,7 @@ def test_gemm_epilogue_chain(ops, planes_out):
     v = v * keep / (1 - p) + resid.double()
     assert rel(out, v + prev.double()) < 1e-5
     assert rel(outp.float(), v + prev.double()) < (4e-3 if planes_out == 1 else 1e-6)
+    assert rel(cs, (v + prev.double()).sum(0) + 1.0) < 1e-5  # bias-gradient column sums of the stored values
     frac = keep.mean().item()
     assert abs(frac - (1 - p)) < 0.01
 
