@@ -136,11 +136,13 @@ int m2f_attn_fwd(const m2f_planes_t* q, const m2f_planes_t* k, const m2f_planes_
                  const uint8_t* key_pad, int64_t B, int64_t S, int32_t H,
                  float drop_p, uint64_t seed, uint64_t step, uint32_t site,
                  const m2f_planes_t* o, void* stream);
-/* backward: recomputes P; d_o planes in, dq/dk/dv planes out. */
+/* backward: recomputes P; d_o planes in, dq/dk/dv planes out.  dbq/dbk/dbv (nullable, fp32 [H*hd]) += column sums of
+ * dq/dk/dv over all B*S rows: the in_proj_bias gradient slices (torch/nn/functional.py:5833-5873). */
 int m2f_attn_bwd(const m2f_planes_t* q, const m2f_planes_t* k, const m2f_planes_t* v,
                  const m2f_planes_t* d_o, const uint8_t* key_pad, int64_t B, int64_t S, int32_t H,
                  float drop_p, uint64_t seed, uint64_t step, uint32_t site,
-                 const m2f_planes_t* dq, const m2f_planes_t* dk, const m2f_planes_t* dv, void* stream);
+                 const m2f_planes_t* dq, const m2f_planes_t* dk, const m2f_planes_t* dv,
+                 float* dbq, float* dbk, float* dbv, void* stream);
 
 /* ---- K4: cross entropy, ignore_index = -1, label smoothing eps, optional class weights
  * (src/train.py:48-50,229).  logits fp32 [M,C] (row stride ld), target int64 [M].

@@ -664,8 +664,10 @@ static int backward_modality(Ctx& c, Modality& mo, const uint8_t* key_pad, const
             M2F_TRY(c.gemm(dxp, false, c.pv(e.wo.w), true, M, D, Epi().pl(dop)));
             m2f_planes_t q = Ctx::cols(qkv, 0, D), k = Ctx::cols(qkv, D, D), v = Ctx::cols(qkv, 2 * D, D);
             m2f_planes_t dq = Ctx::cols(dqkvp, 0, D), dk = Ctx::cols(dqkvp, D, D), dv = Ctx::cols(dqkvp, 2 * D, D);
-            M2F_TRY(m2f_attn_bwd(&q, &k, &v, &dop, key_pad, p->B, p->S, mo.H, pd, seed, step, M2F_SITE_ENC(mo.idx, t, l, 0), &dq, &dk, &dv, c.st));
-            M2F_TRY(lin_wgrad(c, dqkvp, in_pl, c.grd(e.qkv.w_off), e.qkv.in, c.grd(e.qkv.b_off), e.qkv.out, e.qkv.in));
+            float* dbqkv = c.grd(e.qkv.b_off);  // in_proj_bias gradient = column sums of [dq | dk | dv], folded into the attention backward
+            M2F_TRY(m2f_attn_bwd(&q, &k, &v, &dop, key_pad, p->B, p->S, mo.H, pd, seed, step, M2F_SITE_ENC(mo.idx, t, l, 0), &dq, &dk, &dv,
+                                 dbqkv, dbqkv + D, dbqkv + 2 * D, c.st));
+            M2F_TRY(lin_wgrad(c, dqkvp, in_pl, c.grd(e.qkv.w_off), e.qkv.in, nullptr, e.qkv.out, e.qkv.in));
             c.done_down_to(e.qkv.w_off);
             if (!first) {
                 // gradient w.r.t. the layer input = dqkv . Wqkv + d y1 ; at l == 0 it also joins the skip gradient in G
@@ -767,13 +769,14 @@ static int backward_all(Ctx& c, const uint8_t* key_pad, const float* dlogits) {
             M2F_TRY(c.gemm(dxo, false, c.pv(fl.wo.w), true, M, Df, Epi().pl(dattn)));
             m2f_planes_t q = Ctx::cols(qv, 0, Df), v = Ctx::cols(qv, Df, Df), k = Ctx::cols(kall, (int64_t)f * Df, Df);
             m2f_planes_t dq = Ctx::cols(dqv, 0, Df), dv = Ctx::cols(dqv, Df, Df), dk = Ctx::cols(dkall, (int64_t)f * Df, Df);
-            M2F_TRY(m2f_attn_bwd(&q, &k, &v, &dattn, key_pad, p->B, p->S, md->cfg.fam_heads, pd, seed, step, M2F_SITE_FAM(f, 0), &dq, &dk, &dv, c.st));
             // in-projection weight / bias gradients: rows [0,E) = q, [E,2E) = k, [2E,3E) = v of in_proj_weight
             float* dWin = c.grd(fl.inw_off);
             float* dbin = c.grd(fl.inb_off);
-            M2F_TRY(lin_wgrad(c, dq, t_in, dWin, Df, dbin, Df, Df));
-            M2F_TRY(lin_wgrad(c, dv, t_in, dWin + (int64_t)2 * Df * Df, Df, dbin + 2 * Df, Df, Df));
-            M2F_TRY(lin_wgrad(c, dk, a, dWin + (int64_t)Df * Df, Df, dbin + Df, Df, Df));
+            M2F_TRY(m2f_attn_bwd(&q, &k, &v, &dattn, key_pad, p->B, p->S, md->cfg.fam_heads, pd, seed, step, M2F_SITE_FAM(f, 0), &dq, &dk, &dv,
+                                 dbin, dbin + Df, dbin + 2 * Df, c.st));
+            M2F_TRY(lin_wgrad(c, dq, t_in, dWin, Df, nullptr, Df, Df));
+            M2F_TRY(lin_wgrad(c, dv, t_in, dWin + (int64_t)2 * Df * Df, Df, nullptr, Df, Df));
+            M2F_TRY(lin_wgrad(c, dk, a, dWin + (int64_t)Df * Df, Df, nullptr, Df, Df));
             c.done_down_to(fl.inw_off);
             // second + third contributions to the text-input gradient: [dq | dv] . [Wq; Wv], same gate, summed with gt
             if (f > 0) {

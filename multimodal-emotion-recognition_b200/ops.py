@@ -141,11 +141,11 @@ def attn_fwd(q: PlanesTensor, k: PlanesTensor, v: PlanesTensor, key_pad: torch.T
                                        C.byref(co), _stream()), "attn_fwd")
 
 
-def attn_bwd(q, k, v, d_o, key_pad, B, S, H, dq, dk, dv, drop_p=0.0, seed=0, step=0, site=0):
-    _need_cuda(key_pad)
+def attn_bwd(q, k, v, d_o, key_pad, B, S, H, dq, dk, dv, drop_p=0.0, seed=0, step=0, site=0, dbq=None, dbk=None, dbv=None):
+    _need_cuda(key_pad, dbq, dbk, dbv)
     cq, ck, cv, cdo, cdq, cdk, cdv = q.c(), k.c(), v.c(), d_o.c(), dq.c(), dk.c(), dv.c()
     _lib.check(_lib.lib().m2f_attn_bwd(C.byref(cq), C.byref(ck), C.byref(cv), C.byref(cdo), key_pad.data_ptr(), B, S, H, drop_p, seed,
-                                       step, site, C.byref(cdq), C.byref(cdk), C.byref(cdv), _stream()), "attn_bwd")
+                                       step, site, C.byref(cdq), C.byref(cdk), C.byref(cdv), _ptr(dbq), _ptr(dbk), _ptr(dbv), _stream()), "attn_bwd")
 
 
 def ce_fwd_bwd(logits: torch.Tensor, target: torch.Tensor, class_w: Optional[torch.Tensor] = None, eps: float = 0.1,

@@ -53,6 +53,9 @@ CASES = {
                            TEXT=dict(embedding_size=48, n_head=3, n_encoder_layers=1),
                            FAM=dict(enabled=False, embedding_size=32, n_head=4, n_layers=1),
                            CLASSIFIER=dict(hidden_size=32, output_size=5, n_layers=4)), 3, 4, False, False),
+    # MELD-sized widths (text_base 768 + wav2vec2 768, 8 heads, FFN 2048), 2 + 2 encoder layers, 2 fusion layers: the case the
+    # bf16 tolerance of BASELINE.json is judged on.  Inputs are RNG-free (O.synth_inputs) and not stored.
+    "meld_base_2l": (dict(AUDIO=dict(n_encoder_layers=2), TEXT=dict(n_encoder_layers=2), FAM=dict(n_layers=2)), 4, 33, "rngfree", False),
 }
 
 
@@ -65,7 +68,10 @@ def load_reference():
 
 def case_inputs(cfg, B, S, ragged, weighted, seed):
     C = cfg.CLASSIFIER.output_size
-    b = O.synth_batch(B, S, cfg.TEXT.embedding_size, cfg.AUDIO.embedding_size, C=C, seed=seed, ragged=ragged)
+    if ragged == "rngfree":
+        b = O.synth_inputs(B, S, cfg.TEXT.embedding_size, cfg.AUDIO.embedding_size, C=C)
+    else:
+        b = O.synth_batch(B, S, cfg.TEXT.embedding_size, cfg.AUDIO.embedding_size, C=C, seed=seed, ragged=ragged)
     w = None
     if weighted:
         p = torch.tensor([.47, .17, .07, .11, .12, .03, .03], dtype=torch.float64)[:C]
@@ -101,9 +107,20 @@ def main():
         out = model(text, audio, mask)
         loss = crit(out.permute(0, 2, 1), emo)
         loss.backward()
-        blob = {"text": text.numpy(), "audio": audio.numpy(), "mask": mask.numpy(), "emotion": emo.numpy(),
+        store_inputs = ragged != "rngfree"
+        blob = {"text": text.numpy() if store_inputs else np.zeros(0), "audio": audio.numpy() if store_inputs else np.zeros(0),
+                "mask": mask.numpy(), "emotion": emo.numpy(),
                 "logits": out.detach().numpy(), "loss": np.array(loss.item()),
                 "ce_weight": (w.numpy() if w is not None else np.zeros(0))}
+        if name == "meld_base_2l":  # error level of an ideal bf16-operand pipeline on this case (the bf16 mode's yardstick)
+            from oracle import bf16_emulation as E
+            lg_e, _, g_e = E.loss_and_grads(params, cfg, text, audio, mask, emo, w)
+            valid = ~mask
+            ref_g = {O.canonical_name(n): p_.grad for n, p_ in model.named_parameters()}
+            names = list(g_e)
+            blob["bf16emu/logits"] = np.array(O.rel_l2(lg_e[valid], out.detach()[valid]))
+            blob["bf16emu/grads"] = np.array(O.rel_l2(torch.cat([g_e[k].flatten() for k in names]), torch.cat([ref_g[k].flatten() for k in names])))
+            print("   ideal bf16-operand pipeline: logits", float(blob["bf16emu/logits"]), "grads", float(blob["bf16emu/grads"]))
         seen = set()
         for pname, prm in model.named_parameters():  # named_parameters de-duplicates the shared norm
             cn = O.canonical_name(pname)

@@ -201,6 +201,22 @@ def synth_params(cfg, dtype=torch.float64) -> Dict[str, torch.Tensor]:
     return {k: synth_param(k, s).to(dtype) for k, s in param_shapes(cfg).items()}
 
 
+def synth_inputs(B, S, Dt, Da, C=7):
+    """RNG-free MELD-shaped batch (sin-hash values with the statistics of SURVEY.md section 8(d); ragged lengths from a
+    fixed pattern, dialogue 0 full, last dialogue of length 1) so that large golden cases need not store their inputs."""
+    def field(n, d, a, b, amp, off):
+        i = torch.arange(n * d, dtype=torch.float64)
+        return (amp * (torch.sin(i * a + 0.3) + 0.41 * torch.cos(i * b)) + off).reshape(n, d)
+    text = field(B * S, Dt, 0.9127, 2.7183, 0.63 / 0.765, 0.025).reshape(B, S, Dt)
+    audio = field(B * S, Da, 1.3371, 0.5772, 0.233 / 0.765, 0.0).reshape(B, S, Da)
+    L = torch.tensor([S if b == 0 else (1 if b == B - 1 and B > 1 else 2 + (7 * b) % max(1, S - 2)) for b in range(B)])
+    pos = torch.arange(S)[None, :]
+    mask = pos >= L[:, None]
+    emotion = ((torch.arange(B * S) * 5 + 3) % 11 % C).reshape(B, S)
+    return {"text": text.masked_fill(mask[..., None], 0.0).float(), "audio": audio.masked_fill(mask[..., None], 0.0).float(),
+            "padding_mask": mask, "emotion": emotion.masked_fill(mask, -1)}
+
+
 # ----------------------------------------------------------------------------- forward ops
 
 

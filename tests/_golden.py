@@ -35,3 +35,13 @@ def grad_errors(z, grads):
         num += d * d
         den += r * r
     return per, (num / den) ** 0.5 if den > 0 else num ** 0.5
+
+
+def case_inputs(z, cfg, B, S, ragged):
+    """(text, audio) fp64 tensors of a case: stored in the fixture, or regenerated when the case is RNG-free."""
+    if ragged == "rngfree":
+        from oracle import m2fnet_oracle as O
+        b = O.synth_inputs(B, S, cfg.TEXT.embedding_size, cfg.AUDIO.embedding_size, C=cfg.CLASSIFIER.output_size)
+        assert torch.equal(b["padding_mask"], torch.from_numpy(z["mask"])) and torch.equal(b["emotion"], torch.from_numpy(z["emotion"]))
+        return b["text"].double(), b["audio"].double()
+    return torch.from_numpy(z["text"]), torch.from_numpy(z["audio"])

@@ -215,7 +215,8 @@ def _attn_ref(q, k, v, pad, H, keep=None, p=0.0):
 
 
 @pytest.mark.parametrize("planes", [1, 3])
-@pytest.mark.parametrize("B,S,H,hd,p", [(6, 33, 8, 96, 0.0), (6, 33, 8, 96, 0.4), (3, 7, 10, 30, 0.4), (2, 64, 4, 64, 0.0), (2, 1, 2, 32, 0.0)])
+@pytest.mark.parametrize("B,S,H,hd,p", [(6, 33, 8, 96, 0.0), (6, 33, 8, 96, 0.4), (3, 7, 10, 30, 0.4), (2, 64, 4, 64, 0.0), (2, 1, 2, 32, 0.0),
+                                        (3, 48, 2, 128, 0.4), (5, 17, 3, 16, 0.0), (2, 100, 2, 64, 0.4), (64, 33, 8, 96, 0.4)])
 def test_attention_forward_backward(ops, B, S, H, hd, p, planes):
     E = H * hd
     g = torch.Generator().manual_seed(40)
@@ -238,8 +239,12 @@ def test_attention_forward_backward(ops, B, S, H, hd, p, planes):
     dop = ops.PlanesTensor.from_float(d_o, planes)
     ref.backward(dop.float().double().reshape(B, S, E))
     dqkv = ops.PlanesTensor.empty(B * S, 3 * E, planes, "cuda", zero=True)
-    ops.attn_bwd(q, k, v, dop, pad, B, S, H, dqkv.cview(0, E), dqkv.cview(E, E), dqkv.cview(2 * E, E), drop_p=p, seed=9, step=1, site=0x3000)
+    db = torch.ones(3 * E, device="cuda")
+    ops.attn_bwd(q, k, v, dop, pad, B, S, H, dqkv.cview(0, E), dqkv.cview(E, E), dqkv.cview(2 * E, E), drop_p=p, seed=9, step=1, site=0x3000,
+                 dbq=db[:E], dbk=db[E:2 * E], dbv=db[2 * E:])
     got = dqkv.float()
+    ref_db = torch.cat([t.grad.reshape(B * S, E).sum(0) for t in (qd, kd, vd)]) + 1.0  # in_proj_bias gradient slices
+    assert rel(db, ref_db) < (2e-2 if planes == 1 else 1e-5)
     assert rel(got[:, :E], qd.grad.reshape(B * S, E)) < tol
     assert rel(got[:, E:2 * E], kd.grad.reshape(B * S, E)) < tol
     assert rel(got[:, 2 * E:], vd.grad.reshape(B * S, E)) < tol

@@ -28,7 +28,8 @@ def test_oracle_matches_reference_fixture(name, golden_dir):
     cfg = O.default_model_cfg(dropout=0.0, **over)
     z = np.load(os.path.join(golden_dir, name + ".npz"))
     params = O.synth_params(cfg)
-    text, audio = torch.from_numpy(z["text"]), torch.from_numpy(z["audio"])
+    from tests._golden import case_inputs
+    text, audio = case_inputs(z, cfg, B, S, ragged)
     mask, emo = torch.from_numpy(z["mask"]), torch.from_numpy(z["emotion"])
     w = torch.from_numpy(z["ce_weight"]) if z["ce_weight"].size else None
     logits, loss, grads = O.loss_and_grads(params, cfg, text, audio, mask, emo, weight=w)
