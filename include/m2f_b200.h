@@ -131,7 +131,8 @@ int m2f_ln_bwd(const float* g, int64_t g_ld, const float* x, int64_t x_ld, const
  * P = softmax(q k^T / sqrt(hd) with -inf on padded KEYS), O = dropout(P) v
  * (torch/nn/functional.py:6607-6690; fusion layers: q,v from text, k from audio, src/model.py:14).
  * q,k,v,o: planes views of [B*S, H*hd] (cols = H*hd; they may alias one packed buffer through
- * different base pointers and a common ld).  key_pad: uint8 [B,S], 1 = padded. */
+ * different base pointers and a common ld).  key_pad: uint8 [B,S], 1 = padded.
+ * Dropout element of probability (b, h, query i, key j): ((b*H + h)*S + i) * S8 + j of `site`, S8 = S rounded up to 8. */
 int m2f_attn_fwd(const m2f_planes_t* q, const m2f_planes_t* k, const m2f_planes_t* v,
                  const uint8_t* key_pad, int64_t B, int64_t S, int32_t H,
                  float drop_p, uint64_t seed, uint64_t step, uint32_t site,

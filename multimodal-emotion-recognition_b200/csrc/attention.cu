@@ -100,7 +100,7 @@ attn_fwd_kernel(PlanesView q, PlanesView k, PlanesView v, const uint8_t* __restr
             const int j = lane + 32 * t;
             if (j < S) {
                 float p = sc[t] * inv;
-                if (drop.enabled) p *= drop_mult1(drop, ((uint64_t)blockIdx.x * S + i) * S + j);
+                if (drop.enabled) p *= drop_mult1(drop, ((uint64_t)blockIdx.x * S + i) * ((S + 7) & ~7) + j);
                 myP[j] = p;
             }
         }
@@ -176,7 +176,7 @@ attn_bwd_kernel(PlanesView q, PlanesView k, PlanesView v, PlanesView d_o, const 
             const int j = lane + 32 * t;
             sc[t] *= inv;  // P
             mlt[t] = 1.f;
-            if (drop.enabled && j < S) mlt[t] = drop_mult1(drop, ((uint64_t)blockIdx.x * S + i) * S + j);
+            if (drop.enabled && j < S) mlt[t] = drop_mult1(drop, ((uint64_t)blockIdx.x * S + i) * ((S + 7) & ~7) + j);
             dp[t] *= mlt[t];  // dP
             delta += dp[t] * sc[t];
         }
@@ -208,242 +208,15 @@ attn_bwd_kernel(PlanesView q, PlanesView k, PlanesView v, PlanesView d_o, const 
 }
 
 // ------------------------------------------------------------------------------------ tensor-path kernels (S <= 64)
+// attention_mma_p{1,2,3}.cu instantiate attention_mma_impl.cuh for one plane count each (compile time, code size)
 namespace amma {
-
-template <int HD, int SP>
-struct Smem {
-    static constexpr int LDS = HD + 8, LDP = SP + 8;
-    static size_t fwd_bytes(int P) { return (size_t)3 * P * SP * LDS * 2; }
-    static size_t bwd_bytes(int P) { return (size_t)4 * P * SP * LDS * 2 + (size_t)2 * P * SP * LDP * 2; }
-};
-
-// scores (already scaled) -> probabilities in place; returns nothing.  Accumulator layout: thread (g, q) holds rows
-// i0 + g (values [nt][0..1]) and i0 + g + 8 ([nt][2..3]), columns nt*8 + 2q, 2q + 1.
-template <int SP>
-__device__ __forceinline__ void softmax_rows(float (&s)[SP / 8][4], const uint8_t* pad, int S, int lane) {
-    const int q = lane & 3;
-    float mx0 = -INFINITY, mx1 = -INFINITY;
-#pragma unroll
-    for (int nt = 0; nt < SP / 8; ++nt) {
-#pragma unroll
-        for (int c = 0; c < 2; ++c) {
-            const int j = nt * 8 + 2 * q + c;
-            const bool dead = j >= S || pad[j];
-            if (dead) { s[nt][c] = -INFINITY; s[nt][2 + c] = -INFINITY; }
-            mx0 = fmaxf(mx0, s[nt][c]);
-            mx1 = fmaxf(mx1, s[nt][2 + c]);
-        }
-    }
-    mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 1)); mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 2));
-    mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 1)); mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 2));
-    float sm0 = 0.f, sm1 = 0.f;
-#pragma unroll
-    for (int nt = 0; nt < SP / 8; ++nt) {
-#pragma unroll
-        for (int c = 0; c < 2; ++c) {
-            s[nt][c] = (s[nt][c] == -INFINITY) ? 0.f : __expf(s[nt][c] - mx0);
-            s[nt][2 + c] = (s[nt][2 + c] == -INFINITY) ? 0.f : __expf(s[nt][2 + c] - mx1);
-            sm0 += s[nt][c];
-            sm1 += s[nt][2 + c];
-        }
-    }
-    sm0 += __shfl_xor_sync(0xffffffffu, sm0, 1); sm0 += __shfl_xor_sync(0xffffffffu, sm0, 2);
-    sm1 += __shfl_xor_sync(0xffffffffu, sm1, 1); sm1 += __shfl_xor_sync(0xffffffffu, sm1, 2);
-    const float i0 = 1.f / sm0, i1 = 1.f / sm1;  // every dialogue keeps >= 1 valid key
-#pragma unroll
-    for (int nt = 0; nt < SP / 8; ++nt) { s[nt][0] *= i0; s[nt][1] *= i0; s[nt][2] *= i1; s[nt][3] *= i1; }
-}
-
-template <int HD, int SP>
-__global__ void __launch_bounds__(SP * 2)
-attn_fwd_mma_kernel(View q, View k, View v, const uint8_t* __restrict__ key_pad, int S, int H, int P, float scale, Drop drop, OutView o) {
-    extern __shared__ __align__(16) uint8_t smraw[];
-    constexpr int LDS = HD + 8;
-    __nv_bfloat16* sQ = reinterpret_cast<__nv_bfloat16*>(smraw);
-    __nv_bfloat16* sK = sQ + P * SP * LDS;
-    __nv_bfloat16* sV = sK + P * SP * LDS;
-    const int b = blockIdx.x / H, h = blockIdx.x - b * H;
-    const int64_t row0 = (int64_t)b * S;
-    const int col0 = h * HD;
-    load_tile<HD, SP>(sQ, q, P, row0, col0, S);
-    load_tile<HD, SP>(sK, k, P, row0, col0, S);
-    load_tile<HD, SP>(sV, v, P, row0, col0, S);
-    __syncthreads();
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int i0 = warp * 16;
-    if (i0 >= S) return;
-    const int g = lane >> 2, qd = lane & 3;
-    float s[SP / 8][4];
-#pragma unroll
-    for (int nt = 0; nt < SP / 8; ++nt) s[nt][0] = s[nt][1] = s[nt][2] = s[nt][3] = 0.f;
-    strip_nt<HD, SP>(s, sQ, sK, P, i0, lane);
-#pragma unroll
-    for (int nt = 0; nt < SP / 8; ++nt) { s[nt][0] *= scale; s[nt][1] *= scale; s[nt][2] *= scale; s[nt][3] *= scale; }
-    softmax_rows<SP>(s, key_pad + row0, S, lane);
-    if (drop.enabled) {
-#pragma unroll
-        for (int nt = 0; nt < SP / 8; ++nt)
-#pragma unroll
-            for (int c = 0; c < 4; ++c) {
-                const int i = i0 + g + (c >> 1) * 8, j = nt * 8 + 2 * qd + (c & 1);
-                if (i < S && j < S) s[nt][c] *= drop_mult1(drop, ((uint64_t)blockIdx.x * S + i) * S + j);
-            }
-    }
-    float acc[HD / 8][4];
-#pragma unroll
-    for (int nt = 0; nt < HD / 8; ++nt) acc[nt][0] = acc[nt][1] = acc[nt][2] = acc[nt][3] = 0.f;
-    strip_regA_nn<HD, SP>(acc, s, sV, P, lane);
-    store_strip<HD>(acc, 1.f, o, P, row0, col0, i0, S, lane, nullptr);
-}
-
-// Backward.  Pd = P * M (M = dropout multiplier), dPd = dO V^T, dP = dPd * M, dS = P * (dP - rowsum(dP * P)),
-// dQ = c dS K, dK = c dS^T Q, dV = Pd^T dO.  db* (nullable) += column sums of dQ / dK / dV (in-projection bias grads).
-template <int HD, int SP>
-__global__ void __launch_bounds__(SP * 2)
-attn_bwd_mma_kernel(View q, View k, View v, View d_o, const uint8_t* __restrict__ key_pad, int S, int H, int P, float scale, Drop drop,
-                    OutView dq, OutView dk, OutView dv, float* dbq, float* dbk, float* dbv) {
-    extern __shared__ __align__(16) uint8_t smraw[];
-    constexpr int LDS = HD + 8, LDP = SP + 8;
-    __nv_bfloat16* sQ = reinterpret_cast<__nv_bfloat16*>(smraw);
-    __nv_bfloat16* sK = sQ + P * SP * LDS;
-    __nv_bfloat16* sV = sK + P * SP * LDS;
-    __nv_bfloat16* sdO = sV + P * SP * LDS;
-    __nv_bfloat16* sPd = sdO + P * SP * LDS;  // [P][SP queries][LDP keys]
-    __nv_bfloat16* sdS = sPd + P * SP * LDP;
-    const int b = blockIdx.x / H, h = blockIdx.x - b * H;
-    const int64_t row0 = (int64_t)b * S;
-    const int col0 = h * HD;
-    load_tile<HD, SP>(sQ, q, P, row0, col0, S);
-    load_tile<HD, SP>(sK, k, P, row0, col0, S);
-    load_tile<HD, SP>(sV, v, P, row0, col0, S);
-    load_tile<HD, SP>(sdO, d_o, P, row0, col0, S);
-    __syncthreads();
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int i0 = warp * 16;  // blockDim = 32 * SP / 16: every warp owns one 16-row strip
-    const int g = lane >> 2, qd = lane & 3;
-    {
-        float s[SP / 8][4], dp[SP / 8][4];
-#pragma unroll
-        for (int nt = 0; nt < SP / 8; ++nt) {
-            s[nt][0] = s[nt][1] = s[nt][2] = s[nt][3] = 0.f;
-            dp[nt][0] = dp[nt][1] = dp[nt][2] = dp[nt][3] = 0.f;
-        }
-        strip_nt<HD, SP>(s, sQ, sK, P, i0, lane);
-        strip_nt<HD, SP>(dp, sdO, sV, P, i0, lane);
-#pragma unroll
-        for (int nt = 0; nt < SP / 8; ++nt) { s[nt][0] *= scale; s[nt][1] *= scale; s[nt][2] *= scale; s[nt][3] *= scale; }
-        softmax_rows<SP>(s, key_pad + row0, S, lane);
-        // dp <- dP = dPd * M; s stays P; pd = P * M written to shared; then dS
-        float del0 = 0.f, del1 = 0.f;
-#pragma unroll
-        for (int nt = 0; nt < SP / 8; ++nt) {
-            float pdv[4];
-#pragma unroll
-            for (int c = 0; c < 4; ++c) {
-                const int i = i0 + g + (c >> 1) * 8, j = nt * 8 + 2 * qd + (c & 1);
-                float m = 1.f;
-                if (drop.enabled && i < S && j < S) m = drop_mult1(drop, ((uint64_t)blockIdx.x * S + i) * S + j);
-                if (i >= S) m = 0.f;  // rows beyond the dialogue contribute nothing to dK / dV
-                dp[nt][c] *= m;
-                pdv[c] = s[nt][c] * m;
-                if (c < 2) del0 += dp[nt][c] * s[nt][c]; else del1 += dp[nt][c] * s[nt][c];
-            }
-            uint32_t h0[3], h1[3];
-            split2(pdv[0], pdv[1], P, h0);
-            split2(pdv[2], pdv[3], P, h1);
-            for (int pl = 0; pl < P; ++pl) {
-                *reinterpret_cast<uint32_t*>(sPd + (pl * SP + i0 + g) * LDP + nt * 8 + 2 * qd) = pl == 0 ? h0[0] : (pl == 1 ? h0[1] : h0[2]);
-                *reinterpret_cast<uint32_t*>(sPd + (pl * SP + i0 + g + 8) * LDP + nt * 8 + 2 * qd) = pl == 0 ? h1[0] : (pl == 1 ? h1[1] : h1[2]);
-            }
-        }
-        del0 += __shfl_xor_sync(0xffffffffu, del0, 1); del0 += __shfl_xor_sync(0xffffffffu, del0, 2);
-        del1 += __shfl_xor_sync(0xffffffffu, del1, 1); del1 += __shfl_xor_sync(0xffffffffu, del1, 2);
-#pragma unroll
-        for (int nt = 0; nt < SP / 8; ++nt) {
-            dp[nt][0] = s[nt][0] * (dp[nt][0] - del0);
-            dp[nt][1] = s[nt][1] * (dp[nt][1] - del0);
-            dp[nt][2] = s[nt][2] * (dp[nt][2] - del1);
-            dp[nt][3] = s[nt][3] * (dp[nt][3] - del1);
-            uint32_t h0[3], h1[3];
-            split2(dp[nt][0], dp[nt][1], P, h0);
-            split2(dp[nt][2], dp[nt][3], P, h1);
-            for (int pl = 0; pl < P; ++pl) {
-                *reinterpret_cast<uint32_t*>(sdS + (pl * SP + i0 + g) * LDP + nt * 8 + 2 * qd) = pl == 0 ? h0[0] : (pl == 1 ? h0[1] : h0[2]);
-                *reinterpret_cast<uint32_t*>(sdS + (pl * SP + i0 + g + 8) * LDP + nt * 8 + 2 * qd) = pl == 0 ? h1[0] : (pl == 1 ? h1[1] : h1[2]);
-            }
-        }
-        // dQ strip = c * dS K   (K stored [key][d]: k = key, n = d)
-        float acc[HD / 8][4];
-#pragma unroll
-        for (int nt = 0; nt < HD / 8; ++nt) acc[nt][0] = acc[nt][1] = acc[nt][2] = acc[nt][3] = 0.f;
-        strip_regA_nn<HD, SP>(acc, dp, sK, P, lane);
-        store_strip<HD>(acc, scale, dq, P, row0, col0, i0, S, lane, dbq);
-    }
-    __syncthreads();
-    {   // this warp's 16 keys j0 = i0: dV = Pd^T dO, dK = c dS^T Q
-        float acc[HD / 8][4];
-#pragma unroll
-        for (int nt = 0; nt < HD / 8; ++nt) acc[nt][0] = acc[nt][1] = acc[nt][2] = acc[nt][3] = 0.f;
-        strip_tn<HD, SP>(acc, sPd, sdO, P, i0, lane);
-        store_strip<HD>(acc, 1.f, dv, P, row0, col0, i0, S, lane, dbv);
-#pragma unroll
-        for (int nt = 0; nt < HD / 8; ++nt) acc[nt][0] = acc[nt][1] = acc[nt][2] = acc[nt][3] = 0.f;
-        strip_tn<HD, SP>(acc, sdS, sQ, P, i0, lane);
-        store_strip<HD>(acc, scale, dk, P, row0, col0, i0, S, lane, dbk);
-    }
-}
-
-template <int HD, int SP>
-static int launch_fwd(const View& q, const View& k, const View& v, const uint8_t* pad, int64_t BH, int S, int H, int P, float scale,
-                      const Drop& drop, const OutView& o, cudaStream_t st) {
-    const size_t smem = Smem<HD, SP>::fwd_bytes(P);
-    static size_t set = 0;
-    if (smem > 48 * 1024 && smem > set) {
-        M2F_CUDA(cudaFuncSetAttribute(attn_fwd_mma_kernel<HD, SP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        set = smem;
-    }
-    attn_fwd_mma_kernel<HD, SP><<<(unsigned)BH, SP * 2, smem, st>>>(q, k, v, pad, S, H, P, scale, drop, o);
-    M2F_LAUNCH_CHECK();
-    return M2F_OK;
-}
-template <int HD, int SP>
-static int launch_bwd(const View& q, const View& k, const View& v, const View& d_o, const uint8_t* pad, int64_t BH, int S, int H, int P,
-                      float scale, const Drop& drop, const OutView& dq, const OutView& dk, const OutView& dv, float* dbq, float* dbk,
-                      float* dbv, cudaStream_t st) {
-    const size_t smem = Smem<HD, SP>::bwd_bytes(P);
-    static size_t set = 0;
-    if (smem > 48 * 1024 && smem > set) {
-        M2F_CUDA(cudaFuncSetAttribute(attn_bwd_mma_kernel<HD, SP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        set = smem;
-    }
-    attn_bwd_mma_kernel<HD, SP><<<(unsigned)BH, SP * 2, smem, st>>>(q, k, v, d_o, pad, S, H, P, scale, drop, dq, dk, dv, dbq, dbk, dbv);
-    M2F_LAUNCH_CHECK();
-    return M2F_OK;
-}
-
-#define M2F_ATT_DISPATCH(HDV, SPV, CALL)                                                     \
-    do {                                                                                     \
-        if (HDV == 16) { M2F_ATT_SP(16, SPV, CALL); }                                        \
-        else if (HDV == 32) { M2F_ATT_SP(32, SPV, CALL); }                                   \
-        else if (HDV == 64) { M2F_ATT_SP(64, SPV, CALL); }                                   \
-        else if (HDV == 96) { M2F_ATT_SP(96, SPV, CALL); }                                   \
-        else { M2F_ATT_SP(128, SPV, CALL); }                                                 \
-    } while (0)
-#define M2F_ATT_SP(HDC, SPV, CALL)                                                           \
-    do {                                                                                     \
-        constexpr int HD_ = HDC;                                                             \
-        if (SPV == 16) { constexpr int SP_ = 16; return CALL; }                              \
-        else if (SPV == 32) { constexpr int SP_ = 32; return CALL; }                         \
-        else if (SPV == 48) { constexpr int SP_ = 48; return CALL; }                         \
-        else { constexpr int SP_ = 64; return CALL; }                                        \
-    } while (0)
-
+int fwd_p1(AMMA_FWD_ARGS); int fwd_p2(AMMA_FWD_ARGS); int fwd_p3(AMMA_FWD_ARGS);
+int bwd_p1(AMMA_BWD_ARGS); int bwd_p2(AMMA_BWD_ARGS); int bwd_p3(AMMA_BWD_ARGS);
 static bool supported(int hd, int64_t S) { return S <= 64 && (hd == 16 || hd == 32 || hd == 64 || hd == 96 || hd == 128); }
 // 16-byte row chunks: base, leading dimension, plane stride and the head's first column must be multiples of 8 elements
 static bool aligned16(const m2f_planes_t* t) {
     return (reinterpret_cast<uintptr_t>(t->ptr) % 16) == 0 && (t->ld % 8) == 0 && (t->planes == 1 || (t->plane_stride % 8) == 0);
 }
-
 }  // namespace amma
 
 static int att_view(const m2f_planes_t* t, const char* name, int64_t rows, int64_t cols, PlanesView* out) {
@@ -483,8 +256,7 @@ extern "C" int m2f_attn_fwd(const m2f_planes_t* q, const m2f_planes_t* k, const 
     M2F_REQUIRE(vec_ok(q) && vec_ok(k) && vec_ok(v), M2F_ERR_ALIGN, "attn_fwd: q/k/v need ld %% 4 == 0 and 8-byte aligned bases");
     M2F_REQUIRE(S <= 32 * ATT_MAX_KPL, M2F_ERR_UNSUPPORTED, "attn_fwd: S = %lld exceeds the single-CTA limit %d", (long long)S, 32 * ATT_MAX_KPL);
     M2F_REQUIRE(q->planes == k->planes && q->planes == v->planes && q->planes == o->planes, M2F_ERR_ARG, "attn_fwd: plane counts differ");
-    if (amma::supported(hd, S) && amma::aligned16(q) && amma::aligned16(k) && amma::aligned16(v) && (o->ld % 2) == 0 &&
-        (reinterpret_cast<uintptr_t>(o->ptr) % 4) == 0 && (o->planes == 1 || (o->plane_stride % 2) == 0)) {
+    if (amma::supported(hd, S) && amma::aligned16(q) && amma::aligned16(k) && amma::aligned16(v) && amma::aligned16(o)) {
         // short dialogues: tensor-path kernel, whole (dialogue, head) problem on chip
         const amma::View aq{vq.ptr, vq.ld, vq.stride}, ak{vk.ptr, vk.ld, vk.stride}, av{vv.ptr, vv.ld, vv.stride};
         const amma::OutView ao{const_cast<__nv_bfloat16*>(vo.ptr), vo.ld, vo.stride};
@@ -492,7 +264,8 @@ extern "C" int m2f_attn_fwd(const m2f_planes_t* q, const m2f_planes_t* k, const 
         const Drop dropm = drop_make(drop_p, seed, step, site);
         const float sc = 1.f / sqrtf((float)hd);
         auto st = reinterpret_cast<cudaStream_t>(stream);
-        M2F_ATT_DISPATCH(hd, SPv, (amma::launch_fwd<HD_, SP_>(aq, ak, av, key_pad, B * H, (int)S, H, q->planes, sc, dropm, ao, st)));
+        auto fn = q->planes == 1 ? amma::fwd_p1 : (q->planes == 2 ? amma::fwd_p2 : amma::fwd_p3);
+        return fn(hd, SPv, aq, ak, av, key_pad, B * H, (int)S, H, sc, dropm, ao, st);
     }
     const int hd_pad = hd | 1;
     const size_t smem = sizeof(float) * ((size_t)2 * S * hd_pad + ATT_WARPS * hd_pad + ATT_WARPS * S);
@@ -532,11 +305,9 @@ extern "C" int m2f_attn_bwd(const m2f_planes_t* q, const m2f_planes_t* k, const 
     M2F_REQUIRE(S <= 32 * ATT_MAX_KPL, M2F_ERR_UNSUPPORTED, "attn_bwd: S = %lld exceeds the single-CTA limit %d", (long long)S, 32 * ATT_MAX_KPL);
     M2F_REQUIRE(q->planes == k->planes && q->planes == v->planes && q->planes == d_o->planes && q->planes == dq->planes &&
                     q->planes == dk->planes && q->planes == dv->planes, M2F_ERR_ARG, "attn_bwd: plane counts differ");
-    auto out_ok = [](const m2f_planes_t* t) {
-        return (t->ld % 2) == 0 && (reinterpret_cast<uintptr_t>(t->ptr) % 4) == 0 && (t->planes == 1 || (t->plane_stride % 2) == 0);
-    };
+    auto out_ok = [](const m2f_planes_t* t) { return amma::aligned16(t); };
     if (amma::supported(hd, S) && amma::aligned16(q) && amma::aligned16(k) && amma::aligned16(v) && amma::aligned16(d_o) && out_ok(dq) &&
-        out_ok(dk) && out_ok(dv) && amma::Smem<128, 64>::bwd_bytes(1) > 0) {
+        out_ok(dk) && out_ok(dv)) {
         const amma::View aq{vq.ptr, vq.ld, vq.stride}, ak{vk.ptr, vk.ld, vk.stride}, av{vv.ptr, vv.ld, vv.stride}, ado{vdo.ptr, vdo.ld, vdo.stride};
         const amma::OutView odq{const_cast<__nv_bfloat16*>(vdq.ptr), vdq.ld, vdq.stride}, odk{const_cast<__nv_bfloat16*>(vdk.ptr), vdk.ld, vdk.stride},
             odv{const_cast<__nv_bfloat16*>(vdv.ptr), vdv.ld, vdv.stride};
@@ -546,8 +317,8 @@ extern "C" int m2f_attn_bwd(const m2f_planes_t* q, const m2f_planes_t* k, const 
             const Drop dropm = drop_make(drop_p, seed, step, site);
             const float sc = 1.f / sqrtf((float)hd);
             auto st = reinterpret_cast<cudaStream_t>(stream);
-            M2F_ATT_DISPATCH(hd, SPv, (amma::launch_bwd<HD_, SP_>(aq, ak, av, ado, key_pad, B * H, (int)S, H, q->planes, sc, dropm, odq, odk, odv,
-                                                                  dbq, dbk, dbv, st)));
+            auto fn = q->planes == 1 ? amma::bwd_p1 : (q->planes == 2 ? amma::bwd_p2 : amma::bwd_p3);
+            return fn(hd, SPv, aq, ak, av, ado, key_pad, B * H, (int)S, H, sc, dropm, odq, odk, odv, dbq, dbk, dbv, st);
         }
     }
     const int hd_pad = hd | 1, s_pad = (int)S | 1;

@@ -45,6 +45,23 @@ __device__ __forceinline__ void split2(float x, float y, int P, uint32_t (&out)[
     }
 }
 
+// (x, y) pairs of two rows -> bf16x2 planes at d (row A) and d + row_step (row B); planes are plane_step apart
+__device__ __forceinline__ void store_pair_planes(__nv_bfloat16* d, int row_step, int plane_step, int P, float x0, float y0, float x1, float y1) {
+    uint32_t h0[3], h1[3];
+    split2(x0, y0, P, h0);
+    split2(x1, y1, P, h1);
+    *reinterpret_cast<uint32_t*>(d) = h0[0];
+    *reinterpret_cast<uint32_t*>(d + row_step) = h1[0];
+    if (P > 1) {
+        *reinterpret_cast<uint32_t*>(d + plane_step) = h0[1];
+        *reinterpret_cast<uint32_t*>(d + plane_step + row_step) = h1[1];
+        if (P > 2) {
+            *reinterpret_cast<uint32_t*>(d + 2 * plane_step) = h0[2];
+            *reinterpret_cast<uint32_t*>(d + 2 * plane_step + row_step) = h1[2];
+        }
+    }
+}
+
 // plane products (a-plane, b-plane), least significant first
 __device__ __forceinline__ int nprod(int P) { return P == 1 ? 1 : (P == 2 ? 3 : 6); }
 __device__ __forceinline__ void prod(int P, int i, int& pa, int& pb) {
@@ -63,18 +80,32 @@ struct OutView {
     int64_t ld, stride;
 };
 
-// global [S, HD] head slice (all planes) -> shared [P][SP][HD + 8], rows >= S zeroed.  16-byte chunks.
+#define AMMA_FWD_ARGS                                                                                                         \
+    int hd, int SPv, const ::m2f::amma::View &q, const ::m2f::amma::View &k, const ::m2f::amma::View &v, const uint8_t *pad, \
+        int64_t BH, int S, int H, float scale, const ::m2f::Drop &drop, const ::m2f::amma::OutView &o, cudaStream_t st
+#define AMMA_BWD_ARGS                                                                                                            \
+    int hd, int SPv, const ::m2f::amma::View &q, const ::m2f::amma::View &k, const ::m2f::amma::View &v,                        \
+        const ::m2f::amma::View &d_o, const uint8_t *pad, int64_t BH, int S, int H, float scale, const ::m2f::Drop &drop,       \
+        const ::m2f::amma::OutView &dq, const ::m2f::amma::OutView &dk, const ::m2f::amma::OutView &dv, float *dbq, float *dbk, \
+        float *dbv, cudaStream_t st
+
+// global [S, HD] head slice (all planes) -> shared [P][SP][HD + 8], rows >= S zeroed.  Asynchronous 16-byte copies
+// (cp.async, zero-fill for the padding rows): every copy of the CTA is in flight at once; the caller waits with
+// cp_async_wait_all() + __syncthreads().
 template <int HD, int SP>
 __device__ __forceinline__ void load_tile(__nv_bfloat16* dst, const View& t, int P, int64_t row0, int col0, int S) {
     constexpr int LDS = HD + 8, CH = HD / 8;
     for (int i = threadIdx.x; i < P * SP * CH; i += blockDim.x) {
         const int pl = i / (SP * CH), rem = i - pl * (SP * CH);
         const int r = rem / CH, c = (rem - r * CH) * 8;
-        uint4 v = make_uint4(0u, 0u, 0u, 0u);
-        if (r < S) v = *reinterpret_cast<const uint4*>(t.ptr + pl * t.stride + (row0 + r) * t.ld + col0 + c);
-        *reinterpret_cast<uint4*>(dst + (pl * SP + r) * LDS + c) = v;
+        const int rr = r < S ? r : 0;  // keep the address valid; src-size 0 writes zeros
+        const __nv_bfloat16* src = t.ptr + pl * t.stride + (row0 + rr) * t.ld + col0 + c;
+        const uint32_t d = ptx::smem_u32(dst + (pl * SP + r) * LDS + c);
+        const int nbytes = r < S ? 16 : 0;
+        asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(d), "l"(src), "r"(nbytes) : "memory");
     }
 }
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
 
 // acc[nt][4] (16 x SP strip) += A(16 x HD from sA planes, rows i0..) * B^T (sB planes stored [n][k], k contiguous)
 template <int HD, int SP>
@@ -85,6 +116,7 @@ __device__ __forceinline__ void strip_nt(float (&acc)[SP / 8][4], const __nv_bfl
     const int np = nprod(P);
 #pragma unroll
     for (int kk = 0; kk < HD / 16; ++kk) {
+#pragma unroll 1
         for (int pi = 0; pi < np; ++pi) {
             int pa, pb;
             prod(P, pi, pa, pb);
@@ -115,6 +147,7 @@ __device__ __forceinline__ void strip_regA_nn(float (&out)[HD / 8][4], const flo
         split2(pv[2 * kt][2], pv[2 * kt][3], P, ap[1]);
         split2(pv[2 * kt + 1][0], pv[2 * kt + 1][1], P, ap[2]);
         split2(pv[2 * kt + 1][2], pv[2 * kt + 1][3], P, ap[3]);
+#pragma unroll 1
         for (int pi = 0; pi < np; ++pi) {
             int pa, pb;
             prod(P, pi, pa, pb);
@@ -134,6 +167,32 @@ __device__ __forceinline__ void strip_regA_nn(float (&out)[HD / 8][4], const flo
     }
 }
 
+// out[nt][4] (16 x HD strip, rows i0..) += A (sA planes stored [m][k], leading dim SP + 8) * B (sB planes stored [k][n])
+template <int HD, int SP>
+__device__ __forceinline__ void strip_smemA_nn(float (&out)[HD / 8][4], const __nv_bfloat16* sA, const __nv_bfloat16* sB, int P, int i0, int lane) {
+    constexpr int LDA = SP + 8, LDB = HD + 8;
+    const int a_row = i0 + (lane & 7) + ((lane >> 3) & 1) * 8, a_col = (lane >> 4) * 8;
+    const int b_row = (lane & 7) + ((lane >> 3) & 1) * 8, b_col = (lane >> 4) * 8;
+    const int np = nprod(P);
+#pragma unroll
+    for (int kt = 0; kt < SP / 16; ++kt) {
+#pragma unroll 1
+        for (int pi = 0; pi < np; ++pi) {
+            int pa, pb;
+            prod(P, pi, pa, pb);
+            uint32_t a[4];
+            ldsm_x4(ptx::smem_u32(sA + (pa * SP + a_row) * LDA + kt * 16 + a_col), a);
+#pragma unroll
+            for (int n2 = 0; n2 < HD / 16; ++n2) {
+                uint32_t b[4];
+                ldsm_x4_t(ptx::smem_u32(sB + (pb * SP + kt * 16 + b_row) * LDB + n2 * 16 + b_col), b);
+                mma16816(out[2 * n2], a, b[0], b[1]);
+                mma16816(out[2 * n2 + 1], a, b[2], b[3]);
+            }
+        }
+    }
+}
+
 // out[nt][4] (16 x HD strip, rows = keys j0..) += A^T * B with A stored [k][m] in sA (planes, leading dim LDA,
 // rows k = queries) and B stored [k][n] in sB (planes, leading dim HD + 8): both through ldmatrix.trans
 template <int HD, int SP>
@@ -144,6 +203,7 @@ __device__ __forceinline__ void strip_tn(float (&out)[HD / 8][4], const __nv_bfl
     const int np = nprod(P);
 #pragma unroll
     for (int kt = 0; kt < SP / 16; ++kt) {
+#pragma unroll 1
         for (int pi = 0; pi < np; ++pi) {
             int pa, pb;
             prod(P, pi, pa, pb);
@@ -160,37 +220,83 @@ __device__ __forceinline__ void strip_tn(float (&out)[HD / 8][4], const __nv_bfl
     }
 }
 
-// store a 16 x HD accumulator strip (rows r0.., valid rows < S) as planes; optional column sums into dbias[col]
-template <int HD>
-__device__ __forceinline__ void store_strip(const float (&acc)[HD / 8][4], float mul, const OutView& o, int P, int64_t row0, int col0, int r0, int S,
-                                            int lane, float* dbias) {
+// 64-bit mask of usable keys (bit j set: j < S and not padded), built by one warp with two ballots
+__device__ __forceinline__ uint64_t key_valid_bits(const uint8_t* pad, int S, int lane) {
+    const bool v0 = lane < S && !pad[lane];
+    const bool v1 = lane + 32 < S && !pad[lane + 32];
+    const uint32_t lo = __ballot_sync(0xffffffffu, v0), hi = __ballot_sync(0xffffffffu, v1);
+    return ((uint64_t)hi << 32) | lo;
+}
+
+// Dropout keep-bits of this thread's probabilities.  Element (query i, key j) of (dialogue, head) `bh` is element
+// (bh*S + i)*S8 + j of the site (S8 = S rounded up to 8), so the two columns a thread owns in an 8-wide tile share one
+// Philox call.  Bit (nt*2 + rowsel)*2 + c  <->  accumulator element [nt][rowsel*2 + c].  Rolled: one Philox body.
+template <int SP>
+__device__ __forceinline__ uint32_t drop_bits(const Drop& d, uint64_t bh, int S, int i0, int lane) {
+    const int g = lane >> 2, q = lane & 3;
+    const uint64_t s8q = (uint64_t)((S + 7) >> 3) * 2;  // S8 / 4
+    uint32_t bits = 0;
+#pragma unroll 1
+    for (int e = 0; e < 2 * (SP / 8); ++e) {
+        const int i = i0 + g + (e & 1) * 8, nt = e >> 1;
+        uint32_t r[4];
+        philox4(d.ph, (bh * S + i) * s8q + nt * 2 + (q >> 1), r);
+        const uint32_t r0 = (q & 1) ? r[2] : r[0], r1 = (q & 1) ? r[3] : r[1];
+        bits |= ((r0 >= d.thresh ? 1u : 0u) | (r1 >= d.thresh ? 2u : 0u)) << (2 * e);
+    }
+    return bits;
+}
+__device__ __forceinline__ float drop_mul(uint32_t bits, int nt, int c, float scale) {
+    return ((bits >> ((nt * 2 + (c >> 1)) * 2 + (c & 1))) & 1u) ? scale : 0.f;
+}
+
+// Accumulator strip (16 rows x HD) -> bf16 planes in this warp's own 16 rows of a shared tile [P][SP][HD + 8]
+template <int HD, int SP>
+__device__ __forceinline__ void stage_strip(const float (&acc)[HD / 8][4], float mul, __nv_bfloat16* tile, int P, int i0, int lane) {
+    constexpr int LDS = HD + 8;
     const int g = lane >> 2, q = lane & 3;
 #pragma unroll
     for (int nt = 0; nt < HD / 8; ++nt) {
-        const int col = col0 + nt * 8 + 2 * q;
-        float v[4] = {acc[nt][0] * mul, acc[nt][1] * mul, acc[nt][2] * mul, acc[nt][3] * mul};
-        const bool ok0 = r0 + g < S, ok1 = r0 + g + 8 < S;
-        if (dbias) {
-            float s0 = (ok0 ? v[0] : 0.f) + (ok1 ? v[2] : 0.f), s1 = (ok0 ? v[1] : 0.f) + (ok1 ? v[3] : 0.f);
-#pragma unroll
-            for (int o2 = 4; o2 < 32; o2 <<= 1) {
-                s0 += __shfl_xor_sync(0xffffffffu, s0, o2);
-                s1 += __shfl_xor_sync(0xffffffffu, s1, o2);
-            }
-            if (g == 0) {
-                atomicAdd(dbias + col, s0);
-                atomicAdd(dbias + col + 1, s1);
-            }
-        }
         uint32_t h0[3], h1[3];
-        split2(v[0], v[1], P, h0);
-        split2(v[2], v[3], P, h1);
-        for (int pl = 0; pl < P; ++pl) {
-            __nv_bfloat16* base = o.ptr + pl * o.stride + col;
-            if (ok0) *reinterpret_cast<uint32_t*>(base + (row0 + r0 + g) * o.ld) = pl == 0 ? h0[0] : (pl == 1 ? h0[1] : h0[2]);
-            if (ok1) *reinterpret_cast<uint32_t*>(base + (row0 + r0 + g + 8) * o.ld) = pl == 0 ? h1[0] : (pl == 1 ? h1[1] : h1[2]);
+        split2(acc[nt][0] * mul, acc[nt][1] * mul, P, h0);
+        split2(acc[nt][2] * mul, acc[nt][3] * mul, P, h1);
+        __nv_bfloat16* d0 = tile + (i0 + g) * LDS + nt * 8 + 2 * q;
+        *reinterpret_cast<uint32_t*>(d0) = h0[0];
+        *reinterpret_cast<uint32_t*>(d0 + 8 * LDS) = h1[0];
+        if (P > 1) {
+            *reinterpret_cast<uint32_t*>(d0 + SP * LDS) = h0[1];
+            *reinterpret_cast<uint32_t*>(d0 + SP * LDS + 8 * LDS) = h1[1];
+            if (P > 2) {
+                *reinterpret_cast<uint32_t*>(d0 + 2 * SP * LDS) = h0[2];
+                *reinterpret_cast<uint32_t*>(d0 + 2 * SP * LDS + 8 * LDS) = h1[2];
+            }
         }
     }
+}
+
+// Staged rows i0 .. i0+15 (valid < S) of all planes -> global, 16 bytes per lane, full rows coalesced; optional column
+// sums over the valid rows (planes added) into dbias[col0 + c] -- the in-projection bias gradient.
+template <int HD, int SP>
+__device__ __forceinline__ void copy_out_strip(const __nv_bfloat16* tile, const OutView& o, int P, int64_t row0, int col0, int i0, int S, int lane,
+                                               float* dbias) {
+    constexpr int LDS = HD + 8, CH = HD / 8;
+    __syncwarp();
+    const int nrow = min(16, S - i0);
+    for (int pl = 0; pl < P; ++pl)
+        for (int idx = lane; idx < nrow * CH; idx += 32) {
+            const int r = idx / CH, c = (idx - r * CH) * 8;
+            const uint4 v = *reinterpret_cast<const uint4*>(tile + (pl * SP + i0 + r) * LDS + c);
+            *reinterpret_cast<uint4*>(o.ptr + pl * o.stride + (row0 + i0 + r) * o.ld + col0 + c) = v;
+        }
+    if (dbias) {
+        for (int c = lane; c < HD; c += 32) {
+            float s = 0.f;
+            for (int pl = 0; pl < P; ++pl)
+                for (int r = 0; r < nrow; ++r) s += __bfloat162float(tile[(pl * SP + i0 + r) * LDS + c]);
+            atomicAdd(dbias + col0 + c, s);
+        }
+    }
+    __syncwarp();
 }
 
 }  // namespace amma

@@ -1,0 +1,3 @@
+// Short-dialogue attention fast path, 1 bf16 plane(s): see attention_mma_impl.cuh
+#define M2F_ATT_P 1
+#include "attention_mma_impl.cuh"

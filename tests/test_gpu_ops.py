@@ -230,7 +230,8 @@ def test_attention_forward_backward(ops, B, S, H, hd, p, planes):
     q, k, v = packed.cview(0, E), packed.cview(E, E), packed.cview(2 * E, E)
     o = ops.PlanesTensor.empty(B * S, E, planes, "cuda", zero=True)
     ops.attn_fwd(q, k, v, pad, B, S, H, o, drop_p=p, seed=9, step=1, site=0x3000)
-    keep = ops.dropout_mask(p, 9, 1, 0x3000, B * H * S * S, "cuda").reshape(B, H, S, S).double() if p > 0 else None
+    S8 = (S + 7) // 8 * 8  # row stride of the attention-probability dropout elements (include/m2f_b200.h)
+    keep = ops.dropout_mask(p, 9, 1, 0x3000, B * H * S * S8, "cuda").reshape(B, H, S, S8)[..., :S].double() if p > 0 else None
     qd, kd, vd = (t.float().double().reshape(B, S, E).requires_grad_(True) for t in (q, k, v))
     ref = _attn_ref(qd, kd, vd, pad, H, keep, p)
     tol = 5e-3 if planes == 1 else 3e-6
