@@ -4,6 +4,8 @@
 // nn.TransformerEncoderLayer norm1/norm2 (torch/nn/modules/transformer.py:977-982), the shared final norm
 // of nn.TransformerEncoder (:550-551) and the outer skip of src/model.py:107,119.
 // One warp per row; a row of D <= 1024 fp32 lives in registers (NCH float4 chunks per lane).
+#include <algorithm>
+
 #include "common.cuh"
 
 namespace m2f {
@@ -72,85 +74,101 @@ ln_fwd_kernel(const float* __restrict__ x, int64_t x_ld, const float* __restrict
     }
 }
 
-// Backward.  Per-warp register partials of dgamma / dbeta / dbias over the rows the warp owns, reduced
-// across the block's warps in shared memory, then one atomicAdd per column per block.
+// Backward.  A block owns groups of 8 rows.  Phase 1, one row per warp: dx (fp32 and / or dropout-masked planes); the
+// row's c1 = mean(g*gamma), c2 = mean(g*gamma*xhat) are parked in shared memory.  Phase 2, one float4 column per
+// thread: the block re-reads its 8 rows of g and x (L1 / L2 hits) and accumulates the dgamma / dbeta / dbias column
+// sums in 12 registers; they leave the block as vector atomics (red.global.add.v4.f32) once, at the end.
+constexpr int LNB_ROWS = 8;
+constexpr int LNB_THREADS = LNB_ROWS * 32;
+
 template <int NCH>
-__global__ void __launch_bounds__(LN_THREADS)
+__global__ void __launch_bounds__(LNB_THREADS)
 ln_bwd_kernel(const float* __restrict__ g, int64_t g_ld, const float* __restrict__ x, int64_t x_ld,
               const float* __restrict__ gamma, const float* __restrict__ stats, int64_t M, int D, float* __restrict__ dx,
               int64_t dx_ld, __nv_bfloat16* __restrict__ dxpl, int64_t dxpl_ld, int64_t dxpl_stride, int P, Drop drop,
               float* __restrict__ dgamma, float* __restrict__ dbeta, float* __restrict__ dbias) {
-    __shared__ float red[LN_WARPS][3][32 * 4 + 4];
+    __shared__ float rowc[LNB_ROWS][4];  // mean, rstd, c1, c2
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int64_t warp0 = (int64_t)blockIdx.x * LN_WARPS + warp;
-    const int64_t nwarps = (int64_t)gridDim.x * LN_WARPS;
     const float invD = 1.f / (float)D;
-    float4 gm[NCH], pg[NCH], pb[NCH], pbias[NCH];
+    const int ccol = threadIdx.x * 4;  // phase-2 column of this thread (D <= 1024 = 256 threads x 4)
+    float4 sg = make_float4(0.f, 0.f, 0.f, 0.f), sb = sg, sbias = sg, gmc = sg;
+    if (ccol < D) gmc = *reinterpret_cast<const float4*>(gamma + ccol);
+    for (int64_t m0 = (int64_t)blockIdx.x * LNB_ROWS; m0 < M; m0 += (int64_t)gridDim.x * LNB_ROWS) {
+        const int64_t m = m0 + warp;
+        if (m < M) {
+            float4 xv[NCH], av[NCH];
 #pragma unroll
-    for (int c = 0; c < NCH; ++c) {
-        const int col = (c * 32 + lane) * 4;
-        gm[c] = col < D ? *reinterpret_cast<const float4*>(gamma + col) : make_float4(0.f, 0.f, 0.f, 0.f);
-        pg[c] = pb[c] = pbias[c] = make_float4(0.f, 0.f, 0.f, 0.f);
-    }
-    for (int64_t m = warp0; m < M; m += nwarps) {
-        const float mean = stats[2 * m], rstd = stats[2 * m + 1];
-        float4 xh[NCH], a[NCH];
-        float s1 = 0.f, s2 = 0.f;
-#pragma unroll
-        for (int c = 0; c < NCH; ++c) {
-            const int col = (c * 32 + lane) * 4;
-            if (col < D) {
-                const float4 xv = *reinterpret_cast<const float4*>(x + m * x_ld + col);
-                const float4 gv = *reinterpret_cast<const float4*>(g + m * g_ld + col);
-                xh[c] = make_float4((xv.x - mean) * rstd, (xv.y - mean) * rstd, (xv.z - mean) * rstd, (xv.w - mean) * rstd);
-                a[c] = make_float4(gv.x * gm[c].x, gv.y * gm[c].y, gv.z * gm[c].z, gv.w * gm[c].w);
-                s1 += a[c].x + a[c].y + a[c].z + a[c].w;
-                s2 += a[c].x * xh[c].x + a[c].y * xh[c].y + a[c].z * xh[c].z + a[c].w * xh[c].w;
-                pg[c].x += gv.x * xh[c].x; pg[c].y += gv.y * xh[c].y; pg[c].z += gv.z * xh[c].z; pg[c].w += gv.w * xh[c].w;
-                pb[c].x += gv.x; pb[c].y += gv.y; pb[c].z += gv.z; pb[c].w += gv.w;
-            } else {
-                xh[c] = a[c] = make_float4(0.f, 0.f, 0.f, 0.f);
-            }
-        }
-        const float c1 = warp_sum(s1) * invD, c2 = warp_sum(s2) * invD;
-#pragma unroll
-        for (int c = 0; c < NCH; ++c) {
-            const int col = (c * 32 + lane) * 4;
-            if (col < D) {
-                float o[4] = {rstd * (a[c].x - c1 - xh[c].x * c2), rstd * (a[c].y - c1 - xh[c].y * c2),
-                              rstd * (a[c].z - c1 - xh[c].z * c2), rstd * (a[c].w - c1 - xh[c].w * c2)};
-                if (dx) *reinterpret_cast<float4*>(dx + m * dx_ld + col) = make_float4(o[0], o[1], o[2], o[3]);
-                if (drop.enabled) {
-                    float dm[4];
-                    drop_mult4(drop, (uint64_t)(m * D + col) >> 2, dm);
-#pragma unroll
-                    for (int i = 0; i < 4; ++i) o[i] *= dm[i];
+            for (int c = 0; c < NCH; ++c) {  // all loads of the row first
+                const int col = (c * 32 + lane) * 4;
+                if (col < D) {
+                    xv[c] = *reinterpret_cast<const float4*>(x + m * x_ld + col);
+                    av[c] = *reinterpret_cast<const float4*>(g + m * g_ld + col);
+                } else {
+                    xv[c] = av[c] = make_float4(0.f, 0.f, 0.f, 0.f);
                 }
-                if (dxpl) store_planes4(dxpl, dxpl_stride, P, m * dxpl_ld + col, o);
-                pbias[c].x += o[0]; pbias[c].y += o[1]; pbias[c].z += o[2]; pbias[c].w += o[3];
+            }
+            const float mean = stats[2 * m], rstd = stats[2 * m + 1];
+            float s1 = 0.f, s2 = 0.f;
+#pragma unroll
+            for (int c = 0; c < NCH; ++c) {
+                const int col = (c * 32 + lane) * 4;
+                if (col < D) {
+                    const float4 gm = *reinterpret_cast<const float4*>(gamma + col);
+                    xv[c] = make_float4((xv[c].x - mean) * rstd, (xv[c].y - mean) * rstd, (xv[c].z - mean) * rstd, (xv[c].w - mean) * rstd);
+                    av[c] = make_float4(av[c].x * gm.x, av[c].y * gm.y, av[c].z * gm.z, av[c].w * gm.w);
+                    s1 += av[c].x + av[c].y + av[c].z + av[c].w;
+                    s2 += av[c].x * xv[c].x + av[c].y * xv[c].y + av[c].z * xv[c].z + av[c].w * xv[c].w;
+                }
+            }
+            const float c1 = warp_sum(s1) * invD, c2 = warp_sum(s2) * invD;
+            if (lane == 0) { rowc[warp][0] = mean; rowc[warp][1] = rstd; rowc[warp][2] = c1; rowc[warp][3] = c2; }
+#pragma unroll
+            for (int c = 0; c < NCH; ++c) {
+                const int col = (c * 32 + lane) * 4;
+                if (col < D) {
+                    float o[4] = {rstd * (av[c].x - c1 - xv[c].x * c2), rstd * (av[c].y - c1 - xv[c].y * c2),
+                                  rstd * (av[c].z - c1 - xv[c].z * c2), rstd * (av[c].w - c1 - xv[c].w * c2)};
+                    if (dx) *reinterpret_cast<float4*>(dx + m * dx_ld + col) = make_float4(o[0], o[1], o[2], o[3]);
+                    if (dxpl) {
+                        if (drop.enabled) {
+                            float dm[4];
+                            drop_mult4(drop, (uint64_t)(m * D + col) >> 2, dm);
+                            o[0] *= dm[0]; o[1] *= dm[1]; o[2] *= dm[2]; o[3] *= dm[3];
+                        }
+                        store_planes4(dxpl, dxpl_stride, P, m * dxpl_ld + col, o);
+                    }
+                }
             }
         }
+        __syncthreads();
+        if (ccol < D) {
+            const int nrow = (int)min((int64_t)LNB_ROWS, M - m0);
+            for (int r = 0; r < nrow; ++r) {
+                const int64_t mm = m0 + r;
+                const float4 xr = *reinterpret_cast<const float4*>(x + mm * x_ld + ccol);
+                const float4 gr = *reinterpret_cast<const float4*>(g + mm * g_ld + ccol);
+                const float mean = rowc[r][0], rstd = rowc[r][1], c1 = rowc[r][2], c2 = rowc[r][3];
+                const float4 xh = make_float4((xr.x - mean) * rstd, (xr.y - mean) * rstd, (xr.z - mean) * rstd, (xr.w - mean) * rstd);
+                sg.x += gr.x * xh.x; sg.y += gr.y * xh.y; sg.z += gr.z * xh.z; sg.w += gr.w * xh.w;
+                sb.x += gr.x; sb.y += gr.y; sb.z += gr.z; sb.w += gr.w;
+                if (dbias) {
+                    float o[4] = {rstd * (gr.x * gmc.x - c1 - xh.x * c2), rstd * (gr.y * gmc.y - c1 - xh.y * c2),
+                                  rstd * (gr.z * gmc.z - c1 - xh.z * c2), rstd * (gr.w * gmc.w - c1 - xh.w * c2)};
+                    if (drop.enabled) {
+                        float dm[4];
+                        drop_mult4(drop, (uint64_t)(mm * D + ccol) >> 2, dm);
+                        o[0] *= dm[0]; o[1] *= dm[1]; o[2] *= dm[2]; o[3] *= dm[3];
+                    }
+                    sbias.x += o[0]; sbias.y += o[1]; sbias.z += o[2]; sbias.w += o[3];
+                }
+            }
+        }
+        __syncthreads();
     }
-    // block reduction, one 128-column chunk at a time
-#pragma unroll
-    for (int c = 0; c < NCH; ++c) {
-        if (c * 128 >= D) break;
-        __syncthreads();
-        *reinterpret_cast<float4*>(&red[warp][0][lane * 4]) = pg[c];
-        *reinterpret_cast<float4*>(&red[warp][1][lane * 4]) = pb[c];
-        *reinterpret_cast<float4*>(&red[warp][2][lane * 4]) = pbias[c];
-        __syncthreads();
-        for (int i = threadIdx.x; i < 3 * 128; i += LN_THREADS) {
-            const int which = i / 128, j = i - which * 128;
-            const int col = c * 128 + j;
-            float* dst = which == 0 ? dgamma : (which == 1 ? dbeta : dbias);
-            if (col < D && dst) {
-                float s = 0.f;
-#pragma unroll
-                for (int w = 0; w < LN_WARPS; ++w) s += red[w][which][j];
-                atomicAdd(dst + col, s);
-            }
-        }
+    if (ccol < D) {
+        if (dgamma) asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(dgamma + ccol), "f"(sg.x), "f"(sg.y), "f"(sg.z), "f"(sg.w) : "memory");
+        if (dbeta) asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(dbeta + ccol), "f"(sb.x), "f"(sb.y), "f"(sb.z), "f"(sb.w) : "memory");
+        if (dbias) asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(dbias + ccol), "f"(sbias.x), "f"(sbias.y), "f"(sbias.z), "f"(sbias.w) : "memory");
     }
 }
 
@@ -238,7 +256,10 @@ extern "C" int m2f_ln_bwd(const float* g, int64_t g_ld, const float* x, int64_t 
     }
     const Drop drop = drop_make(drop_p, seed, step, site);
     auto st = reinterpret_cast<cudaStream_t>(stream);
-    M2F_LN_DISPATCH(D, (ln_bwd_kernel<NCH><<<ln_grid(M, 4), LN_THREADS, 0, st>>>(g, g_ld, x, x_ld, gamma, stats, M, (int)D, dx_f32, dx_ld, dpl,
+    M2F_REQUIRE((!dgamma || (reinterpret_cast<uintptr_t>(dgamma) % 16) == 0) && (!dbeta || (reinterpret_cast<uintptr_t>(dbeta) % 16) == 0) &&
+                    (!dbias || (reinterpret_cast<uintptr_t>(dbias) % 16) == 0), M2F_ERR_ALIGN, "ln_bwd: dgamma / dbeta / dbias must be 16-byte aligned");
+    const int lnb_grid = (int)std::min<int64_t>((M + LNB_ROWS - 1) / LNB_ROWS, 148 * 4);
+    M2F_LN_DISPATCH(D, (ln_bwd_kernel<NCH><<<lnb_grid, LNB_THREADS, 0, st>>>(g, g_ld, x, x_ld, gamma, stats, M, (int)D, dx_f32, dx_ld, dpl,
                                                                                   dpl_ld, dpl_stride, P, drop, dgamma, dbeta, dbias)));
     M2F_LAUNCH_CHECK();
     return M2F_OK;
