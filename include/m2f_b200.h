@@ -208,12 +208,15 @@ int m2f_plan_loss(m2f_plan_t* p, void* workspace, const float* logits, const int
 int m2f_plan_backward(m2f_plan_t* p, const float* params, const void* shadow, void* workspace, const float* dlogits,
                       float* grads, void* stream);
 
-/* Data-parallel variant: `cb(user, lo, hi)` is called on the host, in enqueue order, each time the gradients of the
- * arena range [lo, hi) (floats) are final on `stream` and at least `bucket_floats` of them have accumulated -- the 2-D
- * weights complete from the top of the arena downwards (classifier, fusion layers, text stack, audio stack), the 1-D
- * region [m2f_model_arena_1d_offset, arena_floats) last.  The caller records an event / launches its NCCL all-reduce
- * of that range from the callback, so the exchange overlaps the rest of the backward. */
-typedef void (*m2f_bucket_cb)(void* user, int64_t lo, int64_t hi);
+/* Data-parallel variant: `cb(user, lo, hi, ready)` is called on the host, in enqueue order, each time at least
+ * `bucket_floats` gradients have accumulated: the arena range [lo, hi) (floats) is final once the work enqueued so far
+ * on the CUDA stream `ready` has completed (the plan runs the backward on several internal streams; `ready` is the one
+ * ordered after the producers of this range, not necessarily `stream`).  The 2-D weights complete from the top of the
+ * arena downwards (classifier, fusion layers, text stack, audio stack), the 1-D region
+ * [m2f_model_arena_1d_offset, arena_floats) last.  The caller launches its NCCL all-reduce of that range behind
+ * `ready` from the callback, so the exchange overlaps the rest of the backward.  When the
+ * call returns, everything (all internal streams) has been joined back into `stream`. */
+typedef void (*m2f_bucket_cb)(void* user, int64_t lo, int64_t hi, void* ready);
 int m2f_plan_backward_bucketed(m2f_plan_t* p, const float* params, const void* shadow, void* workspace,
                                const float* dlogits, float* grads, int64_t bucket_floats, m2f_bucket_cb cb, void* user,
                                void* stream);

@@ -48,7 +48,7 @@ class ModelCfg(C.Structure):
                 ("cls_layers", C.c_int32), ("dropout", C.c_float), ("ffn_dim", C.c_int32), ("planes", C.c_int32)]
 
 
-BUCKET_CB = C.CFUNCTYPE(None, C.c_void_p, C.c_int64, C.c_int64)  # m2f_bucket_cb
+BUCKET_CB = C.CFUNCTYPE(None, C.c_void_p, C.c_int64, C.c_int64, C.c_void_p)  # m2f_bucket_cb
 
 PP = C.POINTER(Planes)
 _i64, _i32, _u64, _u32, _f32, _vp = C.c_int64, C.c_int32, C.c_uint64, C.c_uint32, C.c_float, C.c_void_p

@@ -11,6 +11,7 @@
 //   * concat operands are column halves of one buffer (fusion `u_i`, classifier input `zc`).
 #include <string>
 #include <unordered_map>
+#include <cstdlib>
 #include <vector>
 
 #include "common.cuh"
@@ -180,10 +181,48 @@ struct m2f_plan {
     Buf dl_pl;                              // dlogits planes [M, 8-padded]
     Buf logits_copy;                        // unused placeholder
     // backward scratch
-    Buf gG, gA, gB;                         // fp32 [M, Dmax]
-    Buf dx_pl, dh_pl, do_pl, dqkv_pl;       // encoder backward operands
+    // per modality (the two stacks run concurrently): fp32 chain buffers and two alternating sets (layer parity) of the
+    // operand buffers that the weight-gradient stream reads while the data-gradient chain has moved on
+    struct StackScratch {
+        Buf gG, gA, gB;                     // fp32 [M, D]
+        Buf dx2[2], dx1[2], dh[2], do_[2], dqkv[2];
+    } ss[2];
     Buf dcls_a, dcls_b;                     // classifier hidden gradients (ping-pong)
-    Buf dz_pl, dz2_pl, dxo_pl, dattn_pl, dqv_pl, dkall_pl, dproj_pl, dprojt_pl, gt_f32, ga_f32;
+    Buf dz[3], dxo[2], dattn[2], dqv[2];    // fusion backward (rotating: read by the weight-gradient stream)
+    Buf dkall_pl, dproj_pl, dprojt_pl, gt_f32, ga_f32;
+    // concurrency: aux[0] = audio stack chain, aux[1] = weight gradients of classifier / fusion / text stack,
+    // aux[2] = weight gradients of the audio stack; a ring of events orders work across them
+    cudaStream_t aux[3] = {nullptr, nullptr, nullptr};
+    cudaStream_t ready = nullptr;            // gradient buckets are reported as "final on this stream"
+    cudaEvent_t wg_ev[2][2] = {{nullptr, nullptr}, {nullptr, nullptr}};  // weight gradients of (modality, layer parity) done
+    cudaEvent_t wgf_ev[3] = {nullptr, nullptr, nullptr};                // ... of fusion layer f % 3
+    std::vector<cudaEvent_t> evs;
+    size_t ev_next = 0;
+    int use_streams = 1;
+
+    int ensure_streams() {
+        if (aux[0]) return M2F_OK;
+        for (int i = 0; i < 3; ++i) M2F_CUDA(cudaStreamCreateWithFlags(&aux[i], cudaStreamNonBlocking));
+        M2F_CUDA(cudaStreamCreateWithFlags(&ready, cudaStreamNonBlocking));
+        evs.resize(128);
+        for (auto& e : evs) M2F_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+        for (int i = 0; i < 2; ++i)
+            for (int j = 0; j < 2; ++j) M2F_CUDA(cudaEventCreateWithFlags(&wg_ev[i][j], cudaEventDisableTiming));
+        for (int j = 0; j < 3; ++j) M2F_CUDA(cudaEventCreateWithFlags(&wgf_ev[j], cudaEventDisableTiming));
+        return M2F_OK;
+    }
+    void release_streams() {
+        for (auto& e : evs) cudaEventDestroy(e);
+        evs.clear();
+        for (int i = 0; i < 2; ++i)
+            for (int j = 0; j < 2; ++j)
+                if (wg_ev[i][j]) { cudaEventDestroy(wg_ev[i][j]); wg_ev[i][j] = nullptr; }
+        for (int j = 0; j < 3; ++j)
+            if (wgf_ev[j]) { cudaEventDestroy(wgf_ev[j]); wgf_ev[j] = nullptr; }
+        if (ready) { cudaStreamDestroy(ready); ready = nullptr; }
+        for (int i = 0; i < 3; ++i)
+            if (aux[i]) { cudaStreamDestroy(aux[i]); aux[i] = nullptr; }
+    }
     // state of the last forward
     float p_used = 0.f;
     uint64_t seed = 0, step = 0;
@@ -417,21 +456,38 @@ struct Ctx {
     float* grads;
     uint8_t* shadow;
     uint8_t* ws;
-    cudaStream_t st;
+    cudaStream_t st;   // the caller's stream: everything forks from and joins back into it
     int P;
+    cudaStream_t cur = nullptr;  // stream the next kernels are enqueued on
+
+    cudaStream_t stream() const { return cur ? cur : st; }
+    // work enqueued on `to` after this call waits for everything enqueued on `from` so far
+    int dep(cudaStream_t from, cudaStream_t to) {
+        if (from == to) return M2F_OK;
+        cudaEvent_t e = p->evs[p->ev_next++ % p->evs.size()];
+        M2F_CUDA(cudaEventRecord(e, from));
+        M2F_CUDA(cudaStreamWaitEvent(to, e, 0));
+        return M2F_OK;
+    }
+    cudaStream_t side(int i) const { return p->use_streams ? p->aux[i] : st; }
     // gradient-bucket notification (data-parallel overlap): the 2-D gradients complete top-down in the arena
     int64_t bucket_floats = 0;
     m2f_bucket_cb cb = nullptr;
     void* cb_user = nullptr;
     int64_t hi = 0;
 
-    // every 2-D gradient at arena offsets >= w is final (enqueued on the stream)
-    void done_down_to(int64_t w, bool flush = false) {
-        if (!cb) return;
+    // Every 2-D gradient at arena offsets >= w has been enqueued.  When a bucket is due, the plan's
+    // ready stream is ordered after the weight-gradient streams and handed to the callback: the caller's collective waits on it alone.
+    int done_down_to(int64_t w, bool flush = false) {
+        if (!cb) return M2F_OK;
         if (hi - w >= bucket_floats || (flush && hi > w)) {
-            cb(cb_user, w, hi);
+            cudaStream_t ready = p->use_streams ? p->ready : st;
+            M2F_TRY(dep(side(1), ready));  // the two weight-gradient streams
+            M2F_TRY(dep(side(2), ready));
+            cb(cb_user, w, hi, ready);
             hi = w;
         }
+        return M2F_OK;
     }
 
     m2f_planes_t pv(const Buf& b) const {
@@ -477,7 +533,7 @@ struct Ctx {
         const CUtensorMap *ta, *tb;
         M2F_TRY(tmap(A, a_mn ? BLOCK_K : BLOCK_M, &ta));
         M2F_TRY(tmap(B, b_mn ? BLOCK_K : bn, &tb));
-        return gemm_launch(*ta, *tb, gp, bn, a_mn, b_mn, st);
+        return gemm_launch(*ta, *tb, gp, bn, a_mn, b_mn, stream());
     }
 };
 
@@ -507,7 +563,7 @@ static int forward_modality(Ctx& c, Modality& mo, const float* input, const uint
     const float pd = p->p_used;
     const uint64_t seed = p->seed, step = p->step;
     m2f_planes_t in_pl = c.pv(mo.in_pl);
-    M2F_TRY(m2f_split_planes(input, D, &in_pl, c.st));
+    M2F_TRY(m2f_split_planes(input, D, &in_pl, c.stream()));
     const float* x_f32 = input;
     int64_t x_ld = D;
     m2f_planes_t x_pl = in_pl;
@@ -521,19 +577,19 @@ static int forward_modality(Ctx& c, Modality& mo, const float* input, const uint
             // packed QKV projection (torch/nn/functional.py:5833-5846)
             M2F_TRY(c.gemm(cur_pl, false, c.pv(e.qkv.w), false, M, 3 * D, Epi().bias(c.prm(e.qkv.b_off)).pl(qkv)));
             m2f_planes_t q = Ctx::cols(qkv, 0, D), k = Ctx::cols(qkv, D, D), v = Ctx::cols(qkv, 2 * D, D);
-            M2F_TRY(m2f_attn_fwd(&q, &k, &v, key_pad, p->B, p->S, mo.H, pd, seed, step, M2F_SITE_ENC(mo.idx, t, l, 0), &o, c.st));
+            M2F_TRY(m2f_attn_fwd(&q, &k, &v, key_pad, p->B, p->S, mo.H, pd, seed, step, M2F_SITE_ENC(mo.idx, t, l, 0), &o, c.stream()));
             // x = norm1(x + dropout1(out_proj(attn)))   (transformer.py:951-977)
             M2F_TRY(c.gemm(o, false, c.pv(e.wo.w), false, M, D,
                            Epi().bias(c.prm(e.wo.b_off)).drop(pd, seed, step, M2F_SITE_ENC(mo.idx, t, l, 1), D).resid(cur, cur_ld).f32(c.f32(e.y1), e.y1.ld)));
             M2F_TRY(m2f_ln_fwd(c.f32(e.y1), e.y1.ld, c.prm(e.g1), c.prm(e.be1), nullptr, 0, M, D, c.f32(e.x1), e.x1.ld, &x1p, 0.f, 0, 0, 0,
-                               c.f32(e.st1), c.st));
+                               c.f32(e.st1), c.stream()));
             // x = norm2(x + dropout2(linear2(dropout(relu(linear1(x))))))   (transformer.py:980-982)
             M2F_TRY(c.gemm(x1p, false, c.pv(e.w1.w), false, M, e.w1.out,
                            Epi().bias(c.prm(e.w1.b_off)).relu().drop(pd, seed, step, M2F_SITE_ENC(mo.idx, t, l, 2), e.w1.out).pl(h)));
             M2F_TRY(c.gemm(h, false, c.pv(e.w2.w), false, M, D,
                            Epi().bias(c.prm(e.w2.b_off)).drop(pd, seed, step, M2F_SITE_ENC(mo.idx, t, l, 3), D).resid(c.f32(e.x1), e.x1.ld).f32(c.f32(e.y2), e.y2.ld)));
             M2F_TRY(m2f_ln_fwd(c.f32(e.y2), e.y2.ld, c.prm(e.g2), c.prm(e.be2), nullptr, 0, M, D, c.f32(e.x2), e.x2.ld, &x2p, 0.f, 0, 0, 0,
-                               c.f32(e.st2), c.st));
+                               c.f32(e.st2), c.stream()));
             cur = c.f32(e.x2);
             cur_ld = e.x2.ld;
             cur_pl = x2p;
@@ -543,7 +599,7 @@ static int forward_modality(Ctx& c, Modality& mo, const float* input, const uint
         const bool last = (t == mo.T - 1);
         m2f_planes_t outp = c.pv(mo.xout_pl[t]);
         M2F_TRY(m2f_ln_fwd(cur, cur_ld, c.prm(mo.gf), c.prm(mo.bef), x_f32, x_ld, M, D, last ? nullptr : c.f32(mo.xout[t]), mo.xout[t].ld, &outp,
-                           last ? pd : 0.f, seed, step, M2F_SITE_MOD(mo.idx, 0), c.f32(mo.stf[t]), c.st));
+                           last ? pd : 0.f, seed, step, M2F_SITE_MOD(mo.idx, 0), c.f32(mo.stf[t]), c.stream()));
         x_f32 = c.f32(mo.xout[t]);
         x_ld = mo.xout[t].ld;
         x_pl = outp;
@@ -563,11 +619,21 @@ static int forward_all(Ctx& c, const float* text, const float* audio, const uint
     const uint64_t seed = p->seed, step = p->step;
     m2f_planes_t zc = c.pv(p->zc_pl);
     const bool fam = !p->fam.empty();
-    if (p->mod[0].enabled) M2F_TRY(forward_modality(c, p->mod[0], audio, key_pad, md->both ? Ctx::cols(zc, 0, Df) : zc));
+    // the two modality stacks are independent until the first fusion layer: audio runs on its own stream
+    const bool fork = md->both && p->use_streams;
+    if (p->mod[0].enabled) {
+        if (fork) {
+            M2F_TRY(c.dep(c.st, c.side(0)));
+            c.cur = c.side(0);
+        }
+        M2F_TRY(forward_modality(c, p->mod[0], audio, key_pad, md->both ? Ctx::cols(zc, 0, Df) : zc));
+        c.cur = nullptr;
+    }
     if (p->mod[1].enabled) {
         m2f_planes_t dst = fam ? c.pv(p->t0_pl) : (md->both ? Ctx::cols(zc, Df, Df) : zc);
         M2F_TRY(forward_modality(c, p->mod[1], text, key_pad, dst));
     }
+    if (fork) M2F_TRY(c.dep(c.side(0), c.st));
     if (fam) {
         const int F = (int)p->fam.size();
         m2f_planes_t a = Ctx::cols(zc, 0, Df);
@@ -577,7 +643,7 @@ static int forward_all(Ctx& c, const float* text, const float* audio, const uint
         m2f_planes_t t_cur = c.pv(p->t0_pl);
         {   // relu(text) half of the first concat operand (src/model.py:16-17); later layers' text is already >= 0
             m2f_planes_t u0r = Ctx::cols(c.pv(p->fam[0].u_pl), Df, Df);
-            M2F_TRY(m2f_relu_planes(&t_cur, &u0r, c.st));
+            M2F_TRY(m2f_relu_planes(&t_cur, &u0r, c.stream()));
         }
         for (int f = 0; f < F; ++f) {
             FusionLayer& fl = p->fam[f];
@@ -585,7 +651,7 @@ static int forward_all(Ctx& c, const float* text, const float* audio, const uint
             M2F_TRY(c.gemm(t_cur, false, c.pv(fl.qv.w), false, M, 2 * Df, Epi().bias(c.f32(fl.bqv)).pl(qv)));
             // query = text, key = audio, value = text  (src/model.py:14)
             m2f_planes_t q = Ctx::cols(qv, 0, Df), v = Ctx::cols(qv, Df, Df), k = Ctx::cols(kall, (int64_t)f * Df, Df);
-            M2F_TRY(m2f_attn_fwd(&q, &k, &v, key_pad, p->B, p->S, md->cfg.fam_heads, pd, seed, step, M2F_SITE_FAM(f, 0), &xo, c.st));
+            M2F_TRY(m2f_attn_fwd(&q, &k, &v, key_pad, p->B, p->S, md->cfg.fam_heads, pd, seed, step, M2F_SITE_FAM(f, 0), &xo, c.stream()));
             M2F_TRY(c.gemm(xo, false, c.pv(fl.wo.w), false, M, Df, Epi().bias(c.prm(fl.wo.b_off)).relu().pl(Ctx::cols(u, 0, Df))));
             m2f_planes_t t_next = (f < F - 1) ? Ctx::cols(c.pv(p->fam[f + 1].u_pl), Df, Df) : Ctx::cols(zc, Df, Df);
             // relu(linear(relu(cat(x, text)))) then the model-level dropout (src/model.py:16-19,131)
@@ -615,60 +681,73 @@ static int forward_all(Ctx& c, const float* text, const float* audio, const uint
 
 // ------------------------------------------------------------------------------------------ backward
 // wgrad + bias grad of one Linear: dW[out,in] = dY^T X, db = colsum(dY)
-static int lin_wgrad(Ctx& c, const m2f_planes_t& dY, const m2f_planes_t& X, float* dW, int64_t dW_ld, float* db, int64_t out, int64_t in) {
-    M2F_TRY(c.gemm(dY, true, X, true, out, in, Epi().f32(dW, dW_ld)));
-    if (db) M2F_TRY(m2f_colsum_planes(&dY, db, c.st));
-    return M2F_OK;
+// Off the critical path: enqueued on the weight-gradient stream `wst`, ordered after what the current stream holds so far.
+static int lin_wgrad(Ctx& c, cudaStream_t wst, const m2f_planes_t& dY, const m2f_planes_t& X, float* dW, int64_t dW_ld, float* db, int64_t out,
+                     int64_t in) {
+    cudaStream_t chain = c.stream();
+    M2F_TRY(c.dep(chain, wst));
+    c.cur = wst;
+    int rc = c.gemm(dY, true, X, true, out, in, Epi().f32(dW, dW_ld));
+    if (rc == M2F_OK && db) rc = m2f_colsum_planes(&dY, db, wst);
+    c.cur = chain == c.st ? nullptr : chain;
+    return rc;
 }
 
-static int backward_modality(Ctx& c, Modality& mo, const uint8_t* key_pad, const m2f_planes_t& dproj) {
+// One modality stack, last layer first.  The data-gradient chain runs on the current stream; every weight gradient goes
+// to `wst` (they are off the critical path).  The operand buffers the weight-gradient stream reads alternate between two
+// sets by layer parity; a set is reused only after the weight gradients of its previous user (two layers earlier) are done.
+static int backward_modality(Ctx& c, Modality& mo, const uint8_t* key_pad, const m2f_planes_t& dproj, cudaStream_t wst) {
     m2f_plan* p = c.p;
     const int64_t M = p->M;
     const int D = mo.D;
     const float pd = p->p_used;
     const uint64_t seed = p->seed, step = p->step;
-    float* G = c.f32(p->gG);
-    float* A = c.f32(p->gA);
-    float* Bq = c.f32(p->gB);
-    const int64_t gld = p->gG.ld;
+    m2f_plan::StackScratch& sc = p->ss[mo.idx];
+    float* G = c.f32(sc.gG);
+    float* A = c.f32(sc.gA);
+    float* Bq = c.f32(sc.gB);
+    const int64_t gld = sc.gG.ld;
     // projection: dW, db, and g = dropmask0(dproj . Wp)
     m2f_planes_t xp = c.pv(mo.xout_pl[mo.T - 1]);
-    M2F_TRY(lin_wgrad(c, dproj, xp, c.grd(mo.proj.w_off), mo.proj.in, nullptr, mo.proj.out, mo.proj.in));  // db: by dproj's producer
-    c.done_down_to(mo.proj.w_off);
+    M2F_TRY(lin_wgrad(c, wst, dproj, xp, c.grd(mo.proj.w_off), mo.proj.in, nullptr, mo.proj.out, mo.proj.in));  // db: by dproj's producer
+    M2F_TRY(c.done_down_to(mo.proj.w_off));
     M2F_TRY(c.gemm(dproj, false, c.pv(mo.proj.w), true, M, D, Epi().drop(pd, seed, step, M2F_SITE_MOD(mo.idx, 0), D).f32(G, gld)));
-    m2f_planes_t dxp = c.pv(p->dx_pl), dhp = c.pv(p->dh_pl), dop = c.pv(p->do_pl), dqkvp = c.pv(p->dqkv_pl);
-    dxp.cols = D; dop.cols = D; dqkvp.cols = 3 * D;  // scratch buffers are sized for the wider modality
+    int nlayer = 0;
     for (int t = mo.T - 1; t >= 0; --t) {
         const EncLayer& lastl = mo.layers[(size_t)t * mo.L + mo.L - 1];
         // x_out = x_in + LN_f(x2_last): G is d x_out; A <- d x2_last; G stays as the skip gradient
         M2F_TRY(m2f_ln_bwd(G, gld, c.f32(lastl.x2), lastl.x2.ld, c.prm(mo.gf), c.f32(mo.stf[t]), M, D, A, gld, nullptr, 0.f, 0, 0, 0,
-                           c.grd(mo.gf), c.grd(mo.bef), nullptr, c.st));
-        for (int l = mo.L - 1; l >= 0; --l) {
+                           c.grd(mo.gf), c.grd(mo.bef), nullptr, c.stream()));
+        for (int l = mo.L - 1; l >= 0; --l, ++nlayer) {
             EncLayer& e = mo.layers[(size_t)t * mo.L + l];
             const bool first = (t == 0 && l == 0);
+            const int par = nlayer & 1;
+            if (nlayer >= 2 && wst != c.stream()) M2F_CUDA(cudaStreamWaitEvent(c.stream(), p->wg_ev[mo.idx][par], 0));
+            m2f_planes_t dx2 = c.pv(sc.dx2[par]), dx1 = c.pv(sc.dx1[par]), dhp = c.pv(sc.dh[par]), dop = c.pv(sc.do_[par]), dqkvp = c.pv(sc.dqkv[par]);
             m2f_planes_t in_pl = (l > 0) ? c.pv(mo.layers[(size_t)t * mo.L + l - 1].x2_pl) : (t > 0 ? c.pv(mo.xout_pl[t - 1]) : c.pv(mo.in_pl));
             m2f_planes_t h = c.pv(e.h_pl), x1p = c.pv(e.x1_pl), o = c.pv(e.o_pl), qkv = c.pv(e.qkv_pl);
-            // LN2: A = d x2 -> Bq = d y2 (fp32), dxp = dropmask3(d y2), db2 += colsum
-            M2F_TRY(m2f_ln_bwd(A, gld, c.f32(e.y2), e.y2.ld, c.prm(e.g2), c.f32(e.st2), M, D, Bq, gld, &dxp, pd, seed, step,
-                               M2F_SITE_ENC(mo.idx, t, l, 3), c.grd(e.g2), c.grd(e.be2), c.grd(e.w2.b_off), c.st));
-            M2F_TRY(lin_wgrad(c, dxp, h, c.grd(e.w2.w_off), e.w2.in, nullptr, e.w2.out, e.w2.in));
+            // LN2: A = d x2 -> Bq = d y2 (fp32), dx2 = dropmask3(d y2), db2 += colsum
+            M2F_TRY(m2f_ln_bwd(A, gld, c.f32(e.y2), e.y2.ld, c.prm(e.g2), c.f32(e.st2), M, D, Bq, gld, &dx2, pd, seed, step,
+                               M2F_SITE_ENC(mo.idx, t, l, 3), c.grd(e.g2), c.grd(e.be2), c.grd(e.w2.b_off), c.stream()));
+            M2F_TRY(lin_wgrad(c, wst, dx2, h, c.grd(e.w2.w_off), e.w2.in, nullptr, e.w2.out, e.w2.in));
             // dh = (d y2 . W2) * [h > 0] / (1-p)   (relu + dropout backward from the saved output)
-            M2F_TRY(c.gemm(dxp, false, c.pv(e.w2.w), true, M, e.w2.in, Epi().gate(h, inv_keep(pd)).pl(dhp).colsum(c.grd(e.w1.b_off))));
-            M2F_TRY(lin_wgrad(c, dhp, x1p, c.grd(e.w1.w_off), e.w1.in, nullptr, e.w1.out, e.w1.in));
+            M2F_TRY(c.gemm(dx2, false, c.pv(e.w2.w), true, M, e.w2.in, Epi().gate(h, inv_keep(pd)).pl(dhp).colsum(c.grd(e.w1.b_off))));
+            M2F_TRY(lin_wgrad(c, wst, dhp, x1p, c.grd(e.w1.w_off), e.w1.in, nullptr, e.w1.out, e.w1.in));
             // A = d x1 = dh . W1 + d y2
             M2F_TRY(c.gemm(dhp, false, c.pv(e.w1.w), true, M, D, Epi().resid(Bq, gld).f32(A, gld)));
-            // LN1: A -> Bq = d y1, dxp = dropmask1(d y1), dbo += colsum
-            M2F_TRY(m2f_ln_bwd(A, gld, c.f32(e.y1), e.y1.ld, c.prm(e.g1), c.f32(e.st1), M, D, Bq, gld, &dxp, pd, seed, step,
-                               M2F_SITE_ENC(mo.idx, t, l, 1), c.grd(e.g1), c.grd(e.be1), c.grd(e.wo.b_off), c.st));
-            M2F_TRY(lin_wgrad(c, dxp, o, c.grd(e.wo.w_off), e.wo.in, nullptr, e.wo.out, e.wo.in));
-            M2F_TRY(c.gemm(dxp, false, c.pv(e.wo.w), true, M, D, Epi().pl(dop)));
+            // LN1: A -> Bq = d y1, dx1 = dropmask1(d y1), dbo += colsum
+            M2F_TRY(m2f_ln_bwd(A, gld, c.f32(e.y1), e.y1.ld, c.prm(e.g1), c.f32(e.st1), M, D, Bq, gld, &dx1, pd, seed, step,
+                               M2F_SITE_ENC(mo.idx, t, l, 1), c.grd(e.g1), c.grd(e.be1), c.grd(e.wo.b_off), c.stream()));
+            M2F_TRY(lin_wgrad(c, wst, dx1, o, c.grd(e.wo.w_off), e.wo.in, nullptr, e.wo.out, e.wo.in));
+            M2F_TRY(c.gemm(dx1, false, c.pv(e.wo.w), true, M, D, Epi().pl(dop)));
             m2f_planes_t q = Ctx::cols(qkv, 0, D), k = Ctx::cols(qkv, D, D), v = Ctx::cols(qkv, 2 * D, D);
             m2f_planes_t dq = Ctx::cols(dqkvp, 0, D), dk = Ctx::cols(dqkvp, D, D), dv = Ctx::cols(dqkvp, 2 * D, D);
             float* dbqkv = c.grd(e.qkv.b_off);  // in_proj_bias gradient = column sums of [dq | dk | dv], folded into the attention backward
             M2F_TRY(m2f_attn_bwd(&q, &k, &v, &dop, key_pad, p->B, p->S, mo.H, pd, seed, step, M2F_SITE_ENC(mo.idx, t, l, 0), &dq, &dk, &dv,
-                                 dbqkv, dbqkv + D, dbqkv + 2 * D, c.st));
-            M2F_TRY(lin_wgrad(c, dqkvp, in_pl, c.grd(e.qkv.w_off), e.qkv.in, nullptr, e.qkv.out, e.qkv.in));
-            c.done_down_to(e.qkv.w_off);
+                                 dbqkv, dbqkv + D, dbqkv + 2 * D, c.stream()));
+            M2F_TRY(lin_wgrad(c, wst, dqkvp, in_pl, c.grd(e.qkv.w_off), e.qkv.in, nullptr, e.qkv.out, e.qkv.in));
+            if (wst != c.stream()) M2F_CUDA(cudaEventRecord(p->wg_ev[mo.idx][par], wst));
+            M2F_TRY(c.done_down_to(e.qkv.w_off));
             if (!first) {
                 // gradient w.r.t. the layer input = dqkv . Wqkv + d y1 ; at l == 0 it also joins the skip gradient in G
                 if (l > 0) M2F_TRY(c.gemm(dqkvp, false, c.pv(e.qkv.w), true, M, D, Epi().resid(Bq, gld).f32(A, gld)));
@@ -693,7 +772,7 @@ static int backward_all(Ctx& c, const uint8_t* key_pad, const float* dlogits) {
     if (dlogits) {
         m2f_planes_t dlc = dl;
         dlc.cols = md->cfg.cls_out;
-        M2F_TRY(m2f_split_planes(dlogits, md->cfg.cls_out, &dlc, c.st));
+        M2F_TRY(m2f_split_planes(dlogits, md->cfg.cls_out, &dlc, c.stream()));
     } else {
         M2F_REQUIRE(p->have_loss_grad, M2F_ERR_ARG, "plan_backward: dlogits is NULL but m2f_plan_loss was not called after the forward");
     }
@@ -705,13 +784,15 @@ static int backward_all(Ctx& c, const uint8_t* key_pad, const float* dlogits) {
     m2f_planes_t dproj[2];
     dproj[0] = c.pv(p->dproj_pl);
     dproj[1] = c.pv(p->dprojt_pl);
-    m2f_planes_t dz = c.pv(p->dz_pl);
+    m2f_planes_t dz = c.pv(p->dz[0]);
+    cudaStream_t ws1 = c.side(1);  // weight gradients of the classifier, the fusion layers and the text stack
     for (int j = n_lin - 1; j >= 0; --j) {
         Lin& L = md->cls[j];
         m2f_planes_t in = (j == 0) ? zc : c.pv(p->cls_h[j - 1]);
         // bias gradients ride in the epilogue of the GEMM that produces dY; only dlogits comes from elsewhere
-        M2F_TRY(lin_wgrad(c, d_cur, in, c.grd(L.w_off), L.in, j == n_lin - 1 ? c.grd(L.b_off) : nullptr, L.out, L.in));
+        M2F_TRY(lin_wgrad(c, ws1, d_cur, in, c.grd(L.w_off), L.in, j == n_lin - 1 ? c.grd(L.b_off) : nullptr, L.out, L.in));
         if (j > 0) {
+            if (j <= n_lin - 3) M2F_TRY(c.dep(ws1, c.st));  // the buffer written next was an operand of the weight gradient two layers up
             m2f_planes_t dn = c.pv((j & 1) ? p->dcls_a : p->dcls_b);
             const float sc = (j == n_lin - 1) ? inv_keep(pd) : 1.f;  // only the last hidden layer has dropout
             M2F_TRY(c.gemm(d_cur, false, c.pv(L.w), true, M, L.in, Epi().gate(in, sc).pl(dn).colsum(c.grd(md->cls[j - 1].b_off))));
@@ -737,22 +818,27 @@ static int backward_all(Ctx& c, const uint8_t* key_pad, const float* dlogits) {
                            Epi().drop(pd, seed, step, M2F_SITE_MOD(mi, 1), Df).pl(dproj[mi]).colsum(c.grd(p->mod[mi].proj.b_off))));
         }
     }
-    c.done_down_to(md->cls[0].w_off);
+    M2F_TRY(c.done_down_to(md->cls[0].w_off));
     // ---- fusion stack, last layer first
     if (fam) {
         const int F = (int)p->fam.size();
         m2f_planes_t a = Ctx::cols(zc, 0, Df);
-        m2f_planes_t dxo = c.pv(p->dxo_pl), dattn = c.pv(p->dattn_pl), dqv = c.pv(p->dqv_pl), dkall = c.pv(p->dkall_pl), kall = c.pv(p->kall_pl);
-        m2f_planes_t dz_cur = dz, dz_other = c.pv(p->dz2_pl);
+        m2f_planes_t dkall = c.pv(p->dkall_pl), kall = c.pv(p->kall_pl);
         float* gt = c.f32(p->gt_f32);
         const int64_t gt_ld = p->gt_f32.ld;
-        for (int f = F - 1; f >= 0; --f) {
+        int n = 0;
+        for (int f = F - 1; f >= 0; --f, ++n) {
             FusionLayer& fl = p->fam[f];
+            // scratch rotates (dz over three buffers, the rest over two); a buffer is rewritten only after the weight
+            // gradients of the layer that last read it -- two layers up -- have been computed
+            if (n >= 2 && ws1 != c.st) M2F_CUDA(cudaStreamWaitEvent(c.st, p->wgf_ev[n & 1], 0));
+            m2f_planes_t dz_cur = c.pv(p->dz[n % 3]), dz_other = c.pv(p->dz[(n + 1) % 3]);
+            m2f_planes_t dxo = c.pv(p->dxo[n & 1]), dattn = c.pv(p->dattn[n & 1]), dqv = c.pv(p->dqv[n & 1]);
             m2f_planes_t u = c.pv(fl.u_pl), qv = c.pv(fl.qv_pl), xo = c.pv(fl.xo_pl);
             m2f_planes_t t_in = (f == 0) ? c.pv(p->t0_pl) : Ctx::cols(u, Df, Df);  // the layer's text input
             m2f_planes_t wl = c.pv(fl.lin.w);
             // linear on the concat
-            M2F_TRY(lin_wgrad(c, dz_cur, u, c.grd(fl.lin.w_off), fl.lin.in, nullptr, fl.lin.out, fl.lin.in));
+            M2F_TRY(lin_wgrad(c, ws1, dz_cur, u, c.grd(fl.lin.w_off), fl.lin.in, nullptr, fl.lin.out, fl.lin.in));
             // left half of d u -> gradient w.r.t. the out-proj output (gate: relu(x) > 0)
             M2F_TRY(c.gemm(dz_cur, false, Ctx::cols(wl, 0, Df), true, M, Df, Epi().gate(Ctx::cols(u, 0, Df), 1.f).pl(dxo).colsum(c.grd(fl.wo.b_off))));
             // right half of d u -> first contribution to the gradient of this layer's text input, already in the
@@ -765,7 +851,7 @@ static int backward_all(Ctx& c, const uint8_t* key_pad, const float* dlogits) {
                                Epi().gate(t_in, 1.f).drop(pd, seed, step, M2F_SITE_MOD(1, 1), Df).f32(gt, gt_ld)));
             }
             // attention out-proj
-            M2F_TRY(lin_wgrad(c, dxo, xo, c.grd(fl.wo.w_off), fl.wo.in, nullptr, fl.wo.out, fl.wo.in));
+            M2F_TRY(lin_wgrad(c, ws1, dxo, xo, c.grd(fl.wo.w_off), fl.wo.in, nullptr, fl.wo.out, fl.wo.in));
             M2F_TRY(c.gemm(dxo, false, c.pv(fl.wo.w), true, M, Df, Epi().pl(dattn)));
             m2f_planes_t q = Ctx::cols(qv, 0, Df), v = Ctx::cols(qv, Df, Df), k = Ctx::cols(kall, (int64_t)f * Df, Df);
             m2f_planes_t dq = Ctx::cols(dqv, 0, Df), dv = Ctx::cols(dqv, Df, Df), dk = Ctx::cols(dkall, (int64_t)f * Df, Df);
@@ -773,16 +859,16 @@ static int backward_all(Ctx& c, const uint8_t* key_pad, const float* dlogits) {
             float* dWin = c.grd(fl.inw_off);
             float* dbin = c.grd(fl.inb_off);
             M2F_TRY(m2f_attn_bwd(&q, &k, &v, &dattn, key_pad, p->B, p->S, md->cfg.fam_heads, pd, seed, step, M2F_SITE_FAM(f, 0), &dq, &dk, &dv,
-                                 dbin, dbin + Df, dbin + 2 * Df, c.st));
-            M2F_TRY(lin_wgrad(c, dq, t_in, dWin, Df, nullptr, Df, Df));
-            M2F_TRY(lin_wgrad(c, dv, t_in, dWin + (int64_t)2 * Df * Df, Df, nullptr, Df, Df));
-            M2F_TRY(lin_wgrad(c, dk, a, dWin + (int64_t)Df * Df, Df, nullptr, Df, Df));
-            c.done_down_to(fl.inw_off);
+                                 dbin, dbin + Df, dbin + 2 * Df, c.stream()));
+            M2F_TRY(lin_wgrad(c, ws1, dq, t_in, dWin, Df, nullptr, Df, Df));
+            M2F_TRY(lin_wgrad(c, ws1, dv, t_in, dWin + (int64_t)2 * Df * Df, Df, nullptr, Df, Df));
+            M2F_TRY(lin_wgrad(c, ws1, dk, a, dWin + (int64_t)Df * Df, Df, nullptr, Df, Df));
+            if (ws1 != c.st) M2F_CUDA(cudaEventRecord(p->wgf_ev[n & 1], ws1));
+            M2F_TRY(c.done_down_to(fl.inw_off));
             // second + third contributions to the text-input gradient: [dq | dv] . [Wq; Wv], same gate, summed with gt
             if (f > 0) {
                 M2F_TRY(c.gemm(dqv, false, c.pv(fl.qv.w), true, M, Df,
                                Epi().gate(t_in, inv_keep(pd)).resid(gt, gt_ld).pl(dz_other).colsum(c.grd(p->fam[f - 1].lin.b_off))));
-                std::swap(dz_cur, dz_other);
             } else {
                 M2F_TRY(c.gemm(dqv, false, c.pv(fl.qv.w), true, M, Df,
                                Epi().drop(pd, seed, step, M2F_SITE_MOD(1, 1), Df).resid(gt, gt_ld).pl(dproj[1]).colsum(c.grd(p->mod[1].proj.b_off))));
@@ -795,10 +881,23 @@ static int backward_all(Ctx& c, const uint8_t* key_pad, const float* dlogits) {
     // NOTE on the f == 0 text contribution through q/v: q and v read t0 itself (no cat-relu on that path), so only the
     // projection dropout mask applies -- handled above by not gating the [dq | dv] GEMM at f == 0.
     // text first, audio last: gradients then complete in exactly the reverse of the arena order
-    for (int i = 1; i >= 0; --i)
-        if (p->mod[i].enabled) M2F_TRY(backward_modality(c, p->mod[i], key_pad, dproj[i]));
-    c.done_down_to(0, true);
-    if (c.cb) c.cb(c.cb_user, md->off_1d, md->arena_floats);  // biases / LayerNorm parameters (atomically accumulated)
+    // The two stacks are independent from here on: text continues on the caller's stream, audio runs beside it.
+    if (p->mod[1].enabled) M2F_TRY(backward_modality(c, p->mod[1], key_pad, dproj[1], ws1));
+    if (p->mod[0].enabled) {
+        cudaStream_t as = p->mod[1].enabled ? c.side(0) : c.st;
+        M2F_TRY(c.dep(c.st, as));
+        c.cur = (as == c.st) ? nullptr : as;
+        int rc = backward_modality(c, p->mod[0], key_pad, dproj[0], c.side(2));
+        c.cur = nullptr;
+        M2F_TRY(rc);
+    }
+    M2F_TRY(c.done_down_to(0, true));
+    for (int i = 0; i < 3; ++i) M2F_TRY(c.dep(c.side(i), c.st));
+    if (c.cb) {  // biases / LayerNorm parameters (atomically accumulated by every stream): final once everything has joined
+        cudaStream_t ready = p->use_streams ? p->ready : c.st;
+        M2F_TRY(c.dep(c.st, ready));
+        c.cb(c.cb_user, md->off_1d, md->arena_floats, ready);
+    }
     return M2F_OK;
 }
 
@@ -930,35 +1029,45 @@ extern "C" int m2f_plan_create(m2f_model_t* m, int64_t B, int64_t S, int32_t tra
     for (size_t j = 0; j + 1 < m->cls.size(); ++j) p->cls_h[j] = p->alloc_pl(M, m->cls[j].out, P);
     if (training_plan) {
         p->dl_pl = p->alloc_pl(M, 8 * ((m->cfg.cls_out + 7) / 8), P);
-        const int Dg = std::max(Dmax, Df);
-        p->gG = p->alloc_f32(M, Dg);
-        p->gA = p->alloc_f32(M, Dg);
-        p->gB = p->alloc_f32(M, Dg);
-        // every backward scratch matrix gets ld = its own width; views narrow `cols` only
-        p->dx_pl = p->alloc_pl(M, Dg, P);
-        p->dh_pl = p->alloc_pl(M, FF, P);
-        p->do_pl = p->alloc_pl(M, Dg, P);
-        p->dqkv_pl = p->alloc_pl(M, 3 * Dmax, P);
+        // every backward scratch matrix gets ld = its own width; the two stacks run side by side, so each has its own
+        for (int i = 0; i < 2; ++i) {
+            if (!m->mod[i].enabled) continue;
+            const int D = m->mod[i].D;
+            m2f_plan::StackScratch& sc = p->ss[i];
+            sc.gG = p->alloc_f32(M, D);
+            sc.gA = p->alloc_f32(M, D);
+            sc.gB = p->alloc_f32(M, D);
+            for (int j = 0; j < 2; ++j) {
+                sc.dx2[j] = p->alloc_pl(M, D, P);
+                sc.dx1[j] = p->alloc_pl(M, D, P);
+                sc.dh[j] = p->alloc_pl(M, FF, P);
+                sc.do_[j] = p->alloc_pl(M, D, P);
+                sc.dqkv[j] = p->alloc_pl(M, 3 * D, P);
+            }
+        }
         p->dcls_a = p->alloc_pl(M, m->cfg.cls_hidden, P);
         p->dcls_b = p->alloc_pl(M, m->cfg.cls_hidden, P);
-        p->dz_pl = p->alloc_pl(M, Df, P);
-        p->dz2_pl = p->alloc_pl(M, Df, P);
+        for (int j = 0; j < 3; ++j) p->dz[j] = p->alloc_pl(M, Df, P);
         p->dproj_pl = p->alloc_pl(M, Df, P);
         p->dprojt_pl = p->alloc_pl(M, Df, P);
         if (!m->fam.empty()) {
-            p->dxo_pl = p->alloc_pl(M, Df, P);
-            p->dattn_pl = p->alloc_pl(M, Df, P);
-            p->dqv_pl = p->alloc_pl(M, 2 * Df, P);
+            for (int j = 0; j < 2; ++j) {
+                p->dxo[j] = p->alloc_pl(M, Df, P);
+                p->dattn[j] = p->alloc_pl(M, Df, P);
+                p->dqv[j] = p->alloc_pl(M, 2 * Df, P);
+            }
             p->dkall_pl = p->alloc_pl(M, (int64_t)m->fam.size() * Df, P);
             p->gt_f32 = p->alloc_f32(M, Df);
             p->ga_f32 = p->alloc_f32(M, Df);
         }
     }
+    if (const char* e = std::getenv("M2F_STREAMS")) p->use_streams = (e[0] != '0');  // 0: everything on the caller's stream
     p->ws_bytes = round_up(p->ws_bytes, 256);
     *out = p;
     return M2F_OK;
 }
 extern "C" int m2f_plan_destroy(m2f_plan_t* p) {
+    if (p) p->release_streams();
     delete p;
     return M2F_OK;
 }
@@ -986,6 +1095,7 @@ extern "C" int m2f_plan_forward(m2f_plan_t* p, const float* params, const void* 
                     (reinterpret_cast<uintptr_t>(logits) % 16) == 0 && (reinterpret_cast<uintptr_t>(params) % 16) == 0,
                 M2F_ERR_ALIGN, "plan_forward: text / audio / logits / params must be 16-byte aligned");
     M2F_TRY(bind(p, shadow, workspace));
+    M2F_TRY(p->ensure_streams());
     p->p_used = dropout_on ? md->cfg.dropout : 0.f;
     p->seed = seed;
     p->step = step;
@@ -993,7 +1103,7 @@ extern "C" int m2f_plan_forward(m2f_plan_t* p, const float* params, const void* 
     Ctx c{p, params, nullptr, reinterpret_cast<uint8_t*>(const_cast<void*>(shadow)), reinterpret_cast<uint8_t*>(workspace),
           reinterpret_cast<cudaStream_t>(stream), md->cfg.planes};
     uint8_t* kp = c.ws + p->key_pad.off;
-    M2F_CUDA(cudaMemcpyAsync(kp, key_pad, (size_t)p->M, cudaMemcpyDeviceToDevice, c.st));
+    M2F_CUDA(cudaMemcpyAsync(kp, key_pad, (size_t)p->M, cudaMemcpyDeviceToDevice, c.stream()));
     return forward_all(c, text, audio, kp, logits);
 }
 
@@ -1016,6 +1126,7 @@ extern "C" int m2f_plan_backward_bucketed(m2f_plan_t* p, const float* params, co
     M2F_REQUIRE(p->training, M2F_ERR_ARG, "plan_backward: this plan was created for inference (training_plan = 0)");
     M2F_REQUIRE((reinterpret_cast<uintptr_t>(grads) % 16) == 0, M2F_ERR_ALIGN, "plan_backward: grads must be 16-byte aligned");
     M2F_TRY(bind(p, shadow, workspace));
+    M2F_TRY(p->ensure_streams());
     Ctx c{p, params, grads, reinterpret_cast<uint8_t*>(const_cast<void*>(shadow)), reinterpret_cast<uint8_t*>(workspace),
           reinterpret_cast<cudaStream_t>(stream), p->m->cfg.planes};
     c.bucket_floats = bucket_floats > 0 ? bucket_floats : 1;

@@ -288,9 +288,10 @@ class M2FNet(nn.Module):
         if self._bucket_hook is not None and fresh:
             errors = []
 
-            def _cb(_user, lo, hi):
-                try:
-                    self._bucket_hook(int(lo), int(hi))
+            def _cb(_user, lo, hi, ready):
+                try:  # the range is final behind `ready`: collectives launched by the hook queue up after that stream
+                    with torch.cuda.stream(torch.cuda.ExternalStream(int(ready))):
+                        self._bucket_hook(int(lo), int(hi))
                 except BaseException as e:  # an exception cannot cross the C frame
                     errors.append(e)
 
