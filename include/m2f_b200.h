@@ -84,6 +84,12 @@ const char* m2f_last_error(void);
 /* Number of kernels this library has launched in this process so far (bench.py's `gpu_launches`). */
 int64_t m2f_launch_count(void);
 
+/* Dropout randomness from device memory: while `seed_step` (device pointer to {uint64 seed, uint64 step}) is non-NULL,
+ * every dropout-carrying launch made from the calling host thread reads its (seed, step) from there when the kernel
+ * runs, and ignores the by-value pair -- what lets a captured CUDA graph be replayed with a new step counter.
+ * NULL restores the by-value behaviour. */
+int m2f_set_rng_source(const uint64_t* seed_step);
+
 /* Device capability check: returns M2F_OK only on an sm_100 device. */
 int m2f_check_device(void);
 

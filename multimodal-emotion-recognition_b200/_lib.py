@@ -59,6 +59,7 @@ PROTOTYPES = {
     "m2f_last_error": [],
     "m2f_check_device": [],
     "m2f_launch_count": [],
+    "m2f_set_rng_source": [C.c_void_p],
     "m2f_gemm": [PP, C.c_int, PP, C.c_int, C.POINTER(KSeg), C.c_int, _i64, _i64, C.POINTER(Epilogue), _vp],
     "m2f_split_planes": [_vp, _i64, PP, _vp],
     "m2f_relu_planes": [PP, PP, _vp],

@@ -12,6 +12,9 @@ static thread_local char g_err[512] = "";
 static std::atomic<long long> g_launches{0};
 
 void note_launch() { g_launches.fetch_add(1, std::memory_order_relaxed); }
+void note_launches(long long n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
+static thread_local const unsigned long long* tl_rng_source = nullptr;
+const unsigned long long* rng_source() { return tl_rng_source; }
 
 void set_error(const char* fmt, ...) {
     va_list ap;
@@ -86,6 +89,7 @@ __global__ void colsum_planes_kernel(const __nv_bfloat16* __restrict__ src, int6
 }
 
 __global__ void dropout_mask_kernel(Drop d, int64_t n, uint8_t* mask) {
+    d = drop_resolve(d);
     for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
         mask[i] = drop_mult1(d, (uint64_t)i) > 0.f ? 1 : 0;
 }
@@ -103,6 +107,10 @@ using namespace m2f;
 extern "C" int m2f_abi_version(void) { return M2F_ABI_VERSION; }
 extern "C" const char* m2f_last_error(void) { return g_err; }
 
+extern "C" int m2f_set_rng_source(const uint64_t* seed_step) {
+    m2f::tl_rng_source = reinterpret_cast<const unsigned long long*>(seed_step);
+    return M2F_OK;
+}
 extern "C" int64_t m2f_launch_count(void) { return (int64_t)g_launches.load(std::memory_order_relaxed); }
 
 extern "C" int m2f_check_device(void) {

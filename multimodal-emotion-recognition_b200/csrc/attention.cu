@@ -53,6 +53,7 @@ __device__ __forceinline__ void load_head(float* dst, int hd_pad, const PlanesVi
 __global__ void __launch_bounds__(ATT_THREADS)
 attn_fwd_kernel(PlanesView q, PlanesView k, PlanesView v, const uint8_t* __restrict__ key_pad, int S, int H, int hd, float scale,
                 Drop drop, PlanesOut o) {
+    drop = drop_resolve(drop);
     extern __shared__ float sm[];
     const int hd_pad = hd | 1;  // odd row stride: conflict-free column walks
     float* sK = sm;
@@ -120,6 +121,7 @@ attn_fwd_kernel(PlanesView q, PlanesView k, PlanesView v, const uint8_t* __restr
 __global__ void __launch_bounds__(ATTB_THREADS)
 attn_bwd_kernel(PlanesView q, PlanesView k, PlanesView v, PlanesView d_o, const uint8_t* __restrict__ key_pad, int S, int H, int hd,
                 float scale, Drop drop, PlanesOut dq, PlanesOut dk, PlanesOut dv) {
+    drop = drop_resolve(drop);
     extern __shared__ float sm[];
     const int hd_pad = hd | 1;
     const int s_pad = S | 1;

@@ -61,6 +61,7 @@ __device__ __forceinline__ void softmax_rows(float (&s)[SP / 8][4], uint64_t kv,
 template <int HD, int SP>
 __global__ void __launch_bounds__(SP * 2)
 attn_fwd_mma_kernel(View q, View k, View v, const uint8_t* __restrict__ key_pad, int S, int H, float scale, Drop drop, OutView o) {
+    drop = drop_resolve(drop);
     extern __shared__ __align__(16) uint8_t smraw[];
     constexpr int LDS = HD + 8;
     __nv_bfloat16* sQ = reinterpret_cast<__nv_bfloat16*>(smraw);
@@ -107,6 +108,7 @@ template <int HD, int SP>
 __global__ void __launch_bounds__(SP * 2)
 attn_bwd_mma_kernel(View q, View k, View v, View d_o, const uint8_t* __restrict__ key_pad, int S, int H, float scale, Drop drop,
                     OutView dq, OutView dk, OutView dv, float* dbq, float* dbk, float* dbv) {
+    drop = drop_resolve(drop);
     extern __shared__ __align__(16) uint8_t smraw[];
     constexpr int LDS = HD + 8, LDP = SP + 8;
     __nv_bfloat16* sQ = reinterpret_cast<__nv_bfloat16*>(smraw);

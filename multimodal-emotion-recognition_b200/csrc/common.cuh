@@ -35,6 +35,7 @@ int cuda_fail(cudaError_t e, const char* what, const char* file, int line);
 
 // after a kernel launch: catches bad launch configurations without synchronising
 void note_launch();
+void note_launches(long long n);  // kernels replayed by a CUDA graph launch
 #define M2F_LAUNCH_CHECK()                  \
     do {                                    \
         ::m2f::note_launch();               \
@@ -95,14 +96,32 @@ struct Drop {
     uint32_t thresh;
     float scale;  // 1 / (1 - p)
     int enabled;
+    const unsigned long long* rng;  // device {seed, step} that replaces the by-value pair (m2f_set_rng_source), or NULL
 };
 
-__host__ __device__ __forceinline__ Drop drop_make(float p, uint64_t seed, uint64_t step, uint32_t site) {
+// m2f_set_rng_source: set per host thread; every dropout launch made while it is non-NULL reads (seed, step) from there
+const unsigned long long* rng_source();
+
+__host__ __device__ __forceinline__ Drop drop_make_raw(float p, uint64_t seed, uint64_t step, uint32_t site) {
     Drop d;
     d.ph = philox_make(seed, step, site);
     d.thresh = drop_threshold(p);
     d.scale = p < 1.f ? 1.f / (1.f - p) : 0.f;
     d.enabled = p > 0.f;
+    d.rng = nullptr;
+    return d;
+}
+static inline Drop drop_make(float p, uint64_t seed, uint64_t step, uint32_t site) {
+    Drop d = drop_make_raw(p, seed, step, site);
+    d.rng = rng_source();
+    return d;
+}
+// first thing a kernel does with its descriptor: pick up the device-resident (seed, step) if there is one
+__device__ __forceinline__ Drop drop_resolve(Drop d) {
+    if (d.enabled && d.rng) {
+        const unsigned long long seed = __ldg(d.rng), step = __ldg(d.rng + 1);
+        d.ph = philox_make(seed, step, d.ph.site);
+    }
     return d;
 }
 

@@ -13,6 +13,7 @@
 // (MMA -> epilogue).  One 128 x BLOCK_N output tile per CTA.
 #include <mutex>
 
+#include <cstdlib>
 #include "common.cuh"
 #include "gemm.cuh"
 #include "ptx.cuh"
@@ -328,7 +329,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ C
         e.gate_ld = p.gate_ld; e.resid_ld = p.resid_ld; e.out_f32_ld = p.out_f32_ld; e.out_pl_ld = p.out_pl_ld;
         e.out_pl_stride = p.out_pl_stride; e.drop_ld = p.drop_ld; e.gate_scale = p.gate_scale; e.floor_ = p.relu ? 0.f : -INFINITY;
         e.M = p.M; e.N = p.N; e.out_pl_n = p.out_pl_n; e.accumulate = p.accumulate; e.vec4 = p.vec4; e.drop_on = p.drop.enabled;
-        const Drop drop = p.drop;
+        const Drop drop = drop_resolve(p.drop);
         ptx::mbar_wait(tmem_full_bar, 0);
         if (threadIdx.x == 64) M2F_TRACE(4);
         ptx::tcgen05_fence_after();
@@ -431,6 +432,8 @@ static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const GemmP
 int gemm_block_n(int64_t M, int64_t N) {
     // one 128 x BLOCK_N tile per CTA: prefer the widest tile that still yields >= 148 CTAs
     const int64_t mt = (M + BLOCK_M - 1) / BLOCK_M;
+    static const int forced = [] { const char* e = std::getenv("M2F_GEMM_BN"); return e ? std::atoi(e) : 0; }();  // tuning aid
+    if (forced == 64 || forced == 128 || forced == 256) return (N <= 64) ? 64 : ((N <= 128 && forced == 256) ? 128 : forced);
     if (N > 128 && mt * ((N + 255) / 256) >= 148) return 256;
     if (N > 64 && mt * ((N + 127) / 128) >= 120) return 128;
     return N > 64 && mt * ((N + 63) / 64) > 296 ? 128 : 64;

@@ -19,6 +19,7 @@ __global__ void __launch_bounds__(LN_THREADS)
 ln_fwd_kernel(const float* __restrict__ x, int64_t x_ld, const float* __restrict__ gamma, const float* __restrict__ beta,
               const float* __restrict__ skip, int64_t skip_ld, int64_t M, int D, float* __restrict__ y, int64_t y_ld,
               __nv_bfloat16* __restrict__ ypl, int64_t ypl_ld, int64_t ypl_stride, int P, Drop drop, float* __restrict__ stats) {
+    drop = drop_resolve(drop);
     const int lane = threadIdx.x & 31;
     const int64_t warp0 = (int64_t)blockIdx.x * LN_WARPS + (threadIdx.x >> 5);
     const int64_t nwarps = (int64_t)gridDim.x * LN_WARPS;
@@ -87,6 +88,7 @@ ln_bwd_kernel(const float* __restrict__ g, int64_t g_ld, const float* __restrict
               const float* __restrict__ gamma, const float* __restrict__ stats, int64_t M, int D, float* __restrict__ dx,
               int64_t dx_ld, __nv_bfloat16* __restrict__ dxpl, int64_t dxpl_ld, int64_t dxpl_stride, int P, Drop drop,
               float* __restrict__ dgamma, float* __restrict__ dbeta, float* __restrict__ dbias) {
+    drop = drop_resolve(drop);
     __shared__ float rowc[LNB_ROWS][4];  // mean, rstd, c1, c2
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const float invD = 1.f / (float)D;

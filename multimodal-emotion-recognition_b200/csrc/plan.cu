@@ -11,6 +11,7 @@
 //   * concat operands are column halves of one buffer (fusion `u_i`, classifier input `zc`).
 #include <string>
 #include <unordered_map>
+#include <cstdio>
 #include <cstdlib>
 #include <vector>
 
@@ -199,11 +200,36 @@ struct m2f_plan {
     std::vector<cudaEvent_t> evs;
     size_t ev_next = 0;
     int use_streams = 1;
+    // CUDA graphs: the body of the forward / backward is captured once (on `cap`, with its forks onto aux[]) and replayed
+    // into the caller's stream; whatever depends on per-call pointers (inputs, logits, dlogits) stays outside.
+    struct GraphKey {
+        const void *params = nullptr, *shadow = nullptr, *ws = nullptr, *grads = nullptr;
+        float p_used = -1.f;
+        int flags = 0;
+        bool operator==(const GraphKey& o) const {
+            return params == o.params && shadow == o.shadow && ws == o.ws && grads == o.grads && p_used == o.p_used && flags == o.flags;
+        }
+    };
+    struct GraphSlot {
+        cudaGraphExec_t exec = nullptr;
+        GraphKey key;
+        long long kernels = 0;
+        void reset() {
+            if (exec) cudaGraphExecDestroy(exec);
+            exec = nullptr;
+        }
+    } gf, gb;
+    cudaStream_t cap = nullptr;
+    unsigned long long* rng_dev = nullptr;   // {seed, step} read by the dropout kernels of the captured graphs
+    int use_graph = 1;
+    Buf text_in, audio_in;                   // fp32 staging of the inputs (graph mode: the captured kernels read these)
 
     int ensure_streams() {
         if (aux[0]) return M2F_OK;
         for (int i = 0; i < 3; ++i) M2F_CUDA(cudaStreamCreateWithFlags(&aux[i], cudaStreamNonBlocking));
         M2F_CUDA(cudaStreamCreateWithFlags(&ready, cudaStreamNonBlocking));
+        M2F_CUDA(cudaStreamCreateWithFlags(&cap, cudaStreamNonBlocking));
+        M2F_CUDA(cudaMalloc(&rng_dev, 2 * sizeof(unsigned long long)));
         evs.resize(128);
         for (auto& e : evs) M2F_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
         for (int i = 0; i < 2; ++i)
@@ -219,10 +245,20 @@ struct m2f_plan {
                 if (wg_ev[i][j]) { cudaEventDestroy(wg_ev[i][j]); wg_ev[i][j] = nullptr; }
         for (int j = 0; j < 3; ++j)
             if (wgf_ev[j]) { cudaEventDestroy(wgf_ev[j]); wgf_ev[j] = nullptr; }
+        gf.reset();
+        gb.reset();
+        if (rng_dev) { cudaFree(rng_dev); rng_dev = nullptr; }
+        if (tl_dev) { cudaFree(tl_dev); tl_dev = nullptr; }
+        if (cap) { cudaStreamDestroy(cap); cap = nullptr; }
         if (ready) { cudaStreamDestroy(ready); ready = nullptr; }
         for (int i = 0; i < 3; ++i)
             if (aux[i]) { cudaStreamDestroy(aux[i]); aux[i] = nullptr; }
     }
+    // debug timeline (M2F_TIMELINE=<file>): a 1-thread kernel after every op stamps %globaltimer on the op's stream
+    bool tl_on = false;
+    unsigned long long* tl_dev = nullptr;
+    std::vector<std::pair<std::string, int>> tl_labels;
+    int64_t tl_calls = 0;
     // state of the last forward
     float p_used = 0.f;
     uint64_t seed = 0, step = 0;
@@ -450,6 +486,13 @@ shadow_refresh_kernel(const float* __restrict__ params, uint8_t* __restrict__ sh
 }
 
 // ------------------------------------------------------------------------------------------ execution context
+__global__ void timeline_stamp_kernel(unsigned long long* slot) {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    *slot = t;
+}
+constexpr int TL_CAP = 4096;
+
 struct Ctx {
     m2f_plan* p;
     const float* params;
@@ -462,14 +505,26 @@ struct Ctx {
 
     cudaStream_t stream() const { return cur ? cur : st; }
     // work enqueued on `to` after this call waits for everything enqueued on `from` so far
+    bool forked[3] = {false, false, false};  // side streams that carry work of this call (only those are joined back)
     int dep(cudaStream_t from, cudaStream_t to) {
         if (from == to) return M2F_OK;
+        for (int i = 0; i < 3; ++i) {
+            if (to == p->aux[i]) forked[i] = true;
+            if (from == p->aux[i] && !forked[i]) return M2F_OK;  // nothing was enqueued there
+        }
         cudaEvent_t e = p->evs[p->ev_next++ % p->evs.size()];
         M2F_CUDA(cudaEventRecord(e, from));
         M2F_CUDA(cudaStreamWaitEvent(to, e, 0));
         return M2F_OK;
     }
     cudaStream_t side(int i) const { return p->use_streams ? p->aux[i] : st; }
+    void stamp(const char* label) {
+        if (!p->tl_on || (int)p->tl_labels.size() >= TL_CAP) return;
+        cudaStream_t s = stream();
+        const int sid = (s == st) ? 0 : (s == p->aux[0] ? 1 : (s == p->aux[1] ? 2 : 3));  // main, audio chain, wgrad, wgrad
+        timeline_stamp_kernel<<<1, 1, 0, s>>>(p->tl_dev + p->tl_labels.size());
+        p->tl_labels.emplace_back(std::string(label).substr(0, 70), sid);
+    }
     // gradient-bucket notification (data-parallel overlap): the 2-D gradients complete top-down in the arena
     int64_t bucket_floats = 0;
     m2f_bucket_cb cb = nullptr;
@@ -555,6 +610,13 @@ struct Epi {
 
 static inline float inv_keep(float p) { return 1.f / (1.f - p); }
 
+// an op of the step: M2F_TRY + (debug) a timeline stamp behind it on the same stream
+#define OP(expr)          \
+    do {                  \
+        M2F_TRY(expr);    \
+        c.stamp(#expr);   \
+    } while (0)
+
 // ------------------------------------------------------------------------------------------ forward
 static int forward_modality(Ctx& c, Modality& mo, const float* input, const uint8_t* key_pad, const m2f_planes_t& proj_dst) {
     m2f_plan* p = c.p;
@@ -563,7 +625,7 @@ static int forward_modality(Ctx& c, Modality& mo, const float* input, const uint
     const float pd = p->p_used;
     const uint64_t seed = p->seed, step = p->step;
     m2f_planes_t in_pl = c.pv(mo.in_pl);
-    M2F_TRY(m2f_split_planes(input, D, &in_pl, c.stream()));
+    OP(m2f_split_planes(input, D, &in_pl, c.stream()));
     const float* x_f32 = input;
     int64_t x_ld = D;
     m2f_planes_t x_pl = in_pl;
@@ -575,20 +637,20 @@ static int forward_modality(Ctx& c, Modality& mo, const float* input, const uint
             EncLayer& e = mo.layers[(size_t)t * mo.L + l];
             m2f_planes_t qkv = c.pv(e.qkv_pl), o = c.pv(e.o_pl), x1p = c.pv(e.x1_pl), h = c.pv(e.h_pl), x2p = c.pv(e.x2_pl);
             // packed QKV projection (torch/nn/functional.py:5833-5846)
-            M2F_TRY(c.gemm(cur_pl, false, c.pv(e.qkv.w), false, M, 3 * D, Epi().bias(c.prm(e.qkv.b_off)).pl(qkv)));
+            OP(c.gemm(cur_pl, false, c.pv(e.qkv.w), false, M, 3 * D, Epi().bias(c.prm(e.qkv.b_off)).pl(qkv)));
             m2f_planes_t q = Ctx::cols(qkv, 0, D), k = Ctx::cols(qkv, D, D), v = Ctx::cols(qkv, 2 * D, D);
-            M2F_TRY(m2f_attn_fwd(&q, &k, &v, key_pad, p->B, p->S, mo.H, pd, seed, step, M2F_SITE_ENC(mo.idx, t, l, 0), &o, c.stream()));
+            OP(m2f_attn_fwd(&q, &k, &v, key_pad, p->B, p->S, mo.H, pd, seed, step, M2F_SITE_ENC(mo.idx, t, l, 0), &o, c.stream()));
             // x = norm1(x + dropout1(out_proj(attn)))   (transformer.py:951-977)
-            M2F_TRY(c.gemm(o, false, c.pv(e.wo.w), false, M, D,
+            OP(c.gemm(o, false, c.pv(e.wo.w), false, M, D,
                            Epi().bias(c.prm(e.wo.b_off)).drop(pd, seed, step, M2F_SITE_ENC(mo.idx, t, l, 1), D).resid(cur, cur_ld).f32(c.f32(e.y1), e.y1.ld)));
-            M2F_TRY(m2f_ln_fwd(c.f32(e.y1), e.y1.ld, c.prm(e.g1), c.prm(e.be1), nullptr, 0, M, D, c.f32(e.x1), e.x1.ld, &x1p, 0.f, 0, 0, 0,
+            OP(m2f_ln_fwd(c.f32(e.y1), e.y1.ld, c.prm(e.g1), c.prm(e.be1), nullptr, 0, M, D, c.f32(e.x1), e.x1.ld, &x1p, 0.f, 0, 0, 0,
                                c.f32(e.st1), c.stream()));
             // x = norm2(x + dropout2(linear2(dropout(relu(linear1(x))))))   (transformer.py:980-982)
-            M2F_TRY(c.gemm(x1p, false, c.pv(e.w1.w), false, M, e.w1.out,
+            OP(c.gemm(x1p, false, c.pv(e.w1.w), false, M, e.w1.out,
                            Epi().bias(c.prm(e.w1.b_off)).relu().drop(pd, seed, step, M2F_SITE_ENC(mo.idx, t, l, 2), e.w1.out).pl(h)));
-            M2F_TRY(c.gemm(h, false, c.pv(e.w2.w), false, M, D,
+            OP(c.gemm(h, false, c.pv(e.w2.w), false, M, D,
                            Epi().bias(c.prm(e.w2.b_off)).drop(pd, seed, step, M2F_SITE_ENC(mo.idx, t, l, 3), D).resid(c.f32(e.x1), e.x1.ld).f32(c.f32(e.y2), e.y2.ld)));
-            M2F_TRY(m2f_ln_fwd(c.f32(e.y2), e.y2.ld, c.prm(e.g2), c.prm(e.be2), nullptr, 0, M, D, c.f32(e.x2), e.x2.ld, &x2p, 0.f, 0, 0, 0,
+            OP(m2f_ln_fwd(c.f32(e.y2), e.y2.ld, c.prm(e.g2), c.prm(e.be2), nullptr, 0, M, D, c.f32(e.x2), e.x2.ld, &x2p, 0.f, 0, 0, 0,
                                c.f32(e.st2), c.stream()));
             cur = c.f32(e.x2);
             cur_ld = e.x2.ld;
@@ -598,19 +660,23 @@ static int forward_modality(Ctx& c, Modality& mo, const float* input, const uint
         // also applies the dropout in front of the projection (src/model.py:111,123) to its operand copy
         const bool last = (t == mo.T - 1);
         m2f_planes_t outp = c.pv(mo.xout_pl[t]);
-        M2F_TRY(m2f_ln_fwd(cur, cur_ld, c.prm(mo.gf), c.prm(mo.bef), x_f32, x_ld, M, D, last ? nullptr : c.f32(mo.xout[t]), mo.xout[t].ld, &outp,
+        OP(m2f_ln_fwd(cur, cur_ld, c.prm(mo.gf), c.prm(mo.bef), x_f32, x_ld, M, D, last ? nullptr : c.f32(mo.xout[t]), mo.xout[t].ld, &outp,
                            last ? pd : 0.f, seed, step, M2F_SITE_MOD(mo.idx, 0), c.f32(mo.stf[t]), c.stream()));
         x_f32 = c.f32(mo.xout[t]);
         x_ld = mo.xout[t].ld;
         x_pl = outp;
     }
     // projection to the fusion width + dropout (src/model.py:112-113,124-125)
-    M2F_TRY(c.gemm(x_pl, false, c.pv(mo.proj.w), false, M, mo.proj.out,
+    OP(c.gemm(x_pl, false, c.pv(mo.proj.w), false, M, mo.proj.out,
                    Epi().bias(c.prm(mo.proj.b_off)).drop(pd, seed, step, M2F_SITE_MOD(mo.idx, 1), mo.proj.out).pl(proj_dst)));
     return M2F_OK;
 }
 
-static int forward_all(Ctx& c, const float* text, const float* audio, const uint8_t* key_pad, float* logits) {
+enum { PH_HEAD = 1, PH_BODY = 2, PH_TAIL = 4, PH_ALL = 7 };
+
+// PH_BODY: everything up to the classifier's last hidden layer (capturable: touches only plan-owned memory when text /
+// audio point at the staging copies); PH_TAIL: the logits GEMM (writes the caller's buffer).
+static int forward_all(Ctx& c, const float* text, const float* audio, const uint8_t* key_pad, float* logits, int phases) {
     m2f_plan* p = c.p;
     m2f_model* md = p->m;
     const int64_t M = p->M;
@@ -621,7 +687,9 @@ static int forward_all(Ctx& c, const float* text, const float* audio, const uint
     const bool fam = !p->fam.empty();
     // the two modality stacks are independent until the first fusion layer: audio runs on its own stream
     const bool fork = md->both && p->use_streams;
-    if (p->mod[0].enabled) {
+    const bool body = phases & PH_BODY;
+    if (body) c.stamp("begin");
+    if (body && p->mod[0].enabled) {
         if (fork) {
             M2F_TRY(c.dep(c.st, c.side(0)));
             c.cur = c.side(0);
@@ -629,33 +697,33 @@ static int forward_all(Ctx& c, const float* text, const float* audio, const uint
         M2F_TRY(forward_modality(c, p->mod[0], audio, key_pad, md->both ? Ctx::cols(zc, 0, Df) : zc));
         c.cur = nullptr;
     }
-    if (p->mod[1].enabled) {
+    if (body && p->mod[1].enabled) {
         m2f_planes_t dst = fam ? c.pv(p->t0_pl) : (md->both ? Ctx::cols(zc, Df, Df) : zc);
         M2F_TRY(forward_modality(c, p->mod[1], text, key_pad, dst));
     }
-    if (fork) M2F_TRY(c.dep(c.side(0), c.st));
-    if (fam) {
+    if (body && fork) M2F_TRY(c.dep(c.side(0), c.st));
+    if (body && fam) {
         const int F = (int)p->fam.size();
         m2f_planes_t a = Ctx::cols(zc, 0, Df);
         m2f_planes_t kall = c.pv(p->kall_pl);
         // K projections of every fusion layer read the same audio features: one GEMM
-        M2F_TRY(c.gemm(a, false, c.pv(md->wk_all.w), false, M, (int64_t)F * Df, Epi().bias(c.f32(md->bk_all)).pl(kall)));
+        OP(c.gemm(a, false, c.pv(md->wk_all.w), false, M, (int64_t)F * Df, Epi().bias(c.f32(md->bk_all)).pl(kall)));
         m2f_planes_t t_cur = c.pv(p->t0_pl);
         {   // relu(text) half of the first concat operand (src/model.py:16-17); later layers' text is already >= 0
             m2f_planes_t u0r = Ctx::cols(c.pv(p->fam[0].u_pl), Df, Df);
-            M2F_TRY(m2f_relu_planes(&t_cur, &u0r, c.stream()));
+            OP(m2f_relu_planes(&t_cur, &u0r, c.stream()));
         }
         for (int f = 0; f < F; ++f) {
             FusionLayer& fl = p->fam[f];
             m2f_planes_t qv = c.pv(fl.qv_pl), xo = c.pv(fl.xo_pl), u = c.pv(fl.u_pl);
-            M2F_TRY(c.gemm(t_cur, false, c.pv(fl.qv.w), false, M, 2 * Df, Epi().bias(c.f32(fl.bqv)).pl(qv)));
+            OP(c.gemm(t_cur, false, c.pv(fl.qv.w), false, M, 2 * Df, Epi().bias(c.f32(fl.bqv)).pl(qv)));
             // query = text, key = audio, value = text  (src/model.py:14)
             m2f_planes_t q = Ctx::cols(qv, 0, Df), v = Ctx::cols(qv, Df, Df), k = Ctx::cols(kall, (int64_t)f * Df, Df);
-            M2F_TRY(m2f_attn_fwd(&q, &k, &v, key_pad, p->B, p->S, md->cfg.fam_heads, pd, seed, step, M2F_SITE_FAM(f, 0), &xo, c.stream()));
-            M2F_TRY(c.gemm(xo, false, c.pv(fl.wo.w), false, M, Df, Epi().bias(c.prm(fl.wo.b_off)).relu().pl(Ctx::cols(u, 0, Df))));
+            OP(m2f_attn_fwd(&q, &k, &v, key_pad, p->B, p->S, md->cfg.fam_heads, pd, seed, step, M2F_SITE_FAM(f, 0), &xo, c.stream()));
+            OP(c.gemm(xo, false, c.pv(fl.wo.w), false, M, Df, Epi().bias(c.prm(fl.wo.b_off)).relu().pl(Ctx::cols(u, 0, Df))));
             m2f_planes_t t_next = (f < F - 1) ? Ctx::cols(c.pv(p->fam[f + 1].u_pl), Df, Df) : Ctx::cols(zc, Df, Df);
             // relu(linear(relu(cat(x, text)))) then the model-level dropout (src/model.py:16-19,131)
-            M2F_TRY(c.gemm(u, false, c.pv(fl.lin.w), false, M, Df,
+            OP(c.gemm(u, false, c.pv(fl.lin.w), false, M, Df,
                            Epi().bias(c.prm(fl.lin.b_off)).relu().drop(pd, seed, step, M2F_SITE_FAM(f, 1), Df).pl(t_next)));
             t_cur = t_next;
         }
@@ -670,10 +738,10 @@ static int forward_all(Ctx& c, const float* text, const float* audio, const uint
             Epi e;
             e.bias(c.prm(L.b_off)).relu().pl(hj);
             if (j == n_lin - 2) e.drop(pd, seed, step, M2F_SITE_CLS, L.out);
-            M2F_TRY(c.gemm(in, false, c.pv(L.w), false, M, L.out, e));
+            if (body) OP(c.gemm(in, false, c.pv(L.w), false, M, L.out, e));
             in = hj;
-        } else {
-            M2F_TRY(c.gemm(in, false, c.pv(L.w), false, M, L.out, Epi().bias(c.prm(L.b_off)).f32(logits, L.out)));
+        } else if (phases & PH_TAIL) {
+            OP(c.gemm(in, false, c.pv(L.w), false, M, L.out, Epi().bias(c.prm(L.b_off)).f32(logits, L.out)));
         }
     }
     return M2F_OK;
@@ -689,6 +757,7 @@ static int lin_wgrad(Ctx& c, cudaStream_t wst, const m2f_planes_t& dY, const m2f
     c.cur = wst;
     int rc = c.gemm(dY, true, X, true, out, in, Epi().f32(dW, dW_ld));
     if (rc == M2F_OK && db) rc = m2f_colsum_planes(&dY, db, wst);
+    c.stamp("wgrad");
     c.cur = chain == c.st ? nullptr : chain;
     return rc;
 }
@@ -711,12 +780,12 @@ static int backward_modality(Ctx& c, Modality& mo, const uint8_t* key_pad, const
     m2f_planes_t xp = c.pv(mo.xout_pl[mo.T - 1]);
     M2F_TRY(lin_wgrad(c, wst, dproj, xp, c.grd(mo.proj.w_off), mo.proj.in, nullptr, mo.proj.out, mo.proj.in));  // db: by dproj's producer
     M2F_TRY(c.done_down_to(mo.proj.w_off));
-    M2F_TRY(c.gemm(dproj, false, c.pv(mo.proj.w), true, M, D, Epi().drop(pd, seed, step, M2F_SITE_MOD(mo.idx, 0), D).f32(G, gld)));
+    OP(c.gemm(dproj, false, c.pv(mo.proj.w), true, M, D, Epi().drop(pd, seed, step, M2F_SITE_MOD(mo.idx, 0), D).f32(G, gld)));
     int nlayer = 0;
     for (int t = mo.T - 1; t >= 0; --t) {
         const EncLayer& lastl = mo.layers[(size_t)t * mo.L + mo.L - 1];
         // x_out = x_in + LN_f(x2_last): G is d x_out; A <- d x2_last; G stays as the skip gradient
-        M2F_TRY(m2f_ln_bwd(G, gld, c.f32(lastl.x2), lastl.x2.ld, c.prm(mo.gf), c.f32(mo.stf[t]), M, D, A, gld, nullptr, 0.f, 0, 0, 0,
+        OP(m2f_ln_bwd(G, gld, c.f32(lastl.x2), lastl.x2.ld, c.prm(mo.gf), c.f32(mo.stf[t]), M, D, A, gld, nullptr, 0.f, 0, 0, 0,
                            c.grd(mo.gf), c.grd(mo.bef), nullptr, c.stream()));
         for (int l = mo.L - 1; l >= 0; --l, ++nlayer) {
             EncLayer& e = mo.layers[(size_t)t * mo.L + l];
@@ -727,38 +796,39 @@ static int backward_modality(Ctx& c, Modality& mo, const uint8_t* key_pad, const
             m2f_planes_t in_pl = (l > 0) ? c.pv(mo.layers[(size_t)t * mo.L + l - 1].x2_pl) : (t > 0 ? c.pv(mo.xout_pl[t - 1]) : c.pv(mo.in_pl));
             m2f_planes_t h = c.pv(e.h_pl), x1p = c.pv(e.x1_pl), o = c.pv(e.o_pl), qkv = c.pv(e.qkv_pl);
             // LN2: A = d x2 -> Bq = d y2 (fp32), dx2 = dropmask3(d y2), db2 += colsum
-            M2F_TRY(m2f_ln_bwd(A, gld, c.f32(e.y2), e.y2.ld, c.prm(e.g2), c.f32(e.st2), M, D, Bq, gld, &dx2, pd, seed, step,
+            OP(m2f_ln_bwd(A, gld, c.f32(e.y2), e.y2.ld, c.prm(e.g2), c.f32(e.st2), M, D, Bq, gld, &dx2, pd, seed, step,
                                M2F_SITE_ENC(mo.idx, t, l, 3), c.grd(e.g2), c.grd(e.be2), c.grd(e.w2.b_off), c.stream()));
             M2F_TRY(lin_wgrad(c, wst, dx2, h, c.grd(e.w2.w_off), e.w2.in, nullptr, e.w2.out, e.w2.in));
             // dh = (d y2 . W2) * [h > 0] / (1-p)   (relu + dropout backward from the saved output)
-            M2F_TRY(c.gemm(dx2, false, c.pv(e.w2.w), true, M, e.w2.in, Epi().gate(h, inv_keep(pd)).pl(dhp).colsum(c.grd(e.w1.b_off))));
+            OP(c.gemm(dx2, false, c.pv(e.w2.w), true, M, e.w2.in, Epi().gate(h, inv_keep(pd)).pl(dhp).colsum(c.grd(e.w1.b_off))));
             M2F_TRY(lin_wgrad(c, wst, dhp, x1p, c.grd(e.w1.w_off), e.w1.in, nullptr, e.w1.out, e.w1.in));
             // A = d x1 = dh . W1 + d y2
-            M2F_TRY(c.gemm(dhp, false, c.pv(e.w1.w), true, M, D, Epi().resid(Bq, gld).f32(A, gld)));
+            OP(c.gemm(dhp, false, c.pv(e.w1.w), true, M, D, Epi().resid(Bq, gld).f32(A, gld)));
             // LN1: A -> Bq = d y1, dx1 = dropmask1(d y1), dbo += colsum
-            M2F_TRY(m2f_ln_bwd(A, gld, c.f32(e.y1), e.y1.ld, c.prm(e.g1), c.f32(e.st1), M, D, Bq, gld, &dx1, pd, seed, step,
+            OP(m2f_ln_bwd(A, gld, c.f32(e.y1), e.y1.ld, c.prm(e.g1), c.f32(e.st1), M, D, Bq, gld, &dx1, pd, seed, step,
                                M2F_SITE_ENC(mo.idx, t, l, 1), c.grd(e.g1), c.grd(e.be1), c.grd(e.wo.b_off), c.stream()));
             M2F_TRY(lin_wgrad(c, wst, dx1, o, c.grd(e.wo.w_off), e.wo.in, nullptr, e.wo.out, e.wo.in));
-            M2F_TRY(c.gemm(dx1, false, c.pv(e.wo.w), true, M, D, Epi().pl(dop)));
+            OP(c.gemm(dx1, false, c.pv(e.wo.w), true, M, D, Epi().pl(dop)));
             m2f_planes_t q = Ctx::cols(qkv, 0, D), k = Ctx::cols(qkv, D, D), v = Ctx::cols(qkv, 2 * D, D);
             m2f_planes_t dq = Ctx::cols(dqkvp, 0, D), dk = Ctx::cols(dqkvp, D, D), dv = Ctx::cols(dqkvp, 2 * D, D);
             float* dbqkv = c.grd(e.qkv.b_off);  // in_proj_bias gradient = column sums of [dq | dk | dv], folded into the attention backward
-            M2F_TRY(m2f_attn_bwd(&q, &k, &v, &dop, key_pad, p->B, p->S, mo.H, pd, seed, step, M2F_SITE_ENC(mo.idx, t, l, 0), &dq, &dk, &dv,
+            OP(m2f_attn_bwd(&q, &k, &v, &dop, key_pad, p->B, p->S, mo.H, pd, seed, step, M2F_SITE_ENC(mo.idx, t, l, 0), &dq, &dk, &dv,
                                  dbqkv, dbqkv + D, dbqkv + 2 * D, c.stream()));
             M2F_TRY(lin_wgrad(c, wst, dqkvp, in_pl, c.grd(e.qkv.w_off), e.qkv.in, nullptr, e.qkv.out, e.qkv.in));
             if (wst != c.stream()) M2F_CUDA(cudaEventRecord(p->wg_ev[mo.idx][par], wst));
             M2F_TRY(c.done_down_to(e.qkv.w_off));
             if (!first) {
                 // gradient w.r.t. the layer input = dqkv . Wqkv + d y1 ; at l == 0 it also joins the skip gradient in G
-                if (l > 0) M2F_TRY(c.gemm(dqkvp, false, c.pv(e.qkv.w), true, M, D, Epi().resid(Bq, gld).f32(A, gld)));
-                else       M2F_TRY(c.gemm(dqkvp, false, c.pv(e.qkv.w), true, M, D, Epi().resid(Bq, gld).f32(G, gld, true)));
+                if (l > 0) OP(c.gemm(dqkvp, false, c.pv(e.qkv.w), true, M, D, Epi().resid(Bq, gld).f32(A, gld)));
+                else       OP(c.gemm(dqkvp, false, c.pv(e.qkv.w), true, M, D, Epi().resid(Bq, gld).f32(G, gld, true)));
             }
         }
     }
     return M2F_OK;
 }
 
-static int backward_all(Ctx& c, const uint8_t* key_pad, const float* dlogits) {
+// PH_HEAD: dlogits -> planes (reads the caller's buffer); PH_BODY: the rest (capturable)
+static int backward_all(Ctx& c, const uint8_t* key_pad, const float* dlogits, int phases) {
     m2f_plan* p = c.p;
     m2f_model* md = p->m;
     const int64_t M = p->M;
@@ -766,16 +836,19 @@ static int backward_all(Ctx& c, const uint8_t* key_pad, const float* dlogits) {
     const float pd = p->p_used;
     const uint64_t seed = p->seed, step = p->step;
     const bool fam = !p->fam.empty();
+    m2f_planes_t dl = c.pv(p->dl_pl);
+    if (phases & PH_HEAD) {
+        if (dlogits) {
+            m2f_planes_t dlc = dl;
+            dlc.cols = md->cfg.cls_out;
+            OP(m2f_split_planes(dlogits, md->cfg.cls_out, &dlc, c.stream()));
+        } else {
+            M2F_REQUIRE(p->have_loss_grad, M2F_ERR_ARG, "plan_backward: dlogits is NULL but m2f_plan_loss was not called after the forward");
+        }
+    }
+    if (!(phases & PH_BODY)) return M2F_OK;
     // 1-D gradients are accumulated with atomics: zero that region of the arena
     M2F_CUDA(cudaMemsetAsync(c.grads + md->off_1d, 0, (size_t)(md->arena_floats - md->off_1d) * 4, c.st));
-    m2f_planes_t dl = c.pv(p->dl_pl);
-    if (dlogits) {
-        m2f_planes_t dlc = dl;
-        dlc.cols = md->cfg.cls_out;
-        M2F_TRY(m2f_split_planes(dlogits, md->cfg.cls_out, &dlc, c.stream()));
-    } else {
-        M2F_REQUIRE(p->have_loss_grad, M2F_ERR_ARG, "plan_backward: dlogits is NULL but m2f_plan_loss was not called after the forward");
-    }
     dl.cols = md->cfg.cls_out;
     m2f_planes_t zc = c.pv(p->zc_pl);
     // ---- classifier
@@ -795,26 +868,26 @@ static int backward_all(Ctx& c, const uint8_t* key_pad, const float* dlogits) {
             if (j <= n_lin - 3) M2F_TRY(c.dep(ws1, c.st));  // the buffer written next was an operand of the weight gradient two layers up
             m2f_planes_t dn = c.pv((j & 1) ? p->dcls_a : p->dcls_b);
             const float sc = (j == n_lin - 1) ? inv_keep(pd) : 1.f;  // only the last hidden layer has dropout
-            M2F_TRY(c.gemm(d_cur, false, c.pv(L.w), true, M, L.in, Epi().gate(in, sc).pl(dn).colsum(c.grd(md->cls[j - 1].b_off))));
+            OP(c.gemm(d_cur, false, c.pv(L.w), true, M, L.in, Epi().gate(in, sc).pl(dn).colsum(c.grd(md->cls[j - 1].b_off))));
             d_cur = dn;
         } else if (md->both) {
             m2f_planes_t w = c.pv(L.w);
             // audio half of the concat: gradient w.r.t. the projection's pre-dropout output (mask regenerated)
             if (fam) {
-                M2F_TRY(c.gemm(d_cur, false, Ctx::cols(w, 0, Df), true, M, Df,
+                OP(c.gemm(d_cur, false, Ctx::cols(w, 0, Df), true, M, Df,
                                Epi().drop(pd, seed, step, M2F_SITE_MOD(0, 1), Df).f32(c.f32(p->ga_f32), p->ga_f32.ld)));
                 // text half: gradient w.r.t. the last fusion linear's pre-activation
-                M2F_TRY(c.gemm(d_cur, false, Ctx::cols(w, Df, Df), true, M, Df,
+                OP(c.gemm(d_cur, false, Ctx::cols(w, Df, Df), true, M, Df,
                                Epi().gate(Ctx::cols(zc, Df, Df), inv_keep(pd)).pl(dz).colsum(c.grd(p->fam.back().lin.b_off))));
             } else {
-                M2F_TRY(c.gemm(d_cur, false, Ctx::cols(w, 0, Df), true, M, Df,
+                OP(c.gemm(d_cur, false, Ctx::cols(w, 0, Df), true, M, Df,
                                Epi().drop(pd, seed, step, M2F_SITE_MOD(0, 1), Df).pl(dproj[0]).colsum(c.grd(p->mod[0].proj.b_off))));
-                M2F_TRY(c.gemm(d_cur, false, Ctx::cols(w, Df, Df), true, M, Df,
+                OP(c.gemm(d_cur, false, Ctx::cols(w, Df, Df), true, M, Df,
                                Epi().drop(pd, seed, step, M2F_SITE_MOD(1, 1), Df).pl(dproj[1]).colsum(c.grd(p->mod[1].proj.b_off))));
             }
         } else {
             const int mi = p->mod[0].enabled ? 0 : 1;
-            M2F_TRY(c.gemm(d_cur, false, c.pv(L.w), true, M, Df,
+            OP(c.gemm(d_cur, false, c.pv(L.w), true, M, Df,
                            Epi().drop(pd, seed, step, M2F_SITE_MOD(mi, 1), Df).pl(dproj[mi]).colsum(c.grd(p->mod[mi].proj.b_off))));
         }
     }
@@ -840,25 +913,25 @@ static int backward_all(Ctx& c, const uint8_t* key_pad, const float* dlogits) {
             // linear on the concat
             M2F_TRY(lin_wgrad(c, ws1, dz_cur, u, c.grd(fl.lin.w_off), fl.lin.in, nullptr, fl.lin.out, fl.lin.in));
             // left half of d u -> gradient w.r.t. the out-proj output (gate: relu(x) > 0)
-            M2F_TRY(c.gemm(dz_cur, false, Ctx::cols(wl, 0, Df), true, M, Df, Epi().gate(Ctx::cols(u, 0, Df), 1.f).pl(dxo).colsum(c.grd(fl.wo.b_off))));
+            OP(c.gemm(dz_cur, false, Ctx::cols(wl, 0, Df), true, M, Df, Epi().gate(Ctx::cols(u, 0, Df), 1.f).pl(dxo).colsum(c.grd(fl.wo.b_off))));
             // right half of d u -> first contribution to the gradient of this layer's text input, already in the
             // pre-activation space of its producer: previous fusion linear (relu + dropout: gate [t > 0] / (1-p))
             // or the text projection (cat-relu gate [t0 > 0], then the regenerated projection dropout mask)
             if (f > 0) {
-                M2F_TRY(c.gemm(dz_cur, false, Ctx::cols(wl, Df, Df), true, M, Df, Epi().gate(t_in, inv_keep(pd)).f32(gt, gt_ld)));
+                OP(c.gemm(dz_cur, false, Ctx::cols(wl, Df, Df), true, M, Df, Epi().gate(t_in, inv_keep(pd)).f32(gt, gt_ld)));
             } else {
-                M2F_TRY(c.gemm(dz_cur, false, Ctx::cols(wl, Df, Df), true, M, Df,
+                OP(c.gemm(dz_cur, false, Ctx::cols(wl, Df, Df), true, M, Df,
                                Epi().gate(t_in, 1.f).drop(pd, seed, step, M2F_SITE_MOD(1, 1), Df).f32(gt, gt_ld)));
             }
             // attention out-proj
             M2F_TRY(lin_wgrad(c, ws1, dxo, xo, c.grd(fl.wo.w_off), fl.wo.in, nullptr, fl.wo.out, fl.wo.in));
-            M2F_TRY(c.gemm(dxo, false, c.pv(fl.wo.w), true, M, Df, Epi().pl(dattn)));
+            OP(c.gemm(dxo, false, c.pv(fl.wo.w), true, M, Df, Epi().pl(dattn)));
             m2f_planes_t q = Ctx::cols(qv, 0, Df), v = Ctx::cols(qv, Df, Df), k = Ctx::cols(kall, (int64_t)f * Df, Df);
             m2f_planes_t dq = Ctx::cols(dqv, 0, Df), dv = Ctx::cols(dqv, Df, Df), dk = Ctx::cols(dkall, (int64_t)f * Df, Df);
             // in-projection weight / bias gradients: rows [0,E) = q, [E,2E) = k, [2E,3E) = v of in_proj_weight
             float* dWin = c.grd(fl.inw_off);
             float* dbin = c.grd(fl.inb_off);
-            M2F_TRY(m2f_attn_bwd(&q, &k, &v, &dattn, key_pad, p->B, p->S, md->cfg.fam_heads, pd, seed, step, M2F_SITE_FAM(f, 0), &dq, &dk, &dv,
+            OP(m2f_attn_bwd(&q, &k, &v, &dattn, key_pad, p->B, p->S, md->cfg.fam_heads, pd, seed, step, M2F_SITE_FAM(f, 0), &dq, &dk, &dv,
                                  dbin, dbin + Df, dbin + 2 * Df, c.stream()));
             M2F_TRY(lin_wgrad(c, ws1, dq, t_in, dWin, Df, nullptr, Df, Df));
             M2F_TRY(lin_wgrad(c, ws1, dv, t_in, dWin + (int64_t)2 * Df * Df, Df, nullptr, Df, Df));
@@ -867,15 +940,15 @@ static int backward_all(Ctx& c, const uint8_t* key_pad, const float* dlogits) {
             M2F_TRY(c.done_down_to(fl.inw_off));
             // second + third contributions to the text-input gradient: [dq | dv] . [Wq; Wv], same gate, summed with gt
             if (f > 0) {
-                M2F_TRY(c.gemm(dqv, false, c.pv(fl.qv.w), true, M, Df,
+                OP(c.gemm(dqv, false, c.pv(fl.qv.w), true, M, Df,
                                Epi().gate(t_in, inv_keep(pd)).resid(gt, gt_ld).pl(dz_other).colsum(c.grd(p->fam[f - 1].lin.b_off))));
             } else {
-                M2F_TRY(c.gemm(dqv, false, c.pv(fl.qv.w), true, M, Df,
+                OP(c.gemm(dqv, false, c.pv(fl.qv.w), true, M, Df,
                                Epi().drop(pd, seed, step, M2F_SITE_MOD(1, 1), Df).resid(gt, gt_ld).pl(dproj[1]).colsum(c.grd(p->mod[1].proj.b_off))));
             }
         }
         // audio: every layer's K projection + the classifier half, through the projection dropout mask
-        M2F_TRY(c.gemm(dkall, false, c.pv(md->wk_all.w), true, M, Df,
+        OP(c.gemm(dkall, false, c.pv(md->wk_all.w), true, M, Df,
                        Epi().drop(pd, seed, step, M2F_SITE_MOD(0, 1), Df).resid(c.f32(p->ga_f32), p->ga_f32.ld).pl(dproj[0]).colsum(c.grd(p->mod[0].proj.b_off))));
     }
     // NOTE on the f == 0 text contribution through q/v: q and v read t0 itself (no cat-relu on that path), so only the
@@ -1061,7 +1134,10 @@ extern "C" int m2f_plan_create(m2f_model_t* m, int64_t B, int64_t S, int32_t tra
             p->ga_f32 = p->alloc_f32(M, Df);
         }
     }
-    if (const char* e = std::getenv("M2F_STREAMS")) p->use_streams = (e[0] != '0');  // 0: everything on the caller's stream
+    if (const char* e = std::getenv("M2F_STREAMS")) p->use_streams = (e[0] != '0');
+    if (const char* e = std::getenv("M2F_GRAPH")) p->use_graph = (e[0] != '0');      // 0: launch every kernel eagerly
+    if (m->mod[1].enabled) p->text_in = p->alloc_f32(M, m->mod[1].D);
+    if (m->mod[0].enabled) p->audio_in = p->alloc_f32(M, m->mod[0].D);  // 0: everything on the caller's stream
     p->ws_bytes = round_up(p->ws_bytes, 256);
     *out = p;
     return M2F_OK;
@@ -1084,6 +1160,42 @@ static int bind(m2f_plan* p, const void* shadow, void* ws) {
     return M2F_OK;
 }
 
+// Capture `body` (enqueued on the plan's capture stream, forking onto its side streams) once per key, then replay it
+// into the caller's stream.  Dropout kernels captured here read (seed, step) from p->rng_dev.
+template <class F>
+static int run_graphed(m2f_plan* p, m2f_plan::GraphSlot& g, const m2f_plan::GraphKey& key, cudaStream_t user, F&& body) {
+    if (!g.exec || !(g.key == key)) {
+        g.reset();
+        const long long l0 = m2f_launch_count();
+        M2F_CUDA(cudaStreamBeginCapture(p->cap, cudaStreamCaptureModeThreadLocal));
+        m2f_set_rng_source(reinterpret_cast<const uint64_t*>(p->rng_dev));
+        const int rc = body(p->cap);
+        m2f_set_rng_source(nullptr);
+        cudaGraph_t graph = nullptr;
+        const cudaError_t e = cudaStreamEndCapture(p->cap, &graph);
+        const long long captured = m2f_launch_count() - l0;
+        note_launches(-captured);  // nothing ran yet
+        if (rc != M2F_OK) {
+            if (graph) cudaGraphDestroy(graph);
+            return rc;
+        }
+        M2F_CUDA(e);
+        const cudaError_t ei = cudaGraphInstantiate(&g.exec, graph, 0);
+        cudaGraphDestroy(graph);
+        M2F_CUDA(ei);
+        g.key = key;
+        g.kernels = captured;
+    }
+    M2F_CUDA(cudaGraphLaunch(g.exec, user));
+    note_launches(g.kernels);
+    return M2F_OK;
+}
+
+__global__ void set_rng_kernel(unsigned long long* dst, unsigned long long seed, unsigned long long step) {
+    dst[0] = seed;
+    dst[1] = step;
+}
+
 extern "C" int m2f_plan_forward(m2f_plan_t* p, const float* params, const void* shadow, void* workspace, const float* text,
                                 const float* audio, const uint8_t* key_pad, int32_t dropout_on, uint64_t seed, uint64_t step, float* logits,
                                 void* stream) {
@@ -1100,11 +1212,45 @@ extern "C" int m2f_plan_forward(m2f_plan_t* p, const float* params, const void* 
     p->seed = seed;
     p->step = step;
     p->have_loss_grad = false;
-    Ctx c{p, params, nullptr, reinterpret_cast<uint8_t*>(const_cast<void*>(shadow)), reinterpret_cast<uint8_t*>(workspace),
-          reinterpret_cast<cudaStream_t>(stream), md->cfg.planes};
+    cudaStream_t user = reinterpret_cast<cudaStream_t>(stream);
+    Ctx c{p, params, nullptr, reinterpret_cast<uint8_t*>(const_cast<void*>(shadow)), reinterpret_cast<uint8_t*>(workspace), user,
+          md->cfg.planes};
     uint8_t* kp = c.ws + p->key_pad.off;
-    M2F_CUDA(cudaMemcpyAsync(kp, key_pad, (size_t)p->M, cudaMemcpyDeviceToDevice, c.stream()));
-    return forward_all(c, text, audio, kp, logits);
+    M2F_CUDA(cudaMemcpyAsync(kp, key_pad, (size_t)p->M, cudaMemcpyDeviceToDevice, user));
+    const bool timeline = std::getenv("M2F_TIMELINE") != nullptr && p->training;
+    if (timeline) {
+        if (!p->tl_dev) M2F_CUDA(cudaMalloc(&p->tl_dev, TL_CAP * sizeof(unsigned long long)));
+        p->tl_on = true;
+    }
+    if (!p->use_graph) {
+        if (timeline) p->tl_labels.clear();
+        return forward_all(c, text, audio, kp, logits, PH_ALL);
+    }
+    // graph mode: stage what changes per call (inputs, rng counters) into plan-owned memory, replay the body, finish eagerly
+    const float* t_in = nullptr;
+    const float* a_in = nullptr;
+    if (md->mod[1].enabled) {
+        M2F_CUDA(cudaMemcpyAsync(c.f32(p->text_in), text, (size_t)p->M * md->mod[1].D * 4, cudaMemcpyDeviceToDevice, user));
+        t_in = c.f32(p->text_in);
+    }
+    if (md->mod[0].enabled) {
+        M2F_CUDA(cudaMemcpyAsync(c.f32(p->audio_in), audio, (size_t)p->M * md->mod[0].D * 4, cudaMemcpyDeviceToDevice, user));
+        a_in = c.f32(p->audio_in);
+    }
+    set_rng_kernel<<<1, 1, 0, user>>>(p->rng_dev, seed, step);
+    M2F_LAUNCH_CHECK();
+    m2f_plan::GraphKey key;
+    key.params = params; key.shadow = shadow; key.ws = workspace; key.p_used = p->p_used;
+    if (timeline && (!p->gf.exec || !(p->gf.key == key))) {  // stamps are captured with the graph: slots restart at 0
+        p->tl_labels.clear();
+        p->gb.reset();
+    }
+    M2F_TRY(run_graphed(p, p->gf, key, user, [&](cudaStream_t cs) {
+        Ctx g = c;
+        g.st = cs;
+        return forward_all(g, t_in, a_in, kp, nullptr, PH_BODY);
+    }));
+    return forward_all(c, t_in, a_in, kp, logits, PH_TAIL);
 }
 
 extern "C" int m2f_plan_loss(m2f_plan_t* p, void* workspace, const float* logits, const int64_t* target, const float* class_w, float eps,
@@ -1127,13 +1273,47 @@ extern "C" int m2f_plan_backward_bucketed(m2f_plan_t* p, const float* params, co
     M2F_REQUIRE((reinterpret_cast<uintptr_t>(grads) % 16) == 0, M2F_ERR_ALIGN, "plan_backward: grads must be 16-byte aligned");
     M2F_TRY(bind(p, shadow, workspace));
     M2F_TRY(p->ensure_streams());
-    Ctx c{p, params, grads, reinterpret_cast<uint8_t*>(const_cast<void*>(shadow)), reinterpret_cast<uint8_t*>(workspace),
-          reinterpret_cast<cudaStream_t>(stream), p->m->cfg.planes};
+    cudaStream_t ust = reinterpret_cast<cudaStream_t>(stream);
+    Ctx c{p, params, grads, reinterpret_cast<uint8_t*>(const_cast<void*>(shadow)), reinterpret_cast<uint8_t*>(workspace), ust,
+          p->m->cfg.planes};
     c.bucket_floats = bucket_floats > 0 ? bucket_floats : 1;
     c.cb = cb;
     c.cb_user = user;
     c.hi = p->m->off_1d;
-    return backward_all(c, c.ws + p->key_pad.off, dlogits);
+    const uint8_t* kp = c.ws + p->key_pad.off;
+    int rc;
+    if (!p->use_graph || cb) {  // the bucket callbacks launch the caller's collectives between our kernels: not capturable
+        if (p->use_graph) m2f_set_rng_source(reinterpret_cast<const uint64_t*>(p->rng_dev));  // the forward ran from a graph
+        rc = backward_all(c, kp, dlogits, PH_ALL);
+        m2f_set_rng_source(nullptr);
+    } else {
+        M2F_TRY(backward_all(c, kp, dlogits, PH_HEAD));
+        m2f_plan::GraphKey key;
+        key.params = params; key.shadow = shadow; key.ws = workspace; key.grads = grads; key.p_used = p->p_used;
+        rc = run_graphed(p, p->gb, key, ust, [&](cudaStream_t cs) {
+            Ctx g = c;
+            g.st = cs;
+            int r = backward_all(g, kp, nullptr, PH_BODY);
+            if (r == M2F_OK) g.stamp("end");
+            return r;
+        });
+    }
+    if (p->tl_on && rc == M2F_OK) {
+        if (!p->use_graph || cb) c.stamp("end");
+        const char* n = std::getenv("M2F_TIMELINE_STEP");
+        if (++p->tl_calls == (n ? std::atoll(n) : 5)) {
+            M2F_CUDA(cudaDeviceSynchronize());
+            std::vector<unsigned long long> t(p->tl_labels.size());
+            M2F_CUDA(cudaMemcpy(t.data(), p->tl_dev, t.size() * sizeof(unsigned long long), cudaMemcpyDeviceToHost));
+            if (FILE* f = std::fopen(std::getenv("M2F_TIMELINE"), "w")) {
+                for (size_t i = 0; i < t.size(); ++i)
+                    std::fprintf(f, "%zu\t%d\t%.3f\t%s\n", i, p->tl_labels[i].second, ((double)t[i] - (double)t[0]) * 1e-3,
+                                 p->tl_labels[i].first.c_str());
+                std::fclose(f);
+            }
+        }
+    }
+    return rc;
 }
 
 extern "C" int m2f_plan_backward(m2f_plan_t* p, const float* params, const void* shadow, void* workspace, const float* dlogits,
