@@ -4,6 +4,7 @@
 #include <atomic>
 #include <stdio.h>
 
+#include <cstdlib>
 #include "common.cuh"
 
 namespace m2f {
@@ -15,6 +16,10 @@ void note_launch() { g_launches.fetch_add(1, std::memory_order_relaxed); }
 void note_launches(long long n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
 static thread_local const unsigned long long* tl_rng_source = nullptr;
 const unsigned long long* rng_source() { return tl_rng_source; }
+bool pdl_enabled() {
+    static const bool on = [] { const char* e = std::getenv("M2F_PDL"); return !(e && e[0] == '0'); }();
+    return on;
+}
 
 void set_error(const char* fmt, ...) {
     va_list ap;

@@ -61,6 +61,8 @@ __device__ __forceinline__ void softmax_rows(float (&s)[SP / 8][4], uint64_t kv,
 template <int HD, int SP>
 __global__ void __launch_bounds__(SP * 2)
 attn_fwd_mma_kernel(View q, View k, View v, const uint8_t* __restrict__ key_pad, int S, int H, float scale, Drop drop, OutView o) {
+    pdl_wait();
+    pdl_trigger();
     drop = drop_resolve(drop);
     extern __shared__ __align__(16) uint8_t smraw[];
     constexpr int LDS = HD + 8;
@@ -108,6 +110,8 @@ template <int HD, int SP>
 __global__ void __launch_bounds__(SP * 2)
 attn_bwd_mma_kernel(View q, View k, View v, View d_o, const uint8_t* __restrict__ key_pad, int S, int H, float scale, Drop drop,
                     OutView dq, OutView dk, OutView dv, float* dbq, float* dbk, float* dbv) {
+    pdl_wait();
+    pdl_trigger();
     drop = drop_resolve(drop);
     extern __shared__ __align__(16) uint8_t smraw[];
     constexpr int LDS = HD + 8, LDP = SP + 8;
@@ -202,7 +206,7 @@ static int launch_fwd(const View& q, const View& k, const View& v, const uint8_t
         M2F_CUDA(cudaFuncSetAttribute(attn_fwd_mma_kernel<HD, SP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         set = smem;
     }
-    attn_fwd_mma_kernel<HD, SP><<<(unsigned)BH, SP * 2, smem, st>>>(q, k, v, pad, S, H, scale, drop, o);
+    M2F_CUDA(launch_chain(attn_fwd_mma_kernel<HD, SP>, dim3((unsigned)BH), dim3(SP * 2), smem, st, 1, q, k, v, pad, S, H, scale, drop, o));
     M2F_LAUNCH_CHECK();
     return M2F_OK;
 }
@@ -216,7 +220,8 @@ static int launch_bwd(const View& q, const View& k, const View& v, const View& d
         M2F_CUDA(cudaFuncSetAttribute(attn_bwd_mma_kernel<HD, SP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         set = smem;
     }
-    attn_bwd_mma_kernel<HD, SP><<<(unsigned)BH, SP * 2, smem, st>>>(q, k, v, d_o, pad, S, H, scale, drop, dq, dk, dv, dbq, dbk, dbv);
+    M2F_CUDA(launch_chain(attn_bwd_mma_kernel<HD, SP>, dim3((unsigned)BH), dim3(SP * 2), smem, st, 1, q, k, v, d_o, pad, S, H, scale, drop, dq, dk,
+                          dv, dbq, dbk, dbv));
     M2F_LAUNCH_CHECK();
     return M2F_OK;
 }

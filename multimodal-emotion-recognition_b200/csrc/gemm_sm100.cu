@@ -33,19 +33,28 @@ __device__ __forceinline__ unsigned long long gtimer() {
         if (p.trace) p.trace[(size_t)(blockIdx.y * gridDim.x + blockIdx.x) * 8 + (slot)] = gtimer();             \
     } while (0)
 
-template <int BLOCK_N>
+// CTA2: the CTA is half of a cta_group::2 pair -- the pair computes a 256 x BLOCK_N tile, this CTA owns 128 rows of it
+// and stages only BLOCK_N / 2 rows of B (twice the flops per byte an SM ingests from L2).
+template <int BLOCK_N, bool CTA2>
 struct GemmCfg {
+    static constexpr int B_ROWS = CTA2 ? BLOCK_N / 2 : BLOCK_N;
     static constexpr int A_BYTES = BLOCK_M * BLOCK_K * 2;
-    static constexpr int B_BYTES = BLOCK_N * BLOCK_K * 2;
+    static constexpr int B_BYTES = B_ROWS * BLOCK_K * 2;
     static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
-    // 96 KB of operand ring per CTA, so that TWO CTAs are co-resident per SM: one CTA's epilogue overlaps the other's
-    // prologue / main loop (TMEM: 2 x BLOCK_N <= 512 columns)
-    static constexpr int STAGES = (96 * 1024) / STAGE_BYTES;
+    // Single CTAs: 96 KB of operand ring, so that TWO CTAs are co-resident per SM and one's epilogue overlaps the other's
+    // prologue / main loop (TMEM: 2 x BLOCK_N <= 512 columns); 4 epilogue warps each.
+    // Pairs: one CTA per SM with a 192 KB ring (enough bytes in flight to cover the L2 latency at the rate the
+    // 256-row MMA consumes them) and 8 epilogue warps -- the epilogue of a 128 x 256 tile is instruction-latency bound,
+    // two warps per TMEM lane group halve it.
+    static constexpr int CTAS_PER_SM = CTA2 ? 1 : 2;
+    static constexpr int EPI_WARPS = CTA2 ? 8 : 4;
+    static constexpr int THREADS = 64 + 32 * EPI_WARPS;
+    static constexpr int STAGES = ((CTA2 ? 192 : 96) * 1024) / STAGE_BYTES;
     static constexpr int BAR_BYTES = (2 * STAGES + 1) * 8 + 16;
     static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + BAR_BYTES + 1024;  // + alignment slack
     static constexpr int TMEM_COLS = BLOCK_N < 32 ? 32 : BLOCK_N;
     static_assert(STAGES >= 2, "pipeline too shallow");
-    static_assert(4 * EPI_STG_FLOATS * 4 <= STAGES * STAGE_BYTES, "epilogue staging must fit in the operand ring");
+    static_assert(EPI_WARPS * EPI_STG_FLOATS * 4 <= STAGES * STAGE_BYTES, "epilogue staging must fit in the operand ring");
 };
 
 __device__ __forceinline__ uint2 pack_bf16x4(const float v[4]) {
@@ -88,7 +97,8 @@ __device__ __forceinline__ void sts128(uint32_t addr, uint32_t a, uint32_t b, ui
 // [32 rows][EPI_STG_LD floats]; lane l handles columns 4*(l%8)..+3 of rows it*4 + l/8, it = 0..7, so every global
 // access of the warp covers 4 full 128-byte rows.  Fast path in phases (all shared loads, all global loads, math,
 // all stores) so that the memory latencies of the 8 row groups overlap; the rare ragged path goes element by element.
-__device__ __forceinline__ void epilogue_chunk(const EpiRegs& e, const Drop& drop, uint32_t stg, int lane, int64_t m0, int n0) {
+__device__ __forceinline__ void epilogue_chunk(const EpiRegs& e, const Drop& drop, uint32_t stg, int lane, int64_t m0, int n0,
+                                               const float4 b, const uint2 (&g)[8], const float4 (&q)[8]) {
     const int cg = (lane & 7) * 4;
     const int n = n0 + cg;
     const int r0 = lane >> 3;
@@ -101,8 +111,7 @@ __device__ __forceinline__ void epilogue_chunk(const EpiRegs& e, const Drop& dro
         bool ok[8];
 #pragma unroll
         for (int it = 0; it < 8; ++it) ok[it] = (m0 + it * 4 + r0) < e.M;
-        if (e.bias) {
-            const float4 b = *reinterpret_cast<const float4*>(e.bias + n);
+        if (e.bias) {  // b: this lane's four bias values, loaded by the caller ahead of the accumulator read
 #pragma unroll
             for (int it = 0; it < 8; ++it) { v[it].x += b.x; v[it].y += b.y; v[it].z += b.z; v[it].w += b.w; }
         }
@@ -111,11 +120,7 @@ __device__ __forceinline__ void epilogue_chunk(const EpiRegs& e, const Drop& dro
             v[it].x = fmaxf(v[it].x, e.floor_); v[it].y = fmaxf(v[it].y, e.floor_);
             v[it].z = fmaxf(v[it].z, e.floor_); v[it].w = fmaxf(v[it].w, e.floor_);
         }
-        if (e.gate) {
-            uint2 g[8];
-#pragma unroll
-            for (int it = 0; it < 8; ++it)
-                g[it] = ok[it] ? *reinterpret_cast<const uint2*>(e.gate + (m0 + it * 4 + r0) * e.gate_ld + n) : make_uint2(0u, 0u);
+        if (e.gate) {  // g: prefetched by the caller
 #pragma unroll
             for (int it = 0; it < 8; ++it) {
                 const __nv_bfloat162 g0 = *reinterpret_cast<const __nv_bfloat162*>(&g[it].x);
@@ -134,11 +139,7 @@ __device__ __forceinline__ void epilogue_chunk(const EpiRegs& e, const Drop& dro
                 v[it].x *= dm[0]; v[it].y *= dm[1]; v[it].z *= dm[2]; v[it].w *= dm[3];
             }
         }
-        if (e.resid) {
-            float4 q[8];
-#pragma unroll
-            for (int it = 0; it < 8; ++it)
-                q[it] = ok[it] ? *reinterpret_cast<const float4*>(e.resid + (m0 + it * 4 + r0) * e.resid_ld + n) : make_float4(0.f, 0.f, 0.f, 0.f);
+        if (e.resid) {  // q: prefetched by the caller
 #pragma unroll
             for (int it = 0; it < 8; ++it) { v[it].x += q[it].x; v[it].y += q[it].y; v[it].z += q[it].z; v[it].w += q[it].w; }
         }
@@ -155,9 +156,11 @@ __device__ __forceinline__ void epilogue_chunk(const EpiRegs& e, const Drop& dro
             for (int it = 0; it < 8; ++it)
                 if (ok[it]) *reinterpret_cast<float4*>(e.out_f32 + (m0 + it * 4 + r0) * e.out_f32_ld + n) = v[it];
         }
+        if (e.colsum) {
 #pragma unroll
-        for (int it = 0; it < 8; ++it)
-            if (ok[it]) { cs0 += v[it].x; cs1 += v[it].y; cs2 += v[it].z; cs3 += v[it].w; }
+            for (int it = 0; it < 8; ++it)
+                if (ok[it]) { cs0 += v[it].x; cs1 += v[it].y; cs2 += v[it].z; cs3 += v[it].w; }
+        }
         if (e.out_pl) {  // hi / mid / lo bf16 planes, registers only
             for (int pl = 0; pl < e.out_pl_n; ++pl) {
                 __nv_bfloat16* base = e.out_pl + pl * e.out_pl_stride + n;
@@ -166,8 +169,10 @@ __device__ __forceinline__ void epilogue_chunk(const EpiRegs& e, const Drop& dro
                     float t[4] = {v[it].x, v[it].y, v[it].z, v[it].w};
                     const uint2 h = pack_bf16x4(t);
                     if (ok[it]) *reinterpret_cast<uint2*>(base + (m0 + it * 4 + r0) * e.out_pl_ld) = h;
-                    unpack_sub(h, t);  // residual feeds the next plane
-                    v[it] = make_float4(t[0], t[1], t[2], t[3]);
+                    if (pl + 1 < e.out_pl_n) {
+                        unpack_sub(h, t);  // residual feeds the next plane
+                        v[it] = make_float4(t[0], t[1], t[2], t[3]);
+                    }
                 }
             }
         }
@@ -215,10 +220,10 @@ __device__ __forceinline__ void epilogue_chunk(const EpiRegs& e, const Drop& dro
     }
 }
 
-template <int BLOCK_N, bool A_MN, bool B_MN>
-__global__ void __launch_bounds__(GEMM_THREADS, 2)
+template <int BLOCK_N, bool A_MN, bool B_MN, bool CTA2>
+__global__ void __launch_bounds__(GemmCfg<BLOCK_N, CTA2>::THREADS, GemmCfg<BLOCK_N, CTA2>::CTAS_PER_SM)
 gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b, const GemmParams p) {
-    using Cfg = GemmCfg<BLOCK_N>;
+    using Cfg = GemmCfg<BLOCK_N, CTA2>;
     constexpr int STAGES = Cfg::STAGES;
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -232,6 +237,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ C
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
     const int m_blk = blockIdx.x, n_blk = blockIdx.y;
+    const uint32_t cta_rank = CTA2 ? ptx::cluster_ctarank() : 0u;  // (2,1,1) cluster: rank = blockIdx.x & 1
     if (threadIdx.x == 0) M2F_TRACE(0);
 
     if (warp == 0 && lane == 0) {
@@ -246,11 +252,17 @@ gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ C
         ptx::mbar_init(tmem_full_bar, 1);
         ptx::fence_barrier_init();
     }
-    if (warp == 2) ptx::tmem_alloc(tmem_slot, Cfg::TMEM_COLS);
+    if (warp == 2) {
+        if constexpr (CTA2) ptx::tmem_alloc_2cta(tmem_slot, Cfg::TMEM_COLS);
+        else ptx::tmem_alloc(tmem_slot, Cfg::TMEM_COLS);
+    }
     ptx::tcgen05_fence_before();
-    __syncthreads();
+    if constexpr (CTA2) ptx::cluster_sync();  // the peer's barriers must exist before anything is signalled across
+    else __syncthreads();
     ptx::tcgen05_fence_after();
     const uint32_t tmem_base = *tmem_slot;
+    pdl_wait();     // everything above overlapped the previous kernel's tail; operands / epilogue inputs are final from here
+    pdl_trigger();
     if (threadIdx.x == 0) M2F_TRACE(1);
 
     if (warp == 0) {
@@ -264,26 +276,46 @@ gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ C
                         const int stage = it % STAGES;
                         const uint32_t phase = (it / STAGES) & 1;
                         ptx::mbar_wait(&empty_bar[stage], phase ^ 1);
-                        ptx::mbar_expect_tx(&full_bar[stage], Cfg::STAGE_BYTES);
                         const int ka = p.seg_a_k0[sg] + kb * BLOCK_K;
                         const int kbb = p.seg_b_k0[sg] + kb * BLOCK_K;
                         uint8_t* sa = smem_a + stage * Cfg::A_BYTES;
                         uint8_t* sb = smem_b + stage * Cfg::B_BYTES;
-                        if (!A_MN) {
-                            ptx::tma_load_3d(sa, &tma_a, &full_bar[stage], ka, m_blk * BLOCK_M, pa);
-                        } else {
+                        const int nb0 = n_blk * BLOCK_N + (int)cta_rank * Cfg::B_ROWS;  // this CTA's share of the B tile
+                        if constexpr (CTA2) {
+                            // both CTAs' bytes are credited to the leader's barrier: it alone is armed, with the pair's total
+                            if (cta_rank == 0) ptx::mbar_expect_tx(&full_bar[stage], 2 * Cfg::STAGE_BYTES);
+                            const uint32_t fb = ptx::mapa(ptx::smem_u32(&full_bar[stage]), 0);
+                            if (!A_MN) {
+                                ptx::tma_load_3d_2cta(sa, &tma_a, fb, ka, m_blk * BLOCK_M, pa);
+                            } else {
 #pragma unroll
-                            for (int j = 0; j < BLOCK_M / 64; ++j)
-                                ptx::tma_load_3d(sa + j * (64 * BLOCK_K * 2), &tma_a, &full_bar[stage],
-                                                 m_blk * BLOCK_M + j * 64, ka, pa);
-                        }
-                        if (!B_MN) {
-                            ptx::tma_load_3d(sb, &tma_b, &full_bar[stage], kbb, n_blk * BLOCK_N, pb);
-                        } else {
+                                for (int j = 0; j < BLOCK_M / 64; ++j)
+                                    ptx::tma_load_3d_2cta(sa + j * (64 * BLOCK_K * 2), &tma_a, fb, m_blk * BLOCK_M + j * 64, ka, pa);
+                            }
+                            if (!B_MN) {
+                                ptx::tma_load_3d_2cta(sb, &tma_b, fb, kbb, nb0, pb);
+                            } else {
 #pragma unroll
-                            for (int j = 0; j < BLOCK_N / 64; ++j)
-                                ptx::tma_load_3d(sb + j * (64 * BLOCK_K * 2), &tma_b, &full_bar[stage],
-                                                 n_blk * BLOCK_N + j * 64, kbb, pb);
+                                for (int j = 0; j < Cfg::B_ROWS / 64; ++j)
+                                    ptx::tma_load_3d_2cta(sb + j * (64 * BLOCK_K * 2), &tma_b, fb, nb0 + j * 64, kbb, pb);
+                            }
+                        } else {
+                            ptx::mbar_expect_tx(&full_bar[stage], Cfg::STAGE_BYTES);
+                            if (!A_MN) {
+                                ptx::tma_load_3d(sa, &tma_a, &full_bar[stage], ka, m_blk * BLOCK_M, pa);
+                            } else {
+#pragma unroll
+                                for (int j = 0; j < BLOCK_M / 64; ++j)
+                                    ptx::tma_load_3d(sa + j * (64 * BLOCK_K * 2), &tma_a, &full_bar[stage],
+                                                     m_blk * BLOCK_M + j * 64, ka, pa);
+                            }
+                            if (!B_MN) {
+                                ptx::tma_load_3d(sb, &tma_b, &full_bar[stage], kbb, nb0, pb);
+                            } else {
+#pragma unroll
+                                for (int j = 0; j < BLOCK_N / 64; ++j)
+                                    ptx::tma_load_3d(sb + j * (64 * BLOCK_K * 2), &tma_b, &full_bar[stage], nb0 + j * 64, kbb, pb);
+                            }
                         }
                     }
                 }
@@ -292,8 +324,8 @@ gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ C
         __syncwarp();
     } else if (warp == 1) {
         // ------------------------------------------------------------------ MMA issuer
-        if (ptx::elect_one()) {
-            constexpr uint32_t idesc = ptx::instr_desc_bf16(BLOCK_M, BLOCK_N, A_MN, B_MN);
+        if (cta_rank == 0 && ptx::elect_one()) {  // in a pair only the leader issues; its MMAs read both CTAs' smem
+            constexpr uint32_t idesc = ptx::instr_desc_bf16(CTA2 ? 2 * BLOCK_M : BLOCK_M, BLOCK_N, A_MN, B_MN);
             // K-major SW128: 8-row groups 1024 B apart (SBO), one atom along K (LBO unused);
             //   advancing K by 16 elements = +32 B inside the swizzle atom.
             // MN-major SW128: 64-element MN atoms BLOCK_K*128 B apart (LBO), 8-k-row groups 1024 B apart (SBO);
@@ -312,11 +344,15 @@ gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ C
                 for (int k = 0; k < BLOCK_K / UMMA_K; ++k) {
                     const uint64_t ad = ptx::smem_desc_sw128(sa + k * A_KSTEP, A_LBO, 1024);
                     const uint64_t bd = ptx::smem_desc_sw128(sb + k * B_KSTEP, B_LBO, 1024);
-                    ptx::umma_bf16(tmem_base, ad, bd, idesc, (it > 0 || k > 0) ? 1u : 0u);
+                    if constexpr (CTA2) ptx::umma_bf16_2cta(tmem_base, ad, bd, idesc, (it > 0 || k > 0) ? 1u : 0u);
+                    else ptx::umma_bf16(tmem_base, ad, bd, idesc, (it > 0 || k > 0) ? 1u : 0u);
                 }
-                ptx::umma_commit(&empty_bar[stage]);  // frees the smem slot once these MMAs retire
+                // frees the smem slot (in both CTAs of a pair) once these MMAs retire
+                if constexpr (CTA2) ptx::umma_commit_2cta(&empty_bar[stage], 3);
+                else ptx::umma_commit(&empty_bar[stage]);
             }
-            ptx::umma_commit(tmem_full_bar);
+            if constexpr (CTA2) ptx::umma_commit_2cta(tmem_full_bar, 3);
+            else ptx::umma_commit(tmem_full_bar);
             M2F_TRACE(3);
         }
         __syncwarp();
@@ -334,15 +370,37 @@ gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ C
         if (threadIdx.x == 64) M2F_TRACE(4);
         ptx::tcgen05_fence_after();
         const int lg = warp & 3;  // TMEM lane group this warp may access
-        const uint32_t stg = ptx::smem_u32(smem) + (uint32_t)(lg * EPI_STG_FLOATS * 4);
+        const int ew = warp - 2;  // epilogue warps of the same lane group interleave the 32-column chunks
+        const uint32_t stg = ptx::smem_u32(smem) + (uint32_t)(ew * EPI_STG_FLOATS * 4);
         const int64_t m0 = (int64_t)m_blk * BLOCK_M + lg * 32;
         if (m0 < p.M) {
 #pragma unroll 1
-            for (int c = 0; c < BLOCK_N / 32; ++c) {
+            for (int c = ew >> 2; c < BLOCK_N / 32; c += Cfg::EPI_WARPS / 4) {
                 const int n0 = n_blk * BLOCK_N + c * 32;
                 if (n0 >= p.N) break;  // warp-uniform
                 uint32_t r[32];
                 long long c0 = 0, c1 = 0, c2 = 0;
+                float4 bias4 = make_float4(0.f, 0.f, 0.f, 0.f);
+                uint2 gate8[8];
+                float4 res8[8];
+                {   // issued before the TMEM read and the staging round trip so that its latency hides behind them
+                    const int nb = n0 + (lane & 7) * 4;
+                    const bool vecp = e.vec4 && nb + 4 <= e.N;
+                    if (e.bias && vecp) bias4 = *reinterpret_cast<const float4*>(e.bias + nb);
+                    const int rr = lane >> 3;
+                    if (e.gate && vecp) {
+#pragma unroll
+                        for (int it = 0; it < 8; ++it)
+                            gate8[it] = (m0 + it * 4 + rr) < e.M ? *reinterpret_cast<const uint2*>(e.gate + (m0 + it * 4 + rr) * e.gate_ld + nb)
+                                                                 : make_uint2(0u, 0u);
+                    }
+                    if (e.resid && vecp) {
+#pragma unroll
+                        for (int it = 0; it < 8; ++it)
+                            res8[it] = (m0 + it * 4 + rr) < e.M ? *reinterpret_cast<const float4*>(e.resid + (m0 + it * 4 + rr) * e.resid_ld + nb)
+                                                                : make_float4(0.f, 0.f, 0.f, 0.f);
+                    }
+                }
                 if (p.trace) c0 = clock64();
                 ptx::tmem_ld_32x32(tmem_base + ((uint32_t)(lg * 32) << 16) + (uint32_t)(c * 32), r);
                 ptx::tmem_ld_wait();
@@ -353,9 +411,9 @@ gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ C
                     sts128(stg + (uint32_t)((lane * EPI_STG_LD + j * 4) * 4), r[4 * j], r[4 * j + 1], r[4 * j + 2], r[4 * j + 3]);
                 __syncwarp();
                 if (p.trace) c2 = clock64();
-                epilogue_chunk(e, drop, stg, lane, m0, n0);
-                if (p.trace && threadIdx.x == 64 && c < 2) {
-                    unsigned long long* t2 = p.trace + (size_t)4096 * 8 + (size_t)(blockIdx.y * gridDim.x + blockIdx.x) * 8 + c * 4;
+                epilogue_chunk(e, drop, stg, lane, m0, n0, bias4, gate8, res8);
+                if (p.trace && threadIdx.x == 64 && c < 2 * (Cfg::EPI_WARPS / 4)) {
+                    unsigned long long* t2 = p.trace + (size_t)4096 * 8 + (size_t)(blockIdx.y * gridDim.x + blockIdx.x) * 8 + (c / (Cfg::EPI_WARPS / 4)) * 4;
                     t2[0] = c1 - c0; t2[1] = c2 - c1; t2[2] = clock64() - c2; t2[3] = c0;
                 }
             }
@@ -363,11 +421,13 @@ gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ C
         ptx::tcgen05_fence_before();
         if (threadIdx.x == 64) M2F_TRACE(5);
     }
-    __syncthreads();
+    if constexpr (CTA2) ptx::cluster_sync();  // neither CTA may release its TMEM / exit while the pair is in flight
+    else __syncthreads();
     if (threadIdx.x == 0) M2F_TRACE(6);
     if (warp == 2) {
         ptx::tcgen05_fence_after();
-        ptx::tmem_dealloc(tmem_base, Cfg::TMEM_COLS);
+        if constexpr (CTA2) ptx::tmem_dealloc_2cta(tmem_base, Cfg::TMEM_COLS);
+        else ptx::tmem_dealloc(tmem_base, Cfg::TMEM_COLS);
     }
 }
 
@@ -414,25 +474,38 @@ int make_planes_tmap(CUtensorMap* map, const m2f_planes_t* t, int box_rows) {
     return M2F_OK;
 }
 
-template <int BLOCK_N, bool A_MN, bool B_MN>
+template <int BLOCK_N, bool A_MN, bool B_MN, bool CTA2>
 static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p, cudaStream_t stream) {
-    using Cfg = GemmCfg<BLOCK_N>;
-    auto kern = gemm_kernel<BLOCK_N, A_MN, B_MN>;
+    using Cfg = GemmCfg<BLOCK_N, CTA2>;
+    auto kern = gemm_kernel<BLOCK_N, A_MN, B_MN, CTA2>;
     static bool attr_set = false;  // per instantiation
     if (!attr_set) {
         M2F_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES));
         attr_set = true;
     }
     dim3 grid(ceil_div(p.M, BLOCK_M), ceil_div(p.N, BLOCK_N));
-    kern<<<grid, GEMM_THREADS, Cfg::SMEM_BYTES, stream>>>(ta, tb, p);
+    if constexpr (CTA2) {
+        grid.x = (grid.x + 1) & ~1u;  // whole pairs; a row tile past M loads zeros and stores nothing
+        M2F_CUDA(launch_chain(kern, grid, dim3(Cfg::THREADS), Cfg::SMEM_BYTES, stream, 2, ta, tb, p));
+    } else {
+        M2F_CUDA(launch_chain(kern, grid, dim3(Cfg::THREADS), Cfg::SMEM_BYTES, stream, 1, ta, tb, p));
+    }
     M2F_LAUNCH_CHECK();
     return M2F_OK;
 }
+
+// Tile code: BLOCK_N, plus GEMM_TILE_CTA2 when the tile is computed by a CTA pair (256 x BLOCK_N per pair).
+int gemm_b_box_rows(int tile) { return (tile & GEMM_TILE_CTA2) ? (tile & 0xfff) / 2 : (tile & 0xfff); }
 
 int gemm_block_n(int64_t M, int64_t N) {
     // one 128 x BLOCK_N tile per CTA: prefer the widest tile that still yields >= 148 CTAs
     const int64_t mt = (M + BLOCK_M - 1) / BLOCK_M;
     static const int forced = [] { const char* e = std::getenv("M2F_GEMM_BN"); return e ? std::atoi(e) : 0; }();  // tuning aid
+    static const int pairs = [] { const char* e = std::getenv("M2F_GEMM_CTA2"); return e ? std::atoi(e) : 0; }();
+    if (pairs && N > 64) {
+        const int bn = (forced == 128 || forced == 256) ? forced : 256;
+        return ((N <= 128) ? 128 : bn) | GEMM_TILE_CTA2;
+    }
     if (forced == 64 || forced == 128 || forced == 256) return (N <= 64) ? 64 : ((N <= 128 && forced == 256) ? 128 : forced);
     if (N > 128 && mt * ((N + 255) / 256) >= 148) return 256;
     if (N > 64 && mt * ((N + 127) / 128) >= 120) return 128;
@@ -510,20 +583,24 @@ int gemm_fill_params(GemmParams& p, const m2f_planes_t* A, int a_mn, const m2f_p
     return M2F_OK;
 }
 
-int gemm_launch(const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p, int block_n, int a_mn, int b_mn,
+int gemm_launch(const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p, int tile, int a_mn, int b_mn,
                 cudaStream_t stream) {
-#define M2F_GEMM_CASE(BN)                                                              \
-    if (block_n == BN) {                                                               \
-        if (!a_mn && !b_mn) return launch_gemm<BN, false, false>(ta, tb, p, stream);   \
-        if (!a_mn && b_mn) return launch_gemm<BN, false, true>(ta, tb, p, stream);     \
-        if (a_mn && b_mn) return launch_gemm<BN, true, true>(ta, tb, p, stream);       \
-        return launch_gemm<BN, true, false>(ta, tb, p, stream);                        \
+    const int block_n = tile & 0xfff;
+    const bool cta2 = (tile & GEMM_TILE_CTA2) != 0;
+#define M2F_GEMM_CASE(BN, C2)                                                              \
+    if (block_n == BN && cta2 == C2) {                                                     \
+        if (!a_mn && !b_mn) return launch_gemm<BN, false, false, C2>(ta, tb, p, stream);   \
+        if (!a_mn && b_mn) return launch_gemm<BN, false, true, C2>(ta, tb, p, stream);     \
+        if (a_mn && b_mn) return launch_gemm<BN, true, true, C2>(ta, tb, p, stream);       \
+        return launch_gemm<BN, true, false, C2>(ta, tb, p, stream);                        \
     }
-    M2F_GEMM_CASE(64)
-    M2F_GEMM_CASE(128)
-    M2F_GEMM_CASE(256)
+    M2F_GEMM_CASE(64, false)
+    M2F_GEMM_CASE(128, false)
+    M2F_GEMM_CASE(256, false)
+    M2F_GEMM_CASE(128, true)
+    M2F_GEMM_CASE(256, true)
 #undef M2F_GEMM_CASE
-    set_error("gemm: unsupported BLOCK_N %d", block_n);
+    set_error("gemm: unsupported tile code %d", tile);
     return M2F_ERR_UNSUPPORTED;
 }
 
@@ -542,6 +619,6 @@ extern "C" int m2f_gemm(const m2f_planes_t* A, int a_mn_major, const m2f_planes_
     const int bn = gemm_block_n(M, N);
     CUtensorMap ta, tb;
     M2F_TRY(make_planes_tmap(&ta, A, a_mn_major ? BLOCK_K : BLOCK_M));
-    M2F_TRY(make_planes_tmap(&tb, B, b_mn_major ? BLOCK_K : bn));
+    M2F_TRY(make_planes_tmap(&tb, B, b_mn_major ? BLOCK_K : gemm_b_box_rows(bn)));
     return gemm_launch(ta, tb, p, bn, a_mn_major, b_mn_major, reinterpret_cast<cudaStream_t>(stream));
 }

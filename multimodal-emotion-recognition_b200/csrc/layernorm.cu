@@ -19,6 +19,8 @@ __global__ void __launch_bounds__(LN_THREADS)
 ln_fwd_kernel(const float* __restrict__ x, int64_t x_ld, const float* __restrict__ gamma, const float* __restrict__ beta,
               const float* __restrict__ skip, int64_t skip_ld, int64_t M, int D, float* __restrict__ y, int64_t y_ld,
               __nv_bfloat16* __restrict__ ypl, int64_t ypl_ld, int64_t ypl_stride, int P, Drop drop, float* __restrict__ stats) {
+    pdl_wait();
+    pdl_trigger();
     drop = drop_resolve(drop);
     const int lane = threadIdx.x & 31;
     const int64_t warp0 = (int64_t)blockIdx.x * LN_WARPS + (threadIdx.x >> 5);
@@ -88,6 +90,8 @@ ln_bwd_kernel(const float* __restrict__ g, int64_t g_ld, const float* __restrict
               const float* __restrict__ gamma, const float* __restrict__ stats, int64_t M, int D, float* __restrict__ dx,
               int64_t dx_ld, __nv_bfloat16* __restrict__ dxpl, int64_t dxpl_ld, int64_t dxpl_stride, int P, Drop drop,
               float* __restrict__ dgamma, float* __restrict__ dbeta, float* __restrict__ dbias) {
+    pdl_wait();
+    pdl_trigger();
     drop = drop_resolve(drop);
     __shared__ float rowc[LNB_ROWS][4];  // mean, rstd, c1, c2
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -230,8 +234,8 @@ extern "C" int m2f_ln_fwd(const float* x, int64_t x_ld, const float* gamma, cons
     M2F_REQUIRE(y_f32 || ypl, M2F_ERR_ARG, "ln_fwd: no output given");
     const Drop drop = drop_make(drop_p, seed, step, site);
     auto st = reinterpret_cast<cudaStream_t>(stream);
-    M2F_LN_DISPATCH(D, (ln_fwd_kernel<NCH><<<ln_grid(M, 1), LN_THREADS, 0, st>>>(x, x_ld, gamma, beta, skip, skip_ld, M, (int)D, y_f32, y_ld,
-                                                                                  ypl, ypl_ld, ypl_stride, P, drop, stats)));
+    M2F_LN_DISPATCH(D, M2F_CUDA(launch_chain(ln_fwd_kernel<NCH>, dim3(ln_grid(M, 1)), dim3(LN_THREADS), 0, st, 1, x, x_ld, gamma, beta, skip,
+                                             skip_ld, M, (int)D, y_f32, y_ld, ypl, ypl_ld, ypl_stride, P, drop, stats)));
     M2F_LAUNCH_CHECK();
     return M2F_OK;
 }
@@ -261,8 +265,8 @@ extern "C" int m2f_ln_bwd(const float* g, int64_t g_ld, const float* x, int64_t 
     M2F_REQUIRE((!dgamma || (reinterpret_cast<uintptr_t>(dgamma) % 16) == 0) && (!dbeta || (reinterpret_cast<uintptr_t>(dbeta) % 16) == 0) &&
                     (!dbias || (reinterpret_cast<uintptr_t>(dbias) % 16) == 0), M2F_ERR_ALIGN, "ln_bwd: dgamma / dbeta / dbias must be 16-byte aligned");
     const int lnb_grid = (int)std::min<int64_t>((M + LNB_ROWS - 1) / LNB_ROWS, 148 * 4);
-    M2F_LN_DISPATCH(D, (ln_bwd_kernel<NCH><<<lnb_grid, LNB_THREADS, 0, st>>>(g, g_ld, x, x_ld, gamma, stats, M, (int)D, dx_f32, dx_ld, dpl,
-                                                                                  dpl_ld, dpl_stride, P, drop, dgamma, dbeta, dbias)));
+    M2F_LN_DISPATCH(D, M2F_CUDA(launch_chain(ln_bwd_kernel<NCH>, dim3(lnb_grid), dim3(LNB_THREADS), 0, st, 1, g, g_ld, x, x_ld, gamma, stats, M,
+                                             (int)D, dx_f32, dx_ld, dpl, dpl_ld, dpl_stride, P, drop, dgamma, dbeta, dbias)));
     M2F_LAUNCH_CHECK();
     return M2F_OK;
 }

@@ -587,7 +587,7 @@ struct Ctx {
         const int bn = gemm_block_n(M, N);
         const CUtensorMap *ta, *tb;
         M2F_TRY(tmap(A, a_mn ? BLOCK_K : BLOCK_M, &ta));
-        M2F_TRY(tmap(B, b_mn ? BLOCK_K : bn, &tb));
+        M2F_TRY(tmap(B, b_mn ? BLOCK_K : gemm_b_box_rows(bn), &tb));
         return gemm_launch(*ta, *tb, gp, bn, a_mn, b_mn, stream());
     }
 };
