@@ -40,7 +40,18 @@ struct GemmParams {
     __nv_bfloat16* out_pl;
     int64_t out_pl_ld, out_pl_stride;
     int out_pl_n;
+    int epi_tma;  // 1: the [M,N]-shaped epilogue operands have tensor maps (EpiMaps) -- TMA epilogue; 0: pointer epilogue
 };
+
+// Tensor maps of the [M,N]-shaped epilogue operands, box = 32 rows x 32 columns (one epilogue warp's chunk):
+// fp32 maps use the 128-byte swizzle (32 x 4 B rows), bf16 maps the 64-byte swizzle.  Unused ones stay zeroed.
+struct EpiMaps {
+    CUtensorMap out_f32;  // 2-D fp32 [M, N]: stored, and loaded first when accumulating
+    CUtensorMap out_pl;   // 3-D bf16 [planes, M, N]
+    CUtensorMap gate;     // 2-D bf16 [M, N]
+    CUtensorMap resid;    // 2-D fp32 [M, N]
+};
+constexpr int EPI2_WARP_BYTES = 20 * 1024;  // per epilogue warp: out f32 4K | out planes 3 x 2K | gate 2K | resid 4K | accumulate 4K
 
 // host helpers (gemm_sm100.cu)
 int make_planes_tmap(CUtensorMap* map, const m2f_planes_t* t, int box_rows);
@@ -49,7 +60,9 @@ int gemm_block_n(int64_t M, int64_t N);   // tile code: BLOCK_N | GEMM_TILE_CTA2
 int gemm_b_box_rows(int tile);            // rows of B one CTA stages per k-block (K-major tensor-map box)
 int gemm_fill_params(GemmParams& p, const m2f_planes_t* A, int a_mn, const m2f_planes_t* B, int b_mn, const m2f_kseg_t* segs,
                      int nsegs, int64_t M, int64_t N, const m2f_epilogue_t* e);
-int gemm_launch(const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p, int tile, int a_mn, int b_mn,
+// decides whether the TMA epilogue applies (alignment of every operand present) and encodes its maps; sets p.epi_tma
+int gemm_make_epi_maps(GemmParams& p, EpiMaps* maps);
+int gemm_launch(const CUtensorMap& ta, const CUtensorMap& tb, const EpiMaps& em, const GemmParams& p, int tile, int a_mn, int b_mn,
                 cudaStream_t stream);
 
 }  // namespace m2f

@@ -14,6 +14,7 @@
 #include <mutex>
 
 #include <cstdlib>
+#include <cstring>
 #include "common.cuh"
 #include "gemm.cuh"
 #include "ptx.cuh"
@@ -50,11 +51,13 @@ struct GemmCfg {
     static constexpr int EPI_WARPS = CTA2 ? 8 : 4;
     static constexpr int THREADS = 64 + 32 * EPI_WARPS;
     static constexpr int STAGES = ((CTA2 ? 192 : 96) * 1024) / STAGE_BYTES;
-    static constexpr int BAR_BYTES = (2 * STAGES + 1) * 8 + 16;
-    static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + BAR_BYTES + 1024;  // + alignment slack
+    static constexpr int BAR_BYTES = (2 * STAGES + 1) * 8 + 16 + 8 * 8;  // ring, accumulator-ready, TMEM slot, 8 epilogue-load barriers
+    static constexpr int BIAS_BYTES = BLOCK_N * 4;  // the tile's bias values, staged while the main loop runs (so not in the ring)
+    static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + BAR_BYTES + BIAS_BYTES + 16 + 1024;  // + alignment slack
     static constexpr int TMEM_COLS = BLOCK_N < 32 ? 32 : BLOCK_N;
     static_assert(STAGES >= 2, "pipeline too shallow");
     static_assert(EPI_WARPS * EPI_STG_FLOATS * 4 <= STAGES * STAGE_BYTES, "epilogue staging must fit in the operand ring");
+    static_assert(EPI_WARPS * EPI2_WARP_BYTES <= STAGES * STAGE_BYTES, "TMA epilogue staging must fit in the operand ring");
 };
 
 __device__ __forceinline__ uint2 pack_bf16x4(const float v[4]) {
@@ -220,9 +223,176 @@ __device__ __forceinline__ void epilogue_chunk(const EpiRegs& e, const Drop& dro
     }
 }
 
+__device__ __forceinline__ float4 lds128u(uint32_t addr) { return lds128(addr); }
+
+// TMA epilogue of one warp.  The warp owns TMEM lanes 32*lg..+31 = 32 output rows; lane t holds row t of each
+// 32-column chunk exactly as tcgen05.ld delivers it, so nothing is transposed: per-element inputs (gate, residual,
+// previous value when accumulating) arrive as TMA tiles in shared memory, results leave as TMA tile stores, and the
+// hardware does the address arithmetic, the coalescing and the clipping at M / N.  Swizzled tiles keep the
+// "lane = row" shared-memory accesses conflict-free: 16-byte chunk j of row t sits at chunk j ^ (t & 7) (128-byte
+// rows, fp32) or j ^ ((t >> 1) & 3) (64-byte rows, bf16).
+template <int BLOCK_N, int EPI_WARPS>
+__device__ __forceinline__ void epilogue_tma(const GemmParams& p, const EpiMaps& em, uint8_t* smem, uint32_t s_bias, uint64_t* epi_bar,
+                                             uint64_t* tmem_full_bar, uint32_t tmem_base, int warp, int lane, int m_blk, int n_blk) {
+    const int lg = warp & 3, ew = warp - 2;
+    const uint32_t s_of = ptx::smem_u32(smem) + (uint32_t)(ew * EPI2_WARP_BYTES);
+    const uint32_t s_pl = s_of + 4096, s_gate = s_of + 10240, s_res = s_of + 12288, s_acc = s_of + 16384;
+    uint64_t* bar = &epi_bar[ew];
+    const int m0 = m_blk * BLOCK_M + lg * 32;
+    const int nt0 = n_blk * BLOCK_N;
+    const bool rows_live = m0 < p.M;
+    const bool has_gate = p.gate != nullptr, has_res = p.resid != nullptr, has_acc = p.accumulate && p.out_f32;
+    const uint32_t in_bytes = (has_gate ? 2048u : 0u) + (has_res ? 4096u : 0u) + (has_acc ? 4096u : 0u);
+    constexpr int CSTEP = EPI_WARPS / 4;
+    const int c_first = ew >> 2;
+    auto issue_loads = [&](int c) {
+        const int n0 = nt0 + c * 32;
+        if (lane == 0 && in_bytes && n0 < p.N) {
+            ptx::mbar_expect_tx(bar, in_bytes);
+            if (has_gate) ptx::tma_load_2d(s_gate, &em.gate, bar, n0, m0);
+            if (has_res) ptx::tma_load_2d(s_res, &em.resid, bar, n0, m0);
+            if (has_acc) ptx::tma_load_2d(s_acc, &em.out_f32, bar, n0, m0);
+        }
+    };
+    // bias of this CTA's columns -> shared (read back as broadcasts); its own region: the operand ring is still live
+    if (p.bias) {
+        for (int i = (warp - 2) * 32 + lane; i < BLOCK_N; i += EPI_WARPS * 32) {
+            const int n = nt0 + i;
+            const float b = n < p.N ? p.bias[n] : 0.f;
+            asm volatile("st.shared.f32 [%0], %1;" ::"r"(s_bias + (uint32_t)i * 4u), "f"(b) : "memory");
+        }
+    }
+    const Drop drop = drop_resolve(p.drop);
+    const float floor_ = p.relu ? 0.f : -INFINITY;
+    ptx::named_bar_sync(1, EPI_WARPS * 32);  // bias visible to every epilogue warp
+    ptx::mbar_wait(tmem_full_bar, 0);
+    ptx::tcgen05_fence_after();
+    if (!rows_live) return;
+    issue_loads(c_first);  // the ring is free from here on: it becomes the staging area
+    uint32_t phase = 0;
+    const int row = m0 + lane;
+    const uint32_t sw128 = (uint32_t)(lane & 7), sw64 = (uint32_t)((lane >> 1) & 3);
+#pragma unroll 1
+    for (int c = c_first; c < BLOCK_N / 32; c += CSTEP) {
+        const int n0 = nt0 + c * 32;
+        if (n0 >= p.N) break;
+        float x[32];
+        {
+            uint32_t r[32];
+            ptx::tmem_ld_32x32(tmem_base + ((uint32_t)(lg * 32) << 16) + (uint32_t)(c * 32), r);
+            ptx::tmem_ld_wait();
+#pragma unroll
+            for (int j = 0; j < 32; ++j) x[j] = __uint_as_float(r[j]);
+        }
+        if (p.bias) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                const float4 b = lds128u(s_bias + (uint32_t)(c * 32 + j * 4) * 4u);
+                x[4 * j] += b.x; x[4 * j + 1] += b.y; x[4 * j + 2] += b.z; x[4 * j + 3] += b.w;
+            }
+        }
+#pragma unroll
+        for (int j = 0; j < 32; ++j) x[j] = fmaxf(x[j], floor_);
+        if (in_bytes) {
+            ptx::mbar_wait(bar, phase);
+            phase ^= 1;
+        }
+        if (has_gate) {
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const float4 g = lds128u(s_gate + (uint32_t)lane * 64u + (((uint32_t)j ^ sw64) << 4));
+                const uint32_t w[4] = {__float_as_uint(g.x), __float_as_uint(g.y), __float_as_uint(g.z), __float_as_uint(g.w)};
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    const __nv_bfloat162 gg = *reinterpret_cast<const __nv_bfloat162*>(&w[q]);
+                    x[8 * j + 2 * q] = __low2float(gg) > 0.f ? x[8 * j + 2 * q] * p.gate_scale : 0.f;
+                    x[8 * j + 2 * q + 1] = __high2float(gg) > 0.f ? x[8 * j + 2 * q + 1] * p.gate_scale : 0.f;
+                }
+            }
+        }
+        if (drop.enabled) {
+            const uint64_t base4 = (uint64_t)((int64_t)row * p.drop_ld + n0) >> 2;
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                float dm[4];
+                drop_mult4(drop, base4 + j, dm);
+                x[4 * j] *= dm[0]; x[4 * j + 1] *= dm[1]; x[4 * j + 2] *= dm[2]; x[4 * j + 3] *= dm[3];
+            }
+        }
+        if (has_res) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                const float4 q = lds128u(s_res + (uint32_t)lane * 128u + (((uint32_t)j ^ sw128) << 4));
+                x[4 * j] += q.x; x[4 * j + 1] += q.y; x[4 * j + 2] += q.z; x[4 * j + 3] += q.w;
+            }
+        }
+        if (has_acc) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                const float4 q = lds128u(s_acc + (uint32_t)lane * 128u + (((uint32_t)j ^ sw128) << 4));
+                x[4 * j] += q.x; x[4 * j + 1] += q.y; x[4 * j + 2] += q.z; x[4 * j + 3] += q.w;
+            }
+        }
+        __syncwarp();                                   // every lane has consumed the input tiles
+        if (c + CSTEP < BLOCK_N / 32) issue_loads(c + CSTEP);
+        if (lane == 0) ptx::bulk_wait_read0();          // the previous chunk's stores have read their staging tiles
+        __syncwarp();
+        if (p.colsum && row >= p.M) {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) x[j] = 0.f;    // rows past M are clipped on store but must not reach the column sums
+        }
+        if (p.out_f32 || p.colsum) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j)
+                sts128(s_of + (uint32_t)lane * 128u + (((uint32_t)j ^ sw128) << 4), __float_as_uint(x[4 * j]), __float_as_uint(x[4 * j + 1]),
+                       __float_as_uint(x[4 * j + 2]), __float_as_uint(x[4 * j + 3]));
+        }
+        if (p.out_pl) {
+            for (int pl = 0; pl < p.out_pl_n; ++pl) {
+                uint32_t h[16];
+#pragma unroll
+                for (int j = 0; j < 16; ++j) {
+                    const __nv_bfloat162 b2 = __floats2bfloat162_rn(x[2 * j], x[2 * j + 1]);
+                    h[j] = *reinterpret_cast<const uint32_t*>(&b2);
+                    if (pl + 1 < p.out_pl_n) {
+                        x[2 * j] -= __low2float(b2);
+                        x[2 * j + 1] -= __high2float(b2);
+                    }
+                }
+#pragma unroll
+                for (int j = 0; j < 4; ++j)
+                    sts128(s_pl + (uint32_t)pl * 2048u + (uint32_t)lane * 64u + (((uint32_t)j ^ sw64) << 4), h[4 * j], h[4 * j + 1], h[4 * j + 2],
+                           h[4 * j + 3]);
+            }
+        }
+        ptx::fence_proxy_async();
+        __syncwarp();
+        if (lane == 0) {
+            if (p.out_f32) ptx::tma_store_2d(&em.out_f32, s_of, n0, m0);
+            if (p.out_pl)
+                for (int pl = 0; pl < p.out_pl_n; ++pl) ptx::tma_store_3d(&em.out_pl, s_pl + (uint32_t)pl * 2048u, n0, m0, pl);
+            ptx::bulk_commit();
+        }
+        if (p.colsum) {  // bias gradient: lane j sums column j of the staged fp32 tile (planes were taken from the same values)
+            float cs = 0.f;
+            const uint32_t cj = (uint32_t)(lane >> 2), wj = (uint32_t)(lane & 3) * 4u;
+#pragma unroll
+            for (int r = 0; r < 32; ++r) {
+                float v;
+                asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(s_of + (uint32_t)r * 128u + ((cj ^ (uint32_t)(r & 7)) << 4) + wj));
+                cs += v;
+            }
+            if (n0 + lane < p.N) atomicAdd(p.colsum + n0 + lane, cs);
+        }
+    }
+    if (lane == 0) ptx::bulk_wait0();
+    __syncwarp();
+}
+
 template <int BLOCK_N, bool A_MN, bool B_MN, bool CTA2>
 __global__ void __launch_bounds__(GemmCfg<BLOCK_N, CTA2>::THREADS, GemmCfg<BLOCK_N, CTA2>::CTAS_PER_SM)
-gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b, const GemmParams p) {
+gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b, const __grid_constant__ EpiMaps em,
+            const GemmParams p) {
     using Cfg = GemmCfg<BLOCK_N, CTA2>;
     constexpr int STAGES = Cfg::STAGES;
     extern __shared__ uint8_t smem_raw[];
@@ -233,6 +403,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ C
     uint64_t* empty_bar = full_bar + STAGES;
     uint64_t* tmem_full_bar = empty_bar + STAGES;
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full_bar + 1);
+    uint64_t* epi_bar = tmem_full_bar + 3;  // after the 16-byte TMEM slot
 
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
@@ -250,6 +421,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ C
             ptx::mbar_init(&empty_bar[s], 1);
         }
         ptx::mbar_init(tmem_full_bar, 1);
+        for (int s = 0; s < 8; ++s) ptx::mbar_init(&epi_bar[s], 1);
         ptx::fence_barrier_init();
     }
     if (warp == 2) {
@@ -356,8 +528,12 @@ gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ C
             M2F_TRACE(3);
         }
         __syncwarp();
+    } else if (p.epi_tma) {
+        // ------------------------------------------------------------------ epilogue, TMA tiles in and out
+        epilogue_tma<BLOCK_N, Cfg::EPI_WARPS>(p, em, smem, (ptx::smem_u32(epi_bar + 8) + 15u) & ~15u, epi_bar, tmem_full_bar, tmem_base, warp, lane, m_blk, n_blk);
+        ptx::tcgen05_fence_before();
     } else {
-        // ------------------------------------------------------------------ epilogue
+        // ------------------------------------------------------------------ epilogue, pointer path (ragged / unaligned operands)
         // TMEM -> registers (thread = row) -> shared (transpose) -> registers (lane = 4 columns) -> global, coalesced.
         // The operand ring is free by now: the accumulator-ready commit fires after the last MMA has read it.
         EpiRegs e;
@@ -366,6 +542,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ C
         e.out_pl_stride = p.out_pl_stride; e.drop_ld = p.drop_ld; e.gate_scale = p.gate_scale; e.floor_ = p.relu ? 0.f : -INFINITY;
         e.M = p.M; e.N = p.N; e.out_pl_n = p.out_pl_n; e.accumulate = p.accumulate; e.vec4 = p.vec4; e.drop_on = p.drop.enabled;
         const Drop drop = drop_resolve(p.drop);
+        if (p.dbg & 1) { e.out_f32 = nullptr; e.out_pl = nullptr; }  // experiment: epilogue without its global stores
         ptx::mbar_wait(tmem_full_bar, 0);
         if (threadIdx.x == 64) M2F_TRACE(4);
         ptx::tcgen05_fence_after();
@@ -474,8 +651,45 @@ int make_planes_tmap(CUtensorMap* map, const m2f_planes_t* t, int box_rows) {
     return M2F_OK;
 }
 
+// 2-D / 3-D tensor map with a 32 x 32 box for the TMA epilogue
+static int make_epi_tmap(CUtensorMap* map, CUtensorMapDataType dt, int esize, void* ptr, int64_t rows, int64_t cols, int64_t ld, int planes,
+                         int64_t plane_stride) {
+    EncodeTiledFn enc = get_encode_fn();
+    M2F_REQUIRE(enc != nullptr, M2F_ERR_CUDA, "cuTensorMapEncodeTiled entry point not available");
+    cuuint64_t dims[3] = {(cuuint64_t)cols, (cuuint64_t)rows, (cuuint64_t)planes};
+    cuuint64_t strides[2] = {(cuuint64_t)ld * esize, (cuuint64_t)plane_stride * esize};
+    cuuint32_t box[3] = {32, 32, 1};
+    cuuint32_t estr[3] = {1, 1, 1};
+    const int rank = planes > 0 ? 3 : 2;
+    CUresult r = enc(map, dt, rank, ptr, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                     esize == 4 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    M2F_REQUIRE(r == CUDA_SUCCESS, M2F_ERR_CUDA, "cuTensorMapEncodeTiled (epilogue operand) failed with CUresult %d", (int)r);
+    return M2F_OK;
+}
+
+int gemm_make_epi_maps(GemmParams& p, EpiMaps* em) {
+    static const bool off = [] { const char* e = std::getenv("M2F_GEMM_EPI_TMA"); return e && e[0] == '0'; }();
+    p.epi_tma = 0;
+    auto ok = [](const void* ptr, int64_t ld, int esize) { return (reinterpret_cast<uintptr_t>(ptr) & 15) == 0 && (ld * esize) % 16 == 0; };
+    if (off) return M2F_OK;
+    if (p.out_f32 && !ok(p.out_f32, p.out_f32_ld, 4)) return M2F_OK;
+    if (p.resid && !ok(p.resid, p.resid_ld, 4)) return M2F_OK;
+    if (p.gate && !ok(p.gate, p.gate_ld, 2)) return M2F_OK;
+    if (p.out_pl && (!ok(p.out_pl, p.out_pl_ld, 2) || (p.out_pl_n > 1 && (p.out_pl_stride * 2) % 16 != 0))) return M2F_OK;
+    if (p.drop.enabled && (p.drop_ld & 3)) return M2F_OK;
+    if (p.out_f32) M2F_TRY(make_epi_tmap(&em->out_f32, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, p.out_f32, p.M, p.N, p.out_f32_ld, 0, 0));
+    if (p.resid) M2F_TRY(make_epi_tmap(&em->resid, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, const_cast<float*>(p.resid), p.M, p.N, p.resid_ld, 0, 0));
+    if (p.gate) M2F_TRY(make_epi_tmap(&em->gate, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<__nv_bfloat16*>(p.gate), p.M, p.N, p.gate_ld, 0, 0));
+    if (p.out_pl)
+        M2F_TRY(make_epi_tmap(&em->out_pl, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, p.out_pl, p.M, p.N, p.out_pl_ld, p.out_pl_n,
+                              p.out_pl_n > 1 ? p.out_pl_stride : (int64_t)p.M * p.out_pl_ld));
+    p.epi_tma = 1;
+    return M2F_OK;
+}
+
 template <int BLOCK_N, bool A_MN, bool B_MN, bool CTA2>
-static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p, cudaStream_t stream) {
+static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const EpiMaps& em, const GemmParams& p, cudaStream_t stream) {
     using Cfg = GemmCfg<BLOCK_N, CTA2>;
     auto kern = gemm_kernel<BLOCK_N, A_MN, B_MN, CTA2>;
     static bool attr_set = false;  // per instantiation
@@ -486,9 +700,9 @@ static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const GemmP
     dim3 grid(ceil_div(p.M, BLOCK_M), ceil_div(p.N, BLOCK_N));
     if constexpr (CTA2) {
         grid.x = (grid.x + 1) & ~1u;  // whole pairs; a row tile past M loads zeros and stores nothing
-        M2F_CUDA(launch_chain(kern, grid, dim3(Cfg::THREADS), Cfg::SMEM_BYTES, stream, 2, ta, tb, p));
+        M2F_CUDA(launch_chain(kern, grid, dim3(Cfg::THREADS), Cfg::SMEM_BYTES, stream, 2, ta, tb, em, p));
     } else {
-        M2F_CUDA(launch_chain(kern, grid, dim3(Cfg::THREADS), Cfg::SMEM_BYTES, stream, 1, ta, tb, p));
+        M2F_CUDA(launch_chain(kern, grid, dim3(Cfg::THREADS), Cfg::SMEM_BYTES, stream, 1, ta, tb, em, p));
     }
     M2F_LAUNCH_CHECK();
     return M2F_OK;
@@ -583,16 +797,16 @@ int gemm_fill_params(GemmParams& p, const m2f_planes_t* A, int a_mn, const m2f_p
     return M2F_OK;
 }
 
-int gemm_launch(const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p, int tile, int a_mn, int b_mn,
+int gemm_launch(const CUtensorMap& ta, const CUtensorMap& tb, const EpiMaps& em, const GemmParams& p, int tile, int a_mn, int b_mn,
                 cudaStream_t stream) {
     const int block_n = tile & 0xfff;
     const bool cta2 = (tile & GEMM_TILE_CTA2) != 0;
 #define M2F_GEMM_CASE(BN, C2)                                                              \
     if (block_n == BN && cta2 == C2) {                                                     \
-        if (!a_mn && !b_mn) return launch_gemm<BN, false, false, C2>(ta, tb, p, stream);   \
-        if (!a_mn && b_mn) return launch_gemm<BN, false, true, C2>(ta, tb, p, stream);     \
-        if (a_mn && b_mn) return launch_gemm<BN, true, true, C2>(ta, tb, p, stream);       \
-        return launch_gemm<BN, true, false, C2>(ta, tb, p, stream);                        \
+        if (!a_mn && !b_mn) return launch_gemm<BN, false, false, C2>(ta, tb, em, p, stream);   \
+        if (!a_mn && b_mn) return launch_gemm<BN, false, true, C2>(ta, tb, em, p, stream);     \
+        if (a_mn && b_mn) return launch_gemm<BN, true, true, C2>(ta, tb, em, p, stream);       \
+        return launch_gemm<BN, true, false, C2>(ta, tb, em, p, stream);                        \
     }
     M2F_GEMM_CASE(64, false)
     M2F_GEMM_CASE(128, false)
@@ -618,7 +832,10 @@ extern "C" int m2f_gemm(const m2f_planes_t* A, int a_mn_major, const m2f_planes_
     M2F_TRY(gemm_fill_params(p, A, a_mn_major, B, b_mn_major, segs, nsegs, M, N, epi));
     const int bn = gemm_block_n(M, N);
     CUtensorMap ta, tb;
+    EpiMaps em;
+    memset(&em, 0, sizeof(em));
+    M2F_TRY(gemm_make_epi_maps(p, &em));
     M2F_TRY(make_planes_tmap(&ta, A, a_mn_major ? BLOCK_K : BLOCK_M));
     M2F_TRY(make_planes_tmap(&tb, B, b_mn_major ? BLOCK_K : gemm_b_box_rows(bn)));
-    return gemm_launch(ta, tb, p, bn, a_mn_major, b_mn_major, reinterpret_cast<cudaStream_t>(stream));
+    return gemm_launch(ta, tb, em, p, bn, a_mn_major, b_mn_major, reinterpret_cast<cudaStream_t>(stream));
 }

@@ -13,6 +13,7 @@
 #include <unordered_map>
 #include <cstdio>
 #include <cstdlib>
+#include <cstring>
 #include <vector>
 
 #include "common.cuh"
@@ -167,6 +168,25 @@ struct TmapKeyHash {
     }
 };
 
+struct EpiKey {
+    const void *out_f32, *out_pl, *gate, *resid;
+    int64_t out_f32_ld, out_pl_ld, out_pl_stride, gate_ld, resid_ld;
+    int M, N, out_pl_n;
+    bool operator==(const EpiKey& o) const { return std::memcmp(this, &o, sizeof(EpiKey)) == 0; }
+};
+struct EpiKeyHash {
+    size_t operator()(const EpiKey& k) const {
+        size_t h = 1469598103934665603ull;
+        const unsigned char* b = reinterpret_cast<const unsigned char*>(&k);
+        for (size_t i = 0; i < sizeof(EpiKey); ++i) h = (h ^ b[i]) * 1099511628211ull;
+        return h;
+    }
+};
+struct EpiEntry {
+    EpiMaps maps;
+    int epi_tma;
+};
+
 struct m2f_plan {
     m2f_model* m;
     int64_t B, S, M;
@@ -267,6 +287,7 @@ struct m2f_plan {
     const void* bound_ws = nullptr;
     const void* bound_shadow = nullptr;
     std::unordered_map<TmapKey, CUtensorMap, TmapKeyHash> tmaps;
+    std::unordered_map<EpiKey, EpiEntry, EpiKeyHash> epimaps;
 
     Buf alloc_pl(int64_t rows, int64_t cols, int planes) {
         Buf b;
@@ -585,10 +606,24 @@ struct Ctx {
         GemmParams gp;
         M2F_TRY(gemm_fill_params(gp, &A, a_mn, &B, b_mn, segs, nsegs, M, N, &e));
         const int bn = gemm_block_n(M, N);
+        EpiKey ek;
+        std::memset(&ek, 0, sizeof(ek));  // padding bytes take part in the comparison
+        ek.out_f32 = gp.out_f32; ek.out_pl = gp.out_pl; ek.gate = gp.gate; ek.resid = gp.resid;
+        ek.out_f32_ld = gp.out_f32_ld; ek.out_pl_ld = gp.out_pl_ld; ek.out_pl_stride = gp.out_pl_stride; ek.gate_ld = gp.gate_ld;
+        ek.resid_ld = gp.resid_ld; ek.M = gp.M; ek.N = gp.N; ek.out_pl_n = gp.out_pl_n;
+        auto eit = p->epimaps.find(ek);
+        if (eit == p->epimaps.end()) {
+            EpiEntry ent;
+            std::memset(&ent, 0, sizeof(ent));
+            M2F_TRY(gemm_make_epi_maps(gp, &ent.maps));
+            ent.epi_tma = gp.epi_tma;
+            eit = p->epimaps.emplace(ek, ent).first;
+        }
+        gp.epi_tma = eit->second.epi_tma;
         const CUtensorMap *ta, *tb;
         M2F_TRY(tmap(A, a_mn ? BLOCK_K : BLOCK_M, &ta));
         M2F_TRY(tmap(B, b_mn ? BLOCK_K : gemm_b_box_rows(bn), &tb));
-        return gemm_launch(*ta, *tb, gp, bn, a_mn, b_mn, stream());
+        return gemm_launch(*ta, *tb, eit->second.maps, gp, bn, a_mn, b_mn, stream());
     }
 };
 
@@ -1154,6 +1189,7 @@ static int bind(m2f_plan* p, const void* shadow, void* ws) {
                 "plan: workspace and shadow must be 256-byte aligned");
     if (p->bound_ws != ws || p->bound_shadow != shadow) {
         p->tmaps.clear();
+        p->epimaps.clear();
         p->bound_ws = ws;
         p->bound_shadow = shadow;
     }
