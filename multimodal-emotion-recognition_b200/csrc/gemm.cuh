@@ -40,6 +40,7 @@ struct GemmParams {
     __nv_bfloat16* out_pl;
     int64_t out_pl_ld, out_pl_stride;
     int out_pl_n;
+    int b_static;  // B is not written by any kernel of the step (weights): its first tiles may be fetched before the PDL wait
     int epi_tma;  // 1: the [M,N]-shaped epilogue operands have tensor maps (EpiMaps) -- TMA epilogue; 0: pointer epilogue
 };
 

@@ -267,6 +267,7 @@ __device__ __forceinline__ void epilogue_tma(const GemmParams& p, const EpiMaps&
     ptx::named_bar_sync(1, EPI_WARPS * 32);  // bias visible to every epilogue warp
     ptx::mbar_wait(tmem_full_bar, 0);
     ptx::tcgen05_fence_after();
+    if (threadIdx.x == 64) M2F_TRACE(4);
     if (!rows_live) return;
     issue_loads(c_first);  // the ring is free from here on: it becomes the staging area
     uint32_t phase = 0;
@@ -385,8 +386,9 @@ __device__ __forceinline__ void epilogue_tma(const GemmParams& p, const EpiMaps&
             if (n0 + lane < p.N) atomicAdd(p.colsum + n0 + lane, cs);
         }
     }
-    if (lane == 0) ptx::bulk_wait0();
+    if (lane == 0) ptx::bulk_wait_read0();  // the staging tiles must outlive the stores' reads; the writes complete on their own
     __syncwarp();
+    if (threadIdx.x == 64) M2F_TRACE(5);
 }
 
 template <int BLOCK_N, bool A_MN, bool B_MN, bool CTA2>
@@ -433,13 +435,60 @@ gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ C
     else __syncthreads();
     ptx::tcgen05_fence_after();
     const uint32_t tmem_base = *tmem_slot;
-    pdl_wait();     // everything above overlapped the previous kernel's tail; operands / epilogue inputs are final from here
-    pdl_trigger();
+    // Programmatic dependent launch: everything above overlapped the previous kernel's tail.  The producer additionally
+    // starts the loads of a B operand that no kernel of the step writes (weights) before it waits.
+    if (!(warp == 0 && p.b_static)) {
+        pdl_wait();
+        pdl_trigger();
+    }
     if (threadIdx.x == 0) M2F_TRACE(1);
 
     if (warp == 0) {
         // ------------------------------------------------------------------ TMA producer
         if (ptx::elect_one()) {
+            // issue one k-block's B tile(s); in a pair both CTAs' bytes are credited to the leader's barrier
+            auto load_b = [&](int stage, int kbb, int pb) {
+                uint8_t* sb = smem_b + stage * Cfg::B_BYTES;
+                const int nb0 = n_blk * BLOCK_N + (int)cta_rank * Cfg::B_ROWS;  // this CTA's share of the B tile
+                if constexpr (CTA2) {
+                    const uint32_t fb = ptx::mapa(ptx::smem_u32(&full_bar[stage]), 0);
+                    if (!B_MN) {
+                        ptx::tma_load_3d_2cta(sb, &tma_b, fb, kbb, nb0, pb);
+                    } else {
+#pragma unroll
+                        for (int j = 0; j < Cfg::B_ROWS / 64; ++j)
+                            ptx::tma_load_3d_2cta(sb + j * (64 * BLOCK_K * 2), &tma_b, fb, nb0 + j * 64, kbb, pb);
+                    }
+                } else {
+                    if (!B_MN) {
+                        ptx::tma_load_3d(sb, &tma_b, &full_bar[stage], kbb, nb0, pb);
+                    } else {
+#pragma unroll
+                        for (int j = 0; j < BLOCK_N / 64; ++j)
+                            ptx::tma_load_3d(sb + j * (64 * BLOCK_K * 2), &tma_b, &full_bar[stage], nb0 + j * 64, kbb, pb);
+                    }
+                }
+            };
+            auto arm = [&](int stage) {
+                if constexpr (CTA2) {
+                    if (cta_rank == 0) ptx::mbar_expect_tx(&full_bar[stage], 2 * Cfg::STAGE_BYTES);
+                } else {
+                    ptx::mbar_expect_tx(&full_bar[stage], Cfg::STAGE_BYTES);
+                }
+            };
+            int pre = 0;  // k-blocks whose B tile is already in flight
+            if (p.b_static) {
+                int it0 = 0;
+                for (int pr = 0; pr < p.nprod && it0 < STAGES; ++pr)
+                    for (int sg = 0; sg < p.nsegs && it0 < STAGES; ++sg)
+                        for (int kb = 0; kb < p.seg_nkb[sg] && it0 < STAGES; ++kb, ++it0) {
+                            arm(it0);
+                            load_b(it0, p.seg_b_k0[sg] + kb * BLOCK_K, p.prod_b[pr]);
+                        }
+                pre = it0;
+                pdl_wait();
+                pdl_trigger();
+            }
             int it = 0;
             for (int pr = 0; pr < p.nprod; ++pr) {
                 const int pa = p.prod_a[pr], pb = p.prod_b[pr];
@@ -447,15 +496,15 @@ gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ C
                     for (int kb = 0; kb < p.seg_nkb[sg]; ++kb, ++it) {
                         const int stage = it % STAGES;
                         const uint32_t phase = (it / STAGES) & 1;
-                        ptx::mbar_wait(&empty_bar[stage], phase ^ 1);
                         const int ka = p.seg_a_k0[sg] + kb * BLOCK_K;
                         const int kbb = p.seg_b_k0[sg] + kb * BLOCK_K;
                         uint8_t* sa = smem_a + stage * Cfg::A_BYTES;
-                        uint8_t* sb = smem_b + stage * Cfg::B_BYTES;
-                        const int nb0 = n_blk * BLOCK_N + (int)cta_rank * Cfg::B_ROWS;  // this CTA's share of the B tile
+                        if (it >= pre) {
+                            ptx::mbar_wait(&empty_bar[stage], phase ^ 1);
+                            arm(stage);
+                            load_b(stage, kbb, pb);
+                        }
                         if constexpr (CTA2) {
-                            // both CTAs' bytes are credited to the leader's barrier: it alone is armed, with the pair's total
-                            if (cta_rank == 0) ptx::mbar_expect_tx(&full_bar[stage], 2 * Cfg::STAGE_BYTES);
                             const uint32_t fb = ptx::mapa(ptx::smem_u32(&full_bar[stage]), 0);
                             if (!A_MN) {
                                 ptx::tma_load_3d_2cta(sa, &tma_a, fb, ka, m_blk * BLOCK_M, pa);
@@ -464,15 +513,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ C
                                 for (int j = 0; j < BLOCK_M / 64; ++j)
                                     ptx::tma_load_3d_2cta(sa + j * (64 * BLOCK_K * 2), &tma_a, fb, m_blk * BLOCK_M + j * 64, ka, pa);
                             }
-                            if (!B_MN) {
-                                ptx::tma_load_3d_2cta(sb, &tma_b, fb, kbb, nb0, pb);
-                            } else {
-#pragma unroll
-                                for (int j = 0; j < Cfg::B_ROWS / 64; ++j)
-                                    ptx::tma_load_3d_2cta(sb + j * (64 * BLOCK_K * 2), &tma_b, fb, nb0 + j * 64, kbb, pb);
-                            }
                         } else {
-                            ptx::mbar_expect_tx(&full_bar[stage], Cfg::STAGE_BYTES);
                             if (!A_MN) {
                                 ptx::tma_load_3d(sa, &tma_a, &full_bar[stage], ka, m_blk * BLOCK_M, pa);
                             } else {
@@ -481,17 +522,14 @@ gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ C
                                     ptx::tma_load_3d(sa + j * (64 * BLOCK_K * 2), &tma_a, &full_bar[stage],
                                                      m_blk * BLOCK_M + j * 64, ka, pa);
                             }
-                            if (!B_MN) {
-                                ptx::tma_load_3d(sb, &tma_b, &full_bar[stage], kbb, nb0, pb);
-                            } else {
-#pragma unroll
-                                for (int j = 0; j < BLOCK_N / 64; ++j)
-                                    ptx::tma_load_3d(sb + j * (64 * BLOCK_K * 2), &tma_b, &full_bar[stage], nb0 + j * 64, kbb, pb);
-                            }
                         }
                     }
                 }
             }
+        }
+        else if (p.b_static) {  // the other lanes of the producer warp
+            pdl_wait();
+            pdl_trigger();
         }
         __syncwarp();
     } else if (warp == 1) {
@@ -781,6 +819,8 @@ int gemm_fill_params(GemmParams& p, const m2f_planes_t* A, int a_mn, const m2f_p
     p.out_pl_stride = e->out_planes.plane_stride;
     p.out_pl_n = e->out_planes.planes;
     p.trace = g_trace;
+    p.b_static = 0;
+    p.epi_tma = 0;
     p.dbg = g_dbg;
     p.colsum = e->colsum;
     p.vec4 = (p.out_f32 == nullptr || (p.out_f32_ld & 3) == 0) && (p.resid == nullptr || (p.resid_ld & 3) == 0) && ((p.drop_ld & 3) == 0);

@@ -605,6 +605,10 @@ struct Ctx {
         }
         GemmParams gp;
         M2F_TRY(gemm_fill_params(gp, &A, a_mn, &B, b_mn, segs, nsegs, M, N, &e));
+        {   // weights live in the shadow buffer, which only the refresh after the optimizer step writes
+            const uint8_t* bp = reinterpret_cast<const uint8_t*>(B.ptr);
+            gp.b_static = (bp >= shadow && bp < shadow + p->m->shadow_bytes) ? 1 : 0;
+        }
         const int bn = gemm_block_n(M, N);
         EpiKey ek;
         std::memset(&ek, 0, sizeof(ek));  // padding bytes take part in the comparison
