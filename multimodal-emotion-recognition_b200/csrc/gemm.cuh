@@ -57,7 +57,7 @@ constexpr int EPI2_WARP_BYTES = 20 * 1024;  // per epilogue warp: out f32 4K | o
 // host helpers (gemm_sm100.cu)
 int make_planes_tmap(CUtensorMap* map, const m2f_planes_t* t, int box_rows);
 constexpr int GEMM_TILE_CTA2 = 0x1000;
-int gemm_block_n(int64_t M, int64_t N);   // tile code: BLOCK_N | GEMM_TILE_CTA2
+int gemm_block_n(int64_t M, int64_t N, int64_t K);   // tile code: BLOCK_N | GEMM_TILE_CTA2
 int gemm_b_box_rows(int tile);            // rows of B one CTA stages per k-block (K-major tensor-map box)
 int gemm_fill_params(GemmParams& p, const m2f_planes_t* A, int a_mn, const m2f_planes_t* B, int b_mn, const m2f_kseg_t* segs,
                      int nsegs, int64_t M, int64_t N, const m2f_epilogue_t* e);

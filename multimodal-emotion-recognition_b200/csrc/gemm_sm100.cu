@@ -749,14 +749,20 @@ static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const EpiMa
 // Tile code: BLOCK_N, plus GEMM_TILE_CTA2 when the tile is computed by a CTA pair (256 x BLOCK_N per pair).
 int gemm_b_box_rows(int tile) { return (tile & GEMM_TILE_CTA2) ? (tile & 0xfff) / 2 : (tile & 0xfff); }
 
-int gemm_block_n(int64_t M, int64_t N) {
+int gemm_block_n(int64_t M, int64_t N, int64_t K) {
     // one 128 x BLOCK_N tile per CTA: prefer the widest tile that still yields >= 148 CTAs
     const int64_t mt = (M + BLOCK_M - 1) / BLOCK_M;
     static const int forced = [] { const char* e = std::getenv("M2F_GEMM_BN"); return e ? std::atoi(e) : 0; }();  // tuning aid
-    static const int pairs = [] { const char* e = std::getenv("M2F_GEMM_CTA2"); return e ? std::atoi(e) : 0; }();
-    if (pairs && N > 64) {
+    static const int pairs = [] { const char* e = std::getenv("M2F_GEMM_CTA2"); return e ? std::atoi(e) : 2; }();  // 0 never, 1 always, 2 by shape
+    if (pairs == 1 && N > 64) {
         const int bn = (forced == 128 || forced == 256) ? forced : 256;
         return ((N <= 128) ? 128 : bn) | GEMM_TILE_CTA2;
+    }
+    if (pairs == 2 && !forced && N >= 256) {
+        // CTA pairs halve the B bytes each SM ingests: they win where the main loop dominates (long K) and, with
+        // 256-wide tiles, once there are several waves of row tiles; short-K GEMMs keep two small CTAs per SM.
+        if (mt >= 48) return 256 | GEMM_TILE_CTA2;
+        if (K >= 1536) return 128 | GEMM_TILE_CTA2;
     }
     if (forced == 64 || forced == 128 || forced == 256) return (N <= 64) ? 64 : ((N <= 128 && forced == 256) ? 128 : forced);
     if (N > 128 && mt * ((N + 255) / 256) >= 148) return 256;
@@ -870,7 +876,9 @@ extern "C" int m2f_gemm(const m2f_planes_t* A, int a_mn_major, const m2f_planes_
     using namespace m2f;
     GemmParams p;
     M2F_TRY(gemm_fill_params(p, A, a_mn_major, B, b_mn_major, segs, nsegs, M, N, epi));
-    const int bn = gemm_block_n(M, N);
+    int64_t ktot = 0;
+    for (int i = 0; i < nsegs; ++i) ktot += segs[i].klen;
+    const int bn = gemm_block_n(M, N, ktot);
     CUtensorMap ta, tb;
     EpiMaps em;
     memset(&em, 0, sizeof(em));

@@ -11,6 +11,7 @@
 //   * concat operands are column halves of one buffer (fusion `u_i`, classifier input `zc`).
 #include <string>
 #include <unordered_map>
+#include <chrono>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -609,7 +610,9 @@ struct Ctx {
             const uint8_t* bp = reinterpret_cast<const uint8_t*>(B.ptr);
             gp.b_static = (bp >= shadow && bp < shadow + p->m->shadow_bytes) ? 1 : 0;
         }
-        const int bn = gemm_block_n(M, N);
+        int64_t ktot = 0;
+        for (int i = 0; i < nsegs; ++i) ktot += segs[i].klen;
+        const int bn = gemm_block_n(M, N, ktot);
         EpiKey ek;
         std::memset(&ek, 0, sizeof(ek));  // padding bytes take part in the comparison
         ek.out_f32 = gp.out_f32; ek.out_pl = gp.out_pl; ek.gate = gp.gate; ek.resid = gp.resid;
@@ -1226,7 +1229,15 @@ static int run_graphed(m2f_plan* p, m2f_plan::GraphSlot& g, const m2f_plan::Grap
         g.key = key;
         g.kernels = captured;
     }
-    M2F_CUDA(cudaGraphLaunch(g.exec, user));
+    static const bool host_time = std::getenv("M2F_HOSTTIME") != nullptr;
+    if (host_time) {
+        const auto t0 = std::chrono::steady_clock::now();
+        M2F_CUDA(cudaGraphLaunch(g.exec, user));
+        const double us = std::chrono::duration<double, std::micro>(std::chrono::steady_clock::now() - t0).count();
+        std::fprintf(stderr, "m2f: cudaGraphLaunch of %lld kernels took %.1f us on the host\n", g.kernels, us);
+    } else {
+        M2F_CUDA(cudaGraphLaunch(g.exec, user));
+    }
     note_launches(g.kernels);
     return M2F_OK;
 }

@@ -128,3 +128,40 @@ def batch_metrics_device(logits: torch.Tensor, emotion: torch.Tensor):
     acc = tp.sum().item() / n if n else 0.0
     f1w = (f1 * support)[present].sum().item() / n if n else 0.0
     return acc, f1w
+
+
+class DevicePrefetcher:
+    """Host -> device staging for the reference's train()/test() loops (src/train.py:223-227, src/test.py:59-62: one
+    `.to(device)` per tensor per batch): wraps any iterable of batch dicts, keeps the host copies in pinned memory and
+    issues the copy of batch i+1 on its own stream while batch i computes.  Iterating yields device batches whose
+    copies the current stream has been ordered after."""
+
+    def __init__(self, loader, device, depth: int = 2):
+        self.loader, self.device, self.depth = loader, torch.device(device), max(1, int(depth))
+        self.stream = torch.cuda.Stream(device=self.device)
+
+    def _stage(self, batch):
+        with torch.cuda.stream(self.stream):
+            dev = {k: (v if v.is_pinned() else v.pin_memory()).to(self.device, non_blocking=True) for k, v in batch.items()}
+        ev = torch.cuda.Event()
+        ev.record(self.stream)
+        return dev, ev
+
+    def __iter__(self):
+        it = iter(self.loader)
+        queue = []
+        try:
+            while len(queue) < self.depth:
+                queue.append(self._stage(next(it)))
+        except StopIteration:
+            pass
+        while queue:
+            dev, ev = queue.pop(0)
+            torch.cuda.current_stream(self.device).wait_event(ev)
+            for v in dev.values():  # the caching allocator must not hand the memory out while the consumer still reads it
+                v.record_stream(torch.cuda.current_stream(self.device))
+            try:
+                queue.append(self._stage(next(it)))
+            except StopIteration:
+                pass
+            yield dev

@@ -12,6 +12,7 @@ from __future__ import annotations
 
 import ctypes as C
 import math
+import operator
 from typing import Dict, List, Optional, Tuple
 
 import torch
@@ -57,6 +58,9 @@ def _default_planes() -> int:
     if mode not in table:
         raise ValueError(f"M2F_PRECISION={mode!r}: expected one of {sorted(table)}")
     return table[mode]
+
+
+_VERSION_OF = operator.attrgetter("_version")
 
 
 class _Plan:
@@ -149,7 +153,10 @@ class M2FNet(nn.Module):
                 for ti in range(1, mc.n_transformers):
                     getattr(encs, str(ti)).add_module("norm", getattr(encs, "0").norm)
         self.reset_parameters()
+        self._plist = [p for p, _, _ in self._flat]
         self._grad_arena: Optional[torch.Tensor] = None
+        self._grad_views = None          # p.grad views into the gradient arena, built once
+        self._grads_cleared = False      # FusedAdam.zero_grad(): views still attached, contents dead
         self._shadow: Optional[torch.Tensor] = None
         self._shadow_version = None
         self._plans: Dict[Tuple[int, int, bool], _Plan] = {}
@@ -225,7 +232,10 @@ class M2FNet(nn.Module):
             p.data = view
             p.grad = None
         self._arena = arena
+        self._plist = [p for p, _, _ in self._flat]
         self._grad_arena = None
+        self._grad_views = None
+        self._grads_cleared = False
         self._shadow = None
         self._shadow_version = None
         for pl in self._plans.values():
@@ -241,7 +251,7 @@ class M2FNet(nn.Module):
         return True
 
     def _param_version(self) -> int:
-        return sum(p._version for p, _, _ in self._flat)
+        return sum(map(_VERSION_OF, self._plist))
 
     def _ensure_shadow(self):
         if not self._views_intact():
@@ -281,9 +291,14 @@ class M2FNet(nn.Module):
             raise RuntimeError("M2FNet backward: the workspace of this (B,S) plan was overwritten by a later forward; "
                                "call backward before the next forward of the same shape")
         dlogits = dlogits.contiguous().float()
-        fresh = all(p.grad is None for p, _, _ in self._flat)
+        # `_grads_cleared`: FusedAdam.zero_grad() left the p.grad views attached and only promised they are dead
+        attached = self._grads_cleared and self._grad_views is not None
+        fresh = attached or all(p.grad is None for p in self._plist)
         if self._grad_arena is None:
             self._grad_arena = torch.zeros(self._arena_floats, dtype=torch.float32, device=self._arena.device)
+            self._grad_views = None
+        if self._grad_views is None:
+            self._grad_views = [self._grad_arena[o:o + n].view(p.shape) for p, o, n in self._flat]
         target = self._grad_arena if fresh else torch.empty_like(self._grad_arena)
         if self._bucket_hook is not None and fresh:
             errors = []
@@ -308,10 +323,12 @@ class M2FNet(nn.Module):
             _lib.check(_lib.lib().m2f_plan_backward(plan.handle, self._arena.data_ptr(), self._shadow.data_ptr(), plan.ws.data_ptr(),
                                                     dlogits.data_ptr(), target.data_ptr(), _stream()), "plan_backward")
         self.launches += 1
-        if fresh:
-            for p, o, n in self._flat:
+        if attached:
+            self._grads_cleared = False  # the views already point at the arena the kernels just wrote
+        elif fresh:
+            for p, v in zip(self._plist, self._grad_views):
                 if p.requires_grad:
-                    p.grad = self._grad_arena[o:o + n].view(p.shape)
+                    p.grad = v
         else:  # gradient accumulation (zero_grad(set_to_none=False) or several backwards per step)
             for p, o, n in self._flat:
                 if not p.requires_grad:

@@ -45,6 +45,18 @@ class FusedAdam(torch.optim.Optimizer):
         self.model._shadow_version = None  # the kernel wrote through raw pointers: the bf16 weight shadow is stale
         return loss
 
+    def zero_grad(self, set_to_none: bool = True):
+        """With `set_to_none=True` (the default, and what the reference's loop does, src/train.py:225) the gradient views
+        stay attached to the arena and are only declared dead: the next backward overwrites the arena in place, so
+        nothing has to be detached and re-attached for 186 parameters every step.  Until that backward `p.grad` still
+        shows the previous step's values."""
+        m = self.model
+        if set_to_none and m._grad_views is not None and all(p.grad is v for p, v in zip(m._plist[:4], m._grad_views[:4])):
+            m._grads_cleared = True
+            return
+        m._grads_cleared = False
+        super().zero_grad(set_to_none=set_to_none)
+
     def state_dict(self):
         for st in self.state.values():
             st["step"] = torch.tensor(float(self._t))
