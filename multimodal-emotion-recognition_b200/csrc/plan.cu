@@ -227,19 +227,23 @@ struct m2f_plan {
         const void *params = nullptr, *shadow = nullptr, *ws = nullptr, *grads = nullptr;
         float p_used = -1.f;
         int flags = 0;
+        int64_t bucket_floats = 0;
         bool operator==(const GraphKey& o) const {
-            return params == o.params && shadow == o.shadow && ws == o.ws && grads == o.grads && p_used == o.p_used && flags == o.flags;
+            return params == o.params && shadow == o.shadow && ws == o.ws && grads == o.grads && p_used == o.p_used && flags == o.flags &&
+                   bucket_floats == o.bucket_floats;
         }
     };
     struct GraphSlot {
         cudaGraphExec_t exec = nullptr;
         GraphKey key;
         long long kernels = 0;
+        std::vector<std::pair<int64_t, int64_t>> marks;  // gradient ranges reported through external events (data parallel)
         void reset() {
             if (exec) cudaGraphExecDestroy(exec);
             exec = nullptr;
         }
     } gf, gb;
+    std::vector<cudaEvent_t> bucket_evs;     // recorded by event nodes of the backward graph, one per reported range
     cudaStream_t cap = nullptr;
     unsigned long long* rng_dev = nullptr;   // {seed, step} read by the dropout kernels of the captured graphs
     int use_graph = 1;
@@ -268,6 +272,8 @@ struct m2f_plan {
             if (wgf_ev[j]) { cudaEventDestroy(wgf_ev[j]); wgf_ev[j] = nullptr; }
         gf.reset();
         gb.reset();
+        for (auto& e : bucket_evs) cudaEventDestroy(e);
+        bucket_evs.clear();
         if (rng_dev) { cudaFree(rng_dev); rng_dev = nullptr; }
         if (tl_dev) { cudaFree(tl_dev); tl_dev = nullptr; }
         if (cap) { cudaStreamDestroy(cap); cap = nullptr; }
@@ -556,14 +562,33 @@ struct Ctx {
     // Every 2-D gradient at arena offsets >= w has been enqueued.  When a bucket is due, the plan's
     // ready stream is ordered after the weight-gradient streams and handed to the callback: the caller's collective waits on it alone.
     int done_down_to(int64_t w, bool flush = false) {
-        if (!cb) return M2F_OK;
+        if (!cb && !marks) return M2F_OK;
         if (hi - w >= bucket_floats || (flush && hi > w)) {
             cudaStream_t ready = p->use_streams ? p->ready : st;
+            if (marks) M2F_TRY(dep(st, ready));  // capture: pulls `ready` into the graph even when no side stream has run yet
             M2F_TRY(dep(side(1), ready));  // the two weight-gradient streams
             M2F_TRY(dep(side(2), ready));
-            cb(cb_user, w, hi, ready);
+            M2F_TRY(report(w, hi, ready));
             hi = w;
         }
+        return M2F_OK;
+    }
+    // eager: tell the caller now; capture: leave an external event-record node behind, the caller is told after the launch
+    std::vector<std::pair<int64_t, int64_t>>* marks = nullptr;
+    bool ready_in_capture = false;
+    int report(int64_t lo, int64_t hi_, cudaStream_t ready) {
+        if (!marks) {
+            cb(cb_user, lo, hi_, ready);
+            return M2F_OK;
+        }
+        while (p->bucket_evs.size() <= marks->size()) {
+            cudaEvent_t e;
+            M2F_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+            p->bucket_evs.push_back(e);
+        }
+        M2F_CUDA(cudaEventRecordWithFlags(p->bucket_evs[marks->size()], ready, cudaEventRecordExternal));
+        marks->emplace_back(lo, hi_);
+        if (ready != st) ready_in_capture = true;
         return M2F_OK;
     }
 
@@ -1008,10 +1033,11 @@ static int backward_all(Ctx& c, const uint8_t* key_pad, const float* dlogits, in
     }
     M2F_TRY(c.done_down_to(0, true));
     for (int i = 0; i < 3; ++i) M2F_TRY(c.dep(c.side(i), c.st));
-    if (c.cb) {  // biases / LayerNorm parameters (atomically accumulated by every stream): final once everything has joined
+    if (c.cb || c.marks) {  // biases / LayerNorm parameters (atomically accumulated by every stream): final once everything has joined
         cudaStream_t ready = p->use_streams ? p->ready : c.st;
         M2F_TRY(c.dep(c.st, ready));
-        c.cb(c.cb_user, md->off_1d, md->arena_floats, ready);
+        M2F_TRY(c.report(md->off_1d, md->arena_floats, ready));
+        if (c.marks && c.ready_in_capture) M2F_TRY(c.dep(ready, c.st));  // a capture must end with every forked stream joined
     }
     return M2F_OK;
 }
@@ -1333,24 +1359,38 @@ extern "C" int m2f_plan_backward_bucketed(m2f_plan_t* p, const float* params, co
     c.hi = p->m->off_1d;
     const uint8_t* kp = c.ws + p->key_pad.off;
     int rc;
-    if (!p->use_graph || cb) {  // the bucket callbacks launch the caller's collectives between our kernels: not capturable
-        if (p->use_graph) m2f_set_rng_source(reinterpret_cast<const uint64_t*>(p->rng_dev));  // the forward ran from a graph
+    if (!p->use_graph) {
         rc = backward_all(c, kp, dlogits, PH_ALL);
-        m2f_set_rng_source(nullptr);
     } else {
+        // With bucket callbacks the graph carries one external event-record node per reported range; after the launch each
+        // callback gets the plan's ready stream, ordered behind its event, so the caller's collectives still overlap the rest.
         M2F_TRY(backward_all(c, kp, dlogits, PH_HEAD));
         m2f_plan::GraphKey key;
         key.params = params; key.shadow = shadow; key.ws = workspace; key.grads = grads; key.p_used = p->p_used;
+        key.flags = cb ? 1 : 0;
+        key.bucket_floats = cb ? c.bucket_floats : 0;
+        std::vector<std::pair<int64_t, int64_t>> marks;
+        bool captured = false;
         rc = run_graphed(p, p->gb, key, ust, [&](cudaStream_t cs) {
             Ctx g = c;
             g.st = cs;
+            g.cb = nullptr;
+            if (cb) g.marks = &marks;
+            captured = true;
             int r = backward_all(g, kp, nullptr, PH_BODY);
             if (r == M2F_OK) g.stamp("end");
             return r;
         });
+        if (rc == M2F_OK && cb) {
+            if (captured) p->gb.marks = marks;
+            for (size_t k = 0; k < p->gb.marks.size(); ++k) {
+                M2F_CUDA(cudaStreamWaitEvent(p->ready, p->bucket_evs[k], 0));
+                cb(user, p->gb.marks[k].first, p->gb.marks[k].second, p->ready);
+            }
+        }
     }
     if (p->tl_on && rc == M2F_OK) {
-        if (!p->use_graph || cb) c.stamp("end");
+        if (!p->use_graph) c.stamp("end");
         const char* n = std::getenv("M2F_TIMELINE_STEP");
         if (++p->tl_calls == (n ? std::atoll(n) : 5)) {
             M2F_CUDA(cudaDeviceSynchronize());

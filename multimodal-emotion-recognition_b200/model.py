@@ -154,6 +154,7 @@ class M2FNet(nn.Module):
                     getattr(encs, str(ti)).add_module("norm", getattr(encs, "0").norm)
         self.reset_parameters()
         self._plist = [p for p, _, _ in self._flat]
+        self._anchor_box = [None]  # in a list: assigning a Parameter as an attribute would register it under that name
         self._grad_arena: Optional[torch.Tensor] = None
         self._grad_views = None          # p.grad views into the gradient arena, built once
         self._grads_cleared = False      # FusedAdam.zero_grad(): views still attached, contents dead
@@ -368,13 +369,22 @@ class M2FNet(nn.Module):
         mask_u8 = mask_u8.view(torch.uint8) if mask_u8.dtype == torch.bool else (mask_u8 != 0).view(torch.uint8)
         with torch.cuda.device(self._arena.device):
             self._ensure_shadow()
-            needs_grad = torch.is_grad_enabled() and any(p.requires_grad for p, _, _ in self._flat)
+            anchor = self._grad_anchor()
+            needs_grad = torch.is_grad_enabled() and anchor is not None
             plan = self._plan(B, S, needs_grad)
             dropout_on = self.training and float(self.config.dropout) > 0.0
             if needs_grad:
-                anchor = next(p for p, _, _ in self._flat if p.requires_grad)
                 return _M2FStep.apply(self, plan, text, audio, mask_u8, dropout_on, anchor)
             return self._launch_forward(plan, text, audio, mask_u8, dropout_on)
+
+    def _grad_anchor(self):
+        """First parameter that requires grad (autograd needs one differentiable input to record the step's node); the
+        scan over all parameters is repeated only when the cached one stops requiring grad or nothing was cached."""
+        a = self._anchor_box[0]
+        if a is not None and a.requires_grad:
+            return a
+        self._anchor_box[0] = next((p for p in self._plist if p.requires_grad), None)
+        return self._anchor_box[0]
 
     # ------------------------------------------------------------------------------------------ extras
     def flat_parameters(self) -> torch.Tensor:

@@ -41,11 +41,29 @@ def _worker(rank, world, port, out):
     crit(solo(fb["text"], fb["audio"], fb["padding_mask"]).permute(0, 2, 1), fb["emotion"]).backward()
     torch.cuda.synchronize()
     err = (torch.linalg.vector_norm(g_dp - solo.flat_grads()) / torch.linalg.vector_norm(solo.flat_grads())).item()
+    # several more steps through the optimizer: the replayed backward graph must keep ordering every bucket's
+    # all-reduce behind the kernels that produce it (a stale event would reduce half-written gradients)
+    opt_dp = pkg.FusedAdam(model, lr=1e-3, weight_decay=0.01)
+    opt_solo = pkg.FusedAdam(solo, lr=1e-3, weight_decay=0.01)
+    opt_dp.step()
+    opt_solo.step()
+    for it in range(3):
+        fb2 = D.synth_batch(8, 9, 128, 64, seed=50 + it)
+        b2 = {k: v[lo:hi].cuda() for k, v in fb2.items()}
+        fb2 = {k: v.cuda() for k, v in fb2.items()}
+        opt_dp.zero_grad()
+        crit(net(b2["text"], b2["audio"], b2["padding_mask"]).permute(0, 2, 1), b2["emotion"]).backward()
+        opt_dp.step()
+        opt_solo.zero_grad()
+        crit(solo(fb2["text"], fb2["audio"], fb2["padding_mask"]).permute(0, 2, 1), fb2["emotion"]).backward()
+        opt_solo.step()
+    torch.cuda.synchronize()
+    perr = (torch.linalg.vector_norm(model.flat_parameters() - solo.flat_parameters()) / torch.linalg.vector_norm(solo.flat_parameters())).item()
     gathered = [torch.empty_like(g_dp) for _ in range(world)]
     dist.all_gather(gathered, g_dp)
     same = all(torch.equal(gathered[0], x) for x in gathered)
     if rank == 0:
-        torch.save({"err": err, "same": same, "buckets": n_buckets}, out)
+        torch.save({"err": err, "same": same, "buckets": n_buckets, "param_err_after_4_steps": perr}, out)
     dist.destroy_process_group()
 
 
@@ -58,3 +76,4 @@ def test_dp2_gradients_equal_single_gpu(tmp_path):
     r = torch.load(out)
     assert r["same"] and r["buckets"] >= 3
     assert r["err"] < 2e-5, r
+    assert r["param_err_after_4_steps"] < 1e-5, r

@@ -90,3 +90,17 @@ def test_strict_checkpoint_interchange_with_reference(pkg):
     assert not ours.load_state_dict(r.state_dict(), strict=True).missing_keys
     assert not r.load_state_dict(ours.state_dict(), strict=True).missing_keys
     assert [n for n, _ in r.named_parameters()].sort() == [n for n, _ in ours.named_parameters()].sort()
+
+
+def test_state_dict_keys_survive_a_forward_setup(pkg):
+    """Internal caches must not leak into state_dict (nn.Module registers any Parameter assigned as an attribute)."""
+    import importlib
+    D = importlib.import_module(pkg.__name__ + ".data")
+    m = pkg.M2FNet(D.default_model_config(AUDIO=dict(embedding_size=32, n_head=2, n_encoder_layers=1),
+                                          TEXT=dict(embedding_size=32, n_head=2, n_encoder_layers=1),
+                                          FAM=dict(embedding_size=32, n_head=2, n_layers=1),
+                                          CLASSIFIER=dict(hidden_size=32, output_size=7, n_layers=2)))
+    keys = set(m.state_dict().keys())
+    assert m._grad_anchor() is not None
+    assert set(m.state_dict().keys()) == keys
+    assert all(not k.startswith("_") for k in keys)
