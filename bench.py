@@ -39,7 +39,7 @@ def parse():
     ap.add_argument("--seq", type=int, default=33)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
-    ap.add_argument("--bucket-mb", type=float, default=32.0)
+    ap.add_argument("--bucket-mb", type=float, default=128.0)
     return ap.parse_args()
 
 
