@@ -232,6 +232,13 @@ int m2f_plan_backward_bucketed(m2f_plan_t* p, const float* params, const void* s
 int m2f_adam_step(float* params, const float* grads, float* exp_avg, float* exp_avg_sq, int64_t n, float lr,
                   float beta1, float beta2, float eps, float weight_decay, int64_t t, float grad_scale, void* stream);
 
+/* The same update for a model's arena, fused with the refresh of the bf16 weight shadow (m2f_model_refresh_shadow):
+ * each updated 2-D weight is split into its planes while still in registers, saving one pass over the parameters.
+ * Bit-identical to m2f_adam_step over the whole arena followed by m2f_model_refresh_shadow. */
+int m2f_model_adam_step(const m2f_model_t* m, float* params, const float* grads, float* exp_avg, float* exp_avg_sq,
+                        void* shadow, float lr, float beta1, float beta2, float eps, float weight_decay, int64_t t,
+                        float grad_scale, void* stream);
+
 /* test helper: mask[i] = 1 if element i of `site` is kept, for i in [0, n) */
 int m2f_dropout_mask(float p, uint64_t seed, uint64_t step, uint32_t site, int64_t n, uint8_t* mask,
                      void* stream);

@@ -12,6 +12,7 @@
 #include <string>
 #include <unordered_map>
 #include <chrono>
+#include <cmath>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -509,6 +510,58 @@ shadow_refresh_kernel(const float* __restrict__ params, uint8_t* __restrict__ sh
             const int64_t r = i / e.cols;
             const int cc = (int)(i - r * e.cols);
             store_planes(dst, e.stride, e.planes, r * e.dst_ld + cc, src[r * e.src_ld + cc]);
+        }
+    }
+}
+
+// Adam update of the 2-D weights fused with the refresh of their bf16 shadow: same arithmetic as adam_kernel (optim.cu),
+// walked entry by entry so that each updated value is split into planes while it is still in registers.
+struct AdamArgs {
+    float b1, b2, eps, wd, step_size, inv_sqrt_bc2, grad_scale;
+};
+__device__ __forceinline__ float adam_one(float& p, float g, float& m, float& v, const AdamArgs& a) {
+    const float gr = g * a.grad_scale + a.wd * p;
+    m = a.b1 * m + (1.f - a.b1) * gr;
+    v = a.b2 * v + (1.f - a.b2) * gr * gr;
+    const float denom = sqrtf(v) * a.inv_sqrt_bc2 + a.eps;
+    p -= a.step_size * (m / denom);
+    return p;
+}
+__global__ void __launch_bounds__(256)
+adam_shadow_kernel(float* __restrict__ params, const float* __restrict__ grads, float* __restrict__ em, float* __restrict__ ev,
+                   uint8_t* __restrict__ shadow, const ShadowBatch batch, const AdamArgs a) {
+    const SEntry& e = batch.e[blockIdx.y];
+    __nv_bfloat16* dst = reinterpret_cast<__nv_bfloat16*>(shadow + e.dst_off);
+    if ((e.cols & 3) == 0 && (e.src_ld & 3) == 0 && (e.src_off & 3) == 0) {
+        const int c4 = e.cols >> 2;
+        const int64_t total = (int64_t)e.rows * c4;
+        for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+            const int64_t r = i / c4;
+            const int cc = (int)(i - r * c4) * 4;
+            const int64_t idx = e.src_off + r * e.src_ld + cc;
+            float4 pp = *reinterpret_cast<const float4*>(params + idx);
+            const float4 gg = *reinterpret_cast<const float4*>(grads + idx);
+            float4 mm = *reinterpret_cast<const float4*>(em + idx), vv = *reinterpret_cast<const float4*>(ev + idx);
+            float o[4];
+            o[0] = adam_one(pp.x, gg.x, mm.x, vv.x, a);
+            o[1] = adam_one(pp.y, gg.y, mm.y, vv.y, a);
+            o[2] = adam_one(pp.z, gg.z, mm.z, vv.z, a);
+            o[3] = adam_one(pp.w, gg.w, mm.w, vv.w, a);
+            *reinterpret_cast<float4*>(params + idx) = pp;
+            *reinterpret_cast<float4*>(em + idx) = mm;
+            *reinterpret_cast<float4*>(ev + idx) = vv;
+            store_planes4(dst, e.stride, e.planes, r * e.dst_ld + cc, o);
+        }
+    } else {
+        const int64_t total = (int64_t)e.rows * e.cols;
+        for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+            const int64_t r = i / e.cols;
+            const int cc = (int)(i - r * e.cols);
+            const int64_t idx = e.src_off + r * e.src_ld + cc;
+            float pp = params[idx], mm = em[idx], vv = ev[idx];
+            adam_one(pp, grads[idx], mm, vv, a);
+            params[idx] = pp; em[idx] = mm; ev[idx] = vv;
+            store_planes(dst, e.stride, e.planes, r * e.dst_ld + cc, pp);
         }
     }
 }
@@ -1086,6 +1139,48 @@ extern "C" int m2f_model_refresh_shadow(const m2f_model_t* m, const float* param
         b.n = (int)std::min<size_t>(SHADOW_CHUNK, m->sentries.size() - i);
         for (int j = 0; j < b.n; ++j) b.e[j] = m->sentries[i + j];
         shadow_refresh_kernel<<<dim3(64, b.n), 256, 0, st>>>(params, reinterpret_cast<uint8_t*>(shadow), b);
+        M2F_LAUNCH_CHECK();
+    }
+    return M2F_OK;
+}
+
+extern "C" int m2f_model_adam_step(const m2f_model_t* m, float* params, const float* grads, float* exp_avg, float* exp_avg_sq, void* shadow,
+                                   float lr, float beta1, float beta2, float eps, float weight_decay, int64_t t, float grad_scale,
+                                   void* stream) {
+    M2F_REQUIRE(m && params && grads && exp_avg && exp_avg_sq && shadow && t >= 1, M2F_ERR_ARG, "model_adam_step: bad argument");
+    M2F_REQUIRE(((reinterpret_cast<uintptr_t>(params) | reinterpret_cast<uintptr_t>(grads) | reinterpret_cast<uintptr_t>(exp_avg) |
+                  reinterpret_cast<uintptr_t>(exp_avg_sq)) % 16) == 0 && (reinterpret_cast<uintptr_t>(shadow) % 256) == 0,
+                M2F_ERR_ALIGN, "model_adam_step: arenas must be 16-byte, shadow 256-byte aligned");
+    auto st = reinterpret_cast<cudaStream_t>(stream);
+    const double bc1 = 1.0 - pow((double)beta1, (double)t), bc2 = 1.0 - pow((double)beta2, (double)t);
+    AdamArgs a{beta1, beta2, eps, weight_decay, (float)((double)lr / bc1), (float)(1.0 / sqrt(bc2)), grad_scale};
+    // 2-D weights: every element belongs to exactly one planes entry of the shadow table
+    std::vector<SEntry> copies;
+    ShadowBatch b;
+    b.n = 0;
+    auto flush = [&]() -> int {
+        if (b.n == 0) return M2F_OK;
+        adam_shadow_kernel<<<dim3(96, b.n), 256, 0, st>>>(params, grads, exp_avg, exp_avg_sq, reinterpret_cast<uint8_t*>(shadow), b, a);
+        M2F_LAUNCH_CHECK();
+        b.n = 0;
+        return M2F_OK;
+    };
+    for (const SEntry& e : m->sentries) {
+        if (e.planes == 0) {
+            copies.push_back(e);
+            continue;
+        }
+        b.e[b.n++] = e;
+        if (b.n == SHADOW_CHUNK) M2F_TRY(flush());
+    }
+    M2F_TRY(flush());
+    // biases / LayerNorm vectors, then their packed fp32 copies in the shadow
+    M2F_TRY(m2f_adam_step(params + m->off_1d, grads + m->off_1d, exp_avg + m->off_1d, exp_avg_sq + m->off_1d, m->arena_floats - m->off_1d, lr,
+                          beta1, beta2, eps, weight_decay, t, grad_scale, stream));
+    for (size_t i = 0; i < copies.size(); i += SHADOW_CHUNK) {
+        b.n = (int)std::min<size_t>(SHADOW_CHUNK, copies.size() - i);
+        for (int j = 0; j < b.n; ++j) b.e[j] = copies[i + j];
+        shadow_refresh_kernel<<<dim3(4, b.n), 256, 0, st>>>(params, reinterpret_cast<uint8_t*>(shadow), b);
         M2F_LAUNCH_CHECK();
     }
     return M2F_OK;

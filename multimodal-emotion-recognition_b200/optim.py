@@ -38,11 +38,17 @@ class FusedAdam(torch.optim.Optimizer):
         grp = self.param_groups[0]
         self._t += 1
         arena = self.model.flat_parameters()
-        _lib.check(_lib.lib().m2f_adam_step(arena.data_ptr(), g.data_ptr(), self._m.data_ptr(), self._v.data_ptr(), arena.numel(),
-                                            float(grp["lr"]), float(grp["betas"][0]), float(grp["betas"][1]), float(grp["eps"]),
-                                            float(grp["weight_decay"]), self._t, self.grad_scale,
-                                            torch.cuda.current_stream().cuda_stream), "adam_step")
-        self.model._shadow_version = None  # the kernel wrote through raw pointers: the bf16 weight shadow is stale
+        mdl = self.model
+        hp = (float(grp["lr"]), float(grp["betas"][0]), float(grp["betas"][1]), float(grp["eps"]), float(grp["weight_decay"]), self._t,
+              self.grad_scale, torch.cuda.current_stream().cuda_stream)
+        if mdl._shadow is not None and mdl._shadow_version == mdl._param_version() and mdl._views_intact():
+            # shadow is current: update and re-split the weights in one pass; it stays current
+            _lib.check(_lib.lib().m2f_model_adam_step(mdl._handle, arena.data_ptr(), g.data_ptr(), self._m.data_ptr(), self._v.data_ptr(),
+                                                      mdl._shadow.data_ptr(), *hp), "model_adam_step")
+        else:
+            _lib.check(_lib.lib().m2f_adam_step(arena.data_ptr(), g.data_ptr(), self._m.data_ptr(), self._v.data_ptr(), arena.numel(), *hp),
+                       "adam_step")
+            mdl._shadow_version = None  # the kernel wrote through raw pointers: the bf16 weight shadow is stale
         return loss
 
     def zero_grad(self, set_to_none: bool = True):

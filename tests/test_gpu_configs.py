@@ -110,3 +110,33 @@ def test_reference_train_loop_body_tracks_oracle(P):
     num = sum(float(((got[n] - v.detach()) ** 2).sum()) for n, v in leaves.items())
     den = sum(float((v.detach() ** 2).sum()) for v in leaves.values())
     assert (num / den) ** 0.5 < 1e-5
+
+
+def test_fused_adam_keeps_the_weight_shadow_current(P):
+    """FusedAdam updates the weights and re-splits their bf16 shadow in one pass (m2f_model_adam_step): the next forward
+    must see exactly what an explicit shadow refresh of the updated parameters gives, and the update itself must equal
+    torch.optim.Adam's."""
+    cfg = O.default_model_cfg(dropout=0.0, TEXT=dict(embedding_size=128, n_head=4, n_encoder_layers=1),
+                              AUDIO=dict(embedding_size=64, n_head=4, n_encoder_layers=1), FAM=dict(embedding_size=64, n_head=4, n_layers=2),
+                              CLASSIFIER=dict(hidden_size=64, output_size=7, n_layers=2))
+    b = {k: v.cuda() for k, v in O.synth_inputs(5, 7, 128, 64).items()}
+    crit = torch.nn.CrossEntropyLoss(ignore_index=-1, label_smoothing=0.1)
+    model, _ = _build(P, cfg, planes=1)
+    twin, _ = _build(P, cfg, planes=1)
+    model.train(), twin.train()
+    opt = P.FusedAdam(model, lr=1e-3, weight_decay=0.01)
+    ref = torch.optim.Adam(twin.parameters(), lr=1e-3, weight_decay=0.01)
+    for _ in range(3):
+        for m, o in ((model, opt), (twin, ref)):
+            o.zero_grad()
+            crit(m(b["text"], b["audio"], b["padding_mask"]).permute(0, 2, 1), b["emotion"]).backward()
+            o.step()
+    assert model._shadow_version is not None  # the fused path ran (shadow stayed current)
+    rel = (torch.linalg.vector_norm(model.flat_parameters() - twin.flat_parameters()) / torch.linalg.vector_norm(twin.flat_parameters())).item()
+    assert rel < 1e-6, rel
+    model.eval()
+    with torch.inference_mode():
+        fused = model(b["text"], b["audio"], b["padding_mask"]).clone()
+        model._shadow_version = None  # force m2f_model_refresh_shadow
+        fresh = model(b["text"], b["audio"], b["padding_mask"])
+    assert torch.equal(fused, fresh)
