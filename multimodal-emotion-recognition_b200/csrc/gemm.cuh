@@ -52,7 +52,9 @@ struct EpiMaps {
     CUtensorMap gate;     // 2-D bf16 [M, N]
     CUtensorMap resid;    // 2-D fp32 [M, N]
 };
-constexpr int EPI2_WARP_BYTES = 20 * 1024;  // per epilogue warp: out f32 4K | out planes 3 x 2K | gate 2K | resid 4K | accumulate 4K
+// per epilogue warp; <= 1 output plane: 2 x out f32 4K | 2 x out plane 2K | gate 2K | resid 4K | accumulate 4K (22 K);
+// 2-3 planes: out f32 4K | out planes 3 x 2K | gate 2K | resid 4K | accumulate 4K (20 K)
+constexpr int EPI2_WARP_BYTES = 23 * 1024;
 
 // host helpers (gemm_sm100.cu)
 int make_planes_tmap(CUtensorMap* map, const m2f_planes_t* t, int box_rows);

@@ -231,17 +231,31 @@ __device__ __forceinline__ float4 lds128u(uint32_t addr) { return lds128(addr); 
 // hardware does the address arithmetic, the coalescing and the clipping at M / N.  Swizzled tiles keep the
 // "lane = row" shared-memory accesses conflict-free: 16-byte chunk j of row t sits at chunk j ^ (t & 7) (128-byte
 // rows, fp32) or j ^ ((t >> 1) & 3) (64-byte rows, bf16).
-template <int BLOCK_N, int EPI_WARPS>
+// FEAT: the epilogue's feature set as a compile-time mask for the combinations the training step launches most (the
+// feature tests then fold away: ~180 instead of ~330 instructions per 32x32 chunk), or -1 = decide everything at run time.
+enum : int { F_BIAS = 1, F_GATE = 2, F_DROP = 4, F_RES = 8, F_ACC = 16, F_OF32 = 32, F_OPL = 64, F_COLSUM = 128, F_RELU = 256, F_P1 = 512 };
+#define M2F_FEAT(bit, runtime) (FEAT < 0 ? (runtime) : ((FEAT & (bit)) != 0))
+
+template <int BLOCK_N, int EPI_WARPS, int FEAT>
 __device__ __forceinline__ void epilogue_tma(const GemmParams& p, const EpiMaps& em, uint8_t* smem, uint32_t s_bias, uint64_t* epi_bar,
                                              uint64_t* tmem_full_bar, uint32_t tmem_base, int warp, int lane, int m_blk, int n_blk) {
     const int lg = warp & 3, ew = warp - 2;
-    const uint32_t s_of = ptx::smem_u32(smem) + (uint32_t)(ew * EPI2_WARP_BYTES);
-    const uint32_t s_pl = s_of + 4096, s_gate = s_of + 10240, s_res = s_of + 12288, s_acc = s_of + 16384;
+    // staging of this warp: with at most one output plane the output tiles are double-buffered (a tile store's read of
+    // shared memory takes about as long as producing the next chunk), with 2-3 planes there is room for one set only
+    const uint32_t s_base = ptx::smem_u32(smem) + (uint32_t)(ew * EPI2_WARP_BYTES);
+    const bool f_bias = M2F_FEAT(F_BIAS, p.bias != nullptr), f_relu = M2F_FEAT(F_RELU, p.relu != 0);
+    const bool f_of32 = M2F_FEAT(F_OF32, p.out_f32 != nullptr), f_opl = M2F_FEAT(F_OPL, p.out_pl != nullptr);
+    const bool f_colsum = M2F_FEAT(F_COLSUM, p.colsum != nullptr), f_drop = M2F_FEAT(F_DROP, p.drop.enabled != 0);
+    const int n_pl = f_opl ? ((FEAT >= 0 && (FEAT & F_P1)) ? 1 : p.out_pl_n) : 0;
+    const bool dbl = n_pl <= 1;
+    const uint32_t s_pl0 = s_base + (dbl ? 8192u : 4096u);
+    const uint32_t s_gate = s_base + (dbl ? 12288u : 10240u), s_res = s_gate + 2048u, s_acc = s_res + 4096u;
     uint64_t* bar = &epi_bar[ew];
     const int m0 = m_blk * BLOCK_M + lg * 32;
     const int nt0 = n_blk * BLOCK_N;
     const bool rows_live = m0 < p.M;
-    const bool has_gate = p.gate != nullptr, has_res = p.resid != nullptr, has_acc = p.accumulate && p.out_f32;
+    const bool has_gate = M2F_FEAT(F_GATE, p.gate != nullptr), has_res = M2F_FEAT(F_RES, p.resid != nullptr);
+    const bool has_acc = M2F_FEAT(F_ACC, p.accumulate && p.out_f32);
     const uint32_t in_bytes = (has_gate ? 2048u : 0u) + (has_res ? 4096u : 0u) + (has_acc ? 4096u : 0u);
     constexpr int CSTEP = EPI_WARPS / 4;
     const int c_first = ew >> 2;
@@ -255,7 +269,7 @@ __device__ __forceinline__ void epilogue_tma(const GemmParams& p, const EpiMaps&
         }
     };
     // bias of this CTA's columns -> shared (read back as broadcasts); its own region: the operand ring is still live
-    if (p.bias) {
+    if (f_bias) {
         for (int i = (warp - 2) * 32 + lane; i < BLOCK_N; i += EPI_WARPS * 32) {
             const int n = nt0 + i;
             const float b = n < p.N ? p.bias[n] : 0.f;
@@ -263,14 +277,13 @@ __device__ __forceinline__ void epilogue_tma(const GemmParams& p, const EpiMaps&
         }
     }
     const Drop drop = drop_resolve(p.drop);
-    const float floor_ = p.relu ? 0.f : -INFINITY;
-    ptx::named_bar_sync(1, EPI_WARPS * 32);  // bias visible to every epilogue warp
+    if (f_bias) ptx::named_bar_sync(1, EPI_WARPS * 32);  // bias visible to every epilogue warp
     ptx::mbar_wait(tmem_full_bar, 0);
     ptx::tcgen05_fence_after();
     if (threadIdx.x == 64) M2F_TRACE(4);
     if (!rows_live) return;
     issue_loads(c_first);  // the ring is free from here on: it becomes the staging area
-    uint32_t phase = 0;
+    uint32_t phase = 0, buf = 0;
     const int row = m0 + lane;
     const uint32_t sw128 = (uint32_t)(lane & 7), sw64 = (uint32_t)((lane >> 1) & 3);
 #pragma unroll 1
@@ -285,15 +298,17 @@ __device__ __forceinline__ void epilogue_tma(const GemmParams& p, const EpiMaps&
 #pragma unroll
             for (int j = 0; j < 32; ++j) x[j] = __uint_as_float(r[j]);
         }
-        if (p.bias) {
+        if (f_bias) {
 #pragma unroll
             for (int j = 0; j < 8; ++j) {
                 const float4 b = lds128u(s_bias + (uint32_t)(c * 32 + j * 4) * 4u);
                 x[4 * j] += b.x; x[4 * j + 1] += b.y; x[4 * j + 2] += b.z; x[4 * j + 3] += b.w;
             }
         }
+        if (f_relu) {
 #pragma unroll
-        for (int j = 0; j < 32; ++j) x[j] = fmaxf(x[j], floor_);
+            for (int j = 0; j < 32; ++j) x[j] = fmaxf(x[j], 0.f);
+        }
         if (in_bytes) {
             ptx::mbar_wait(bar, phase);
             phase ^= 1;
@@ -311,7 +326,7 @@ __device__ __forceinline__ void epilogue_tma(const GemmParams& p, const EpiMaps&
                 }
             }
         }
-        if (drop.enabled) {
+        if (f_drop) {
             const uint64_t base4 = (uint64_t)((int64_t)row * p.drop_ld + n0) >> 2;
 #pragma unroll
             for (int j = 0; j < 8; ++j) {
@@ -336,26 +351,31 @@ __device__ __forceinline__ void epilogue_tma(const GemmParams& p, const EpiMaps&
         }
         __syncwarp();                                   // every lane has consumed the input tiles
         if (c + CSTEP < BLOCK_N / 32) issue_loads(c + CSTEP);
-        if (lane == 0) ptx::bulk_wait_read0();          // the previous chunk's stores have read their staging tiles
+        const uint32_t s_of = s_base + buf * 4096u, s_pl = s_pl0 + buf * 2048u;
+        if (lane == 0) {  // the stores that last used this staging set have read it
+            if (dbl) ptx::bulk_wait_read1();
+            else ptx::bulk_wait_read0();
+        }
+        if (dbl) buf ^= 1u;
         __syncwarp();
-        if (p.colsum && row >= p.M) {
+        if (f_colsum && row >= p.M) {
 #pragma unroll
             for (int j = 0; j < 32; ++j) x[j] = 0.f;    // rows past M are clipped on store but must not reach the column sums
         }
-        if (p.out_f32 || p.colsum) {
+        if (f_of32 || f_colsum) {
 #pragma unroll
             for (int j = 0; j < 8; ++j)
                 sts128(s_of + (uint32_t)lane * 128u + (((uint32_t)j ^ sw128) << 4), __float_as_uint(x[4 * j]), __float_as_uint(x[4 * j + 1]),
                        __float_as_uint(x[4 * j + 2]), __float_as_uint(x[4 * j + 3]));
         }
-        if (p.out_pl) {
-            for (int pl = 0; pl < p.out_pl_n; ++pl) {
+        if (f_opl) {
+            for (int pl = 0; pl < n_pl; ++pl) {
                 uint32_t h[16];
 #pragma unroll
                 for (int j = 0; j < 16; ++j) {
                     const __nv_bfloat162 b2 = __floats2bfloat162_rn(x[2 * j], x[2 * j + 1]);
                     h[j] = *reinterpret_cast<const uint32_t*>(&b2);
-                    if (pl + 1 < p.out_pl_n) {
+                    if (pl + 1 < n_pl) {
                         x[2 * j] -= __low2float(b2);
                         x[2 * j + 1] -= __high2float(b2);
                     }
@@ -369,12 +389,12 @@ __device__ __forceinline__ void epilogue_tma(const GemmParams& p, const EpiMaps&
         ptx::fence_proxy_async();
         __syncwarp();
         if (lane == 0) {
-            if (p.out_f32) ptx::tma_store_2d(&em.out_f32, s_of, n0, m0);
-            if (p.out_pl)
-                for (int pl = 0; pl < p.out_pl_n; ++pl) ptx::tma_store_3d(&em.out_pl, s_pl + (uint32_t)pl * 2048u, n0, m0, pl);
+            if (f_of32) ptx::tma_store_2d(&em.out_f32, s_of, n0, m0);
+            if (f_opl)
+                for (int pl = 0; pl < n_pl; ++pl) ptx::tma_store_3d(&em.out_pl, s_pl + (uint32_t)pl * 2048u, n0, m0, pl);
             ptx::bulk_commit();
         }
-        if (p.colsum) {  // bias gradient: lane j sums column j of the staged fp32 tile (planes were taken from the same values)
+        if (f_colsum) {  // bias gradient: lane j sums column j of the staged fp32 tile (planes were taken from the same values)
             float cs = 0.f;
             const uint32_t cj = (uint32_t)(lane >> 2), wj = (uint32_t)(lane & 3) * 4u;
 #pragma unroll
@@ -568,7 +588,28 @@ gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ C
         __syncwarp();
     } else if (p.epi_tma) {
         // ------------------------------------------------------------------ epilogue, TMA tiles in and out
-        epilogue_tma<BLOCK_N, Cfg::EPI_WARPS>(p, em, smem, (ptx::smem_u32(epi_bar + 8) + 15u) & ~15u, epi_bar, tmem_full_bar, tmem_base, warp, lane, m_blk, n_blk);
+        const uint32_t s_bias = (ptx::smem_u32(epi_bar + 8) + 15u) & ~15u;
+        const int feat = (p.bias ? F_BIAS : 0) | (p.gate ? F_GATE : 0) | (p.drop.enabled ? F_DROP : 0) | (p.resid ? F_RES : 0) |
+                         ((p.accumulate && p.out_f32) ? F_ACC : 0) | (p.out_f32 ? F_OF32 : 0) | (p.out_pl ? F_OPL : 0) |
+                         (p.colsum ? F_COLSUM : 0) | (p.relu ? F_RELU : 0) | ((p.out_pl && p.out_pl_n == 1) ? F_P1 : 0);
+#define M2F_EPI_CASE(MASK)                                                                                                            \
+    case (MASK):                                                                                                                      \
+        epilogue_tma<BLOCK_N, Cfg::EPI_WARPS, (MASK)>(p, em, smem, s_bias, epi_bar, tmem_full_bar, tmem_base, warp, lane, m_blk, n_blk); \
+        break;
+        switch (feat) {  // warp-uniform
+            M2F_EPI_CASE(F_OF32)                                             // weight gradients
+            M2F_EPI_CASE(F_BIAS | F_OPL | F_P1)                              // QKV / K / QV projections
+            M2F_EPI_CASE(F_BIAS | F_DROP | F_RES | F_OF32)                   // attention out-projection, FFN2 (pre-LN sums)
+            M2F_EPI_CASE(F_BIAS | F_RELU | F_DROP | F_OPL | F_P1)            // FFN1, fusion linear
+            M2F_EPI_CASE(F_GATE | F_OPL | F_P1 | F_COLSUM)                   // d(hidden) through ReLU / dropout
+            M2F_EPI_CASE(F_RES | F_OF32)                                     // data gradients joining a skip path
+            M2F_EPI_CASE(F_OPL | F_P1)                                       // d(attention output)
+            M2F_EPI_CASE(F_BIAS | F_RELU | F_OPL | F_P1)                     // fusion out-projection; FFN1 without dropout (eval)
+            M2F_EPI_CASE(F_BIAS | F_RES | F_OF32)                            // out-projection / FFN2 without dropout (eval)
+            default:
+                epilogue_tma<BLOCK_N, Cfg::EPI_WARPS, -1>(p, em, smem, s_bias, epi_bar, tmem_full_bar, tmem_base, warp, lane, m_blk, n_blk);
+        }
+#undef M2F_EPI_CASE
         ptx::tcgen05_fence_before();
     } else {
         // ------------------------------------------------------------------ epilogue, pointer path (ragged / unaligned operands)

@@ -14,7 +14,7 @@ M, N, K = (int(x) for x in sys.argv[1:4])
 mode = sys.argv[4] if len(sys.argv) > 4 else "tn"
 g = torch.Generator(device="cuda").manual_seed(1)
 kw = {}
-if mode == "tn":
+if mode in ("tn", "ffn1"):
     A = ops.PlanesTensor.from_float(torch.randn(M, K, generator=g, device="cuda"), 1)
     Bm = ops.PlanesTensor.from_float(torch.randn(N, K, generator=g, device="cuda"), 1)
 elif mode == "dgrad":
@@ -26,15 +26,18 @@ else:
     Bm = ops.PlanesTensor.from_float(torch.randn(K, N, generator=g, device="cuda"), 1)
     kw = dict(a_mn=True, b_mn=True)
 out = torch.empty(M, N, device="cuda")
+okw = dict(out_f32=out)
+if mode == "ffn1":  # bias + ReLU + bf16 planes output (the FFN1 epilogue)
+    okw = dict(bias=torch.zeros(N, device="cuda"), relu=True, out_planes=ops.PlanesTensor.empty(M, N, 1, "cuda"))
 for _ in range(5):
-    ops.gemm(A, Bm, M, N, out_f32=out, **kw)
+    ops.gemm(A, Bm, M, N, **okw, **kw)
 torch.cuda.synchronize()
 tr = torch.zeros(2 * 4096 * 8, dtype=torch.int64, device="cuda")
 L = ctypes.CDLL(pkg._lib.LIB_PATH)
 L.m2f_debug_set_gemm_trace.argtypes = [ctypes.c_void_p]
 L.m2f_debug_set_gemm_flags(int(os.environ.get("M2F_GEMM_DBG", "0")))
 L.m2f_debug_set_gemm_trace(tr.data_ptr())
-ops.gemm(A, Bm, M, N, out_f32=out, **kw)
+ops.gemm(A, Bm, M, N, **okw, **kw)
 torch.cuda.synchronize()
 L.m2f_debug_set_gemm_trace(None)
 t2 = tr.cpu()[4096 * 8:].reshape(-1, 8)
