@@ -239,6 +239,27 @@ int m2f_model_adam_step(const m2f_model_t* m, float* params, const float* grads,
                         void* shadow, float lr, float beta1, float beta2, float eps, float weight_decay, int64_t t,
                         float grad_scale, void* stream);
 
+/* ---- either side of the step ---------------------------------------------------
+ * Batch assembly on the device, replacing Dataset.__getitem__ + collate_fn + apply_padding
+ * (src/dataset.py:32-65,71-89; src/utils.py:15-31).  The embedding tables stay resident in HBM: text_table
+ * fp32 [n_rows, Dt] (row stride text_ld), audio_table fp32 [n_rows, Da], labels int64 [n_rows] (one per CSV row).
+ * Dialogue d owns utt_rows[dlg_offsets[d] .. dlg_offsets[d+1]) = its table rows sorted by Utterance_ID.
+ * batch_dialogues int64 [B] picks the dialogues.  Outputs (contiguous): text_out [B,S,Dt] and audio_out [B,S,Da]
+ * padded with 0, emotion_out int64 [B,S] padded with -1, mask_out uint8 [B,S] = (emotion == -1).  All pointers
+ * are device pointers; the caller guarantees S >= every selected dialogue's length (longer ones are truncated). */
+int m2f_collate_dialogues(const float* text_table, int64_t text_ld, int32_t Dt, const float* audio_table,
+                          int64_t audio_ld, int32_t Da, const int64_t* labels, const int64_t* utt_rows,
+                          const int64_t* dlg_offsets, const int64_t* batch_dialogues, int64_t B, int64_t S,
+                          float* text_out, float* audio_out, int64_t* emotion_out, uint8_t* mask_out, void* stream);
+
+/* Per-batch accuracy_score and f1_score(average='weighted') of src/test.py:65-71 / src/train.py:262-267 without the
+ * per-batch device->host copy: argmax over the C logits of each row (first maximum), confusion int32 [C*C]
+ * (overwritten; row = true class, column = predicted) over rows whose target != ignore_index, then
+ * sums[0] += accuracy, sums[1] += weighted F1, sums[2] += 1 (double[3], accumulated across calls: the reference
+ * averages the per-batch scores over the batches).  pred (nullable) int64 [M] receives the argmax.  C <= 32. */
+int m2f_batch_metrics(const float* logits, int64_t ld, const int64_t* target, int64_t M, int32_t C,
+                      int64_t ignore_index, int32_t* confusion, double* sums, int64_t* pred, void* stream);
+
 /* test helper: mask[i] = 1 if element i of `site` is kept, for i in [0, n) */
 int m2f_dropout_mask(float p, uint64_t seed, uint64_t step, uint32_t site, int64_t n, uint8_t* mask,
                      void* stream);

@@ -87,6 +87,8 @@ PROTOTYPES = {
     "m2f_plan_backward_bucketed": [_vp, _vp, _vp, _vp, _vp, _vp, _i64, _vp, _vp, _vp],
     "m2f_adam_step": [_vp, _vp, _vp, _vp, _i64, _f32, _f32, _f32, _f32, _f32, _i64, _f32, _vp],
     "m2f_model_adam_step": [_vp, _vp, _vp, _vp, _vp, _vp, _f32, _f32, _f32, _f32, _f32, _i64, _f32, _vp],
+    "m2f_collate_dialogues": [_vp, _i64, _i32, _vp, _i64, _i32, _vp, _vp, _vp, _vp, _i64, _i64, _vp, _vp, _vp, _vp, _vp],
+    "m2f_batch_metrics": [_vp, _i64, _vp, _i64, _i32, _i64, _vp, _vp, _vp, _vp],
 }
 
 # functions that return a 64-bit count instead of an error code

@@ -214,10 +214,10 @@ attn_bwd_kernel(PlanesView q, PlanesView k, PlanesView v, PlanesView d_o, const 
 namespace amma {
 int fwd_p1(AMMA_FWD_ARGS); int fwd_p2(AMMA_FWD_ARGS); int fwd_p3(AMMA_FWD_ARGS);
 int bwd_p1(AMMA_BWD_ARGS); int bwd_p2(AMMA_BWD_ARGS); int bwd_p3(AMMA_BWD_ARGS);
-// attention_mma_long.cu: forward only, one plane, no probability dropout, 64 < S <= 256 (online softmax over key tiles)
+// attention_mma_long.cu: forward only, no probability dropout, 64 < S <= 256 (online softmax over key tiles)
 bool long_supported(int hd, int64_t S);
-int fwd_long_p1(int hd, const View& q, const View& k, const View& v, const uint8_t* pad, int64_t BH, int S, int H, float scale, const OutView& o,
-                cudaStream_t st);
+int fwd_long(int hd, int P, const View& q, const View& k, const View& v, const uint8_t* pad, int64_t BH, int S, int H, float scale,
+             const OutView& o, cudaStream_t st);
 static bool supported(int hd, int64_t S) { return S <= 64 && (hd == 16 || hd == 32 || hd == 64 || hd == 96 || hd == 128); }
 // 16-byte row chunks: base, leading dimension, plane stride and the head's first column must be multiples of 8 elements
 static bool aligned16(const m2f_planes_t* t) {
@@ -273,12 +273,12 @@ extern "C" int m2f_attn_fwd(const m2f_planes_t* q, const m2f_planes_t* k, const 
         auto fn = q->planes == 1 ? amma::fwd_p1 : (q->planes == 2 ? amma::fwd_p2 : amma::fwd_p3);
         return fn(hd, SPv, aq, ak, av, key_pad, B * H, (int)S, H, sc, dropm, ao, st);
     }
-    if (q->planes == 1 && drop_p == 0.f && amma::long_supported(hd, S) && amma::aligned16(q) && amma::aligned16(k) && amma::aligned16(v) &&
+    if (drop_p == 0.f && amma::long_supported(hd, S) && amma::aligned16(q) && amma::aligned16(k) && amma::aligned16(v) &&
         amma::aligned16(o)) {
-        // long dialogues at inference: K/V of the dialogue in shared memory, online softmax over 64-key tiles
+        // long dialogues at inference: K/V tiles through shared memory, online softmax over 64-key tiles
         const amma::View aq{vq.ptr, vq.ld, vq.stride}, ak{vk.ptr, vk.ld, vk.stride}, av{vv.ptr, vv.ld, vv.stride};
         const amma::OutView ao{const_cast<__nv_bfloat16*>(vo.ptr), vo.ld, vo.stride};
-        return amma::fwd_long_p1(hd, aq, ak, av, key_pad, B * H, (int)S, H, 1.f / sqrtf((float)hd), ao, reinterpret_cast<cudaStream_t>(stream));
+        return amma::fwd_long(hd, q->planes, aq, ak, av, key_pad, B * H, (int)S, H, 1.f / sqrtf((float)hd), ao, reinterpret_cast<cudaStream_t>(stream));
     }
     const int hd_pad = hd | 1;
     const size_t smem = sizeof(float) * ((size_t)2 * S * hd_pad + ATT_WARPS * hd_pad + ATT_WARPS * S);

@@ -57,15 +57,3 @@ def test_synthetic_loader_layout_matches_collate_fn(pkg):
     assert (b["emotion"][b["padding_mask"]] == -1).all() and (b["emotion"][~b["padding_mask"]] >= 0).all()
     assert (b["text"][b["padding_mask"]] == 0).all() and (~b["padding_mask"]).any(dim=1).all()
 
-
-def test_device_metrics_equal_sklearn(pkg):
-    from sklearn.metrics import accuracy_score, f1_score
-    D = __import__("importlib").import_module(PKG_NAME + ".data")
-    g = torch.Generator().manual_seed(3)
-    logits = torch.randn(6, 9, 7, generator=g)
-    tgt = torch.randint(0, 7, (6, 9), generator=g)
-    tgt[1, 4:] = -1
-    acc, f1 = D.batch_metrics_device(logits, tgt)
-    m = tgt != -1
-    y, yp = tgt[m].numpy(), logits.argmax(-1)[m].numpy()
-    assert abs(acc - accuracy_score(y, yp)) < 1e-12 and abs(f1 - f1_score(y, yp, average="weighted")) < 1e-12
