@@ -39,7 +39,9 @@ def parse():
     ap.add_argument("--seq", type=int, default=33)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
-    ap.add_argument("--bucket-mb", type=float, default=128.0)
+    ap.add_argument("--bucket-mb", type=float, default=None, help="gradient bucket size (default: 32 for the peer exchange, 128 for NCCL)")
+    ap.add_argument("--exchange", default=None, choices=["auto", "peer", "nccl"],
+                    help="gradient exchange at N > 1: NVSwitch peer-memory kernel or NCCL buckets (default: $M2F_EXCHANGE or auto)")
     return ap.parse_args()
 
 
@@ -177,7 +179,7 @@ def main():
     cfg = D.default_model_config()  # src/config.yaml defaults, dropout 0.4
     torch.manual_seed(0)
     model = pkg.M2FNet(cfg, planes=planes).to(dev).train()
-    net = pkg.DataParallelM2FNet(model, bucket_mb=args.bucket_mb) if world > 1 else model
+    net = pkg.DataParallelM2FNet(model, bucket_mb=args.bucket_mb, exchange=args.exchange) if world > 1 else model
     crit = pkg.FusedCrossEntropyLoss().to(dev)
     opt = pkg.FusedAdam(model, lr=5e-5, weight_decay=0.01)
 
@@ -281,10 +283,17 @@ def main():
         cpu = cpu_baseline()
 
     if rank == 0:
+        cfg_out = workload_config(args, world)
+        if world > 1:
+            cfg_out["exchange"] = ("gradient all-reduce: m2f_grad_allreduce_peer over NVSwitch " +
+                                   ("multicast (multimem.ld_reduce / multimem.st)" if getattr(net.reducer, "multicast", False) else "peer loads / stores")
+                                   if net.exchange == "peer" else "gradient all-reduce: NCCL, async buckets behind the backward")
+            cfg_out["bucket_mb"] = net.bucket_mb
+            cfg_out["exchange_calls_per_step"] = len(net.reducer.log)
         out = {"metric": "M2FNet train utterances/sec", "value": value, "unit": "utterances/s", "n_gpus": world,
                "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms / args.steps, "higher_is_better": True,
                "scaling": "weak", "vs_baseline": None, "dtype": "bf16" if planes == 1 else "f32 (3 x bf16 planes)",
-               "data": "synthetic", "config": workload_config(args, world), "clocks": clocks, "e2e": e2e,
+               "data": "synthetic", "config": cfg_out, "clocks": clocks, "e2e": e2e,
                "gpu_launches": launches, "roofline": roof, "cpu_baseline": cpu}
         print(json.dumps(out))
     if world > 1:

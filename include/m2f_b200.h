@@ -227,6 +227,32 @@ int m2f_plan_backward_bucketed(m2f_plan_t* p, const float* params, const void* s
                                const float* dlogits, float* grads, int64_t bucket_floats, m2f_bucket_cb cb, void* user,
                                void* stream);
 
+/* ---- gradient exchange over NVLink / NVSwitch peer memory -------------------------------------
+ * The reference trains on one device (src/train.py:20); the data-parallel path adds exactly one exchange between
+ * loss.backward() (src/train.py:230) and optimizer.step() (src/train.py:231): the all-reduce of the gradient arena.
+ * Here it is one kernel over a *symmetric* gradient buffer: the same allocation mapped on every GPU of the node
+ * (peer_base[r] = rank r's copy as seen from this GPU, own copy included) and, where the fabric offers it, through an
+ * NVSwitch multicast object (mc_base, else NULL).  The host obtains both mappings from its symmetric-memory allocator
+ * (torch.distributed._symmetric_memory: buffer_ptrs / multicast_ptr); the library only consumes the addresses.
+ * `signal_off_bytes` locates M2F_XCHG_MAX_CTAS x M2F_XCHG_MAX_RANKS uint32 barrier words inside the buffer, behind
+ * the gradients, zeroed once before the first call (and after any aborted one). */
+#define M2F_XCHG_MAX_RANKS 16
+#define M2F_XCHG_MAX_CTAS 64
+#define M2F_XCHG_SIGNAL_BYTES (M2F_XCHG_MAX_CTAS * M2F_XCHG_MAX_RANKS * 4)
+typedef struct {
+    void* mc_base;                        /* multicast mapping of the buffer (multimem.ld_reduce / multimem.st), or NULL */
+    void* peer_base[M2F_XCHG_MAX_RANKS];  /* unicast mapping of every rank's buffer; entries >= world are ignored */
+    int64_t signal_off_bytes;
+    int32_t rank, world;
+} m2f_peer_group_t;
+
+/* In-place all-reduce of the float range [lo, hi) of the symmetric buffer: on return of the *kernel* every rank holds
+ * scale * sum over ranks.  Two-shot: rank r reduces slice r (in the switch with multicast, by world peer loads without)
+ * and writes it to every rank.  Stream-ordered; every rank must issue the same sequence of calls (same lo, hi, ctas)
+ * and have one GPU to itself -- the kernels of the ranks wait for each other.  ctas <= 0 picks the default (32).
+ * With world == 1 it degenerates to an in-place scale (used by the single-GPU tests of the slicing arithmetic). */
+int m2f_grad_allreduce_peer(const m2f_peer_group_t* g, int64_t lo, int64_t hi, float scale, int32_t ctas, void* stream);
+
 /* Adam with L2 weight decay folded into the gradient (torch.optim.Adam semantics, src/train.py:56,231), one
  * launch over the arena; `t` is the 1-based step count.  grad_scale multiplies g first (DDP averaging). */
 int m2f_adam_step(float* params, const float* grads, float* exp_avg, float* exp_avg_sq, int64_t n, float lr,

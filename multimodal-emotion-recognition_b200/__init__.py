@@ -8,6 +8,6 @@ from .model import FusedCrossEntropyLoss, FusionAttentionModule, M2FNet  # noqa:
 
 __all__ = ["_lib", "ops", "M2FNet", "FusionAttentionModule", "FusedCrossEntropyLoss"]
 from .optim import FusedAdam  # noqa: F401,E402
-from .parallel import DataParallelM2FNet, GradBucketReducer, shard_range  # noqa: F401,E402
+from .parallel import DataParallelM2FNet, GradBucketReducer, PeerGradExchange, shard_range  # noqa: F401,E402
 
-__all__ += ["FusedAdam", "DataParallelM2FNet", "GradBucketReducer", "shard_range"]
+__all__ += ["FusedAdam", "DataParallelM2FNet", "GradBucketReducer", "PeerGradExchange", "shard_range"]

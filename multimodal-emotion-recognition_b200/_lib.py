@@ -13,6 +13,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(HERE, "libm2f_b200.so")
 
 M2F_OK = 0
+M2F_ERR_ARG, M2F_ERR_UNSUPPORTED, M2F_ERR_CUDA, M2F_ERR_ALIGN = -1, -2, -3, -4
 
 
 class Planes(C.Structure):
@@ -46,6 +47,16 @@ class ModelCfg(C.Structure):
     _fields_ = [("audio", ModalityCfg), ("text", ModalityCfg), ("fam_enabled", C.c_int32), ("fam_dim", C.c_int32),
                 ("fam_heads", C.c_int32), ("fam_layers", C.c_int32), ("cls_hidden", C.c_int32), ("cls_out", C.c_int32),
                 ("cls_layers", C.c_int32), ("dropout", C.c_float), ("ffn_dim", C.c_int32), ("planes", C.c_int32)]
+
+
+XCHG_MAX_RANKS, XCHG_MAX_CTAS = 16, 64
+XCHG_SIGNAL_BYTES = XCHG_MAX_CTAS * XCHG_MAX_RANKS * 4
+
+
+class PeerGroup(C.Structure):
+    """m2f_peer_group_t"""
+    _fields_ = [("mc_base", C.c_void_p), ("peer_base", C.c_void_p * XCHG_MAX_RANKS), ("signal_off_bytes", C.c_int64),
+                ("rank", C.c_int32), ("world", C.c_int32)]
 
 
 BUCKET_CB = C.CFUNCTYPE(None, C.c_void_p, C.c_int64, C.c_int64, C.c_void_p)  # m2f_bucket_cb
@@ -85,6 +96,7 @@ PROTOTYPES = {
     "m2f_plan_loss": [_vp, _vp, _vp, _vp, _vp, _f32, _f32, _vp, _vp],
     "m2f_plan_backward": [_vp, _vp, _vp, _vp, _vp, _vp, _vp],
     "m2f_plan_backward_bucketed": [_vp, _vp, _vp, _vp, _vp, _vp, _i64, _vp, _vp, _vp],
+    "m2f_grad_allreduce_peer": [C.POINTER(PeerGroup), _i64, _i64, _f32, _i32, _vp],
     "m2f_adam_step": [_vp, _vp, _vp, _vp, _i64, _f32, _f32, _f32, _f32, _f32, _i64, _f32, _vp],
     "m2f_model_adam_step": [_vp, _vp, _vp, _vp, _vp, _vp, _f32, _f32, _f32, _f32, _f32, _i64, _f32, _vp],
     "m2f_collate_dialogues": [_vp, _i64, _i32, _vp, _i64, _i32, _vp, _vp, _vp, _vp, _i64, _i64, _vp, _vp, _vp, _vp, _vp],

@@ -1,0 +1,216 @@
+// Gradient exchange of the data-parallel step as one kernel over NVLink 5 / NVSwitch peer memory.
+//
+// The reference has no multi-GPU path (src/train.py:20 pins cuda:0); the exchange the sharded hot path needs is the
+// all-reduce of the gradient arena between the backward (src/train.py:230) and optimizer.step() (src/train.py:231).
+//
+// Every rank's gradient arena lives in a *symmetric* allocation: the same buffer is mapped on every GPU (peer_base[r])
+// and, where the fabric supports it, once more through an NVSwitch multicast object (mc_base).  A range [lo, hi) is
+// reduced in two shots by a few CTAs per GPU:
+//   1. barrier: block b of every rank has started  => every rank's producers of the range have completed
+//   2. rank r owns slice r of the range: `multimem.ld_reduce.add.v4.f32` returns the sum over all GPUs computed *inside
+//      the switch* (one load, one NVLink response), the sum is scaled (1/world) and `multimem.st` writes it back to every
+//      GPU through the same multicast mapping.  Without multicast: world peer loads + world peer stores per element.
+//   3. barrier: block b of every rank has stored  => when the kernel has completed on a rank, all of its range is final.
+// Per GPU and step that is arena/world bytes pulled and arena/world pushed by SMs; the switch does the fan-in / fan-out,
+// which is why 16-32 CTAs are enough and the kernel can run beside the backward's GEMMs (NCCL's ring / tree kernels
+// compete with them for SMs and L2).
+//
+// Barrier words: uint32 [M2F_XCHG_MAX_CTAS][M2F_XCHG_MAX_RANKS] at signal_off_bytes inside the symmetric buffer, zero
+// before the first call.  Slot (b, s) on rank d is written by rank s only: put = CAS 0 -> 1 (release, system scope, spins
+// while the previous signal has not been consumed), wait = CAS 1 -> 0 (acquire) on the local copy; the protocol resets
+// itself, so calls can follow each other (and be replayed from CUDA graphs) without host involvement.
+#include <stdio.h>
+
+#include "common.cuh"
+
+namespace m2f {
+
+struct PeerPtrs {
+    float* base[M2F_XCHG_MAX_RANKS];
+    uint32_t* sig[M2F_XCHG_MAX_RANKS];
+};
+
+__device__ __forceinline__ uint64_t gtimer() {
+    uint64_t t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+
+__device__ __forceinline__ uint32_t cas_release_sys(uint32_t* a, uint32_t cmp, uint32_t val) {
+    uint32_t old;
+    asm volatile("atom.global.release.sys.cas.b32 %0, [%1], %2, %3;" : "=r"(old) : "l"(a), "r"(cmp), "r"(val) : "memory");
+    return old;
+}
+__device__ __forceinline__ uint32_t cas_acquire_sys(uint32_t* a, uint32_t cmp, uint32_t val) {
+    uint32_t old;
+    asm volatile("atom.global.acquire.sys.cas.b32 %0, [%1], %2, %3;" : "=r"(old) : "l"(a), "r"(cmp), "r"(val) : "memory");
+    return old;
+}
+
+// A peer that never arrives (crashed rank, mismatched call sequence) must not hang the GPU: give up after ~20 s.
+constexpr uint64_t XCHG_TIMEOUT_NS = 20ull * 1000 * 1000 * 1000;
+
+// All threads of the block call this.  Threads [0, world) each handshake with one peer.
+__device__ __forceinline__ void block_barrier_all_ranks(const PeerPtrs& pp, int rank, int world) {
+    __syncthreads();  // the block's earlier global writes happen-before the release below (cumulativity through bar.sync)
+    const int t = threadIdx.x;
+    if (t < world) {
+        const int slot_base = blockIdx.x * M2F_XCHG_MAX_RANKS;
+        const uint64_t t0 = gtimer();
+        uint32_t* theirs = pp.sig[t] + slot_base + rank;  // my slot on peer t
+        while (cas_release_sys(theirs, 0u, 1u) != 0u) {
+            if (gtimer() - t0 > XCHG_TIMEOUT_NS) {
+                printf("m2f exchange: rank %d block %d timed out signalling rank %d\n", rank, (int)blockIdx.x, t);
+                asm volatile("trap;");
+            }
+        }
+        uint32_t* mine = pp.sig[rank] + slot_base + t;  // peer t's slot on me
+        while (cas_acquire_sys(mine, 1u, 0u) != 1u) {
+            if (gtimer() - t0 > XCHG_TIMEOUT_NS) {
+                printf("m2f exchange: rank %d block %d timed out waiting for rank %d\n", rank, (int)blockIdx.x, t);
+                asm volatile("trap;");
+            }
+        }
+    }
+    __syncthreads();
+}
+
+__device__ __forceinline__ float4 mc_ld_reduce_v4(const float* mc) {
+    float4 v;
+    asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0,%1,%2,%3}, [%4];"
+                 : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(mc) : "memory");
+    return v;
+}
+__device__ __forceinline__ void mc_st_v4(float* mc, float4 v) {
+    asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(mc), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+}
+__device__ __forceinline__ float mc_ld_reduce_f32(const float* mc) {
+    float v;
+    asm volatile("multimem.ld_reduce.relaxed.sys.global.add.f32 %0, [%1];" : "=f"(v) : "l"(mc) : "memory");
+    return v;
+}
+__device__ __forceinline__ void mc_st_f32(float* mc, float v) {
+    asm volatile("multimem.st.relaxed.sys.global.f32 [%0], %1;" ::"l"(mc), "f"(v) : "memory");
+}
+__device__ __forceinline__ float4 peer_ld_v4(const float* p) {
+    float4 v;
+    asm volatile("ld.relaxed.sys.global.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void peer_st_v4(float* p, float4 v) {
+    asm volatile("st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(p), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+}
+__device__ __forceinline__ float peer_ld_f32(const float* p) {
+    float v;
+    asm volatile("ld.relaxed.sys.global.f32 %0, [%1];" : "=f"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void peer_st_f32(float* p, float v) { asm volatile("st.relaxed.sys.global.f32 [%0], %1;" ::"l"(p), "f"(v) : "memory"); }
+
+// float offsets: [lo, lo + head) scalar, then n4 float4, then `tail` scalars; head / tail < 4 (arena ranges that do not
+// start or end on 16 bytes, e.g. the 7-wide classifier bias at the end of the 1-D region)
+constexpr int XCHG_THREADS = 512;
+constexpr int XCHG_UNROLL = 4;
+
+template <bool MC>
+__global__ void __launch_bounds__(XCHG_THREADS)
+grad_allreduce_kernel(float* __restrict__ mc, PeerPtrs pp, int rank, int world, int64_t lo, int head, int64_t n4, int tail, float scale) {
+    block_barrier_all_ranks(pp, rank, world);
+
+    // the slice of the vector body this rank reduces, split over the blocks in contiguous runs of XCHG_UNROLL vectors per thread
+    const int64_t per_rank = (n4 + world - 1) / world;
+    const int64_t v_lo = min(n4, per_rank * rank), v_hi = min(n4, v_lo + per_rank);
+    const int64_t body = lo + head;  // float offset of vector 0
+    const int64_t stride = (int64_t)gridDim.x * XCHG_THREADS;
+    for (int64_t i0 = v_lo + blockIdx.x * (int64_t)XCHG_THREADS + threadIdx.x; i0 < v_hi; i0 += stride * XCHG_UNROLL) {
+        float4 acc[XCHG_UNROLL];
+#pragma unroll
+        for (int u = 0; u < XCHG_UNROLL; ++u) {
+            const int64_t i = i0 + u * stride;
+            if (i < v_hi) {
+                if (MC) {
+                    acc[u] = mc_ld_reduce_v4(mc + body + 4 * i);
+                } else {
+                    acc[u] = peer_ld_v4(pp.base[0] + body + 4 * i);
+                    for (int r = 1; r < world; ++r) {
+                        const float4 x = peer_ld_v4(pp.base[r] + body + 4 * i);
+                        acc[u].x += x.x; acc[u].y += x.y; acc[u].z += x.z; acc[u].w += x.w;
+                    }
+                }
+            }
+        }
+#pragma unroll
+        for (int u = 0; u < XCHG_UNROLL; ++u) {
+            const int64_t i = i0 + u * stride;
+            if (i < v_hi) {
+                float4 v = acc[u];
+                v.x *= scale; v.y *= scale; v.z *= scale; v.w *= scale;
+                if (MC) {
+                    mc_st_v4(mc + body + 4 * i, v);
+                } else {
+                    for (int r = 0; r < world; ++r) peer_st_v4(pp.base[r] + body + 4 * i, v);
+                }
+            }
+        }
+    }
+    // unaligned ends: a handful of scalars, done by the last rank's first block
+    if (rank == world - 1 && blockIdx.x == 0 && (int)threadIdx.x < head + tail) {
+        const int k = threadIdx.x;
+        const int64_t off = (k < head) ? lo + k : body + 4 * n4 + (k - head);
+        float v;
+        if (MC) {
+            v = mc_ld_reduce_f32(mc + off) * scale;
+            mc_st_f32(mc + off, v);
+        } else {
+            v = 0.f;
+            for (int r = 0; r < world; ++r) v += peer_ld_f32(pp.base[r] + off);
+            v *= scale;
+            for (int r = 0; r < world; ++r) peer_st_f32(pp.base[r] + off, v);
+        }
+    }
+    __threadfence_system();
+    block_barrier_all_ranks(pp, rank, world);
+}
+
+}  // namespace m2f
+
+using namespace m2f;
+
+extern "C" int m2f_grad_allreduce_peer(const m2f_peer_group_t* g, int64_t lo, int64_t hi, float scale, int32_t ctas, void* stream) {
+    M2F_REQUIRE(g != nullptr, M2F_ERR_ARG, "grad_allreduce_peer: group is NULL");
+    M2F_REQUIRE(g->world >= 1 && g->world <= M2F_XCHG_MAX_RANKS && g->rank >= 0 && g->rank < g->world, M2F_ERR_ARG,
+                "grad_allreduce_peer: rank %d / world %d outside [1, %d]", g->rank, g->world, M2F_XCHG_MAX_RANKS);
+    M2F_REQUIRE(lo >= 0 && hi >= lo, M2F_ERR_ARG, "grad_allreduce_peer: bad range [%lld, %lld)", (long long)lo, (long long)hi);
+    M2F_REQUIRE(g->signal_off_bytes >= hi * 4 && (g->signal_off_bytes % 16) == 0, M2F_ERR_ARG,
+                "grad_allreduce_peer: the signal area (offset %lld) must lie behind the reduced range and be 16-byte aligned",
+                (long long)g->signal_off_bytes);
+    if (hi == lo) return M2F_OK;
+    PeerPtrs pp;
+    for (int r = 0; r < M2F_XCHG_MAX_RANKS; ++r) {
+        pp.base[r] = nullptr;
+        pp.sig[r] = nullptr;
+    }
+    for (int r = 0; r < g->world; ++r) {
+        M2F_REQUIRE(g->peer_base[r] != nullptr, M2F_ERR_ARG, "grad_allreduce_peer: peer_base[%d] is NULL", r);
+        M2F_REQUIRE((reinterpret_cast<uintptr_t>(g->peer_base[r]) % 16) == 0, M2F_ERR_ALIGN, "grad_allreduce_peer: peer_base[%d] must be 16-byte aligned", r);
+        pp.base[r] = reinterpret_cast<float*>(g->peer_base[r]);
+        pp.sig[r] = reinterpret_cast<uint32_t*>(reinterpret_cast<uint8_t*>(g->peer_base[r]) + g->signal_off_bytes);
+    }
+    M2F_REQUIRE((reinterpret_cast<uintptr_t>(g->mc_base) % 16) == 0, M2F_ERR_ALIGN, "grad_allreduce_peer: mc_base must be 16-byte aligned");
+    const int head = (int)((4 - (lo & 3)) & 3) < (hi - lo) ? (int)((4 - (lo & 3)) & 3) : (int)(hi - lo);
+    const int64_t n4 = (hi - lo - head) / 4;
+    const int tail = (int)(hi - lo - head - 4 * n4);
+    // enough CTAs to keep a few hundred KB of loads in flight over the switch, few enough to leave the SMs to the backward;
+    // every rank must use the same count (the barrier slots are per block), so it depends on the range and `ctas` only
+    int grid = ctas > 0 ? ctas : 32;
+    if (grid > M2F_XCHG_MAX_CTAS) grid = M2F_XCHG_MAX_CTAS;
+    const int64_t per_rank = (n4 + g->world - 1) / g->world;
+    const int64_t need = (per_rank + XCHG_THREADS * XCHG_UNROLL - 1) / (XCHG_THREADS * XCHG_UNROLL);
+    if (need < grid) grid = need < 1 ? 1 : (int)need;
+    cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+    float* mc = reinterpret_cast<float*>(g->mc_base);
+    if (mc) grad_allreduce_kernel<true><<<grid, XCHG_THREADS, 0, st>>>(mc, pp, g->rank, g->world, lo, head, n4, tail, scale);
+    else    grad_allreduce_kernel<false><<<grid, XCHG_THREADS, 0, st>>>(nullptr, pp, g->rank, g->world, lo, head, n4, tail, scale);
+    M2F_LAUNCH_CHECK();
+    return M2F_OK;
+}

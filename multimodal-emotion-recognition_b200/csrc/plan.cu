@@ -245,6 +245,7 @@ struct m2f_plan {
         }
     } gf, gb;
     std::vector<cudaEvent_t> bucket_evs;     // recorded by event nodes of the backward graph, one per reported range
+    std::vector<cudaEvent_t> stack_evs;      // "weight gradients of this stack down to here are enqueued" (interleaved stack reports)
     cudaStream_t cap = nullptr;
     unsigned long long* rng_dev = nullptr;   // {seed, step} read by the dropout kernels of the captured graphs
     int use_graph = 1;
@@ -253,7 +254,11 @@ struct m2f_plan {
     int ensure_streams() {
         if (aux[0]) return M2F_OK;
         for (int i = 0; i < 3; ++i) M2F_CUDA(cudaStreamCreateWithFlags(&aux[i], cudaStreamNonBlocking));
-        M2F_CUDA(cudaStreamCreateWithFlags(&ready, cudaStreamNonBlocking));
+        {   // the exchange launched behind `ready` is a few CTAs that should start as soon as their range is final
+            int lo_prio = 0, hi_prio = 0;
+            M2F_CUDA(cudaDeviceGetStreamPriorityRange(&lo_prio, &hi_prio));
+            M2F_CUDA(cudaStreamCreateWithPriority(&ready, cudaStreamNonBlocking, hi_prio));
+        }
         M2F_CUDA(cudaStreamCreateWithFlags(&cap, cudaStreamNonBlocking));
         M2F_CUDA(cudaMalloc(&rng_dev, 2 * sizeof(unsigned long long)));
         evs.resize(128);
@@ -275,6 +280,8 @@ struct m2f_plan {
         gb.reset();
         for (auto& e : bucket_evs) cudaEventDestroy(e);
         bucket_evs.clear();
+        for (auto& e : stack_evs) cudaEventDestroy(e);
+        stack_evs.clear();
         if (rng_dev) { cudaFree(rng_dev); rng_dev = nullptr; }
         if (tl_dev) { cudaFree(tl_dev); tl_dev = nullptr; }
         if (cap) { cudaStreamDestroy(cap); cap = nullptr; }
@@ -616,6 +623,20 @@ struct Ctx {
     // ready stream is ordered after the weight-gradient streams and handed to the callback: the caller's collective waits on it alone.
     int done_down_to(int64_t w, bool flush = false) {
         if (!cb && !marks) return M2F_OK;
+        if (collecting >= 0) {  // inside a modality stack: remember the range behind an event on the stack's weight-gradient stream
+            if (hi - w >= bucket_floats || (flush && hi > w)) {
+                if (stack_ev_used == p->stack_evs.size()) {
+                    cudaEvent_t e;
+                    M2F_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+                    p->stack_evs.push_back(e);
+                }
+                cudaEvent_t e = p->stack_evs[stack_ev_used++];
+                M2F_CUDA(cudaEventRecord(e, collect_stream));
+                stack_ranges[collecting].push_back({w, hi, e});
+                hi = w;
+            }
+            return M2F_OK;
+        }
         if (hi - w >= bucket_floats || (flush && hi > w)) {
             cudaStream_t ready = p->use_streams ? p->ready : st;
             if (marks) M2F_TRY(dep(st, ready));  // capture: pulls `ready` into the graph even when no side stream has run yet
@@ -624,6 +645,31 @@ struct Ctx {
             M2F_TRY(report(w, hi, ready));
             hi = w;
         }
+        return M2F_OK;
+    }
+    // The two modality stacks run side by side and finish together, but are enqueued one after the other: reporting their
+    // ranges in enqueue order would make every audio range wait for the whole text stack and leave a stack's worth of
+    // exchange behind the end of the backward.  Their ranges are therefore collected per stack, each behind an event on
+    // that stack's weight-gradient stream, and reported alternately (text, audio, text, ...) once both are enqueued.
+    struct StackRange { int64_t lo, hi; cudaEvent_t ev; };
+    std::vector<StackRange> stack_ranges[2];
+    int collecting = -1;
+    cudaStream_t collect_stream = nullptr;
+    size_t stack_ev_used = 0;
+    void collect_begin(int modality, cudaStream_t wst) { collecting = modality; collect_stream = wst; }
+    void collect_end() { collecting = -1; }
+    int report_stacks() {
+        cudaStream_t ready = p->use_streams ? p->ready : st;
+        const size_t n = std::max(stack_ranges[0].size(), stack_ranges[1].size());
+        for (size_t i = 0; i < n; ++i)
+            for (int s = 1; s >= 0; --s) {
+                if (i >= stack_ranges[s].size()) continue;
+                const StackRange& r = stack_ranges[s][i];
+                if (ready != st || p->use_streams) M2F_CUDA(cudaStreamWaitEvent(ready, r.ev, 0));
+                M2F_TRY(report(r.lo, r.hi, ready));
+            }
+        stack_ranges[0].clear();
+        stack_ranges[1].clear();
         return M2F_OK;
     }
     // eager: tell the caller now; capture: leave an external event-record node behind, the caller is told after the launch
@@ -1075,7 +1121,16 @@ static int backward_all(Ctx& c, const uint8_t* key_pad, const float* dlogits, in
     // projection dropout mask applies -- handled above by not gating the [dq | dv] GEMM at f == 0.
     // text first, audio last: gradients then complete in exactly the reverse of the arena order
     // The two stacks are independent from here on: text continues on the caller's stream, audio runs beside it.
+    const bool interleave = (c.cb || c.marks) && p->mod[0].enabled && p->mod[1].enabled;
+    if (interleave) {
+        M2F_TRY(c.done_down_to(fam ? p->fam[0].inw_off : md->cls[0].w_off, true));  // everything above the stacks
+        c.collect_begin(1, ws1);
+    }
     if (p->mod[1].enabled) M2F_TRY(backward_modality(c, p->mod[1], key_pad, dproj[1], ws1));
+    if (interleave) {
+        M2F_TRY(c.done_down_to(p->mod[1].layers[0].qkv.w_off, true));
+        c.collect_begin(0, c.side(2));
+    }
     if (p->mod[0].enabled) {
         cudaStream_t as = p->mod[1].enabled ? c.side(0) : c.st;
         M2F_TRY(c.dep(c.st, as));
@@ -1083,6 +1138,11 @@ static int backward_all(Ctx& c, const uint8_t* key_pad, const float* dlogits, in
         int rc = backward_modality(c, p->mod[0], key_pad, dproj[0], c.side(2));
         c.cur = nullptr;
         M2F_TRY(rc);
+    }
+    if (interleave) {
+        M2F_TRY(c.done_down_to(0, true));
+        c.collect_end();
+        M2F_TRY(c.report_stacks());
     }
     M2F_TRY(c.done_down_to(0, true));
     for (int i = 0; i < 3; ++i) M2F_TRY(c.dep(c.side(i), c.st));

@@ -394,6 +394,16 @@ class M2FNet(nn.Module):
     def flat_grads(self) -> Optional[torch.Tensor]:
         return self._grad_arena
 
+    def adopt_grad_arena(self, buf: Optional[torch.Tensor]):
+        """Make the backward write its gradients into `buf` (fp32, arena_floats elements, on the model's device) -- the
+        peer gradient exchange places the arena in a symmetric allocation this way.  None reverts to a private arena."""
+        if buf is not None:
+            if buf.dtype != torch.float32 or buf.numel() != self._arena_floats or buf.device != self._arena.device or not buf.is_contiguous():
+                raise ValueError("adopt_grad_arena: need a contiguous fp32 tensor of arena size on the model's device")
+        for p in self._plist:
+            p.grad = None
+        self._grad_arena, self._grad_views, self._grads_cleared = buf, None, False
+
     def __del__(self):
         try:
             for pl in self._plans.values():

@@ -8,10 +8,15 @@ the kernels enqueued so far, and the compute stream joins all of them at the end
 """
 from __future__ import annotations
 
+import ctypes
+import os
+import warnings
 from typing import Callable, List, Optional, Tuple
 
 import torch
 import torch.distributed as dist
+
+from . import _lib
 
 
 def shard_range(n_items: int, rank: int, world: int) -> Tuple[int, int]:
@@ -61,19 +66,118 @@ class GradBucketReducer:
         self.pending = []
 
 
+class PeerGradExchange:
+    """The same contract as `GradBucketReducer`, over NVLink / NVSwitch peer memory instead of NCCL: the model's gradient
+    arena is placed in a symmetric allocation (torch.distributed._symmetric_memory: every rank's copy mapped on every
+    GPU, plus the NVSwitch multicast mapping when the fabric has one) and each reported range is reduced in place by
+    `m2f_grad_allreduce_peer` (csrc/exchange.cu) -- one kernel of a few CTAs whose reduction runs inside the switch
+    (`multimem.ld_reduce` / `multimem.st`), launched on the stream the backward reports the range on.  torch is used for
+    the allocation and the handle exchange only.
+
+    Environment: M2F_EXCHANGE_MC=0 forces the peer load / store variant, M2F_EXCHANGE_CTAS sets the CTAs per call."""
+
+    def __init__(self, model, group=None, average: bool = True, ctas: int = 0):
+        import torch.distributed._symmetric_memory as symm_mem
+
+        self.group = group if group is not None else dist.group.WORLD
+        self.world = dist.get_world_size(self.group)
+        if self.world > _lib.XCHG_MAX_RANKS:
+            raise RuntimeError(f"peer gradient exchange supports up to {_lib.XCHG_MAX_RANKS} ranks (one NVSwitch domain)")
+        arena = model.flat_parameters()
+        if not arena.is_cuda:
+            raise RuntimeError("peer gradient exchange needs the model on the GPU")
+        n = arena.numel()
+        self.signal_off = (n * 4 + 127) // 128 * 128
+        total_floats = (self.signal_off + _lib.XCHG_SIGNAL_BYTES) // 4
+        with torch.cuda.device(arena.device):
+            self.buf = symm_mem.empty(total_floats, dtype=torch.float32, device=arena.device)
+            self.buf.zero_()
+            self.handle = symm_mem.rendezvous(self.buf, self.group)
+            torch.cuda.synchronize()
+        dist.barrier(self.group)  # every rank's barrier words are zero before anybody signals
+        h = self.handle
+        mc = int(h.multicast_ptr) if os.environ.get("M2F_EXCHANGE_MC", "1") != "0" else 0
+        ptrs = [int(x) for x in h.buffer_ptrs]
+        if int(h.world_size) != self.world or ptrs[int(h.rank)] != self.buf.data_ptr():
+            raise RuntimeError("symmetric-memory rendezvous returned an inconsistent handle")
+        self.pg = _lib.PeerGroup()
+        self.pg.mc_base = mc or None
+        for r, x in enumerate(ptrs):
+            self.pg.peer_base[r] = x
+        self.pg.signal_off_bytes = self.signal_off
+        self.pg.rank, self.pg.world = int(h.rank), self.world
+        self.multicast = bool(mc)
+        self.scale = 1.0 / self.world if average else 1.0
+        self.ctas = int(os.environ.get("M2F_EXCHANGE_CTAS", ctas))
+        self.grads = self.buf[:n]
+        self._ev = torch.cuda.Event()
+        self._pending = False
+        self.log: List[Tuple[int, int]] = []
+        self.bytes_last_step = 0
+        model.adopt_grad_arena(self.grads)
+
+    def begin_step(self):
+        self.log = []
+        self.bytes_last_step = 0
+
+    def on_bucket(self, lo: int, hi: int):
+        if hi <= lo:
+            return
+        st = torch.cuda.current_stream()  # the stream the range is final on (model._launch_backward sets it)
+        _lib.check(_lib.lib().m2f_grad_allreduce_peer(ctypes.byref(self.pg), lo, hi, self.scale, self.ctas, st.cuda_stream),
+                   "grad_allreduce_peer")
+        self._ev.record(st)
+        self._pending = True
+        self.log.append((lo, hi))
+        self.bytes_last_step += (hi - lo) * 4
+
+    def finish(self):
+        if self._pending:  # the ranges are reduced one after the other on one stream: the last event covers them all
+            torch.cuda.current_stream().wait_event(self._ev)
+            self._pending = False
+
+
 class DataParallelM2FNet(torch.nn.Module):
     """Wraps a (CUDA) `M2FNet` for data-parallel training: broadcasts rank 0's parameters, then overlaps the bucketed
     gradient all-reduce with the backward.  `forward` is the wrapped model's; `train.train()` of the reference can be
-    called with this object as `model` (it only uses __call__, train/eval, parameters, state_dict)."""
+    called with this object as `model` (it only uses __call__, train/eval, parameters, state_dict).
 
-    def __init__(self, model, group=None, bucket_mb: float = 32.0, average: bool = True):
+    `exchange`: "peer" = the NVSwitch peer-memory kernel (`PeerGradExchange`), "nccl" = bucketed NCCL all-reduce,
+    "auto" (default, or $M2F_EXCHANGE) = peer when the symmetric allocation can be set up on every rank, else nccl."""
+
+    def __init__(self, model, group=None, bucket_mb: Optional[float] = None, average: bool = True, exchange: Optional[str] = None):
         super().__init__()
         self.module = model
         self.group = group
         flat = model.flat_parameters()
         dist.broadcast(flat, src=dist.get_global_rank(group, 0) if group is not None else 0, group=group)
-        self.reducer = GradBucketReducer(model.flat_grads, group, average)
-        model.set_grad_hooks(self._on_bucket, int(bucket_mb * (1 << 20) / 4), self.reducer.finish)
+        exchange = (exchange or os.environ.get("M2F_EXCHANGE", "auto")).lower()
+        if exchange not in ("auto", "peer", "nccl"):
+            raise ValueError(f"exchange must be auto, peer or nccl, got {exchange!r}")
+        self.reducer = None
+        if exchange != "nccl" and flat.is_cuda:
+            err = None
+            try:
+                self.reducer = PeerGradExchange(model, group, average)
+            except Exception as e:  # no symmetric memory on this box / fabric
+                err = e
+            ok = torch.tensor([0 if self.reducer is None else 1], device=flat.device)
+            dist.all_reduce(ok, op=dist.ReduceOp.MIN, group=group)  # all ranks take the same path
+            if int(ok.item()) == 0:
+                if exchange == "peer":
+                    raise RuntimeError(f"peer gradient exchange unavailable: {err!r}")
+                if self.reducer is not None:
+                    model.adopt_grad_arena(None)
+                    self.reducer = None
+                if dist.get_rank(group) == 0:
+                    warnings.warn(f"peer gradient exchange unavailable ({err!r}); using NCCL buckets")
+        if self.reducer is None:
+            self.reducer = GradBucketReducer(model.flat_grads, group, average)
+        self.exchange = "peer" if isinstance(self.reducer, PeerGradExchange) else "nccl"
+        if bucket_mb is None:  # NCCL kernels compete for SMs: few large buckets; the peer kernel is light: finer overlap
+            bucket_mb = 32.0 if self.exchange == "peer" else 128.0
+        self.bucket_mb = float(bucket_mb)
+        model.set_grad_hooks(self._on_bucket, int(self.bucket_mb * (1 << 20) / 4), self.reducer.finish)
         self._first = True
 
     def _on_bucket(self, lo: int, hi: int):

@@ -24,7 +24,7 @@ def _worker(rank, world, port, out):
                                  CLASSIFIER=dict(hidden_size=64, output_size=7, n_layers=2))
     torch.manual_seed(100 + rank)  # different init per rank: the wrapper must broadcast rank 0's
     model = pkg.M2FNet(cfg, planes=3).to("cuda").train()
-    net = pkg.DataParallelM2FNet(model, bucket_mb=0.05)
+    net = pkg.DataParallelM2FNet(model, bucket_mb=0.05, exchange="nccl")
     full = D.synth_batch(8, 9, 128, 64, seed=5)
     lo, hi = pkg.shard_range(8, rank, world)
     b = {k: v[lo:hi].cuda() for k, v in full.items()}

@@ -1,0 +1,168 @@
+"""Gradient exchange over peer memory (csrc/exchange.cu, include/m2f_b200.h: m2f_grad_allreduce_peer).
+
+One GPU: the slicing / unaligned-end arithmetic and the self-resetting barrier words with world == 1 (peer load / store
+variant on an ordinary allocation).  Two GPUs: the kernel on a symmetric allocation, multicast (multimem) and peer
+variants, against torch's sum of the two buffers; then the data-parallel step through `DataParallelM2FNet(exchange=
+"peer")` against a single-GPU run on the concatenated batch (the same bar as tests/test_gpu_dp.py sets for NCCL)."""
+import ctypes
+import os
+
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+PKG_NAME = "multimodal-emotion-recognition_b200"
+
+
+def _pkg():
+    import importlib
+    return importlib.import_module(PKG_NAME)
+
+
+def test_world1_ranges_scale_in_place():
+    pkg = _pkg()
+    L, lib = pkg._lib, pkg._lib.lib()
+    n = 1 << 20
+    sig_off = n * 4
+    buf = torch.zeros(n + L.XCHG_SIGNAL_BYTES // 4, device="cuda")
+    x = torch.randn(n, device="cuda")
+    buf[:n] = x
+    pg = L.PeerGroup()
+    pg.mc_base = None
+    pg.peer_base[0] = buf.data_ptr()
+    pg.signal_off_bytes = sig_off
+    pg.rank, pg.world = 0, 1
+    st = torch.cuda.current_stream().cuda_stream
+    expect = x.clone()
+    # aligned, unaligned head, unaligned tail, both, shorter than one vector, empty; several CTA counts
+    for lo, hi, ctas in [(0, n, 0), (4096, 8192, 1), (5, 4099, 7), (8, 1003, 64), (1001, 1003, 0), (77, 78, 0), (300, 300, 0),
+                         (3, n - 1, 200)]:
+        L.check(lib.m2f_grad_allreduce_peer(ctypes.byref(pg), lo, hi, 0.5, ctas, st), "grad_allreduce_peer")
+        expect[lo:hi] *= 0.5
+    torch.cuda.synchronize()
+    assert torch.equal(buf[:n], expect)
+    assert int(buf[n:].view(torch.int32).abs().sum()) == 0  # every barrier word consumed
+
+
+def test_bad_arguments_are_errors():
+    pkg = _pkg()
+    L, lib = pkg._lib, pkg._lib.lib()
+    buf = torch.zeros(1024 + L.XCHG_SIGNAL_BYTES // 4, device="cuda")
+    pg = L.PeerGroup()
+    pg.peer_base[0] = buf.data_ptr()
+    pg.signal_off_bytes = 4096
+    pg.rank, pg.world = 0, 1
+    assert lib.m2f_grad_allreduce_peer(ctypes.byref(pg), 0, 2048, 1.0, 0, None) == L.M2F_ERR_ARG  # range overlaps the signal area
+    pg.world = 17
+    assert lib.m2f_grad_allreduce_peer(ctypes.byref(pg), 0, 16, 1.0, 0, None) == L.M2F_ERR_ARG
+    pg.world, pg.rank = 2, 0  # peer 1 missing
+    assert lib.m2f_grad_allreduce_peer(ctypes.byref(pg), 0, 16, 1.0, 0, None) == L.M2F_ERR_ARG
+    assert lib.m2f_grad_allreduce_peer(None, 0, 16, 1.0, 0, None) == L.M2F_ERR_ARG
+
+
+def _worker(rank, world, port, out):
+    import importlib
+    import sys
+    import torch.distributed as dist
+    sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+    pkg = importlib.import_module(PKG_NAME)
+    D = importlib.import_module(PKG_NAME + ".data")
+    L, lib = pkg._lib, pkg._lib.lib()
+    os.environ["MASTER_ADDR"], os.environ["MASTER_PORT"] = "127.0.0.1", str(port)
+    torch.cuda.set_device(rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
+    res = {}
+    cfg = D.default_model_config(dropout=0.0, AUDIO=dict(embedding_size=64, n_head=4, n_encoder_layers=2),
+                                 TEXT=dict(embedding_size=128, n_head=4, n_encoder_layers=2), FAM=dict(embedding_size=64, n_head=4, n_layers=2),
+                                 CLASSIFIER=dict(hidden_size=64, output_size=7, n_layers=2))
+    torch.manual_seed(100 + rank)
+    model = pkg.M2FNet(cfg, planes=3).to("cuda").train()
+    try:
+        net = pkg.DataParallelM2FNet(model, bucket_mb=0.05, exchange="peer")
+    except RuntimeError as e:
+        if rank == 0:
+            torch.save({"unavailable": repr(e)}, out)
+        dist.destroy_process_group()
+        return
+    ex = net.reducer
+    res["multicast"] = ex.multicast
+    # ---- the kernel alone: random buffers, unaligned ranges, multicast and peer variants
+    n = ex.grads.numel()
+    kerr = {}
+    for variant in (["mc"] if ex.multicast else []) + ["p2p"]:
+        pg = L.PeerGroup()
+        ctypes.memmove(ctypes.byref(pg), ctypes.byref(ex.pg), ctypes.sizeof(pg))
+        if variant == "p2p":
+            pg.mc_base = None
+        g = torch.Generator(device="cuda").manual_seed(7 + rank)
+        x = torch.randn(n, device="cuda", generator=g)
+        ex.grads.copy_(x)
+        both = [torch.empty_like(x) for _ in range(world)]
+        dist.all_gather(both, x)
+        total = sum(both)
+        expect = x.clone()
+        torch.cuda.synchronize()
+        dist.barrier()
+        st = torch.cuda.current_stream().cuda_stream
+        for lo, hi, ctas in [(n // 2 + 3, n - 1, 0), (16, 4096, 3), (5, 9, 0), (4099, n // 2 + 3, 64)]:
+            L.check(lib.m2f_grad_allreduce_peer(ctypes.byref(pg), lo, hi, 0.5, ctas, st), "grad_allreduce_peer")
+            expect[lo:hi] = total[lo:hi] * 0.5
+        torch.cuda.synchronize()
+        dist.barrier()
+        kerr[variant] = (ex.grads - expect).abs().max().item()
+    res["kernel_max_abs_err"] = kerr
+    # ---- the data-parallel step
+    full = D.synth_batch(8, 9, 128, 64, seed=5)
+    lo, hi = pkg.shard_range(8, rank, world)
+    b = {k: v[lo:hi].cuda() for k, v in full.items()}
+    crit = pkg.FusedCrossEntropyLoss()
+    crit(net(b["text"], b["audio"], b["padding_mask"]).permute(0, 2, 1), b["emotion"]).backward()
+    torch.cuda.synchronize()
+    g_dp = model.flat_grads().clone()
+    res["buckets"] = len(ex.log)
+    solo = pkg.M2FNet(cfg, planes=3).to("cuda").train()
+    solo.load_state_dict(model.state_dict())
+    fb = {k: v.cuda() for k, v in full.items()}
+    crit(solo(fb["text"], fb["audio"], fb["padding_mask"]).permute(0, 2, 1), fb["emotion"]).backward()
+    torch.cuda.synchronize()
+    res["err"] = (torch.linalg.vector_norm(g_dp - solo.flat_grads()) / torch.linalg.vector_norm(solo.flat_grads())).item()
+    opt_dp = pkg.FusedAdam(model, lr=1e-3, weight_decay=0.01)
+    opt_solo = pkg.FusedAdam(solo, lr=1e-3, weight_decay=0.01)
+    opt_dp.step()
+    opt_solo.step()
+    for it in range(3):  # replayed backward graph + exchange kernels behind its event nodes
+        fb2 = D.synth_batch(8, 9, 128, 64, seed=50 + it)
+        b2 = {k: v[lo:hi].cuda() for k, v in fb2.items()}
+        fb2 = {k: v.cuda() for k, v in fb2.items()}
+        opt_dp.zero_grad()
+        crit(net(b2["text"], b2["audio"], b2["padding_mask"]).permute(0, 2, 1), b2["emotion"]).backward()
+        opt_dp.step()
+        opt_solo.zero_grad()
+        crit(solo(fb2["text"], fb2["audio"], fb2["padding_mask"]).permute(0, 2, 1), fb2["emotion"]).backward()
+        opt_solo.step()
+    torch.cuda.synchronize()
+    res["param_err_after_4_steps"] = (torch.linalg.vector_norm(model.flat_parameters() - solo.flat_parameters()) /
+                                      torch.linalg.vector_norm(solo.flat_parameters())).item()
+    gathered = [torch.empty_like(g_dp) for _ in range(world)]
+    dist.all_gather(gathered, g_dp)
+    res["same"] = all(torch.equal(gathered[0], x) for x in gathered)
+    if rank == 0:
+        torch.save(res, out)
+    dist.destroy_process_group()
+
+
+def test_dp2_peer_exchange_equals_single_gpu(tmp_path):
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    import torch.multiprocessing as mp
+    out = str(tmp_path / "peer.pt")
+    mp.spawn(_worker, args=(2, 29641, out), nprocs=2, join=True)
+    r = torch.load(out)
+    if "unavailable" in r:
+        pytest.skip("symmetric memory unavailable on this box: " + r["unavailable"])
+    print(r)
+    for variant, e in r["kernel_max_abs_err"].items():
+        assert e < 1e-5, (variant, r)
+    assert r["same"] and r["buckets"] >= 3
+    assert r["err"] < 2e-5, r
+    assert r["param_err_after_4_steps"] < 1e-5, r
