@@ -253,6 +253,13 @@ typedef struct {
  * With world == 1 it degenerates to an in-place scale (used by the single-GPU tests of the slicing arithmetic). */
 int m2f_grad_allreduce_peer(const m2f_peer_group_t* g, int64_t lo, int64_t hi, float scale, int32_t ctas, void* stream);
 
+/* Debug aid: the exchange kernel keeps a ring of the last M2F_XCHG_TRACE_RECORDS launches on this device, 6 x uint64 each:
+ * %globaltimer (ns) at entry, after the first barrier, after the data phase, at exit; lo; floats.  Copies the ring to
+ * out_records (host, M2F_XCHG_TRACE_RECORDS * 6 values; record i of the process sits at slot i % RECORDS) and returns
+ * the number of launches so far.  Synchronises the device. */
+#define M2F_XCHG_TRACE_RECORDS 512
+int64_t m2f_exchange_trace(uint64_t* out_records);
+
 /* Adam with L2 weight decay folded into the gradient (torch.optim.Adam semantics, src/train.py:56,231), one
  * launch over the arena; `t` is the 1-based step count.  grad_scale multiplies g first (DDP averaging). */
 int m2f_adam_step(float* params, const float* grads, float* exp_avg, float* exp_avg_sq, int64_t n, float lr,

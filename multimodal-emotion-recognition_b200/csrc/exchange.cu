@@ -107,6 +107,11 @@ __device__ __forceinline__ float peer_ld_f32(const float* p) {
 }
 __device__ __forceinline__ void peer_st_f32(float* p, float v) { asm volatile("st.relaxed.sys.global.f32 [%0], %1;" ::"l"(p), "f"(v) : "memory"); }
 
+// Debug trace (always on, one thread per launch): ring of {t_enter, t_after_first_barrier, t_data_done, t_exit (globaltimer ns),
+// lo, floats} so the exchange can be placed on the step's timeline (tools/dp_trace.py, M2F_TIMELINE).
+__device__ unsigned long long g_xchg_trace[M2F_XCHG_TRACE_RECORDS * 6];
+__device__ unsigned int g_xchg_trace_n;
+
 // float offsets: [lo, lo + head) scalar, then n4 float4, then `tail` scalars; head / tail < 4 (arena ranges that do not
 // start or end on 16 bytes, e.g. the 7-wide classifier bias at the end of the 1-D region)
 constexpr int XCHG_THREADS = 512;
@@ -115,7 +120,16 @@ constexpr int XCHG_UNROLL = 4;
 template <bool MC>
 __global__ void __launch_bounds__(XCHG_THREADS)
 grad_allreduce_kernel(float* __restrict__ mc, PeerPtrs pp, int rank, int world, int64_t lo, int head, int64_t n4, int tail, float scale) {
+    const bool tracer = blockIdx.x == 0 && threadIdx.x == 0;
+    unsigned long long* tr = nullptr;
+    if (tracer) {
+        tr = g_xchg_trace + (size_t)(atomicAdd(&g_xchg_trace_n, 1u) % M2F_XCHG_TRACE_RECORDS) * 6;
+        tr[0] = gtimer();
+        tr[4] = (unsigned long long)lo;
+        tr[5] = (unsigned long long)(head + 4 * n4 + tail);
+    }
     block_barrier_all_ranks(pp, rank, world);
+    if (tracer) tr[1] = gtimer();
 
     // the slice of the vector body this rank reduces, split over the blocks in contiguous runs of XCHG_UNROLL vectors per thread
     const int64_t per_rank = (n4 + world - 1) / world;
@@ -169,7 +183,9 @@ grad_allreduce_kernel(float* __restrict__ mc, PeerPtrs pp, int rank, int world, 
         }
     }
     __threadfence_system();
+    if (tracer) tr[2] = gtimer();
     block_barrier_all_ranks(pp, rank, world);
+    if (tracer) tr[3] = gtimer();
 }
 
 }  // namespace m2f
@@ -213,4 +229,12 @@ extern "C" int m2f_grad_allreduce_peer(const m2f_peer_group_t* g, int64_t lo, in
     else    grad_allreduce_kernel<false><<<grid, XCHG_THREADS, 0, st>>>(nullptr, pp, g->rank, g->world, lo, head, n4, tail, scale);
     M2F_LAUNCH_CHECK();
     return M2F_OK;
+}
+
+extern "C" int64_t m2f_exchange_trace(uint64_t* out_records) {
+    if (!out_records) return 0;
+    unsigned int n = 0;
+    if (cudaMemcpyFromSymbol(&n, g_xchg_trace_n, sizeof(n)) != cudaSuccess) return 0;
+    if (cudaMemcpyFromSymbol(out_records, g_xchg_trace, sizeof(unsigned long long) * M2F_XCHG_TRACE_RECORDS * 6) != cudaSuccess) return 0;
+    return (int64_t)n;
 }

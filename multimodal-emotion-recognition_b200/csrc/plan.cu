@@ -1552,6 +1552,7 @@ extern "C" int m2f_plan_backward_bucketed(m2f_plan_t* p, const float* params, co
             std::vector<unsigned long long> t(p->tl_labels.size());
             M2F_CUDA(cudaMemcpy(t.data(), p->tl_dev, t.size() * sizeof(unsigned long long), cudaMemcpyDeviceToHost));
             if (FILE* f = std::fopen(std::getenv("M2F_TIMELINE"), "w")) {
+                std::fprintf(f, "#t0_ns\t%llu\n", t.empty() ? 0ull : t[0]);  // absolute %globaltimer of entry 0
                 for (size_t i = 0; i < t.size(); ++i)
                     std::fprintf(f, "%zu\t%d\t%.3f\t%s\n", i, p->tl_labels[i].second, ((double)t[i] - (double)t[0]) * 1e-3,
                                  p->tl_labels[i].first.c_str());

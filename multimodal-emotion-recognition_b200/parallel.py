@@ -110,6 +110,7 @@ class PeerGradExchange:
         self.scale = 1.0 / self.world if average else 1.0
         self.ctas = int(os.environ.get("M2F_EXCHANGE_CTAS", ctas))
         self.grads = self.buf[:n]
+        self._dryrun = os.environ.get("M2F_EXCHANGE_DRYRUN", "0") == "1"
         self._ev = torch.cuda.Event()
         self._pending = False
         self.log: List[Tuple[int, int]] = []
@@ -124,6 +125,9 @@ class PeerGradExchange:
         if hi <= lo:
             return
         st = torch.cuda.current_stream()  # the stream the range is final on (model._launch_backward sets it)
+        if self._dryrun:  # timing experiments only: the ranges are reported but not exchanged
+            self.log.append((lo, hi))
+            return
         _lib.check(_lib.lib().m2f_grad_allreduce_peer(ctypes.byref(self.pg), lo, hi, self.scale, self.ctas, st.cuda_stream),
                    "grad_allreduce_peer")
         self._ev.record(st)
