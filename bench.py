@@ -39,7 +39,7 @@ def parse():
     ap.add_argument("--seq", type=int, default=33)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
-    ap.add_argument("--bucket-mb", type=float, default=None, help="gradient bucket size (default: 32 for the peer exchange, 128 for NCCL)")
+    ap.add_argument("--bucket-mb", type=float, default=None, help="gradient bucket size (default: 16 for the peer exchange, 128 for NCCL)")
     ap.add_argument("--exchange", default=None, choices=["auto", "peer", "nccl"],
                     help="gradient exchange at N > 1: NVSwitch peer-memory kernel or NCCL buckets (default: $M2F_EXCHANGE or auto)")
     return ap.parse_args()

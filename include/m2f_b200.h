@@ -249,7 +249,7 @@ typedef struct {
 /* In-place all-reduce of the float range [lo, hi) of the symmetric buffer: on return of the *kernel* every rank holds
  * scale * sum over ranks.  Two-shot: rank r reduces slice r (in the switch with multicast, by world peer loads without)
  * and writes it to every rank.  Stream-ordered; every rank must issue the same sequence of calls (same lo, hi, ctas)
- * and have one GPU to itself -- the kernels of the ranks wait for each other.  ctas <= 0 picks the default (32).
+ * and have one GPU to itself -- the kernels of the ranks wait for each other.  ctas <= 0: one CTA per 256 KB of a rank's slice, at most 64.
  * With world == 1 it degenerates to an in-place scale (used by the single-GPU tests of the slicing arithmetic). */
 int m2f_grad_allreduce_peer(const m2f_peer_group_t* g, int64_t lo, int64_t hi, float scale, int32_t ctas, void* stream);
 

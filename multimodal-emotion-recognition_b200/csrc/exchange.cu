@@ -115,7 +115,7 @@ __device__ unsigned int g_xchg_trace_n;
 // float offsets: [lo, lo + head) scalar, then n4 float4, then `tail` scalars; head / tail < 4 (arena ranges that do not
 // start or end on 16 bytes, e.g. the 7-wide classifier bias at the end of the 1-D region)
 constexpr int XCHG_THREADS = 512;
-constexpr int XCHG_UNROLL = 4;
+constexpr int XCHG_UNROLL = 8;  // 512 threads x 8 x 16 B = 64 KB of loads in flight per CTA
 
 template <bool MC>
 __global__ void __launch_bounds__(XCHG_THREADS)
@@ -216,11 +216,20 @@ extern "C" int m2f_grad_allreduce_peer(const m2f_peer_group_t* g, int64_t lo, in
     const int head = (int)((4 - (lo & 3)) & 3) < (hi - lo) ? (int)((4 - (lo & 3)) & 3) : (int)(hi - lo);
     const int64_t n4 = (hi - lo - head) / 4;
     const int tail = (int)(hi - lo - head - 4 * n4);
-    // enough CTAs to keep a few hundred KB of loads in flight over the switch, few enough to leave the SMs to the backward;
-    // every rank must use the same count (the barrier slots are per block), so it depends on the range and `ctas` only
-    int grid = ctas > 0 ? ctas : 32;
-    if (grid > M2F_XCHG_MAX_CTAS) grid = M2F_XCHG_MAX_CTAS;
+    // The kernel is latency-bound (a multimem load takes microseconds): SM time spent = bytes x latency / bytes in flight per
+    // CTA, whatever the CTA count, and every resident CTA displaces one of the backward's GEMM CTAs (they fill the register
+    // file).  So: as much in flight per CTA as registers allow, and one CTA per 256 KB of this rank's slice -- a short kernel
+    // for the large slices of a small world, a handful of CTAs for the small slices of a large one.  Every rank must use the
+    // same count (the barrier slots are per block): it depends on the range, the world size and `ctas` only.
     const int64_t per_rank = (n4 + g->world - 1) / g->world;
+    int grid;
+    if (ctas > 0) {
+        grid = ctas;
+    } else {
+        const int64_t want = (per_rank * 16 + (256 << 10) - 1) / (256 << 10);
+        grid = want < 1 ? 1 : (want > M2F_XCHG_MAX_CTAS ? M2F_XCHG_MAX_CTAS : (int)want);
+    }
+    if (grid > M2F_XCHG_MAX_CTAS) grid = M2F_XCHG_MAX_CTAS;
     const int64_t need = (per_rank + XCHG_THREADS * XCHG_UNROLL - 1) / (XCHG_THREADS * XCHG_UNROLL);
     if (need < grid) grid = need < 1 ? 1 : (int)need;
     cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);

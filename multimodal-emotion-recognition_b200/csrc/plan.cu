@@ -1126,14 +1126,15 @@ static int backward_all(Ctx& c, const uint8_t* key_pad, const float* dlogits, in
         M2F_TRY(c.done_down_to(fam ? p->fam[0].inw_off : md->cls[0].w_off, true));  // everything above the stacks
         c.collect_begin(1, ws1);
     }
+    // fork before the text stack is enqueued: the audio chain needs only what the main stream holds so far (its dproj)
+    cudaStream_t as = p->mod[1].enabled ? c.side(0) : c.st;
+    if (p->mod[0].enabled) M2F_TRY(c.dep(c.st, as));
     if (p->mod[1].enabled) M2F_TRY(backward_modality(c, p->mod[1], key_pad, dproj[1], ws1));
     if (interleave) {
         M2F_TRY(c.done_down_to(p->mod[1].layers[0].qkv.w_off, true));
         c.collect_begin(0, c.side(2));
     }
     if (p->mod[0].enabled) {
-        cudaStream_t as = p->mod[1].enabled ? c.side(0) : c.st;
-        M2F_TRY(c.dep(c.st, as));
         c.cur = (as == c.st) ? nullptr : as;
         int rc = backward_modality(c, p->mod[0], key_pad, dproj[0], c.side(2));
         c.cur = nullptr;

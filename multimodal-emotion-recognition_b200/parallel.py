@@ -179,7 +179,7 @@ class DataParallelM2FNet(torch.nn.Module):
             self.reducer = GradBucketReducer(model.flat_grads, group, average)
         self.exchange = "peer" if isinstance(self.reducer, PeerGradExchange) else "nccl"
         if bucket_mb is None:  # NCCL kernels compete for SMs: few large buckets; the peer kernel is light: finer overlap
-            bucket_mb = 32.0 if self.exchange == "peer" else 128.0
+            bucket_mb = 16.0 if self.exchange == "peer" else 128.0
         self.bucket_mb = float(bucket_mb)
         model.set_grad_hooks(self._on_bucket, int(self.bucket_mb * (1 << 20) / 4), self.reducer.finish)
         self._first = True
