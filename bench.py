@@ -289,7 +289,9 @@ def main():
                                    ("multicast (multimem.ld_reduce / multimem.st)" if getattr(net.reducer, "multicast", False) else "peer loads / stores")
                                    if net.exchange == "peer" else "gradient all-reduce: NCCL, async buckets behind the backward")
             cfg_out["bucket_mb"] = net.bucket_mb
-            cfg_out["exchange_calls_per_step"] = len(net.reducer.log)
+            cfg_out["exchange_calls_per_step"] = getattr(net.reducer, "calls_per_step", len(net.reducer.log))
+            if net.exchange == "peer":
+                cfg_out["exchange_launch"] = "kernels captured in the backward's CUDA graph" if net.reducer.in_graph else "bucket callbacks"
         out = {"metric": "M2FNet train utterances/sec", "value": value, "unit": "utterances/s", "n_gpus": world,
                "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms / args.steps, "higher_is_better": True,
                "scaling": "weak", "vs_baseline": None, "dtype": "bf16" if planes == 1 else "f32 (3 x bf16 planes)",

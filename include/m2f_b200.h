@@ -253,6 +253,15 @@ typedef struct {
  * With world == 1 it degenerates to an in-place scale (used by the single-GPU tests of the slicing arithmetic). */
 int m2f_grad_allreduce_peer(const m2f_peer_group_t* g, int64_t lo, int64_t hi, float scale, int32_t ctas, void* stream);
 
+/* The exchange as part of the backward: after this call m2f_plan_backward_bucketed(..., bucket_floats > 0, cb = NULL, ...)
+ * all-reduces every finished gradient range itself -- m2f_grad_allreduce_peer on the plan's ready stream, captured into
+ * the backward's CUDA graph, so a data-parallel step needs no host work per range -- and the caller's stream continues
+ * only after the last range has been exchanged.  `grads` of that call must be this rank's copy of the symmetric buffer
+ * (group->peer_base[group->rank]).  The group is copied.  group == NULL detaches.  m2f_plan_exchange_ranges: number of
+ * ranges the last such backward exchanged (identical on every rank). */
+int m2f_plan_set_exchange(m2f_plan_t* p, const m2f_peer_group_t* group, float scale, int32_t ctas);
+int64_t m2f_plan_exchange_ranges(const m2f_plan_t* p);
+
 /* Debug aid: the exchange kernel keeps a ring of the last M2F_XCHG_TRACE_RECORDS launches on this device, 6 x uint64 each:
  * %globaltimer (ns) at entry, after the first barrier, after the data phase, at exit; lo; floats.  Copies the ring to
  * out_records (host, M2F_XCHG_TRACE_RECORDS * 6 values; record i of the process sits at slot i % RECORDS) and returns

@@ -98,6 +98,8 @@ PROTOTYPES = {
     "m2f_plan_backward_bucketed": [_vp, _vp, _vp, _vp, _vp, _vp, _i64, _vp, _vp, _vp],
     "m2f_grad_allreduce_peer": [C.POINTER(PeerGroup), _i64, _i64, _f32, _i32, _vp],
     "m2f_exchange_trace": [_vp],
+    "m2f_plan_set_exchange": [_vp, C.POINTER(PeerGroup), _f32, _i32],
+    "m2f_plan_exchange_ranges": [_vp],
     "m2f_adam_step": [_vp, _vp, _vp, _vp, _i64, _f32, _f32, _f32, _f32, _f32, _i64, _f32, _vp],
     "m2f_model_adam_step": [_vp, _vp, _vp, _vp, _vp, _vp, _f32, _f32, _f32, _f32, _f32, _i64, _f32, _vp],
     "m2f_collate_dialogues": [_vp, _i64, _i32, _vp, _i64, _i32, _vp, _vp, _vp, _vp, _i64, _i64, _vp, _vp, _vp, _vp, _vp],
@@ -105,7 +107,7 @@ PROTOTYPES = {
 }
 
 # functions that return a 64-bit count instead of an error code
-_RET_I64 = {"m2f_launch_count", "m2f_exchange_trace", "m2f_model_num_params", "m2f_model_arena_floats", "m2f_model_arena_1d_offset", "m2f_model_shadow_bytes",
+_RET_I64 = {"m2f_launch_count", "m2f_exchange_trace", "m2f_plan_exchange_ranges", "m2f_model_num_params", "m2f_model_arena_floats", "m2f_model_arena_1d_offset", "m2f_model_shadow_bytes",
             "m2f_plan_workspace_bytes"}
 
 _lock = threading.Lock()

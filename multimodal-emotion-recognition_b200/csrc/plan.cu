@@ -246,6 +246,12 @@ struct m2f_plan {
     } gf, gb;
     std::vector<cudaEvent_t> bucket_evs;     // recorded by event nodes of the backward graph, one per reported range
     std::vector<cudaEvent_t> stack_evs;      // "weight gradients of this stack down to here are enqueued" (interleaved stack reports)
+    // gradient exchange inside the backward (m2f_plan_set_exchange): each finished range is all-reduced by a kernel on `ready`
+    bool xchg_on = false;
+    m2f_peer_group_t xchg_group = {};
+    float xchg_scale = 1.f;
+    int xchg_ctas = 0;
+    int64_t xchg_ranges = 0;                 // ranges exchanged by the last backward
     cudaStream_t cap = nullptr;
     unsigned long long* rng_dev = nullptr;   // {seed, step} read by the dropout kernels of the captured graphs
     int use_graph = 1;
@@ -622,7 +628,7 @@ struct Ctx {
     // Every 2-D gradient at arena offsets >= w has been enqueued.  When a bucket is due, the plan's
     // ready stream is ordered after the weight-gradient streams and handed to the callback: the caller's collective waits on it alone.
     int done_down_to(int64_t w, bool flush = false) {
-        if (!cb && !marks) return M2F_OK;
+        if (!cb && !marks && !xchg) return M2F_OK;
         if (collecting >= 0) {  // inside a modality stack: remember the range behind an event on the stack's weight-gradient stream
             if (hi - w >= bucket_floats || (flush && hi > w)) {
                 if (stack_ev_used == p->stack_evs.size()) {
@@ -639,7 +645,7 @@ struct Ctx {
         }
         if (hi - w >= bucket_floats || (flush && hi > w)) {
             cudaStream_t ready = p->use_streams ? p->ready : st;
-            if (marks) M2F_TRY(dep(st, ready));  // capture: pulls `ready` into the graph even when no side stream has run yet
+            if (marks || capturing) M2F_TRY(dep(st, ready));  // capture: pulls `ready` into the graph even when no side stream has run yet
             M2F_TRY(dep(side(1), ready));  // the two weight-gradient streams
             M2F_TRY(dep(side(2), ready));
             M2F_TRY(report(w, hi, ready));
@@ -675,7 +681,15 @@ struct Ctx {
     // eager: tell the caller now; capture: leave an external event-record node behind, the caller is told after the launch
     std::vector<std::pair<int64_t, int64_t>>* marks = nullptr;
     bool ready_in_capture = false;
+    bool xchg = false;       // exchange the range here (kernel on `ready`, captured with the graph) instead of telling the caller
+    bool capturing = false;
     int report(int64_t lo, int64_t hi_, cudaStream_t ready) {
+        if (xchg) {
+            M2F_TRY(m2f_grad_allreduce_peer(&p->xchg_group, lo, hi_, p->xchg_scale, p->xchg_ctas, ready));
+            ++p->xchg_ranges;
+            if (ready != st) ready_in_capture = true;
+            return M2F_OK;
+        }
         if (!marks) {
             cb(cb_user, lo, hi_, ready);
             return M2F_OK;
@@ -1121,7 +1135,7 @@ static int backward_all(Ctx& c, const uint8_t* key_pad, const float* dlogits, in
     // projection dropout mask applies -- handled above by not gating the [dq | dv] GEMM at f == 0.
     // text first, audio last: gradients then complete in exactly the reverse of the arena order
     // The two stacks are independent from here on: text continues on the caller's stream, audio runs beside it.
-    const bool interleave = (c.cb || c.marks) && p->mod[0].enabled && p->mod[1].enabled;
+    const bool interleave = (c.cb || c.marks || c.xchg) && p->mod[0].enabled && p->mod[1].enabled;
     if (interleave) {
         M2F_TRY(c.done_down_to(fam ? p->fam[0].inw_off : md->cls[0].w_off, true));  // everything above the stacks
         c.collect_begin(1, ws1);
@@ -1147,11 +1161,13 @@ static int backward_all(Ctx& c, const uint8_t* key_pad, const float* dlogits, in
     }
     M2F_TRY(c.done_down_to(0, true));
     for (int i = 0; i < 3; ++i) M2F_TRY(c.dep(c.side(i), c.st));
-    if (c.cb || c.marks) {  // biases / LayerNorm parameters (atomically accumulated by every stream): final once everything has joined
+    if (c.cb || c.marks || c.xchg) {  // biases / LayerNorm parameters (atomically accumulated by every stream): final once everything has joined
         cudaStream_t ready = p->use_streams ? p->ready : c.st;
         M2F_TRY(c.dep(c.st, ready));
         M2F_TRY(c.report(md->off_1d, md->arena_floats, ready));
-        if (c.marks && c.ready_in_capture) M2F_TRY(c.dep(ready, c.st));  // a capture must end with every forked stream joined
+        // a capture must end with every forked stream joined; with the exchange inside the backward the caller's stream
+        // continues (optimizer) only after the last range has been exchanged
+        if ((c.marks || c.xchg) && c.ready_in_capture) M2F_TRY(c.dep(ready, c.st));
     }
     return M2F_OK;
 }
@@ -1498,6 +1514,24 @@ extern "C" int m2f_plan_loss(m2f_plan_t* p, void* workspace, const float* logits
     return M2F_OK;
 }
 
+extern "C" int m2f_plan_set_exchange(m2f_plan_t* p, const m2f_peer_group_t* group, float scale, int32_t ctas) {
+    M2F_REQUIRE(p, M2F_ERR_ARG, "plan_set_exchange: plan is NULL");
+    p->gb.reset();  // the captured backward embeds (or lacks) the exchange kernels
+    if (!group) {
+        p->xchg_on = false;
+        return M2F_OK;
+    }
+    M2F_REQUIRE(group->world >= 1 && group->world <= M2F_XCHG_MAX_RANKS && group->rank >= 0 && group->rank < group->world, M2F_ERR_ARG,
+                "plan_set_exchange: rank %d / world %d outside [1, %d]", group->rank, group->world, M2F_XCHG_MAX_RANKS);
+    p->xchg_group = *group;
+    p->xchg_scale = scale;
+    p->xchg_ctas = ctas;
+    p->xchg_on = true;
+    return M2F_OK;
+}
+
+extern "C" int64_t m2f_plan_exchange_ranges(const m2f_plan_t* p) { return p ? p->xchg_ranges : 0; }
+
 extern "C" int m2f_plan_backward_bucketed(m2f_plan_t* p, const float* params, const void* shadow, void* workspace,
                                           const float* dlogits, float* grads, int64_t bucket_floats, m2f_bucket_cb cb, void* user,
                                           void* stream) {
@@ -1513,6 +1547,13 @@ extern "C" int m2f_plan_backward_bucketed(m2f_plan_t* p, const float* params, co
     c.cb = cb;
     c.cb_user = user;
     c.hi = p->m->off_1d;
+    c.xchg = !cb && bucket_floats > 0 && p->xchg_on;
+    if (c.xchg) {
+        M2F_REQUIRE(grads == p->xchg_group.peer_base[p->xchg_group.rank], M2F_ERR_ARG,
+                    "plan_backward: with an exchange attached the gradients must be written to this rank's copy of the symmetric buffer");
+        M2F_REQUIRE(p->xchg_group.signal_off_bytes >= p->m->arena_floats * 4, M2F_ERR_ARG, "plan_backward: the exchange's signal area overlaps the gradient arena");
+        p->xchg_ranges = 0;
+    }
     const uint8_t* kp = c.ws + p->key_pad.off;
     int rc;
     if (!p->use_graph) {
@@ -1523,15 +1564,17 @@ extern "C" int m2f_plan_backward_bucketed(m2f_plan_t* p, const float* params, co
         M2F_TRY(backward_all(c, kp, dlogits, PH_HEAD));
         m2f_plan::GraphKey key;
         key.params = params; key.shadow = shadow; key.ws = workspace; key.grads = grads; key.p_used = p->p_used;
-        key.flags = cb ? 1 : 0;
-        key.bucket_floats = cb ? c.bucket_floats : 0;
+        key.flags = cb ? 1 : (c.xchg ? 2 : 0);
+        key.bucket_floats = (cb || c.xchg) ? c.bucket_floats : 0;
         std::vector<std::pair<int64_t, int64_t>> marks;
         bool captured = false;
         rc = run_graphed(p, p->gb, key, ust, [&](cudaStream_t cs) {
             Ctx g = c;
             g.st = cs;
             g.cb = nullptr;
+            g.capturing = true;
             if (cb) g.marks = &marks;
+            if (c.xchg) p->xchg_ranges = 0;
             captured = true;
             int r = backward_all(g, kp, nullptr, PH_BODY);
             if (r == M2F_OK) g.stamp("end");

@@ -75,6 +75,8 @@ class _Plan:
         self.ws_bytes = int(L.m2f_plan_workspace_bytes(h))
         self.ws = torch.empty(self.ws_bytes, dtype=torch.uint8, device=model._arena.device)
         self.token = 0  # bumped by every forward; a backward must match the forward that filled the workspace
+        if training and model._exchange is not None:
+            model._attach_exchange(self)
 
     def destroy(self):
         if self.handle:
@@ -156,6 +158,7 @@ class M2FNet(nn.Module):
         self._plist = [p for p, _, _ in self._flat]
         self._anchor_box = [None]  # in a list: assigning a Parameter as an attribute would register it under that name
         self._grad_arena: Optional[torch.Tensor] = None
+        self._exchange = None            # (PeerGroup, scale, ctas, bucket_floats): gradient exchange inside the backward
         self._grad_views = None          # p.grad views into the gradient arena, built once
         self._grads_cleared = False      # FusedAdam.zero_grad(): views still attached, contents dead
         self._shadow: Optional[torch.Tensor] = None
@@ -301,7 +304,16 @@ class M2FNet(nn.Module):
         if self._grad_views is None:
             self._grad_views = [self._grad_arena[o:o + n].view(p.shape) for p, o, n in self._flat]
         target = self._grad_arena if fresh else torch.empty_like(self._grad_arena)
-        if self._bucket_hook is not None and fresh:
+        if self._exchange is not None:
+            if not fresh:
+                raise RuntimeError("data-parallel M2FNet needs zero_grad(set_to_none=True) (gradient accumulation across "
+                                   "backwards is not supported with the in-backward gradient exchange)")
+            # every finished range is all-reduced by kernels inside the backward's graph; nothing to do per range on the host
+            _lib.check(_lib.lib().m2f_plan_backward_bucketed(plan.handle, self._arena.data_ptr(), self._shadow.data_ptr(),
+                                                             plan.ws.data_ptr(), dlogits.data_ptr(), target.data_ptr(),
+                                                             int(self._exchange[3]), None, None, _stream()), "plan_backward (exchange)")
+            self.exchange_ranges = int(_lib.lib().m2f_plan_exchange_ranges(plan.handle))
+        elif self._bucket_hook is not None and fresh:
             errors = []
 
             def _cb(_user, lo, hi, ready):
@@ -393,6 +405,22 @@ class M2FNet(nn.Module):
 
     def flat_grads(self) -> Optional[torch.Tensor]:
         return self._grad_arena
+
+    def _attach_exchange(self, plan: "_Plan"):
+        pg, scale, ctas, _ = self._exchange
+        _lib.check(_lib.lib().m2f_plan_set_exchange(plan.handle, C.byref(pg), float(scale), int(ctas)), "plan_set_exchange")
+
+    def set_exchange(self, peer_group, scale: float = 1.0, ctas: int = 0, bucket_floats: int = 4 << 20):
+        """Attach (or with None detach) a peer gradient exchange: the backward all-reduces each finished range of the
+        gradient arena itself (m2f_plan_set_exchange).  The gradient arena must already be this rank's copy of the
+        symmetric buffer the group describes (`adopt_grad_arena`)."""
+        self._exchange = None if peer_group is None else (peer_group, float(scale), int(ctas), int(bucket_floats))
+        for pl in self._plans.values():
+            if pl.training and pl.handle:
+                if self._exchange is None:
+                    _lib.check(_lib.lib().m2f_plan_set_exchange(pl.handle, None, 1.0, 0), "plan_set_exchange")
+                else:
+                    self._attach_exchange(pl)
 
     def adopt_grad_arena(self, buf: Optional[torch.Tensor]):
         """Make the backward write its gradients into `buf` (fp32, arena_floats elements, on the model's device) -- the

@@ -74,10 +74,18 @@ class PeerGradExchange:
     (`multimem.ld_reduce` / `multimem.st`), launched on the stream the backward reports the range on.  torch is used for
     the allocation and the handle exchange only.
 
-    Environment: M2F_EXCHANGE_MC=0 forces the peer load / store variant, M2F_EXCHANGE_CTAS sets the CTAs per call."""
+    Two ways to drive it: `in_graph=True` (default) hands the group to the model, whose backward then launches the exchange
+    kernels itself, captured in its CUDA graph (m2f_plan_set_exchange: no host work per range); `in_graph=False` launches
+    them from the bucket callback like the NCCL reducer does.
 
-    def __init__(self, model, group=None, average: bool = True, ctas: int = 0):
+    Environment: M2F_EXCHANGE_MC=0 forces the peer load / store variant, M2F_EXCHANGE_CTAS sets the CTAs per call,
+    M2F_EXCHANGE_IN_GRAPH=0 selects the callback mode."""
+
+    def __init__(self, model, group=None, average: bool = True, ctas: int = 0, in_graph: Optional[bool] = None):
         import torch.distributed._symmetric_memory as symm_mem
+
+        self.model = model
+        self.in_graph = (os.environ.get("M2F_EXCHANGE_IN_GRAPH", "1") != "0") if in_graph is None else bool(in_graph)
 
         self.group = group if group is not None else dist.group.WORLD
         self.world = dist.get_world_size(self.group)
@@ -116,6 +124,18 @@ class PeerGradExchange:
         self.log: List[Tuple[int, int]] = []
         self.bytes_last_step = 0
         model.adopt_grad_arena(self.grads)
+
+    def attach(self, bucket_floats: int):
+        """Called by DataParallelM2FNet once the bucket size is known."""
+        if self.in_graph:
+            self.model.set_exchange(self.pg, self.scale, self.ctas, bucket_floats)
+            self.model.set_grad_hooks(None, 0, None)
+        else:
+            self.model.set_exchange(None)
+
+    @property
+    def calls_per_step(self) -> int:
+        return int(getattr(self.model, "exchange_ranges", 0)) if self.in_graph else len(self.log)
 
     def begin_step(self):
         self.log = []
@@ -171,6 +191,7 @@ class DataParallelM2FNet(torch.nn.Module):
                 if exchange == "peer":
                     raise RuntimeError(f"peer gradient exchange unavailable: {err!r}")
                 if self.reducer is not None:
+                    model.set_exchange(None)
                     model.adopt_grad_arena(None)
                     self.reducer = None
                 if dist.get_rank(group) == 0:
@@ -182,6 +203,8 @@ class DataParallelM2FNet(torch.nn.Module):
             bucket_mb = 16.0 if self.exchange == "peer" else 128.0
         self.bucket_mb = float(bucket_mb)
         model.set_grad_hooks(self._on_bucket, int(self.bucket_mb * (1 << 20) / 4), self.reducer.finish)
+        if self.exchange == "peer":
+            self.reducer.attach(int(self.bucket_mb * (1 << 20) / 4))
         self._first = True
 
     def _on_bucket(self, lo: int, hi: int):

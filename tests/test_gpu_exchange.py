@@ -60,7 +60,8 @@ def test_bad_arguments_are_errors():
     assert lib.m2f_grad_allreduce_peer(None, 0, 16, 1.0, 0, None) == L.M2F_ERR_ARG
 
 
-def _worker(rank, world, port, out):
+def _worker(rank, world, port, out, in_graph):
+    os.environ["M2F_EXCHANGE_IN_GRAPH"] = "1" if in_graph else "0"
     import importlib
     import sys
     import torch.distributed as dist
@@ -119,7 +120,8 @@ def _worker(rank, world, port, out):
     crit(net(b["text"], b["audio"], b["padding_mask"]).permute(0, 2, 1), b["emotion"]).backward()
     torch.cuda.synchronize()
     g_dp = model.flat_grads().clone()
-    res["buckets"] = len(ex.log)
+    res["buckets"] = ex.calls_per_step
+    res["in_graph"] = ex.in_graph
     solo = pkg.M2FNet(cfg, planes=3).to("cuda").train()
     solo.load_state_dict(model.state_dict())
     fb = {k: v.cuda() for k, v in full.items()}
@@ -151,16 +153,18 @@ def _worker(rank, world, port, out):
     dist.destroy_process_group()
 
 
-def test_dp2_peer_exchange_equals_single_gpu(tmp_path):
+@pytest.mark.parametrize("in_graph", [True, False], ids=["in_graph", "callbacks"])
+def test_dp2_peer_exchange_equals_single_gpu(tmp_path, in_graph):
     if torch.cuda.device_count() < 2:
         pytest.skip("needs 2 GPUs")
     import torch.multiprocessing as mp
     out = str(tmp_path / "peer.pt")
-    mp.spawn(_worker, args=(2, 29641, out), nprocs=2, join=True)
+    mp.spawn(_worker, args=(2, 29641 + int(in_graph), out, in_graph), nprocs=2, join=True)
     r = torch.load(out)
     if "unavailable" in r:
         pytest.skip("symmetric memory unavailable on this box: " + r["unavailable"])
     print(r)
+    assert r["in_graph"] == in_graph
     for variant, e in r["kernel_max_abs_err"].items():
         assert e < 1e-5, (variant, r)
     assert r["same"] and r["buckets"] >= 3

@@ -56,6 +56,30 @@ dist.barrier()
 print(f"[rank {rank}] untraced step: fwd+loss {ev[0].elapsed_time(ev[1]):.3f} ms, bwd (+exchange wait) {ev[1].elapsed_time(ev[2]):.3f} ms, "
       f"adam {ev[2].elapsed_time(ev[3]):.3f} ms", flush=True)
 
+# host time per step: how long the Python thread needs to enqueue a step (no device sync inside the loop)
+import time
+torch.cuda.synchronize()
+dist.barrier()
+t_h = [0.0, 0.0, 0.0, 0.0]
+w0 = time.perf_counter()
+for i in range(20):
+    a = time.perf_counter()
+    opt.zero_grad(set_to_none=True)
+    loss = crit(net(b["text"], b["audio"], b["padding_mask"]).permute(0, 2, 1), b["emotion"])
+    c1 = time.perf_counter()
+    loss.backward()
+    c2 = time.perf_counter()
+    opt.step()
+    c3 = time.perf_counter()
+    t_h[0] += c1 - a
+    t_h[1] += c2 - c1
+    t_h[2] += c3 - c2
+w1 = time.perf_counter()
+torch.cuda.synchronize()
+w2 = time.perf_counter()
+print(f"[rank {rank}] host enqueue per step: fwd+loss {t_h[0] / 20 * 1e3:.3f} ms, bwd {t_h[1] / 20 * 1e3:.3f} ms, adam {t_h[2] / 20 * 1e3:.3f} ms; "
+      f"loop {1e3 * (w1 - w0) / 20:.3f} ms/step, with final sync {1e3 * (w2 - w0) / 20:.3f} ms/step", flush=True)
+
 rows, t0 = [], 0
 for line in open(tl_file):
     if line.startswith("#t0_ns"):
@@ -67,7 +91,7 @@ if net.exchange == "peer":
     N = 512
     buf = (ctypes.c_uint64 * (N * 6))()
     n = int(L.m2f_exchange_trace(buf))
-    per_step = len(net.reducer.log)
+    per_step = net.reducer.calls_per_step
     # the traced backward is call number STEP (1-based) of STEP + 2: its records are [per_step*(STEP-1), per_step*STEP)
     for k in range(per_step * (STEP - 1), per_step * STEP):
         r = [int(buf[(k % N) * 6 + j]) for j in range(6)]
