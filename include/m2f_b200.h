@@ -253,6 +253,10 @@ typedef struct {
  * With world == 1 it degenerates to an in-place scale (used by the single-GPU tests of the slicing arithmetic). */
 int m2f_grad_allreduce_peer(const m2f_peer_group_t* g, int64_t lo, int64_t hi, float scale, int32_t ctas, void* stream);
 
+/* Tuning knob: CTA shape of the exchange kernel -- threads x unroll x 16 B of loads in flight per CTA; one of
+ * (512,8) [default], (512,4), (256,8), (256,16), (1024,4), (128,16).  Process-wide; every rank must set the same. */
+int m2f_exchange_tune(int32_t threads, int32_t unroll);
+
 /* The exchange as part of the backward: after this call m2f_plan_backward_bucketed(..., bucket_floats > 0, cb = NULL, ...)
  * all-reduces every finished gradient range itself -- m2f_grad_allreduce_peer on the plan's ready stream, captured into
  * the backward's CUDA graph, so a data-parallel step needs no host work per range -- and the caller's stream continues

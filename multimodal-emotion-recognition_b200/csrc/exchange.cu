@@ -114,10 +114,8 @@ __device__ unsigned int g_xchg_trace_n;
 
 // float offsets: [lo, lo + head) scalar, then n4 float4, then `tail` scalars; head / tail < 4 (arena ranges that do not
 // start or end on 16 bytes, e.g. the 7-wide classifier bias at the end of the 1-D region)
-constexpr int XCHG_THREADS = 512;
-constexpr int XCHG_UNROLL = 8;  // 512 threads x 8 x 16 B = 64 KB of loads in flight per CTA
-
-template <bool MC>
+// THREADS x UNROLL x 16 B of loads are in flight per CTA (512 x 8: 64 KB)
+template <bool MC, int XCHG_THREADS, int XCHG_UNROLL>
 __global__ void __launch_bounds__(XCHG_THREADS)
 grad_allreduce_kernel(float* __restrict__ mc, PeerPtrs pp, int rank, int world, int64_t lo, int head, int64_t n4, int tail, float scale) {
     const bool tracer = blockIdx.x == 0 && threadIdx.x == 0;
@@ -192,6 +190,18 @@ grad_allreduce_kernel(float* __restrict__ mc, PeerPtrs pp, int rank, int world, 
 
 using namespace m2f;
 
+// launch shape (tools/exchange_sweep.py): every rank must use the same one
+static int g_xchg_threads = 512, g_xchg_unroll = 8;
+
+extern "C" int m2f_exchange_tune(int32_t threads, int32_t unroll) {
+    const bool ok = (threads == 512 && (unroll == 8 || unroll == 4)) || (threads == 256 && (unroll == 8 || unroll == 16)) ||
+                    (threads == 1024 && unroll == 4) || (threads == 128 && unroll == 16);
+    M2F_REQUIRE(ok, M2F_ERR_UNSUPPORTED, "exchange_tune: (threads, unroll) must be one of (512,8) (512,4) (256,8) (256,16) (1024,4) (128,16)");
+    g_xchg_threads = threads;
+    g_xchg_unroll = unroll;
+    return M2F_OK;
+}
+
 extern "C" int m2f_grad_allreduce_peer(const m2f_peer_group_t* g, int64_t lo, int64_t hi, float scale, int32_t ctas, void* stream) {
     M2F_REQUIRE(g != nullptr, M2F_ERR_ARG, "grad_allreduce_peer: group is NULL");
     M2F_REQUIRE(g->world >= 1 && g->world <= M2F_XCHG_MAX_RANKS && g->rank >= 0 && g->rank < g->world, M2F_ERR_ARG,
@@ -222,20 +232,32 @@ extern "C" int m2f_grad_allreduce_peer(const m2f_peer_group_t* g, int64_t lo, in
     // for the large slices of a small world, a handful of CTAs for the small slices of a large one.  Every rank must use the
     // same count (the barrier slots are per block): it depends on the range, the world size and `ctas` only.
     const int64_t per_rank = (n4 + g->world - 1) / g->world;
+    const int threads = g_xchg_threads, unroll = g_xchg_unroll;
+    const int64_t per_iter = (int64_t)threads * unroll;  // vectors one CTA moves per loop iteration
     int grid;
     if (ctas > 0) {
         grid = ctas;
     } else {
-        const int64_t want = (per_rank * 16 + (256 << 10) - 1) / (256 << 10);
+        const int64_t want = (per_rank + 4 * per_iter - 1) / (4 * per_iter);
         grid = want < 1 ? 1 : (want > M2F_XCHG_MAX_CTAS ? M2F_XCHG_MAX_CTAS : (int)want);
     }
     if (grid > M2F_XCHG_MAX_CTAS) grid = M2F_XCHG_MAX_CTAS;
-    const int64_t need = (per_rank + XCHG_THREADS * XCHG_UNROLL - 1) / (XCHG_THREADS * XCHG_UNROLL);
+    const int64_t need = (per_rank + per_iter - 1) / per_iter;
     if (need < grid) grid = need < 1 ? 1 : (int)need;
     cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
     float* mc = reinterpret_cast<float*>(g->mc_base);
-    if (mc) grad_allreduce_kernel<true><<<grid, XCHG_THREADS, 0, st>>>(mc, pp, g->rank, g->world, lo, head, n4, tail, scale);
-    else    grad_allreduce_kernel<false><<<grid, XCHG_THREADS, 0, st>>>(nullptr, pp, g->rank, g->world, lo, head, n4, tail, scale);
+#define M2F_XCHG_LAUNCH(T, U)                                                                                                          \
+    if (threads == T && unroll == U) {                                                                                                 \
+        if (mc) grad_allreduce_kernel<true, T, U><<<grid, T, 0, st>>>(mc, pp, g->rank, g->world, lo, head, n4, tail, scale);             \
+        else    grad_allreduce_kernel<false, T, U><<<grid, T, 0, st>>>(nullptr, pp, g->rank, g->world, lo, head, n4, tail, scale);        \
+    }
+    M2F_XCHG_LAUNCH(512, 8)
+    M2F_XCHG_LAUNCH(512, 4)
+    M2F_XCHG_LAUNCH(256, 8)
+    M2F_XCHG_LAUNCH(256, 16)
+    M2F_XCHG_LAUNCH(1024, 4)
+    M2F_XCHG_LAUNCH(128, 16)
+#undef M2F_XCHG_LAUNCH
     M2F_LAUNCH_CHECK();
     return M2F_OK;
 }

@@ -239,6 +239,7 @@ struct m2f_plan {
         GraphKey key;
         long long kernels = 0;
         std::vector<std::pair<int64_t, int64_t>> marks;  // gradient ranges reported through external events (data parallel)
+        int64_t xchg_ranges = 0;                         // exchange kernels captured in this graph
         void reset() {
             if (exec) cudaGraphExecDestroy(exec);
             exec = nullptr;
@@ -979,15 +980,19 @@ static int backward_modality(Ctx& c, Modality& mo, const uint8_t* key_pad, const
             OP(m2f_ln_bwd(A, gld, c.f32(e.y2), e.y2.ld, c.prm(e.g2), c.f32(e.st2), M, D, Bq, gld, &dx2, pd, seed, step,
                                M2F_SITE_ENC(mo.idx, t, l, 3), c.grd(e.g2), c.grd(e.be2), c.grd(e.w2.b_off), c.stream()));
             M2F_TRY(lin_wgrad(c, wst, dx2, h, c.grd(e.w2.w_off), e.w2.in, nullptr, e.w2.out, e.w2.in));
+            // the layer computed last: hand its weights over one by one, so that only the final one is left behind the backward
+            if (first) M2F_TRY(c.done_down_to(e.w2.w_off, true));
             // dh = (d y2 . W2) * [h > 0] / (1-p)   (relu + dropout backward from the saved output)
             OP(c.gemm(dx2, false, c.pv(e.w2.w), true, M, e.w2.in, Epi().gate(h, inv_keep(pd)).pl(dhp).colsum(c.grd(e.w1.b_off))));
             M2F_TRY(lin_wgrad(c, wst, dhp, x1p, c.grd(e.w1.w_off), e.w1.in, nullptr, e.w1.out, e.w1.in));
+            if (first) M2F_TRY(c.done_down_to(e.w1.w_off, true));
             // A = d x1 = dh . W1 + d y2
             OP(c.gemm(dhp, false, c.pv(e.w1.w), true, M, D, Epi().resid(Bq, gld).f32(A, gld)));
             // LN1: A -> Bq = d y1, dx1 = dropmask1(d y1), dbo += colsum
             OP(m2f_ln_bwd(A, gld, c.f32(e.y1), e.y1.ld, c.prm(e.g1), c.f32(e.st1), M, D, Bq, gld, &dx1, pd, seed, step,
                                M2F_SITE_ENC(mo.idx, t, l, 1), c.grd(e.g1), c.grd(e.be1), c.grd(e.wo.b_off), c.stream()));
             M2F_TRY(lin_wgrad(c, wst, dx1, o, c.grd(e.wo.w_off), e.wo.in, nullptr, e.wo.out, e.wo.in));
+            if (first) M2F_TRY(c.done_down_to(e.wo.w_off, true));
             OP(c.gemm(dx1, false, c.pv(e.wo.w), true, M, D, Epi().pl(dop)));
             m2f_planes_t q = Ctx::cols(qkv, 0, D), k = Ctx::cols(qkv, D, D), v = Ctx::cols(qkv, 2 * D, D);
             m2f_planes_t dq = Ctx::cols(dqkvp, 0, D), dk = Ctx::cols(dqkvp, D, D), dv = Ctx::cols(dqkvp, 2 * D, D);
@@ -1580,6 +1585,10 @@ extern "C" int m2f_plan_backward_bucketed(m2f_plan_t* p, const float* params, co
             if (r == M2F_OK) g.stamp("end");
             return r;
         });
+        if (rc == M2F_OK && c.xchg) {
+            if (captured) p->gb.xchg_ranges = p->xchg_ranges;
+            else p->xchg_ranges = p->gb.xchg_ranges;
+        }
         if (rc == M2F_OK && cb) {
             if (captured) p->gb.marks = marks;
             for (size_t k = 0; k < p->gb.marks.size(); ++k) {
