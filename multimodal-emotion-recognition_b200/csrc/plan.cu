@@ -943,6 +943,13 @@ static int lin_wgrad(Ctx& c, cudaStream_t wst, const m2f_planes_t& dY, const m2f
     return rc;
 }
 
+// M2F_FINE_TAIL=1: the layer computed last reports its four weight gradients one by one (shorter exchange after the end of
+// the backward, three more exchange calls per stack)
+static bool fine_tail() {
+    static const bool on = [] { const char* e = std::getenv("M2F_FINE_TAIL"); return e && e[0] == '1'; }();
+    return on;
+}
+
 // One modality stack, last layer first.  The data-gradient chain runs on the current stream; every weight gradient goes
 // to `wst` (they are off the critical path).  The operand buffers the weight-gradient stream reads alternate between two
 // sets by layer parity; a set is reused only after the weight gradients of its previous user (two layers earlier) are done.
@@ -981,18 +988,18 @@ static int backward_modality(Ctx& c, Modality& mo, const uint8_t* key_pad, const
                                M2F_SITE_ENC(mo.idx, t, l, 3), c.grd(e.g2), c.grd(e.be2), c.grd(e.w2.b_off), c.stream()));
             M2F_TRY(lin_wgrad(c, wst, dx2, h, c.grd(e.w2.w_off), e.w2.in, nullptr, e.w2.out, e.w2.in));
             // the layer computed last: hand its weights over one by one, so that only the final one is left behind the backward
-            if (first) M2F_TRY(c.done_down_to(e.w2.w_off, true));
+            if (first && fine_tail()) M2F_TRY(c.done_down_to(e.w2.w_off, true));
             // dh = (d y2 . W2) * [h > 0] / (1-p)   (relu + dropout backward from the saved output)
             OP(c.gemm(dx2, false, c.pv(e.w2.w), true, M, e.w2.in, Epi().gate(h, inv_keep(pd)).pl(dhp).colsum(c.grd(e.w1.b_off))));
             M2F_TRY(lin_wgrad(c, wst, dhp, x1p, c.grd(e.w1.w_off), e.w1.in, nullptr, e.w1.out, e.w1.in));
-            if (first) M2F_TRY(c.done_down_to(e.w1.w_off, true));
+            if (first && fine_tail()) M2F_TRY(c.done_down_to(e.w1.w_off, true));
             // A = d x1 = dh . W1 + d y2
             OP(c.gemm(dhp, false, c.pv(e.w1.w), true, M, D, Epi().resid(Bq, gld).f32(A, gld)));
             // LN1: A -> Bq = d y1, dx1 = dropmask1(d y1), dbo += colsum
             OP(m2f_ln_bwd(A, gld, c.f32(e.y1), e.y1.ld, c.prm(e.g1), c.f32(e.st1), M, D, Bq, gld, &dx1, pd, seed, step,
                                M2F_SITE_ENC(mo.idx, t, l, 1), c.grd(e.g1), c.grd(e.be1), c.grd(e.wo.b_off), c.stream()));
             M2F_TRY(lin_wgrad(c, wst, dx1, o, c.grd(e.wo.w_off), e.wo.in, nullptr, e.wo.out, e.wo.in));
-            if (first) M2F_TRY(c.done_down_to(e.wo.w_off, true));
+            if (first && fine_tail()) M2F_TRY(c.done_down_to(e.wo.w_off, true));
             OP(c.gemm(dx1, false, c.pv(e.wo.w), true, M, D, Epi().pl(dop)));
             m2f_planes_t q = Ctx::cols(qkv, 0, D), k = Ctx::cols(qkv, D, D), v = Ctx::cols(qkv, 2 * D, D);
             m2f_planes_t dq = Ctx::cols(dqkvp, 0, D), dk = Ctx::cols(dqkvp, D, D), dv = Ctx::cols(dqkvp, 2 * D, D);

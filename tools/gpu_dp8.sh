@@ -1,0 +1,17 @@
+set -x
+N=${1:-8}
+mkdir -p gpurun_out
+TR="python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29761"
+show() { python - "$1" <<'PY'
+import json, sys
+for l in open(sys.argv[1]):
+    if l.startswith('{'):
+        d = json.loads(l)
+        print(sys.argv[1], 'value', round(d['value']), 'ms', round(d['ms_per_step'], 3), 'e2e', d.get('e2e') and round(d['e2e']['ms_per_step'], 3), d['config'].get('exchange_launch'), d['config'].get('exchange_calls_per_step'))
+PY
+}
+run() { name=$1; shift; timeout 300 $TR bench.py --gpus $N --steps 20 --warmup 5 "$@" > gpurun_out/bench${N}_$name.json 2> gpurun_out/bench${N}_$name.err; show gpurun_out/bench${N}_$name.json; }
+run peer_graph16 --exchange peer --no-e2e
+run peer_graph32 --exchange peer --no-e2e --bucket-mb 32
+M2F_FINE_TAIL=1 run peer_graph16_fine --exchange peer --no-e2e
+timeout 300 $TR tools/dp_trace.py peer 16 gpurun_out/trace${N}_peer_graph 2>&1 | grep "^\[rank [01]\]"
