@@ -238,6 +238,7 @@ int m2f_plan_backward_bucketed(m2f_plan_t* p, const float* params, const void* s
  * the gradients, zeroed once before the first call (and after any aborted one). */
 #define M2F_XCHG_MAX_RANKS 16
 #define M2F_XCHG_MAX_CTAS 64
+#define M2F_XCHG_NO_EXIT_BARRIER 1
 #define M2F_XCHG_SIGNAL_BYTES (M2F_XCHG_MAX_CTAS * M2F_XCHG_MAX_RANKS * 4)
 typedef struct {
     void* mc_base;                        /* multicast mapping of the buffer (multimem.ld_reduce / multimem.st), or NULL */
@@ -249,9 +250,12 @@ typedef struct {
 /* In-place all-reduce of the float range [lo, hi) of the symmetric buffer: on return of the *kernel* every rank holds
  * scale * sum over ranks.  Two-shot: rank r reduces slice r (in the switch with multicast, by world peer loads without)
  * and writes it to every rank.  Stream-ordered; every rank must issue the same sequence of calls (same lo, hi, ctas)
- * and have one GPU to itself -- the kernels of the ranks wait for each other.  ctas <= 0: one CTA per 256 KB of a rank's slice, at most 64.
+ * and have one GPU to itself -- the kernels of the ranks wait for each other.  ctas <= 0: one CTA per 64 KB of a rank's slice, at most 64.
+ * flags: M2F_XCHG_NO_EXIT_BARRIER skips the closing handshake -- allowed on every call of a sequence on one stream except the
+ * last one, whose handshake then covers the whole sequence (consumers must wait for that last kernel).
  * With world == 1 it degenerates to an in-place scale (used by the single-GPU tests of the slicing arithmetic). */
-int m2f_grad_allreduce_peer(const m2f_peer_group_t* g, int64_t lo, int64_t hi, float scale, int32_t ctas, void* stream);
+int m2f_grad_allreduce_peer(const m2f_peer_group_t* g, int64_t lo, int64_t hi, float scale, int32_t ctas, int32_t flags,
+                            void* stream);
 
 /* Tuning knob: CTA shape of the exchange kernel -- threads x unroll x 16 B of loads in flight per CTA; one of
  * (512,8) [default], (512,4), (256,8), (256,16), (1024,4), (128,16).  Process-wide; every rank must set the same. */

@@ -51,6 +51,7 @@ class ModelCfg(C.Structure):
 
 XCHG_MAX_RANKS, XCHG_MAX_CTAS = 16, 64
 XCHG_SIGNAL_BYTES = XCHG_MAX_CTAS * XCHG_MAX_RANKS * 4
+XCHG_NO_EXIT_BARRIER = 1
 
 
 class PeerGroup(C.Structure):
@@ -96,7 +97,7 @@ PROTOTYPES = {
     "m2f_plan_loss": [_vp, _vp, _vp, _vp, _vp, _f32, _f32, _vp, _vp],
     "m2f_plan_backward": [_vp, _vp, _vp, _vp, _vp, _vp, _vp],
     "m2f_plan_backward_bucketed": [_vp, _vp, _vp, _vp, _vp, _vp, _i64, _vp, _vp, _vp],
-    "m2f_grad_allreduce_peer": [C.POINTER(PeerGroup), _i64, _i64, _f32, _i32, _vp],
+    "m2f_grad_allreduce_peer": [C.POINTER(PeerGroup), _i64, _i64, _f32, _i32, _i32, _vp],
     "m2f_exchange_trace": [_vp],
     "m2f_exchange_tune": [_i32, _i32],
     "m2f_plan_set_exchange": [_vp, C.POINTER(PeerGroup), _f32, _i32],

@@ -117,7 +117,7 @@ __device__ unsigned int g_xchg_trace_n;
 // THREADS x UNROLL x 16 B of loads are in flight per CTA (512 x 8: 64 KB)
 template <bool MC, int XCHG_THREADS, int XCHG_UNROLL>
 __global__ void __launch_bounds__(XCHG_THREADS)
-grad_allreduce_kernel(float* __restrict__ mc, PeerPtrs pp, int rank, int world, int64_t lo, int head, int64_t n4, int tail, float scale) {
+grad_allreduce_kernel(float* __restrict__ mc, PeerPtrs pp, int rank, int world, int64_t lo, int head, int64_t n4, int tail, float scale, int flags) {
     const bool tracer = blockIdx.x == 0 && threadIdx.x == 0;
     unsigned long long* tr = nullptr;
     if (tracer) {
@@ -182,7 +182,10 @@ grad_allreduce_kernel(float* __restrict__ mc, PeerPtrs pp, int rank, int world, 
     }
     __threadfence_system();
     if (tracer) tr[2] = gtimer();
-    block_barrier_all_ranks(pp, rank, world);
+    // Exit barrier: "every rank has stored its slice into my copy".  A sequence of exchanges on one stream needs it on the last
+    // call only: a rank's stores of call k are complete before its kernel of call k+1 starts, so the last call's handshake
+    // vouches for all of them (the ranges are disjoint and nobody reads them in between).
+    if (!(flags & M2F_XCHG_NO_EXIT_BARRIER)) block_barrier_all_ranks(pp, rank, world);
     if (tracer) tr[3] = gtimer();
 }
 
@@ -202,7 +205,8 @@ extern "C" int m2f_exchange_tune(int32_t threads, int32_t unroll) {
     return M2F_OK;
 }
 
-extern "C" int m2f_grad_allreduce_peer(const m2f_peer_group_t* g, int64_t lo, int64_t hi, float scale, int32_t ctas, void* stream) {
+extern "C" int m2f_grad_allreduce_peer(const m2f_peer_group_t* g, int64_t lo, int64_t hi, float scale, int32_t ctas, int32_t flags,
+                                       void* stream) {
     M2F_REQUIRE(g != nullptr, M2F_ERR_ARG, "grad_allreduce_peer: group is NULL");
     M2F_REQUIRE(g->world >= 1 && g->world <= M2F_XCHG_MAX_RANKS && g->rank >= 0 && g->rank < g->world, M2F_ERR_ARG,
                 "grad_allreduce_peer: rank %d / world %d outside [1, %d]", g->rank, g->world, M2F_XCHG_MAX_RANKS);
@@ -226,11 +230,12 @@ extern "C" int m2f_grad_allreduce_peer(const m2f_peer_group_t* g, int64_t lo, in
     const int head = (int)((4 - (lo & 3)) & 3) < (hi - lo) ? (int)((4 - (lo & 3)) & 3) : (int)(hi - lo);
     const int64_t n4 = (hi - lo - head) / 4;
     const int tail = (int)(hi - lo - head - 4 * n4);
-    // The kernel is latency-bound (a multimem load takes microseconds): SM time spent = bytes x latency / bytes in flight per
-    // CTA, whatever the CTA count, and every resident CTA displaces one of the backward's GEMM CTAs (they fill the register
-    // file).  So: as much in flight per CTA as registers allow, and one CTA per 256 KB of this rank's slice -- a short kernel
-    // for the large slices of a small world, a handful of CTAs for the small slices of a large one.  Every rank must use the
-    // same count (the barrier slots are per block): it depends on the range, the world size and `ctas` only.
+    // The kernel is latency-bound (a multimem load round trip through the switch takes microseconds; measured with
+    // tools/exchange_sweep.py): SM time spent = bytes x latency / bytes in flight per CTA whatever the CTA count, and every
+    // resident CTA displaces one of the backward's GEMM CTAs (they fill the register file).  So: as much in flight per CTA as
+    // registers allow, and enough CTAs (up to 64) that each makes one pass -- the call is then as short as one round trip,
+    // which is what the exchange of the last ranges, behind the end of the backward, costs.  Every rank must use the same
+    // count (the barrier slots are per block): it depends on the range, the world size and `ctas` only.
     const int64_t per_rank = (n4 + g->world - 1) / g->world;
     const int threads = g_xchg_threads, unroll = g_xchg_unroll;
     const int64_t per_iter = (int64_t)threads * unroll;  // vectors one CTA moves per loop iteration
@@ -238,7 +243,7 @@ extern "C" int m2f_grad_allreduce_peer(const m2f_peer_group_t* g, int64_t lo, in
     if (ctas > 0) {
         grid = ctas;
     } else {
-        const int64_t want = (per_rank + 4 * per_iter - 1) / (4 * per_iter);
+        const int64_t want = (per_rank + per_iter - 1) / per_iter;
         grid = want < 1 ? 1 : (want > M2F_XCHG_MAX_CTAS ? M2F_XCHG_MAX_CTAS : (int)want);
     }
     if (grid > M2F_XCHG_MAX_CTAS) grid = M2F_XCHG_MAX_CTAS;
@@ -248,8 +253,8 @@ extern "C" int m2f_grad_allreduce_peer(const m2f_peer_group_t* g, int64_t lo, in
     float* mc = reinterpret_cast<float*>(g->mc_base);
 #define M2F_XCHG_LAUNCH(T, U)                                                                                                          \
     if (threads == T && unroll == U) {                                                                                                 \
-        if (mc) grad_allreduce_kernel<true, T, U><<<grid, T, 0, st>>>(mc, pp, g->rank, g->world, lo, head, n4, tail, scale);             \
-        else    grad_allreduce_kernel<false, T, U><<<grid, T, 0, st>>>(nullptr, pp, g->rank, g->world, lo, head, n4, tail, scale);        \
+        if (mc) grad_allreduce_kernel<true, T, U><<<grid, T, 0, st>>>(mc, pp, g->rank, g->world, lo, head, n4, tail, scale, flags);      \
+        else    grad_allreduce_kernel<false, T, U><<<grid, T, 0, st>>>(nullptr, pp, g->rank, g->world, lo, head, n4, tail, scale, flags); \
     }
     M2F_XCHG_LAUNCH(512, 8)
     M2F_XCHG_LAUNCH(512, 4)

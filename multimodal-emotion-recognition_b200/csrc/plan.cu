@@ -684,9 +684,9 @@ struct Ctx {
     bool ready_in_capture = false;
     bool xchg = false;       // exchange the range here (kernel on `ready`, captured with the graph) instead of telling the caller
     bool capturing = false;
-    int report(int64_t lo, int64_t hi_, cudaStream_t ready) {
-        if (xchg) {
-            M2F_TRY(m2f_grad_allreduce_peer(&p->xchg_group, lo, hi_, p->xchg_scale, p->xchg_ctas, ready));
+    int report(int64_t lo, int64_t hi_, cudaStream_t ready, bool last = false) {
+        if (xchg) {  // one sequence on `ready`: only the last call needs the closing handshake
+            M2F_TRY(m2f_grad_allreduce_peer(&p->xchg_group, lo, hi_, p->xchg_scale, p->xchg_ctas, last ? 0 : M2F_XCHG_NO_EXIT_BARRIER, ready));
             ++p->xchg_ranges;
             if (ready != st) ready_in_capture = true;
             return M2F_OK;
@@ -1176,7 +1176,7 @@ static int backward_all(Ctx& c, const uint8_t* key_pad, const float* dlogits, in
     if (c.cb || c.marks || c.xchg) {  // biases / LayerNorm parameters (atomically accumulated by every stream): final once everything has joined
         cudaStream_t ready = p->use_streams ? p->ready : c.st;
         M2F_TRY(c.dep(c.st, ready));
-        M2F_TRY(c.report(md->off_1d, md->arena_floats, ready));
+        M2F_TRY(c.report(md->off_1d, md->arena_floats, ready, true));
         // a capture must end with every forked stream joined; with the exchange inside the backward the caller's stream
         // continues (optimizer) only after the last range has been exchanged
         if ((c.marks || c.xchg) && c.ready_in_capture) M2F_TRY(c.dep(ready, c.st));

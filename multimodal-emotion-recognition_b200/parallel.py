@@ -148,7 +148,7 @@ class PeerGradExchange:
         if self._dryrun:  # timing experiments only: the ranges are reported but not exchanged
             self.log.append((lo, hi))
             return
-        _lib.check(_lib.lib().m2f_grad_allreduce_peer(ctypes.byref(self.pg), lo, hi, self.scale, self.ctas, st.cuda_stream),
+        _lib.check(_lib.lib().m2f_grad_allreduce_peer(ctypes.byref(self.pg), lo, hi, self.scale, self.ctas, 0, st.cuda_stream),
                    "grad_allreduce_peer")
         self._ev.record(st)
         self._pending = True

@@ -68,8 +68,8 @@ def test_struct_layouts_match_the_header(pkg, tmp_path):
 def test_exchange_argument_errors_without_a_gpu(pkg):
     L = pkg._lib
     lib = L.lib()
-    assert lib.m2f_grad_allreduce_peer(None, 0, 16, 1.0, 0, None) == L.M2F_ERR_ARG
+    assert lib.m2f_grad_allreduce_peer(None, 0, 16, 1.0, 0, 0, None) == L.M2F_ERR_ARG
     pg = L.PeerGroup()
     pg.rank, pg.world = 0, 17
-    assert lib.m2f_grad_allreduce_peer(ctypes.byref(pg), 0, 16, 1.0, 0, None) == L.M2F_ERR_ARG
+    assert lib.m2f_grad_allreduce_peer(ctypes.byref(pg), 0, 16, 1.0, 0, 0, None) == L.M2F_ERR_ARG
     assert b"world" in lib.m2f_last_error()

@@ -37,7 +37,8 @@ def test_world1_ranges_scale_in_place():
     # aligned, unaligned head, unaligned tail, both, shorter than one vector, empty; several CTA counts
     for lo, hi, ctas in [(0, n, 0), (4096, 8192, 1), (5, 4099, 7), (8, 1003, 64), (1001, 1003, 0), (77, 78, 0), (300, 300, 0),
                          (3, n - 1, 200)]:
-        L.check(lib.m2f_grad_allreduce_peer(ctypes.byref(pg), lo, hi, 0.5, ctas, st), "grad_allreduce_peer")
+        L.check(lib.m2f_grad_allreduce_peer(ctypes.byref(pg), lo, hi, 0.5, ctas, L.XCHG_NO_EXIT_BARRIER if hi < n else 0, st),
+                "grad_allreduce_peer")
         expect[lo:hi] *= 0.5
     torch.cuda.synchronize()
     assert torch.equal(buf[:n], expect)
@@ -52,12 +53,12 @@ def test_bad_arguments_are_errors():
     pg.peer_base[0] = buf.data_ptr()
     pg.signal_off_bytes = 4096
     pg.rank, pg.world = 0, 1
-    assert lib.m2f_grad_allreduce_peer(ctypes.byref(pg), 0, 2048, 1.0, 0, None) == L.M2F_ERR_ARG  # range overlaps the signal area
+    assert lib.m2f_grad_allreduce_peer(ctypes.byref(pg), 0, 2048, 1.0, 0, 0, None) == L.M2F_ERR_ARG  # range overlaps the signal area
     pg.world = 17
-    assert lib.m2f_grad_allreduce_peer(ctypes.byref(pg), 0, 16, 1.0, 0, None) == L.M2F_ERR_ARG
+    assert lib.m2f_grad_allreduce_peer(ctypes.byref(pg), 0, 16, 1.0, 0, 0, None) == L.M2F_ERR_ARG
     pg.world, pg.rank = 2, 0  # peer 1 missing
-    assert lib.m2f_grad_allreduce_peer(ctypes.byref(pg), 0, 16, 1.0, 0, None) == L.M2F_ERR_ARG
-    assert lib.m2f_grad_allreduce_peer(None, 0, 16, 1.0, 0, None) == L.M2F_ERR_ARG
+    assert lib.m2f_grad_allreduce_peer(ctypes.byref(pg), 0, 16, 1.0, 0, 0, None) == L.M2F_ERR_ARG
+    assert lib.m2f_grad_allreduce_peer(None, 0, 16, 1.0, 0, 0, None) == L.M2F_ERR_ARG
 
 
 def _worker(rank, world, port, out, in_graph):
@@ -105,8 +106,11 @@ def _worker(rank, world, port, out, in_graph):
         torch.cuda.synchronize()
         dist.barrier()
         st = torch.cuda.current_stream().cuda_stream
-        for lo, hi, ctas in [(n // 2 + 3, n - 1, 0), (16, 4096, 3), (5, 9, 0), (4099, n // 2 + 3, 64)]:
-            L.check(lib.m2f_grad_allreduce_peer(ctypes.byref(pg), lo, hi, 0.5, ctas, st), "grad_allreduce_peer")
+        # a sequence on one stream: only the last call closes with the handshake (M2F_XCHG_NO_EXIT_BARRIER on the others)
+        seq = [(n // 2 + 3, n - 1, 0), (16, 4096, 3), (5, 9, 0), (4099, n // 2 + 3, 64)]
+        for k, (lo, hi, ctas) in enumerate(seq):
+            flags = 0 if k == len(seq) - 1 else L.XCHG_NO_EXIT_BARRIER
+            L.check(lib.m2f_grad_allreduce_peer(ctypes.byref(pg), lo, hi, 0.5, ctas, flags, st), "grad_allreduce_peer")
             expect[lo:hi] = total[lo:hi] * 0.5
         torch.cuda.synchronize()
         dist.barrier()

@@ -47,13 +47,13 @@ for kind, t, u in variants:
         for ctas in (8, 16, 32, 64):
             reps = 20 if mb < 100 else 5
             for _ in range(2):
-                L.check(lib.m2f_grad_allreduce_peer(ctypes.byref(g), 0, floats, 1.0, ctas, st), "xchg")
+                L.check(lib.m2f_grad_allreduce_peer(ctypes.byref(g), 0, floats, 1.0, ctas, 0, st), "xchg")
             torch.cuda.synchronize()
             dist.barrier()
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             e0.record()
             for _ in range(reps):
-                L.check(lib.m2f_grad_allreduce_peer(ctypes.byref(g), 0, floats, 1.0, ctas, st), "xchg")
+                L.check(lib.m2f_grad_allreduce_peer(ctypes.byref(g), 0, floats, 1.0, ctas, 0, st), "xchg")
             e1.record()
             torch.cuda.synchronize()
             us = e0.elapsed_time(e1) * 1e3 / reps
