@@ -250,7 +250,7 @@ typedef struct {
 /* In-place all-reduce of the float range [lo, hi) of the symmetric buffer: on return of the *kernel* every rank holds
  * scale * sum over ranks.  Two-shot: rank r reduces slice r (in the switch with multicast, by world peer loads without)
  * and writes it to every rank.  Stream-ordered; every rank must issue the same sequence of calls (same lo, hi, ctas)
- * and have one GPU to itself -- the kernels of the ranks wait for each other.  ctas <= 0: one CTA per 64 KB of a rank's slice, at most 64.
+ * and have one GPU to itself -- the kernels of the ranks wait for each other.  ctas <= 0: one CTA per 128 KB of a rank's slice, at most 16 (enough to saturate NVLink).
  * flags: M2F_XCHG_NO_EXIT_BARRIER skips the closing handshake -- allowed on every call of a sequence on one stream except the
  * last one, whose handshake then covers the whole sequence (consumers must wait for that last kernel).
  * With world == 1 it degenerates to an in-place scale (used by the single-GPU tests of the slicing arithmetic). */

@@ -230,12 +230,12 @@ extern "C" int m2f_grad_allreduce_peer(const m2f_peer_group_t* g, int64_t lo, in
     const int head = (int)((4 - (lo & 3)) & 3) < (hi - lo) ? (int)((4 - (lo & 3)) & 3) : (int)(hi - lo);
     const int64_t n4 = (hi - lo - head) / 4;
     const int tail = (int)(hi - lo - head - 4 * n4);
-    // The kernel is latency-bound (a multimem load round trip through the switch takes microseconds; measured with
-    // tools/exchange_sweep.py): SM time spent = bytes x latency / bytes in flight per CTA whatever the CTA count, and every
-    // resident CTA displaces one of the backward's GEMM CTAs (they fill the register file).  So: as much in flight per CTA as
-    // registers allow, and enough CTAs (up to 64) that each makes one pass -- the call is then as short as one round trip,
-    // which is what the exchange of the last ranges, behind the end of the backward, costs.  Every rank must use the same
-    // count (the barrier slots are per block): it depends on the range, the world size and `ctas` only.
+    // Measured (tools/exchange_sweep.py, profiles/r1_exchange_sweep_2gpu.txt): the multicast path is bound by the NVLink
+    // traffic of the range (every GPU serves the whole range to the switch and receives the whole reduced range back:
+    // ~400 GB/s of range bytes at 2 GPUs) and 8 CTAs of 512 threads x 8 vectors already saturate it; more CTAs only displace
+    // more of the backward's GEMM CTAs (those fill the register file, so every resident exchange CTA costs one).  So: at
+    // most 16 CTAs, each making at least two passes.  Every rank must use the same count (the barrier slots are per block):
+    // it depends on the range, the world size and `ctas` only.
     const int64_t per_rank = (n4 + g->world - 1) / g->world;
     const int threads = g_xchg_threads, unroll = g_xchg_unroll;
     const int64_t per_iter = (int64_t)threads * unroll;  // vectors one CTA moves per loop iteration
@@ -243,8 +243,8 @@ extern "C" int m2f_grad_allreduce_peer(const m2f_peer_group_t* g, int64_t lo, in
     if (ctas > 0) {
         grid = ctas;
     } else {
-        const int64_t want = (per_rank + per_iter - 1) / per_iter;
-        grid = want < 1 ? 1 : (want > M2F_XCHG_MAX_CTAS ? M2F_XCHG_MAX_CTAS : (int)want);
+        const int64_t want = (per_rank + 2 * per_iter - 1) / (2 * per_iter);
+        grid = want < 1 ? 1 : (want > 16 ? 16 : (int)want);
     }
     if (grid > M2F_XCHG_MAX_CTAS) grid = M2F_XCHG_MAX_CTAS;
     const int64_t need = (per_rank + per_iter - 1) / per_iter;
