@@ -267,6 +267,17 @@ def main():
                "note": "pinned host batches copied on a side stream one batch ahead (DevicePrefetcher); every step's loss is copied to "
                        "pinned host memory behind the loss kernel and read by the host in the same step, after backward + Adam were queued"}
 
+    # ---- data parallel: every replica must hold bit-identical parameters after the timed steps (each rank received the
+    # same reduced gradients and applied the same update); a lost or torn exchange shows up here
+    in_sync = None
+    if world > 1:
+        flat = model.flat_parameters()
+        chk = torch.stack([flat.double().sum(), flat.double().abs().sum(), flat[::9973].double().square().sum()])
+        hi_, lo_ = chk.clone(), chk.clone()
+        dist.all_reduce(hi_, op=dist.ReduceOp.MAX)
+        dist.all_reduce(lo_, op=dist.ReduceOp.MIN)
+        in_sync = bool(torch.equal(hi_, lo_)) and bool(torch.isfinite(chk).all())
+
     # ---- roofline of the dominant kernel (the tcgen05 GEMM), timed alone with CUDA events, operands rotated past L2
     roof = None
     if rank == 0:
@@ -289,6 +300,7 @@ def main():
                                    ("multicast (multimem.ld_reduce / multimem.st)" if getattr(net.reducer, "multicast", False) else "peer loads / stores")
                                    if net.exchange == "peer" else "gradient all-reduce: NCCL, async buckets behind the backward")
             cfg_out["bucket_mb"] = net.bucket_mb
+            cfg_out["replicas_in_sync_after_run"] = in_sync
             cfg_out["exchange_calls_per_step"] = getattr(net.reducer, "calls_per_step", len(net.reducer.log))
             if net.exchange == "peer":
                 cfg_out["exchange_launch"] = "kernels captured in the backward's CUDA graph" if net.reducer.in_graph else "bucket callbacks"
