@@ -260,13 +260,20 @@ struct m2f_plan {
 
     int ensure_streams() {
         if (aux[0]) return M2F_OK;
-        for (int i = 0; i < 3; ++i) M2F_CUDA(cudaStreamCreateWithFlags(&aux[i], cudaStreamNonBlocking));
-        {   // the exchange launched behind `ready` is a few CTAs that should start as soon as their range is final
+        {   // Priorities (M2F_STREAM_PRIO=0: all equal): the data-gradient chains are the critical path, the weight gradients
+            // fill the SMs they leave free; the exchange launched behind `ready` is a few CTAs that should start as soon as
+            // their range is final.  Kernel nodes captured from these streams keep the priority.
             int lo_prio = 0, hi_prio = 0;
             M2F_CUDA(cudaDeviceGetStreamPriorityRange(&lo_prio, &hi_prio));
+            const char* e = std::getenv("M2F_STREAM_PRIO");
+            const bool prio = !(e && e[0] == '0');
+            const int chain_prio = prio ? (hi_prio + lo_prio) / 2 : lo_prio;  // numerically lower = more urgent
+            M2F_CUDA(cudaStreamCreateWithPriority(&aux[0], cudaStreamNonBlocking, chain_prio));
+            M2F_CUDA(cudaStreamCreateWithPriority(&aux[1], cudaStreamNonBlocking, lo_prio));
+            M2F_CUDA(cudaStreamCreateWithPriority(&aux[2], cudaStreamNonBlocking, lo_prio));
             M2F_CUDA(cudaStreamCreateWithPriority(&ready, cudaStreamNonBlocking, hi_prio));
+            M2F_CUDA(cudaStreamCreateWithPriority(&cap, cudaStreamNonBlocking, chain_prio));
         }
-        M2F_CUDA(cudaStreamCreateWithFlags(&cap, cudaStreamNonBlocking));
         M2F_CUDA(cudaMalloc(&rng_dev, 2 * sizeof(unsigned long long)));
         evs.resize(128);
         for (auto& e : evs) M2F_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
