@@ -794,7 +794,11 @@ int gemm_block_n(int64_t M, int64_t N, int64_t K) {
     // one 128 x BLOCK_N tile per CTA: prefer the widest tile that still yields >= 148 CTAs
     const int64_t mt = (M + BLOCK_M - 1) / BLOCK_M;
     static const int forced = [] { const char* e = std::getenv("M2F_GEMM_BN"); return e ? std::atoi(e) : 0; }();  // tuning aid
-    static const int pairs = [] { const char* e = std::getenv("M2F_GEMM_CTA2"); return e ? std::atoi(e) : 2; }();  // 0 never, 1 always, 2 by shape
+    // M2F_GEMM_CTA2: 0 never, 1 always (default), 2 by shape.  Timed alone, a short-K GEMM is as fast with two small CTAs per SM
+    // as with CTA pairs (rule 2 below was tuned that way); inside the step four to six GEMMs share the GPU, latency hiding comes
+    // from the neighbours, and what counts is the L2 -> SM operand traffic per flop, which pairs halve for B: the whole train
+    // step is 3.7 % (bf16) / 6.5 % (fp32-parity) faster with pairs everywhere (profiles/r1_ab_gemm_pairs.txt).
+    static const int pairs = [] { const char* e = std::getenv("M2F_GEMM_CTA2"); return e ? std::atoi(e) : 1; }();
     if (pairs == 1 && N > 64) {
         const int bn = (forced == 128 || forced == 256) ? forced : 256;
         return ((N <= 128) ? 128 : bn) | GEMM_TILE_CTA2;
