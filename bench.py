@@ -205,6 +205,7 @@ def main():
         torch.cuda.synchronize()
 
     def timed(fn, steps, warmup):
+        barrier()  # ranks start the warm-up together (the exchange kernels of the ranks wait for each other)
         for i in range(warmup):
             fn(i)
         barrier()

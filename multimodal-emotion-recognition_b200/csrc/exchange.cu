@@ -47,8 +47,9 @@ __device__ __forceinline__ uint32_t cas_acquire_sys(uint32_t* a, uint32_t cmp, u
     return old;
 }
 
-// A peer that never arrives (crashed rank, mismatched call sequence) must not hang the GPU: give up after ~20 s.
-constexpr uint64_t XCHG_TIMEOUT_NS = 20ull * 1000 * 1000 * 1000;
+// A peer that never arrives (crashed rank, mismatched call sequence) must not hang the GPU for good: give up after 2 minutes
+// (long enough for the start-up skew of 8 processes sharing a few host cores).
+constexpr uint64_t XCHG_TIMEOUT_NS = 120ull * 1000 * 1000 * 1000;
 
 // All threads of the block call this.  Threads [0, world) each handshake with one peer.
 __device__ __forceinline__ void block_barrier_all_ranks(const PeerPtrs& pp, int rank, int world) {
@@ -251,10 +252,27 @@ extern "C" int m2f_grad_allreduce_peer(const m2f_peer_group_t* g, int64_t lo, in
     if (need < grid) grid = need < 1 ? 1 : (int)need;
     cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
     float* mc = reinterpret_cast<float*>(g->mc_base);
+    // The few exchange CTAs go in front of the backward's pending GEMM CTAs: the priority is set on the launch itself, so it
+    // also holds for the kernel nodes of a captured graph, whatever stream they were captured from.
+    static const int prio = [] {
+        int lo_p = 0, hi_p = 0;
+        return cudaDeviceGetStreamPriorityRange(&lo_p, &hi_p) == cudaSuccess ? hi_p : 0;
+    }();
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributePriority;
+    attr[0].val.priority = prio;
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)grid);
+    cfg.stream = st;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    float* mc_arg = mc;
+    const int rank = g->rank, world = g->world;
 #define M2F_XCHG_LAUNCH(T, U)                                                                                                          \
     if (threads == T && unroll == U) {                                                                                                 \
-        if (mc) grad_allreduce_kernel<true, T, U><<<grid, T, 0, st>>>(mc, pp, g->rank, g->world, lo, head, n4, tail, scale, flags);      \
-        else    grad_allreduce_kernel<false, T, U><<<grid, T, 0, st>>>(nullptr, pp, g->rank, g->world, lo, head, n4, tail, scale, flags); \
+        cfg.blockDim = dim3(T);                                                                                                        \
+        if (mc) M2F_CUDA(cudaLaunchKernelEx(&cfg, grad_allreduce_kernel<true, T, U>, mc_arg, pp, rank, world, lo, head, n4, tail, scale, (int)flags));  \
+        else    M2F_CUDA(cudaLaunchKernelEx(&cfg, grad_allreduce_kernel<false, T, U>, mc_arg, pp, rank, world, lo, head, n4, tail, scale, (int)flags)); \
     }
     M2F_XCHG_LAUNCH(512, 8)
     M2F_XCHG_LAUNCH(512, 4)
