@@ -11,9 +11,11 @@
 //      the switch* (one load, one NVLink response), the sum is scaled (1/world) and `multimem.st` writes it back to every
 //      GPU through the same multicast mapping.  Without multicast: world peer loads + world peer stores per element.
 //   3. barrier: block b of every rank has stored  => when the kernel has completed on a rank, all of its range is final.
-// Per GPU and step that is arena/world bytes pulled and arena/world pushed by SMs; the switch does the fan-in / fan-out,
-// which is why 16-32 CTAs are enough and the kernel can run beside the backward's GEMMs (NCCL's ring / tree kernels
-// compete with them for SMs and L2).
+//      Within a sequence of calls on one stream only the last call needs it (M2F_XCHG_NO_EXIT_BARRIER on the others).
+// SMs pull and push range / world bytes per GPU; the switch does the fan-in / fan-out, and the NVLink traffic of the range
+// (every GPU serves the whole range and receives the whole reduced range) is what bounds the kernel: 8 CTAs saturate it, the
+// default is at most 16, so it runs beside the backward's GEMMs at the cost of a few of their CTA slots (NCCL's ring /
+// tree kernels take many more).
 //
 // Barrier words: uint32 [M2F_XCHG_MAX_CTAS][M2F_XCHG_MAX_RANKS] at signal_off_bytes inside the symmetric buffer, zero
 // before the first call.  Slot (b, s) on rank d is written by rank s only: put = CAS 0 -> 1 (release, system scope, spins
