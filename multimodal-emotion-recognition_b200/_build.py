@@ -48,9 +48,19 @@ def build(force: bool = False, verbose: bool = False) -> str:
         if force or _stale(obj, [src] + hdrs):
             jobs.append((src, obj))
 
+    # build-time experiments: extra -D definitions (e.g. M2F_NVCC_DEFS="-DM2F_PAIR_RING_KB=96 -DM2F_PAIR_EPI_WARPS=4");
+    # when set, everything is recompiled, and the next build without it recompiles again (stamp file)
+    extra = os.environ.get("M2F_NVCC_DEFS", "").split()
+    stamp = os.path.join(BUILD, "defs.stamp")
+    prev = open(stamp).read() if os.path.exists(stamp) else ""
+    if " ".join(extra) != prev:
+        jobs = [(os.path.join(CSRC, s), os.path.join(BUILD, s.replace(".cu", ".o"))) for s in srcs]
+        with open(stamp, "w") as f:
+            f.write(" ".join(extra))
+
     def compile_one(job):
         src, obj = job
-        cmd = [nvcc] + [f for f in NVCC_FLAGS if not f.startswith("--use_fast_math")] + ["-c", src, "-o", obj]
+        cmd = [nvcc] + [f for f in NVCC_FLAGS if not f.startswith("--use_fast_math")] + extra + ["-c", src, "-o", obj]
         if verbose:
             cmd.insert(1, "-Xptxas=-v")
         r = subprocess.run(cmd, capture_output=True, text=True)

@@ -36,6 +36,12 @@ __device__ __forceinline__ unsigned long long gtimer() {
 
 // CTA2: the CTA is half of a cta_group::2 pair -- the pair computes a 256 x BLOCK_N tile, this CTA owns 128 rows of it
 // and stages only BLOCK_N / 2 rows of B (twice the flops per byte an SM ingests from L2).
+#ifndef M2F_PAIR_RING_KB
+#define M2F_PAIR_RING_KB 192
+#endif
+#ifndef M2F_PAIR_EPI_WARPS
+#define M2F_PAIR_EPI_WARPS 8
+#endif
 template <int BLOCK_N, bool CTA2>
 struct GemmCfg {
     static constexpr int B_ROWS = CTA2 ? BLOCK_N / 2 : BLOCK_N;
@@ -47,10 +53,13 @@ struct GemmCfg {
     // Pairs: one CTA per SM with a 192 KB ring (enough bytes in flight to cover the L2 latency at the rate the
     // 256-row MMA consumes them) and 8 epilogue warps -- the epilogue of a 128 x 256 tile is instruction-latency bound,
     // two warps per TMEM lane group halve it.
-    static constexpr int CTAS_PER_SM = CTA2 ? 1 : 2;
-    static constexpr int EPI_WARPS = CTA2 ? 8 : 4;
+    // Build-time experiment (M2F_NVCC_DEFS="-DM2F_PAIR_RING_KB=96 -DM2F_PAIR_EPI_WARPS=4", see _build.py): pairs with a
+    // half-size ring and four epilogue warps, so that two pairs share an SM and one's epilogue overlaps the other's main loop.
+    static constexpr int PAIR_RING_KB = M2F_PAIR_RING_KB;
+    static constexpr int CTAS_PER_SM = CTA2 ? (PAIR_RING_KB <= 100 ? 2 : 1) : 2;
+    static constexpr int EPI_WARPS = CTA2 ? M2F_PAIR_EPI_WARPS : 4;
     static constexpr int THREADS = 64 + 32 * EPI_WARPS;
-    static constexpr int STAGES = ((CTA2 ? 192 : 96) * 1024) / STAGE_BYTES;
+    static constexpr int STAGES = ((CTA2 ? PAIR_RING_KB : 96) * 1024) / STAGE_BYTES;
     static constexpr int BAR_BYTES = (2 * STAGES + 1) * 8 + 16 + 8 * 8;  // ring, accumulator-ready, TMEM slot, 8 epilogue-load barriers
     static constexpr int BIAS_BYTES = BLOCK_N * 4;  // the tile's bias values, staged while the main loop runs (so not in the ring)
     static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + BAR_BYTES + BIAS_BYTES + 16 + 1024;  // + alignment slack
