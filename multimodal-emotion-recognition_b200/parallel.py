@@ -174,10 +174,12 @@ class DataParallelM2FNet(torch.nn.Module):
         self.module = model
         self.group = group
         flat = model.flat_parameters()
-        dist.broadcast(flat, src=dist.get_global_rank(group, 0) if group is not None else 0, group=group)
         exchange = (exchange or os.environ.get("M2F_EXCHANGE", "auto")).lower()
         if exchange not in ("auto", "peer", "nccl"):
             raise ValueError(f"exchange must be auto, peer or nccl, got {exchange!r}")
+        if exchange == "peer" and not flat.is_cuda:
+            raise RuntimeError("peer gradient exchange needs the model on the GPU (there is no CPU path)")
+        dist.broadcast(flat, src=dist.get_global_rank(group, 0) if group is not None else 0, group=group)
         self.reducer = None
         if exchange != "nccl" and flat.is_cuda:
             err = None
