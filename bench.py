@@ -290,6 +290,13 @@ def main():
                         "frac_of_sustained_bf16_peak": step_flops / (ms / args.steps * 1e-3) / 1e12 / peaks["bf16_tflops_sustained"],
                         "note": "whole train step incl. attention/LN/loss/Adam kernels and launch gaps; fp32 mode runs 6 plane products per GEMM"}
 
+    if rank == 0 and world == 1 and roof is not None:
+        try:  # additional evidence only: never let it cost the bench line
+            roof["hbm_kernels"] = hbm_kernel_rooflines(pkg, torch, dev, opt, model)
+        except Exception as e:  # noqa: BLE001
+            roof["hbm_kernels"] = None
+            roof["hbm_kernels_error"] = repr(e)[:200]
+
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         cpu = cpu_baseline()
@@ -313,6 +320,55 @@ def main():
         print(json.dumps(out))
     if world > 1:
         dist.destroy_process_group()
+
+
+def hbm_kernel_rooflines(pkg, torch, dev, opt, model):
+    """The bandwidth-bound kernels against the measured HBM peak, at sizes whose working set exceeds the 126 MB L2
+    (at M = 2112 these tensors sit in L2 and the kernels are launch-bound): LayerNorm forward / backward over
+    M = 131 072 rows of 768 (the C5 batch), and the fused Adam + shadow pass over the model's arena.  Algorithmic bytes as in
+    DESIGN.md section 5.  Each timed alone, CUDA events on the launch stream, 10 launches after 2 warm-ups."""
+    ops = pkg.ops
+    peak = load_peaks()["hbm_gbs"]
+    out = []
+
+    def time_us(fn, reps=10):
+        for _ in range(2):
+            fn()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(reps):
+            fn()
+        e1.record()
+        torch.cuda.synchronize()
+        return e0.elapsed_time(e1) * 1e3 / reps
+
+    def add(name, nbytes, us):
+        gbs = nbytes / us / 1e3
+        out.append({"kernel": name, "algorithmic_bytes": nbytes, "us_per_launch": us, "achieved": gbs, "unit": "GB/s", "peak": peak,
+                    "frac": gbs / peak})
+
+    M, D, P = 131072, 768, 1
+    g = torch.Generator(device=dev).manual_seed(3)
+    x = torch.randn(M, D, generator=g, device=dev)
+    skip = torch.randn(M, D, generator=g, device=dev)
+    gamma, beta = torch.ones(D, device=dev), torch.zeros(D, device=dev)
+    y = torch.empty(M, D, device=dev)
+    ypl = ops.PlanesTensor.empty(M, D, P, dev)
+    stats = torch.empty(M, 2, device=dev)
+    us = time_us(lambda: ops.ln_fwd(x, gamma, beta, skip=skip, y=y, y_planes=ypl, drop_p=0.4, seed=1, step=2, site=3, stats=stats))
+    add("ln_fwd_kernel: y = LN(x) + skip, fp32 + 1 bf16 plane (dropout 0.4), M=131072 D=768", (3 * 4 + 2 * P) * M * D + 8 * M, us)
+    dx = torch.empty(M, D, device=dev)
+    dgamma, dbeta, dbias = (torch.zeros(D, device=dev) for _ in range(3))
+    us = time_us(lambda: ops.ln_bwd(skip, x, gamma, stats, dx=dx, dx_planes=ypl, drop_p=0.4, seed=4, step=5, site=6, dgamma=dgamma, dbeta=dbeta,
+                                    dbias=dbias))
+    add("ln_bwd_kernel: dx fp32 + 1 masked bf16 plane, dgamma / dbeta / dbias, M=131072 D=768", (3 * 4 + 2 * P) * M * D + 8 * M, us)
+    del x, skip, y, ypl, dx
+    n = model.flat_parameters().numel()
+    shadow_bytes = int(model._shadow.numel()) if getattr(model, "_shadow", None) is not None else 0
+    us = time_us(lambda: opt.step(), reps=5)
+    add("adam_shadow_kernel: fused Adam over the parameter arena + bf16 shadow refresh", 7 * 4 * n + shadow_bytes, us)
+    return out
 
 
 def load_peaks():
