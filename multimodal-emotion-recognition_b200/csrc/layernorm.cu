@@ -5,8 +5,10 @@
 // of nn.TransformerEncoder (:550-551) and the outer skip of src/model.py:107,119.
 // One warp per row; a row of D <= 1024 fp32 lives in registers (NCH float4 chunks per lane).
 #include <algorithm>
+#include <cstdlib>
 
 #include "common.cuh"
+#include "ptx.cuh"
 
 namespace m2f {
 
@@ -178,6 +180,138 @@ ln_bwd_kernel(const float* __restrict__ g, int64_t g_ld, const float* __restrict
     }
 }
 
+// ------------------------------------------------------------------------------------------ forward, staged through shared memory
+// EXPERIMENT (M2F_LN_V2=1, off by default, not yet run on a GPU): the register-resident kernel above keeps 16 - 20 warps per
+// SM with one 3 KB row in flight each and reaches 0.48 of the HBM peak at M = 131 072.  Here a block moves tiles of 8 rows
+// of x (and skip) into a 2-deep shared-memory ring with bulk asynchronous copies issued by one thread (cp.async.bulk,
+// completion on an mbarrier): 48 KB per stage and 96 KB per block are in flight without costing registers, and the
+// arithmetic of tile t overlaps the landing of tile t + 1.  Same arithmetic and the same Philox element indices as above.
+constexpr int LN2_ROWS = 8;
+constexpr int LN2_THREADS = LN2_ROWS * 32;
+constexpr int LN2_STAGES = 2;
+
+__device__ __forceinline__ void bulk_g2s(void* smem_dst, const void* gsrc, uint32_t bytes, uint64_t* bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(ptx::smem_u32(smem_dst)),
+                 "l"(gsrc), "r"(bytes), "r"(ptx::smem_u32(bar))
+                 : "memory");
+}
+
+template <int NCH>
+__global__ void __launch_bounds__(LN2_THREADS)
+ln_fwd_staged_kernel(const float* __restrict__ x, int64_t x_ld, const float* __restrict__ gamma, const float* __restrict__ beta,
+                     const float* __restrict__ skip, int64_t skip_ld, int64_t M, int D, float* __restrict__ y, int64_t y_ld,
+                     __nv_bfloat16* __restrict__ ypl, int64_t ypl_ld, int64_t ypl_stride, int P, Drop drop, float* __restrict__ stats) {
+    extern __shared__ __align__(128) uint8_t ln2_smem[];
+    __shared__ __align__(8) uint64_t full_bar[LN2_STAGES];
+    float* ring = reinterpret_cast<float*>(ln2_smem);
+    const bool has_skip = skip != nullptr;
+    const int tile_floats = LN2_ROWS * D;
+    const int stage_floats = tile_floats * (has_skip ? 2 : 1);
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const float invD = 1.f / (float)D;
+    const int64_t ntiles = (M + LN2_ROWS - 1) / LN2_ROWS;
+    if (threadIdx.x == 0) {
+        for (int s2 = 0; s2 < LN2_STAGES; ++s2) ptx::mbar_init(&full_bar[s2], 1);
+        ptx::fence_barrier_init();
+    }
+    __syncthreads();
+    pdl_wait();
+    pdl_trigger();
+    drop = drop_resolve(drop);
+    // thread 0: request one tile into stage s2 (rows past M are not requested; their warps skip the arithmetic)
+    auto issue = [&](int64_t tile, int s2) {
+        const int64_t m0 = tile * LN2_ROWS;
+        const int rows = (int)((M - m0) < LN2_ROWS ? (M - m0) : LN2_ROWS);
+        const uint32_t row_bytes = (uint32_t)D * 4u;
+        ptx::mbar_expect_tx(&full_bar[s2], (uint32_t)rows * row_bytes * (has_skip ? 2u : 1u));
+        float* dx = ring + (size_t)s2 * stage_floats;
+        if (x_ld == D) {
+            bulk_g2s(dx, x + m0 * x_ld, (uint32_t)rows * row_bytes, &full_bar[s2]);
+        } else {
+            for (int r = 0; r < rows; ++r) bulk_g2s(dx + (size_t)r * D, x + (m0 + r) * x_ld, row_bytes, &full_bar[s2]);
+        }
+        if (has_skip) {
+            float* ds = dx + tile_floats;
+            if (skip_ld == D) {
+                bulk_g2s(ds, skip + m0 * skip_ld, (uint32_t)rows * row_bytes, &full_bar[s2]);
+            } else {
+                for (int r = 0; r < rows; ++r) bulk_g2s(ds + (size_t)r * D, skip + (m0 + r) * skip_ld, row_bytes, &full_bar[s2]);
+            }
+        }
+    };
+    if (threadIdx.x == 0) {
+        for (int s2 = 0; s2 < LN2_STAGES; ++s2) {
+            const int64_t t = (int64_t)blockIdx.x + (int64_t)s2 * gridDim.x;
+            if (t < ntiles) issue(t, s2);
+        }
+    }
+    int it = 0;
+    for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
+        const int s2 = it % LN2_STAGES;
+        ptx::mbar_wait(&full_bar[s2], (uint32_t)((it / LN2_STAGES) & 1));
+        const int64_t m = tile * LN2_ROWS + warp;
+        if (m < M) {
+            const float* xs = ring + (size_t)s2 * stage_floats + (size_t)warp * D;
+            const float* ks = xs + tile_floats;
+            float4 v[NCH];
+            float s = 0.f;
+#pragma unroll
+            for (int c = 0; c < NCH; ++c) {
+                const int col = (c * 32 + lane) * 4;
+                v[c] = col < D ? *reinterpret_cast<const float4*>(xs + col) : make_float4(0.f, 0.f, 0.f, 0.f);
+                s += v[c].x + v[c].y + v[c].z + v[c].w;
+            }
+            const float mean = warp_sum(s) * invD;
+            float q = 0.f;
+#pragma unroll
+            for (int c = 0; c < NCH; ++c) {
+                const int col = (c * 32 + lane) * 4;
+                if (col < D) {
+                    const float a = v[c].x - mean, b = v[c].y - mean, cc = v[c].z - mean, d = v[c].w - mean;
+                    q += a * a + b * b + cc * cc + d * d;
+                }
+            }
+            const float rstd = rsqrtf(warp_sum(q) * invD + LN_EPS);
+            if (lane == 0 && stats) {
+                stats[2 * m] = mean;
+                stats[2 * m + 1] = rstd;
+            }
+#pragma unroll
+            for (int c = 0; c < NCH; ++c) {
+                const int col = (c * 32 + lane) * 4;
+                if (col < D) {
+                    const float4 g = *reinterpret_cast<const float4*>(gamma + col);
+                    const float4 b = *reinterpret_cast<const float4*>(beta + col);
+                    float o[4] = {(v[c].x - mean) * rstd * g.x + b.x, (v[c].y - mean) * rstd * g.y + b.y,
+                                  (v[c].z - mean) * rstd * g.z + b.z, (v[c].w - mean) * rstd * g.w + b.w};
+                    if (has_skip) {
+                        const float4 k = *reinterpret_cast<const float4*>(ks + col);
+                        o[0] += k.x; o[1] += k.y; o[2] += k.z; o[3] += k.w;
+                    }
+                    if (y) *reinterpret_cast<float4*>(y + m * y_ld + col) = make_float4(o[0], o[1], o[2], o[3]);
+                    if (ypl) {
+                        if (drop.enabled) {
+                            float dm[4];
+                            drop_mult4(drop, (uint64_t)(m * D + col) >> 2, dm);
+#pragma unroll
+                            for (int i = 0; i < 4; ++i) o[i] *= dm[i];
+                        }
+                        store_planes4(ypl, ypl_stride, P, m * ypl_ld + col, o);
+                    }
+                }
+            }
+        }
+        __syncthreads();  // every warp has read stage s2: it can be refilled
+        const int64_t nxt = tile + (int64_t)LN2_STAGES * gridDim.x;
+        if (threadIdx.x == 0 && nxt < ntiles) issue(nxt, s2);
+    }
+}
+
+static bool ln_v2_enabled() {
+    static const bool on = [] { const char* e = std::getenv("M2F_LN_V2"); return e && e[0] == '1'; }();
+    return on;
+}
+
 static int ln_grid(int64_t M, int rows_per_warp) {
     int64_t blocks = (M + LN_WARPS * rows_per_warp - 1) / (LN_WARPS * rows_per_warp);
     if (blocks > 148 * 4) blocks = 148 * 4;
@@ -234,6 +368,18 @@ extern "C" int m2f_ln_fwd(const float* x, int64_t x_ld, const float* gamma, cons
     M2F_REQUIRE(y_f32 || ypl, M2F_ERR_ARG, "ln_fwd: no output given");
     const Drop drop = drop_make(drop_p, seed, step, site);
     auto st = reinterpret_cast<cudaStream_t>(stream);
+    if (ln_v2_enabled() && (!skip || (reinterpret_cast<uintptr_t>(skip) % 16 == 0 && skip_ld % 4 == 0))) {
+        const size_t smem = (size_t)LN2_STAGES * LN2_ROWS * D * 4 * (skip ? 2 : 1);
+        int64_t blocks = (M + LN2_ROWS - 1) / LN2_ROWS;
+        if (blocks > 148 * 2) blocks = 148 * 2;
+        M2F_LN_DISPATCH(D, {
+            M2F_CUDA(cudaFuncSetAttribute(ln_fwd_staged_kernel<NCH>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            M2F_CUDA(launch_chain(ln_fwd_staged_kernel<NCH>, dim3((unsigned)blocks), dim3(LN2_THREADS), smem, st, 1, x, x_ld, gamma, beta, skip,
+                                  skip_ld, M, (int)D, y_f32, y_ld, ypl, ypl_ld, ypl_stride, P, drop, stats));
+        });
+        M2F_LAUNCH_CHECK();
+        return M2F_OK;
+    }
     M2F_LN_DISPATCH(D, M2F_CUDA(launch_chain(ln_fwd_kernel<NCH>, dim3(ln_grid(M, 1)), dim3(LN_THREADS), 0, st, 1, x, x_ld, gamma, beta, skip,
                                              skip_ld, M, (int)D, y_f32, y_ld, ypl, ypl_ld, ypl_stride, P, drop, stats)));
     M2F_LAUNCH_CHECK();
