@@ -181,8 +181,9 @@ ln_bwd_kernel(const float* __restrict__ g, int64_t g_ld, const float* __restrict
 }
 
 // ------------------------------------------------------------------------------------------ forward, staged through shared memory
-// EXPERIMENT (M2F_LN_V2=1, off by default, not yet run on a GPU): the register-resident kernel above keeps 16 - 20 warps per
-// SM with one 3 KB row in flight each and reaches 0.48 of the HBM peak at M = 131 072.  Here a block moves tiles of 8 rows
+// EXPERIMENT (M2F_LN_V2=1: forward, measured 0.74 of the HBM peak at M = 131 072, op parity green; M2F_LN_V2=2: backward too,
+// not yet run on a GPU; off by default): the register-resident kernel above keeps 16 - 20 warps per SM with one 3 KB row in
+// flight each and reaches 0.48 of the HBM peak at M = 131 072.  Here a block moves tiles of 8 rows
 // of x (and skip) into a 2-deep shared-memory ring with bulk asynchronous copies issued by one thread (cp.async.bulk,
 // completion on an mbarrier): 48 KB per stage and 96 KB per block are in flight without costing registers, and the
 // arithmetic of tile t overlaps the landing of tile t + 1.  Same arithmetic and the same Philox element indices as above.
@@ -307,10 +308,151 @@ ln_fwd_staged_kernel(const float* __restrict__ x, int64_t x_ld, const float* __r
     }
 }
 
-static bool ln_v2_enabled() {
-    static const bool on = [] { const char* e = std::getenv("M2F_LN_V2"); return e && e[0] == '1'; }();
-    return on;
+// Backward, same staging: tiles of 8 rows of g and x land in shared memory; phase 1 (one row per warp: dx) and phase 2 (one
+// float4 column per thread: dgamma / dbeta / dbias partial sums) both read them from there, so every row is fetched from
+// global memory once.  Same arithmetic, summation order and Philox element indices as ln_bwd_kernel.
+template <int NCH>
+__global__ void __launch_bounds__(LN2_THREADS)
+ln_bwd_staged_kernel(const float* __restrict__ g, int64_t g_ld, const float* __restrict__ x, int64_t x_ld,
+                     const float* __restrict__ gamma, const float* __restrict__ stats, int64_t M, int D, float* __restrict__ dx,
+                     int64_t dx_ld, __nv_bfloat16* __restrict__ dxpl, int64_t dxpl_ld, int64_t dxpl_stride, int P, Drop drop,
+                     float* __restrict__ dgamma, float* __restrict__ dbeta, float* __restrict__ dbias) {
+    extern __shared__ __align__(128) uint8_t ln2_smem[];
+    __shared__ __align__(8) uint64_t full_bar[LN2_STAGES];
+    __shared__ float rowc[LN2_ROWS][4];  // mean, rstd, c1, c2
+    float* ring = reinterpret_cast<float*>(ln2_smem);
+    const int tile_floats = LN2_ROWS * D;
+    const int stage_floats = 2 * tile_floats;  // x tile, then g tile
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const float invD = 1.f / (float)D;
+    const int ccol = threadIdx.x * 4;
+    const int64_t ntiles = (M + LN2_ROWS - 1) / LN2_ROWS;
+    if (threadIdx.x == 0) {
+        for (int s2 = 0; s2 < LN2_STAGES; ++s2) ptx::mbar_init(&full_bar[s2], 1);
+        ptx::fence_barrier_init();
+    }
+    __syncthreads();
+    pdl_wait();
+    pdl_trigger();
+    drop = drop_resolve(drop);
+    auto issue = [&](int64_t tile, int s2) {
+        const int64_t m0 = tile * LN2_ROWS;
+        const int rows = (int)((M - m0) < LN2_ROWS ? (M - m0) : LN2_ROWS);
+        const uint32_t row_bytes = (uint32_t)D * 4u;
+        ptx::mbar_expect_tx(&full_bar[s2], (uint32_t)rows * row_bytes * 2u);
+        float* sx = ring + (size_t)s2 * stage_floats;
+        float* sgr = sx + tile_floats;
+        if (x_ld == D) {
+            bulk_g2s(sx, x + m0 * x_ld, (uint32_t)rows * row_bytes, &full_bar[s2]);
+        } else {
+            for (int r = 0; r < rows; ++r) bulk_g2s(sx + (size_t)r * D, x + (m0 + r) * x_ld, row_bytes, &full_bar[s2]);
+        }
+        if (g_ld == D) {
+            bulk_g2s(sgr, g + m0 * g_ld, (uint32_t)rows * row_bytes, &full_bar[s2]);
+        } else {
+            for (int r = 0; r < rows; ++r) bulk_g2s(sgr + (size_t)r * D, g + (m0 + r) * g_ld, row_bytes, &full_bar[s2]);
+        }
+    };
+    if (threadIdx.x == 0) {
+        for (int s2 = 0; s2 < LN2_STAGES; ++s2) {
+            const int64_t t = (int64_t)blockIdx.x + (int64_t)s2 * gridDim.x;
+            if (t < ntiles) issue(t, s2);
+        }
+    }
+    float4 sg = make_float4(0.f, 0.f, 0.f, 0.f), sb = sg, sbias = sg, gmc = sg;
+    if (ccol < D) gmc = *reinterpret_cast<const float4*>(gamma + ccol);
+    int it = 0;
+    for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
+        const int s2 = it % LN2_STAGES;
+        const int64_t m0 = tile * LN2_ROWS;
+        const int64_t m = m0 + warp;
+        float mean = 0.f, rstd = 0.f;
+        if (m < M) {  // the row statistics do not come through the ring: fetch them while the tile lands
+            mean = stats[2 * m];
+            rstd = stats[2 * m + 1];
+        }
+        ptx::mbar_wait(&full_bar[s2], (uint32_t)((it / LN2_STAGES) & 1));
+        const float* sx = ring + (size_t)s2 * stage_floats;
+        const float* sgr = sx + tile_floats;
+        if (m < M) {
+            float4 xv[NCH], av[NCH];
+            float s1 = 0.f, s2sum = 0.f;
+#pragma unroll
+            for (int c = 0; c < NCH; ++c) {
+                const int col = (c * 32 + lane) * 4;
+                if (col < D) {
+                    const float4 gm = *reinterpret_cast<const float4*>(gamma + col);
+                    const float4 xr = *reinterpret_cast<const float4*>(sx + (size_t)warp * D + col);
+                    const float4 gr = *reinterpret_cast<const float4*>(sgr + (size_t)warp * D + col);
+                    xv[c] = make_float4((xr.x - mean) * rstd, (xr.y - mean) * rstd, (xr.z - mean) * rstd, (xr.w - mean) * rstd);
+                    av[c] = make_float4(gr.x * gm.x, gr.y * gm.y, gr.z * gm.z, gr.w * gm.w);
+                    s1 += av[c].x + av[c].y + av[c].z + av[c].w;
+                    s2sum += av[c].x * xv[c].x + av[c].y * xv[c].y + av[c].z * xv[c].z + av[c].w * xv[c].w;
+                } else {
+                    xv[c] = av[c] = make_float4(0.f, 0.f, 0.f, 0.f);
+                }
+            }
+            const float c1 = warp_sum(s1) * invD, c2 = warp_sum(s2sum) * invD;
+            if (lane == 0) { rowc[warp][0] = mean; rowc[warp][1] = rstd; rowc[warp][2] = c1; rowc[warp][3] = c2; }
+#pragma unroll
+            for (int c = 0; c < NCH; ++c) {
+                const int col = (c * 32 + lane) * 4;
+                if (col < D) {
+                    float o[4] = {rstd * (av[c].x - c1 - xv[c].x * c2), rstd * (av[c].y - c1 - xv[c].y * c2),
+                                  rstd * (av[c].z - c1 - xv[c].z * c2), rstd * (av[c].w - c1 - xv[c].w * c2)};
+                    if (dx) *reinterpret_cast<float4*>(dx + m * dx_ld + col) = make_float4(o[0], o[1], o[2], o[3]);
+                    if (dxpl) {
+                        if (drop.enabled) {
+                            float dm[4];
+                            drop_mult4(drop, (uint64_t)(m * D + col) >> 2, dm);
+#pragma unroll
+                            for (int i = 0; i < 4; ++i) o[i] *= dm[i];
+                        }
+                        store_planes4(dxpl, dxpl_stride, P, m * dxpl_ld + col, o);
+                    }
+                }
+            }
+        }
+        __syncthreads();  // rowc complete
+        if (ccol < D) {
+            const int nrow = (int)min((int64_t)LN2_ROWS, M - m0);
+            for (int r = 0; r < nrow; ++r) {
+                const int64_t mm = m0 + r;
+                const float4 xr = *reinterpret_cast<const float4*>(sx + (size_t)r * D + ccol);
+                const float4 gr = *reinterpret_cast<const float4*>(sgr + (size_t)r * D + ccol);
+                const float rmean = rowc[r][0], rrstd = rowc[r][1], c1 = rowc[r][2], c2 = rowc[r][3];
+                const float4 xh = make_float4((xr.x - rmean) * rrstd, (xr.y - rmean) * rrstd, (xr.z - rmean) * rrstd, (xr.w - rmean) * rrstd);
+                sg.x += gr.x * xh.x; sg.y += gr.y * xh.y; sg.z += gr.z * xh.z; sg.w += gr.w * xh.w;
+                sb.x += gr.x; sb.y += gr.y; sb.z += gr.z; sb.w += gr.w;
+                if (dbias) {
+                    float o[4] = {rrstd * (gr.x * gmc.x - c1 - xh.x * c2), rrstd * (gr.y * gmc.y - c1 - xh.y * c2),
+                                  rrstd * (gr.z * gmc.z - c1 - xh.z * c2), rrstd * (gr.w * gmc.w - c1 - xh.w * c2)};
+                    if (drop.enabled) {
+                        float dm[4];
+                        drop_mult4(drop, (uint64_t)(mm * D + ccol) >> 2, dm);
+                        o[0] *= dm[0]; o[1] *= dm[1]; o[2] *= dm[2]; o[3] *= dm[3];
+                    }
+                    sbias.x += o[0]; sbias.y += o[1]; sbias.z += o[2]; sbias.w += o[3];
+                }
+            }
+        }
+        __syncthreads();  // every thread has read stage s2 and rowc: both can be overwritten
+        const int64_t nxt = tile + (int64_t)LN2_STAGES * gridDim.x;
+        if (threadIdx.x == 0 && nxt < ntiles) issue(nxt, s2);
+    }
+    if (ccol < D) {
+        if (dgamma) asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(dgamma + ccol), "f"(sg.x), "f"(sg.y), "f"(sg.z), "f"(sg.w) : "memory");
+        if (dbeta) asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(dbeta + ccol), "f"(sb.x), "f"(sb.y), "f"(sb.z), "f"(sb.w) : "memory");
+        if (dbias) asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(dbias + ccol), "f"(sbias.x), "f"(sbias.y), "f"(sbias.z), "f"(sbias.w) : "memory");
+    }
 }
+
+// M2F_LN_V2: 0 / unset = register-resident kernels, 1 = staged forward, 2 = staged forward and backward
+static int ln_v2_level() {
+    static const int lvl = [] { const char* e = std::getenv("M2F_LN_V2"); return e ? std::atoi(e) : 0; }();
+    return lvl;
+}
+static bool ln_v2_enabled() { return ln_v2_level() >= 1; }
 
 static int ln_grid(int64_t M, int rows_per_warp) {
     int64_t blocks = (M + LN_WARPS * rows_per_warp - 1) / (LN_WARPS * rows_per_warp);
@@ -410,6 +552,18 @@ extern "C" int m2f_ln_bwd(const float* g, int64_t g_ld, const float* x, int64_t 
     auto st = reinterpret_cast<cudaStream_t>(stream);
     M2F_REQUIRE((!dgamma || (reinterpret_cast<uintptr_t>(dgamma) % 16) == 0) && (!dbeta || (reinterpret_cast<uintptr_t>(dbeta) % 16) == 0) &&
                     (!dbias || (reinterpret_cast<uintptr_t>(dbias) % 16) == 0), M2F_ERR_ALIGN, "ln_bwd: dgamma / dbeta / dbias must be 16-byte aligned");
+    if (ln_v2_level() >= 2) {
+        const size_t smem = (size_t)LN2_STAGES * LN2_ROWS * D * 4 * 2;
+        int64_t blocks = (M + LN2_ROWS - 1) / LN2_ROWS;
+        if (blocks > 148 * 2) blocks = 148 * 2;
+        M2F_LN_DISPATCH(D, {
+            M2F_CUDA(cudaFuncSetAttribute(ln_bwd_staged_kernel<NCH>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            M2F_CUDA(launch_chain(ln_bwd_staged_kernel<NCH>, dim3((unsigned)blocks), dim3(LN2_THREADS), smem, st, 1, g, g_ld, x, x_ld, gamma, stats,
+                                  M, (int)D, dx_f32, dx_ld, dpl, dpl_ld, dpl_stride, P, drop, dgamma, dbeta, dbias));
+        });
+        M2F_LAUNCH_CHECK();
+        return M2F_OK;
+    }
     const int lnb_grid = (int)std::min<int64_t>((M + LNB_ROWS - 1) / LNB_ROWS, 148 * 4);
     M2F_LN_DISPATCH(D, M2F_CUDA(launch_chain(ln_bwd_kernel<NCH>, dim3(lnb_grid), dim3(LNB_THREADS), 0, st, 1, g, g_ld, x, x_ld, gamma, stats, M,
                                              (int)D, dx_f32, dx_ld, dpl, dpl_ld, dpl_stride, P, drop, dgamma, dbeta, dbias)));
