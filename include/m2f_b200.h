@@ -27,7 +27,7 @@
 extern "C" {
 #endif
 
-#define M2F_ABI_VERSION 1
+#define M2F_ABI_VERSION 2
 
 #define M2F_OK 0
 #define M2F_ERR_ARG (-1)         /* bad argument / shape */
@@ -173,7 +173,14 @@ typedef struct {
     int32_t cls_hidden, cls_out, cls_layers;
     float dropout;
     int32_t ffn_dim;
-    int32_t planes; /* 1 = bf16 throughput mode, 3 = fp32-parity mode (2 = 16-bit mantissa) */
+    int32_t planes; /* planes of everything the FORWARD multiplies (weights shadow, saved activations): 1 = plain bf16,
+                     * 2 = 16-bit mantissa, 3 = fp32-parity mode */
+    int32_t planes_bwd; /* planes of the BACKWARD's GEMM / attention operands: the gradients, and the leading planes_bwd
+                         * planes of the saved activations and weights.  0 = same as `planes`; must be <= planes.
+                         * (planes, planes_bwd) = (2, 1) is the "bf16x2f" training mode: ReLU gates and softmax
+                         * weights are decided by a 16-bit-mantissa forward -- what the gradient error at bf16 is
+                         * dominated by (profiles/r2_bf16_protocol_cpu.json) -- while both backward products per
+                         * Linear stay single bf16 products: 5 plane products per Linear instead of 9 (bf16x2). */
 } m2f_model_cfg_t;
 
 typedef struct m2f_model m2f_model_t;

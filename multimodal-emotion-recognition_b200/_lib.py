@@ -46,7 +46,8 @@ class ModelCfg(C.Structure):
     """m2f_model_cfg_t"""
     _fields_ = [("audio", ModalityCfg), ("text", ModalityCfg), ("fam_enabled", C.c_int32), ("fam_dim", C.c_int32),
                 ("fam_heads", C.c_int32), ("fam_layers", C.c_int32), ("cls_hidden", C.c_int32), ("cls_out", C.c_int32),
-                ("cls_layers", C.c_int32), ("dropout", C.c_float), ("ffn_dim", C.c_int32), ("planes", C.c_int32)]
+                ("cls_layers", C.c_int32), ("dropout", C.c_float), ("ffn_dim", C.c_int32), ("planes", C.c_int32),
+                ("planes_bwd", C.c_int32)]
 
 
 XCHG_MAX_RANKS, XCHG_MAX_CTAS = 16, 64

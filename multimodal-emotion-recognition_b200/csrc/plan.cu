@@ -357,6 +357,7 @@ static int build_model(m2f_model* md) {
     M2F_REQUIRE(!c.fam_enabled || (c.audio.enabled && c.text.enabled), M2F_ERR_ARG,
                 "Fusion Attention Module can only be used with both audio and text enabled!");
     M2F_REQUIRE(c.planes >= 1 && c.planes <= 3, M2F_ERR_ARG, "planes must be 1, 2 or 3");
+    M2F_REQUIRE(c.planes_bwd >= 0 && c.planes_bwd <= c.planes, M2F_ERR_ARG, "planes_bwd must be 0 (= planes) or 1..planes");
     M2F_REQUIRE(c.dropout >= 0.f && c.dropout < 1.f, M2F_ERR_ARG, "dropout must be in [0, 1)");
     M2F_REQUIRE(c.ffn_dim > 0 && c.ffn_dim % 8 == 0, M2F_ERR_ARG, "ffn_dim must be a positive multiple of 8");
     M2F_REQUIRE(c.fam_dim > 0 && c.fam_dim % 8 == 0, M2F_ERR_UNSUPPORTED, "FAM.embedding_size must be a positive multiple of 8");
@@ -602,7 +603,7 @@ struct Ctx {
     uint8_t* shadow;
     uint8_t* ws;
     cudaStream_t st;   // the caller's stream: everything forks from and joins back into it
-    int P;
+    int P;             // planes of the forward's operands (weights shadow, saved activations)
     cudaStream_t cur = nullptr;  // stream the next kernels are enqueued on
 
     cudaStream_t stream() const { return cur ? cur : st; }
@@ -717,6 +718,14 @@ struct Ctx {
         m2f_planes_t t;
         t.ptr = (b.base == WS ? ws : shadow) + b.off;
         t.rows = b.rows; t.cols = b.cols; t.ld = b.ld; t.plane_stride = b.stride; t.planes = b.planes; t._pad = 0;
+        return t;
+    }
+    // Backward operand view: the leading planes_bwd planes of a saved activation / weight matrix (scratch buffers of the
+    // backward are allocated with planes_bwd planes, for them this is the whole matrix).
+    m2f_planes_t pvb(const Buf& b) const {
+        m2f_planes_t t = pv(b);
+        const int pb = p->m->cfg.planes_bwd > 0 ? p->m->cfg.planes_bwd : p->m->cfg.planes;
+        if (t.planes > pb) t.planes = pb;
         return t;
     }
     static m2f_planes_t cols(m2f_planes_t t, int64_t c0, int64_t n) {
@@ -972,10 +981,10 @@ static int backward_modality(Ctx& c, Modality& mo, const uint8_t* key_pad, const
     float* Bq = c.f32(sc.gB);
     const int64_t gld = sc.gG.ld;
     // projection: dW, db, and g = dropmask0(dproj . Wp)
-    m2f_planes_t xp = c.pv(mo.xout_pl[mo.T - 1]);
+    m2f_planes_t xp = c.pvb(mo.xout_pl[mo.T - 1]);
     M2F_TRY(lin_wgrad(c, wst, dproj, xp, c.grd(mo.proj.w_off), mo.proj.in, nullptr, mo.proj.out, mo.proj.in));  // db: by dproj's producer
     M2F_TRY(c.done_down_to(mo.proj.w_off));
-    OP(c.gemm(dproj, false, c.pv(mo.proj.w), true, M, D, Epi().drop(pd, seed, step, M2F_SITE_MOD(mo.idx, 0), D).f32(G, gld)));
+    OP(c.gemm(dproj, false, c.pvb(mo.proj.w), true, M, D, Epi().drop(pd, seed, step, M2F_SITE_MOD(mo.idx, 0), D).f32(G, gld)));
     int nlayer = 0;
     for (int t = mo.T - 1; t >= 0; --t) {
         const EncLayer& lastl = mo.layers[(size_t)t * mo.L + mo.L - 1];
@@ -987,9 +996,9 @@ static int backward_modality(Ctx& c, Modality& mo, const uint8_t* key_pad, const
             const bool first = (t == 0 && l == 0);
             const int par = nlayer & 1;
             if (nlayer >= 2 && wst != c.stream()) M2F_CUDA(cudaStreamWaitEvent(c.stream(), p->wg_ev[mo.idx][par], 0));
-            m2f_planes_t dx2 = c.pv(sc.dx2[par]), dx1 = c.pv(sc.dx1[par]), dhp = c.pv(sc.dh[par]), dop = c.pv(sc.do_[par]), dqkvp = c.pv(sc.dqkv[par]);
-            m2f_planes_t in_pl = (l > 0) ? c.pv(mo.layers[(size_t)t * mo.L + l - 1].x2_pl) : (t > 0 ? c.pv(mo.xout_pl[t - 1]) : c.pv(mo.in_pl));
-            m2f_planes_t h = c.pv(e.h_pl), x1p = c.pv(e.x1_pl), o = c.pv(e.o_pl), qkv = c.pv(e.qkv_pl);
+            m2f_planes_t dx2 = c.pvb(sc.dx2[par]), dx1 = c.pvb(sc.dx1[par]), dhp = c.pvb(sc.dh[par]), dop = c.pvb(sc.do_[par]), dqkvp = c.pvb(sc.dqkv[par]);
+            m2f_planes_t in_pl = (l > 0) ? c.pvb(mo.layers[(size_t)t * mo.L + l - 1].x2_pl) : (t > 0 ? c.pvb(mo.xout_pl[t - 1]) : c.pvb(mo.in_pl));
+            m2f_planes_t h = c.pvb(e.h_pl), x1p = c.pvb(e.x1_pl), o = c.pvb(e.o_pl), qkv = c.pvb(e.qkv_pl);
             // LN2: A = d x2 -> Bq = d y2 (fp32), dx2 = dropmask3(d y2), db2 += colsum
             OP(m2f_ln_bwd(A, gld, c.f32(e.y2), e.y2.ld, c.prm(e.g2), c.f32(e.st2), M, D, Bq, gld, &dx2, pd, seed, step,
                                M2F_SITE_ENC(mo.idx, t, l, 3), c.grd(e.g2), c.grd(e.be2), c.grd(e.w2.b_off), c.stream()));
@@ -997,17 +1006,17 @@ static int backward_modality(Ctx& c, Modality& mo, const uint8_t* key_pad, const
             // the layer computed last: hand its weights over one by one, so that only the final one is left behind the backward
             if (first && fine_tail()) M2F_TRY(c.done_down_to(e.w2.w_off, true));
             // dh = (d y2 . W2) * [h > 0] / (1-p)   (relu + dropout backward from the saved output)
-            OP(c.gemm(dx2, false, c.pv(e.w2.w), true, M, e.w2.in, Epi().gate(h, inv_keep(pd)).pl(dhp).colsum(c.grd(e.w1.b_off))));
+            OP(c.gemm(dx2, false, c.pvb(e.w2.w), true, M, e.w2.in, Epi().gate(h, inv_keep(pd)).pl(dhp).colsum(c.grd(e.w1.b_off))));
             M2F_TRY(lin_wgrad(c, wst, dhp, x1p, c.grd(e.w1.w_off), e.w1.in, nullptr, e.w1.out, e.w1.in));
             if (first && fine_tail()) M2F_TRY(c.done_down_to(e.w1.w_off, true));
             // A = d x1 = dh . W1 + d y2
-            OP(c.gemm(dhp, false, c.pv(e.w1.w), true, M, D, Epi().resid(Bq, gld).f32(A, gld)));
+            OP(c.gemm(dhp, false, c.pvb(e.w1.w), true, M, D, Epi().resid(Bq, gld).f32(A, gld)));
             // LN1: A -> Bq = d y1, dx1 = dropmask1(d y1), dbo += colsum
             OP(m2f_ln_bwd(A, gld, c.f32(e.y1), e.y1.ld, c.prm(e.g1), c.f32(e.st1), M, D, Bq, gld, &dx1, pd, seed, step,
                                M2F_SITE_ENC(mo.idx, t, l, 1), c.grd(e.g1), c.grd(e.be1), c.grd(e.wo.b_off), c.stream()));
             M2F_TRY(lin_wgrad(c, wst, dx1, o, c.grd(e.wo.w_off), e.wo.in, nullptr, e.wo.out, e.wo.in));
             if (first && fine_tail()) M2F_TRY(c.done_down_to(e.wo.w_off, true));
-            OP(c.gemm(dx1, false, c.pv(e.wo.w), true, M, D, Epi().pl(dop)));
+            OP(c.gemm(dx1, false, c.pvb(e.wo.w), true, M, D, Epi().pl(dop)));
             m2f_planes_t q = Ctx::cols(qkv, 0, D), k = Ctx::cols(qkv, D, D), v = Ctx::cols(qkv, 2 * D, D);
             m2f_planes_t dq = Ctx::cols(dqkvp, 0, D), dk = Ctx::cols(dqkvp, D, D), dv = Ctx::cols(dqkvp, 2 * D, D);
             float* dbqkv = c.grd(e.qkv.b_off);  // in_proj_bias gradient = column sums of [dq | dk | dv], folded into the attention backward
@@ -1018,8 +1027,8 @@ static int backward_modality(Ctx& c, Modality& mo, const uint8_t* key_pad, const
             M2F_TRY(c.done_down_to(e.qkv.w_off));
             if (!first) {
                 // gradient w.r.t. the layer input = dqkv . Wqkv + d y1 ; at l == 0 it also joins the skip gradient in G
-                if (l > 0) OP(c.gemm(dqkvp, false, c.pv(e.qkv.w), true, M, D, Epi().resid(Bq, gld).f32(A, gld)));
-                else       OP(c.gemm(dqkvp, false, c.pv(e.qkv.w), true, M, D, Epi().resid(Bq, gld).f32(G, gld, true)));
+                if (l > 0) OP(c.gemm(dqkvp, false, c.pvb(e.qkv.w), true, M, D, Epi().resid(Bq, gld).f32(A, gld)));
+                else       OP(c.gemm(dqkvp, false, c.pvb(e.qkv.w), true, M, D, Epi().resid(Bq, gld).f32(G, gld, true)));
             }
         }
     }
@@ -1035,7 +1044,7 @@ static int backward_all(Ctx& c, const uint8_t* key_pad, const float* dlogits, in
     const float pd = p->p_used;
     const uint64_t seed = p->seed, step = p->step;
     const bool fam = !p->fam.empty();
-    m2f_planes_t dl = c.pv(p->dl_pl);
+    m2f_planes_t dl = c.pvb(p->dl_pl);
     if (phases & PH_HEAD) {
         if (dlogits) {
             m2f_planes_t dlc = dl;
@@ -1049,28 +1058,28 @@ static int backward_all(Ctx& c, const uint8_t* key_pad, const float* dlogits, in
     // 1-D gradients are accumulated with atomics: zero that region of the arena
     M2F_CUDA(cudaMemsetAsync(c.grads + md->off_1d, 0, (size_t)(md->arena_floats - md->off_1d) * 4, c.st));
     dl.cols = md->cfg.cls_out;
-    m2f_planes_t zc = c.pv(p->zc_pl);
+    m2f_planes_t zc = c.pvb(p->zc_pl);
     // ---- classifier
     const int n_lin = (int)md->cls.size();
     m2f_planes_t d_cur = dl;
     m2f_planes_t dproj[2];
-    dproj[0] = c.pv(p->dproj_pl);
-    dproj[1] = c.pv(p->dprojt_pl);
-    m2f_planes_t dz = c.pv(p->dz[0]);
+    dproj[0] = c.pvb(p->dproj_pl);
+    dproj[1] = c.pvb(p->dprojt_pl);
+    m2f_planes_t dz = c.pvb(p->dz[0]);
     cudaStream_t ws1 = c.side(1);  // weight gradients of the classifier, the fusion layers and the text stack
     for (int j = n_lin - 1; j >= 0; --j) {
         Lin& L = md->cls[j];
-        m2f_planes_t in = (j == 0) ? zc : c.pv(p->cls_h[j - 1]);
+        m2f_planes_t in = (j == 0) ? zc : c.pvb(p->cls_h[j - 1]);
         // bias gradients ride in the epilogue of the GEMM that produces dY; only dlogits comes from elsewhere
         M2F_TRY(lin_wgrad(c, ws1, d_cur, in, c.grd(L.w_off), L.in, j == n_lin - 1 ? c.grd(L.b_off) : nullptr, L.out, L.in));
         if (j > 0) {
             if (j <= n_lin - 3) M2F_TRY(c.dep(ws1, c.st));  // the buffer written next was an operand of the weight gradient two layers up
-            m2f_planes_t dn = c.pv((j & 1) ? p->dcls_a : p->dcls_b);
+            m2f_planes_t dn = c.pvb((j & 1) ? p->dcls_a : p->dcls_b);
             const float sc = (j == n_lin - 1) ? inv_keep(pd) : 1.f;  // only the last hidden layer has dropout
-            OP(c.gemm(d_cur, false, c.pv(L.w), true, M, L.in, Epi().gate(in, sc).pl(dn).colsum(c.grd(md->cls[j - 1].b_off))));
+            OP(c.gemm(d_cur, false, c.pvb(L.w), true, M, L.in, Epi().gate(in, sc).pl(dn).colsum(c.grd(md->cls[j - 1].b_off))));
             d_cur = dn;
         } else if (md->both) {
-            m2f_planes_t w = c.pv(L.w);
+            m2f_planes_t w = c.pvb(L.w);
             // audio half of the concat: gradient w.r.t. the projection's pre-dropout output (mask regenerated)
             if (fam) {
                 OP(c.gemm(d_cur, false, Ctx::cols(w, 0, Df), true, M, Df,
@@ -1086,7 +1095,7 @@ static int backward_all(Ctx& c, const uint8_t* key_pad, const float* dlogits, in
             }
         } else {
             const int mi = p->mod[0].enabled ? 0 : 1;
-            OP(c.gemm(d_cur, false, c.pv(L.w), true, M, Df,
+            OP(c.gemm(d_cur, false, c.pvb(L.w), true, M, Df,
                            Epi().drop(pd, seed, step, M2F_SITE_MOD(mi, 1), Df).pl(dproj[mi]).colsum(c.grd(p->mod[mi].proj.b_off))));
         }
     }
@@ -1095,7 +1104,7 @@ static int backward_all(Ctx& c, const uint8_t* key_pad, const float* dlogits, in
     if (fam) {
         const int F = (int)p->fam.size();
         m2f_planes_t a = Ctx::cols(zc, 0, Df);
-        m2f_planes_t dkall = c.pv(p->dkall_pl), kall = c.pv(p->kall_pl);
+        m2f_planes_t dkall = c.pvb(p->dkall_pl), kall = c.pvb(p->kall_pl);
         float* gt = c.f32(p->gt_f32);
         const int64_t gt_ld = p->gt_f32.ld;
         int n = 0;
@@ -1104,11 +1113,11 @@ static int backward_all(Ctx& c, const uint8_t* key_pad, const float* dlogits, in
             // scratch rotates (dz over three buffers, the rest over two); a buffer is rewritten only after the weight
             // gradients of the layer that last read it -- two layers up -- have been computed
             if (n >= 2 && ws1 != c.st) M2F_CUDA(cudaStreamWaitEvent(c.st, p->wgf_ev[n & 1], 0));
-            m2f_planes_t dz_cur = c.pv(p->dz[n % 3]), dz_other = c.pv(p->dz[(n + 1) % 3]);
-            m2f_planes_t dxo = c.pv(p->dxo[n & 1]), dattn = c.pv(p->dattn[n & 1]), dqv = c.pv(p->dqv[n & 1]);
-            m2f_planes_t u = c.pv(fl.u_pl), qv = c.pv(fl.qv_pl), xo = c.pv(fl.xo_pl);
-            m2f_planes_t t_in = (f == 0) ? c.pv(p->t0_pl) : Ctx::cols(u, Df, Df);  // the layer's text input
-            m2f_planes_t wl = c.pv(fl.lin.w);
+            m2f_planes_t dz_cur = c.pvb(p->dz[n % 3]), dz_other = c.pvb(p->dz[(n + 1) % 3]);
+            m2f_planes_t dxo = c.pvb(p->dxo[n & 1]), dattn = c.pvb(p->dattn[n & 1]), dqv = c.pvb(p->dqv[n & 1]);
+            m2f_planes_t u = c.pvb(fl.u_pl), qv = c.pvb(fl.qv_pl), xo = c.pvb(fl.xo_pl);
+            m2f_planes_t t_in = (f == 0) ? c.pvb(p->t0_pl) : Ctx::cols(u, Df, Df);  // the layer's text input
+            m2f_planes_t wl = c.pvb(fl.lin.w);
             // linear on the concat
             M2F_TRY(lin_wgrad(c, ws1, dz_cur, u, c.grd(fl.lin.w_off), fl.lin.in, nullptr, fl.lin.out, fl.lin.in));
             // left half of d u -> gradient w.r.t. the out-proj output (gate: relu(x) > 0)
@@ -1124,7 +1133,7 @@ static int backward_all(Ctx& c, const uint8_t* key_pad, const float* dlogits, in
             }
             // attention out-proj
             M2F_TRY(lin_wgrad(c, ws1, dxo, xo, c.grd(fl.wo.w_off), fl.wo.in, nullptr, fl.wo.out, fl.wo.in));
-            OP(c.gemm(dxo, false, c.pv(fl.wo.w), true, M, Df, Epi().pl(dattn)));
+            OP(c.gemm(dxo, false, c.pvb(fl.wo.w), true, M, Df, Epi().pl(dattn)));
             m2f_planes_t q = Ctx::cols(qv, 0, Df), v = Ctx::cols(qv, Df, Df), k = Ctx::cols(kall, (int64_t)f * Df, Df);
             m2f_planes_t dq = Ctx::cols(dqv, 0, Df), dv = Ctx::cols(dqv, Df, Df), dk = Ctx::cols(dkall, (int64_t)f * Df, Df);
             // in-projection weight / bias gradients: rows [0,E) = q, [E,2E) = k, [2E,3E) = v of in_proj_weight
@@ -1139,15 +1148,15 @@ static int backward_all(Ctx& c, const uint8_t* key_pad, const float* dlogits, in
             M2F_TRY(c.done_down_to(fl.inw_off));
             // second + third contributions to the text-input gradient: [dq | dv] . [Wq; Wv], same gate, summed with gt
             if (f > 0) {
-                OP(c.gemm(dqv, false, c.pv(fl.qv.w), true, M, Df,
+                OP(c.gemm(dqv, false, c.pvb(fl.qv.w), true, M, Df,
                                Epi().gate(t_in, inv_keep(pd)).resid(gt, gt_ld).pl(dz_other).colsum(c.grd(p->fam[f - 1].lin.b_off))));
             } else {
-                OP(c.gemm(dqv, false, c.pv(fl.qv.w), true, M, Df,
+                OP(c.gemm(dqv, false, c.pvb(fl.qv.w), true, M, Df,
                                Epi().drop(pd, seed, step, M2F_SITE_MOD(1, 1), Df).resid(gt, gt_ld).pl(dproj[1]).colsum(c.grd(p->mod[1].proj.b_off))));
             }
         }
         // audio: every layer's K projection + the classifier half, through the projection dropout mask
-        OP(c.gemm(dkall, false, c.pv(md->wk_all.w), true, M, Df,
+        OP(c.gemm(dkall, false, c.pvb(md->wk_all.w), true, M, Df,
                        Epi().drop(pd, seed, step, M2F_SITE_MOD(0, 1), Df).resid(c.f32(p->ga_f32), p->ga_f32.ld).pl(dproj[0]).colsum(c.grd(p->mod[0].proj.b_off))));
     }
     // NOTE on the f == 0 text contribution through q/v: q and v read t0 itself (no cat-relu on that path), so only the
@@ -1291,6 +1300,7 @@ extern "C" int m2f_plan_create(m2f_model_t* m, int64_t B, int64_t S, int32_t tra
     p->training = training_plan;
     const int64_t M = p->M;
     const int P = m->cfg.planes, FF = m->cfg.ffn_dim, Df = m->Df;
+    const int Pb = m->cfg.planes_bwd > 0 ? m->cfg.planes_bwd : P;  // planes of the backward's own buffers
     int Dmax = 0;
     p->mod[0] = m->mod[0];
     p->mod[1] = m->mod[1];
@@ -1360,7 +1370,7 @@ extern "C" int m2f_plan_create(m2f_model_t* m, int64_t B, int64_t S, int32_t tra
     p->cls_h.resize(m->cls.size() - 1);
     for (size_t j = 0; j + 1 < m->cls.size(); ++j) p->cls_h[j] = p->alloc_pl(M, m->cls[j].out, P);
     if (training_plan) {
-        p->dl_pl = p->alloc_pl(M, 8 * ((m->cfg.cls_out + 7) / 8), P);
+        p->dl_pl = p->alloc_pl(M, 8 * ((m->cfg.cls_out + 7) / 8), Pb);
         // every backward scratch matrix gets ld = its own width; the two stacks run side by side, so each has its own
         for (int i = 0; i < 2; ++i) {
             if (!m->mod[i].enabled) continue;
@@ -1370,25 +1380,25 @@ extern "C" int m2f_plan_create(m2f_model_t* m, int64_t B, int64_t S, int32_t tra
             sc.gA = p->alloc_f32(M, D);
             sc.gB = p->alloc_f32(M, D);
             for (int j = 0; j < 2; ++j) {
-                sc.dx2[j] = p->alloc_pl(M, D, P);
-                sc.dx1[j] = p->alloc_pl(M, D, P);
-                sc.dh[j] = p->alloc_pl(M, FF, P);
-                sc.do_[j] = p->alloc_pl(M, D, P);
-                sc.dqkv[j] = p->alloc_pl(M, 3 * D, P);
+                sc.dx2[j] = p->alloc_pl(M, D, Pb);
+                sc.dx1[j] = p->alloc_pl(M, D, Pb);
+                sc.dh[j] = p->alloc_pl(M, FF, Pb);
+                sc.do_[j] = p->alloc_pl(M, D, Pb);
+                sc.dqkv[j] = p->alloc_pl(M, 3 * D, Pb);
             }
         }
-        p->dcls_a = p->alloc_pl(M, m->cfg.cls_hidden, P);
-        p->dcls_b = p->alloc_pl(M, m->cfg.cls_hidden, P);
-        for (int j = 0; j < 3; ++j) p->dz[j] = p->alloc_pl(M, Df, P);
-        p->dproj_pl = p->alloc_pl(M, Df, P);
-        p->dprojt_pl = p->alloc_pl(M, Df, P);
+        p->dcls_a = p->alloc_pl(M, m->cfg.cls_hidden, Pb);
+        p->dcls_b = p->alloc_pl(M, m->cfg.cls_hidden, Pb);
+        for (int j = 0; j < 3; ++j) p->dz[j] = p->alloc_pl(M, Df, Pb);
+        p->dproj_pl = p->alloc_pl(M, Df, Pb);
+        p->dprojt_pl = p->alloc_pl(M, Df, Pb);
         if (!m->fam.empty()) {
             for (int j = 0; j < 2; ++j) {
-                p->dxo[j] = p->alloc_pl(M, Df, P);
-                p->dattn[j] = p->alloc_pl(M, Df, P);
-                p->dqv[j] = p->alloc_pl(M, 2 * Df, P);
+                p->dxo[j] = p->alloc_pl(M, Df, Pb);
+                p->dattn[j] = p->alloc_pl(M, Df, Pb);
+                p->dqv[j] = p->alloc_pl(M, 2 * Df, Pb);
             }
-            p->dkall_pl = p->alloc_pl(M, (int64_t)m->fam.size() * Df, P);
+            p->dkall_pl = p->alloc_pl(M, (int64_t)m->fam.size() * Df, Pb);
             p->gt_f32 = p->alloc_f32(M, Df);
             p->ga_f32 = p->alloc_f32(M, Df);
         }

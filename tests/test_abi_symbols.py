@@ -29,7 +29,7 @@ def test_library_exports_every_declared_symbol(pkg):
 def test_binding_covers_every_declared_symbol(pkg):
     assert sorted(pkg._lib.PROTOTYPES) == declared()
     L = pkg._lib.lib()
-    assert L.m2f_abi_version() == 1
+    assert L.m2f_abi_version() == 2
     assert L.m2f_launch_count() == 0
 
 

@@ -1,0 +1,136 @@
+"""Train-mode parity of the WHOLE model with dropout on (the mode every bench number is taken in).
+
+The reference fires dropout at 63 sites per forward (src/model.py:57,97,111,113,123,125,131; attention-probability dropout
+after the softmax, torch/nn/functional.py:6643-6645; dropout1 / dropout / dropout2 of every encoder layer,
+torch/nn/modules/transformer.py:977,981-982) from torch's global RNG, which nothing else can reproduce bit for bit.  The
+product draws its masks from Philox keyed by (seed, step, site, element); the oracle takes masks as inputs.  So the test
+runs the product in train() with p = 0.4, pulls the keep-mask of EVERY site for that (seed, step) out of the library
+(`m2f_dropout_mask`, sites M2F_SITE_ENC / MOD / FAM / CLS, attention masks with the S8 row stride), feeds exactly those
+masks to the fp64 oracle, and compares logits (valid rows), loss and every parameter gradient at the fp32-parity
+tolerance.  That pins, end to end: the site numbering of plan.cu, forward / backward mask agreement at all sites, the
+element-index conventions (m * ld + col in GEMM epilogues and LayerNorm kernels, ((b*H + h)*S + i)*S8 + j in attention),
+the 1/(1-p) of the ReLU-gate epilogues, and the final LayerNorm that also applies the pre-projection dropout."""
+import pytest
+import torch
+
+from oracle import m2fnet_oracle as O
+from oracle.gen_golden import CASES
+
+pytestmark = pytest.mark.gpu
+
+P_DROP = 0.4
+
+
+@pytest.fixture(scope="module")
+def P(pkg):
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    pkg._lib.check(pkg._lib.lib().m2f_check_device(), "check_device")
+    return pkg
+
+
+class SiteMasks:
+    """drop_masks callable for oracle.forward: (site, shape) -> {0,1} tensor regenerated from the library's Philox stream."""
+
+    def __init__(self, P, seed, step, p=P_DROP):
+        self.P, self.seed, self.step, self.p = P, seed, step, p
+        self.sites = {}
+
+    def __call__(self, site, shape):
+        if len(shape) == 4:  # attention probabilities [B, H, S, S]: element ((b*H + h)*S + i)*S8 + j
+            B, H, S, _ = shape
+            S8 = (S + 7) // 8 * 8
+            m = self.P.ops.dropout_mask(self.p, self.seed, self.step, site, B * H * S * S8, "cuda").cpu()
+            m = m.reshape(B, H, S, S8)[..., :S]
+        else:  # [B, S, width]: element (b*S + s)*width + col
+            n = 1
+            for d in shape:
+                n *= d
+            m = self.P.ops.dropout_mask(self.p, self.seed, self.step, site, n, "cuda").cpu().reshape(shape)
+        assert site not in self.sites, f"site {site:#x} used twice in one forward"
+        self.sites[site] = float(m.double().mean())
+        return m.double()
+
+
+def expected_sites(cfg):
+    n = 0
+    for mc in (cfg.AUDIO, cfg.TEXT):
+        if mc.enabled:
+            n += 4 * mc.n_transformers * mc.n_encoder_layers + 2
+    if cfg.FAM.enabled:
+        n += 2 * cfg.FAM.n_layers
+    return n + 1
+
+
+def run_train_mode(P, cfg, B, S, weighted, steps=1, **model_kw):
+    params = O.synth_params(cfg)
+    model = P.M2FNet(cfg, **model_kw)
+    model.load_state_dict({k: v.float() for k, v in params.items()}, strict=True)
+    model = model.to("cuda").train()
+    b = O.synth_inputs(B, S, cfg.TEXT.embedding_size, cfg.AUDIO.embedding_size, C=cfg.CLASSIFIER.output_size)
+    w = None
+    if weighted:
+        p = torch.tensor([.47, .17, .07, .11, .12, .03, .03], dtype=torch.float64)[:cfg.CLASSIFIER.output_size]
+        w = 1.0 / (cfg.CLASSIFIER.output_size * p / p.sum())
+    crit = torch.nn.CrossEntropyLoss(weight=None if w is None else w.float().cuda(), ignore_index=-1, label_smoothing=0.1)
+    results = []
+    for _ in range(steps):
+        model.zero_grad(set_to_none=True)
+        out = model(b["text"].cuda(), b["audio"].cuda(), b["padding_mask"].cuda())
+        loss = crit(out.permute(0, 2, 1), b["emotion"].cuda())
+        loss.backward()
+        torch.cuda.synchronize()
+        masks = SiteMasks(P, model._seed, model._step)
+        ref_logits, ref_loss, ref_grads = O.loss_and_grads(params, cfg, b["text"].double(), b["audio"].double(), b["padding_mask"],
+                                                           b["emotion"], w, drop_masks=masks, p=P_DROP)
+        valid = ~b["padding_mask"]
+        got = {O.canonical_name(n): q.grad.detach().cpu().double() for n, q in model.named_parameters()}
+        names = [n for n in ref_grads]
+        per = {n: O.rel_l2(got[n], ref_grads[n]) for n in names if float(ref_grads[n].abs().max()) > 0}
+        cat = O.rel_l2(torch.cat([got[n].flatten() for n in names]), torch.cat([ref_grads[n].flatten() for n in names]))
+        results.append(dict(logits=O.rel_l2(out.detach().cpu()[valid], ref_logits[valid]),
+                            loss=abs(loss.item() - ref_loss.item()) / abs(ref_loss.item()), grads=cat,
+                            worst=max(per.items(), key=lambda kv: kv[1]), sites=masks.sites, out=out.detach().cpu(), valid=valid))
+    return results
+
+
+@pytest.mark.parametrize("name", ["meld_base_2l", "shared_norm_cls3_weighted", "concat_no_fam", "audio_only"])
+def test_train_mode_parity_with_replayed_masks(P, name):
+    over, B, S, ragged, weighted = CASES[name]
+    cfg = O.default_model_cfg(dropout=P_DROP, **over)
+    r1, r2 = run_train_mode(P, cfg, B, S, weighted, steps=2, planes=3)
+    for r in (r1, r2):
+        print(f"{name}: logits {r['logits']:.2e} loss {r['loss']:.2e} grads {r['grads']:.2e} worst {r['worst']}")
+        assert len(r["sites"]) == expected_sites(cfg), (len(r["sites"]), expected_sites(cfg))
+        assert r["logits"] < 1e-4 and r["loss"] < 1e-4 and r["grads"] < 1e-4
+        assert r["worst"][1] < 1e-3, r["worst"]
+    if name == "meld_base_2l":  # large sites: the keep rate is 1 - p
+        big = [v for v in r1["sites"].values()]
+        assert all(abs(v - (1 - P_DROP)) < 0.02 for v in big), sorted(r1["sites"].items(), key=lambda kv: abs(kv[1] - 0.6))[-3:]
+    # the second step drew different masks: same weights, same batch, different logits
+    v = r1["valid"]
+    assert O.rel_l2(r2["out"][v], r1["out"][v]) > 1e-2
+
+
+def test_masks_depend_on_step_and_site(P):
+    a = P.ops.dropout_mask(P_DROP, 11, 5, 0x1001, 1 << 16, "cuda")
+    b = P.ops.dropout_mask(P_DROP, 11, 6, 0x1001, 1 << 16, "cuda")
+    c = P.ops.dropout_mask(P_DROP, 11, 5, 0x1002, 1 << 16, "cuda")
+    d = P.ops.dropout_mask(P_DROP, 11, 5, 0x1001, 1 << 16, "cuda")
+    assert torch.equal(a, d)
+    for other in (b, c):
+        agree = (a == other).float().mean().item()
+        assert 0.45 < agree < 0.60  # independent Bernoulli(0.6) masks agree with probability 0.52
+
+
+def test_train_mode_parity_in_the_default_precision_mode(P):
+    """The benched configuration (bf16x2f: 2-plane forward, 1-plane backward; dropout 0.4) against the oracle fed the same masks:
+    BASELINE.json's bf16 tolerance."""
+    over, B, S, ragged, weighted = CASES["meld_base_2l"]
+    cfg = O.default_model_cfg(dropout=P_DROP, **over)
+    model = P.M2FNet(cfg, precision="bf16x2f")
+    assert (model.planes, model.planes_bwd) == (2, 1)
+    del model
+    (r,) = run_train_mode(P, cfg, B, S, weighted, steps=1, precision="bf16x2f")
+    print(f"bf16x2f + dropout: logits {r['logits']:.2e} loss {r['loss']:.2e} grads {r['grads']:.2e} worst {r['worst']}")
+    assert r["logits"] < 2e-2 and r["loss"] < 2e-2 and r["grads"] < 2e-2

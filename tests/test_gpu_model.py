@@ -1,6 +1,7 @@
 """Model-level parity on the GPU: the product `M2FNet` (one C call forward, one C call backward, sm_100a kernels)
 against the golden fixtures recorded from the UNMODIFIED reference module in fp64 (tests/golden/, oracle/gen_golden.py).
-Tolerances are BASELINE.json's: 1e-4 relative in the fp32-parity mode (planes = 3), 2e-2 in bf16 (planes = 1);
+Tolerances are BASELINE.json's: 1e-4 relative in the fp32-parity mode (planes = 3), 2e-2 in the bf16 training mode
+(planes = 2 forward / 1 backward, "bf16x2f");
 logits are compared on valid rows only; per-tensor gradient bounds follow SURVEY.md 8c."""
 import pytest
 import torch
@@ -20,11 +21,11 @@ def P(pkg):
     return pkg
 
 
-def run_case(P, name, planes, fused_loss=False):
+def run_case(P, name, planes, fused_loss=False, planes_bwd=None):
     over, B, S, ragged, weighted = CASES[name]
     cfg = O.default_model_cfg(dropout=0.0, **over)
     z = load_case(name)
-    model = P.M2FNet(cfg, planes=planes)
+    model = P.M2FNet(cfg, planes=planes, planes_bwd=planes_bwd)
     model.load_state_dict({k: v.float() for k, v in O.synth_params(cfg).items()}, strict=True)
     model = model.to("cuda")
     model.train()
@@ -58,16 +59,28 @@ def test_fp32_parity_mode(P, name):
 
 
 @pytest.mark.parametrize("name", sorted(CASES))
-def test_bf16_mode(P, name):
-    """BASELINE.json's bf16 tolerance (2e-2 on logits and on the concatenated gradients) is judged on the MELD-sized case.
-    The toy cases (widths 32-64, 12-36 rows) are too small for bf16 rounding to average out -- torch's own bf16 autocast
-    of the reference misses 2e-2 on gradients even at full size -- so they only get a sanity bound."""
+def test_bf16_training_mode_meets_2e2(P, name):
+    """The declared bf16 training mode (precision "bf16x2f": two bf16 planes in the forward, one in the backward -- the
+    default, and what bench.py's headline runs) at BASELINE.json's numbers: 2e-2 on logits, loss AND the concatenated
+    gradients, every case.  SURVEY.md 8c's protocol (real init, full depth, per-tensor list) is tests/test_gpu_protocol.py."""
+    over, B, S, ragged, weighted = CASES[name]
+    e_logits, e_loss, e_grad, per, pred_same = run_case(P, name, planes=2, planes_bwd=1)
+    worst = max(per.items(), key=lambda kv: kv[1])
+    print(f"{name}: logits {e_logits:.2e} loss {e_loss:.2e} grads {e_grad:.2e} worst {worst}")
+    assert e_logits < 2e-2 and e_loss < 2e-2 and e_grad < 2e-2
+    assert pred_same == 1.0
+
+
+@pytest.mark.parametrize("name", sorted(CASES))
+def test_plain_bf16_mode(P, name):
+    """One bf16 plane everywhere (precision "bf16"): the inference mode.  Logits and loss meet 2e-2; its gradients do NOT
+    (ReLU gates decided by a rounded forward, profiles/r2_bf16_protocol_cpu.json) -- which is why it is not the training
+    default -- and are only held to the level of an ideal bf16-operand pipeline (oracle/bf16_emulation.py)."""
     e_logits, e_loss, e_grad, per, pred_same = run_case(P, name, planes=1)
     worst = max(per.items(), key=lambda kv: kv[1])
     print(f"{name}: logits {e_logits:.2e} loss {e_loss:.2e} grads {e_grad:.2e} worst {worst}")
     assert e_logits < 2e-2 and e_loss < 2e-2
     if name == "meld_base_2l":
-        # gradients: no worse than an ideal bf16-operand pipeline (oracle/bf16_emulation.py, level stored in the fixture)
         z = load_case(name)
         assert e_logits < 1.25 * float(z["bf16emu/logits"]) and e_grad < 1.25 * float(z["bf16emu/grads"])
     else:
@@ -75,8 +88,7 @@ def test_bf16_mode(P, name):
 
 
 def test_bf16x2_mode_meets_2e2_on_gradients(P):
-    """Two bf16 planes (16 mantissa bits, 3 plane products per GEMM) is the cheapest mode that meets BASELINE.json's 2e-2 on
-    gradients as well as on logits at MELD sizes."""
+    """Two bf16 planes everywhere (16 mantissa bits, 3 + 3 + 3 plane products per Linear)."""
     e_logits, e_loss, e_grad, per, pred_same = run_case(P, "meld_base_2l", planes=2)
     print(f"bf16x2: logits {e_logits:.2e} loss {e_loss:.2e} grads {e_grad:.2e}")
     assert e_logits < 1e-3 and e_grad < 2e-2 and pred_same == 1.0

@@ -87,3 +87,31 @@ def test_batch_metrics_match_sklearn():
     y, yp = tgt[m].numpy(), logits.argmax(-1)[m].numpy()
     assert abs(acc - accuracy_score(y, yp)) < 1e-12
     assert abs(f1 - f1_score(y, yp, average="weighted")) < 1e-12
+
+
+def test_protocol_default_init_matches_the_reference_distributions():
+    """oracle/bf16_protocol.default_init (used on the GPU box, where /root/reference does not exist) restates the init of the
+    reference's torch modules: same names / shapes, same per-tensor spread, same cloned-layer structure."""
+    import os
+    import pytest
+    import torch
+    from oracle import bf16_protocol as BP
+    from oracle import m2fnet_oracle as O
+    if not os.path.exists("/root/reference/src/model.py"):
+        pytest.skip("reference not present (GPU box)")
+    cfg = O.default_model_cfg(dropout=0.0, AUDIO=dict(n_encoder_layers=2), TEXT=dict(n_encoder_layers=2), FAM=dict(n_layers=2))
+    torch.manual_seed(0)
+    mine = BP.default_init(cfg)
+    ref = BP.protocol_params(cfg, seed=0, perturb=0.0)  # the imported reference's state_dict
+    assert sorted(mine) == sorted(ref)
+    for k in mine:
+        a, b = mine[k].double(), ref[k].double()
+        assert a.shape == b.shape, k
+        if b.std() == 0:  # zero biases, LayerNorm ones / zeros
+            assert torch.equal(a, b), k
+        elif a.numel() >= 512:
+            assert abs(a.std() / b.std() - 1) < 0.08 and abs(a.abs().max() / b.abs().max() - 1) < 0.08, k
+        else:  # a handful of values: same order of magnitude is all that can be said
+            assert 0.2 < float(a.abs().max() / b.abs().max()) < 5.0, k
+    assert torch.equal(mine["text_encoders.0.layers.0.linear1.weight"], mine["text_encoders.0.layers.1.linear1.weight"])
+    assert not torch.equal(mine["text_encoders.0.layers.0.linear1.weight"], mine["audio_encoders.0.layers.0.linear1.weight"])
