@@ -181,9 +181,8 @@ ln_bwd_kernel(const float* __restrict__ g, int64_t g_ld, const float* __restrict
 }
 
 // ------------------------------------------------------------------------------------------ forward, staged through shared memory
-// EXPERIMENT (M2F_LN_V2=1: forward, measured 0.74 of the HBM peak at M = 131 072, op parity green; M2F_LN_V2=2: backward too,
-// not yet run on a GPU; off by default): the register-resident kernel above keeps 16 - 20 warps per SM with one 3 KB row in
-// flight each and reaches 0.48 of the HBM peak at M = 131 072.  Here a block moves tiles of 8 rows
+// Large-M variant (selected by ln_v2_level below): the register-resident kernel above keeps 16 - 20 warps per SM with one 3 KB
+// row in flight each and reaches 0.48 of the HBM peak at M = 131 072.  Here a block moves tiles of 8 rows
 // of x (and skip) into a 2-deep shared-memory ring with bulk asynchronous copies issued by one thread (cp.async.bulk,
 // completion on an mbarrier): 48 KB per stage and 96 KB per block are in flight without costing registers, and the
 // arithmetic of tile t overlaps the landing of tile t + 1.  Same arithmetic and the same Philox element indices as above.
@@ -447,12 +446,18 @@ ln_bwd_staged_kernel(const float* __restrict__ g, int64_t g_ld, const float* __r
     }
 }
 
-// M2F_LN_V2: 0 / unset = register-resident kernels, 1 = staged forward, 2 = staged forward and backward
-static int ln_v2_level() {
-    static const int lvl = [] { const char* e = std::getenv("M2F_LN_V2"); return e ? std::atoi(e) : 0; }();
-    return lvl;
+// Which kernel family: the register-resident kernels keep a row per warp in registers -- best while the tensors sit in
+// L2 (training sizes: 9 - 13 us per launch, and their 0 bytes of dynamic shared memory let them share an SM with a GEMM CTA
+// pair) -- but only 16 - 20 warps fit an SM, too few loads in flight for HBM: 0.48 / 0.44 of the HBM peak at M = 131 072.
+// The staged kernels (bulk asynchronous copies into a 2-deep ring, 96 KB in flight per block) reach 0.74 there.  Rule: staged
+// once one fp32 [M, D] operand is 32 MB or more (the kernel's three to four operands then exceed the 126 MB L2).
+// M2F_LN_V2 overrides: 0 = never staged, 1 = staged forward always, 2 = staged forward and backward always.
+constexpr int64_t LN_STAGED_MIN_BYTES = 32ll << 20;
+static int ln_v2_level(int64_t M, int64_t D) {
+    if (const char* e = std::getenv("M2F_LN_V2")) return std::atoi(e);  // read per call: tests switch it inside one process
+    return M * D * 4 >= LN_STAGED_MIN_BYTES ? 2 : 0;
 }
-static bool ln_v2_enabled() { return ln_v2_level() >= 1; }
+static bool ln_v2_enabled(int64_t M, int64_t D) { return ln_v2_level(M, D) >= 1; }
 
 static int ln_grid(int64_t M, int rows_per_warp) {
     int64_t blocks = (M + LN_WARPS * rows_per_warp - 1) / (LN_WARPS * rows_per_warp);
@@ -510,7 +515,7 @@ extern "C" int m2f_ln_fwd(const float* x, int64_t x_ld, const float* gamma, cons
     M2F_REQUIRE(y_f32 || ypl, M2F_ERR_ARG, "ln_fwd: no output given");
     const Drop drop = drop_make(drop_p, seed, step, site);
     auto st = reinterpret_cast<cudaStream_t>(stream);
-    if (ln_v2_enabled() && (!skip || (reinterpret_cast<uintptr_t>(skip) % 16 == 0 && skip_ld % 4 == 0))) {
+    if (ln_v2_enabled(M, D) && (!skip || (reinterpret_cast<uintptr_t>(skip) % 16 == 0 && skip_ld % 4 == 0))) {
         const size_t smem = (size_t)LN2_STAGES * LN2_ROWS * D * 4 * (skip ? 2 : 1);
         int64_t blocks = (M + LN2_ROWS - 1) / LN2_ROWS;
         if (blocks > 148 * 2) blocks = 148 * 2;
@@ -552,7 +557,7 @@ extern "C" int m2f_ln_bwd(const float* g, int64_t g_ld, const float* x, int64_t 
     auto st = reinterpret_cast<cudaStream_t>(stream);
     M2F_REQUIRE((!dgamma || (reinterpret_cast<uintptr_t>(dgamma) % 16) == 0) && (!dbeta || (reinterpret_cast<uintptr_t>(dbeta) % 16) == 0) &&
                     (!dbias || (reinterpret_cast<uintptr_t>(dbias) % 16) == 0), M2F_ERR_ALIGN, "ln_bwd: dgamma / dbeta / dbias must be 16-byte aligned");
-    if (ln_v2_level() >= 2) {
+    if (ln_v2_level(M, D) >= 2) {
         const size_t smem = (size_t)LN2_STAGES * LN2_ROWS * D * 4 * 2;
         int64_t blocks = (M + LN2_ROWS - 1) / LN2_ROWS;
         if (blocks > 148 * 2) blocks = 148 * 2;

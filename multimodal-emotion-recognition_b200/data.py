@@ -87,6 +87,10 @@ class SyntheticMELD:
                  pool: int = 0):
         from .parallel import shard_range
         self.lo, self.hi = shard_range(n_dialogues, rank, world)
+        # every rank must run the SAME number of steps (the gradient exchange is collective: a rank with one batch more
+        # would wait for peers that never come): all ranks keep the size of the smallest shard, i.e. at most world - 1
+        # dialogues of the epoch are dropped (the DistributedSampler(drop_last=True) convention)
+        self.hi = self.lo + n_dialogues // world
         self.bs, self.S, self.Dt, self.Da, self.C = batch_size, S, Dt, Da, C
         self.seed, self.ragged, self.audio_kind, self.pin = seed, ragged, audio_kind, pin
         self.pool = [self._make(i) for i in range(pool)] if pool else None
@@ -281,6 +285,9 @@ class LengthBucketSampler:
                 out.append((chunk, S))
         if self.shuffle:
             out = [out[i] for i in rng.permutation(len(out))]
+        # equal step counts on every rank (the gradient exchange is collective): the last len(out) % world batches of the
+        # epoch's (reshuffled every epoch) order are dropped, DistributedSampler(drop_last=True) style
+        out = out[:len(out) // self.world * self.world]
         return out[self.rank::self.world]
 
     def __len__(self):

@@ -182,14 +182,33 @@ class DataParallelM2FNet(torch.nn.Module):
         dist.broadcast(flat, src=dist.get_global_rank(group, 0) if group is not None else 0, group=group)
         self.reducer = None
         if exchange != "nccl" and flat.is_cuda:
+            # Collective-safe choice of the path: (1) every rank probes, WITHOUT any collective, whether it could take part
+            # (the private symmetric-memory module imports, the device supports it); (2) the ranks vote with one all-reduce;
+            # (3) only if all can, they enter the set-up (its rendezvous / barrier are collectives every rank then reaches);
+            # (4) a second vote catches a rank whose set-up raised after the rendezvous.  A rank never blocks in a collective
+            # its peers skipped.
             err = None
             try:
-                self.reducer = PeerGradExchange(model, group, average)
-            except Exception as e:  # no symmetric memory on this box / fabric
-                err = e
-            ok = torch.tensor([0 if self.reducer is None else 1], device=flat.device)
-            dist.all_reduce(ok, op=dist.ReduceOp.MIN, group=group)  # all ranks take the same path
-            if int(ok.item()) == 0:
+                import torch.distributed._symmetric_memory as _sm  # (private API: allocation + handle exchange only)
+                with torch.cuda.device(flat.device):
+                    _probe = _sm.empty(256, dtype=torch.float32, device=flat.device)  # local allocation, no collective
+                del _probe
+                can = 1
+            except Exception as e:  # torch built without symmetric memory
+                err, can = e, 0
+            vote = torch.tensor([can], device=flat.device)
+            dist.all_reduce(vote, op=dist.ReduceOp.MIN, group=group)
+            if int(vote.item()) == 1:
+                try:
+                    self.reducer = PeerGradExchange(model, group, average)
+                except Exception as e:  # no symmetric memory on this box / fabric
+                    err = e
+                ok = torch.tensor([0 if self.reducer is None else 1], device=flat.device)
+                dist.all_reduce(ok, op=dist.ReduceOp.MIN, group=group)  # all ranks take the same path
+                can = int(ok.item())
+            else:
+                can = 0
+            if can == 0:
                 if exchange == "peer":
                     raise RuntimeError(f"peer gradient exchange unavailable: {err!r}")
                 if self.reducer is not None:

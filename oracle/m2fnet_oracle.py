@@ -24,8 +24,8 @@ the oracle is pinned against outputs of the reference module itself, imported in
 build container by `oracle/gen_golden.py` and committed under `tests/golden/`
 (`tests/test_oracle_golden.py` checks every case, fp64, logits + loss + all gradients).
 
-Gradients come from autograd over this restatement; the explicit backward formulas the
-CUDA kernels implement are restated in `oracle/ops_backward.py` and checked against it.
+Gradients come from autograd over this restatement (fp64); the CUDA kernels' explicit
+backward formulas are checked against it op by op in tests/test_gpu_ops.py.
 
 Dropout: the reference draws 63 Bernoulli masks per forward from torch's global RNG
 (SURVEY.md G9), which no other implementation can reproduce bit-for-bit.  The oracle

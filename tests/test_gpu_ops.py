@@ -171,8 +171,12 @@ def _ln_ref(x, g, b):
     return (x - mu) / torch.sqrt(var + 1e-5) * g + b
 
 
-@pytest.mark.parametrize("M,D", [(2112, 768), (264, 1024), (77, 300), (5, 64)])
-def test_layernorm_forward_backward(ops, M, D):
+@pytest.mark.parametrize("staged", ["0", "2"])
+@pytest.mark.parametrize("M,D", [(2112, 768), (264, 1024), (77, 300), (5, 64), (4099, 768)])
+def test_layernorm_forward_backward(ops, M, D, staged, monkeypatch):
+    """Both kernel families (M2F_LN_V2 is read per call): 0 = register-resident rows, 2 = rows staged through shared memory with
+    bulk asynchronous copies (what the size rule picks once an [M, D] fp32 operand reaches 32 MB)."""
+    monkeypatch.setenv("M2F_LN_V2", staged)
     x, skip = rnd(M, D, seed=30) * 2 + 0.3, rnd(M, D, seed=31)
     gamma, beta = 1 + 0.1 * rnd(D, seed=32), 0.1 * rnd(D, seed=33)
     p = 0.4

@@ -89,7 +89,7 @@ def test_strict_checkpoint_interchange_with_reference(pkg):
     ours = pkg.M2FNet(cfg)
     assert not ours.load_state_dict(r.state_dict(), strict=True).missing_keys
     assert not r.load_state_dict(ours.state_dict(), strict=True).missing_keys
-    assert [n for n, _ in r.named_parameters()].sort() == [n for n, _ in ours.named_parameters()].sort()
+    assert sorted(n for n, _ in r.named_parameters()) == sorted(n for n, _ in ours.named_parameters())
 
 
 def test_state_dict_keys_survive_a_forward_setup(pkg):

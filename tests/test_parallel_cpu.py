@@ -96,3 +96,54 @@ def test_synthetic_loader_layout_matches_collate_fn(pkg):
     assert (b["emotion"][b["padding_mask"]] == -1).all() and (b["emotion"][~b["padding_mask"]] >= 0).all()
     assert (b["text"][b["padding_mask"]] == 0).all() and (~b["padding_mask"]).any(dim=1).all()
 
+
+
+def test_every_rank_runs_the_same_number_of_steps(pkg):
+    """A rank with one batch more than its peers would wait in the (collective) gradient exchange for ever: the sharded
+    loaders give every rank the same step count whatever the dialogue count (uneven shards)."""
+    import numpy as np
+    D = __import__("importlib").import_module(PKG_NAME + ".data")
+    for n, bs, world in ((97, 32, 3), (21, 8, 2), (100000, 64, 8), (7, 2, 4)):
+        lens = [len(D.SyntheticMELD(n_dialogues=n, batch_size=bs, S=5, Dt=8, Da=8, rank=r, world=world)) for r in range(world)]
+        assert len(set(lens)) == 1, (n, bs, world, lens)
+    rng = np.random.default_rng(0)
+    lengths = rng.integers(1, 34, size=1037)
+    for world in (2, 3, 8):
+        per_rank = [list(D.LengthBucketSampler(lengths, 16, seed=3, rank=r, world=world)) for r in range(world)]
+        assert len({len(b) for b in per_rank}) == 1
+        seen = np.concatenate([c for b in per_rank for c, _ in b])
+        assert len(seen) == len(set(seen.tolist()))  # no dialogue served twice
+        assert len(seen) >= 1037 - 16 * (world - 1) - 16 * 4  # only tail batches were dropped
+
+
+def _uneven_worker(rank, world, port, out):
+    """Drives the sharded sampler + reducer the way a data-parallel epoch does, with a dialogue count that does not divide."""
+    import importlib
+    import sys
+    import numpy as np
+    sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+    pkg = importlib.import_module(PKG_NAME)
+    D = importlib.import_module(PKG_NAME + ".data")
+    os.environ["MASTER_ADDR"], os.environ["MASTER_PORT"] = "127.0.0.1", str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    lengths = np.random.default_rng(1).integers(1, 34, size=203)
+    sampler = D.LengthBucketSampler(lengths, 8, seed=5, rank=rank, world=world)
+    flat = torch.zeros(64)
+    red = pkg.GradBucketReducer(lambda: flat, average=False)
+    steps = 0
+    for idx, S in sampler:  # one collective per step: hangs (and the test times out) if the ranks disagree on the count
+        flat.fill_(float(len(idx)))
+        red.begin_step()
+        red.on_bucket(0, 64)
+        red.finish()
+        steps += 1
+    if rank == 0:
+        torch.save({"steps": steps}, out)
+    dist.destroy_process_group()
+
+
+@pytest.mark.timeout(120)
+def test_uneven_dialogue_count_world2_gloo(tmp_path):
+    out = str(tmp_path / "u.pt")
+    mp.spawn(_uneven_worker, args=(2, 29617, out), nprocs=2, join=True)
+    assert torch.load(out)["steps"] > 0
