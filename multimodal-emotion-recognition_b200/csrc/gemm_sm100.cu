@@ -242,7 +242,7 @@ __device__ __forceinline__ float4 lds128u(uint32_t addr) { return lds128(addr); 
 // rows, fp32) or j ^ ((t >> 1) & 3) (64-byte rows, bf16).
 // FEAT: the epilogue's feature set as a compile-time mask for the combinations the training step launches most (the
 // feature tests then fold away: ~180 instead of ~330 instructions per 32x32 chunk), or -1 = decide everything at run time.
-enum : int { F_BIAS = 1, F_GATE = 2, F_DROP = 4, F_RES = 8, F_ACC = 16, F_OF32 = 32, F_OPL = 64, F_COLSUM = 128, F_RELU = 256, F_P1 = 512 };
+enum : int { F_BIAS = 1, F_GATE = 2, F_DROP = 4, F_RES = 8, F_ACC = 16, F_OF32 = 32, F_OPL = 64, F_COLSUM = 128, F_RELU = 256, F_P1 = 512, F_P2 = 1024 };
 #define M2F_FEAT(bit, runtime) (FEAT < 0 ? (runtime) : ((FEAT & (bit)) != 0))
 
 template <int BLOCK_N, int EPI_WARPS, int FEAT>
@@ -255,9 +255,13 @@ __device__ __forceinline__ void epilogue_tma(const GemmParams& p, const EpiMaps&
     const bool f_bias = M2F_FEAT(F_BIAS, p.bias != nullptr), f_relu = M2F_FEAT(F_RELU, p.relu != 0);
     const bool f_of32 = M2F_FEAT(F_OF32, p.out_f32 != nullptr), f_opl = M2F_FEAT(F_OPL, p.out_pl != nullptr);
     const bool f_colsum = M2F_FEAT(F_COLSUM, p.colsum != nullptr), f_drop = M2F_FEAT(F_DROP, p.drop.enabled != 0);
-    const int n_pl = f_opl ? ((FEAT >= 0 && (FEAT & F_P1)) ? 1 : p.out_pl_n) : 0;
-    const bool dbl = n_pl <= 1;
-    const uint32_t s_pl0 = s_base + (dbl ? 8192u : 4096u);
+    // P2: exactly two output planes and nothing else staged (the forward GEMMs of the 2-plane-forward precision modes): the
+    // two plane tiles of a chunk are double-buffered in the region the fp32 tiles would take (2 x (2 x 2 KB))
+    constexpr bool P2 = FEAT >= 0 && (FEAT & F_P2) != 0;
+    static_assert(!P2 || (FEAT & (F_OF32 | F_COLSUM | F_P1)) == 0, "F_P2 is for planes-only outputs");
+    const int n_pl = f_opl ? ((FEAT >= 0 && (FEAT & F_P1)) ? 1 : (P2 ? 2 : p.out_pl_n)) : 0;
+    const bool dbl = n_pl <= 1 || P2;
+    const uint32_t s_pl0 = P2 ? s_base : s_base + (dbl ? 8192u : 4096u);
     const uint32_t s_gate = s_base + (dbl ? 12288u : 10240u), s_res = s_gate + 2048u, s_acc = s_res + 4096u;
     uint64_t* bar = &epi_bar[ew];
     const int m0 = m_blk * BLOCK_M + lg * 32;
@@ -360,7 +364,7 @@ __device__ __forceinline__ void epilogue_tma(const GemmParams& p, const EpiMaps&
         }
         __syncwarp();                                   // every lane has consumed the input tiles
         if (c + CSTEP < BLOCK_N / 32) issue_loads(c + CSTEP);
-        const uint32_t s_of = s_base + buf * 4096u, s_pl = s_pl0 + buf * 2048u;
+        const uint32_t s_of = s_base + buf * 4096u, s_pl = s_pl0 + buf * (P2 ? 4096u : 2048u);
         if (lane == 0) {  // the stores that last used this staging set have read it
             if (dbl) ptx::bulk_wait_read1();
             else ptx::bulk_wait_read0();
@@ -600,7 +604,8 @@ gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ C
         const uint32_t s_bias = (ptx::smem_u32(epi_bar + 8) + 15u) & ~15u;
         const int feat = (p.bias ? F_BIAS : 0) | (p.gate ? F_GATE : 0) | (p.drop.enabled ? F_DROP : 0) | (p.resid ? F_RES : 0) |
                          ((p.accumulate && p.out_f32) ? F_ACC : 0) | (p.out_f32 ? F_OF32 : 0) | (p.out_pl ? F_OPL : 0) |
-                         (p.colsum ? F_COLSUM : 0) | (p.relu ? F_RELU : 0) | ((p.out_pl && p.out_pl_n == 1) ? F_P1 : 0);
+                         (p.colsum ? F_COLSUM : 0) | (p.relu ? F_RELU : 0) | ((p.out_pl && p.out_pl_n == 1) ? F_P1 : 0) |
+                         ((p.out_pl && p.out_pl_n == 2 && !p.out_f32 && !p.colsum) ? F_P2 : 0);
 #define M2F_EPI_CASE(MASK)                                                                                                            \
     case (MASK):                                                                                                                      \
         epilogue_tma<BLOCK_N, Cfg::EPI_WARPS, (MASK)>(p, em, smem, s_bias, epi_bar, tmem_full_bar, tmem_base, warp, lane, m_blk, n_blk); \
@@ -615,6 +620,9 @@ gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ C
             M2F_EPI_CASE(F_OPL | F_P1)                                       // d(attention output)
             M2F_EPI_CASE(F_BIAS | F_RELU | F_OPL | F_P1)                     // fusion out-projection; FFN1 without dropout (eval)
             M2F_EPI_CASE(F_BIAS | F_RES | F_OF32)                            // out-projection / FFN2 without dropout (eval)
+            M2F_EPI_CASE(F_BIAS | F_OPL | F_P2)                              // 2-plane forward: QKV / K / QV projections
+            M2F_EPI_CASE(F_BIAS | F_RELU | F_DROP | F_OPL | F_P2)            // 2-plane forward: FFN1, fusion linear, classifier hidden
+            M2F_EPI_CASE(F_BIAS | F_RELU | F_OPL | F_P2)                     // 2-plane forward: fusion out-projection
             default:
                 epilogue_tma<BLOCK_N, Cfg::EPI_WARPS, -1>(p, em, smem, s_bias, epi_bar, tmem_full_bar, tmem_base, warp, lane, m_blk, n_blk);
         }

@@ -606,6 +606,7 @@ struct Ctx {
     int P;             // planes of the forward's operands (weights shadow, saved activations)
     cudaStream_t cur = nullptr;  // stream the next kernels are enqueued on
 
+    bool narrow = false;         // prefer half-width GEMM tiles when a launch would fill less than half of the SMs (M2F_NARROW=1)
     cudaStream_t stream() const { return cur ? cur : st; }
     // work enqueued on `to` after this call waits for everything enqueued on `from` so far
     bool forked[3] = {false, false, false};  // side streams that carry work of this call (only those are joined back)
@@ -767,7 +768,12 @@ struct Ctx {
         }
         int64_t ktot = 0;
         for (int i = 0; i < nsegs; ++i) ktot += segs[i].klen;
-        const int bn = gemm_block_n(M, N, ktot);
+        int bn = gemm_block_n(M, N, ktot);
+        // Serial sections (fusion layers, classifier: nothing else runs beside the chain): a 768-wide GEMM at M = 2112 is
+        // 9 x 3 pair tiles = 54 CTAs, a third of the SMs.  Half-width tiles double the CTAs and halve each CTA's main loop.
+        if (narrow && (bn & GEMM_TILE_CTA2) && (bn & 0xfff) == 256 && N > 128 &&
+            ((M + 2 * BLOCK_M - 1) / (2 * BLOCK_M)) * 2 * ((N + 255) / 256) <= 74)
+            bn = 128 | GEMM_TILE_CTA2;
         EpiKey ek;
         std::memset(&ek, 0, sizeof(ek));  // padding bytes take part in the comparison
         ek.out_f32 = gp.out_f32; ek.out_pl = gp.out_pl; ek.gate = gp.gate; ek.resid = gp.resid;
@@ -871,6 +877,11 @@ static int forward_modality(Ctx& c, Modality& mo, const float* input, const uint
 
 enum { PH_HEAD = 1, PH_BODY = 2, PH_TAIL = 4, PH_ALL = 7 };
 
+static bool narrow_enabled() {
+    static const bool on = [] { const char* e = std::getenv("M2F_NARROW"); return e && e[0] == '1'; }();
+    return on;
+}
+
 // PH_BODY: everything up to the classifier's last hidden layer (capturable: touches only plan-owned memory when text /
 // audio point at the staging copies); PH_TAIL: the logits GEMM (writes the caller's buffer).
 static int forward_all(Ctx& c, const float* text, const float* audio, const uint8_t* key_pad, float* logits, int phases) {
@@ -899,6 +910,7 @@ static int forward_all(Ctx& c, const float* text, const float* audio, const uint
         M2F_TRY(forward_modality(c, p->mod[1], text, key_pad, dst));
     }
     if (body && fork) M2F_TRY(c.dep(c.side(0), c.st));
+    c.narrow = narrow_enabled();
     if (body && fam) {
         const int F = (int)p->fam.size();
         m2f_planes_t a = Ctx::cols(zc, 0, Df);
@@ -952,7 +964,10 @@ static int lin_wgrad(Ctx& c, cudaStream_t wst, const m2f_planes_t& dY, const m2f
     cudaStream_t chain = c.stream();
     M2F_TRY(c.dep(chain, wst));
     c.cur = wst;
+    const bool narrow = c.narrow;
+    c.narrow = false;  // weight gradients run beside the chain: full-width tiles
     int rc = c.gemm(dY, true, X, true, out, in, Epi().f32(dW, dW_ld));
+    c.narrow = narrow;
     if (rc == M2F_OK && db) rc = m2f_colsum_planes(&dY, db, wst);
     c.stamp("wgrad");
     c.cur = chain == c.st ? nullptr : chain;
@@ -1067,6 +1082,7 @@ static int backward_all(Ctx& c, const uint8_t* key_pad, const float* dlogits, in
     dproj[1] = c.pvb(p->dprojt_pl);
     m2f_planes_t dz = c.pvb(p->dz[0]);
     cudaStream_t ws1 = c.side(1);  // weight gradients of the classifier, the fusion layers and the text stack
+    c.narrow = narrow_enabled();
     for (int j = n_lin - 1; j >= 0; --j) {
         Lin& L = md->cls[j];
         m2f_planes_t in = (j == 0) ? zc : c.pvb(p->cls_h[j - 1]);
@@ -1163,6 +1179,7 @@ static int backward_all(Ctx& c, const uint8_t* key_pad, const float* dlogits, in
     // projection dropout mask applies -- handled above by not gating the [dq | dv] GEMM at f == 0.
     // text first, audio last: gradients then complete in exactly the reverse of the arena order
     // The two stacks are independent from here on: text continues on the caller's stream, audio runs beside it.
+    c.narrow = false;  // the two stacks run side by side from here on
     const bool interleave = (c.cb || c.marks || c.xchg) && p->mod[0].enabled && p->mod[1].enabled;
     if (interleave) {
         M2F_TRY(c.done_down_to(fam ? p->fam[0].inw_off : md->cls[0].w_off, true));  // everything above the stacks

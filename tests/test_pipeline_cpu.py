@@ -61,8 +61,11 @@ def test_length_buckets_cover_every_dialogue_once(D):
             assert lengths[idx].max() <= S and len(idx) <= 16
             assert S == 8 or lengths[idx].min() > {16: 8, 24: 16, 33: 24}[S]  # smallest bucket that fits
             seen.extend(idx.tolist())
-    assert sorted(seen) == list(range(1000))
+    # every rank gets the same number of batches (the gradient exchange is collective), so up to world - 1 batches of the
+    # epoch's order are dropped; nothing is served twice
+    assert len(seen) == len(set(seen)) and len(seen) >= 1000 - 16 * (world - 1)
     s = D.LengthBucketSampler(lengths, 16, buckets=(8, 16, 24, 33), seed=5)
+    assert sorted(i for idx, _ in s for i in idx.tolist()) == list(range(1000))  # one rank: every dialogue exactly once
     one_bucket = D.LengthBucketSampler(lengths, 16, buckets=(33,), seed=5)
     assert s.padded_fraction() < 0.35 < one_bucket.padded_fraction()  # MELD-like lengths: most of a 33-wide batch is padding
     with pytest.raises(ValueError, match="exceeds the last bucket"):
