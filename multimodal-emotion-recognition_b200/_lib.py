@@ -10,7 +10,8 @@ import os
 import threading
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "libm2f_b200.so")
+# M2F_LIB_PATH: load another build of the same library (A/B of build-time variants, tools/gpu_r2_ab.sh); default: the in-tree .so
+LIB_PATH = os.environ.get("M2F_LIB_PATH") or os.path.join(HERE, "libm2f_b200.so")
 
 M2F_OK = 0
 M2F_ERR_ARG, M2F_ERR_UNSUPPORTED, M2F_ERR_CUDA, M2F_ERR_ALIGN = -1, -2, -3, -4

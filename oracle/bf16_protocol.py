@@ -41,7 +41,7 @@ def planes_round(x: torch.Tensor, n: int) -> torch.Tensor:
 
 
 class Mode:
-    def __init__(self, x=1, w=1, g=1, attn=None, gx=None, gw=None, per=None, name=""):
+    def __init__(self, x=1, w=1, g=1, attn=None, gx=None, gw=None, per=None, name="", noise=0.0, noise_seed=0):
         """x / w / g: planes of activations / weights / gradients as GEMM operands; attn: planes inside the attention core
         (default: x forward, g backward); gx / gw: planes of the activations / weights as operands of the two backward
         products (default x / w); per: {GEMM class: (x, w)} overrides for the forward products of that class
@@ -51,6 +51,11 @@ class Mode:
         self.gx = x if gx is None else gx
         self.gw = w if gw is None else gw
         self.per = per or {}
+        # additive noise of relative size `noise` (x the rms of the output) on every Linear's forward output: a model of a
+        # correct implementation whose forward carries that much rounding error (fp32 accumulation over K terms); used to
+        # measure how sensitive the GRADIENTS of this ReLU network are to forward error (gate flips)
+        self.noise = float(noise)
+        self.gen = torch.Generator().manual_seed(noise_seed) if noise else None
         self.name = name or f"x{x}w{w}g{g}"
 
 
@@ -64,7 +69,10 @@ def make_ops(mode: Mode):
             sx = min(px, mode.gx) if (px and mode.gx) else (px or mode.gx)
             sw = min(pw, mode.gw) if (pw and mode.gw) else (pw or mode.gw)
             ctx.save_for_backward(planes_round(x, sx), planes_round(w, sw))
-            return xr @ wr.T
+            y = xr @ wr.T
+            if mode.noise:
+                y = y + mode.noise * y.pow(2).mean().sqrt() * torch.randn(y.shape, generator=mode.gen, dtype=y.dtype)
+            return y
 
         @staticmethod
         def backward(ctx, g):

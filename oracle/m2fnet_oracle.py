@@ -255,11 +255,21 @@ def mha(q_in, k_in, v_in, W, b, Wo, bo, H, keymask, site=None, drop_masks=None, 
 
 
 def forward(params: Dict[str, torch.Tensor], cfg, text, audio, mask,
-            drop_masks=None, p: float = 0.0) -> torch.Tensor:
+            drop_masks=None, p: float = 0.0, relu_taps: Optional[dict] = None) -> torch.Tensor:
     """M2FNet.forward restated (model.py:102-145).  text [B,S,Dt], audio [B,S,Da],
-    mask [B,S] bool (True = padding).  `p = 0` or `drop_masks is None` => eval()."""
+    mask [B,S] bool (True = padding).  `p = 0` or `drop_masks is None` => eval().
+    `relu_taps` (a dict) receives, per ReLU site, the smallest |pre-activation| over the valid rows relative to the
+    site's rms: how close the nearest ReLU gate is to flipping (SURVEY.md G15 -- a gate within the forward's rounding
+    error of zero makes the gradients of two correct implementations differ by O(1 / sqrt(rows x width)))."""
     g = lambda n: params[canonical_name(n)]
     dm = drop_masks
+
+    def relu(z, site_name):
+        if relu_taps is not None:
+            zv = z.detach()[~mask]
+            nz = zv.abs()[zv != 0]  # exact zeros were produced by an earlier ReLU (the text half of a fusion concat): no gate to flip
+            relu_taps[site_name] = float(nz.min() / zv.pow(2).mean().sqrt())
+        return torch.relu(z)
 
     def modality(x, mod, mc):
         m = MOD_NAME[mod]
@@ -272,7 +282,7 @@ def forward(params: Dict[str, torch.Tensor], cfg, text, audio, mask,
                          mc.n_head, mask, site_enc(mod, t, l, 0), dm, p)
                 y = layer_norm(y + _drop(sa, site_enc(mod, t, l, 1), dm, p),
                                g(P + "norm1.weight"), g(P + "norm1.bias"))
-                h = torch.relu(y @ g(P + "linear1.weight").T + g(P + "linear1.bias"))
+                h = relu(y @ g(P + "linear1.weight").T + g(P + "linear1.bias"), P + "linear1")
                 h = _drop(h, site_enc(mod, t, l, 2), dm, p)
                 f = h @ g(P + "linear2.weight").T + g(P + "linear2.bias")
                 y = layer_norm(y + _drop(f, site_enc(mod, t, l, 3), dm, p),
@@ -294,8 +304,8 @@ def forward(params: Dict[str, torch.Tensor], cfg, text, audio, mask,
                     g(P + "multihead_attention.out_proj.weight"),
                     g(P + "multihead_attention.out_proj.bias"),
                     cfg.FAM.n_head, mask, site_fam(i, 0), dm, p)
-            u = torch.relu(torch.cat((x, t_), dim=2))
-            t_ = torch.relu(u @ g(P + "linear.weight").T + g(P + "linear.bias"))
+            u = relu(torch.cat((x, t_), dim=2), P + "cat")
+            t_ = relu(u @ g(P + "linear.weight").T + g(P + "linear.bias"), P + "linear")
             t_ = _drop(t_, site_fam(i, 1), dm, p)
         z = torch.cat((a, t_), dim=2)
     elif cfg.AUDIO.enabled and cfg.TEXT.enabled:
@@ -307,7 +317,7 @@ def forward(params: Dict[str, torch.Tensor], cfg, text, audio, mask,
     for j, k in enumerate(idx):
         z = z @ g(f"output_layer.{k}.weight").T + g(f"output_layer.{k}.bias")
         if j < len(idx) - 1:
-            z = torch.relu(z)
+            z = relu(z, f"output_layer.{k}")
             if j == len(idx) - 2:
                 z = _drop(z, SITE_CLS, dm, p)
     return z

@@ -13,11 +13,11 @@ pkg = importlib.import_module("multimodal-emotion-recognition_b200")
 D = importlib.import_module("multimodal-emotion-recognition_b200.data")
 
 steps = int(sys.argv[1]) if len(sys.argv) > 1 else 3
-planes = 3 if (len(sys.argv) > 2 and sys.argv[2] == "fp32") else 1
+precision = sys.argv[2] if len(sys.argv) > 2 else "bf16x2f"
 B = int(sys.argv[3]) if len(sys.argv) > 3 else 64
 S = int(sys.argv[4]) if len(sys.argv) > 4 else 33
 torch.manual_seed(0)
-model = pkg.M2FNet(D.default_model_config(), planes=planes).to("cuda").train()
+model = pkg.M2FNet(D.default_model_config(), precision=precision).to("cuda").train()
 crit = pkg.FusedCrossEntropyLoss().cuda()
 opt = pkg.FusedAdam(model, lr=5e-5, weight_decay=0.01)
 b = {k: v.cuda() for k, v in D.synth_batch(B, S, 768, 768).items()}
