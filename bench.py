@@ -59,8 +59,6 @@ def parse():
     ap.add_argument("--no-context", action="store_true", help="skip the stock-PyTorch-eager-on-B200 context numbers")
     ap.add_argument("--no-rooflines", action="store_true")
     ap.add_argument("--c4-dialogues", type=int, default=100000)
-    ap.add_argument("--optimizer", default="in_backward", choices=["in_backward", "step"],
-                    help="FusedAdam applied inside the backward as gradient ranges become final (default) or by optimizer.step() afterwards")
     ap.add_argument("--bucket-mb", type=float, default=None, help="gradient bucket size (default: 16 for the peer exchange, 128 for NCCL)")
     ap.add_argument("--exchange", default=None, choices=["auto", "peer", "nccl"],
                     help="gradient exchange at N > 1: NVSwitch peer-memory kernel or NCCL buckets (default: $M2F_EXCHANGE or auto)")
@@ -73,8 +71,6 @@ def workload_config(args, world, dialogues=None):
                         f"{b} dialogues x {args.seq} utterances per GPU; train step = fwd + CE(ls 0.1) + bwd + Adam; dropout 0.4",
             "dialogues_per_gpu": b, "utterances_per_dialogue": args.seq, "global_dialogues": b * world,
             "parallelism": f"dp{world}", "precision_mode": args.precision, "precision_note": MODE_NOTE[args.precision],
-            "optimizer": "FusedAdam, update launched inside the backward per finished gradient range" if args.optimizer == "in_backward"
-                         else "FusedAdam.step() after the backward",
             "l2": "16 distinct device-resident batches (208 MB) cycled + >1.5 GB of weight/gradient/Adam traffic per step: "
                   "working set exceeds the 126 MB L2, no explicit flush"}
 
@@ -342,7 +338,7 @@ def main():
         model = pkg.M2FNet(cfg, precision=precision).to(dev).train()
         net = pkg.DataParallelM2FNet(model, bucket_mb=args.bucket_mb, exchange=args.exchange) if dp else model
         crit = pkg.FusedCrossEntropyLoss().to(dev)
-        opt = pkg.FusedAdam(model, lr=5e-5, weight_decay=0.01, in_backward=(args.optimizer == "in_backward"))
+        opt = pkg.FusedAdam(model, lr=5e-5, weight_decay=0.01)
 
         def step(b):
             opt.zero_grad(set_to_none=True)
@@ -515,8 +511,6 @@ def verify_exchange(torch, dist, net, model, crit, b):
     runs of the same backward differ in the last bits: tolerance 1e-5 relative L2 per range class)."""
     world = dist.get_world_size()
     saved_x, saved_hooks = model._exchange, (model._bucket_hook, model._bucket_floats, model._done_hook)
-    saved_opt = model._inbwd
-    model.set_inbackward_optimizer(None)  # the check runs two backwards on the same weights: no updates in between
 
     def fwd_bwd(wrapper):
         model.zero_grad(set_to_none=True)
@@ -539,8 +533,6 @@ def verify_exchange(torch, dist, net, model, crit, b):
         model.set_exchange(*saved_x)
     model.set_grad_hooks(*saved_hooks)
     g_x = fwd_bwd(net)
-    if saved_opt is not None:
-        model.set_inbackward_optimizer(saved_opt)
     off = model._off_1d
     num2 = (g_x[:off].double() - ref[:off].double()).norm().item()
     den2 = ref[:off].double().norm().item()

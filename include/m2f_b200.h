@@ -296,20 +296,6 @@ int m2f_model_adam_step(const m2f_model_t* m, float* params, const float* grads,
                         void* shadow, float lr, float beta1, float beta2, float eps, float weight_decay, int64_t t,
                         float grad_scale, void* stream);
 
-/* The optimizer inside the backward.  After m2f_plan_set_optimizer, m2f_plan_backward_bucketed(..., bucket_floats > 0, cb = NULL)
- * applies the Adam update (and the refresh of the bf16 weight shadow) to every gradient range as soon as it is final -- with an
- * exchange attached: as soon as it has been all-reduced -- on a low-priority stream beside the rest of the backward, captured in
- * its CUDA graph: optimizer.step() (src/train.py:231) then has nothing left to do but count.  Same arithmetic, bit for bit, as
- * m2f_model_adam_step after the backward.  The hyper-parameters live in device memory (M2F_ADAM_HYPER_FLOATS floats, 16-byte
- * aligned) so that a replayed graph sees the current step count / learning rate: call m2f_adam_hyper on the same stream before
- * each such backward (t = 1-based count of the update about to be applied).  exp_avg == NULL detaches.
- * Constraints: gradients are WRITTEN per backward (no accumulation across backwards); parameters and `shadow` change during the
- * backward call instead of during step(). */
-#define M2F_ADAM_HYPER_FLOATS 8
-int m2f_plan_set_optimizer(m2f_plan_t* p, float* exp_avg, float* exp_avg_sq, const float* hyper_dev);
-int m2f_adam_hyper(float* hyper_dev, float lr, float beta1, float beta2, float eps, float weight_decay, int64_t t,
-                   float grad_scale, void* stream);
-
 /* ---- either side of the step ---------------------------------------------------
  * Batch assembly on the device, replacing Dataset.__getitem__ + collate_fn + apply_padding
  * (src/dataset.py:32-65,71-89; src/utils.py:15-31).  The embedding tables stay resident in HBM: text_table

@@ -225,13 +225,13 @@ struct m2f_plan {
     // CUDA graphs: the body of the forward / backward is captured once (on `cap`, with its forks onto aux[]) and replayed
     // into the caller's stream; whatever depends on per-call pointers (inputs, logits, dlogits) stays outside.
     struct GraphKey {
-        const void *params = nullptr, *shadow = nullptr, *ws = nullptr, *grads = nullptr, *opt_m = nullptr;
+        const void *params = nullptr, *shadow = nullptr, *ws = nullptr, *grads = nullptr;
         float p_used = -1.f;
         int flags = 0;
         int64_t bucket_floats = 0;
         bool operator==(const GraphKey& o) const {
-            return params == o.params && shadow == o.shadow && ws == o.ws && grads == o.grads && opt_m == o.opt_m && p_used == o.p_used &&
-                   flags == o.flags && bucket_floats == o.bucket_floats;
+            return params == o.params && shadow == o.shadow && ws == o.ws && grads == o.grads && p_used == o.p_used && flags == o.flags &&
+                   bucket_floats == o.bucket_floats;
         }
     };
     struct GraphSlot {
@@ -253,12 +253,6 @@ struct m2f_plan {
     float xchg_scale = 1.f;
     int xchg_ctas = 0;
     int64_t xchg_ranges = 0;                 // ranges exchanged by the last backward
-    // optimizer inside the backward (m2f_plan_set_optimizer): every finished (and, data parallel, exchanged) gradient range is
-    // applied by Adam kernels on a low-priority stream while the rest of the backward runs
-    bool opt_on = false;
-    float *opt_m = nullptr, *opt_v = nullptr;
-    const float* opt_hp = nullptr;           // device: AdamArgs, rewritten by m2f_adam_hyper before each backward
-    cudaStream_t adam_st = nullptr;
     cudaStream_t cap = nullptr;
     unsigned long long* rng_dev = nullptr;   // {seed, step} read by the dropout kernels of the captured graphs
     int use_graph = 1;
@@ -279,7 +273,6 @@ struct m2f_plan {
             M2F_CUDA(cudaStreamCreateWithPriority(&aux[2], cudaStreamNonBlocking, lo_prio));
             M2F_CUDA(cudaStreamCreateWithPriority(&ready, cudaStreamNonBlocking, hi_prio));
             M2F_CUDA(cudaStreamCreateWithPriority(&cap, cudaStreamNonBlocking, chain_prio));
-            M2F_CUDA(cudaStreamCreateWithPriority(&adam_st, cudaStreamNonBlocking, lo_prio));
         }
         M2F_CUDA(cudaMalloc(&rng_dev, 2 * sizeof(unsigned long long)));
         evs.resize(128);
@@ -306,7 +299,6 @@ struct m2f_plan {
         if (rng_dev) { cudaFree(rng_dev); rng_dev = nullptr; }
         if (tl_dev) { cudaFree(tl_dev); tl_dev = nullptr; }
         if (cap) { cudaStreamDestroy(cap); cap = nullptr; }
-        if (adam_st) { cudaStreamDestroy(adam_st); adam_st = nullptr; }
         if (ready) { cudaStreamDestroy(ready); ready = nullptr; }
         for (int i = 0; i < 3; ++i)
             if (aux[i]) { cudaStreamDestroy(aux[i]); aux[i] = nullptr; }
@@ -557,12 +549,9 @@ __device__ __forceinline__ float adam_one(float& p, float g, float& m, float& v,
     p -= a.step_size * (m / denom);
     return p;
 }
-// `hp` (nullable): the hyper-parameters in device memory instead of the by-value copy -- what lets the update be captured into
-// the backward's CUDA graph and replayed with a new step count / learning rate (m2f_adam_hyper writes them before each launch).
 __global__ void __launch_bounds__(256)
 adam_shadow_kernel(float* __restrict__ params, const float* __restrict__ grads, float* __restrict__ em, float* __restrict__ ev,
-                   uint8_t* __restrict__ shadow, const ShadowBatch batch, const AdamArgs a_val, const AdamArgs* __restrict__ hp) {
-    const AdamArgs a = hp ? *hp : a_val;
+                   uint8_t* __restrict__ shadow, const ShadowBatch batch, const AdamArgs a) {
     const SEntry& e = batch.e[blockIdx.y];
     __nv_bfloat16* dst = reinterpret_cast<__nv_bfloat16*>(shadow + e.dst_off);
     if ((e.cols & 3) == 0 && (e.src_ld & 3) == 0 && (e.src_off & 3) == 0) {
@@ -598,22 +587,6 @@ adam_shadow_kernel(float* __restrict__ params, const float* __restrict__ grads, 
         }
     }
 }
-
-// the 1-D region (biases, LayerNorm vectors) with device-resident hyper-parameters: same arithmetic as adam_kernel (optim.cu)
-__global__ void __launch_bounds__(256)
-adam_range_kernel(float4* __restrict__ p, const float4* __restrict__ g, float4* __restrict__ m, float4* __restrict__ v, int64_t n4,
-                  const AdamArgs* __restrict__ hp) {
-    const AdamArgs a = *hp;
-    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n4; i += (int64_t)gridDim.x * blockDim.x) {
-        float4 pp = p[i], gg = g[i], mm = m[i], vv = v[i];
-        adam_one(pp.x, gg.x, mm.x, vv.x, a);
-        adam_one(pp.y, gg.y, mm.y, vv.y, a);
-        adam_one(pp.z, gg.z, mm.z, vv.z, a);
-        adam_one(pp.w, gg.w, mm.w, vv.w, a);
-        p[i] = pp; m[i] = mm; v[i] = vv;
-    }
-}
-__global__ void adam_hyper_kernel(AdamArgs* dst, const AdamArgs a) { *dst = a; }
 
 // ------------------------------------------------------------------------------------------ execution context
 __global__ void timeline_stamp_kernel(unsigned long long* slot) {
@@ -665,7 +638,7 @@ struct Ctx {
     // Every 2-D gradient at arena offsets >= w has been enqueued.  When a bucket is due, the plan's
     // ready stream is ordered after the weight-gradient streams and handed to the callback: the caller's collective waits on it alone.
     int done_down_to(int64_t w, bool flush = false) {
-        if (!cb && !marks && !xchg && !adam) return M2F_OK;
+        if (!cb && !marks && !xchg) return M2F_OK;
         if (collecting >= 0) {  // inside a modality stack: remember the range behind an event on the stack's weight-gradient stream
             if (hi - w >= bucket_floats || (flush && hi > w)) {
                 if (stack_ev_used == p->stack_evs.size()) {
@@ -682,9 +655,7 @@ struct Ctx {
         }
         if (hi - w >= bucket_floats || (flush && hi > w)) {
             cudaStream_t ready = p->use_streams ? p->ready : st;
-            // capture: pulls `ready` into the graph even when no side stream has run yet; optimizer in the backward: the chain's reads
-            // of the weights' shadow (data-gradient GEMMs enqueued so far) must precede the update of the range
-            if (marks || capturing || adam) M2F_TRY(dep(st, ready));
+            if (marks || capturing) M2F_TRY(dep(st, ready));  // capture: pulls `ready` into the graph even when no side stream has run yet
             M2F_TRY(dep(side(1), ready));  // the two weight-gradient streams
             M2F_TRY(dep(side(2), ready));
             M2F_TRY(report(w, hi, ready));
@@ -727,97 +698,21 @@ struct Ctx {
             M2F_TRY(m2f_grad_allreduce_peer(&p->xchg_group, lo, hi_, p->xchg_scale, p->xchg_ctas, last ? 0 : M2F_XCHG_NO_EXIT_BARRIER, ready));
             ++p->xchg_ranges;
             if (ready != st) ready_in_capture = true;
-        } else if (marks) {
-            while (p->bucket_evs.size() <= marks->size()) {
-                cudaEvent_t e;
-                M2F_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
-                p->bucket_evs.push_back(e);
-            }
-            M2F_CUDA(cudaEventRecordWithFlags(p->bucket_evs[marks->size()], ready, cudaEventRecordExternal));
-            marks->emplace_back(lo, hi_);
-            if (ready != st) ready_in_capture = true;
-        } else if (cb) {
+            return M2F_OK;
+        }
+        if (!marks) {
             cb(cb_user, lo, hi_, ready);
-        }
-        if (adam) {
-            pend.push_back({lo, hi_, xchg ? p->xchg_ranges : 0});
-            if (ready != st) ready_in_capture = true;
-            M2F_TRY(flush_adam(ready, last));
-        }
-        return M2F_OK;
-    }
-
-    // ---- optimizer inside the backward.  A reported range is updated (Adam + refresh of its bf16 shadow planes) on the plan's
-    // low-priority stream once (a) nothing still to be enqueued reads its weights: stack ranges are reported behind the layer's
-    // last data-gradient GEMM; the fusion / classifier ranges wait for `fusion_safe` (the batched K-projection data gradient after
-    // the fusion loop is the last reader of any fusion weight); and (b) data parallel: a LATER exchange call has been issued on
-    // `ready` -- its entry barrier proves that every rank has completed the call that reduced this range (stores included), so the
-    // range is final here without a closing handshake per call; the step's last call does close, and covers whatever is left.
-    bool adam = false;
-    bool fusion_safe = true;
-    int64_t fam_lo = 0;  // first arena offset of the fusion / classifier weights (ranges at or above it wait for fusion_safe)
-    struct PendAdam { int64_t lo, hi, xseq; };
-    std::vector<PendAdam> pend;
-    int flush_adam(cudaStream_t ready, bool last) {
-        m2f_model* md = p->m;
-        cudaStream_t ast = p->use_streams ? p->adam_st : st;
-        std::vector<PendAdam> keep;
-        bool ordered = false;
-        for (const PendAdam& r : pend) {
-            const bool one_d = r.lo >= md->off_1d;
-            const bool safe = one_d || r.lo < fam_lo || fusion_safe;
-            const bool final_ = !xchg || last || r.xseq < p->xchg_ranges;
-            if (!safe || !final_) { keep.push_back(r); continue; }
-            if (!ordered) { M2F_TRY(dep(ready, ast)); ordered = true; }
-            M2F_TRY(adam_range(r.lo, r.hi, ast));
-        }
-        pend.swap(keep);
-        return M2F_OK;
-    }
-    int adam_range(int64_t lo, int64_t hi_, cudaStream_t ast) {
-        m2f_model* md = p->m;
-        const AdamArgs* hp = reinterpret_cast<const AdamArgs*>(p->opt_hp);
-        float* prm_w = const_cast<float*>(params);
-        if (lo >= md->off_1d) {  // biases / LayerNorm vectors, then their packed fp32 copies in the shadow
-            const int64_t n4 = (hi_ - lo) / 4;
-            int64_t g = (n4 + 255) / 256;
-            if (g > 148 * 2) g = 148 * 2;
-            adam_range_kernel<<<(unsigned)g, 256, 0, ast>>>(reinterpret_cast<float4*>(prm_w + lo), reinterpret_cast<const float4*>(grads + lo),
-                                                           reinterpret_cast<float4*>(p->opt_m + lo), reinterpret_cast<float4*>(p->opt_v + lo), n4, hp);
-            M2F_LAUNCH_CHECK();
-            ShadowBatch b;
-            b.n = 0;
-            for (const SEntry& e : md->sentries) {
-                if (e.planes != 0) continue;
-                b.e[b.n++] = e;
-                if (b.n == SHADOW_CHUNK) {
-                    shadow_refresh_kernel<<<dim3(4, b.n), 256, 0, ast>>>(params, shadow, b);
-                    M2F_LAUNCH_CHECK();
-                    b.n = 0;
-                }
-            }
-            if (b.n) {
-                shadow_refresh_kernel<<<dim3(4, b.n), 256, 0, ast>>>(params, shadow, b);
-                M2F_LAUNCH_CHECK();
-            }
             return M2F_OK;
         }
-        ShadowBatch b;
-        b.n = 0;
-        AdamArgs unused{};
-        auto flush = [&]() -> int {
-            if (b.n == 0) return M2F_OK;
-            adam_shadow_kernel<<<dim3(48, b.n), 256, 0, ast>>>(prm_w, grads, p->opt_m, p->opt_v, shadow, b, unused, hp);
-            M2F_LAUNCH_CHECK();
-            b.n = 0;
-            return M2F_OK;
-        };
-        for (const SEntry& e : md->sentries) {
-            if (e.planes == 0 || e.src_off < lo || e.src_off >= hi_) continue;
-            b.e[b.n++] = e;
-            if (b.n == SHADOW_CHUNK) M2F_TRY(flush());
+        while (p->bucket_evs.size() <= marks->size()) {
+            cudaEvent_t e;
+            M2F_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+            p->bucket_evs.push_back(e);
         }
-        return flush();
+        M2F_CUDA(cudaEventRecordWithFlags(p->bucket_evs[marks->size()], ready, cudaEventRecordExternal));
+        marks->emplace_back(lo, hi_);
+        if (ready != st) ready_in_capture = true;
+        return M2F_OK;
     }
 
     m2f_planes_t pv(const Buf& b) const {
@@ -982,14 +877,10 @@ static int forward_modality(Ctx& c, Modality& mo, const float* input, const uint
 
 enum { PH_HEAD = 1, PH_BODY = 2, PH_TAIL = 4, PH_ALL = 7 };
 
-// M2F_NARROW: 0 = full-width tiles everywhere; 1 (default) = half-width tiles for the under-filled GEMMs of the serial sections
-// (fusion layers, classifier; measured 3.85 -> 3.74 ms per step at C2, profiles/r2_ab_tiles.txt); 2 = also inside the two
-// modality stacks; 3 = also for the weight gradients on the side streams (2 and 3: experiments).
-static int narrow_level() {
-    static const int lvl = [] { const char* e = std::getenv("M2F_NARROW"); return e ? std::atoi(e) : 1; }();
-    return lvl;
+static bool narrow_enabled() {
+    static const bool on = [] { const char* e = std::getenv("M2F_NARROW"); return e && e[0] == '1'; }();
+    return on;
 }
-static bool narrow_enabled() { return narrow_level() >= 1; }
 
 // PH_BODY: everything up to the classifier's last hidden layer (capturable: touches only plan-owned memory when text /
 // audio point at the staging copies); PH_TAIL: the logits GEMM (writes the caller's buffer).
@@ -1006,7 +897,6 @@ static int forward_all(Ctx& c, const float* text, const float* audio, const uint
     const bool fork = md->both && p->use_streams;
     const bool body = phases & PH_BODY;
     if (body) c.stamp("begin");
-    c.narrow = narrow_level() >= 2;
     if (body && p->mod[0].enabled) {
         if (fork) {
             M2F_TRY(c.dep(c.st, c.side(0)));
@@ -1075,7 +965,7 @@ static int lin_wgrad(Ctx& c, cudaStream_t wst, const m2f_planes_t& dY, const m2f
     M2F_TRY(c.dep(chain, wst));
     c.cur = wst;
     const bool narrow = c.narrow;
-    c.narrow = narrow_level() >= 3;  // weight gradients run beside the chain: full-width tiles
+    c.narrow = false;  // weight gradients run beside the chain: full-width tiles
     int rc = c.gemm(dY, true, X, true, out, in, Epi().f32(dW, dW_ld));
     c.narrow = narrow;
     if (rc == M2F_OK && db) rc = m2f_colsum_planes(&dY, db, wst);
@@ -1108,10 +998,8 @@ static int backward_modality(Ctx& c, Modality& mo, const uint8_t* key_pad, const
     // projection: dW, db, and g = dropmask0(dproj . Wp)
     m2f_planes_t xp = c.pvb(mo.xout_pl[mo.T - 1]);
     M2F_TRY(lin_wgrad(c, wst, dproj, xp, c.grd(mo.proj.w_off), mo.proj.in, nullptr, mo.proj.out, mo.proj.in));  // db: by dproj's producer
-    OP(c.gemm(dproj, false, c.pvb(mo.proj.w), true, M, D, Epi().drop(pd, seed, step, M2F_SITE_MOD(mo.idx, 0), D).f32(G, gld)));
-    // reported only now: with the optimizer inside the backward the update of a weight must follow the chain's last read of it
-    if (c.adam && wst != c.stream()) M2F_TRY(c.dep(c.stream(), wst));
     M2F_TRY(c.done_down_to(mo.proj.w_off));
+    OP(c.gemm(dproj, false, c.pvb(mo.proj.w), true, M, D, Epi().drop(pd, seed, step, M2F_SITE_MOD(mo.idx, 0), D).f32(G, gld)));
     int nlayer = 0;
     for (int t = mo.T - 1; t >= 0; --t) {
         const EncLayer& lastl = mo.layers[(size_t)t * mo.L + mo.L - 1];
@@ -1131,18 +1019,18 @@ static int backward_modality(Ctx& c, Modality& mo, const uint8_t* key_pad, const
                                M2F_SITE_ENC(mo.idx, t, l, 3), c.grd(e.g2), c.grd(e.be2), c.grd(e.w2.b_off), c.stream()));
             M2F_TRY(lin_wgrad(c, wst, dx2, h, c.grd(e.w2.w_off), e.w2.in, nullptr, e.w2.out, e.w2.in));
             // the layer computed last: hand its weights over one by one, so that only the final one is left behind the backward
-            if (first && fine_tail() && !c.adam) M2F_TRY(c.done_down_to(e.w2.w_off, true));
+            if (first && fine_tail()) M2F_TRY(c.done_down_to(e.w2.w_off, true));
             // dh = (d y2 . W2) * [h > 0] / (1-p)   (relu + dropout backward from the saved output)
             OP(c.gemm(dx2, false, c.pvb(e.w2.w), true, M, e.w2.in, Epi().gate(h, inv_keep(pd)).pl(dhp).colsum(c.grd(e.w1.b_off))));
             M2F_TRY(lin_wgrad(c, wst, dhp, x1p, c.grd(e.w1.w_off), e.w1.in, nullptr, e.w1.out, e.w1.in));
-            if (first && fine_tail() && !c.adam) M2F_TRY(c.done_down_to(e.w1.w_off, true));
+            if (first && fine_tail()) M2F_TRY(c.done_down_to(e.w1.w_off, true));
             // A = d x1 = dh . W1 + d y2
             OP(c.gemm(dhp, false, c.pvb(e.w1.w), true, M, D, Epi().resid(Bq, gld).f32(A, gld)));
             // LN1: A -> Bq = d y1, dx1 = dropmask1(d y1), dbo += colsum
             OP(m2f_ln_bwd(A, gld, c.f32(e.y1), e.y1.ld, c.prm(e.g1), c.f32(e.st1), M, D, Bq, gld, &dx1, pd, seed, step,
                                M2F_SITE_ENC(mo.idx, t, l, 1), c.grd(e.g1), c.grd(e.be1), c.grd(e.wo.b_off), c.stream()));
             M2F_TRY(lin_wgrad(c, wst, dx1, o, c.grd(e.wo.w_off), e.wo.in, nullptr, e.wo.out, e.wo.in));
-            if (first && fine_tail() && !c.adam) M2F_TRY(c.done_down_to(e.wo.w_off, true));
+            if (first && fine_tail()) M2F_TRY(c.done_down_to(e.wo.w_off, true));
             OP(c.gemm(dx1, false, c.pvb(e.wo.w), true, M, D, Epi().pl(dop)));
             m2f_planes_t q = Ctx::cols(qkv, 0, D), k = Ctx::cols(qkv, D, D), v = Ctx::cols(qkv, 2 * D, D);
             m2f_planes_t dq = Ctx::cols(dqkvp, 0, D), dk = Ctx::cols(dqkvp, D, D), dv = Ctx::cols(dqkvp, 2 * D, D);
@@ -1151,14 +1039,12 @@ static int backward_modality(Ctx& c, Modality& mo, const uint8_t* key_pad, const
                                  dbqkv, dbqkv + D, dbqkv + 2 * D, c.stream()));
             M2F_TRY(lin_wgrad(c, wst, dqkvp, in_pl, c.grd(e.qkv.w_off), e.qkv.in, nullptr, e.qkv.out, e.qkv.in));
             if (wst != c.stream()) M2F_CUDA(cudaEventRecord(p->wg_ev[mo.idx][par], wst));
+            M2F_TRY(c.done_down_to(e.qkv.w_off));
             if (!first) {
                 // gradient w.r.t. the layer input = dqkv . Wqkv + d y1 ; at l == 0 it also joins the skip gradient in G
                 if (l > 0) OP(c.gemm(dqkvp, false, c.pvb(e.qkv.w), true, M, D, Epi().resid(Bq, gld).f32(A, gld)));
                 else       OP(c.gemm(dqkvp, false, c.pvb(e.qkv.w), true, M, D, Epi().resid(Bq, gld).f32(G, gld, true)));
             }
-            // the layer's four weights are final and -- behind the GEMM above -- no longer read by this backward
-            if (c.adam && wst != c.stream()) M2F_TRY(c.dep(c.stream(), wst));
-            M2F_TRY(c.done_down_to(e.qkv.w_off));
         }
     }
     return M2F_OK;
@@ -1288,19 +1174,13 @@ static int backward_all(Ctx& c, const uint8_t* key_pad, const float* dlogits, in
         // audio: every layer's K projection + the classifier half, through the projection dropout mask
         OP(c.gemm(dkall, false, c.pvb(md->wk_all.w), true, M, Df,
                        Epi().drop(pd, seed, step, M2F_SITE_MOD(0, 1), Df).resid(c.f32(p->ga_f32), p->ga_f32.ld).pl(dproj[0]).colsum(c.grd(p->mod[0].proj.b_off))));
-        if (c.adam) {  // that was the last reader of any fusion / classifier weight: their pending updates may go
-            c.fusion_safe = true;
-            cudaStream_t ready = p->use_streams ? p->ready : c.st;
-            M2F_TRY(c.dep(c.st, ready));
-            M2F_TRY(c.flush_adam(ready, false));
-        }
     }
     // NOTE on the f == 0 text contribution through q/v: q and v read t0 itself (no cat-relu on that path), so only the
     // projection dropout mask applies -- handled above by not gating the [dq | dv] GEMM at f == 0.
     // text first, audio last: gradients then complete in exactly the reverse of the arena order
     // The two stacks are independent from here on: text continues on the caller's stream, audio runs beside it.
-    c.narrow = narrow_level() >= 2;  // the two stacks run side by side from here on
-    const bool interleave = (c.cb || c.marks || c.xchg || c.adam) && p->mod[0].enabled && p->mod[1].enabled;
+    c.narrow = false;  // the two stacks run side by side from here on
+    const bool interleave = (c.cb || c.marks || c.xchg) && p->mod[0].enabled && p->mod[1].enabled;
     if (interleave) {
         M2F_TRY(c.done_down_to(fam ? p->fam[0].inw_off : md->cls[0].w_off, true));  // everything above the stacks
         c.collect_begin(1, ws1);
@@ -1326,17 +1206,13 @@ static int backward_all(Ctx& c, const uint8_t* key_pad, const float* dlogits, in
     }
     M2F_TRY(c.done_down_to(0, true));
     for (int i = 0; i < 3; ++i) M2F_TRY(c.dep(c.side(i), c.st));
-    if (c.cb || c.marks || c.xchg || c.adam) {  // biases / LayerNorm parameters (atomically accumulated by every stream): final once everything has joined
+    if (c.cb || c.marks || c.xchg) {  // biases / LayerNorm parameters (atomically accumulated by every stream): final once everything has joined
         cudaStream_t ready = p->use_streams ? p->ready : c.st;
         M2F_TRY(c.dep(c.st, ready));
         M2F_TRY(c.report(md->off_1d, md->arena_floats, ready, true));
         // a capture must end with every forked stream joined; with the exchange inside the backward the caller's stream
         // continues (optimizer) only after the last range has been exchanged
-        if ((c.marks || c.xchg || c.adam) && c.ready_in_capture) M2F_TRY(c.dep(ready, c.st));
-        if (c.adam) {
-            M2F_REQUIRE(c.pend.empty(), M2F_ERR_CUDA, "plan_backward: %zu gradient ranges were never handed to the optimizer", c.pend.size());
-            if (p->use_streams) M2F_TRY(c.dep(p->adam_st, c.st));  // the next forward reads the updated weights
-        }
+        if ((c.marks || c.xchg) && c.ready_in_capture) M2F_TRY(c.dep(ready, c.st));
     }
     return M2F_OK;
 }
@@ -1406,7 +1282,7 @@ extern "C" int m2f_model_adam_step(const m2f_model_t* m, float* params, const fl
     b.n = 0;
     auto flush = [&]() -> int {
         if (b.n == 0) return M2F_OK;
-        adam_shadow_kernel<<<dim3(96, b.n), 256, 0, st>>>(params, grads, exp_avg, exp_avg_sq, reinterpret_cast<uint8_t*>(shadow), b, a, nullptr);
+        adam_shadow_kernel<<<dim3(96, b.n), 256, 0, st>>>(params, grads, exp_avg, exp_avg_sq, reinterpret_cast<uint8_t*>(shadow), b, a);
         M2F_LAUNCH_CHECK();
         b.n = 0;
         return M2F_OK;
@@ -1702,35 +1578,6 @@ extern "C" int m2f_plan_set_exchange(m2f_plan_t* p, const m2f_peer_group_t* grou
 
 extern "C" int64_t m2f_plan_exchange_ranges(const m2f_plan_t* p) { return p ? p->xchg_ranges : 0; }
 
-extern "C" int m2f_plan_set_optimizer(m2f_plan_t* p, float* exp_avg, float* exp_avg_sq, const float* hyper_dev) {
-    M2F_REQUIRE(p, M2F_ERR_ARG, "plan_set_optimizer: plan is NULL");
-    p->gb.reset();  // the captured backward embeds (or lacks) the update kernels
-    if (!exp_avg) {
-        p->opt_on = false;
-        return M2F_OK;
-    }
-    M2F_REQUIRE(exp_avg_sq && hyper_dev, M2F_ERR_ARG, "plan_set_optimizer: null argument");
-    M2F_REQUIRE(((reinterpret_cast<uintptr_t>(exp_avg) | reinterpret_cast<uintptr_t>(exp_avg_sq) | reinterpret_cast<uintptr_t>(hyper_dev)) % 16) == 0,
-                M2F_ERR_ALIGN, "plan_set_optimizer: state and hyper-parameter buffers must be 16-byte aligned");
-    M2F_REQUIRE(p->training, M2F_ERR_ARG, "plan_set_optimizer: needs a training plan");
-    p->opt_m = exp_avg;
-    p->opt_v = exp_avg_sq;
-    p->opt_hp = hyper_dev;
-    p->opt_on = true;
-    return M2F_OK;
-}
-
-extern "C" int m2f_adam_hyper(float* hyper_dev, float lr, float beta1, float beta2, float eps, float weight_decay, int64_t t,
-                              float grad_scale, void* stream) {
-    M2F_REQUIRE(hyper_dev && t >= 1, M2F_ERR_ARG, "adam_hyper: bad argument");
-    static_assert(sizeof(AdamArgs) <= M2F_ADAM_HYPER_FLOATS * sizeof(float), "hyper-parameter block too small");
-    const double bc1 = 1.0 - pow((double)beta1, (double)t), bc2 = 1.0 - pow((double)beta2, (double)t);
-    const AdamArgs a{beta1, beta2, eps, weight_decay, (float)((double)lr / bc1), (float)(1.0 / sqrt(bc2)), grad_scale};
-    adam_hyper_kernel<<<1, 1, 0, reinterpret_cast<cudaStream_t>(stream)>>>(reinterpret_cast<AdamArgs*>(hyper_dev), a);
-    M2F_LAUNCH_CHECK();
-    return M2F_OK;
-}
-
 extern "C" int m2f_plan_backward_bucketed(m2f_plan_t* p, const float* params, const void* shadow, void* workspace,
                                           const float* dlogits, float* grads, int64_t bucket_floats, m2f_bucket_cb cb, void* user,
                                           void* stream) {
@@ -1747,11 +1594,6 @@ extern "C" int m2f_plan_backward_bucketed(m2f_plan_t* p, const float* params, co
     c.cb_user = user;
     c.hi = p->m->off_1d;
     c.xchg = !cb && bucket_floats > 0 && p->xchg_on;
-    c.adam = !cb && bucket_floats > 0 && p->opt_on;
-    if (c.adam) {
-        c.fam_lo = p->fam.empty() ? p->m->cls[0].w_off : p->fam[0].inw_off;
-        c.fusion_safe = p->fam.empty();
-    }
     if (c.xchg) {
         M2F_REQUIRE(grads == p->xchg_group.peer_base[p->xchg_group.rank], M2F_ERR_ARG,
                     "plan_backward: with an exchange attached the gradients must be written to this rank's copy of the symmetric buffer");
@@ -1768,9 +1610,8 @@ extern "C" int m2f_plan_backward_bucketed(m2f_plan_t* p, const float* params, co
         M2F_TRY(backward_all(c, kp, dlogits, PH_HEAD));
         m2f_plan::GraphKey key;
         key.params = params; key.shadow = shadow; key.ws = workspace; key.grads = grads; key.p_used = p->p_used;
-        key.flags = (cb ? 1 : (c.xchg ? 2 : 0)) | (c.adam ? 4 : 0);
-        key.opt_m = c.adam ? p->opt_m : nullptr;
-        key.bucket_floats = (cb || c.xchg || c.adam) ? c.bucket_floats : 0;
+        key.flags = cb ? 1 : (c.xchg ? 2 : 0);
+        key.bucket_floats = (cb || c.xchg) ? c.bucket_floats : 0;
         std::vector<std::pair<int64_t, int64_t>> marks;
         bool captured = false;
         rc = run_graphed(p, p->gb, key, ust, [&](cudaStream_t cs) {

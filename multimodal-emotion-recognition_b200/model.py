@@ -87,8 +87,6 @@ class _Plan:
         self.token = 0  # bumped by every forward; a backward must match the forward that filled the workspace
         if training and model._exchange is not None:
             model._attach_exchange(self)
-        if training and model._inbwd is not None:
-            model._attach_optimizer(self)
 
     def destroy(self):
         if self.handle:
@@ -185,7 +183,6 @@ class M2FNet(nn.Module):
         self._anchor_box = [None]  # in a list: assigning a Parameter as an attribute would register it under that name
         self._grad_arena: Optional[torch.Tensor] = None
         self._exchange = None            # (PeerGroup, scale, ctas, bucket_floats): gradient exchange inside the backward
-        self._inbwd = None               # FusedAdam(in_backward=True): the optimizer update runs inside the backward
         self._grad_views = None          # p.grad views into the gradient arena, built once
         self._grads_cleared = False      # FusedAdam.zero_grad(): views still attached, contents dead
         self._shadow: Optional[torch.Tensor] = None
@@ -331,19 +328,7 @@ class M2FNet(nn.Module):
         if self._grad_views is None:
             self._grad_views = [self._grad_arena[o:o + n].view(p.shape) for p, o, n in self._flat]
         target = self._grad_arena if fresh else torch.empty_like(self._grad_arena)
-        opt = self._inbwd
-        if opt is not None:
-            if not fresh:
-                raise RuntimeError("FusedAdam(in_backward=True) applies the update inside backward(): gradient accumulation across "
-                                   "backwards is not supported (use zero_grad(set_to_none=True), one backward per step)")
-            opt._before_backward()
-        if opt is not None and self._exchange is None:
-            if self._bucket_hook is not None:
-                raise RuntimeError("FusedAdam(in_backward=True) needs the in-graph peer exchange or a single GPU (not bucket callbacks)")
-            _lib.check(_lib.lib().m2f_plan_backward_bucketed(plan.handle, self._arena.data_ptr(), self._shadow.data_ptr(),
-                                                             plan.ws.data_ptr(), dlogits.data_ptr(), target.data_ptr(),
-                                                             4 << 20, None, None, _stream()), "plan_backward (optimizer inside)")
-        elif self._exchange is not None:
+        if self._exchange is not None:
             if not fresh:
                 raise RuntimeError("data-parallel M2FNet needs zero_grad(set_to_none=True) (gradient accumulation across "
                                    "backwards is not supported with the in-backward gradient exchange)")
@@ -375,8 +360,6 @@ class M2FNet(nn.Module):
             _lib.check(_lib.lib().m2f_plan_backward(plan.handle, self._arena.data_ptr(), self._shadow.data_ptr(), plan.ws.data_ptr(),
                                                     dlogits.data_ptr(), target.data_ptr(), _stream()), "plan_backward")
         self.launches += 1
-        if opt is not None:
-            opt._after_backward()
         if attached:
             self._grads_cleared = False  # the views already point at the arena the kernels just wrote
         elif fresh:
@@ -462,20 +445,6 @@ class M2FNet(nn.Module):
                     _lib.check(_lib.lib().m2f_plan_set_exchange(pl.handle, None, 1.0, 0), "plan_set_exchange")
                 else:
                     self._attach_exchange(pl)
-
-    def _attach_optimizer(self, plan: "_Plan"):
-        o = self._inbwd
-        _lib.check(_lib.lib().m2f_plan_set_optimizer(plan.handle, o._m.data_ptr(), o._v.data_ptr(), o._hp.data_ptr()), "plan_set_optimizer")
-
-    def set_inbackward_optimizer(self, opt):
-        """Attach (or with None detach) a FusedAdam whose update runs inside the backward (m2f_plan_set_optimizer)."""
-        self._inbwd = opt
-        for pl in self._plans.values():
-            if pl.training and pl.handle:
-                if opt is None:
-                    _lib.check(_lib.lib().m2f_plan_set_optimizer(pl.handle, None, None, None), "plan_set_optimizer")
-                else:
-                    self._attach_optimizer(pl)
 
     def adopt_grad_arena(self, buf: Optional[torch.Tensor]):
         """Make the backward write its gradients into `buf` (fp32, arena_floats elements, on the model's device) -- the

@@ -11,43 +11,13 @@ from . import _lib
 
 
 class FusedAdam(torch.optim.Optimizer):
-    def __init__(self, model, lr=1e-3, betas=(0.9, 0.999), eps=1e-8, weight_decay=0.0, grad_scale: float = 1.0,
-                 in_backward: bool = False):
-        """`in_backward=True`: the update of every gradient range (and the refresh of its bf16 weight shadow) is launched
-        inside `loss.backward()` as soon as the range is final -- data parallel: as soon as it has been exchanged -- on a
-        low-priority stream beside the rest of the backward (m2f_plan_set_optimizer); `step()` then only advances the step
-        count.  Same arithmetic, bit for bit.  What changes for the caller: parameters move during backward() instead of
-        step(), so every backward must be followed by exactly one step(), and gradients cannot be accumulated across
-        backwards.  The learning rate of `param_groups[0]` is read at each backward (schedulers keep working)."""
+    def __init__(self, model, lr=1e-3, betas=(0.9, 0.999), eps=1e-8, weight_decay=0.0, grad_scale: float = 1.0):
         self.model = getattr(model, "module", model)
         params = [p for p, _, _ in self.model._flat]
         super().__init__(params, dict(lr=lr, betas=betas, eps=eps, weight_decay=weight_decay))
         self.grad_scale = float(grad_scale)
         self._t = 0
-        self.in_backward = bool(in_backward)
-        self._applied = False
         self._bind()
-        if self.in_backward:
-            self._hp = torch.zeros(8, dtype=torch.float32, device=self.model.flat_parameters().device)  # M2F_ADAM_HYPER_FLOATS
-            self.model.set_inbackward_optimizer(self)
-
-    def _before_backward(self):
-        if self._applied:
-            raise RuntimeError("FusedAdam(in_backward=True): backward() was called twice without step() in between -- the first "
-                               "backward has already updated the parameters")
-        grp = self.param_groups[0]
-        _lib.check(_lib.lib().m2f_adam_hyper(self._hp.data_ptr(), float(grp["lr"]), float(grp["betas"][0]), float(grp["betas"][1]),
-                                             float(grp["eps"]), float(grp["weight_decay"]), self._t + 1, self.grad_scale,
-                                             torch.cuda.current_stream().cuda_stream), "adam_hyper")
-
-    def _after_backward(self):
-        self._applied = True
-
-    def detach_from_backward(self):
-        """Back to the ordinary step(): the next backward leaves the parameters alone."""
-        if self.in_backward:
-            self.model.set_inbackward_optimizer(None)
-            self.in_backward = False
 
     def _bind(self):
         arena = self.model.flat_parameters()
@@ -65,12 +35,6 @@ class FusedAdam(torch.optim.Optimizer):
         g = self.model.flat_grads()
         if g is None:
             raise RuntimeError("FusedAdam.step(): no gradients (call backward first)")
-        if self.in_backward:
-            if not self._applied:
-                raise RuntimeError("FusedAdam(in_backward=True).step(): no backward since the last step (the update runs inside backward())")
-            self._applied = False
-            self._t += 1
-            return loss
         grp = self.param_groups[0]
         self._t += 1
         arena = self.model.flat_parameters()
