@@ -877,10 +877,14 @@ static int forward_modality(Ctx& c, Modality& mo, const float* input, const uint
 
 enum { PH_HEAD = 1, PH_BODY = 2, PH_TAIL = 4, PH_ALL = 7 };
 
-static bool narrow_enabled() {
-    static const bool on = [] { const char* e = std::getenv("M2F_NARROW"); return e && e[0] == '1'; }();
-    return on;
+// M2F_NARROW: 0 = full-width tiles everywhere; 1 (default) = half-width tiles for the under-filled GEMMs of the serial sections
+// (fusion layers, classifier; measured 3.85 -> 3.74 ms per step at C2, profiles/r2_ab_tiles.txt); 2 = also inside the two
+// modality stacks (measured slower: 4.05 vs 4.00 in the same run); 3 = also for the weight gradients (slower still).
+static int narrow_level() {
+    static const int lvl = [] { const char* e = std::getenv("M2F_NARROW"); return e ? std::atoi(e) : 1; }();
+    return lvl;
 }
+static bool narrow_enabled() { return narrow_level() >= 1; }
 
 // PH_BODY: everything up to the classifier's last hidden layer (capturable: touches only plan-owned memory when text /
 // audio point at the staging copies); PH_TAIL: the logits GEMM (writes the caller's buffer).
@@ -897,6 +901,7 @@ static int forward_all(Ctx& c, const float* text, const float* audio, const uint
     const bool fork = md->both && p->use_streams;
     const bool body = phases & PH_BODY;
     if (body) c.stamp("begin");
+    c.narrow = narrow_level() >= 2;
     if (body && p->mod[0].enabled) {
         if (fork) {
             M2F_TRY(c.dep(c.st, c.side(0)));
@@ -965,7 +970,7 @@ static int lin_wgrad(Ctx& c, cudaStream_t wst, const m2f_planes_t& dY, const m2f
     M2F_TRY(c.dep(chain, wst));
     c.cur = wst;
     const bool narrow = c.narrow;
-    c.narrow = false;  // weight gradients run beside the chain: full-width tiles
+    c.narrow = narrow_level() >= 3;  // weight gradients run beside the chain: full-width tiles
     int rc = c.gemm(dY, true, X, true, out, in, Epi().f32(dW, dW_ld));
     c.narrow = narrow;
     if (rc == M2F_OK && db) rc = m2f_colsum_planes(&dY, db, wst);
@@ -1179,7 +1184,7 @@ static int backward_all(Ctx& c, const uint8_t* key_pad, const float* dlogits, in
     // projection dropout mask applies -- handled above by not gating the [dq | dv] GEMM at f == 0.
     // text first, audio last: gradients then complete in exactly the reverse of the arena order
     // The two stacks are independent from here on: text continues on the caller's stream, audio runs beside it.
-    c.narrow = false;  // the two stacks run side by side from here on
+    c.narrow = narrow_level() >= 2;  // the two stacks run side by side from here on
     const bool interleave = (c.cb || c.marks || c.xchg) && p->mod[0].enabled && p->mod[1].enabled;
     if (interleave) {
         M2F_TRY(c.done_down_to(fam ? p->fam[0].inw_off : md->cls[0].w_off, true));  // everything above the stacks
