@@ -307,9 +307,12 @@ ln_fwd_staged_kernel(const float* __restrict__ x, int64_t x_ld, const float* __r
     }
 }
 
-// Backward, same staging: tiles of 8 rows of g and x land in shared memory; phase 1 (one row per warp: dx) and phase 2 (one
-// float4 column per thread: dgamma / dbeta / dbias partial sums) both read them from there, so every row is fetched from
-// global memory once.  Same arithmetic, summation order and Philox element indices as ln_bwd_kernel.
+// Backward, same staging: tiles of 8 rows of g and x land in shared memory.  Phase 1 (one row per warp) only reduces: the
+// row's c1 = mean(g*gamma), c2 = mean(g*gamma*xhat).  Phase 2 (one float4 column per thread, 8 rows) does everything else
+// exactly once per element: dx, the Philox mask, the fp32 and plane stores (a warp writes 512 contiguous bytes of a row) and the
+// dgamma / dbeta / dbias partial sums -- the first version of this kernel computed dx and the mask in both phases and ran at
+// 0.46 of the HBM peak, bound by the duplicated Philox rounds rather than by memory.  Same arithmetic and Philox element
+// indices as ln_bwd_kernel; every row is fetched from global memory once.
 template <int NCH>
 __global__ void __launch_bounds__(LN2_THREADS)
 ln_bwd_staged_kernel(const float* __restrict__ g, int64_t g_ld, const float* __restrict__ x, int64_t x_ld,
@@ -373,8 +376,7 @@ ln_bwd_staged_kernel(const float* __restrict__ g, int64_t g_ld, const float* __r
         ptx::mbar_wait(&full_bar[s2], (uint32_t)((it / LN2_STAGES) & 1));
         const float* sx = ring + (size_t)s2 * stage_floats;
         const float* sgr = sx + tile_floats;
-        if (m < M) {
-            float4 xv[NCH], av[NCH];
+        if (m < M) {  // phase 1: the two row means
             float s1 = 0.f, s2sum = 0.f;
 #pragma unroll
             for (int c = 0; c < NCH; ++c) {
@@ -383,38 +385,19 @@ ln_bwd_staged_kernel(const float* __restrict__ g, int64_t g_ld, const float* __r
                     const float4 gm = *reinterpret_cast<const float4*>(gamma + col);
                     const float4 xr = *reinterpret_cast<const float4*>(sx + (size_t)warp * D + col);
                     const float4 gr = *reinterpret_cast<const float4*>(sgr + (size_t)warp * D + col);
-                    xv[c] = make_float4((xr.x - mean) * rstd, (xr.y - mean) * rstd, (xr.z - mean) * rstd, (xr.w - mean) * rstd);
-                    av[c] = make_float4(gr.x * gm.x, gr.y * gm.y, gr.z * gm.z, gr.w * gm.w);
-                    s1 += av[c].x + av[c].y + av[c].z + av[c].w;
-                    s2sum += av[c].x * xv[c].x + av[c].y * xv[c].y + av[c].z * xv[c].z + av[c].w * xv[c].w;
-                } else {
-                    xv[c] = av[c] = make_float4(0.f, 0.f, 0.f, 0.f);
+                    const float4 xh = make_float4((xr.x - mean) * rstd, (xr.y - mean) * rstd, (xr.z - mean) * rstd, (xr.w - mean) * rstd);
+                    const float4 a = make_float4(gr.x * gm.x, gr.y * gm.y, gr.z * gm.z, gr.w * gm.w);
+                    s1 += a.x + a.y + a.z + a.w;
+                    s2sum += a.x * xh.x + a.y * xh.y + a.z * xh.z + a.w * xh.w;
                 }
             }
             const float c1 = warp_sum(s1) * invD, c2 = warp_sum(s2sum) * invD;
             if (lane == 0) { rowc[warp][0] = mean; rowc[warp][1] = rstd; rowc[warp][2] = c1; rowc[warp][3] = c2; }
-#pragma unroll
-            for (int c = 0; c < NCH; ++c) {
-                const int col = (c * 32 + lane) * 4;
-                if (col < D) {
-                    float o[4] = {rstd * (av[c].x - c1 - xv[c].x * c2), rstd * (av[c].y - c1 - xv[c].y * c2),
-                                  rstd * (av[c].z - c1 - xv[c].z * c2), rstd * (av[c].w - c1 - xv[c].w * c2)};
-                    if (dx) *reinterpret_cast<float4*>(dx + m * dx_ld + col) = make_float4(o[0], o[1], o[2], o[3]);
-                    if (dxpl) {
-                        if (drop.enabled) {
-                            float dm[4];
-                            drop_mult4(drop, (uint64_t)(m * D + col) >> 2, dm);
-#pragma unroll
-                            for (int i = 0; i < 4; ++i) o[i] *= dm[i];
-                        }
-                        store_planes4(dxpl, dxpl_stride, P, m * dxpl_ld + col, o);
-                    }
-                }
-            }
         }
         __syncthreads();  // rowc complete
-        if (ccol < D) {
+        if (ccol < D) {   // phase 2: dx, mask, stores and the column sums, once per element
             const int nrow = (int)min((int64_t)LN2_ROWS, M - m0);
+#pragma unroll 2
             for (int r = 0; r < nrow; ++r) {
                 const int64_t mm = m0 + r;
                 const float4 xr = *reinterpret_cast<const float4*>(sx + (size_t)r * D + ccol);
@@ -423,14 +406,16 @@ ln_bwd_staged_kernel(const float* __restrict__ g, int64_t g_ld, const float* __r
                 const float4 xh = make_float4((xr.x - rmean) * rrstd, (xr.y - rmean) * rrstd, (xr.z - rmean) * rrstd, (xr.w - rmean) * rrstd);
                 sg.x += gr.x * xh.x; sg.y += gr.y * xh.y; sg.z += gr.z * xh.z; sg.w += gr.w * xh.w;
                 sb.x += gr.x; sb.y += gr.y; sb.z += gr.z; sb.w += gr.w;
-                if (dbias) {
-                    float o[4] = {rrstd * (gr.x * gmc.x - c1 - xh.x * c2), rrstd * (gr.y * gmc.y - c1 - xh.y * c2),
-                                  rrstd * (gr.z * gmc.z - c1 - xh.z * c2), rrstd * (gr.w * gmc.w - c1 - xh.w * c2)};
+                float o[4] = {rrstd * (gr.x * gmc.x - c1 - xh.x * c2), rrstd * (gr.y * gmc.y - c1 - xh.y * c2),
+                              rrstd * (gr.z * gmc.z - c1 - xh.z * c2), rrstd * (gr.w * gmc.w - c1 - xh.w * c2)};
+                if (dx) *reinterpret_cast<float4*>(dx + mm * dx_ld + ccol) = make_float4(o[0], o[1], o[2], o[3]);
+                if (dxpl || dbias) {
                     if (drop.enabled) {
                         float dm[4];
                         drop_mult4(drop, (uint64_t)(mm * D + ccol) >> 2, dm);
                         o[0] *= dm[0]; o[1] *= dm[1]; o[2] *= dm[2]; o[3] *= dm[3];
                     }
+                    if (dxpl) store_planes4(dxpl, dxpl_stride, P, mm * dxpl_ld + ccol, o);
                     sbias.x += o[0]; sbias.y += o[1]; sbias.z += o[2]; sbias.w += o[3];
                 }
             }

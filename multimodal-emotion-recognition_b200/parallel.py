@@ -79,6 +79,7 @@ class PeerGradExchange:
     them from the bucket callback like the NCCL reducer does.
 
     Environment: M2F_EXCHANGE_MC=0 forces the peer load / store variant, M2F_EXCHANGE_CTAS sets the CTAs per call,
+    M2F_EXCHANGE_SHAPE=threads,unroll their shape (one of the pairs m2f_exchange_tune accepts),
     M2F_EXCHANGE_IN_GRAPH=0 selects the callback mode."""
 
     def __init__(self, model, group=None, average: bool = True, ctas: int = 0, in_graph: Optional[bool] = None):
@@ -117,6 +118,10 @@ class PeerGradExchange:
         self.multicast = bool(mc)
         self.scale = 1.0 / self.world if average else 1.0
         self.ctas = int(os.environ.get("M2F_EXCHANGE_CTAS", ctas))
+        shape = os.environ.get("M2F_EXCHANGE_SHAPE")  # "threads,unroll" of the exchange CTAs (m2f_exchange_tune); every rank the same
+        if shape:
+            t_, u_ = (int(x) for x in shape.split(","))
+            _lib.check(_lib.lib().m2f_exchange_tune(t_, u_), "exchange_tune")
         self.grads = self.buf[:n]
         self._dryrun = os.environ.get("M2F_EXCHANGE_DRYRUN", "0") == "1"
         self._ev = torch.cuda.Event()
