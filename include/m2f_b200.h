@@ -246,12 +246,17 @@ int m2f_plan_backward_bucketed(m2f_plan_t* p, const float* params, const void* s
 #define M2F_XCHG_MAX_RANKS 16
 #define M2F_XCHG_MAX_CTAS 64
 #define M2F_XCHG_NO_EXIT_BARRIER 1
+#define M2F_XCHG_WIRE_BF16 2 /* the range travels as bf16 (needs wire_off_bytes, the multicast mapping, 8-float alignment) */
 #define M2F_XCHG_SIGNAL_BYTES (M2F_XCHG_MAX_CTAS * M2F_XCHG_MAX_RANKS * 4)
 typedef struct {
     void* mc_base;                        /* multicast mapping of the buffer (multimem.ld_reduce / multimem.st), or NULL */
     void* peer_base[M2F_XCHG_MAX_RANKS];  /* unicast mapping of every rank's buffer; entries >= world are ignored */
     int64_t signal_off_bytes;
     int32_t rank, world;
+    int64_t wire_off_bytes;               /* bf16 staging area inside the buffer (2 bytes per gradient float, element i at
+                                           * wire_off_bytes + 2 i), behind the signal words; 0 = none (fp32 wire only) */
+    int32_t wire_bf16;                    /* m2f_plan_set_exchange: exchange the ranges of the backward in bf16 */
+    int32_t _pad;
 } m2f_peer_group_t;
 
 /* In-place all-reduce of the float range [lo, hi) of the symmetric buffer: on return of the *kernel* every rank holds
@@ -260,7 +265,11 @@ typedef struct {
  * and have one GPU to itself -- the kernels of the ranks wait for each other.  ctas <= 0: one CTA per 128 KB of a rank's slice, at most 16 (enough to saturate NVLink).
  * flags: M2F_XCHG_NO_EXIT_BARRIER skips the closing handshake -- allowed on every call of a sequence on one stream except the
  * last one, whose handshake then covers the whole sequence (consumers must wait for that last kernel).
- * With world == 1 it degenerates to an in-place scale (used by the single-GPU tests of the slicing arithmetic). */
+ * With world == 1 it degenerates to an in-place scale (used by the single-GPU tests of the slicing arithmetic).
+ * M2F_XCHG_WIRE_BF16: the range is packed to bf16 into the staging area, all-reduced there (multimem.ld_reduce
+ * .acc::f32.v4.bf16x2: fp32 accumulation in the switch, half the NVLink bytes) and unpacked back to fp32 -- three launches, the
+ * middle one with both handshakes; the result carries two bf16 roundings (relative 2^-9).  Ranges that are not whole
+ * 8-float vectors, groups without multicast or staging area, and world == 1 silently use the fp32 wire. */
 int m2f_grad_allreduce_peer(const m2f_peer_group_t* g, int64_t lo, int64_t hi, float scale, int32_t ctas, int32_t flags,
                             void* stream);
 

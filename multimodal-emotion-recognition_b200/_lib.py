@@ -54,12 +54,13 @@ class ModelCfg(C.Structure):
 XCHG_MAX_RANKS, XCHG_MAX_CTAS = 16, 64
 XCHG_SIGNAL_BYTES = XCHG_MAX_CTAS * XCHG_MAX_RANKS * 4
 XCHG_NO_EXIT_BARRIER = 1
+XCHG_WIRE_BF16 = 2
 
 
 class PeerGroup(C.Structure):
     """m2f_peer_group_t"""
     _fields_ = [("mc_base", C.c_void_p), ("peer_base", C.c_void_p * XCHG_MAX_RANKS), ("signal_off_bytes", C.c_int64),
-                ("rank", C.c_int32), ("world", C.c_int32)]
+                ("rank", C.c_int32), ("world", C.c_int32), ("wire_off_bytes", C.c_int64), ("wire_bf16", C.c_int32), ("_pad", C.c_int32)]
 
 
 BUCKET_CB = C.CFUNCTYPE(None, C.c_void_p, C.c_int64, C.c_int64, C.c_void_p)  # m2f_bucket_cb

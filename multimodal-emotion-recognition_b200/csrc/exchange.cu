@@ -192,6 +192,91 @@ grad_allreduce_kernel(float* __restrict__ mc, PeerPtrs pp, int rank, int world, 
     if (tracer) tr[3] = gtimer();
 }
 
+// ------------------------------------------------------------------------------------------ bf16 wire format
+// The exchange is NVLink-bound for the whole backward (345 MB of fp32 gradients per step against a 1.5 ms backward,
+// profiles/r2_exchange_sweep_2gpu.txt), so the lever is the byte count: with M2F_XCHG_WIRE_BF16 a range travels as bf16.
+// Three launches on the caller's stream: (1) this rank's fp32 range -> its bf16 staging copy in the symmetric buffer (local
+// HBM only); (2) the two-shot all-reduce on the staging copies -- `multimem.ld_reduce.add.acc::f32.v4.bf16x2`: the switch sums
+// the ranks' bf16 values in fp32 and returns eight rounded sums per 16 bytes, `multimem.st` broadcasts them -- with the entry
+// AND the closing handshake (the next launch reads every rank's slices); (3) staging -> this rank's fp32 range.  Half the NVLink
+// bytes for 12 bytes per element of extra local traffic.  The reduced gradient carries one bf16 rounding of each rank's
+// contribution and one of the sum (relative 2^-9 per element, unbiased): well inside the 2e-2 budget of the bf16 training
+// mode, NOT for the fp32-parity mode (the host side only enables it for bf16 precision modes).
+__global__ void __launch_bounds__(256)
+wire_pack_kernel(const float* __restrict__ src, __nv_bfloat16* __restrict__ dst, int64_t n8) {
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n8; i += (int64_t)gridDim.x * blockDim.x) {
+        const float4 a = *reinterpret_cast<const float4*>(src + 8 * i), b = *reinterpret_cast<const float4*>(src + 8 * i + 4);
+        const __nv_bfloat162 p0 = __floats2bfloat162_rn(a.x, a.y), p1 = __floats2bfloat162_rn(a.z, a.w);
+        const __nv_bfloat162 p2 = __floats2bfloat162_rn(b.x, b.y), p3 = __floats2bfloat162_rn(b.z, b.w);
+        uint4 o;
+        o.x = *reinterpret_cast<const uint32_t*>(&p0); o.y = *reinterpret_cast<const uint32_t*>(&p1);
+        o.z = *reinterpret_cast<const uint32_t*>(&p2); o.w = *reinterpret_cast<const uint32_t*>(&p3);
+        *reinterpret_cast<uint4*>(dst + 8 * i) = o;
+    }
+}
+__global__ void __launch_bounds__(256)
+wire_unpack_kernel(const __nv_bfloat16* __restrict__ src, float* __restrict__ dst, int64_t n8) {
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n8; i += (int64_t)gridDim.x * blockDim.x) {
+        const uint4 v = *reinterpret_cast<const uint4*>(src + 8 * i);
+        const __nv_bfloat162 p0 = *reinterpret_cast<const __nv_bfloat162*>(&v.x), p1 = *reinterpret_cast<const __nv_bfloat162*>(&v.y);
+        const __nv_bfloat162 p2 = *reinterpret_cast<const __nv_bfloat162*>(&v.z), p3 = *reinterpret_cast<const __nv_bfloat162*>(&v.w);
+        *reinterpret_cast<float4*>(dst + 8 * i) = make_float4(__low2float(p0), __high2float(p0), __low2float(p1), __high2float(p1));
+        *reinterpret_cast<float4*>(dst + 8 * i + 4) = make_float4(__low2float(p2), __high2float(p2), __low2float(p3), __high2float(p3));
+    }
+}
+__device__ __forceinline__ uint4 mc_ld_reduce_bf16x8(const __nv_bfloat16* mc) {
+    uint4 v;
+    asm volatile("multimem.ld_reduce.relaxed.sys.global.add.acc::f32.v4.bf16x2 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(mc) : "memory");
+    return v;
+}
+__device__ __forceinline__ uint32_t scale_bf16x2(uint32_t w, float scale) {
+    const __nv_bfloat162 p = *reinterpret_cast<const __nv_bfloat162*>(&w);
+    const __nv_bfloat162 q = __floats2bfloat162_rn(__low2float(p) * scale, __high2float(p) * scale);
+    return *reinterpret_cast<const uint32_t*>(&q);
+}
+
+// the all-reduce proper on the bf16 staging copies; wire = multicast address of staging element `lo`, n8 vectors of 8
+template <int XCHG_THREADS, int XCHG_UNROLL>
+__global__ void __launch_bounds__(XCHG_THREADS)
+grad_allreduce_bf16_kernel(__nv_bfloat16* __restrict__ mc_wire, PeerPtrs pp, int rank, int world, int64_t lo, int64_t n8, float scale) {
+    const bool tracer = blockIdx.x == 0 && threadIdx.x == 0;
+    unsigned long long* tr = nullptr;
+    if (tracer) {
+        tr = g_xchg_trace + (size_t)(atomicAdd(&g_xchg_trace_n, 1u) % M2F_XCHG_TRACE_RECORDS) * 6;
+        tr[0] = gtimer();
+        tr[4] = (unsigned long long)lo;
+        tr[5] = (unsigned long long)(8 * n8);
+    }
+    block_barrier_all_ranks(pp, rank, world);  // every rank's staging copy of the range is complete (its pack kernel has finished)
+    if (tracer) tr[1] = gtimer();
+    const int64_t per_rank = (n8 + world - 1) / world;
+    const int64_t v_lo = min(n8, per_rank * rank), v_hi = min(n8, v_lo + per_rank);
+    const int64_t stride = (int64_t)gridDim.x * XCHG_THREADS;
+    for (int64_t i0 = v_lo + blockIdx.x * (int64_t)XCHG_THREADS + threadIdx.x; i0 < v_hi; i0 += stride * XCHG_UNROLL) {
+        uint4 acc[XCHG_UNROLL];
+#pragma unroll
+        for (int u = 0; u < XCHG_UNROLL; ++u) {
+            const int64_t i = i0 + u * stride;
+            if (i < v_hi) acc[u] = mc_ld_reduce_bf16x8(mc_wire + 8 * i);
+        }
+#pragma unroll
+        for (int u = 0; u < XCHG_UNROLL; ++u) {
+            const int64_t i = i0 + u * stride;
+            if (i < v_hi) {
+                uint4 v = acc[u];
+                v.x = scale_bf16x2(v.x, scale); v.y = scale_bf16x2(v.y, scale); v.z = scale_bf16x2(v.z, scale); v.w = scale_bf16x2(v.w, scale);
+                mc_st_v4(reinterpret_cast<float*>(mc_wire + 8 * i),
+                         make_float4(__uint_as_float(v.x), __uint_as_float(v.y), __uint_as_float(v.z), __uint_as_float(v.w)));
+            }
+        }
+    }
+    __threadfence_system();
+    if (tracer) tr[2] = gtimer();
+    block_barrier_all_ranks(pp, rank, world);  // every rank has stored its slice into my staging copy: the unpack launch may read it
+    if (tracer) tr[3] = gtimer();
+}
+
 }  // namespace m2f
 
 using namespace m2f;
@@ -230,6 +315,53 @@ extern "C" int m2f_grad_allreduce_peer(const m2f_peer_group_t* g, int64_t lo, in
         pp.sig[r] = reinterpret_cast<uint32_t*>(reinterpret_cast<uint8_t*>(g->peer_base[r]) + g->signal_off_bytes);
     }
     M2F_REQUIRE((reinterpret_cast<uintptr_t>(g->mc_base) % 16) == 0, M2F_ERR_ALIGN, "grad_allreduce_peer: mc_base must be 16-byte aligned");
+    cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+    float* mc = reinterpret_cast<float*>(g->mc_base);
+    // bf16 wire: needs the multicast mapping, a staging area, more than one rank and a range made of whole 16-byte bf16
+    // vectors (every rank evaluates the same condition: it depends on the arguments only); anything else travels as fp32
+    if ((flags & M2F_XCHG_WIRE_BF16) && mc && g->world > 1 && g->wire_off_bytes > 0 && (lo & 7) == 0 && ((hi - lo) & 7) == 0) {
+        M2F_REQUIRE(g->wire_off_bytes >= g->signal_off_bytes + M2F_XCHG_SIGNAL_BYTES && (g->wire_off_bytes % 16) == 0, M2F_ERR_ARG,
+                    "grad_allreduce_peer: the bf16 staging area (offset %lld) must lie behind the signal words and be 16-byte aligned",
+                    (long long)g->wire_off_bytes);
+        const int64_t n8 = (hi - lo) / 8;
+        float* mine = pp.base[g->rank];
+        __nv_bfloat16* my_wire = reinterpret_cast<__nv_bfloat16*>(reinterpret_cast<uint8_t*>(mine) + g->wire_off_bytes) + lo;
+        __nv_bfloat16* mc_wire = reinterpret_cast<__nv_bfloat16*>(reinterpret_cast<uint8_t*>(mc) + g->wire_off_bytes) + lo;
+        int64_t cg = (n8 + 255) / 256;
+        if (cg > 148 * 2) cg = 148 * 2;
+        wire_pack_kernel<<<(unsigned)cg, 256, 0, st>>>(mine + lo, my_wire, n8);
+        M2F_LAUNCH_CHECK();
+        const int64_t per_rank_w = (n8 + g->world - 1) / g->world;
+        const int64_t per_iter_w = (int64_t)512 * 8;
+        int grid_w;
+        if (ctas > 0) grid_w = ctas;
+        else {
+            const int64_t want = (per_rank_w + 2 * per_iter_w - 1) / (2 * per_iter_w);
+            grid_w = want < 1 ? 1 : (want > 16 ? 16 : (int)want);
+        }
+        if (grid_w > M2F_XCHG_MAX_CTAS) grid_w = M2F_XCHG_MAX_CTAS;
+        const int64_t need_w = (per_rank_w + per_iter_w - 1) / per_iter_w;
+        if (need_w < grid_w) grid_w = need_w < 1 ? 1 : (int)need_w;
+        static const int prio_w = [] {
+            int lo_p = 0, hi_p = 0;
+            return cudaDeviceGetStreamPriorityRange(&lo_p, &hi_p) == cudaSuccess ? hi_p : 0;
+        }();
+        cudaLaunchAttribute attr_w[1];
+        attr_w[0].id = cudaLaunchAttributePriority;
+        attr_w[0].val.priority = prio_w;
+        cudaLaunchConfig_t cfg_w = {};
+        cfg_w.gridDim = dim3((unsigned)grid_w);
+        cfg_w.blockDim = dim3(512);
+        cfg_w.stream = st;
+        cfg_w.attrs = attr_w;
+        cfg_w.numAttrs = 1;
+        const int rank_w = g->rank, world_w = g->world;
+        M2F_CUDA(cudaLaunchKernelEx(&cfg_w, grad_allreduce_bf16_kernel<512, 8>, mc_wire, pp, rank_w, world_w, lo, n8, scale));
+        M2F_LAUNCH_CHECK();
+        wire_unpack_kernel<<<(unsigned)cg, 256, 0, st>>>(my_wire, mine + lo, n8);
+        M2F_LAUNCH_CHECK();
+        return M2F_OK;
+    }
     const int head = (int)((4 - (lo & 3)) & 3) < (hi - lo) ? (int)((4 - (lo & 3)) & 3) : (int)(hi - lo);
     const int64_t n4 = (hi - lo - head) / 4;
     const int tail = (int)(hi - lo - head - 4 * n4);
@@ -252,8 +384,6 @@ extern "C" int m2f_grad_allreduce_peer(const m2f_peer_group_t* g, int64_t lo, in
     if (grid > M2F_XCHG_MAX_CTAS) grid = M2F_XCHG_MAX_CTAS;
     const int64_t need = (per_rank + per_iter - 1) / per_iter;
     if (need < grid) grid = need < 1 ? 1 : (int)need;
-    cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
-    float* mc = reinterpret_cast<float*>(g->mc_base);
     // The few exchange CTAs go in front of the backward's pending GEMM CTAs: the priority is set on the launch itself, so it
     // also holds for the kernel nodes of a captured graph, whatever stream they were captured from.
     static const int prio = [] {

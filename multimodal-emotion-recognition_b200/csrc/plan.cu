@@ -96,7 +96,7 @@ struct m2f_model {
     bool both = false;
 
     int64_t add_param(const std::string& name, int64_t rows, int64_t cols, int64_t& cursor) {
-        cursor = round_up(cursor, 4);
+        cursor = round_up(cursor, 8);  // 32 bytes: float4 access, and ranges of whole 16-byte bf16 vectors for the exchange's bf16 wire
         params.push_back({name, cursor, rows, cols});
         const int64_t off = cursor;
         cursor += rows * (cols ? cols : 1);
@@ -695,7 +695,8 @@ struct Ctx {
     bool capturing = false;
     int report(int64_t lo, int64_t hi_, cudaStream_t ready, bool last = false) {
         if (xchg) {  // one sequence on `ready`: only the last call needs the closing handshake
-            M2F_TRY(m2f_grad_allreduce_peer(&p->xchg_group, lo, hi_, p->xchg_scale, p->xchg_ctas, last ? 0 : M2F_XCHG_NO_EXIT_BARRIER, ready));
+            M2F_TRY(m2f_grad_allreduce_peer(&p->xchg_group, lo, hi_, p->xchg_scale, p->xchg_ctas,
+                                            (last ? 0 : M2F_XCHG_NO_EXIT_BARRIER) | (p->xchg_group.wire_bf16 ? M2F_XCHG_WIRE_BF16 : 0), ready));
             ++p->xchg_ranges;
             if (ready != st) ready_in_capture = true;
             return M2F_OK;

@@ -82,10 +82,16 @@ class PeerGradExchange:
     M2F_EXCHANGE_SHAPE=threads,unroll their shape (one of the pairs m2f_exchange_tune accepts),
     M2F_EXCHANGE_IN_GRAPH=0 selects the callback mode."""
 
-    def __init__(self, model, group=None, average: bool = True, ctas: int = 0, in_graph: Optional[bool] = None):
+    def __init__(self, model, group=None, average: bool = True, ctas: int = 0, in_graph: Optional[bool] = None, wire: Optional[str] = None):
+        """`wire`: "fp32" or "bf16" (default: $M2F_EXCHANGE_WIRE, else bf16 when the model trains in a bf16 precision mode --
+        planes_bwd == 1 -- and fp32 for the fp32-parity modes).  bf16 halves the NVLink bytes of the exchange, which is
+        bandwidth-bound for the whole backward; the reduced gradient then carries two bf16 roundings (relative 2^-9)."""
         import torch.distributed._symmetric_memory as symm_mem
 
         self.model = model
+        wire = (wire or os.environ.get("M2F_EXCHANGE_WIRE") or ("bf16" if getattr(model, "planes_bwd", 3) == 1 else "fp32")).lower()
+        if wire not in ("fp32", "bf16"):
+            raise ValueError(f"exchange wire format must be fp32 or bf16, got {wire!r}")
         self.in_graph = (os.environ.get("M2F_EXCHANGE_IN_GRAPH", "1") != "0") if in_graph is None else bool(in_graph)
 
         self.group = group if group is not None else dist.group.WORLD
@@ -97,7 +103,8 @@ class PeerGradExchange:
             raise RuntimeError("peer gradient exchange needs the model on the GPU")
         n = arena.numel()
         self.signal_off = (n * 4 + 127) // 128 * 128
-        total_floats = (self.signal_off + _lib.XCHG_SIGNAL_BYTES) // 4
+        self.wire_off = self.signal_off + _lib.XCHG_SIGNAL_BYTES  # bf16 staging copy of the gradients (2 bytes per float)
+        total_floats = (self.wire_off + (2 * n + 15) // 16 * 16) // 4 if wire == "bf16" else (self.signal_off + _lib.XCHG_SIGNAL_BYTES) // 4
         with torch.cuda.device(arena.device):
             self.buf = symm_mem.empty(total_floats, dtype=torch.float32, device=arena.device)
             self.buf.zero_()
@@ -116,6 +123,9 @@ class PeerGradExchange:
         self.pg.signal_off_bytes = self.signal_off
         self.pg.rank, self.pg.world = int(h.rank), self.world
         self.multicast = bool(mc)
+        self.wire = wire if (wire == "fp32" or (mc and self.world > 1)) else "fp32"  # the bf16 wire needs the multicast mapping
+        self.pg.wire_off_bytes = self.wire_off if self.wire == "bf16" else 0
+        self.pg.wire_bf16 = 1 if self.wire == "bf16" else 0
         self.scale = 1.0 / self.world if average else 1.0
         self.ctas = int(os.environ.get("M2F_EXCHANGE_CTAS", ctas))
         shape = os.environ.get("M2F_EXCHANGE_SHAPE")  # "threads,unroll" of the exchange CTAs (m2f_exchange_tune); every rank the same
@@ -153,7 +163,8 @@ class PeerGradExchange:
         if self._dryrun:  # timing experiments only: the ranges are reported but not exchanged
             self.log.append((lo, hi))
             return
-        _lib.check(_lib.lib().m2f_grad_allreduce_peer(ctypes.byref(self.pg), lo, hi, self.scale, self.ctas, 0, st.cuda_stream),
+        _lib.check(_lib.lib().m2f_grad_allreduce_peer(ctypes.byref(self.pg), lo, hi, self.scale, self.ctas,
+                                                      _lib.XCHG_WIRE_BF16 if self.wire == "bf16" else 0, st.cuda_stream),
                    "grad_allreduce_peer")
         self._ev.record(st)
         self._pending = True
@@ -174,7 +185,8 @@ class DataParallelM2FNet(torch.nn.Module):
     `exchange`: "peer" = the NVSwitch peer-memory kernel (`PeerGradExchange`), "nccl" = bucketed NCCL all-reduce,
     "auto" (default, or $M2F_EXCHANGE) = peer when the symmetric allocation can be set up on every rank, else nccl."""
 
-    def __init__(self, model, group=None, bucket_mb: Optional[float] = None, average: bool = True, exchange: Optional[str] = None):
+    def __init__(self, model, group=None, bucket_mb: Optional[float] = None, average: bool = True, exchange: Optional[str] = None,
+                 wire: Optional[str] = None):
         super().__init__()
         self.module = model
         self.group = group
@@ -205,7 +217,7 @@ class DataParallelM2FNet(torch.nn.Module):
             dist.all_reduce(vote, op=dist.ReduceOp.MIN, group=group)
             if int(vote.item()) == 1:
                 try:
-                    self.reducer = PeerGradExchange(model, group, average)
+                    self.reducer = PeerGradExchange(model, group, average, wire=wire)
                 except Exception as e:  # no symmetric memory on this box / fabric
                     err = e
                 ok = torch.tensor([0 if self.reducer is None else 1], device=flat.device)

@@ -61,7 +61,7 @@ def test_bad_arguments_are_errors():
     assert lib.m2f_grad_allreduce_peer(None, 0, 16, 1.0, 0, 0, None) == L.M2F_ERR_ARG
 
 
-def _worker(rank, world, port, out, in_graph):
+def _worker(rank, world, port, out, in_graph, wire="fp32"):
     os.environ["M2F_EXCHANGE_IN_GRAPH"] = "1" if in_graph else "0"
     import importlib
     import sys
@@ -80,7 +80,7 @@ def _worker(rank, world, port, out, in_graph):
     torch.manual_seed(100 + rank)
     model = pkg.M2FNet(cfg, planes=3).to("cuda").train()
     try:
-        net = pkg.DataParallelM2FNet(model, bucket_mb=0.05, exchange="peer")
+        net = pkg.DataParallelM2FNet(model, bucket_mb=0.05, exchange="peer", wire=wire)
     except RuntimeError as e:
         if rank == 0:
             torch.save({"unavailable": repr(e)}, out)
@@ -88,6 +88,7 @@ def _worker(rank, world, port, out, in_graph):
         return
     ex = net.reducer
     res["multicast"] = ex.multicast
+    res["wire"] = ex.wire
     # ---- the kernel alone: random buffers, unaligned ranges, multicast and peer variants
     n = ex.grads.numel()
     kerr = {}
@@ -116,6 +117,32 @@ def _worker(rank, world, port, out, in_graph):
         dist.barrier()
         kerr[variant] = (ex.grads - expect).abs().max().item()
     res["kernel_max_abs_err"] = kerr
+    if ex.wire == "bf16":  # the kernel alone with the bf16 wire: aligned ranges take the bf16 path, the unaligned one falls back to fp32
+        g = torch.Generator(device="cuda").manual_seed(70 + rank)
+        x = torch.randn(n, device="cuda", generator=g)
+        ex.grads.copy_(x)
+        both = [torch.empty_like(x) for _ in range(world)]
+        dist.all_gather(both, x)
+        expect = x.clone()
+        torch.cuda.synchronize()
+        dist.barrier()
+        st = torch.cuda.current_stream().cuda_stream
+        n8 = n // 8 * 8
+        seq = [(n8 // 2, n8, 0), (16, 4096, 3), (4099, 5003, 0), (8192, n8 // 2, 64)]
+        for k, (lo, hi, ctas) in enumerate(seq):
+            flags = L.XCHG_WIRE_BF16 | (0 if k == len(seq) - 1 else L.XCHG_NO_EXIT_BARRIER)
+            L.check(lib.m2f_grad_allreduce_peer(ctypes.byref(ex.pg), lo, hi, 0.5, ctas, flags, st), "grad_allreduce_peer (bf16 wire)")
+            if lo % 8 == 0 and (hi - lo) % 8 == 0:  # what the wire does: bf16(x_r) summed in fp32, rounded to bf16, scaled
+                tot = sum(t[lo:hi].bfloat16().float() for t in both)
+                expect[lo:hi] = (tot.bfloat16().float() * 0.5).bfloat16().float()
+            else:
+                expect[lo:hi] = sum(t[lo:hi] for t in both) * 0.5
+        torch.cuda.synchronize()
+        dist.barrier()
+        d = (ex.grads - expect).abs()
+        res["wire_kernel_max_abs_err"] = d.max().item()
+        res["wire_kernel_rel"] = (torch.linalg.vector_norm(ex.grads[16:n8] - (sum(both)[16:n8] * 0.5)) /
+                                  torch.linalg.vector_norm(sum(both)[16:n8] * 0.5)).item()
     # ---- the data-parallel step
     full = D.synth_batch(8, 9, 128, 64, seed=5)
     lo, hi = pkg.shard_range(8, rank, world)
@@ -155,6 +182,30 @@ def _worker(rank, world, port, out, in_graph):
     if rank == 0:
         torch.save(res, out)
     dist.destroy_process_group()
+
+
+def test_dp2_peer_exchange_bf16_wire(tmp_path):
+    """The bf16 wire format: the kernel alone reproduces bf16(sum of bf16(x_r)) bit for bit on aligned ranges (and falls back
+    to the exact fp32 path on an unaligned one); the data-parallel step stays within 4e-3 of the single-GPU gradients."""
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    import torch.multiprocessing as mp
+    out = str(tmp_path / "peer_bf16.pt")
+    mp.spawn(_worker, args=(2, 29651, out, True, "bf16"), nprocs=2, join=True)
+    r = torch.load(out)
+    if "unavailable" in r:
+        pytest.skip("symmetric memory unavailable on this box: " + r["unavailable"])
+    print(r)
+    if not r["multicast"]:
+        pytest.skip("no multicast mapping on this box: the bf16 wire is not used")
+    assert r["wire"] == "bf16"
+    for variant, e in r["kernel_max_abs_err"].items():  # fp32 calls on the same group are untouched
+        assert e < 1e-5, (variant, r)
+    assert r["wire_kernel_max_abs_err"] <= 0.04, r         # bf16(fp32 sum of the bf16 inputs) * 0.5, to one bf16 ulp of |x| <= 8
+    assert r["wire_kernel_rel"] < 4e-3, r
+    assert r["same"] and r["buckets"] >= 3
+    assert r["err"] < 4e-3, r
+    assert r["param_err_after_4_steps"] < 1e-3, r
 
 
 @pytest.mark.parametrize("in_graph", [True, False], ids=["in_graph", "callbacks"])
