@@ -60,7 +60,7 @@ def parse():
     ap.add_argument("--no-rooflines", action="store_true")
     ap.add_argument("--c4-dialogues", type=int, default=100000)
     ap.add_argument("--bucket-mb", type=float, default=None, help="gradient bucket size (default: 16 for the peer exchange, 128 for NCCL)")
-    ap.add_argument("--wire", default=None, choices=["fp32", "bf16"], help="wire format of the peer gradient exchange (default: bf16 for bf16 precision modes)")
+    ap.add_argument("--wire", default=None, choices=["fp32", "bf16"], help="wire format of the peer gradient exchange (default fp32)")
     ap.add_argument("--exchange", default=None, choices=["auto", "peer", "nccl"],
                     help="gradient exchange at N > 1: NVSwitch peer-memory kernel or NCCL buckets (default: $M2F_EXCHANGE or auto)")
     return ap.parse_args()

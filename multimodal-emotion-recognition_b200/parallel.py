@@ -83,13 +83,13 @@ class PeerGradExchange:
     M2F_EXCHANGE_IN_GRAPH=0 selects the callback mode."""
 
     def __init__(self, model, group=None, average: bool = True, ctas: int = 0, in_graph: Optional[bool] = None, wire: Optional[str] = None):
-        """`wire`: "fp32" or "bf16" (default: $M2F_EXCHANGE_WIRE, else bf16 when the model trains in a bf16 precision mode --
-        planes_bwd == 1 -- and fp32 for the fp32-parity modes).  bf16 halves the NVLink bytes of the exchange, which is
-        bandwidth-bound for the whole backward; the reduced gradient then carries two bf16 roundings (relative 2^-9)."""
+        """`wire`: "fp32" (default, or $M2F_EXCHANGE_WIRE) or "bf16".  bf16 halves the NVLink bytes of the exchange (the reduced
+        gradient then carries two bf16 roundings, relative 2^-9) at the price of a pack and an unpack pass over local memory:
+        measured on 2 x B200 it does not pay (profiles/r2_exchange_sweep_2gpu.txt), so it is opt-in."""
         import torch.distributed._symmetric_memory as symm_mem
 
         self.model = model
-        wire = (wire or os.environ.get("M2F_EXCHANGE_WIRE") or ("bf16" if getattr(model, "planes_bwd", 3) == 1 else "fp32")).lower()
+        wire = (wire or os.environ.get("M2F_EXCHANGE_WIRE") or "fp32").lower()
         if wire not in ("fp32", "bf16"):
             raise ValueError(f"exchange wire format must be fp32 or bf16, got {wire!r}")
         self.in_graph = (os.environ.get("M2F_EXCHANGE_IN_GRAPH", "1") != "0") if in_graph is None else bool(in_graph)

@@ -31,8 +31,8 @@ D = importlib.import_module("multimodal-emotion-recognition_b200.data")
 torch.cuda.set_device(local)
 dist.init_process_group("nccl", device_id=torch.device("cuda", local))
 torch.manual_seed(0)
-model = pkg.M2FNet(D.default_model_config(), planes=1).to("cuda").train()
-net = pkg.DataParallelM2FNet(model, bucket_mb=bucket_mb, exchange=exchange)
+model = pkg.M2FNet(D.default_model_config(), precision=os.environ.get("M2F_TRACE_PRECISION", "bf16x2f")).to("cuda").train()
+net = pkg.DataParallelM2FNet(model, bucket_mb=bucket_mb, exchange=exchange, wire=os.environ.get("M2F_TRACE_WIRE", "fp32"))
 crit = pkg.FusedCrossEntropyLoss().cuda()
 opt = pkg.FusedAdam(model, lr=5e-5, weight_decay=0.01)
 b = {k: v.cuda() for k, v in D.synth_batch(64, 33, 768, 768, seed=1234 + rank).items()}
