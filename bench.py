@@ -59,6 +59,7 @@ def parse():
     ap.add_argument("--no-context", action="store_true", help="skip the stock-PyTorch-eager-on-B200 context numbers")
     ap.add_argument("--no-rooflines", action="store_true")
     ap.add_argument("--c4-dialogues", type=int, default=100000)
+    ap.add_argument("--no-overlap-adam", action="store_true", help="data parallel: update in optimizer.step() only, not behind the exchange")
     ap.add_argument("--bucket-mb", type=float, default=None, help="gradient bucket size (default: 16 for the peer exchange, 128 for NCCL)")
     ap.add_argument("--wire", default=None, choices=["fp32", "bf16"], help="wire format of the peer gradient exchange (default fp32)")
     ap.add_argument("--exchange", default=None, choices=["auto", "peer", "nccl"],
@@ -339,7 +340,7 @@ def main():
         model = pkg.M2FNet(cfg, precision=precision).to(dev).train()
         net = pkg.DataParallelM2FNet(model, bucket_mb=args.bucket_mb, exchange=args.exchange, wire=args.wire) if dp else model
         crit = pkg.FusedCrossEntropyLoss().to(dev)
-        opt = pkg.FusedAdam(model, lr=5e-5, weight_decay=0.01)
+        opt = pkg.FusedAdam(model, lr=5e-5, weight_decay=0.01, overlap_exchange=not args.no_overlap_adam)
 
         def step(b):
             opt.zero_grad(set_to_none=True)
@@ -500,7 +501,9 @@ def describe_exchange(net):
     xchg_info["desc"] = ("gradient all-reduce: m2f_grad_allreduce_peer over NVSwitch " +
                          ("multicast (multimem.ld_reduce / multimem.st)" if getattr(net.reducer, "multicast", False) else "peer loads / stores")
                          if net.exchange == "peer" else "gradient all-reduce: NCCL, async buckets behind the backward")
-    xchg_info["cfg"] = {"bucket_mb": net.bucket_mb, "exchange_calls_per_step": getattr(net.reducer, "calls_per_step", len(net.reducer.log)),
+    xchg_info["cfg"] = {"optimizer_overlap": "Adam of each exchanged range enqueued by the backward behind its compute, gated by the next range's exchange"
+                                             if getattr(net.module, "_tail_opt", None) is not None else "optimizer.step() after the last exchange",
+                        "bucket_mb": net.bucket_mb, "exchange_calls_per_step": getattr(net.reducer, "calls_per_step", len(net.reducer.log)),
                         "exchange_wire": getattr(net.reducer, "wire", "fp32")}
     if net.exchange == "peer":
         xchg_info["cfg"]["exchange_launch"] = "kernels captured in the backward's CUDA graph" if net.reducer.in_graph else "bucket callbacks"
@@ -514,6 +517,8 @@ def verify_exchange(torch, dist, net, model, crit, b):
     roundings per element -- 4e-3)."""
     world = dist.get_world_size()
     saved_x, saved_hooks = model._exchange, (model._bucket_hook, model._bucket_floats, model._done_hook)
+    saved_opt = model._tail_opt
+    model.set_tail_optimizer(None)  # the check runs two backwards on the same weights: no updates in between
 
     def fwd_bwd(wrapper):
         model.zero_grad(set_to_none=True)
@@ -536,6 +541,8 @@ def verify_exchange(torch, dist, net, model, crit, b):
         model.set_exchange(*saved_x)
     model.set_grad_hooks(*saved_hooks)
     g_x = fwd_bwd(net)
+    if saved_opt is not None:
+        model.set_tail_optimizer(saved_opt)
     off = model._off_1d
     num2 = (g_x[:off].double() - ref[:off].double()).norm().item()
     den2 = ref[:off].double().norm().item()

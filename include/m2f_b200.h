@@ -305,6 +305,20 @@ int m2f_model_adam_step(const m2f_model_t* m, float* params, const float* grads,
                         void* shadow, float lr, float beta1, float beta2, float eps, float weight_decay, int64_t t,
                         float grad_scale, void* stream);
 
+/* The optimizer behind the exchange.  With an exchange attached (m2f_plan_set_exchange), what follows the backward's last
+ * kernel is the backlog of the exchange stream and then optimizer.step() (src/train.py:231) over the whole arena.  After
+ * m2f_plan_set_optimizer the backward itself enqueues the Adam update (and the refresh of the bf16 weight shadow) of every
+ * exchanged gradient range behind its compute, each gated only by the exchange call after its own -- so the update of the early
+ * ranges overlaps the exchange of the late ones -- all captured in the backward's CUDA graph; step() then only counts.  Same
+ * arithmetic, bit for bit, as m2f_model_adam_step after the backward.  The hyper-parameters live in device memory
+ * (M2F_ADAM_HYPER_FLOATS floats, 16-byte aligned) so that a replayed graph sees the current step count / learning rate: call
+ * m2f_adam_hyper on the same stream before each such backward (t = 1-based count of the update about to be applied).
+ * Without an exchange attached the setting has no effect.  exp_avg == NULL detaches. */
+#define M2F_ADAM_HYPER_FLOATS 8
+int m2f_plan_set_optimizer(m2f_plan_t* p, float* exp_avg, float* exp_avg_sq, const float* hyper_dev);
+int m2f_adam_hyper(float* hyper_dev, float lr, float beta1, float beta2, float eps, float weight_decay, int64_t t,
+                   float grad_scale, void* stream);
+
 /* ---- either side of the step ---------------------------------------------------
  * Batch assembly on the device, replacing Dataset.__getitem__ + collate_fn + apply_padding
  * (src/dataset.py:32-65,71-89; src/utils.py:15-31).  The embedding tables stay resident in HBM: text_table

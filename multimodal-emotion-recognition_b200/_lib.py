@@ -105,6 +105,8 @@ PROTOTYPES = {
     "m2f_exchange_tune": [_i32, _i32],
     "m2f_plan_set_exchange": [_vp, C.POINTER(PeerGroup), _f32, _i32],
     "m2f_plan_exchange_ranges": [_vp],
+    "m2f_plan_set_optimizer": [_vp, _vp, _vp, _vp],
+    "m2f_adam_hyper": [_vp, _f32, _f32, _f32, _f32, _f32, _i64, _f32, _vp],
     "m2f_adam_step": [_vp, _vp, _vp, _vp, _i64, _f32, _f32, _f32, _f32, _f32, _i64, _f32, _vp],
     "m2f_model_adam_step": [_vp, _vp, _vp, _vp, _vp, _vp, _f32, _f32, _f32, _f32, _f32, _i64, _f32, _vp],
     "m2f_collate_dialogues": [_vp, _i64, _i32, _vp, _i64, _i32, _vp, _vp, _vp, _vp, _i64, _i64, _vp, _vp, _vp, _vp, _vp],

@@ -225,13 +225,13 @@ struct m2f_plan {
     // CUDA graphs: the body of the forward / backward is captured once (on `cap`, with its forks onto aux[]) and replayed
     // into the caller's stream; whatever depends on per-call pointers (inputs, logits, dlogits) stays outside.
     struct GraphKey {
-        const void *params = nullptr, *shadow = nullptr, *ws = nullptr, *grads = nullptr;
+        const void *params = nullptr, *shadow = nullptr, *ws = nullptr, *grads = nullptr, *opt_m = nullptr;
         float p_used = -1.f;
         int flags = 0;
         int64_t bucket_floats = 0;
         bool operator==(const GraphKey& o) const {
-            return params == o.params && shadow == o.shadow && ws == o.ws && grads == o.grads && p_used == o.p_used && flags == o.flags &&
-                   bucket_floats == o.bucket_floats;
+            return params == o.params && shadow == o.shadow && ws == o.ws && grads == o.grads && opt_m == o.opt_m && p_used == o.p_used &&
+                   flags == o.flags && bucket_floats == o.bucket_floats;
         }
     };
     struct GraphSlot {
@@ -253,6 +253,12 @@ struct m2f_plan {
     float xchg_scale = 1.f;
     int xchg_ctas = 0;
     int64_t xchg_ranges = 0;                 // ranges exchanged by the last backward
+    // optimizer behind the exchange (m2f_plan_set_optimizer): once the backward's compute has finished, each exchanged gradient
+    // range is updated as soon as IT is final, while the exchange of the later ranges is still running
+    bool opt_on = false;
+    float *opt_m = nullptr, *opt_v = nullptr;
+    const float* opt_hp = nullptr;           // device: AdamArgs, rewritten by m2f_adam_hyper before each backward
+    std::vector<cudaEvent_t> xchg_evs;       // recorded on `ready` behind each exchange call
     cudaStream_t cap = nullptr;
     unsigned long long* rng_dev = nullptr;   // {seed, step} read by the dropout kernels of the captured graphs
     int use_graph = 1;
@@ -296,6 +302,8 @@ struct m2f_plan {
         bucket_evs.clear();
         for (auto& e : stack_evs) cudaEventDestroy(e);
         stack_evs.clear();
+        for (auto& e : xchg_evs) cudaEventDestroy(e);
+        xchg_evs.clear();
         if (rng_dev) { cudaFree(rng_dev); rng_dev = nullptr; }
         if (tl_dev) { cudaFree(tl_dev); tl_dev = nullptr; }
         if (cap) { cudaStreamDestroy(cap); cap = nullptr; }
@@ -549,9 +557,12 @@ __device__ __forceinline__ float adam_one(float& p, float g, float& m, float& v,
     p -= a.step_size * (m / denom);
     return p;
 }
+// `hp` (nullable): the hyper-parameters in device memory instead of the by-value copy -- what lets the update be captured into
+// the backward's CUDA graph and replayed with a new step count / learning rate (m2f_adam_hyper writes them before each launch).
 __global__ void __launch_bounds__(256)
 adam_shadow_kernel(float* __restrict__ params, const float* __restrict__ grads, float* __restrict__ em, float* __restrict__ ev,
-                   uint8_t* __restrict__ shadow, const ShadowBatch batch, const AdamArgs a) {
+                   uint8_t* __restrict__ shadow, const ShadowBatch batch, const AdamArgs a_val, const AdamArgs* __restrict__ hp) {
+    const AdamArgs a = hp ? *hp : a_val;
     const SEntry& e = batch.e[blockIdx.y];
     __nv_bfloat16* dst = reinterpret_cast<__nv_bfloat16*>(shadow + e.dst_off);
     if ((e.cols & 3) == 0 && (e.src_ld & 3) == 0 && (e.src_off & 3) == 0) {
@@ -587,6 +598,22 @@ adam_shadow_kernel(float* __restrict__ params, const float* __restrict__ grads, 
         }
     }
 }
+
+// the 1-D region (biases, LayerNorm vectors) with device-resident hyper-parameters: same arithmetic as adam_kernel (optim.cu)
+__global__ void __launch_bounds__(256)
+adam_range_kernel(float4* __restrict__ p, const float4* __restrict__ g, float4* __restrict__ m, float4* __restrict__ v, int64_t n4,
+                  const AdamArgs* __restrict__ hp) {
+    const AdamArgs a = *hp;
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n4; i += (int64_t)gridDim.x * blockDim.x) {
+        float4 pp = p[i], gg = g[i], mm = m[i], vv = v[i];
+        adam_one(pp.x, gg.x, mm.x, vv.x, a);
+        adam_one(pp.y, gg.y, mm.y, vv.y, a);
+        adam_one(pp.z, gg.z, mm.z, vv.z, a);
+        adam_one(pp.w, gg.w, mm.w, vv.w, a);
+        p[i] = pp; m[i] = mm; v[i] = vv;
+    }
+}
+__global__ void adam_hyper_kernel(AdamArgs* dst, const AdamArgs a) { *dst = a; }
 
 // ------------------------------------------------------------------------------------------ execution context
 __global__ void timeline_stamp_kernel(unsigned long long* slot) {
@@ -699,6 +726,15 @@ struct Ctx {
                                             (last ? 0 : M2F_XCHG_NO_EXIT_BARRIER) | (p->xchg_group.wire_bf16 ? M2F_XCHG_WIRE_BF16 : 0), ready));
             ++p->xchg_ranges;
             if (ready != st) ready_in_capture = true;
+            if (tail_adam) {
+                while (p->xchg_evs.size() < xranges.size() + 1) {
+                    cudaEvent_t e;
+                    M2F_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+                    p->xchg_evs.push_back(e);
+                }
+                M2F_CUDA(cudaEventRecord(p->xchg_evs[xranges.size()], ready));
+                xranges.emplace_back(lo, hi_);
+            }
             return M2F_OK;
         }
         if (!marks) {
@@ -714,6 +750,70 @@ struct Ctx {
         marks->emplace_back(lo, hi_);
         if (ready != st) ready_in_capture = true;
         return M2F_OK;
+    }
+
+    // ---- optimizer behind the exchange.  With an exchange attached, what is left behind the backward's last kernel is the
+    // backlog of the exchange stream (the last few 21 MB ranges, ~0.3 ms at C2), and after it optimizer.step() streams the whole
+    // arena (~0.5 ms).  Here the update of range k is enqueued on the caller's stream -- behind ALL of the backward's compute, so
+    // nothing reads the weights any more and no GEMM competes for L2 -- gated only by the event behind exchange call k + 1: a
+    // later call's entry barrier proves that every rank has completed call k (stores included), so range k is final here while
+    // the calls after it are still in flight; the step's last call closes with its own handshake.  Same arithmetic, bit for
+    // bit, as m2f_model_adam_step after the backward.
+    bool tail_adam = false;
+    std::vector<std::pair<int64_t, int64_t>> xranges;
+    int adam_tail() {
+        const size_t n = xranges.size();
+        for (size_t k = 0; k < n; ++k) {
+            cudaEvent_t gate = p->xchg_evs[k + 1 < n ? k + 1 : n - 1];
+            if (p->use_streams) M2F_CUDA(cudaStreamWaitEvent(st, gate, 0));
+            M2F_TRY(adam_range(xranges[k].first, xranges[k].second, st));
+        }
+        return M2F_OK;
+    }
+    int adam_range(int64_t lo, int64_t hi_, cudaStream_t ast) {
+        m2f_model* md = p->m;
+        const AdamArgs* hp = reinterpret_cast<const AdamArgs*>(p->opt_hp);
+        float* prm_w = const_cast<float*>(params);
+        if (lo >= md->off_1d) {  // biases / LayerNorm vectors, then their packed fp32 copies in the shadow
+            const int64_t n4 = (hi_ - lo) / 4;
+            int64_t g = (n4 + 255) / 256;
+            if (g > 148 * 8) g = 148 * 8;
+            adam_range_kernel<<<(unsigned)g, 256, 0, ast>>>(reinterpret_cast<float4*>(prm_w + lo), reinterpret_cast<const float4*>(grads + lo),
+                                                           reinterpret_cast<float4*>(p->opt_m + lo), reinterpret_cast<float4*>(p->opt_v + lo), n4, hp);
+            M2F_LAUNCH_CHECK();
+            ShadowBatch b;
+            b.n = 0;
+            for (const SEntry& e : md->sentries) {
+                if (e.planes != 0) continue;
+                b.e[b.n++] = e;
+                if (b.n == SHADOW_CHUNK) {
+                    shadow_refresh_kernel<<<dim3(4, b.n), 256, 0, ast>>>(params, shadow, b);
+                    M2F_LAUNCH_CHECK();
+                    b.n = 0;
+                }
+            }
+            if (b.n) {
+                shadow_refresh_kernel<<<dim3(4, b.n), 256, 0, ast>>>(params, shadow, b);
+                M2F_LAUNCH_CHECK();
+            }
+            return M2F_OK;
+        }
+        ShadowBatch b;
+        b.n = 0;
+        const AdamArgs unused{};
+        auto flush = [&]() -> int {
+            if (b.n == 0) return M2F_OK;
+            adam_shadow_kernel<<<dim3(96, b.n), 256, 0, ast>>>(prm_w, grads, p->opt_m, p->opt_v, shadow, b, unused, hp);
+            M2F_LAUNCH_CHECK();
+            b.n = 0;
+            return M2F_OK;
+        };
+        for (const SEntry& e : md->sentries) {
+            if (e.planes == 0 || e.src_off < lo || e.src_off >= hi_) continue;
+            b.e[b.n++] = e;
+            if (b.n == SHADOW_CHUNK) M2F_TRY(flush());
+        }
+        return flush();
     }
 
     m2f_planes_t pv(const Buf& b) const {
@@ -1216,6 +1316,7 @@ static int backward_all(Ctx& c, const uint8_t* key_pad, const float* dlogits, in
         cudaStream_t ready = p->use_streams ? p->ready : c.st;
         M2F_TRY(c.dep(c.st, ready));
         M2F_TRY(c.report(md->off_1d, md->arena_floats, ready, true));
+        if (c.tail_adam) M2F_TRY(c.adam_tail());  // range by range behind the exchange, on the caller's stream
         // a capture must end with every forked stream joined; with the exchange inside the backward the caller's stream
         // continues (optimizer) only after the last range has been exchanged
         if ((c.marks || c.xchg) && c.ready_in_capture) M2F_TRY(c.dep(ready, c.st));
@@ -1288,7 +1389,7 @@ extern "C" int m2f_model_adam_step(const m2f_model_t* m, float* params, const fl
     b.n = 0;
     auto flush = [&]() -> int {
         if (b.n == 0) return M2F_OK;
-        adam_shadow_kernel<<<dim3(96, b.n), 256, 0, st>>>(params, grads, exp_avg, exp_avg_sq, reinterpret_cast<uint8_t*>(shadow), b, a);
+        adam_shadow_kernel<<<dim3(96, b.n), 256, 0, st>>>(params, grads, exp_avg, exp_avg_sq, reinterpret_cast<uint8_t*>(shadow), b, a, nullptr);
         M2F_LAUNCH_CHECK();
         b.n = 0;
         return M2F_OK;
@@ -1584,6 +1685,35 @@ extern "C" int m2f_plan_set_exchange(m2f_plan_t* p, const m2f_peer_group_t* grou
 
 extern "C" int64_t m2f_plan_exchange_ranges(const m2f_plan_t* p) { return p ? p->xchg_ranges : 0; }
 
+extern "C" int m2f_plan_set_optimizer(m2f_plan_t* p, float* exp_avg, float* exp_avg_sq, const float* hyper_dev) {
+    M2F_REQUIRE(p, M2F_ERR_ARG, "plan_set_optimizer: plan is NULL");
+    p->gb.reset();  // the captured backward embeds (or lacks) the update kernels
+    if (!exp_avg) {
+        p->opt_on = false;
+        return M2F_OK;
+    }
+    M2F_REQUIRE(exp_avg_sq && hyper_dev, M2F_ERR_ARG, "plan_set_optimizer: null argument");
+    M2F_REQUIRE(((reinterpret_cast<uintptr_t>(exp_avg) | reinterpret_cast<uintptr_t>(exp_avg_sq) | reinterpret_cast<uintptr_t>(hyper_dev)) % 16) == 0,
+                M2F_ERR_ALIGN, "plan_set_optimizer: state and hyper-parameter buffers must be 16-byte aligned");
+    M2F_REQUIRE(p->training, M2F_ERR_ARG, "plan_set_optimizer: needs a training plan");
+    p->opt_m = exp_avg;
+    p->opt_v = exp_avg_sq;
+    p->opt_hp = hyper_dev;
+    p->opt_on = true;
+    return M2F_OK;
+}
+
+extern "C" int m2f_adam_hyper(float* hyper_dev, float lr, float beta1, float beta2, float eps, float weight_decay, int64_t t,
+                              float grad_scale, void* stream) {
+    M2F_REQUIRE(hyper_dev && t >= 1, M2F_ERR_ARG, "adam_hyper: bad argument");
+    static_assert(sizeof(AdamArgs) <= M2F_ADAM_HYPER_FLOATS * sizeof(float), "hyper-parameter block too small");
+    const double bc1 = 1.0 - pow((double)beta1, (double)t), bc2 = 1.0 - pow((double)beta2, (double)t);
+    const AdamArgs a{beta1, beta2, eps, weight_decay, (float)((double)lr / bc1), (float)(1.0 / sqrt(bc2)), grad_scale};
+    adam_hyper_kernel<<<1, 1, 0, reinterpret_cast<cudaStream_t>(stream)>>>(reinterpret_cast<AdamArgs*>(hyper_dev), a);
+    M2F_LAUNCH_CHECK();
+    return M2F_OK;
+}
+
 extern "C" int m2f_plan_backward_bucketed(m2f_plan_t* p, const float* params, const void* shadow, void* workspace,
                                           const float* dlogits, float* grads, int64_t bucket_floats, m2f_bucket_cb cb, void* user,
                                           void* stream) {
@@ -1600,6 +1730,7 @@ extern "C" int m2f_plan_backward_bucketed(m2f_plan_t* p, const float* params, co
     c.cb_user = user;
     c.hi = p->m->off_1d;
     c.xchg = !cb && bucket_floats > 0 && p->xchg_on;
+    c.tail_adam = c.xchg && p->opt_on;
     if (c.xchg) {
         M2F_REQUIRE(grads == p->xchg_group.peer_base[p->xchg_group.rank], M2F_ERR_ARG,
                     "plan_backward: with an exchange attached the gradients must be written to this rank's copy of the symmetric buffer");
@@ -1616,7 +1747,8 @@ extern "C" int m2f_plan_backward_bucketed(m2f_plan_t* p, const float* params, co
         M2F_TRY(backward_all(c, kp, dlogits, PH_HEAD));
         m2f_plan::GraphKey key;
         key.params = params; key.shadow = shadow; key.ws = workspace; key.grads = grads; key.p_used = p->p_used;
-        key.flags = cb ? 1 : (c.xchg ? 2 : 0);
+        key.flags = (cb ? 1 : (c.xchg ? 2 : 0)) | (c.tail_adam ? 4 : 0);
+        key.opt_m = c.tail_adam ? p->opt_m : nullptr;
         key.bucket_floats = (cb || c.xchg) ? c.bucket_floats : 0;
         std::vector<std::pair<int64_t, int64_t>> marks;
         bool captured = false;

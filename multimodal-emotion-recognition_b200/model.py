@@ -87,6 +87,8 @@ class _Plan:
         self.token = 0  # bumped by every forward; a backward must match the forward that filled the workspace
         if training and model._exchange is not None:
             model._attach_exchange(self)
+        if training and model._tail_opt is not None:
+            model._attach_optimizer(self)
 
     def destroy(self):
         if self.handle:
@@ -183,6 +185,7 @@ class M2FNet(nn.Module):
         self._anchor_box = [None]  # in a list: assigning a Parameter as an attribute would register it under that name
         self._grad_arena: Optional[torch.Tensor] = None
         self._exchange = None            # (PeerGroup, scale, ctas, bucket_floats): gradient exchange inside the backward
+        self._tail_opt = None            # FusedAdam(overlap_exchange=True): the update of each exchanged range runs behind the backward
         self._grad_views = None          # p.grad views into the gradient arena, built once
         self._grads_cleared = False      # FusedAdam.zero_grad(): views still attached, contents dead
         self._shadow: Optional[torch.Tensor] = None
@@ -328,15 +331,20 @@ class M2FNet(nn.Module):
         if self._grad_views is None:
             self._grad_views = [self._grad_arena[o:o + n].view(p.shape) for p, o, n in self._flat]
         target = self._grad_arena if fresh else torch.empty_like(self._grad_arena)
+        tail = self._tail_opt if self._exchange is not None else None
         if self._exchange is not None:
             if not fresh:
                 raise RuntimeError("data-parallel M2FNet needs zero_grad(set_to_none=True) (gradient accumulation across "
                                    "backwards is not supported with the in-backward gradient exchange)")
+            if tail is not None:
+                tail._before_backward()
             # every finished range is all-reduced by kernels inside the backward's graph; nothing to do per range on the host
             _lib.check(_lib.lib().m2f_plan_backward_bucketed(plan.handle, self._arena.data_ptr(), self._shadow.data_ptr(),
                                                              plan.ws.data_ptr(), dlogits.data_ptr(), target.data_ptr(),
                                                              int(self._exchange[3]), None, None, _stream()), "plan_backward (exchange)")
             self.exchange_ranges = int(_lib.lib().m2f_plan_exchange_ranges(plan.handle))
+            if tail is not None:
+                tail._applied = True  # the parameters (and the bf16 shadow) have been updated by this backward
         elif self._bucket_hook is not None and fresh:
             errors = []
 
@@ -445,6 +453,21 @@ class M2FNet(nn.Module):
                     _lib.check(_lib.lib().m2f_plan_set_exchange(pl.handle, None, 1.0, 0), "plan_set_exchange")
                 else:
                     self._attach_exchange(pl)
+
+    def _attach_optimizer(self, plan: "_Plan"):
+        o = self._tail_opt
+        _lib.check(_lib.lib().m2f_plan_set_optimizer(plan.handle, o._m.data_ptr(), o._v.data_ptr(), o._hp.data_ptr()), "plan_set_optimizer")
+
+    def set_tail_optimizer(self, opt):
+        """Attach (or with None detach) a FusedAdam whose update runs behind the backward's gradient exchange
+        (m2f_plan_set_optimizer); it only takes effect while an in-graph exchange is attached."""
+        self._tail_opt = opt
+        for pl in self._plans.values():
+            if pl.training and pl.handle:
+                if opt is None:
+                    _lib.check(_lib.lib().m2f_plan_set_optimizer(pl.handle, None, None, None), "plan_set_optimizer")
+                else:
+                    self._attach_optimizer(pl)
 
     def adopt_grad_arena(self, buf: Optional[torch.Tensor]):
         """Make the backward write its gradients into `buf` (fp32, arena_floats elements, on the model's device) -- the

@@ -11,13 +11,39 @@ from . import _lib
 
 
 class FusedAdam(torch.optim.Optimizer):
-    def __init__(self, model, lr=1e-3, betas=(0.9, 0.999), eps=1e-8, weight_decay=0.0, grad_scale: float = 1.0):
+    def __init__(self, model, lr=1e-3, betas=(0.9, 0.999), eps=1e-8, weight_decay=0.0, grad_scale: float = 1.0,
+                 overlap_exchange: bool = True):
+        """`overlap_exchange` (data parallel with the in-graph peer exchange only; no effect otherwise): the update of every
+        exchanged gradient range is enqueued by `loss.backward()` itself, behind the backward's compute and gated by the
+        exchange of the NEXT range, so that it overlaps the tail of the exchange instead of waiting for all of it
+        (m2f_plan_set_optimizer); `step()` then only advances the step count.  Bit-identical results.  What it asks of the
+        caller: every backward() is followed by one step() before the next forward (the reference's loop, src/train.py:228-231);
+        a second backward() without step() raises.  The learning rate of `param_groups[0]` is read at each backward."""
         self.model = getattr(model, "module", model)
         params = [p for p, _, _ in self.model._flat]
         super().__init__(params, dict(lr=lr, betas=betas, eps=eps, weight_decay=weight_decay))
         self.grad_scale = float(grad_scale)
         self._t = 0
+        self._applied = False
         self._bind()
+        self.overlap_exchange = bool(overlap_exchange)
+        if self.overlap_exchange:
+            self._hp = torch.zeros(8, dtype=torch.float32, device=self.model.flat_parameters().device)  # M2F_ADAM_HYPER_FLOATS
+            self.model.set_tail_optimizer(self)
+
+    def _before_backward(self):
+        if self._applied:
+            raise RuntimeError("FusedAdam(overlap_exchange=True): backward() ran twice without step() in between -- the first "
+                               "backward has already applied its update")
+        grp = self.param_groups[0]
+        _lib.check(_lib.lib().m2f_adam_hyper(self._hp.data_ptr(), float(grp["lr"]), float(grp["betas"][0]), float(grp["betas"][1]),
+                                             float(grp["eps"]), float(grp["weight_decay"]), self._t + 1, self.grad_scale,
+                                             torch.cuda.current_stream().cuda_stream), "adam_hyper")
+
+    def detach_from_backward(self):
+        """Back to updating in step() only."""
+        self.model.set_tail_optimizer(None)
+        self.overlap_exchange = False
 
     def _bind(self):
         arena = self.model.flat_parameters()
@@ -35,6 +61,10 @@ class FusedAdam(torch.optim.Optimizer):
         g = self.model.flat_grads()
         if g is None:
             raise RuntimeError("FusedAdam.step(): no gradients (call backward first)")
+        if self._applied:  # the backward has already applied this update behind its gradient exchange
+            self._applied = False
+            self._t += 1
+            return loss
         grp = self.param_groups[0]
         self._t += 1
         arena = self.model.flat_parameters()

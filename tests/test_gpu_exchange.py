@@ -225,3 +225,118 @@ def test_dp2_peer_exchange_equals_single_gpu(tmp_path, in_graph):
     assert r["same"] and r["buckets"] >= 3
     assert r["err"] < 2e-5, r
     assert r["param_err_after_4_steps"] < 1e-5, r
+
+
+def _train_steps(pkg, cfg, steps, exchange_world1, overlap, graph, bucket_floats=20000, B=5, S=9):
+    """A few full training steps; with `exchange_world1` the gradient arena sits in a buffer with barrier words and a world-1
+    peer group is attached, so the backward runs its in-graph exchange calls (in-place scale by 1) -- the single-GPU stand-in
+    for the data-parallel path."""
+    from oracle import m2fnet_oracle as O
+    os.environ["M2F_GRAPH"] = graph
+    L = pkg._lib
+    params = O.synth_params(cfg)
+    model = pkg.M2FNet(cfg, precision="bf16x2f")
+    model.load_state_dict({k: v.float() for k, v in params.items()}, strict=True)
+    model = model.to("cuda").train()
+    model._seed = 4321
+    keep = None
+    if exchange_world1:
+        n = model.flat_parameters().numel()
+        sig = (n * 4 + 127) // 128 * 128
+        keep = torch.zeros((sig + L.XCHG_SIGNAL_BYTES) // 4, device="cuda")
+        pg = L.PeerGroup()
+        pg.mc_base = None
+        pg.peer_base[0] = keep.data_ptr()
+        pg.signal_off_bytes = sig
+        pg.rank, pg.world = 0, 1
+        model.adopt_grad_arena(keep[:n])
+        model.set_exchange(pg, 1.0, 0, bucket_floats)
+    crit = pkg.FusedCrossEntropyLoss().cuda()
+    opt = pkg.FusedAdam(model, lr=2e-4, weight_decay=0.01, overlap_exchange=overlap)
+    losses, first = [], None
+    for i in range(steps):
+        b = O.synth_inputs(B, S, cfg.TEXT.embedding_size, cfg.AUDIO.embedding_size)
+        opt.param_groups[0]["lr"] = 2e-4 / (i + 1)
+        opt.zero_grad(set_to_none=True)
+        out = model(b["text"].cuda() * (1 + 0.1 * i), b["audio"].cuda(), b["padding_mask"].cuda())
+        loss = crit(out.permute(0, 2, 1), b["emotion"].cuda())
+        loss.backward()
+        applied = opt._applied
+        opt.step()
+        losses.append(loss.item())
+        if i == 0:
+            torch.cuda.synchronize()
+            first = dict(params=model.flat_parameters().clone(), m=opt._m.clone(), v=opt._v.clone(), shadow=model._shadow.clone())
+    torch.cuda.synchronize()
+    os.environ.pop("M2F_GRAPH", None)
+    return dict(params=model.flat_parameters().clone(), m=opt._m.clone(), v=opt._v.clone(), shadow=model._shadow.clone(), losses=losses,
+                applied=applied, t=opt._t, ranges=getattr(model, "exchange_ranges", 0), model=model, opt=opt, keep=keep, first=first,
+                off_1d=model._off_1d)
+
+
+@pytest.mark.parametrize("graph", ["1", "0"])
+@pytest.mark.parametrize("name", ["both_fam", "meld_dims"])
+def test_update_behind_the_exchange_is_bit_identical(name, graph):
+    """FusedAdam(overlap_exchange=True) with an in-graph exchange attached: the backward enqueues the Adam update of every
+    exchanged range itself (m2f_plan_set_optimizer).  It must be the same update as the ordinary backward-then-step() path: bit
+    for bit on the 2-D weights, their moments and the bf16 shadow after the first step, and the same trajectory after four steps
+    with dropout and a changing learning rate."""
+    from oracle import m2fnet_oracle as O
+    pkg = _pkg()
+    over = {"both_fam": dict(AUDIO=dict(embedding_size=64, n_head=4, n_encoder_layers=3), TEXT=dict(embedding_size=128, n_head=4, n_encoder_layers=3),
+                             FAM=dict(embedding_size=64, n_head=4, n_layers=3), CLASSIFIER=dict(hidden_size=64, output_size=7, n_layers=2)),
+            "meld_dims": dict(AUDIO=dict(n_encoder_layers=2), TEXT=dict(n_encoder_layers=2), FAM=dict(n_layers=2))}[name]
+    cfg = O.default_model_cfg(dropout=0.4, **over)
+    bf = 20000 if name == "both_fam" else 2 << 20
+    B, S = (5, 9) if name == "both_fam" else (4, 33)
+    plain = _train_steps(pkg, cfg, 4, False, False, graph, bf, B, S)
+    xchg = _train_steps(pkg, cfg, 4, True, False, graph, bf, B, S)    # exchange calls in the backward, update in step()
+    tail = _train_steps(pkg, cfg, 4, True, True, graph, bf, B, S)     # ... and the update behind the exchange
+    assert not plain["applied"] and not xchg["applied"] and tail["applied"]
+    assert tail["ranges"] >= 4 and xchg["ranges"] == tail["ranges"]
+    assert plain["t"] == xchg["t"] == tail["t"] == 4
+    off = plain["off_1d"]
+    rel = lambda a, b: (torch.linalg.vector_norm(a.double() - b.double()) / torch.linalg.vector_norm(b.double())).item()
+    for other in (xchg, tail):
+        # After the first step: the 2-D weights, their moments and the bf16 shadow are bit-identical (their gradients are written
+        # by one tile each, deterministically).  The 1-D gradients (biases, LayerNorm) are accumulated with atomics, so two runs
+        # of the SAME path already differ in their last bits there -- and Adam's first step turns a gradient that is pure
+        # rounding noise (the key bias of an attention, whose true gradient is 0) into +-lr: only a loose bound holds for them.
+        assert other["losses"][0] == plain["losses"][0]
+        for k in ("params", "m", "v"):
+            assert torch.equal(other["first"][k][:off], plain["first"][k][:off]), k
+        assert rel(other["first"]["params"][off:], plain["first"]["params"][off:]) < 1e-2
+        assert (other["first"]["shadow"] != plain["first"]["shadow"]).float().mean().item() < 1e-3
+        # after four steps (changing learning rate, dropout): the same trajectory, up to what the +-lr noise on the
+        # zero-gradient biases does to later forwards (two runs of the ordinary path differ by as much)
+        assert rel(other["params"][:off], plain["params"][:off]) < 1e-3
+        for k in ("m", "v"):
+            assert rel(other[k][:off], plain[k][:off]) < 1e-1, (k, rel(other[k][:off], plain[k][:off]))
+        assert max(abs(a - b) / abs(b) for a, b in zip(other["losses"], plain["losses"])) < 1e-2
+
+
+def test_update_behind_the_exchange_misuse():
+    from oracle import m2fnet_oracle as O
+    pkg = _pkg()
+    cfg = O.default_model_cfg(dropout=0.0, AUDIO=dict(embedding_size=64, n_head=4, n_encoder_layers=1), TEXT=dict(embedding_size=64, n_head=4, n_encoder_layers=1),
+                              FAM=dict(embedding_size=64, n_head=4, n_layers=1), CLASSIFIER=dict(hidden_size=64, output_size=7, n_layers=2))
+    r = _train_steps(pkg, cfg, 1, True, True, "1")
+    model, opt = r["model"], r["opt"]
+    b = O.synth_inputs(5, 9, 64, 64)
+    crit = pkg.FusedCrossEntropyLoss().cuda()
+    fwd = lambda: crit(model(b["text"].cuda(), b["audio"].cuda(), b["padding_mask"].cuda()).permute(0, 2, 1), b["emotion"].cuda())
+    opt.zero_grad(set_to_none=True)
+    fwd().backward()
+    with pytest.raises(RuntimeError, match="twice without step"):
+        opt.zero_grad(set_to_none=True)
+        fwd().backward()
+    opt.step()
+    opt.detach_from_backward()  # update in step() again
+    before = model.flat_parameters().clone()
+    opt.zero_grad(set_to_none=True)
+    fwd().backward()
+    torch.cuda.synchronize()
+    assert torch.equal(before, model.flat_parameters())
+    opt.step()
+    torch.cuda.synchronize()
+    assert not torch.equal(before, model.flat_parameters())
