@@ -238,7 +238,9 @@ class DataParallelM2FNet(torch.nn.Module):
             self.reducer = GradBucketReducer(model.flat_grads, group, average)
         self.exchange = "peer" if isinstance(self.reducer, PeerGradExchange) else "nccl"
         if bucket_mb is None:  # NCCL kernels compete for SMs: few large buckets; the peer kernel is light: finer overlap
-            bucket_mb = 16.0 if self.exchange == "peer" else 128.0
+            # peer: 32 MB ranges (9 calls per step at the default config) measured best once the optimizer update runs behind the
+            # exchange (profiles/r2_exchange_sweep_2gpu.txt: 16 MB 4.19 ms, 32 MB 4.02 ms, 8 MB 4.22 ms at 2 GPUs)
+            bucket_mb = 32.0 if self.exchange == "peer" else 128.0
         self.bucket_mb = float(bucket_mb)
         model.set_grad_hooks(self._on_bucket, int(self.bucket_mb * (1 << 20) / 4), self.reducer.finish)
         if self.exchange == "peer":
