@@ -159,6 +159,19 @@ int m2f_ce_fwd_bwd(const float* logits, int64_t ld, const int64_t* target, const
                    int64_t M, int32_t C, float eps, float grad_scale, float* loss_out,
                    float* dlogits, int64_t dl_ld, const m2f_planes_t* dl_planes, void* stream);
 
+/* ---- K4s: the same cross entropy for callers that cannot allocate.  No counterpart in the reference: added
+ * (code under CUDA graph capture, serving loops and harnesses that forbid cudaMalloc).
+ * Arguments as m2f_ce_fwd_bwd, except that loss_out is 2 floats of pure OUTPUT (loss_out[0] = loss, loss_out[1] = sum
+ * of weights over valid rows) and nothing the caller passes is used as scratch: the running sums and one log-sum-exp
+ * per row live in a file-scope device array of the library (about 1 MB, held by every GPU that loads the library until
+ * the process exits).  Limit: M <= M2F_CE_STATIC_MAX_ROWS, beyond it M2F_ERR_UNSUPPORTED.  The call performs no
+ * cudaMalloc / cudaFree.  All calls on one device share the array (it keeps the last call's contents; what must start
+ * at zero is cleared on `stream` at the start of the call): calls that overlap on the GPU race -- serialise them. */
+#define M2F_CE_STATIC_MAX_ROWS 262144
+int m2f_ce_fwd_bwd_static(const float* logits, int64_t ld, const int64_t* target, const float* class_w,
+                          int64_t M, int32_t C, float eps, float grad_scale, float* loss_out,
+                          float* dlogits, int64_t dl_ld, const m2f_planes_t* dl_planes, void* stream);
+
 
 /* ---- model-level API: the whole M2FNet forward / backward as one call each ------------------------------
  * m2f_model_cfg_t mirrors the `model:` block of src/config.yaml:31-56 (what M2FNet.__init__ reads,

@@ -84,6 +84,7 @@ PROTOTYPES = {
     "m2f_attn_fwd": [PP, PP, PP, _vp, _i64, _i64, _i32, _f32, _u64, _u64, _u32, PP, _vp],
     "m2f_attn_bwd": [PP, PP, PP, PP, _vp, _i64, _i64, _i32, _f32, _u64, _u64, _u32, PP, PP, PP, _vp, _vp, _vp, _vp],
     "m2f_ce_fwd_bwd": [_vp, _i64, _vp, _vp, _i64, _i32, _f32, _f32, _vp, _vp, _i64, PP, _vp],
+    "m2f_ce_fwd_bwd_static": [_vp, _i64, _vp, _vp, _i64, _i32, _f32, _f32, _vp, _vp, _i64, PP, _vp],
     "m2f_dropout_mask": [_f32, _u64, _u64, _u32, _i64, _vp, _vp],
     "m2f_model_create": [C.POINTER(ModelCfg), C.POINTER(_vp)],
     "m2f_model_destroy": [_vp],

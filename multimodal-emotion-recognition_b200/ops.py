@@ -162,6 +162,23 @@ def ce_fwd_bwd(logits: torch.Tensor, target: torch.Tensor, class_w: Optional[tor
     return out
 
 
+def ce_fwd_bwd_static(logits: torch.Tensor, target: torch.Tensor, out: torch.Tensor, class_w: Optional[torch.Tensor] = None,
+                      eps: float = 0.1, grad_scale: float = 1.0, dlogits: Optional[torch.Tensor] = None,
+                      dl_planes: Optional[PlanesTensor] = None) -> torch.Tensor:
+    """m2f_ce_fwd_bwd_static: the allocation-free cross entropy.  `out` (2 floats, device) is the caller's: [loss, sum of
+    weights]; this wrapper allocates nothing either.  M <= M2F_CE_STATIC_MAX_ROWS; calls sharing a GPU must not overlap."""
+    _need_cuda(logits, target, out, class_w, dlogits)
+    M, Cc = logits.shape
+    assert target.dtype == torch.int64 and target.is_contiguous()
+    assert out.dtype == torch.float32 and out.numel() >= 2 and out.is_contiguous()
+    dp = dl_planes.c() if dl_planes is not None else Planes()
+    _lib.check(_lib.lib().m2f_ce_fwd_bwd_static(logits.data_ptr(), logits.stride(0), target.data_ptr(), _ptr(class_w), M, Cc, eps,
+                                                grad_scale, out.data_ptr(), _ptr(dlogits),
+                                                dlogits.stride(0) if dlogits is not None else 0, C.byref(dp), _stream()),
+               "ce_fwd_bwd_static")
+    return out
+
+
 def dropout_mask(p: float, seed: int, step: int, site: int, n: int, device) -> torch.Tensor:
     m = torch.empty(n, dtype=torch.uint8, device=device)
     _need_cuda(m)
