@@ -255,12 +255,16 @@ def mha(q_in, k_in, v_in, W, b, Wo, bo, H, keymask, site=None, drop_masks=None, 
 
 
 def forward(params: Dict[str, torch.Tensor], cfg, text, audio, mask,
-            drop_masks=None, p: float = 0.0, relu_taps: Optional[dict] = None) -> torch.Tensor:
+            drop_masks=None, p: float = 0.0, relu_taps: Optional[dict] = None, relu_force=None) -> torch.Tensor:
     """M2FNet.forward restated (model.py:102-145).  text [B,S,Dt], audio [B,S,Da],
     mask [B,S] bool (True = padding).  `p = 0` or `drop_masks is None` => eval().
     `relu_taps` (a dict) receives, per ReLU site, the smallest |pre-activation| over the valid rows relative to the
     site's rms: how close the nearest ReLU gate is to flipping (SURVEY.md G15 -- a gate within the forward's rounding
-    error of zero makes the gradients of two correct implementations differ by O(1 / sqrt(rows x width)))."""
+    error of zero makes the gradients of two correct implementations differ by O(1 / sqrt(rows x width))).
+    `relu_force = (tau, "open" | "closed")` evaluates the network with every gate whose |pre-activation| is below tau x the
+    site's rms forced to pass / to block its gradient (the forward value moves by < tau x rms): the gradients of the two
+    settings bracket what any correct implementation with forward error < tau can return (tests use the spread as the G15
+    allowance on top of the fixed tolerance)."""
     g = lambda n: params[canonical_name(n)]
     dm = drop_masks
 
@@ -269,6 +273,12 @@ def forward(params: Dict[str, torch.Tensor], cfg, text, audio, mask,
             zv = z.detach()[~mask]
             nz = zv.abs()[zv != 0]  # exact zeros were produced by an earlier ReLU (the text half of a fusion concat): no gate to flip
             relu_taps[site_name] = float(nz.min() / zv.pow(2).mean().sqrt())
+        if relu_force is not None:
+            tau, how = relu_force
+            zd = z.detach()
+            rms = zd[~mask].pow(2).mean().sqrt()
+            risk = (zd.abs() < tau * rms) & (zd != 0)
+            return torch.where(risk, z if how == "open" else z * 0.0, torch.relu(z))
         return torch.relu(z)
 
     def modality(x, mod, mc):
@@ -342,7 +352,7 @@ def ce_loss(logits, target, weight=None, eps: float = 0.1, ignore_index: int = -
 
 
 def loss_and_grads(params, cfg, text, audio, mask, target, weight=None,
-                   drop_masks=None, p: float = 0.0):
+                   drop_masks=None, p: float = 0.0, relu_force=None):
     """Returns (logits, loss, {canonical param name: grad}).  Shared-norm aliases
     accumulate into the t = 0 entry, as autograd does for the reference."""
     leaves = {}
@@ -350,7 +360,7 @@ def loss_and_grads(params, cfg, text, audio, mask, target, weight=None,
         ck = canonical_name(k)
         if ck not in leaves:
             leaves[ck] = params[ck].detach().clone().requires_grad_(True)
-    logits = forward(leaves, cfg, text, audio, mask, drop_masks, p)
+    logits = forward(leaves, cfg, text, audio, mask, drop_masks, p, relu_force=relu_force)
     loss = ce_loss(logits, target, weight)
     names = list(leaves.keys())
     grads = torch.autograd.grad(loss, [leaves[n] for n in names], allow_unused=True)
