@@ -229,20 +229,21 @@ __device__ __forceinline__ uint64_t key_valid_bits(const uint8_t* pad, int S, in
 }
 
 // Dropout keep-bits of this thread's probabilities.  Element (query i, key j) of (dialogue, head) `bh` is element
-// (bh*S + i)*S8 + j of the site (S8 = S rounded up to 8), so the two columns a thread owns in an 8-wide tile share one
-// Philox call.  Bit (nt*2 + rowsel)*2 + c  <->  accumulator element [nt][rowsel*2 + c].  Rolled: one Philox body.
+// (bh*S + i)*S8 + j of the site (S8 = S rounded up to 8), so an 8-wide tile row is exactly one Philox call (eight 16-bit
+// lanes) and the two columns 2q, 2q+1 a thread owns are the two halves of word q.
+// Bit (nt*2 + rowsel)*2 + c  <->  accumulator element [nt][rowsel*2 + c].  Rolled: one Philox body.
 template <int SP>
 __device__ __forceinline__ uint32_t drop_bits(const Drop& d, uint64_t bh, int S, int i0, int lane) {
     const int g = lane >> 2, q = lane & 3;
-    const uint64_t s8q = (uint64_t)((S + 7) >> 3) * 2;  // S8 / 4
+    const uint64_t s8o = (uint64_t)((S + 7) >> 3);  // S8 / 8
     uint32_t bits = 0;
 #pragma unroll 1
     for (int e = 0; e < 2 * (SP / 8); ++e) {
         const int i = i0 + g + (e & 1) * 8, nt = e >> 1;
         uint32_t r[4];
-        philox4(d.ph, (bh * S + i) * s8q + nt * 2 + (q >> 1), r);
-        const uint32_t r0 = (q & 1) ? r[2] : r[0], r1 = (q & 1) ? r[3] : r[1];
-        bits |= ((r0 >= d.thresh ? 1u : 0u) | (r1 >= d.thresh ? 2u : 0u)) << (2 * e);
+        philox4(d.ph, (bh * S + i) * s8o + nt, r);
+        const uint32_t w = (q & 2) ? ((q & 1) ? r[3] : r[2]) : ((q & 1) ? r[1] : r[0]);
+        bits |= (((w & 0xFFFFu) >= d.thresh ? 1u : 0u) | ((w >> 16) >= d.thresh ? 2u : 0u)) << (2 * e);
     }
     return bits;
 }

@@ -84,9 +84,12 @@ inline cudaError_t launch_chain(void (*kern)(KArgs...), dim3 grid, dim3 block, s
 static inline int ceil_div(int a, int b) { return (a + b - 1) / b; }
 static inline int64_t round_up(int64_t a, int64_t b) { return (a + b - 1) / b * b; }
 
-// ------------------------------------------------------------------ Philox4x32-10
-// Counter layout: (idx4_lo, idx4_hi, site, step_lo) ; key: (seed_lo, seed_hi ^ step_hi).
-// One call yields the four keep/drop decisions of elements 4*idx4 .. 4*idx4+3 of a site.
+// ------------------------------------------------------------------ Philox4x32-7
+// Counter layout: (idx8_lo, idx8_hi, site, step_lo) ; key: (seed_lo, seed_hi ^ step_hi).
+// One call yields 128 bits = eight 16-bit lanes: the keep/drop decisions of elements 8*idx8 .. 8*idx8+7 of a site (lane k of
+// element 8*idx8 + k is bits 16*(k&1).. of word k>>1).  Seven rounds are the fewest with which Philox4x32 passes BigCrush
+// (Salmon et al., SC'11; ten is that paper's safety margin): the dropout-carrying GEMM epilogues and LayerNorm kernels are
+// instruction-issue bound and the generator was most of their instructions (80 per 4 elements -> 56 per 8).
 struct Philox {
     uint32_t k0, k1, site, step;
 };
@@ -100,11 +103,11 @@ __host__ __device__ __forceinline__ Philox philox_make(uint64_t seed, uint64_t s
     return p;
 }
 
-__host__ __device__ __forceinline__ void philox4(const Philox& p, uint64_t idx4, uint32_t out[4]) {
-    uint32_t c0 = (uint32_t)idx4, c1 = (uint32_t)(idx4 >> 32), c2 = p.site, c3 = p.step;
+__host__ __device__ __forceinline__ void philox4(const Philox& p, uint64_t idx8, uint32_t out[4]) {
+    uint32_t c0 = (uint32_t)idx8, c1 = (uint32_t)(idx8 >> 32), c2 = p.site, c3 = p.step;
     uint32_t k0 = p.k0, k1 = p.k1;
 #pragma unroll
-    for (int r = 0; r < 10; ++r) {
+    for (int r = 0; r < 7; ++r) {
         const uint64_t p0 = (uint64_t)0xD2511F53u * c0;
         const uint64_t p1 = (uint64_t)0xCD9E8D57u * c2;
         const uint32_t n0 = (uint32_t)(p1 >> 32) ^ c1 ^ k0;
@@ -119,11 +122,11 @@ __host__ __device__ __forceinline__ void philox4(const Philox& p, uint64_t idx4,
     out[0] = c0; out[1] = c1; out[2] = c2; out[3] = c3;
 }
 
-// keep iff r >= thresh where thresh = round(p * 2^32)  (P(keep) = 1 - p)
+// keep iff lane >= thresh where thresh = floor(p * 2^16)  (P(keep) = 1 - p to within 2^-16)
 __host__ __device__ __forceinline__ uint32_t drop_threshold(float p) {
-    double t = (double)p * 4294967296.0;
+    double t = (double)p * 65536.0;
     if (t <= 0.0) return 0u;
-    if (t >= 4294967295.0) return 0xFFFFFFFFu;
+    if (t >= 65535.0) return 0xFFFFu;
     return (uint32_t)t;
 }
 
@@ -165,16 +168,53 @@ __device__ __forceinline__ Drop drop_resolve(Drop d) {
 // multiplier (0 or scale) for the single element `idx` (slow path: one Philox per element)
 __device__ __forceinline__ float drop_mult1(const Drop& d, uint64_t idx) {
     uint32_t r[4];
-    philox4(d.ph, idx >> 2, r);
-    return r[idx & 3] >= d.thresh ? d.scale : 0.f;
+    philox4(d.ph, idx >> 3, r);
+    const uint32_t k = (uint32_t)idx & 7u;
+    const uint32_t w = (k & 4u) ? ((k & 2u) ? r[3] : r[2]) : ((k & 2u) ? r[1] : r[0]);
+    return ((w >> (16u * (k & 1u))) & 0xFFFFu) >= d.thresh ? d.scale : 0.f;
 }
 
-// multipliers for the aligned group of four elements 4*idx4 .. 4*idx4+3
+// multipliers for the aligned group of four elements 4*idx4 .. 4*idx4+3 (half of a Philox call: the neighbouring group
+// recomputes it -- kernels whose threads own 8 consecutive elements use drop_mult8)
 __device__ __forceinline__ void drop_mult4(const Drop& d, uint64_t idx4, float m[4]) {
     uint32_t r[4];
-    philox4(d.ph, idx4, r);
+    philox4(d.ph, idx4 >> 1, r);
+    const bool hi = (idx4 & 1u) != 0;
+    const uint32_t a = hi ? r[2] : r[0], b = hi ? r[3] : r[1];
+    m[0] = (a & 0xFFFFu) >= d.thresh ? d.scale : 0.f;
+    m[1] = (a >> 16) >= d.thresh ? d.scale : 0.f;
+    m[2] = (b & 0xFFFFu) >= d.thresh ? d.scale : 0.f;
+    m[3] = (b >> 16) >= d.thresh ? d.scale : 0.f;
+}
+
+// Two aligned 4-groups of this lane, idx4_a and idx4_b, in a layout where the neighbouring lane (lane ^ 1) owns idx4_a ^ 1 and
+// idx4_b ^ 1 and both groups' parity equals the lane's: the lane pair makes the two Philox calls once between them (even
+// lane: a's, odd lane: b's) and swaps the halves the other needs -- half a call per group.  Every lane of the warp must call.
+__device__ __forceinline__ void drop_mult4_pair(const Drop& d, uint64_t idx4_a, uint64_t idx4_b, int lane, float ma[4], float mb[4]) {
+    const bool odd = (lane & 1) != 0;
+    uint32_t r[4];
+    philox4(d.ph, (odd ? idx4_b : idx4_a) >> 1, r);
+    const uint32_t g0 = __shfl_xor_sync(0xffffffffu, odd ? r[0] : r[2], 1), g1 = __shfl_xor_sync(0xffffffffu, odd ? r[1] : r[3], 1);
+    const uint32_t a0 = odd ? g0 : r[0], a1 = odd ? g1 : r[1], b0 = odd ? r[2] : g0, b1 = odd ? r[3] : g1;
+    ma[0] = (a0 & 0xFFFFu) >= d.thresh ? d.scale : 0.f;
+    ma[1] = (a0 >> 16) >= d.thresh ? d.scale : 0.f;
+    ma[2] = (a1 & 0xFFFFu) >= d.thresh ? d.scale : 0.f;
+    ma[3] = (a1 >> 16) >= d.thresh ? d.scale : 0.f;
+    mb[0] = (b0 & 0xFFFFu) >= d.thresh ? d.scale : 0.f;
+    mb[1] = (b0 >> 16) >= d.thresh ? d.scale : 0.f;
+    mb[2] = (b1 & 0xFFFFu) >= d.thresh ? d.scale : 0.f;
+    mb[3] = (b1 >> 16) >= d.thresh ? d.scale : 0.f;
+}
+
+// multipliers for the aligned group of eight elements 8*idx8 .. 8*idx8+7: one Philox call
+__device__ __forceinline__ void drop_mult8(const Drop& d, uint64_t idx8, float m[8]) {
+    uint32_t r[4];
+    philox4(d.ph, idx8, r);
 #pragma unroll
-    for (int i = 0; i < 4; ++i) m[i] = r[i] >= d.thresh ? d.scale : 0.f;
+    for (int i = 0; i < 4; ++i) {
+        m[2 * i] = (r[i] & 0xFFFFu) >= d.thresh ? d.scale : 0.f;
+        m[2 * i + 1] = (r[i] >> 16) >= d.thresh ? d.scale : 0.f;
+    }
 }
 
 // ------------------------------------------------------------------ bf16 planes

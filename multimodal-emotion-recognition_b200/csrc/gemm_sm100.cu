@@ -340,12 +340,14 @@ __device__ __forceinline__ void epilogue_tma(const GemmParams& p, const EpiMaps&
             }
         }
         if (f_drop) {
-            const uint64_t base4 = (uint64_t)((int64_t)row * p.drop_ld + n0) >> 2;
+            // drop_ld % 8 == 0 here (gemm_make_epi_maps): the row's 32 columns are four whole Philox calls
+            const uint64_t e8 = (uint64_t)((int64_t)row * p.drop_ld + n0) >> 3;
 #pragma unroll
-            for (int j = 0; j < 8; ++j) {
-                float dm[4];
-                drop_mult4(drop, base4 + j, dm);
-                x[4 * j] *= dm[0]; x[4 * j + 1] *= dm[1]; x[4 * j + 2] *= dm[2]; x[4 * j + 3] *= dm[3];
+            for (int j = 0; j < 4; ++j) {
+                float dm[8];
+                drop_mult8(drop, e8 + j, dm);
+#pragma unroll
+                for (int i = 0; i < 8; ++i) x[8 * j + i] *= dm[i];
             }
         }
         if (has_res) {
@@ -773,7 +775,7 @@ int gemm_make_epi_maps(GemmParams& p, EpiMaps* em) {
     if (p.resid && !ok(p.resid, p.resid_ld, 4)) return M2F_OK;
     if (p.gate && !ok(p.gate, p.gate_ld, 2)) return M2F_OK;
     if (p.out_pl && (!ok(p.out_pl, p.out_pl_ld, 2) || (p.out_pl_n > 1 && (p.out_pl_stride * 2) % 16 != 0))) return M2F_OK;
-    if (p.drop.enabled && (p.drop_ld & 3)) return M2F_OK;
+    if (p.drop.enabled && (p.drop_ld & 7)) return M2F_OK;  // the TMA epilogue draws eight keep/drop decisions per Philox call
     if (p.out_f32) M2F_TRY(make_epi_tmap(&em->out_f32, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, p.out_f32, p.M, p.N, p.out_f32_ld, 0, 0));
     if (p.resid) M2F_TRY(make_epi_tmap(&em->resid, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, const_cast<float*>(p.resid), p.M, p.N, p.resid_ld, 0, 0));
     if (p.gate) M2F_TRY(make_epi_tmap(&em->gate, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<__nv_bfloat16*>(p.gate), p.M, p.N, p.gate_ld, 0, 0));

@@ -276,6 +276,21 @@ ln_fwd_staged_kernel(const float* __restrict__ x, int64_t x_ld, const float* __r
                 stats[2 * m] = mean;
                 stats[2 * m + 1] = rstd;
             }
+            // keep/drop multipliers of the row, before the column loop: with (m * D) % 8 == 0 the 4-groups of lanes 2k, 2k+1 are
+            // the two halves of one Philox call, so a lane pair shares the calls of two chunks (drop_mult4_pair)
+            float dmul[NCH][4];
+            if (ypl && drop.enabled) {
+                const uint64_t row4 = (uint64_t)(m * D) >> 2;
+                const bool pairs = ((m * D) & 7) == 0;
+#pragma unroll
+                for (int c = 0; c < NCH; c += 2) {
+                    if (pairs && c + 1 < NCH) drop_mult4_pair(drop, row4 + c * 32 + lane, row4 + (c + 1) * 32 + lane, lane, dmul[c], dmul[c + 1 < NCH ? c + 1 : c]);
+                    else {
+                        drop_mult4(drop, row4 + c * 32 + lane, dmul[c]);
+                        if (c + 1 < NCH) drop_mult4(drop, row4 + (c + 1) * 32 + lane, dmul[c + 1 < NCH ? c + 1 : c]);
+                    }
+                }
+            }
 #pragma unroll
             for (int c = 0; c < NCH; ++c) {
                 const int col = (c * 32 + lane) * 4;
@@ -291,10 +306,8 @@ ln_fwd_staged_kernel(const float* __restrict__ x, int64_t x_ld, const float* __r
                     if (y) *reinterpret_cast<float4*>(y + m * y_ld + col) = make_float4(o[0], o[1], o[2], o[3]);
                     if (ypl) {
                         if (drop.enabled) {
-                            float dm[4];
-                            drop_mult4(drop, (uint64_t)(m * D + col) >> 2, dm);
 #pragma unroll
-                            for (int i = 0; i < 4; ++i) o[i] *= dm[i];
+                            for (int i = 0; i < 4; ++i) o[i] *= dmul[c][i];
                         }
                         store_planes4(ypl, ypl_stride, P, m * ypl_ld + col, o);
                     }
@@ -321,7 +334,7 @@ ln_bwd_staged_kernel(const float* __restrict__ g, int64_t g_ld, const float* __r
                      float* __restrict__ dgamma, float* __restrict__ dbeta, float* __restrict__ dbias) {
     extern __shared__ __align__(128) uint8_t ln2_smem[];
     __shared__ __align__(8) uint64_t full_bar[LN2_STAGES];
-    __shared__ float rowc[LN2_ROWS][4];  // mean, rstd, c1, c2
+    __shared__ __align__(16) float rowc[LN2_ROWS][4];  // mean, rstd, c1, c2
     float* ring = reinterpret_cast<float*>(ln2_smem);
     const int tile_floats = LN2_ROWS * D;
     const int stage_floats = 2 * tile_floats;  // x tile, then g tile
@@ -395,29 +408,41 @@ ln_bwd_staged_kernel(const float* __restrict__ g, int64_t g_ld, const float* __r
             if (lane == 0) { rowc[warp][0] = mean; rowc[warp][1] = rstd; rowc[warp][2] = c1; rowc[warp][3] = c2; }
         }
         __syncthreads();  // rowc complete
-        if (ccol < D) {   // phase 2: dx, mask, stores and the column sums, once per element
+        {   // phase 2: dx, mask, stores and the column sums, once per element.  Rows go in pairs: with D % 8 == 0 the 4-groups
+            // of threads 2k, 2k+1 in a row are the two halves of one Philox call, so a thread pair shares the calls of two rows.
+            const bool live = ccol < D;
             const int nrow = (int)min((int64_t)LN2_ROWS, M - m0);
-#pragma unroll 2
-            for (int r = 0; r < nrow; ++r) {
+            const bool masked = drop.enabled && (dxpl || dbias);
+            const bool pairs = masked && (D & 7) == 0;
+            auto element = [&](int r, const float dm[4]) {
                 const int64_t mm = m0 + r;
                 const float4 xr = *reinterpret_cast<const float4*>(sx + (size_t)r * D + ccol);
                 const float4 gr = *reinterpret_cast<const float4*>(sgr + (size_t)r * D + ccol);
-                const float rmean = rowc[r][0], rrstd = rowc[r][1], c1 = rowc[r][2], c2 = rowc[r][3];
-                const float4 xh = make_float4((xr.x - rmean) * rrstd, (xr.y - rmean) * rrstd, (xr.z - rmean) * rrstd, (xr.w - rmean) * rrstd);
-                sg.x += gr.x * xh.x; sg.y += gr.y * xh.y; sg.z += gr.z * xh.z; sg.w += gr.w * xh.w;
+                const float4 rc = *reinterpret_cast<const float4*>(rowc[r]);  // mean, rstd, c1, c2
+                const float4 xh = make_float4((xr.x - rc.x) * rc.y, (xr.y - rc.x) * rc.y, (xr.z - rc.x) * rc.y, (xr.w - rc.x) * rc.y);
+                sg.x = fmaf(gr.x, xh.x, sg.x); sg.y = fmaf(gr.y, xh.y, sg.y); sg.z = fmaf(gr.z, xh.z, sg.z); sg.w = fmaf(gr.w, xh.w, sg.w);
                 sb.x += gr.x; sb.y += gr.y; sb.z += gr.z; sb.w += gr.w;
-                float o[4] = {rrstd * (gr.x * gmc.x - c1 - xh.x * c2), rrstd * (gr.y * gmc.y - c1 - xh.y * c2),
-                              rrstd * (gr.z * gmc.z - c1 - xh.z * c2), rrstd * (gr.w * gmc.w - c1 - xh.w * c2)};
+                float o[4] = {rc.y * (gr.x * gmc.x - rc.z - xh.x * rc.w), rc.y * (gr.y * gmc.y - rc.z - xh.y * rc.w),
+                              rc.y * (gr.z * gmc.z - rc.z - xh.z * rc.w), rc.y * (gr.w * gmc.w - rc.z - xh.w * rc.w)};
                 if (dx) *reinterpret_cast<float4*>(dx + mm * dx_ld + ccol) = make_float4(o[0], o[1], o[2], o[3]);
                 if (dxpl || dbias) {
-                    if (drop.enabled) {
-                        float dm[4];
-                        drop_mult4(drop, (uint64_t)(mm * D + ccol) >> 2, dm);
-                        o[0] *= dm[0]; o[1] *= dm[1]; o[2] *= dm[2]; o[3] *= dm[3];
-                    }
+                    if (masked) { o[0] *= dm[0]; o[1] *= dm[1]; o[2] *= dm[2]; o[3] *= dm[3]; }
                     if (dxpl) store_planes4(dxpl, dxpl_stride, P, mm * dxpl_ld + ccol, o);
                     sbias.x += o[0]; sbias.y += o[1]; sbias.z += o[2]; sbias.w += o[3];
                 }
+            };
+            int r = 0;
+            for (; r + 1 < nrow; r += 2) {
+                float da[4] = {1.f, 1.f, 1.f, 1.f}, db[4] = {1.f, 1.f, 1.f, 1.f};
+                const uint64_t ia = ((uint64_t)((m0 + r) * D) >> 2) + threadIdx.x, ib = ia + ((uint64_t)D >> 2);
+                if (pairs) drop_mult4_pair(drop, ia, ib, lane, da, db);  // whole warps: also the lanes past D
+                else if (masked && live) { drop_mult4(drop, ia, da); drop_mult4(drop, ib, db); }
+                if (live) { element(r, da); element(r + 1, db); }
+            }
+            if (r < nrow && live) {
+                float da[4] = {1.f, 1.f, 1.f, 1.f};
+                if (masked) drop_mult4(drop, ((uint64_t)((m0 + r) * D) >> 2) + threadIdx.x, da);
+                element(r, da);
             }
         }
         __syncthreads();  // every thread has read stage s2 and rowc: both can be overwritten
