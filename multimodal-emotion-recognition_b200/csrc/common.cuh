@@ -260,16 +260,23 @@ __device__ __forceinline__ void load_planes4(const __nv_bfloat16* base, int64_t 
 }
 
 __device__ __forceinline__ void store_planes4(__nv_bfloat16* base, int64_t plane_stride, int P, int64_t idx, const float v[4]) {
-    __nv_bfloat16 h[4][3];
+    // registers only: the plane loop is unrolled with static indices (a rolled loop over a runtime P put the residuals in
+    // local memory), each plane packs the rounded residuals two by two and subtracts them for the next one
+    float r[4] = {v[0], v[1], v[2], v[3]};
 #pragma unroll
-    for (int i = 0; i < 4; ++i) split_planes(v[i], P, h[i]);
-    for (int p = 0; p < P; ++p) {
-        __nv_bfloat162 a = __halves2bfloat162(h[0][p], h[1][p]);
-        __nv_bfloat162 b = __halves2bfloat162(h[2][p], h[3][p]);
-        uint2 raw;
-        raw.x = *reinterpret_cast<uint32_t*>(&a);
-        raw.y = *reinterpret_cast<uint32_t*>(&b);
-        *reinterpret_cast<uint2*>(base + p * plane_stride + idx) = raw;
+    for (int p = 0; p < 3; ++p) {
+        if (p < P) {
+            const __nv_bfloat162 a = __floats2bfloat162_rn(r[0], r[1]);
+            const __nv_bfloat162 b = __floats2bfloat162_rn(r[2], r[3]);
+            uint2 raw;
+            raw.x = *reinterpret_cast<const uint32_t*>(&a);
+            raw.y = *reinterpret_cast<const uint32_t*>(&b);
+            *reinterpret_cast<uint2*>(base + p * plane_stride + idx) = raw;
+            if (p + 1 < P) {
+                r[0] -= __low2float(a); r[1] -= __high2float(a);
+                r[2] -= __low2float(b); r[3] -= __high2float(b);
+            }
+        }
     }
 }
 

@@ -431,7 +431,8 @@ ln_bwd_staged_kernel(const float* __restrict__ g, int64_t g_ld, const float* __r
                     sbias.x += o[0]; sbias.y += o[1]; sbias.z += o[2]; sbias.w += o[3];
                 }
             };
-            int r = 0;
+            const bool warp_live = warp * 128 < D;  // a whole warp past D (D = 768: warps 6, 7) has nothing to do in this phase
+            int r = warp_live ? 0 : nrow;
             for (; r + 1 < nrow; r += 2) {
                 float da[4] = {1.f, 1.f, 1.f, 1.f}, db[4] = {1.f, 1.f, 1.f, 1.f};
                 const uint64_t ia = ((uint64_t)((m0 + r) * D) >> 2) + threadIdx.x, ib = ia + ((uint64_t)D >> 2);
