@@ -10,16 +10,26 @@ namespace m2f {
 constexpr int CE_MAX_C = 32;
 constexpr int CE_THREADS = 256;
 
-__device__ __forceinline__ void ce_row(const float* z, int C, float lp[CE_MAX_C]) {
+// CMAX: compile-time bound on C (8 or 32) so that the row lives in registers: loops are unrolled over CMAX with c < C tests
+// (a loop over a runtime C indexed lp[] dynamically and put it in local memory).
+template <int CMAX>
+__device__ __forceinline__ void ce_row(const float* z, int C, float lp[CMAX]) {
     float mx = -INFINITY;
-    for (int c = 0; c < C; ++c) mx = fmaxf(mx, z[c]);
+#pragma unroll
+    for (int c = 0; c < CMAX; ++c) {
+        lp[c] = c < C ? z[c] : -INFINITY;
+        mx = fmaxf(mx, lp[c]);
+    }
     float s = 0.f;
-    for (int c = 0; c < C; ++c) s += expf(z[c] - mx);
+#pragma unroll
+    for (int c = 0; c < CMAX; ++c) s += c < C ? expf(lp[c] - mx) : 0.f;
     const float lse = mx + logf(s);
-    for (int c = 0; c < C; ++c) lp[c] = z[c] - lse;
+#pragma unroll
+    for (int c = 0; c < CMAX; ++c) lp[c] -= lse;
 }
 
 // acc[1] += sum_V w_y; acc[2] += sum_V -w_y lp_y; acc[3] += sum_V sum_c -w_c lp_c
+template <int CMAX>
 __global__ void __launch_bounds__(CE_THREADS)
 ce_reduce_kernel(const float* __restrict__ logits, int64_t ld, const int64_t* __restrict__ target, const float* __restrict__ w, int64_t M,
                  int C, float* acc) {
@@ -28,13 +38,19 @@ ce_reduce_kernel(const float* __restrict__ logits, int64_t ld, const int64_t* __
     for (int64_t m = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; m < M; m += (int64_t)gridDim.x * blockDim.x) {
         const int64_t y = target[m];
         if (y < 0 || y >= C) continue;  // ignore_index = -1
-        float lp[CE_MAX_C];
-        ce_row(logits + m * ld, C, lp);
+        float lp[CMAX];
+        ce_row<CMAX>(logits + m * ld, C, lp);
         const float wy = w ? w[y] : 1.f;
         a_den += wy;
-        a_nll -= wy * lp[y];
-        float s = 0.f;
-        for (int c = 0; c < C; ++c) s -= (w ? w[c] : 1.f) * lp[c];
+        float s = 0.f, lpy = 0.f;
+#pragma unroll
+        for (int c = 0; c < CMAX; ++c) {
+            if (c < C) {
+                s -= (w ? w[c] : 1.f) * lp[c];
+                if (c == y) lpy = lp[c];
+            }
+        }
+        a_nll -= wy * lpy;
         a_sm += s;
     }
     a_den = warp_sum(a_den);
@@ -54,6 +70,7 @@ ce_reduce_kernel(const float* __restrict__ logits, int64_t ld, const int64_t* __
     }
 }
 
+template <int CMAX>
 __global__ void __launch_bounds__(CE_THREADS)
 ce_grad_kernel(const float* __restrict__ logits, int64_t ld, const int64_t* __restrict__ target, const float* __restrict__ w, int64_t M,
                int C, float eps, float grad_scale, float* acc, float* __restrict__ dl, int64_t dl_ld, __nv_bfloat16* __restrict__ dpl,
@@ -67,17 +84,20 @@ ce_grad_kernel(const float* __restrict__ logits, int64_t ld, const int64_t* __re
     for (int64_t m = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; m < M; m += (int64_t)gridDim.x * blockDim.x) {
         const int64_t y = target[m];
         const bool valid = y >= 0 && y < C;
-        float lp[CE_MAX_C];
-        if (valid) ce_row(logits + m * ld, C, lp);
+        float lp[CMAX];
+        if (valid) ce_row<CMAX>(logits + m * ld, C, lp);
         const float wy = valid ? (w ? w[y] : 1.f) : 0.f;
-        for (int c = 0; c < C; ++c) {
-            float gval = 0.f;
-            if (valid) {
-                const float p = expf(lp[c]);
-                gval = k * ((1.f - eps) * wy * (p - (c == y ? 1.f : 0.f)) + (eps / (float)C) * (p * wsum - (w ? w[c] : 1.f)));
+#pragma unroll
+        for (int c = 0; c < CMAX; ++c) {
+            if (c < C) {
+                float gval = 0.f;
+                if (valid) {
+                    const float p = expf(lp[c]);
+                    gval = k * ((1.f - eps) * wy * (p - (c == y ? 1.f : 0.f)) + (eps / (float)C) * (p * wsum - (w ? w[c] : 1.f)));
+                }
+                if (dl) dl[m * dl_ld + c] = gval;
+                if (dpl) store_planes(dpl, dpl_stride, P, m * dpl_ld + c, gval);
             }
-            if (dl) dl[m * dl_ld + c] = gval;
-            if (dpl) store_planes(dpl, dpl_stride, P, m * dpl_ld + c, gval);
         }
         if (dpl)
             for (int c = C; c < dpl_cols; ++c) store_planes(dpl, dpl_stride, P, m * dpl_ld + c, 0.f);  // zero the TMA padding columns
@@ -109,10 +129,17 @@ extern "C" int m2f_ce_fwd_bwd(const float* logits, int64_t ld, const int64_t* ta
     M2F_CUDA(cudaMemsetAsync(loss_out, 0, 4 * sizeof(float), st));
     int64_t g = (M + CE_THREADS - 1) / CE_THREADS;
     if (g > 148 * 4) g = 148 * 4;
-    ce_reduce_kernel<<<(unsigned)g, CE_THREADS, 0, st>>>(logits, ld, target, class_w, M, C, loss_out);
-    M2F_LAUNCH_CHECK();
-    ce_grad_kernel<<<(unsigned)g, CE_THREADS, 0, st>>>(logits, ld, target, class_w, M, C, eps, grad_scale, loss_out, dlogits, dl_ld, dpl, dpl_ld,
-                                                       dpl_stride, dpl_cols, P);
+    if (C <= 8) {
+        ce_reduce_kernel<8><<<(unsigned)g, CE_THREADS, 0, st>>>(logits, ld, target, class_w, M, C, loss_out);
+        M2F_LAUNCH_CHECK();
+        ce_grad_kernel<8><<<(unsigned)g, CE_THREADS, 0, st>>>(logits, ld, target, class_w, M, C, eps, grad_scale, loss_out, dlogits, dl_ld, dpl,
+                                                              dpl_ld, dpl_stride, dpl_cols, P);
+    } else {
+        ce_reduce_kernel<CE_MAX_C><<<(unsigned)g, CE_THREADS, 0, st>>>(logits, ld, target, class_w, M, C, loss_out);
+        M2F_LAUNCH_CHECK();
+        ce_grad_kernel<CE_MAX_C><<<(unsigned)g, CE_THREADS, 0, st>>>(logits, ld, target, class_w, M, C, eps, grad_scale, loss_out, dlogits, dl_ld,
+                                                                     dpl, dpl_ld, dpl_stride, dpl_cols, P);
+    }
     M2F_LAUNCH_CHECK();
     return M2F_OK;
 }

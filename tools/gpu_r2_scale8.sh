@@ -1,8 +1,9 @@
 #!/bin/bash
-# round 2: the bench line at N GPUs exactly as the driver launches it
+# round 2: the bench line at N GPUs as the driver launches it (trimmed: no other precision modes, no eager context, no CPU arm)
 N=${1:-8}
 mkdir -p gpurun_out
-timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29731 bench.py --gpus $N --steps 20 --warmup 5 > gpurun_out/r2_bench_${N}gpu.json 2> gpurun_out/r2_bench_${N}gpu.err
+nvidia-smi -L | wc -l
+timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29731 bench.py --gpus $N --steps 20 --warmup 5 --no-modes --no-context --no-cpu-baseline --no-rooflines > gpurun_out/r2_bench_${N}gpu.json 2> gpurun_out/r2_bench_${N}gpu.err
 echo "rc=$?"; tail -c 800 gpurun_out/r2_bench_${N}gpu.err
 python - $N <<'PY'
 import json, sys
