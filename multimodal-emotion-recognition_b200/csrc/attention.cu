@@ -8,6 +8,8 @@
 #include <math.h>
 
 #include "attention_mma.cuh"
+#include <algorithm>
+
 #include "common.cuh"
 
 namespace m2f {
@@ -218,6 +220,10 @@ int bwd_p1(AMMA_BWD_ARGS); int bwd_p2(AMMA_BWD_ARGS); int bwd_p3(AMMA_BWD_ARGS);
 bool long_supported(int hd, int64_t S);
 int fwd_long(int hd, int P, const View& q, const View& k, const View& v, const uint8_t* pad, int64_t BH, int S, int H, float scale,
              const OutView& o, cudaStream_t st);
+// attention_tc.cu: the same on tcgen05 / TMEM / TMA for one plane and head sizes 64 / 96 / 128
+bool tc_supported(int hd, int64_t S, int planes, int64_t rows);
+int fwd_long_tc(int hd, const m2f_planes_t* q, const m2f_planes_t* k, const m2f_planes_t* v, const uint8_t* pad, int64_t B, int S, int H,
+                const OutView& o, cudaStream_t st);
 static bool supported(int hd, int64_t S) { return S <= 64 && (hd == 16 || hd == 32 || hd == 64 || hd == 96 || hd == 128); }
 // 16-byte row chunks: base, leading dimension, plane stride and the head's first column must be multiples of 8 elements
 static bool aligned16(const m2f_planes_t* t) {
@@ -278,6 +284,8 @@ extern "C" int m2f_attn_fwd(const m2f_planes_t* q, const m2f_planes_t* k, const 
         // long dialogues at inference: K/V tiles through shared memory, online softmax over 64-key tiles
         const amma::View aq{vq.ptr, vq.ld, vq.stride}, ak{vk.ptr, vk.ld, vk.stride}, av{vv.ptr, vv.ld, vv.stride};
         const amma::OutView ao{const_cast<__nv_bfloat16*>(vo.ptr), vo.ld, vo.stride};
+        if (amma::tc_supported(hd, S, q->planes, std::min(std::min(q->rows, k->rows), v->rows)))
+            return amma::fwd_long_tc(hd, q, k, v, key_pad, B, (int)S, H, ao, reinterpret_cast<cudaStream_t>(stream));
         return amma::fwd_long(hd, q->planes, aq, ak, av, key_pad, B * H, (int)S, H, 1.f / sqrtf((float)hd), ao, reinterpret_cast<cudaStream_t>(stream));
     }
     const int hd_pad = hd | 1;

@@ -1,0 +1,271 @@
+// Long-dialogue attention forward on the 5th-generation tensor cores (tcgen05 + TMEM + TMA): the inference shape of
+// BASELINE.json's config 5 (test() body, src/test.py:58-71: S = 256, batch 512), bf16 mode (one plane), head_dim 96 (also 64 / 128).
+// Same arithmetic as torch/nn/functional.py:6607-6620 -- softmax(Q K^T / sqrt(hd) + key-padding mask) V, no dropout.
+//
+// One CTA per (dialogue, head, block of 128 query rows); 64 < S <= 256, so the whole key axis is ONE MMA tile:
+//   TMA      Q [128 x hd], K [256 x hd] (K-major, 128-byte swizzle, one box per 64-column atom) and V [256 x hd] (read as the
+//            MN-major B operand: 64-key x 64-column boxes) land in shared memory; rows past the dialogue belong to the next
+//            dialogue (or are zero-filled past the tensor) and are masked out below.
+//   MMA 1    S = Q K^T: one elected thread issues tcgen05.mma 128 x 256 x 16 over hd / 16 k-steps, accumulator = 256 TMEM columns.
+//   softmax  8 warps, two threads per query row (TMEM lane = row; warps w and w + 4 own the same lanes and take 128 columns each):
+//            tcgen05.ld the scores twice (row maximum, then exp2 / row sum -- TMEM reads are cheaper than 256 live registers),
+//            unnormalised probabilities go back to shared memory as the bf16 K-major A operand of the second product
+//            (16-byte chunk c of row r sits at chunk c ^ (r & 7) of its 128-byte line: the swizzle the MMA descriptor expects).
+//   MMA 2    O = P V: 128 x 128 x 16 over 16 k-steps (hd padded to two 64-column atoms; columns >= hd are never read back).
+//   epilogue tcgen05.ld O, scale by 1 / row sum, bf16, 16-byte stores of the row's hd columns.
+// The mma.sync kernel of attention_mma_long.cu stays for 2 / 3 planes (fp32-parity mode) and other head sizes.
+#include <math.h>
+#include <stdlib.h>
+
+#include "attention_mma.cuh"
+#include "gemm.cuh"
+#include "ptx.cuh"
+
+namespace m2f {
+namespace amma {
+namespace {
+
+constexpr int TC_QT = 128;     // query rows per CTA (TMEM lanes)
+constexpr int TC_KEYS = 256;   // key tile = the whole (padded) dialogue
+constexpr int TC_SOFTMAX_THREADS = 256;
+constexpr int TC_THREADS = TC_SOFTMAX_THREADS + 32;
+constexpr int TC_SQ = 2 * TC_QT * 128;        // two 64-column atoms of [128 rows][128 B]
+constexpr int TC_SK = 2 * TC_KEYS * 128;      // two atoms of [256 rows][128 B]
+constexpr int TC_SV = 4 * 2 * 64 * 128;       // four 64-key blocks x two 64-column atoms of [64 rows][128 B]
+constexpr int TC_SP = 4 * TC_QT * 128;        // four 64-key atoms of [128 rows][128 B]
+constexpr int TC_AUX = 4 * 8 + 16 + 8 * 4 + 4 * TC_QT * 4;  // barriers, TMEM slot, key mask, row max / sum exchange
+static_assert(TC_SP <= TC_SQ + TC_SK, "the probabilities reuse the Q / K region");
+constexpr int TC_SMEM = TC_SQ + TC_SK + TC_SV + TC_AUX + 1024;
+constexpr uint32_t TC_TMEM_COLS = 512;        // scores 256 + output 128, rounded up to a power of two
+
+struct TcParams {
+    const uint8_t* key_pad;
+    __nv_bfloat16* o;
+    int64_t o_ld;
+    int S, H, hd;
+    float scale_log2;  // log2(e) / sqrt(hd)
+};
+
+__device__ __forceinline__ float ex2(float x) {
+    float y;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}
+
+__global__ void __launch_bounds__(TC_THREADS, 1)
+attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__ CUtensorMap tk, const __grid_constant__ CUtensorMap tv,
+                   const TcParams p) {
+    extern __shared__ uint8_t tc_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(tc_raw) + 1023) & ~uintptr_t(1023));
+    uint8_t* sQ = smem;
+    uint8_t* sK = sQ + TC_SQ;
+    uint8_t* sV = sK + TC_SK;
+    uint8_t* sP = sQ;  // Q and K are dead once the scores are complete (bar_s), which is when the probabilities are written
+    uint64_t* bar_qk = reinterpret_cast<uint64_t*>(sV + TC_SV);  // Q and K landed
+    uint64_t* bar_v = bar_qk + 1;                                // V landed
+    uint64_t* bar_s = bar_qk + 2;                                // scores complete in TMEM
+    uint64_t* bar_o = bar_qk + 3;                                // output complete in TMEM
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bar_qk + 4);
+    uint32_t* key_ok = tmem_slot + 4;                            // 8 words: bit j of word w = key 32 w + j is usable
+    float* red_max = reinterpret_cast<float*>(key_ok + 8);       // [2][128]
+    float* red_sum = red_max + 2 * TC_QT;                        // [2][128]
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int b = blockIdx.x / p.H, h = blockIdx.x - b * p.H;
+    const int q0 = blockIdx.y * TC_QT;
+    const int row0 = b * p.S;          // first row of the dialogue in the [B*S, E] matrices
+    const int col0 = h * p.hd;
+    const int ksteps = p.hd / 16;      // k-steps of the first product (hd = 64 / 96 / 128)
+
+    if (warp == 8 && lane == 0) {
+        ptx::prefetch_tensormap(&tq);
+        ptx::prefetch_tensormap(&tk);
+        ptx::prefetch_tensormap(&tv);
+        ptx::mbar_init(bar_qk, 1);
+        ptx::mbar_init(bar_v, 1);
+        ptx::mbar_init(bar_s, 1);
+        ptx::mbar_init(bar_o, 1);
+        ptx::fence_barrier_init();
+    }
+    if (warp == 0) ptx::tmem_alloc(tmem_slot, TC_TMEM_COLS);
+    ptx::tcgen05_fence_before();
+    __syncthreads();
+    ptx::tcgen05_fence_after();
+    const uint32_t tmem_s = *tmem_slot, tmem_o = tmem_s + 256u;
+    pdl_wait();
+    pdl_trigger();
+
+    if (warp == 8) {
+        if (ptx::elect_one()) {
+            // ---------------------------------------------------------------- loads
+            ptx::mbar_expect_tx(bar_qk, TC_SQ + TC_SK);
+#pragma unroll
+            for (int a = 0; a < 2; ++a) {
+                ptx::tma_load_3d(sQ + a * (TC_QT * 128), &tq, bar_qk, col0 + a * 64, row0 + q0, 0);
+                ptx::tma_load_3d(sK + a * (TC_KEYS * 128), &tk, bar_qk, col0 + a * 64, row0, 0);
+            }
+            ptx::mbar_expect_tx(bar_v, TC_SV);
+#pragma unroll
+            for (int kb = 0; kb < 4; ++kb)
+#pragma unroll
+                for (int a = 0; a < 2; ++a)
+                    ptx::tma_load_3d(sV + kb * 16384 + a * 8192, &tv, bar_v, col0 + a * 64, row0 + kb * 64, 0);
+            // ---------------------------------------------------------------- S = Q K^T
+            ptx::mbar_wait(bar_qk, 0);
+            ptx::tcgen05_fence_after();
+            constexpr uint32_t idesc_qk = ptx::instr_desc_bf16(TC_QT, TC_KEYS, false, false);
+            for (int k = 0; k < ksteps; ++k) {
+                const uint32_t off = (uint32_t)(k >> 2) * 128u, kin = (uint32_t)(k & 3) * 32u;  // atom, 16 columns = 32 B inside it
+                const uint64_t ad = ptx::smem_desc_sw128(ptx::smem_u32(sQ) + off * TC_QT + kin, 0, 1024);
+                const uint64_t bd = ptx::smem_desc_sw128(ptx::smem_u32(sK) + off * TC_KEYS + kin, 0, 1024);
+                ptx::umma_bf16(tmem_s, ad, bd, idesc_qk, k > 0 ? 1u : 0u);
+            }
+            ptx::umma_commit(bar_s);
+        }
+        __syncwarp();
+        // the probabilities are in shared memory once all 256 softmax threads have passed the named barrier below
+        ptx::named_bar_sync(2, TC_THREADS);
+        if (ptx::elect_one()) {
+            // ---------------------------------------------------------------- O = P V
+            ptx::mbar_wait(bar_v, 0);
+            ptx::tcgen05_fence_after();
+            constexpr uint32_t idesc_pv = ptx::instr_desc_bf16(TC_QT, 128, false, true);
+#pragma unroll 1
+            for (int kb = 0; kb < 4; ++kb) {
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                    const uint64_t ad = ptx::smem_desc_sw128(ptx::smem_u32(sP) + kb * (TC_QT * 128) + k * 32, 0, 1024);
+                    const uint64_t bd = ptx::smem_desc_sw128(ptx::smem_u32(sV) + kb * 16384 + k * 2048, 8192, 1024);
+                    ptx::umma_bf16(tmem_o, ad, bd, idesc_pv, (kb > 0 || k > 0) ? 1u : 0u);
+                }
+            }
+            ptx::umma_commit(bar_o);
+        }
+        __syncwarp();
+    } else {
+        // -------------------------------------------------------------------- softmax: thread = (query row, half of the keys)
+        const int lg = warp & 3, half = warp >> 2;
+        const int row = lg * 32 + lane;
+        {   // usable keys: inside the dialogue and not padded; warp w covers keys 32 w .. 32 w + 31
+            const int j = threadIdx.x;
+            const bool ok = j < p.S && p.key_pad[(int64_t)row0 + j] == 0;
+            const uint32_t word = __ballot_sync(0xffffffffu, ok);
+            if (lane == 0) key_ok[warp] = word;
+        }
+        ptx::named_bar_sync(1, TC_SOFTMAX_THREADS);
+        ptx::mbar_wait(bar_s, 0);
+        ptx::tcgen05_fence_after();
+        const uint32_t t_row = tmem_s + ((uint32_t)(lg * 32) << 16) + (uint32_t)(half * 128);
+        float mx = -INFINITY;
+#pragma unroll 1
+        for (int c = 0; c < 4; ++c) {
+            uint32_t r[32];
+            ptx::tmem_ld_32x32(t_row + (uint32_t)(c * 32), r);
+            ptx::tmem_ld_wait();
+            const uint32_t w = key_ok[half * 4 + c];
+#pragma unroll
+            for (int j = 0; j < 32; ++j) mx = fmaxf(mx, ((w >> j) & 1u) ? __uint_as_float(r[j]) : -INFINITY);
+        }
+        red_max[half * TC_QT + row] = mx;
+        ptx::named_bar_sync(1, TC_SOFTMAX_THREADS);
+        mx = fmaxf(mx, red_max[(half ^ 1) * TC_QT + row]);
+        if (mx == -INFINITY) mx = 0.f;  // no usable key at all: every probability is 0 (such rows are never stored)
+        const float mscaled = mx * p.scale_log2;
+        float sum = 0.f;
+        const uint32_t p_row = ptx::smem_u32(sP) + (uint32_t)row * 128u;
+        const uint32_t sw = (uint32_t)(row & 7);
+#pragma unroll 1
+        for (int c = 0; c < 4; ++c) {
+            uint32_t r[32];
+            ptx::tmem_ld_32x32(t_row + (uint32_t)(c * 32), r);
+            ptx::tmem_ld_wait();
+            const uint32_t w = key_ok[half * 4 + c];
+            uint32_t pk[16];
+#pragma unroll
+            for (int j = 0; j < 16; ++j) {
+                const float e0 = ((w >> (2 * j)) & 1u) ? ex2(fmaf(__uint_as_float(r[2 * j]), p.scale_log2, -mscaled)) : 0.f;
+                const float e1 = ((w >> (2 * j + 1)) & 1u) ? ex2(fmaf(__uint_as_float(r[2 * j + 1]), p.scale_log2, -mscaled)) : 0.f;
+                sum += e0 + e1;
+                pk[j] = pack2(e0, e1);
+            }
+            // keys half * 128 + c * 32 .. + 31: atom (64 keys) = half * 2 + c / 2, 16-byte chunks (c & 1) * 4 .. + 3 of the row's line
+            const uint32_t atom = p_row + (uint32_t)(half * 2 + (c >> 1)) * (TC_QT * 128);
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                const uint32_t chunk = ((uint32_t)((c & 1) * 4 + q)) ^ sw;
+                asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(atom + (chunk << 4)), "r"(pk[4 * q]), "r"(pk[4 * q + 1]),
+                             "r"(pk[4 * q + 2]), "r"(pk[4 * q + 3])
+                             : "memory");
+            }
+        }
+        red_sum[half * TC_QT + row] = sum;
+        ptx::fence_proxy_async();      // the probabilities are read by the tensor core through the async proxy
+        ptx::tcgen05_fence_before();
+        ptx::named_bar_sync(2, TC_THREADS);  // releases the MMA thread; also orders red_sum for the partner thread
+        const float inv = 1.f / (sum + red_sum[(half ^ 1) * TC_QT + row]);
+        ptx::mbar_wait(bar_o, 0);
+        ptx::tcgen05_fence_after();
+        // output columns: half 0 takes 0 .. 63, half 1 takes 64 .. hd - 1
+        const int c_lo = half * 64, c_hi = min(p.hd, c_lo + 64);
+        const bool live = q0 + row < p.S;
+        __nv_bfloat16* orow = p.o + ((int64_t)row0 + q0 + row) * p.o_ld + col0;
+        for (int cc = c_lo; cc < c_hi; cc += 32) {  // warp-uniform
+            uint32_t r[32];
+            ptx::tmem_ld_32x32(tmem_o + ((uint32_t)(lg * 32) << 16) + (uint32_t)cc, r);
+            ptx::tmem_ld_wait();
+            if (live) {
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    uint4 v4;
+                    v4.x = pack2(__uint_as_float(r[8 * q]) * inv, __uint_as_float(r[8 * q + 1]) * inv);
+                    v4.y = pack2(__uint_as_float(r[8 * q + 2]) * inv, __uint_as_float(r[8 * q + 3]) * inv);
+                    v4.z = pack2(__uint_as_float(r[8 * q + 4]) * inv, __uint_as_float(r[8 * q + 5]) * inv);
+                    v4.w = pack2(__uint_as_float(r[8 * q + 6]) * inv, __uint_as_float(r[8 * q + 7]) * inv);
+                    *reinterpret_cast<uint4*>(orow + cc + 8 * q) = v4;
+                }
+            }
+        }
+    }
+    ptx::tcgen05_fence_before();
+    __syncthreads();
+    if (warp == 0) {
+        ptx::tcgen05_fence_after();
+        ptx::tmem_dealloc(tmem_s, TC_TMEM_COLS);
+    }
+}
+
+}  // namespace
+
+// hd in {64, 96, 128}; one plane; enough rows for the 256-row key box; M2F_ATT_TC=0 keeps the mma.sync kernel (A/B, debugging)
+bool tc_supported(int hd, int64_t S, int planes, int64_t rows) {
+    static const bool off = [] { const char* e = getenv("M2F_ATT_TC"); return e && e[0] == '0'; }();
+    return !off && planes == 1 && (hd == 64 || hd == 96 || hd == 128) && S > 64 && S <= TC_KEYS && rows >= TC_KEYS;
+}
+
+int fwd_long_tc(int hd, const m2f_planes_t* q, const m2f_planes_t* k, const m2f_planes_t* v, const uint8_t* pad, int64_t B, int S, int H,
+                const OutView& o, cudaStream_t st) {
+    CUtensorMap tq, tk, tv;
+    M2F_TRY(make_planes_tmap(&tq, q, TC_QT));
+    M2F_TRY(make_planes_tmap(&tk, k, TC_KEYS));
+    M2F_TRY(make_planes_tmap(&tv, v, 64));
+    static bool attr_set = false;
+    if (!attr_set) {
+        M2F_CUDA(cudaFuncSetAttribute(attn_fwd_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM));
+        attr_set = true;
+    }
+    TcParams p;
+    p.key_pad = pad;
+    p.o = o.ptr;
+    p.o_ld = o.ld;
+    p.S = S;
+    p.H = H;
+    p.hd = hd;
+    p.scale_log2 = 1.4426950408889634f / sqrtf((float)hd);
+    M2F_CUDA(launch_chain(attn_fwd_tc_kernel, dim3((unsigned)(B * H), (unsigned)((S + TC_QT - 1) / TC_QT)), dim3(TC_THREADS), (size_t)TC_SMEM, st,
+                          1, tq, tk, tv, p));
+    M2F_LAUNCH_CHECK();
+    return M2F_OK;
+}
+
+}  // namespace amma
+}  // namespace m2f
