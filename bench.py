@@ -803,9 +803,11 @@ def hbm_kernel_rooflines(pkg, torch, dev, cfg):
     pad = torch.zeros(Bl, Sl, dtype=torch.uint8, device=dev)
     us = time_us(lambda: ops.attn_fwd(q, k, v, pad, Bl, Sl, H, o), reps=5)
     flops = 4.0 * Sl * Dm * Ml
-    add("attention forward, long dialogues (S=256, hd=96, inference), 512 dialogues x 8 heads", 4 * Ml * Dm * 2 + Ml, us)
+    add("attention forward, long dialogues (S=256, hd=96, inference; tcgen05 / TMEM / TMA kernel), 512 dialogues x 8 heads", 4 * Ml * Dm * 2 + Ml, us)
     out[-1]["tensor_tflops"] = flops / (us * 1e-6) / 1e12
-    out[-1]["note"] = "103 GFLOP per launch: this kernel is bound by its contraction rate, not by HBM"
+    out[-1]["note"] = ("103 GFLOP and 33.5 M exponentials per launch; one CTA per (dialogue, head) and SM: the loads of a CTA are not overlapped with "
+                       "the previous CTA's softmax (shared memory holds one dialogue-head: K, V, Q / P), and the softmax is bound by the 16 "
+                       "ex2 per clock of an SM (2 us of the ~12 us a CTA takes)")
     del q, k, v, o
 
     # fused Adam + bf16 shadow refresh over the model arena

@@ -2,7 +2,7 @@
 // BASELINE.json's config 5 (test() body, src/test.py:58-71: S = 256, batch 512), bf16 mode (one plane), head_dim 96 (also 64 / 128).
 // Same arithmetic as torch/nn/functional.py:6607-6620 -- softmax(Q K^T / sqrt(hd) + key-padding mask) V, no dropout.
 //
-// One CTA per (dialogue, head, block of 128 query rows); 64 < S <= 256, so the whole key axis is ONE MMA tile:
+// One CTA per (dialogue, head), one or two tiles of 128 query rows; 64 < S <= 256, so the whole key axis is ONE MMA tile:
 //   TMA      Q [128 x hd], K [256 x hd] (K-major, 128-byte swizzle, one box per 64-column atom) and V [256 x hd] (read as the
 //            MN-major B operand: 64-key x 64-column boxes) land in shared memory; rows past the dialogue belong to the next
 //            dialogue (or are zero-filled past the tensor) and are masked out below.
@@ -25,18 +25,18 @@ namespace m2f {
 namespace amma {
 namespace {
 
-constexpr int TC_QT = 128;     // query rows per CTA (TMEM lanes)
+constexpr int TC_QT = 128;     // query rows per tile (TMEM lanes)
 constexpr int TC_KEYS = 256;   // key tile = the whole (padded) dialogue
 constexpr int TC_SOFTMAX_THREADS = 256;
 constexpr int TC_THREADS = TC_SOFTMAX_THREADS + 32;
-constexpr int TC_SQ = 2 * TC_QT * 128;        // two 64-column atoms of [128 rows][128 B]
+constexpr int TC_SQ = 2 * TC_QT * 128;        // one query tile: two 64-column atoms of [128 rows][128 B]
 constexpr int TC_SK = 2 * TC_KEYS * 128;      // two atoms of [256 rows][128 B]
 constexpr int TC_SV = 4 * 2 * 64 * 128;       // four 64-key blocks x two 64-column atoms of [64 rows][128 B]
-constexpr int TC_SP = 4 * TC_QT * 128;        // four 64-key atoms of [128 rows][128 B]
-constexpr int TC_AUX = 4 * 8 + 16 + 8 * 4 + 4 * TC_QT * 4;  // barriers, TMEM slot, key mask, row max / sum exchange
-static_assert(TC_SP <= TC_SQ + TC_SK, "the probabilities reuse the Q / K region");
-constexpr int TC_SMEM = TC_SQ + TC_SK + TC_SV + TC_AUX + 1024;
-constexpr uint32_t TC_TMEM_COLS = 512;        // scores 256 + output 128, rounded up to a power of two
+constexpr int TC_SP = 4 * TC_QT * 128;        // probabilities of one query tile: four 64-key atoms of [128 rows][128 B]
+constexpr int TC_AUX = 8 * 8 + 16 + 8 * 4 + 4 * TC_QT * 4;  // barriers, TMEM slot, key mask, row max / sum exchange
+static_assert(TC_SP == 2 * TC_SQ && TC_SP == TC_SK, "the probabilities reuse the query region (tile 0) and the key region (tile 1)");
+constexpr int TC_SMEM = TC_SK + TC_SV + 2 * TC_SQ + TC_AUX + 1024;
+constexpr uint32_t TC_TMEM_COLS = 512;        // two score tiles of 256 columns; each output tile reuses 128 columns of its scores
 
 struct TcParams {
     const uint8_t* key_pad;
@@ -52,57 +52,64 @@ __device__ __forceinline__ float ex2(float x) {
     return y;
 }
 
+// One CTA per (dialogue, head): both 128-row query tiles share one copy of K and V.
+//   MMA thread:      S0 = Q0 K^T, S1 = Q1 K^T back to back; O0 = P0 V once the softmax threads have written P0; O1 = P1 V.
+//   softmax threads: softmax(S0) -> P0 (over the dead Q tiles), softmax(S1) -> P1 (over the dead K tile) while the tensor core
+//                    works on O0, then the two output tiles (O_t reuses the first 128 TMEM columns of S_t).
 __global__ void __launch_bounds__(TC_THREADS, 1)
 attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__ CUtensorMap tk, const __grid_constant__ CUtensorMap tv,
                    const TcParams p) {
     extern __shared__ uint8_t tc_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(tc_raw) + 1023) & ~uintptr_t(1023));
-    uint8_t* sQ = smem;
-    uint8_t* sK = sQ + TC_SQ;
+    uint8_t* sK = smem;
     uint8_t* sV = sK + TC_SK;
-    uint8_t* sP = sQ;  // Q and K are dead once the scores are complete (bar_s), which is when the probabilities are written
-    uint64_t* bar_qk = reinterpret_cast<uint64_t*>(sV + TC_SV);  // Q and K landed
-    uint64_t* bar_v = bar_qk + 1;                                // V landed
-    uint64_t* bar_s = bar_qk + 2;                                // scores complete in TMEM
-    uint64_t* bar_o = bar_qk + 3;                                // output complete in TMEM
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bar_qk + 4);
+    uint8_t* sQ = sV + TC_SV;  // tile t at sQ + t * TC_SQ
+    uint64_t* bars = reinterpret_cast<uint64_t*>(sQ + 2 * TC_SQ);
+    uint64_t* bar_q0k = bars;      // Q tile 0 and K landed
+    uint64_t* bar_q1 = bars + 1;   // Q tile 1 landed
+    uint64_t* bar_v = bars + 2;    // V landed
+    uint64_t* bar_s = bars + 3;    // [2] scores of tile t complete in TMEM
+    uint64_t* bar_o = bars + 5;    // [2] output of tile t complete in TMEM
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 8);
     uint32_t* key_ok = tmem_slot + 4;                            // 8 words: bit j of word w = key 32 w + j is usable
     float* red_max = reinterpret_cast<float*>(key_ok + 8);       // [2][128]
     float* red_sum = red_max + 2 * TC_QT;                        // [2][128]
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int b = blockIdx.x / p.H, h = blockIdx.x - b * p.H;
-    const int q0 = blockIdx.y * TC_QT;
     const int row0 = b * p.S;          // first row of the dialogue in the [B*S, E] matrices
     const int col0 = h * p.hd;
     const int ksteps = p.hd / 16;      // k-steps of the first product (hd = 64 / 96 / 128)
+    const int ntiles = p.S > TC_QT ? 2 : 1;
 
     if (warp == 8 && lane == 0) {
         ptx::prefetch_tensormap(&tq);
         ptx::prefetch_tensormap(&tk);
         ptx::prefetch_tensormap(&tv);
-        ptx::mbar_init(bar_qk, 1);
-        ptx::mbar_init(bar_v, 1);
-        ptx::mbar_init(bar_s, 1);
-        ptx::mbar_init(bar_o, 1);
+        for (int i = 0; i < 7; ++i) ptx::mbar_init(bars + i, 1);
         ptx::fence_barrier_init();
     }
     if (warp == 0) ptx::tmem_alloc(tmem_slot, TC_TMEM_COLS);
     ptx::tcgen05_fence_before();
     __syncthreads();
     ptx::tcgen05_fence_after();
-    const uint32_t tmem_s = *tmem_slot, tmem_o = tmem_s + 256u;
+    const uint32_t tmem_base = *tmem_slot;
     pdl_wait();
     pdl_trigger();
 
     if (warp == 8) {
         if (ptx::elect_one()) {
-            // ---------------------------------------------------------------- loads
-            ptx::mbar_expect_tx(bar_qk, TC_SQ + TC_SK);
+            // ---------------------------------------------------------------- loads: what the first product needs goes first
+            ptx::mbar_expect_tx(bar_q0k, TC_SQ + TC_SK);
 #pragma unroll
             for (int a = 0; a < 2; ++a) {
-                ptx::tma_load_3d(sQ + a * (TC_QT * 128), &tq, bar_qk, col0 + a * 64, row0 + q0, 0);
-                ptx::tma_load_3d(sK + a * (TC_KEYS * 128), &tk, bar_qk, col0 + a * 64, row0, 0);
+                ptx::tma_load_3d(sQ + a * (TC_QT * 128), &tq, bar_q0k, col0 + a * 64, row0, 0);
+                ptx::tma_load_3d(sK + a * (TC_KEYS * 128), &tk, bar_q0k, col0 + a * 64, row0, 0);
+            }
+            if (ntiles == 2) {
+                ptx::mbar_expect_tx(bar_q1, TC_SQ);
+#pragma unroll
+                for (int a = 0; a < 2; ++a) ptx::tma_load_3d(sQ + TC_SQ + a * (TC_QT * 128), &tq, bar_q1, col0 + a * 64, row0 + TC_QT, 0);
             }
             ptx::mbar_expect_tx(bar_v, TC_SV);
 #pragma unroll
@@ -110,38 +117,43 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant
 #pragma unroll
                 for (int a = 0; a < 2; ++a)
                     ptx::tma_load_3d(sV + kb * 16384 + a * 8192, &tv, bar_v, col0 + a * 64, row0 + kb * 64, 0);
-            // ---------------------------------------------------------------- S = Q K^T
-            ptx::mbar_wait(bar_qk, 0);
-            ptx::tcgen05_fence_after();
+            // ---------------------------------------------------------------- S_t = Q_t K^T
             constexpr uint32_t idesc_qk = ptx::instr_desc_bf16(TC_QT, TC_KEYS, false, false);
-            for (int k = 0; k < ksteps; ++k) {
-                const uint32_t off = (uint32_t)(k >> 2) * 128u, kin = (uint32_t)(k & 3) * 32u;  // atom, 16 columns = 32 B inside it
-                const uint64_t ad = ptx::smem_desc_sw128(ptx::smem_u32(sQ) + off * TC_QT + kin, 0, 1024);
-                const uint64_t bd = ptx::smem_desc_sw128(ptx::smem_u32(sK) + off * TC_KEYS + kin, 0, 1024);
-                ptx::umma_bf16(tmem_s, ad, bd, idesc_qk, k > 0 ? 1u : 0u);
-            }
-            ptx::umma_commit(bar_s);
-        }
-        __syncwarp();
-        // the probabilities are in shared memory once all 256 softmax threads have passed the named barrier below
-        ptx::named_bar_sync(2, TC_THREADS);
-        if (ptx::elect_one()) {
-            // ---------------------------------------------------------------- O = P V
-            ptx::mbar_wait(bar_v, 0);
-            ptx::tcgen05_fence_after();
-            constexpr uint32_t idesc_pv = ptx::instr_desc_bf16(TC_QT, 128, false, true);
-#pragma unroll 1
-            for (int kb = 0; kb < 4; ++kb) {
-#pragma unroll
-                for (int k = 0; k < 4; ++k) {
-                    const uint64_t ad = ptx::smem_desc_sw128(ptx::smem_u32(sP) + kb * (TC_QT * 128) + k * 32, 0, 1024);
-                    const uint64_t bd = ptx::smem_desc_sw128(ptx::smem_u32(sV) + kb * 16384 + k * 2048, 8192, 1024);
-                    ptx::umma_bf16(tmem_o, ad, bd, idesc_pv, (kb > 0 || k > 0) ? 1u : 0u);
+            for (int t = 0; t < ntiles; ++t) {
+                ptx::mbar_wait(t == 0 ? bar_q0k : bar_q1, 0);
+                ptx::tcgen05_fence_after();
+                for (int k = 0; k < ksteps; ++k) {
+                    const uint32_t off = (uint32_t)(k >> 2) * 128u, kin = (uint32_t)(k & 3) * 32u;  // atom, 16 columns = 32 B inside it
+                    const uint64_t ad = ptx::smem_desc_sw128(ptx::smem_u32(sQ) + t * TC_SQ + off * TC_QT + kin, 0, 1024);
+                    const uint64_t bd = ptx::smem_desc_sw128(ptx::smem_u32(sK) + off * TC_KEYS + kin, 0, 1024);
+                    ptx::umma_bf16(tmem_base + (uint32_t)t * 256u, ad, bd, idesc_qk, k > 0 ? 1u : 0u);
                 }
+                ptx::umma_commit(&bar_s[t]);
             }
-            ptx::umma_commit(bar_o);
         }
         __syncwarp();
+        for (int t = 0; t < ntiles; ++t) {
+            // the probabilities of tile t are in shared memory once all 256 softmax threads have passed this named barrier
+            ptx::named_bar_sync(2 + t, TC_THREADS);
+            if (ptx::elect_one()) {
+                // ------------------------------------------------------------ O_t = P_t V
+                if (t == 0) ptx::mbar_wait(bar_v, 0);
+                ptx::tcgen05_fence_after();
+                constexpr uint32_t idesc_pv = ptx::instr_desc_bf16(TC_QT, 128, false, true);
+                const uint32_t sP = ptx::smem_u32(t == 0 ? sQ : sK);
+#pragma unroll 1
+                for (int kb = 0; kb < 4; ++kb) {
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) {
+                        const uint64_t ad = ptx::smem_desc_sw128(sP + kb * (TC_QT * 128) + k * 32, 0, 1024);
+                        const uint64_t bd = ptx::smem_desc_sw128(ptx::smem_u32(sV) + kb * 16384 + k * 2048, 8192, 1024);
+                        ptx::umma_bf16(tmem_base + (uint32_t)t * 256u, ad, bd, idesc_pv, (kb > 0 || k > 0) ? 1u : 0u);
+                    }
+                }
+                ptx::umma_commit(&bar_o[t]);
+            }
+            __syncwarp();
+        }
     } else {
         // -------------------------------------------------------------------- softmax: thread = (query row, half of the keys)
         const int lg = warp & 3, half = warp >> 2;
@@ -153,75 +165,90 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant
             if (lane == 0) key_ok[warp] = word;
         }
         ptx::named_bar_sync(1, TC_SOFTMAX_THREADS);
-        ptx::mbar_wait(bar_s, 0);
-        ptx::tcgen05_fence_after();
-        const uint32_t t_row = tmem_s + ((uint32_t)(lg * 32) << 16) + (uint32_t)(half * 128);
-        float mx = -INFINITY;
-#pragma unroll 1
-        for (int c = 0; c < 4; ++c) {
-            uint32_t r[32];
-            ptx::tmem_ld_32x32(t_row + (uint32_t)(c * 32), r);
-            ptx::tmem_ld_wait();
-            const uint32_t w = key_ok[half * 4 + c];
-#pragma unroll
-            for (int j = 0; j < 32; ++j) mx = fmaxf(mx, ((w >> j) & 1u) ? __uint_as_float(r[j]) : -INFINITY);
-        }
-        red_max[half * TC_QT + row] = mx;
-        ptx::named_bar_sync(1, TC_SOFTMAX_THREADS);
-        mx = fmaxf(mx, red_max[(half ^ 1) * TC_QT + row]);
-        if (mx == -INFINITY) mx = 0.f;  // no usable key at all: every probability is 0 (such rows are never stored)
-        const float mscaled = mx * p.scale_log2;
-        float sum = 0.f;
-        const uint32_t p_row = ptx::smem_u32(sP) + (uint32_t)row * 128u;
         const uint32_t sw = (uint32_t)(row & 7);
+        float inv[2] = {0.f, 0.f};
+#pragma unroll
+        for (int t = 0; t < 2; ++t) {
+            if (t < ntiles) {
+                ptx::mbar_wait(&bar_s[t], 0);
+                ptx::tcgen05_fence_after();
+                const uint32_t t_row = tmem_base + (uint32_t)t * 256u + ((uint32_t)(lg * 32) << 16) + (uint32_t)(half * 128);
+                float mx = -INFINITY;
 #pragma unroll 1
-        for (int c = 0; c < 4; ++c) {
-            uint32_t r[32];
-            ptx::tmem_ld_32x32(t_row + (uint32_t)(c * 32), r);
-            ptx::tmem_ld_wait();
-            const uint32_t w = key_ok[half * 4 + c];
-            uint32_t pk[16];
+                for (int c = 0; c < 4; ++c) {
+                    uint32_t r[32];
+                    ptx::tmem_ld_32x32(t_row + (uint32_t)(c * 32), r);
+                    ptx::tmem_ld_wait();
+                    const uint32_t w = key_ok[half * 4 + c];
 #pragma unroll
-            for (int j = 0; j < 16; ++j) {
-                const float e0 = ((w >> (2 * j)) & 1u) ? ex2(fmaf(__uint_as_float(r[2 * j]), p.scale_log2, -mscaled)) : 0.f;
-                const float e1 = ((w >> (2 * j + 1)) & 1u) ? ex2(fmaf(__uint_as_float(r[2 * j + 1]), p.scale_log2, -mscaled)) : 0.f;
-                sum += e0 + e1;
-                pk[j] = pack2(e0, e1);
-            }
-            // keys half * 128 + c * 32 .. + 31: atom (64 keys) = half * 2 + c / 2, 16-byte chunks (c & 1) * 4 .. + 3 of the row's line
-            const uint32_t atom = p_row + (uint32_t)(half * 2 + (c >> 1)) * (TC_QT * 128);
+                    for (int j = 0; j < 32; ++j) mx = fmaxf(mx, ((w >> j) & 1u) ? __uint_as_float(r[j]) : -INFINITY);
+                }
+                red_max[half * TC_QT + row] = mx;
+                ptx::named_bar_sync(1, TC_SOFTMAX_THREADS);
+                mx = fmaxf(mx, red_max[(half ^ 1) * TC_QT + row]);
+                if (mx == -INFINITY) mx = 0.f;  // no usable key at all: every probability is 0 (such rows are never stored)
+                const float mscaled = mx * p.scale_log2;
+                // P0 overwrites both query tiles: the second score tile must be complete before the first probability is written
+                if (t == 0 && ntiles == 2) ptx::mbar_wait(&bar_s[1], 0);
+                float sum = 0.f;
+                const uint32_t p_row = ptx::smem_u32(t == 0 ? sQ : sK) + (uint32_t)row * 128u;
+#pragma unroll 1
+                for (int c = 0; c < 4; ++c) {
+                    uint32_t r[32];
+                    ptx::tmem_ld_32x32(t_row + (uint32_t)(c * 32), r);
+                    ptx::tmem_ld_wait();
+                    const uint32_t w = key_ok[half * 4 + c];
+                    uint32_t pk[16];
 #pragma unroll
-            for (int q = 0; q < 4; ++q) {
-                const uint32_t chunk = ((uint32_t)((c & 1) * 4 + q)) ^ sw;
-                asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(atom + (chunk << 4)), "r"(pk[4 * q]), "r"(pk[4 * q + 1]),
-                             "r"(pk[4 * q + 2]), "r"(pk[4 * q + 3])
-                             : "memory");
+                    for (int j = 0; j < 16; ++j) {
+                        const float e0 = ((w >> (2 * j)) & 1u) ? ex2(fmaf(__uint_as_float(r[2 * j]), p.scale_log2, -mscaled)) : 0.f;
+                        const float e1 = ((w >> (2 * j + 1)) & 1u) ? ex2(fmaf(__uint_as_float(r[2 * j + 1]), p.scale_log2, -mscaled)) : 0.f;
+                        sum += e0 + e1;
+                        pk[j] = pack2(e0, e1);
+                    }
+                    // keys half * 128 + c * 32 .. + 31: atom (64 keys) = half * 2 + c / 2, 16-byte chunks (c & 1) * 4 .. + 3 of the row's line
+                    const uint32_t atom = p_row + (uint32_t)(half * 2 + (c >> 1)) * (TC_QT * 128);
+#pragma unroll
+                    for (int q = 0; q < 4; ++q) {
+                        const uint32_t chunk = ((uint32_t)((c & 1) * 4 + q)) ^ sw;
+                        asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(atom + (chunk << 4)), "r"(pk[4 * q]), "r"(pk[4 * q + 1]),
+                                     "r"(pk[4 * q + 2]), "r"(pk[4 * q + 3])
+                                     : "memory");
+                    }
+                }
+                red_sum[half * TC_QT + row] = sum;
+                ptx::fence_proxy_async();      // the probabilities are read by the tensor core through the async proxy
+                ptx::tcgen05_fence_before();   // ... and this tile's score columns are about to be overwritten by its output
+                ptx::named_bar_sync(2 + t, TC_THREADS);  // releases the MMA thread; also orders red_sum for the partner thread
+                inv[t] = 1.f / (sum + red_sum[(half ^ 1) * TC_QT + row]);
             }
         }
-        red_sum[half * TC_QT + row] = sum;
-        ptx::fence_proxy_async();      // the probabilities are read by the tensor core through the async proxy
-        ptx::tcgen05_fence_before();
-        ptx::named_bar_sync(2, TC_THREADS);  // releases the MMA thread; also orders red_sum for the partner thread
-        const float inv = 1.f / (sum + red_sum[(half ^ 1) * TC_QT + row]);
-        ptx::mbar_wait(bar_o, 0);
-        ptx::tcgen05_fence_after();
-        // output columns: half 0 takes 0 .. 63, half 1 takes 64 .. hd - 1
+        // -------------------------------------------------------------------- outputs: half 0 stores columns 0 .. 63, half 1 the rest
         const int c_lo = half * 64, c_hi = min(p.hd, c_lo + 64);
-        const bool live = q0 + row < p.S;
-        __nv_bfloat16* orow = p.o + ((int64_t)row0 + q0 + row) * p.o_ld + col0;
-        for (int cc = c_lo; cc < c_hi; cc += 32) {  // warp-uniform
-            uint32_t r[32];
-            ptx::tmem_ld_32x32(tmem_o + ((uint32_t)(lg * 32) << 16) + (uint32_t)cc, r);
-            ptx::tmem_ld_wait();
-            if (live) {
 #pragma unroll
-                for (int q = 0; q < 4; ++q) {
-                    uint4 v4;
-                    v4.x = pack2(__uint_as_float(r[8 * q]) * inv, __uint_as_float(r[8 * q + 1]) * inv);
-                    v4.y = pack2(__uint_as_float(r[8 * q + 2]) * inv, __uint_as_float(r[8 * q + 3]) * inv);
-                    v4.z = pack2(__uint_as_float(r[8 * q + 4]) * inv, __uint_as_float(r[8 * q + 5]) * inv);
-                    v4.w = pack2(__uint_as_float(r[8 * q + 6]) * inv, __uint_as_float(r[8 * q + 7]) * inv);
-                    *reinterpret_cast<uint4*>(orow + cc + 8 * q) = v4;
+        for (int t = 0; t < 2; ++t) {
+            if (t < ntiles) {
+                ptx::mbar_wait(&bar_o[t], 0);
+                ptx::tcgen05_fence_after();
+                const int qrow = t * TC_QT + row;
+                const bool live = qrow < p.S;
+                __nv_bfloat16* orow = p.o + ((int64_t)row0 + qrow) * p.o_ld + col0;
+                const float iv = inv[t];
+                for (int cc = c_lo; cc < c_hi; cc += 32) {  // warp-uniform
+                    uint32_t r[32];
+                    ptx::tmem_ld_32x32(tmem_base + (uint32_t)t * 256u + ((uint32_t)(lg * 32) << 16) + (uint32_t)cc, r);
+                    ptx::tmem_ld_wait();
+                    if (live) {
+#pragma unroll
+                        for (int q = 0; q < 4; ++q) {
+                            uint4 v4;
+                            v4.x = pack2(__uint_as_float(r[8 * q]) * iv, __uint_as_float(r[8 * q + 1]) * iv);
+                            v4.y = pack2(__uint_as_float(r[8 * q + 2]) * iv, __uint_as_float(r[8 * q + 3]) * iv);
+                            v4.z = pack2(__uint_as_float(r[8 * q + 4]) * iv, __uint_as_float(r[8 * q + 5]) * iv);
+                            v4.w = pack2(__uint_as_float(r[8 * q + 6]) * iv, __uint_as_float(r[8 * q + 7]) * iv);
+                            *reinterpret_cast<uint4*>(orow + cc + 8 * q) = v4;
+                        }
+                    }
                 }
             }
         }
@@ -230,7 +257,7 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant
     __syncthreads();
     if (warp == 0) {
         ptx::tcgen05_fence_after();
-        ptx::tmem_dealloc(tmem_s, TC_TMEM_COLS);
+        ptx::tmem_dealloc(tmem_base, TC_TMEM_COLS);
     }
 }
 
@@ -261,7 +288,7 @@ int fwd_long_tc(int hd, const m2f_planes_t* q, const m2f_planes_t* k, const m2f_
     p.H = H;
     p.hd = hd;
     p.scale_log2 = 1.4426950408889634f / sqrtf((float)hd);
-    M2F_CUDA(launch_chain(attn_fwd_tc_kernel, dim3((unsigned)(B * H), (unsigned)((S + TC_QT - 1) / TC_QT)), dim3(TC_THREADS), (size_t)TC_SMEM, st,
+    M2F_CUDA(launch_chain(attn_fwd_tc_kernel, dim3((unsigned)(B * H)), dim3(TC_THREADS), (size_t)TC_SMEM, st,
                           1, tq, tk, tv, p));
     M2F_LAUNCH_CHECK();
     return M2F_OK;
