@@ -818,7 +818,10 @@ int gemm_block_n(int64_t M, int64_t N, int64_t K) {
     // from the neighbours, and what counts is the L2 -> SM operand traffic per flop, which pairs halve for B: the whole train
     // step is 3.7 % (bf16) / 6.5 % (fp32-parity) faster with pairs everywhere (profiles/r1_ab_gemm_pairs.txt).
     static const int pairs = [] { const char* e = std::getenv("M2F_GEMM_CTA2"); return e ? std::atoi(e) : 1; }();
-    if (pairs == 1 && N > 64) {
+    // ... except with very many row tiles (M >= 65 536: the C5 inference batch has 1024): there every launch is many waves, and two
+    // single CTAs per SM, one in its epilogue while the other is in its main loop, beat one pair per SM whose epilogue overlaps
+    // nothing (C5 batch 43.5 -> 41.5 ms, tools/gpu_r2_c5_tiles.sh).
+    if (pairs == 1 && N > 64 && mt < 512) {
         const int bn = (forced == 128 || forced == 256) ? forced : 256;
         return ((N <= 128) ? 128 : bn) | GEMM_TILE_CTA2;
     }
