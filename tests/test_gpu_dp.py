@@ -76,4 +76,7 @@ def test_dp2_gradients_equal_single_gpu(tmp_path):
     r = torch.load(out)
     assert r["same"] and r["buckets"] >= 3
     assert r["err"] < 2e-5, r
-    assert r["param_err_after_4_steps"] < 1e-5, r
+    # four Adam steps (lr 1e-3) later the two runs may differ by what the 6e-8 of summation-order noise in the first gradients grows
+    # into (Adam divides by sqrt(v): small gradient entries move by lr whatever their size) -- measured 0.9e-5 .. 1.2e-5; a bucket
+    # reduced before its producers finished (what this part of the test is for) shows up as 1e-2 and more
+    assert r["param_err_after_4_steps"] < 5e-5, r
