@@ -280,6 +280,24 @@ __device__ __forceinline__ void store_planes4(__nv_bfloat16* base, int64_t plane
     }
 }
 
+// ------------------------------------------------------------------ streaming accesses
+// L2 eviction policy "evict first" for data that is touched once per step (optimizer state, master weights, consumed gradients):
+// the optimizer pass streams 2.8 GB through a 126 MB L2 that, when the pass runs beside the backward (data parallel), also holds
+// the operands the GEMMs re-read (activations of a layer, weight tiles shared by a column of CTAs).
+__device__ __forceinline__ uint64_t l2_evict_first_policy() {
+    uint64_t pol;
+    asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
+    return pol;
+}
+__device__ __forceinline__ float4 ldg_stream4(const float* ptr, uint64_t pol) {
+    float4 v;
+    asm volatile("ld.global.L2::cache_hint.v4.f32 {%0, %1, %2, %3}, [%4], %5;" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(ptr), "l"(pol));
+    return v;
+}
+__device__ __forceinline__ void stg_stream4(float* ptr, const float4 v, uint64_t pol) {
+    asm volatile("st.global.L2::cache_hint.v4.f32 [%0], {%1, %2, %3, %4}, %5;" ::"l"(ptr), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w), "l"(pol) : "memory");
+}
+
 // ------------------------------------------------------------------ warp helpers
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll
