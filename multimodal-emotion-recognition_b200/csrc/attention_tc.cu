@@ -17,6 +17,8 @@
 #include <math.h>
 #include <stdlib.h>
 
+#include <algorithm>
+
 #include "attention_mma.cuh"
 #include "gemm.cuh"
 #include "ptx.cuh"
@@ -32,18 +34,19 @@ constexpr int TC_THREADS = TC_SOFTMAX_THREADS + 32;
 constexpr int TC_SQ = 2 * TC_QT * 128;        // one query tile: two 64-column atoms of [128 rows][128 B]
 constexpr int TC_SK = 2 * TC_KEYS * 128;      // two atoms of [256 rows][128 B]
 constexpr int TC_SV = 4 * 2 * 64 * 128;       // four 64-key blocks x two 64-column atoms of [64 rows][128 B]
-constexpr int TC_SP = 4 * TC_QT * 128;        // probabilities of one query tile: four 64-key atoms of [128 rows][128 B]
-constexpr int TC_AUX = 8 * 8 + 16 + 8 * 4 + 4 * TC_QT * 4;  // barriers, TMEM slot, key mask, row max / sum exchange
-static_assert(TC_SP == 2 * TC_SQ && TC_SP == TC_SK, "the probabilities reuse the query region (tile 0) and the key region (tile 1)");
-constexpr int TC_SMEM = TC_SK + TC_SV + 2 * TC_SQ + TC_AUX + 1024;
+constexpr int TC_AUX = 16 * 8 + 16 + 8 * 4 + 4 * TC_QT * 4;  // barriers, TMEM slot, key mask, row max / sum exchange
+// K | V | three 32 KB regions: two hold the query tiles of the current (dialogue, head) and then, two 64-key atoms each, its
+// probabilities; the third receives the first query tile of the NEXT one.  No alignment slack: the base is checked at run time.
+constexpr int TC_SMEM = TC_SK + TC_SV + 3 * TC_SQ + TC_AUX;
+static_assert(TC_SMEM <= 227 * 1024, "shared memory budget");
 constexpr uint32_t TC_TMEM_COLS = 512;        // two score tiles of 256 columns; each output tile reuses 128 columns of its scores
 
 struct TcParams {
     const uint8_t* key_pad;
     __nv_bfloat16* o;
     int64_t o_ld;
-    int S, H, hd;
-    float scale_log2;  // log2(e) / sqrt(hd)
+    int S, H, hd, items;  // items = dialogues x heads
+    float scale_log2;     // log2(e) / sqrt(hd)
 };
 
 __device__ __forceinline__ float ex2(float x) {
@@ -52,41 +55,48 @@ __device__ __forceinline__ float ex2(float x) {
     return y;
 }
 
-// One CTA per (dialogue, head): both 128-row query tiles share one copy of K and V.
-//   MMA thread:      S0 = Q0 K^T, S1 = Q1 K^T back to back; O0 = P0 V once the softmax threads have written P0; O1 = P1 V.
-//   softmax threads: softmax(S0) -> P0 (over the dead Q tiles), softmax(S1) -> P1 (over the dead K tile) while the tensor core
-//                    works on O0, then the two output tiles (O_t reuses the first 128 TMEM columns of S_t).
+// Persistent: CTA c works on (dialogue, head) items c, c + gridDim.x, ...; both 128-row query tiles of an item share one copy of K, V.
+//   warp 8, lane 0:  TMA loads and MMA issue.  Per item: S0 = Q0 K^T, S1 = Q1 K^T back to back; as soon as they are complete the key
+//                    tile and the spare query region take the NEXT item's K and Q0; O0 = P0 V when the softmax threads have written
+//                    P0, then O1 = P1 V; when that is complete V and the other query tile of the next item are requested.  So the
+//                    loads of item i + 1 travel under the softmax / PV / output phases of item i.
+//   warps 0-7:       softmax(S0) -> P0 (over the dead query tiles), softmax(S1) -> P1 (same place, once O0 is complete), then the two
+//                    output tiles (O_t reuses the first 128 TMEM columns of S_t; the MMA thread waits for them to be read before
+//                    it overwrites S_t for the next item).
 __global__ void __launch_bounds__(TC_THREADS, 1)
 attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__ CUtensorMap tk, const __grid_constant__ CUtensorMap tv,
                    const TcParams p) {
-    extern __shared__ uint8_t tc_raw[];
-    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(tc_raw) + 1023) & ~uintptr_t(1023));
+    extern __shared__ __align__(1024) uint8_t smem[];
     uint8_t* sK = smem;
     uint8_t* sV = sK + TC_SK;
-    uint8_t* sQ = sV + TC_SV;  // tile t at sQ + t * TC_SQ
-    uint64_t* bars = reinterpret_cast<uint64_t*>(sQ + 2 * TC_SQ);
+    uint8_t* sR = sV + TC_SV;  // region r at sR + r * TC_SQ
+    uint64_t* bars = reinterpret_cast<uint64_t*>(sR + 3 * TC_SQ);
     uint64_t* bar_q0k = bars;      // Q tile 0 and K landed
     uint64_t* bar_q1 = bars + 1;   // Q tile 1 landed
     uint64_t* bar_v = bars + 2;    // V landed
     uint64_t* bar_s = bars + 3;    // [2] scores of tile t complete in TMEM
     uint64_t* bar_o = bars + 5;    // [2] output of tile t complete in TMEM
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 8);
+    uint64_t* bar_free = bars + 7; // [2] output of tile t has been read: its TMEM columns may take the next item's scores
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 16);
     uint32_t* key_ok = tmem_slot + 4;                            // 8 words: bit j of word w = key 32 w + j is usable
     float* red_max = reinterpret_cast<float*>(key_ok + 8);       // [2][128]
     float* red_sum = red_max + 2 * TC_QT;                        // [2][128]
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int b = blockIdx.x / p.H, h = blockIdx.x - b * p.H;
-    const int row0 = b * p.S;          // first row of the dialogue in the [B*S, E] matrices
-    const int col0 = h * p.hd;
     const int ksteps = p.hd / 16;      // k-steps of the first product (hd = 64 / 96 / 128)
     const int ntiles = p.S > TC_QT ? 2 : 1;
 
+    if (threadIdx.x == 0 && (ptx::smem_u32(smem) & 1023u) != 0) {
+        printf("m2f: attn_fwd_tc_kernel needs a 1024-byte aligned shared-memory base\n");
+        __trap();
+    }
     if (warp == 8 && lane == 0) {
         ptx::prefetch_tensormap(&tq);
         ptx::prefetch_tensormap(&tk);
         ptx::prefetch_tensormap(&tv);
         for (int i = 0; i < 7; ++i) ptx::mbar_init(bars + i, 1);
+        ptx::mbar_init(&bar_free[0], TC_SOFTMAX_THREADS);
+        ptx::mbar_init(&bar_free[1], TC_SOFTMAX_THREADS);
         ptx::fence_barrier_init();
     }
     if (warp == 0) ptx::tmem_alloc(tmem_slot, TC_TMEM_COLS);
@@ -97,160 +107,204 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant
     pdl_wait();
     pdl_trigger();
 
+    // region roles: query tile 0 in ra, query tile 1 in rb, rc spare; they rotate (ra, rb, rc) <- (rc, ra, rb) per item
+    int ra = 0, rb = 1, rc = 2;
     if (warp == 8) {
-        if (ptx::elect_one()) {
-            // ---------------------------------------------------------------- loads: what the first product needs goes first
+        auto load_q0k = [&](int item, int r) {
+            const int row0 = (item / p.H) * p.S, col0 = (item % p.H) * p.hd;
             ptx::mbar_expect_tx(bar_q0k, TC_SQ + TC_SK);
 #pragma unroll
             for (int a = 0; a < 2; ++a) {
-                ptx::tma_load_3d(sQ + a * (TC_QT * 128), &tq, bar_q0k, col0 + a * 64, row0, 0);
+                ptx::tma_load_3d(sR + r * TC_SQ + a * (TC_QT * 128), &tq, bar_q0k, col0 + a * 64, row0, 0);
                 ptx::tma_load_3d(sK + a * (TC_KEYS * 128), &tk, bar_q0k, col0 + a * 64, row0, 0);
             }
-            if (ntiles == 2) {
-                ptx::mbar_expect_tx(bar_q1, TC_SQ);
+        };
+        auto load_q1 = [&](int item, int r) {
+            const int row0 = (item / p.H) * p.S, col0 = (item % p.H) * p.hd;
+            ptx::mbar_expect_tx(bar_q1, TC_SQ);
 #pragma unroll
-                for (int a = 0; a < 2; ++a) ptx::tma_load_3d(sQ + TC_SQ + a * (TC_QT * 128), &tq, bar_q1, col0 + a * 64, row0 + TC_QT, 0);
-            }
+            for (int a = 0; a < 2; ++a) ptx::tma_load_3d(sR + r * TC_SQ + a * (TC_QT * 128), &tq, bar_q1, col0 + a * 64, row0 + TC_QT, 0);
+        };
+        auto load_v = [&](int item) {
+            const int row0 = (item / p.H) * p.S, col0 = (item % p.H) * p.hd;
             ptx::mbar_expect_tx(bar_v, TC_SV);
 #pragma unroll
             for (int kb = 0; kb < 4; ++kb)
 #pragma unroll
                 for (int a = 0; a < 2; ++a)
                     ptx::tma_load_3d(sV + kb * 16384 + a * 8192, &tv, bar_v, col0 + a * 64, row0 + kb * 64, 0);
-            // ---------------------------------------------------------------- S_t = Q_t K^T
-            constexpr uint32_t idesc_qk = ptx::instr_desc_bf16(TC_QT, TC_KEYS, false, false);
-            for (int t = 0; t < ntiles; ++t) {
-                ptx::mbar_wait(t == 0 ? bar_q0k : bar_q1, 0);
-                ptx::tcgen05_fence_after();
-                for (int k = 0; k < ksteps; ++k) {
-                    const uint32_t off = (uint32_t)(k >> 2) * 128u, kin = (uint32_t)(k & 3) * 32u;  // atom, 16 columns = 32 B inside it
-                    const uint64_t ad = ptx::smem_desc_sw128(ptx::smem_u32(sQ) + t * TC_SQ + off * TC_QT + kin, 0, 1024);
-                    const uint64_t bd = ptx::smem_desc_sw128(ptx::smem_u32(sK) + off * TC_KEYS + kin, 0, 1024);
-                    ptx::umma_bf16(tmem_base + (uint32_t)t * 256u, ad, bd, idesc_qk, k > 0 ? 1u : 0u);
-                }
-                ptx::umma_commit(&bar_s[t]);
-            }
+        };
+        if (lane == 0 && (int)blockIdx.x < p.items) {
+            load_q0k(blockIdx.x, ra);
+            if (ntiles == 2) load_q1(blockIdx.x, rb);
+            load_v(blockIdx.x);
         }
-        __syncwarp();
-        for (int t = 0; t < ntiles; ++t) {
-            // the probabilities of tile t are in shared memory once all 256 softmax threads have passed this named barrier
-            ptx::named_bar_sync(2 + t, TC_THREADS);
-            if (ptx::elect_one()) {
-                // ------------------------------------------------------------ O_t = P_t V
-                if (t == 0) ptx::mbar_wait(bar_v, 0);
-                ptx::tcgen05_fence_after();
-                constexpr uint32_t idesc_pv = ptx::instr_desc_bf16(TC_QT, 128, false, true);
-                const uint32_t sP = ptx::smem_u32(t == 0 ? sQ : sK);
-#pragma unroll 1
-                for (int kb = 0; kb < 4; ++kb) {
-#pragma unroll
-                    for (int k = 0; k < 4; ++k) {
-                        const uint64_t ad = ptx::smem_desc_sw128(sP + kb * (TC_QT * 128) + k * 32, 0, 1024);
-                        const uint64_t bd = ptx::smem_desc_sw128(ptx::smem_u32(sV) + kb * 16384 + k * 2048, 8192, 1024);
-                        ptx::umma_bf16(tmem_base + (uint32_t)t * 256u, ad, bd, idesc_pv, (kb > 0 || k > 0) ? 1u : 0u);
+        int it = 0;
+        for (int item = blockIdx.x; item < p.items; item += gridDim.x, ++it) {
+            const uint32_t ph = (uint32_t)(it & 1);
+            const int next = item + (int)gridDim.x;
+            const bool has_next = next < p.items;
+            if (lane == 0) {
+                // ------------------------------------------------------------ S_t = Q_t K^T
+                constexpr uint32_t idesc_qk = ptx::instr_desc_bf16(TC_QT, TC_KEYS, false, false);
+                for (int t = 0; t < ntiles; ++t) {
+                    ptx::mbar_wait(t == 0 ? bar_q0k : bar_q1, ph);
+                    if (it > 0) ptx::mbar_wait(&bar_free[t], ph ^ 1u);  // the previous item's output tile t has left TMEM
+                    ptx::tcgen05_fence_after();
+                    const uint32_t q_base = ptx::smem_u32(sR) + (uint32_t)(t == 0 ? ra : rb) * TC_SQ;
+                    for (int k = 0; k < ksteps; ++k) {
+                        const uint32_t off = (uint32_t)(k >> 2) * 128u, kin = (uint32_t)(k & 3) * 32u;  // atom, 16 columns = 32 B inside it
+                        const uint64_t ad = ptx::smem_desc_sw128(q_base + off * TC_QT + kin, 0, 1024);
+                        const uint64_t bd = ptx::smem_desc_sw128(ptx::smem_u32(sK) + off * TC_KEYS + kin, 0, 1024);
+                        ptx::umma_bf16(tmem_base + (uint32_t)t * 256u, ad, bd, idesc_qk, k > 0 ? 1u : 0u);
                     }
+                    ptx::umma_commit(&bar_s[t]);
                 }
-                ptx::umma_commit(&bar_o[t]);
+                if (has_next) {  // K and the spare region are free once the score products are complete
+                    ptx::mbar_wait(&bar_s[ntiles - 1], ph);
+                    load_q0k(next, rc);
+                }
             }
             __syncwarp();
+            for (int t = 0; t < ntiles; ++t) {
+                // the probabilities of tile t are in shared memory once all 256 softmax threads have passed this named barrier
+                ptx::named_bar_sync(2 + t, TC_THREADS);
+                if (lane == 0) {
+                    // -------------------------------------------------------- O_t = P_t V
+                    if (t == 0) ptx::mbar_wait(bar_v, ph);
+                    ptx::tcgen05_fence_after();
+                    constexpr uint32_t idesc_pv = ptx::instr_desc_bf16(TC_QT, 128, false, true);
+#pragma unroll 1
+                    for (int kb = 0; kb < 4; ++kb) {
+                        const uint32_t p_atom = ptx::smem_u32(sR) + (uint32_t)(kb < 2 ? ra : rb) * TC_SQ + (uint32_t)(kb & 1) * (TC_QT * 128);
+#pragma unroll
+                        for (int k = 0; k < 4; ++k) {
+                            const uint64_t ad = ptx::smem_desc_sw128(p_atom + k * 32, 0, 1024);
+                            const uint64_t bd = ptx::smem_desc_sw128(ptx::smem_u32(sV) + kb * 16384 + k * 2048, 8192, 1024);
+                            ptx::umma_bf16(tmem_base + (uint32_t)t * 256u, ad, bd, idesc_pv, (kb > 0 || k > 0) ? 1u : 0u);
+                        }
+                    }
+                    ptx::umma_commit(&bar_o[t]);
+                }
+                __syncwarp();
+            }
+            if (lane == 0 && has_next) {  // V and the probability regions are free once the last output product is complete
+                ptx::mbar_wait(&bar_o[ntiles - 1], ph);
+                load_v(next);
+                if (ntiles == 2) load_q1(next, ra);
+            }
+            __syncwarp();
+            const int r0 = ra;
+            ra = rc; rc = rb; rb = r0;
         }
     } else {
         // -------------------------------------------------------------------- softmax: thread = (query row, half of the keys)
         const int lg = warp & 3, half = warp >> 2;
         const int row = lg * 32 + lane;
-        {   // usable keys: inside the dialogue and not padded; warp w covers keys 32 w .. 32 w + 31
-            const int j = threadIdx.x;
-            const bool ok = j < p.S && p.key_pad[(int64_t)row0 + j] == 0;
-            const uint32_t word = __ballot_sync(0xffffffffu, ok);
-            if (lane == 0) key_ok[warp] = word;
-        }
-        ptx::named_bar_sync(1, TC_SOFTMAX_THREADS);
         const uint32_t sw = (uint32_t)(row & 7);
-        float inv[2] = {0.f, 0.f};
-#pragma unroll
-        for (int t = 0; t < 2; ++t) {
-            if (t < ntiles) {
-                ptx::mbar_wait(&bar_s[t], 0);
-                ptx::tcgen05_fence_after();
-                const uint32_t t_row = tmem_base + (uint32_t)t * 256u + ((uint32_t)(lg * 32) << 16) + (uint32_t)(half * 128);
-                float mx = -INFINITY;
-#pragma unroll 1
-                for (int c = 0; c < 4; ++c) {
-                    uint32_t r[32];
-                    ptx::tmem_ld_32x32(t_row + (uint32_t)(c * 32), r);
-                    ptx::tmem_ld_wait();
-                    const uint32_t w = key_ok[half * 4 + c];
-#pragma unroll
-                    for (int j = 0; j < 32; ++j) mx = fmaxf(mx, ((w >> j) & 1u) ? __uint_as_float(r[j]) : -INFINITY);
-                }
-                red_max[half * TC_QT + row] = mx;
-                ptx::named_bar_sync(1, TC_SOFTMAX_THREADS);
-                mx = fmaxf(mx, red_max[(half ^ 1) * TC_QT + row]);
-                if (mx == -INFINITY) mx = 0.f;  // no usable key at all: every probability is 0 (such rows are never stored)
-                const float mscaled = mx * p.scale_log2;
-                // P0 overwrites both query tiles: the second score tile must be complete before the first probability is written
-                if (t == 0 && ntiles == 2) ptx::mbar_wait(&bar_s[1], 0);
-                float sum = 0.f;
-                const uint32_t p_row = ptx::smem_u32(t == 0 ? sQ : sK) + (uint32_t)row * 128u;
-#pragma unroll 1
-                for (int c = 0; c < 4; ++c) {
-                    uint32_t r[32];
-                    ptx::tmem_ld_32x32(t_row + (uint32_t)(c * 32), r);
-                    ptx::tmem_ld_wait();
-                    const uint32_t w = key_ok[half * 4 + c];
-                    uint32_t pk[16];
-#pragma unroll
-                    for (int j = 0; j < 16; ++j) {
-                        const float e0 = ((w >> (2 * j)) & 1u) ? ex2(fmaf(__uint_as_float(r[2 * j]), p.scale_log2, -mscaled)) : 0.f;
-                        const float e1 = ((w >> (2 * j + 1)) & 1u) ? ex2(fmaf(__uint_as_float(r[2 * j + 1]), p.scale_log2, -mscaled)) : 0.f;
-                        sum += e0 + e1;
-                        pk[j] = pack2(e0, e1);
-                    }
-                    // keys half * 128 + c * 32 .. + 31: atom (64 keys) = half * 2 + c / 2, 16-byte chunks (c & 1) * 4 .. + 3 of the row's line
-                    const uint32_t atom = p_row + (uint32_t)(half * 2 + (c >> 1)) * (TC_QT * 128);
-#pragma unroll
-                    for (int q = 0; q < 4; ++q) {
-                        const uint32_t chunk = ((uint32_t)((c & 1) * 4 + q)) ^ sw;
-                        asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(atom + (chunk << 4)), "r"(pk[4 * q]), "r"(pk[4 * q + 1]),
-                                     "r"(pk[4 * q + 2]), "r"(pk[4 * q + 3])
-                                     : "memory");
-                    }
-                }
-                red_sum[half * TC_QT + row] = sum;
-                ptx::fence_proxy_async();      // the probabilities are read by the tensor core through the async proxy
-                ptx::tcgen05_fence_before();   // ... and this tile's score columns are about to be overwritten by its output
-                ptx::named_bar_sync(2 + t, TC_THREADS);  // releases the MMA thread; also orders red_sum for the partner thread
-                inv[t] = 1.f / (sum + red_sum[(half ^ 1) * TC_QT + row]);
+        const int c_lo = half * 64, c_hi = min(p.hd, c_lo + 64);  // output columns: half 0 stores 0 .. 63, half 1 the rest
+        int it = 0;
+        for (int item = blockIdx.x; item < p.items; item += gridDim.x, ++it) {
+            const uint32_t ph = (uint32_t)(it & 1);
+            const int row0 = (item / p.H) * p.S, col0 = (item % p.H) * p.hd;
+            {   // usable keys: inside the dialogue and not padded; warp w covers keys 32 w .. 32 w + 31
+                const int j = threadIdx.x;
+                const bool ok = j < p.S && p.key_pad[(int64_t)row0 + j] == 0;
+                const uint32_t word = __ballot_sync(0xffffffffu, ok);
+                if (lane == 0) key_ok[warp] = word;
             }
-        }
-        // -------------------------------------------------------------------- outputs: half 0 stores columns 0 .. 63, half 1 the rest
-        const int c_lo = half * 64, c_hi = min(p.hd, c_lo + 64);
+            ptx::named_bar_sync(1, TC_SOFTMAX_THREADS);
+            float inv[2] = {0.f, 0.f};
 #pragma unroll
-        for (int t = 0; t < 2; ++t) {
-            if (t < ntiles) {
-                ptx::mbar_wait(&bar_o[t], 0);
-                ptx::tcgen05_fence_after();
-                const int qrow = t * TC_QT + row;
-                const bool live = qrow < p.S;
-                __nv_bfloat16* orow = p.o + ((int64_t)row0 + qrow) * p.o_ld + col0;
-                const float iv = inv[t];
-                for (int cc = c_lo; cc < c_hi; cc += 32) {  // warp-uniform
-                    uint32_t r[32];
-                    ptx::tmem_ld_32x32(tmem_base + (uint32_t)t * 256u + ((uint32_t)(lg * 32) << 16) + (uint32_t)cc, r);
-                    ptx::tmem_ld_wait();
-                    if (live) {
+            for (int t = 0; t < 2; ++t) {
+                if (t < ntiles) {
+                    ptx::mbar_wait(&bar_s[t], ph);
+                    ptx::tcgen05_fence_after();
+                    const uint32_t t_row = tmem_base + (uint32_t)t * 256u + ((uint32_t)(lg * 32) << 16) + (uint32_t)(half * 128);
+                    float mx = -INFINITY;
+#pragma unroll 1
+                    for (int c = 0; c < 4; ++c) {
+                        uint32_t r[32];
+                        ptx::tmem_ld_32x32(t_row + (uint32_t)(c * 32), r);
+                        ptx::tmem_ld_wait();
+                        const uint32_t w = key_ok[half * 4 + c];
+#pragma unroll
+                        for (int j = 0; j < 32; ++j) mx = fmaxf(mx, ((w >> j) & 1u) ? __uint_as_float(r[j]) : -INFINITY);
+                    }
+                    red_max[half * TC_QT + row] = mx;
+                    ptx::named_bar_sync(1, TC_SOFTMAX_THREADS);
+                    mx = fmaxf(mx, red_max[(half ^ 1) * TC_QT + row]);
+                    if (mx == -INFINITY) mx = 0.f;  // no usable key at all: every probability is 0 (such rows are never stored)
+                    const float mscaled = mx * p.scale_log2;
+                    // the probabilities go where both query tiles were: tile 0 waits for the second score product, tile 1 for the
+                    // first output product (it reads P0 from the same place)
+                    if (t == 0 && ntiles == 2) ptx::mbar_wait(&bar_s[1], ph);
+                    if (t == 1) ptx::mbar_wait(&bar_o[0], ph);
+                    float sum = 0.f;
+                    // keys half * 128 .. + 127 = atoms 2 * half, 2 * half + 1 = the two atoms of region (half == 0 ? ra : rb)
+                    const uint32_t p_row = ptx::smem_u32(sR) + (uint32_t)(half == 0 ? ra : rb) * TC_SQ + (uint32_t)row * 128u;
+#pragma unroll 1
+                    for (int c = 0; c < 4; ++c) {
+                        uint32_t r[32];
+                        ptx::tmem_ld_32x32(t_row + (uint32_t)(c * 32), r);
+                        ptx::tmem_ld_wait();
+                        const uint32_t w = key_ok[half * 4 + c];
+                        uint32_t pk[16];
+#pragma unroll
+                        for (int j = 0; j < 16; ++j) {
+                            const float e0 = ((w >> (2 * j)) & 1u) ? ex2(fmaf(__uint_as_float(r[2 * j]), p.scale_log2, -mscaled)) : 0.f;
+                            const float e1 = ((w >> (2 * j + 1)) & 1u) ? ex2(fmaf(__uint_as_float(r[2 * j + 1]), p.scale_log2, -mscaled)) : 0.f;
+                            sum += e0 + e1;
+                            pk[j] = pack2(e0, e1);
+                        }
+                        // 32 keys = 16-byte chunks (c & 1) * 4 .. + 3 of the row's 128-byte line in atom c / 2 of the region
+                        const uint32_t atom = p_row + (uint32_t)(c >> 1) * (TC_QT * 128);
 #pragma unroll
                         for (int q = 0; q < 4; ++q) {
-                            uint4 v4;
-                            v4.x = pack2(__uint_as_float(r[8 * q]) * iv, __uint_as_float(r[8 * q + 1]) * iv);
-                            v4.y = pack2(__uint_as_float(r[8 * q + 2]) * iv, __uint_as_float(r[8 * q + 3]) * iv);
-                            v4.z = pack2(__uint_as_float(r[8 * q + 4]) * iv, __uint_as_float(r[8 * q + 5]) * iv);
-                            v4.w = pack2(__uint_as_float(r[8 * q + 6]) * iv, __uint_as_float(r[8 * q + 7]) * iv);
-                            *reinterpret_cast<uint4*>(orow + cc + 8 * q) = v4;
+                            const uint32_t chunk = ((uint32_t)((c & 1) * 4 + q)) ^ sw;
+                            asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(atom + (chunk << 4)), "r"(pk[4 * q]), "r"(pk[4 * q + 1]),
+                                         "r"(pk[4 * q + 2]), "r"(pk[4 * q + 3])
+                                         : "memory");
                         }
                     }
+                    red_sum[half * TC_QT + row] = sum;
+                    ptx::fence_proxy_async();      // the probabilities are read by the tensor core through the async proxy
+                    ptx::tcgen05_fence_before();   // ... and this tile's score columns are about to be overwritten by its output
+                    ptx::named_bar_sync(2 + t, TC_THREADS);  // releases the MMA thread; also orders red_sum for the partner thread
+                    inv[t] = 1.f / (sum + red_sum[(half ^ 1) * TC_QT + row]);
                 }
             }
+#pragma unroll
+            for (int t = 0; t < 2; ++t) {
+                if (t < ntiles) {
+                    ptx::mbar_wait(&bar_o[t], ph);
+                    ptx::tcgen05_fence_after();
+                    const int qrow = t * TC_QT + row;
+                    const bool live = qrow < p.S;
+                    __nv_bfloat16* orow = p.o + ((int64_t)row0 + qrow) * p.o_ld + col0;
+                    const float iv = inv[t];
+                    for (int cc = c_lo; cc < c_hi; cc += 32) {  // warp-uniform
+                        uint32_t r[32];
+                        ptx::tmem_ld_32x32(tmem_base + (uint32_t)t * 256u + ((uint32_t)(lg * 32) << 16) + (uint32_t)cc, r);
+                        ptx::tmem_ld_wait();
+                        if (live) {
+#pragma unroll
+                            for (int q = 0; q < 4; ++q) {
+                                uint4 v4;
+                                v4.x = pack2(__uint_as_float(r[8 * q]) * iv, __uint_as_float(r[8 * q + 1]) * iv);
+                                v4.y = pack2(__uint_as_float(r[8 * q + 2]) * iv, __uint_as_float(r[8 * q + 3]) * iv);
+                                v4.z = pack2(__uint_as_float(r[8 * q + 4]) * iv, __uint_as_float(r[8 * q + 5]) * iv);
+                                v4.w = pack2(__uint_as_float(r[8 * q + 6]) * iv, __uint_as_float(r[8 * q + 7]) * iv);
+                                *reinterpret_cast<uint4*>(orow + cc + 8 * q) = v4;
+                            }
+                        }
+                    }
+                    ptx::tcgen05_fence_before();
+                    ptx::mbar_arrive(&bar_free[t]);  // this thread has read its part of output tile t
+                }
+            }
+            const int r0 = ra;
+            ra = rc; rc = rb; rb = r0;
         }
     }
     ptx::tcgen05_fence_before();
@@ -287,9 +341,16 @@ int fwd_long_tc(int hd, const m2f_planes_t* q, const m2f_planes_t* k, const m2f_
     p.S = S;
     p.H = H;
     p.hd = hd;
+    p.items = (int)(B * H);
     p.scale_log2 = 1.4426950408889634f / sqrtf((float)hd);
-    M2F_CUDA(launch_chain(attn_fwd_tc_kernel, dim3((unsigned)(B * H)), dim3(TC_THREADS), (size_t)TC_SMEM, st,
-                          1, tq, tk, tv, p));
+    static int sms = 0;
+    if (sms == 0) {
+        int dev = 0;
+        M2F_CUDA(cudaGetDevice(&dev));
+        M2F_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+    }
+    const unsigned grid = (unsigned)std::min<int64_t>(B * H, sms);  // persistent: one CTA per SM walks the (dialogue, head) items
+    M2F_CUDA(launch_chain(attn_fwd_tc_kernel, dim3(grid), dim3(TC_THREADS), (size_t)TC_SMEM, st, 1, tq, tk, tv, p));
     M2F_LAUNCH_CHECK();
     return M2F_OK;
 }
