@@ -7,7 +7,7 @@
 //            MN-major B operand: 64-key x 64-column boxes) land in shared memory; rows past the dialogue belong to the next
 //            dialogue (or are zero-filled past the tensor) and are masked out below.
 //   MMA 1    S = Q K^T: one elected thread issues tcgen05.mma 128 x 256 x 16 over hd / 16 k-steps, accumulator = 256 TMEM columns.
-//   softmax  8 warps, two threads per query row (TMEM lane = row; warps w and w + 4 own the same lanes and take 128 columns each):
+//   softmax  16 warps, four threads per query row (TMEM lane = row; warps w, w + 4, w + 8, w + 12 own the same lanes and take 64 keys each):
 //            tcgen05.ld the scores twice (row maximum, then exp2 / row sum -- TMEM reads are cheaper than 256 live registers),
 //            unnormalised probabilities go back to shared memory as the bf16 K-major A operand of the second product
 //            (16-byte chunk c of row r sits at chunk c ^ (r & 7) of its 128-byte line: the swizzle the MMA descriptor expects).
@@ -29,8 +29,9 @@ namespace {
 
 constexpr int TC_QT = 128;     // query rows per tile (TMEM lanes)
 constexpr int TC_KEYS = 256;   // key tile = the whole (padded) dialogue
-constexpr int TC_SOFTMAX_THREADS = 256;
+constexpr int TC_SOFTMAX_THREADS = 512;   // 16 warps: four threads per query row, 64 keys each
 constexpr int TC_THREADS = TC_SOFTMAX_THREADS + 32;
+constexpr int TC_MMA_WARP = TC_SOFTMAX_THREADS / 32;
 constexpr int TC_SQ = 2 * TC_QT * 128;        // one query tile: two 64-column atoms of [128 rows][128 B]
 constexpr int TC_SK = 2 * TC_KEYS * 128;      // two atoms of [256 rows][128 B]
 constexpr int TC_SV = 4 * 2 * 64 * 128;       // four 64-key blocks x two 64-column atoms of [64 rows][128 B]
@@ -56,11 +57,11 @@ __device__ __forceinline__ float ex2(float x) {
 }
 
 // Persistent: CTA c works on (dialogue, head) items c, c + gridDim.x, ...; both 128-row query tiles of an item share one copy of K, V.
-//   warp 8, lane 0:  TMA loads and MMA issue.  Per item: S0 = Q0 K^T, S1 = Q1 K^T back to back; as soon as they are complete the key
+//   warp 16, lane 0: TMA loads and MMA issue.  Per item: S0 = Q0 K^T, S1 = Q1 K^T back to back; as soon as they are complete the key
 //                    tile and the spare query region take the NEXT item's K and Q0; O0 = P0 V when the softmax threads have written
 //                    P0, then O1 = P1 V; when that is complete V and the other query tile of the next item are requested.  So the
 //                    loads of item i + 1 travel under the softmax / PV / output phases of item i.
-//   warps 0-7:       softmax(S0) -> P0 (over the dead query tiles), softmax(S1) -> P1 (same place, once O0 is complete), then the two
+//   warps 0-15:      softmax(S0) -> P0 (over the dead query tiles), softmax(S1) -> P1 (same place, once O0 is complete), then the two
 //                    output tiles (O_t reuses the first 128 TMEM columns of S_t; the MMA thread waits for them to be read before
 //                    it overwrites S_t for the next item).
 __global__ void __launch_bounds__(TC_THREADS, 1)
@@ -79,8 +80,8 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant
     uint64_t* bar_free = bars + 7; // [2] output of tile t has been read: its TMEM columns may take the next item's scores
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 16);
     uint32_t* key_ok = tmem_slot + 4;                            // 8 words: bit j of word w = key 32 w + j is usable
-    float* red_max = reinterpret_cast<float*>(key_ok + 8);       // [2][128]
-    float* red_sum = red_max + 2 * TC_QT;                        // [2][128]
+    float* red_max = reinterpret_cast<float*>(key_ok + 8);       // [4][128] partial row maxima, then (after a barrier) ...
+    float* red_sum = red_max;                                    // ... the partial row sums in the same place
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int ksteps = p.hd / 16;      // k-steps of the first product (hd = 64 / 96 / 128)
@@ -90,7 +91,7 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant
         printf("m2f: attn_fwd_tc_kernel needs a 1024-byte aligned shared-memory base\n");
         __trap();
     }
-    if (warp == 8 && lane == 0) {
+    if (warp == TC_MMA_WARP && lane == 0) {
         ptx::prefetch_tensormap(&tq);
         ptx::prefetch_tensormap(&tk);
         ptx::prefetch_tensormap(&tv);
@@ -109,7 +110,7 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant
 
     // region roles: query tile 0 in ra, query tile 1 in rb, rc spare; they rotate (ra, rb, rc) <- (rc, ra, rb) per item
     int ra = 0, rb = 1, rc = 2;
-    if (warp == 8) {
+    if (warp == TC_MMA_WARP) {
         auto load_q0k = [&](int item, int r) {
             const int row0 = (item / p.H) * p.S, col0 = (item % p.H) * p.hd;
             ptx::mbar_expect_tx(bar_q0k, TC_SQ + TC_SK);
@@ -167,7 +168,7 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant
             }
             __syncwarp();
             for (int t = 0; t < ntiles; ++t) {
-                // the probabilities of tile t are in shared memory once all 256 softmax threads have passed this named barrier
+                // the probabilities of tile t are in shared memory once all softmax threads have passed this named barrier
                 ptx::named_bar_sync(2 + t, TC_THREADS);
                 if (lane == 0) {
                     // -------------------------------------------------------- O_t = P_t V
@@ -198,80 +199,98 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant
             ra = rc; rc = rb; rb = r0;
         }
     } else {
-        // -------------------------------------------------------------------- softmax: thread = (query row, half of the keys)
-        const int lg = warp & 3, half = warp >> 2;
+        // -------------------------------------------------------------------- softmax: thread = (query row, quarter of the keys)
+        const int lg = warp & 3, quarter = warp >> 2;
         const int row = lg * 32 + lane;
         const uint32_t sw = (uint32_t)(row & 7);
-        const int c_lo = half * 64, c_hi = min(p.hd, c_lo + 64);  // output columns: half 0 stores 0 .. 63, half 1 the rest
+        const int c_out = quarter * 32;  // output columns of this thread: 32 from c_out, if below hd
         int it = 0;
         for (int item = blockIdx.x; item < p.items; item += gridDim.x, ++it) {
             const uint32_t ph = (uint32_t)(it & 1);
             const int row0 = (item / p.H) * p.S, col0 = (item % p.H) * p.hd;
-            {   // usable keys: inside the dialogue and not padded; warp w covers keys 32 w .. 32 w + 31
+            if (warp < 8) {  // usable keys: inside the dialogue and not padded; warp w covers keys 32 w .. 32 w + 31
                 const int j = threadIdx.x;
                 const bool ok = j < p.S && p.key_pad[(int64_t)row0 + j] == 0;
                 const uint32_t word = __ballot_sync(0xffffffffu, ok);
                 if (lane == 0) key_ok[warp] = word;
             }
             ptx::named_bar_sync(1, TC_SOFTMAX_THREADS);
+            const uint32_t w0 = key_ok[quarter * 2], w1 = key_ok[quarter * 2 + 1];
+            const bool all_ok = (w0 & w1) == 0xffffffffu;  // warp-uniform: no masking work for fully valid key blocks
             float inv[2] = {0.f, 0.f};
 #pragma unroll
             for (int t = 0; t < 2; ++t) {
                 if (t < ntiles) {
                     ptx::mbar_wait(&bar_s[t], ph);
                     ptx::tcgen05_fence_after();
-                    const uint32_t t_row = tmem_base + (uint32_t)t * 256u + ((uint32_t)(lg * 32) << 16) + (uint32_t)(half * 128);
+                    const uint32_t t_row = tmem_base + (uint32_t)t * 256u + ((uint32_t)(lg * 32) << 16) + (uint32_t)(quarter * 64);
                     float mx = -INFINITY;
-#pragma unroll 1
-                    for (int c = 0; c < 4; ++c) {
+#pragma unroll
+                    for (int c = 0; c < 2; ++c) {
                         uint32_t r[32];
                         ptx::tmem_ld_32x32(t_row + (uint32_t)(c * 32), r);
                         ptx::tmem_ld_wait();
-                        const uint32_t w = key_ok[half * 4 + c];
+                        if (all_ok) {
 #pragma unroll
-                        for (int j = 0; j < 32; ++j) mx = fmaxf(mx, ((w >> j) & 1u) ? __uint_as_float(r[j]) : -INFINITY);
+                            for (int j = 0; j < 32; ++j) mx = fmaxf(mx, __uint_as_float(r[j]));
+                        } else {
+                            const uint32_t w = c == 0 ? w0 : w1;
+#pragma unroll
+                            for (int j = 0; j < 32; ++j) mx = fmaxf(mx, ((w >> j) & 1u) ? __uint_as_float(r[j]) : -INFINITY);
+                        }
                     }
-                    red_max[half * TC_QT + row] = mx;
+                    red_max[quarter * TC_QT + row] = mx;
                     ptx::named_bar_sync(1, TC_SOFTMAX_THREADS);
-                    mx = fmaxf(mx, red_max[(half ^ 1) * TC_QT + row]);
+                    mx = fmaxf(fmaxf(red_max[row], red_max[TC_QT + row]), fmaxf(red_max[2 * TC_QT + row], red_max[3 * TC_QT + row]));
                     if (mx == -INFINITY) mx = 0.f;  // no usable key at all: every probability is 0 (such rows are never stored)
                     const float mscaled = mx * p.scale_log2;
+                    ptx::named_bar_sync(1, TC_SOFTMAX_THREADS);  // every partial maximum has been read: the array takes the sums next
                     // the probabilities go where both query tiles were: tile 0 waits for the second score product, tile 1 for the
                     // first output product (it reads P0 from the same place)
                     if (t == 0 && ntiles == 2) ptx::mbar_wait(&bar_s[1], ph);
                     if (t == 1) ptx::mbar_wait(&bar_o[0], ph);
                     float sum = 0.f;
-                    // keys half * 128 .. + 127 = atoms 2 * half, 2 * half + 1 = the two atoms of region (half == 0 ? ra : rb)
-                    const uint32_t p_row = ptx::smem_u32(sR) + (uint32_t)(half == 0 ? ra : rb) * TC_SQ + (uint32_t)row * 128u;
-#pragma unroll 1
-                    for (int c = 0; c < 4; ++c) {
+                    // keys quarter * 64 .. + 63 = atom `quarter`: atoms 0, 1 live in region ra, atoms 2, 3 in region rb
+                    const uint32_t atom = ptx::smem_u32(sR) + (uint32_t)(quarter < 2 ? ra : rb) * TC_SQ + (uint32_t)(quarter & 1) * (TC_QT * 128) +
+                                          (uint32_t)row * 128u;
+#pragma unroll
+                    for (int c = 0; c < 2; ++c) {
                         uint32_t r[32];
                         ptx::tmem_ld_32x32(t_row + (uint32_t)(c * 32), r);
                         ptx::tmem_ld_wait();
-                        const uint32_t w = key_ok[half * 4 + c];
                         uint32_t pk[16];
+                        if (all_ok) {
 #pragma unroll
-                        for (int j = 0; j < 16; ++j) {
-                            const float e0 = ((w >> (2 * j)) & 1u) ? ex2(fmaf(__uint_as_float(r[2 * j]), p.scale_log2, -mscaled)) : 0.f;
-                            const float e1 = ((w >> (2 * j + 1)) & 1u) ? ex2(fmaf(__uint_as_float(r[2 * j + 1]), p.scale_log2, -mscaled)) : 0.f;
-                            sum += e0 + e1;
-                            pk[j] = pack2(e0, e1);
+                            for (int j = 0; j < 16; ++j) {
+                                const float e0 = ex2(fmaf(__uint_as_float(r[2 * j]), p.scale_log2, -mscaled));
+                                const float e1 = ex2(fmaf(__uint_as_float(r[2 * j + 1]), p.scale_log2, -mscaled));
+                                sum += e0 + e1;
+                                pk[j] = pack2(e0, e1);
+                            }
+                        } else {
+                            const uint32_t w = c == 0 ? w0 : w1;
+#pragma unroll
+                            for (int j = 0; j < 16; ++j) {
+                                const float e0 = ((w >> (2 * j)) & 1u) ? ex2(fmaf(__uint_as_float(r[2 * j]), p.scale_log2, -mscaled)) : 0.f;
+                                const float e1 = ((w >> (2 * j + 1)) & 1u) ? ex2(fmaf(__uint_as_float(r[2 * j + 1]), p.scale_log2, -mscaled)) : 0.f;
+                                sum += e0 + e1;
+                                pk[j] = pack2(e0, e1);
+                            }
                         }
-                        // 32 keys = 16-byte chunks (c & 1) * 4 .. + 3 of the row's 128-byte line in atom c / 2 of the region
-                        const uint32_t atom = p_row + (uint32_t)(c >> 1) * (TC_QT * 128);
+                        // 32 keys = 16-byte chunks c * 4 .. + 3 of the row's 128-byte line
 #pragma unroll
                         for (int q = 0; q < 4; ++q) {
-                            const uint32_t chunk = ((uint32_t)((c & 1) * 4 + q)) ^ sw;
+                            const uint32_t chunk = ((uint32_t)(c * 4 + q)) ^ sw;
                             asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(atom + (chunk << 4)), "r"(pk[4 * q]), "r"(pk[4 * q + 1]),
                                          "r"(pk[4 * q + 2]), "r"(pk[4 * q + 3])
                                          : "memory");
                         }
                     }
-                    red_sum[half * TC_QT + row] = sum;
+                    red_sum[quarter * TC_QT + row] = sum;
                     ptx::fence_proxy_async();      // the probabilities are read by the tensor core through the async proxy
                     ptx::tcgen05_fence_before();   // ... and this tile's score columns are about to be overwritten by its output
-                    ptx::named_bar_sync(2 + t, TC_THREADS);  // releases the MMA thread; also orders red_sum for the partner thread
-                    inv[t] = 1.f / (sum + red_sum[(half ^ 1) * TC_QT + row]);
+                    ptx::named_bar_sync(2 + t, TC_THREADS);  // releases the MMA thread; also orders red_sum for the partner threads
+                    inv[t] = 1.f / ((red_sum[row] + red_sum[TC_QT + row]) + (red_sum[2 * TC_QT + row] + red_sum[3 * TC_QT + row]));
                 }
             }
 #pragma unroll
@@ -280,14 +299,13 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant
                     ptx::mbar_wait(&bar_o[t], ph);
                     ptx::tcgen05_fence_after();
                     const int qrow = t * TC_QT + row;
-                    const bool live = qrow < p.S;
-                    __nv_bfloat16* orow = p.o + ((int64_t)row0 + qrow) * p.o_ld + col0;
-                    const float iv = inv[t];
-                    for (int cc = c_lo; cc < c_hi; cc += 32) {  // warp-uniform
+                    if (c_out < p.hd) {  // warp-uniform
                         uint32_t r[32];
-                        ptx::tmem_ld_32x32(tmem_base + (uint32_t)t * 256u + ((uint32_t)(lg * 32) << 16) + (uint32_t)cc, r);
+                        ptx::tmem_ld_32x32(tmem_base + (uint32_t)t * 256u + ((uint32_t)(lg * 32) << 16) + (uint32_t)c_out, r);
                         ptx::tmem_ld_wait();
-                        if (live) {
+                        if (qrow < p.S) {
+                            __nv_bfloat16* orow = p.o + ((int64_t)row0 + qrow) * p.o_ld + col0 + c_out;
+                            const float iv = inv[t];
 #pragma unroll
                             for (int q = 0; q < 4; ++q) {
                                 uint4 v4;
@@ -295,7 +313,7 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant
                                 v4.y = pack2(__uint_as_float(r[8 * q + 2]) * iv, __uint_as_float(r[8 * q + 3]) * iv);
                                 v4.z = pack2(__uint_as_float(r[8 * q + 4]) * iv, __uint_as_float(r[8 * q + 5]) * iv);
                                 v4.w = pack2(__uint_as_float(r[8 * q + 6]) * iv, __uint_as_float(r[8 * q + 7]) * iv);
-                                *reinterpret_cast<uint4*>(orow + cc + 8 * q) = v4;
+                                *reinterpret_cast<uint4*>(orow + 8 * q) = v4;
                             }
                         }
                     }
