@@ -284,7 +284,8 @@ extern "C" int m2f_attn_fwd(const m2f_planes_t* q, const m2f_planes_t* k, const 
         // long dialogues at inference: K/V tiles through shared memory, online softmax over 64-key tiles
         const amma::View aq{vq.ptr, vq.ld, vq.stride}, ak{vk.ptr, vk.ld, vk.stride}, av{vv.ptr, vv.ld, vv.stride};
         const amma::OutView ao{const_cast<__nv_bfloat16*>(vo.ptr), vo.ld, vo.stride};
-        if (amma::tc_supported(hd, S, q->planes, std::min(std::min(q->rows, k->rows), v->rows)))
+        if (amma::tc_supported(hd, S, q->planes, std::min(std::min(q->rows, k->rows), v->rows)) &&
+            (reinterpret_cast<uintptr_t>(o->ptr) % 32) == 0 && (o->ld % 16) == 0)  // 32-byte output stores
             return amma::fwd_long_tc(hd, q, k, v, key_pad, B, (int)S, H, ao, reinterpret_cast<cudaStream_t>(stream));
         return amma::fwd_long(hd, q->planes, aq, ak, av, key_pad, B * H, (int)S, H, 1.f / sqrtf((float)hd), ao, reinterpret_cast<cudaStream_t>(stream));
     }

@@ -48,7 +48,19 @@ struct TcParams {
     int64_t o_ld;
     int S, H, hd, items;  // items = dialogues x heads
     float scale_log2;     // log2(e) / sqrt(hd)
+    unsigned long long* trace;  // debug (m2f_debug_set_attn_trace): %globaltimer stamps of CTA 0's second item, else nullptr
 };
+
+__device__ __forceinline__ unsigned long long tc_now() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)::"memory");
+    return t;
+}
+// slot 0..15: MMA / TMA lane, 16..31: softmax thread 0
+#define TC_STAMP(slot)                                                        \
+    do {                                                                      \
+        if (p.trace && blockIdx.x == 0 && it == 8) p.trace[(slot)] = tc_now(); \
+    } while (0)
 
 __device__ __forceinline__ float ex2(float x) {
     float y;
@@ -148,9 +160,12 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant
             if (lane == 0) {
                 // ------------------------------------------------------------ S_t = Q_t K^T
                 constexpr uint32_t idesc_qk = ptx::instr_desc_bf16(TC_QT, TC_KEYS, false, false);
+                TC_STAMP(0);
                 for (int t = 0; t < ntiles; ++t) {
                     ptx::mbar_wait(t == 0 ? bar_q0k : bar_q1, ph);
+                    TC_STAMP(1 + 3 * t);
                     if (it > 0) ptx::mbar_wait(&bar_free[t], ph ^ 1u);  // the previous item's output tile t has left TMEM
+                    TC_STAMP(2 + 3 * t);
                     ptx::tcgen05_fence_after();
                     const uint32_t q_base = ptx::smem_u32(sR) + (uint32_t)(t == 0 ? ra : rb) * TC_SQ;
                     for (int k = 0; k < ksteps; ++k) {
@@ -160,9 +175,11 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant
                         ptx::umma_bf16(tmem_base + (uint32_t)t * 256u, ad, bd, idesc_qk, k > 0 ? 1u : 0u);
                     }
                     ptx::umma_commit(&bar_s[t]);
+                    TC_STAMP(3 + 3 * t);
                 }
                 if (has_next) {  // K and the spare region are free once the score products are complete
                     ptx::mbar_wait(&bar_s[ntiles - 1], ph);
+                    TC_STAMP(7);
                     load_q0k(next, rc);
                 }
             }
@@ -172,6 +189,7 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant
                 ptx::named_bar_sync(2 + t, TC_THREADS);
                 if (lane == 0) {
                     // -------------------------------------------------------- O_t = P_t V
+                    TC_STAMP(8 + 2 * t);
                     if (t == 0) ptx::mbar_wait(bar_v, ph);
                     ptx::tcgen05_fence_after();
                     constexpr uint32_t idesc_pv = ptx::instr_desc_bf16(TC_QT, 128, false, true);
@@ -186,11 +204,13 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant
                         }
                     }
                     ptx::umma_commit(&bar_o[t]);
+                    TC_STAMP(9 + 2 * t);
                 }
                 __syncwarp();
             }
             if (lane == 0 && has_next) {  // V and the probability regions are free once the last output product is complete
                 ptx::mbar_wait(&bar_o[ntiles - 1], ph);
+                TC_STAMP(12);
                 load_v(next);
                 if (ntiles == 2) load_q1(next, ra);
             }
@@ -215,6 +235,7 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant
                 if (lane == 0) key_ok[warp] = word;
             }
             ptx::named_bar_sync(1, TC_SOFTMAX_THREADS);
+            if (threadIdx.x == 0) TC_STAMP(16);
             const uint32_t w0 = key_ok[quarter * 2], w1 = key_ok[quarter * 2 + 1];
             const bool all_ok = (w0 & w1) == 0xffffffffu;  // warp-uniform: no masking work for fully valid key blocks
             float inv[2] = {0.f, 0.f};
@@ -223,6 +244,7 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant
                 if (t < ntiles) {
                     ptx::mbar_wait(&bar_s[t], ph);
                     ptx::tcgen05_fence_after();
+                    if (threadIdx.x == 0) TC_STAMP(17 + 5 * t);
                     const uint32_t t_row = tmem_base + (uint32_t)t * 256u + ((uint32_t)(lg * 32) << 16) + (uint32_t)(quarter * 64);
                     float mx = -INFINITY;
 #pragma unroll
@@ -245,10 +267,12 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant
                     if (mx == -INFINITY) mx = 0.f;  // no usable key at all: every probability is 0 (such rows are never stored)
                     const float mscaled = mx * p.scale_log2;
                     ptx::named_bar_sync(1, TC_SOFTMAX_THREADS);  // every partial maximum has been read: the array takes the sums next
+                    if (threadIdx.x == 0) TC_STAMP(18 + 5 * t);
                     // the probabilities go where both query tiles were: tile 0 waits for the second score product, tile 1 for the
                     // first output product (it reads P0 from the same place)
                     if (t == 0 && ntiles == 2) ptx::mbar_wait(&bar_s[1], ph);
                     if (t == 1) ptx::mbar_wait(&bar_o[0], ph);
+                    if (threadIdx.x == 0) TC_STAMP(19 + 5 * t);
                     float sum = 0.f;
                     // keys quarter * 64 .. + 63 = atom `quarter`: atoms 0, 1 live in region ra, atoms 2, 3 in region rb
                     const uint32_t atom = ptx::smem_u32(sR) + (uint32_t)(quarter < 2 ? ra : rb) * TC_SQ + (uint32_t)(quarter & 1) * (TC_QT * 128) +
@@ -287,10 +311,12 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant
                         }
                     }
                     red_sum[quarter * TC_QT + row] = sum;
+                    if (threadIdx.x == 0) TC_STAMP(20 + 5 * t);
                     ptx::fence_proxy_async();      // the probabilities are read by the tensor core through the async proxy
                     ptx::tcgen05_fence_before();   // ... and this tile's score columns are about to be overwritten by its output
                     ptx::named_bar_sync(2 + t, TC_THREADS);  // releases the MMA thread; also orders red_sum for the partner threads
                     inv[t] = 1.f / ((red_sum[row] + red_sum[TC_QT + row]) + (red_sum[2 * TC_QT + row] + red_sum[3 * TC_QT + row]));
+                    if (threadIdx.x == 0) TC_STAMP(21 + 5 * t);
                 }
             }
 #pragma unroll
@@ -298,6 +324,7 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant
                 if (t < ntiles) {
                     ptx::mbar_wait(&bar_o[t], ph);
                     ptx::tcgen05_fence_after();
+                    if (threadIdx.x == 0) TC_STAMP(26 + t);
                     const int qrow = t * TC_QT + row;
                     if (c_out < p.hd) {  // warp-uniform
                         uint32_t r[32];
@@ -307,18 +334,20 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant
                             __nv_bfloat16* orow = p.o + ((int64_t)row0 + qrow) * p.o_ld + col0 + c_out;
                             const float iv = inv[t];
 #pragma unroll
-                            for (int q = 0; q < 4; ++q) {
-                                uint4 v4;
-                                v4.x = pack2(__uint_as_float(r[8 * q]) * iv, __uint_as_float(r[8 * q + 1]) * iv);
-                                v4.y = pack2(__uint_as_float(r[8 * q + 2]) * iv, __uint_as_float(r[8 * q + 3]) * iv);
-                                v4.z = pack2(__uint_as_float(r[8 * q + 4]) * iv, __uint_as_float(r[8 * q + 5]) * iv);
-                                v4.w = pack2(__uint_as_float(r[8 * q + 6]) * iv, __uint_as_float(r[8 * q + 7]) * iv);
-                                *reinterpret_cast<uint4*>(orow + 8 * q) = v4;
+                            for (int q = 0; q < 2; ++q) {  // 2 x 32 bytes: whole sectors (16-byte stores cost a transaction per half sector)
+                                uint32_t w[8];
+#pragma unroll
+                                for (int i = 0; i < 8; ++i)
+                                    w[i] = pack2(__uint_as_float(r[16 * q + 2 * i]) * iv, __uint_as_float(r[16 * q + 2 * i + 1]) * iv);
+                                asm volatile("st.global.v8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"l"(orow + 16 * q), "r"(w[0]), "r"(w[1]),
+                                             "r"(w[2]), "r"(w[3]), "r"(w[4]), "r"(w[5]), "r"(w[6]), "r"(w[7])
+                                             : "memory");
                             }
                         }
                     }
                     ptx::tcgen05_fence_before();
                     ptx::mbar_arrive(&bar_free[t]);  // this thread has read its part of output tile t
+                    if (threadIdx.x == 0) TC_STAMP(28 + t);
                 }
             }
             const int r0 = ra;
@@ -336,6 +365,8 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant
 }  // namespace
 
 // hd in {64, 96, 128}; one plane; enough rows for the 256-row key box; M2F_ATT_TC=0 keeps the mma.sync kernel (A/B, debugging)
+static unsigned long long* g_tc_trace = nullptr;
+
 bool tc_supported(int hd, int64_t S, int planes, int64_t rows) {
     static const bool off = [] { const char* e = getenv("M2F_ATT_TC"); return e && e[0] == '0'; }();
     return !off && planes == 1 && (hd == 64 || hd == 96 || hd == 128) && S > 64 && S <= TC_KEYS && rows >= TC_KEYS;
@@ -361,6 +392,7 @@ int fwd_long_tc(int hd, const m2f_planes_t* q, const m2f_planes_t* k, const m2f_
     p.hd = hd;
     p.items = (int)(B * H);
     p.scale_log2 = 1.4426950408889634f / sqrtf((float)hd);
+    p.trace = g_tc_trace;
     static int sms = 0;
     if (sms == 0) {
         int dev = 0;
@@ -375,3 +407,6 @@ int fwd_long_tc(int hd, const m2f_planes_t* q, const m2f_planes_t* k, const m2f_
 
 }  // namespace amma
 }  // namespace m2f
+
+// profiling aid (tools/atc_trace.py): 32 x u64 of %globaltimer stamps written by CTA 0 during its second item; nullptr turns it off
+extern "C" void m2f_debug_set_attn_trace(unsigned long long* buf) { m2f::amma::g_tc_trace = buf; }
