@@ -29,18 +29,22 @@ namespace {
 
 constexpr int TC_QT = 128;     // query rows per tile (TMEM lanes)
 constexpr int TC_KEYS = 256;   // key tile = the whole (padded) dialogue
-constexpr int TC_SOFTMAX_THREADS = 512;   // 16 warps: four threads per query row, 64 keys each
-constexpr int TC_THREADS = TC_SOFTMAX_THREADS + 32;
-constexpr int TC_MMA_WARP = TC_SOFTMAX_THREADS / 32;
+constexpr int TC_SOFTMAX_WARPS = 16;          // four threads per query row, 64 keys each
+constexpr int TC_SOFTMAX_THREADS = TC_SOFTMAX_WARPS * 32;
+constexpr int TC_OUT_WARPS = 4;               // one thread per query row: output tile TMEM -> global
+constexpr int TC_OUT_THREADS = TC_OUT_WARPS * 32;
+constexpr int TC_MMA_WARP = TC_SOFTMAX_WARPS + TC_OUT_WARPS;
+constexpr int TC_THREADS = (TC_MMA_WARP + 1) * 32;
+constexpr int TC_BAR_THREADS = TC_SOFTMAX_THREADS + 32;  // named barriers "probabilities ready": softmax warps + the MMA warp
 constexpr int TC_SQ = 2 * TC_QT * 128;        // one query tile: two 64-column atoms of [128 rows][128 B]
 constexpr int TC_SK = 2 * TC_KEYS * 128;      // two atoms of [256 rows][128 B]
 constexpr int TC_SV = 4 * 2 * 64 * 128;       // four 64-key blocks x two 64-column atoms of [64 rows][128 B]
-constexpr int TC_AUX = 16 * 8 + 16 + 8 * 4 + 4 * TC_QT * 4;  // barriers, TMEM slot, key mask, row max / sum exchange
-// K | V | three 32 KB regions: two hold the query tiles of the current (dialogue, head) and then, two 64-key atoms each, its
-// probabilities; the third receives the first query tile of the NEXT one.  No alignment slack: the base is checked at run time.
-constexpr int TC_SMEM = TC_SK + TC_SV + 3 * TC_SQ + TC_AUX;
+constexpr int TC_SP = 4 * TC_QT * 128;        // probabilities of one query tile: four 64-key atoms of [128 rows][128 B]
+constexpr int TC_AUX = 16 * 8 + 16 + 8 * 4 + 4 * TC_QT * 4;  // barriers, TMEM slot, key mask, row-maximum exchange
+// K | V | P | one query tile.  No alignment slack: the base is checked at run time.
+constexpr int TC_SMEM = TC_SK + TC_SV + TC_SP + TC_SQ + TC_AUX;
 static_assert(TC_SMEM <= 227 * 1024, "shared memory budget");
-constexpr uint32_t TC_TMEM_COLS = 512;        // two score tiles of 256 columns; each output tile reuses 128 columns of its scores
+constexpr uint32_t TC_TMEM_COLS = 512;        // two score tiles of 256 columns; O_t reuses columns 0..127 of S_t, the row sums 128..131
 
 struct TcParams {
     const uint8_t* key_pad;
@@ -48,7 +52,7 @@ struct TcParams {
     int64_t o_ld;
     int S, H, hd, items;  // items = dialogues x heads
     float scale_log2;     // log2(e) / sqrt(hd)
-    unsigned long long* trace;  // debug (m2f_debug_set_attn_trace): %globaltimer stamps of CTA 0's second item, else nullptr
+    unsigned long long* trace;  // debug (m2f_debug_set_attn_trace): %globaltimer stamps of CTA 0's ninth item, else nullptr
 };
 
 __device__ __forceinline__ unsigned long long tc_now() {
@@ -56,7 +60,7 @@ __device__ __forceinline__ unsigned long long tc_now() {
     asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)::"memory");
     return t;
 }
-// slot 0..15: MMA / TMA lane, 16..31: softmax thread 0
+// slot 0..15: MMA / TMA lane, 16..27: softmax thread 0, 28..31: first output thread
 #define TC_STAMP(slot)                                                        \
     do {                                                                      \
         if (p.trace && blockIdx.x == 0 && it == 8) p.trace[(slot)] = tc_now(); \
@@ -67,23 +71,33 @@ __device__ __forceinline__ float ex2(float x) {
     asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
     return y;
 }
+__device__ __forceinline__ void tmem_st_1(uint32_t taddr, uint32_t v) {
+    asm volatile("tcgen05.st.sync.aligned.32x32b.x1.b32 [%0], {%1};" ::"r"(taddr), "r"(v) : "memory");
+}
+__device__ __forceinline__ void tmem_st_wait() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
+__device__ __forceinline__ void tmem_ld_4(uint32_t taddr, uint32_t (&r)[4]) {
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(taddr) : "memory");
+}
 
 // Persistent: CTA c works on (dialogue, head) items c, c + gridDim.x, ...; both 128-row query tiles of an item share one copy of K, V.
-//   warp 16, lane 0: TMA loads and MMA issue.  Per item: S0 = Q0 K^T, S1 = Q1 K^T back to back; as soon as they are complete the key
-//                    tile and the spare query region take the NEXT item's K and Q0; O0 = P0 V when the softmax threads have written
-//                    P0, then O1 = P1 V; when that is complete V and the other query tile of the next item are requested.  So the
-//                    loads of item i + 1 travel under the softmax / PV / output phases of item i.
-//   warps 0-15:      softmax(S0) -> P0 (over the dead query tiles), softmax(S1) -> P1 (same place, once O0 is complete), then the two
-//                    output tiles (O_t reuses the first 128 TMEM columns of S_t; the MMA thread waits for them to be read before
-//                    it overwrites S_t for the next item).
+// Three roles:
+//   warp 20, lane 0: TMA loads and MMA issue.  Per item: S0 = Q0 K^T; the query slot then takes Q1; S1 = Q1 K^T; once the score
+//                    products are complete the key tile and the query slot take the NEXT item's K and Q0; O0 = P0 V when the softmax
+//                    warps have written P0, then O1 = P1 V; V of the next item is requested when that is complete.
+//   warps 0-15:      softmax(S0) -> P0, softmax(S1) -> P1 (same buffer, once O0 is complete): scores from TMEM, probabilities to
+//                    shared memory, the thread's partial row sum to a spare TMEM column of the tile.  Nothing else: they go
+//                    straight on to the next item.
+//   warps 16-19:     output: wait for O_t, tcgen05.ld it together with the four partial row sums, scale, store 32-byte pieces; then
+//                    release the tile's TMEM columns for the next item's scores.
 __global__ void __launch_bounds__(TC_THREADS, 1)
 attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__ CUtensorMap tk, const __grid_constant__ CUtensorMap tv,
                    const TcParams p) {
     extern __shared__ __align__(1024) uint8_t smem[];
     uint8_t* sK = smem;
     uint8_t* sV = sK + TC_SK;
-    uint8_t* sR = sV + TC_SV;  // region r at sR + r * TC_SQ
-    uint64_t* bars = reinterpret_cast<uint64_t*>(sR + 3 * TC_SQ);
+    uint8_t* sP = sV + TC_SV;
+    uint8_t* sQ = sP + TC_SP;
+    uint64_t* bars = reinterpret_cast<uint64_t*>(sQ + TC_SQ);
     uint64_t* bar_q0k = bars;      // Q tile 0 and K landed
     uint64_t* bar_q1 = bars + 1;   // Q tile 1 landed
     uint64_t* bar_v = bars + 2;    // V landed
@@ -92,8 +106,7 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant
     uint64_t* bar_free = bars + 7; // [2] output of tile t has been read: its TMEM columns may take the next item's scores
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 16);
     uint32_t* key_ok = tmem_slot + 4;                            // 8 words: bit j of word w = key 32 w + j is usable
-    float* red_max = reinterpret_cast<float*>(key_ok + 8);       // [4][128] partial row maxima, then (after a barrier) ...
-    float* red_sum = red_max;                                    // ... the partial row sums in the same place
+    float* red_max = reinterpret_cast<float*>(key_ok + 8);       // [4][128] partial row maxima
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int ksteps = p.hd / 16;      // k-steps of the first product (hd = 64 / 96 / 128)
@@ -108,8 +121,8 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant
         ptx::prefetch_tensormap(&tk);
         ptx::prefetch_tensormap(&tv);
         for (int i = 0; i < 7; ++i) ptx::mbar_init(bars + i, 1);
-        ptx::mbar_init(&bar_free[0], TC_SOFTMAX_THREADS);
-        ptx::mbar_init(&bar_free[1], TC_SOFTMAX_THREADS);
+        ptx::mbar_init(&bar_free[0], TC_OUT_THREADS);
+        ptx::mbar_init(&bar_free[1], TC_OUT_THREADS);
         ptx::fence_barrier_init();
     }
     if (warp == 0) ptx::tmem_alloc(tmem_slot, TC_TMEM_COLS);
@@ -120,23 +133,21 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant
     pdl_wait();
     pdl_trigger();
 
-    // region roles: query tile 0 in ra, query tile 1 in rb, rc spare; they rotate (ra, rb, rc) <- (rc, ra, rb) per item
-    int ra = 0, rb = 1, rc = 2;
     if (warp == TC_MMA_WARP) {
-        auto load_q0k = [&](int item, int r) {
+        auto load_q0k = [&](int item) {
             const int row0 = (item / p.H) * p.S, col0 = (item % p.H) * p.hd;
             ptx::mbar_expect_tx(bar_q0k, TC_SQ + TC_SK);
 #pragma unroll
             for (int a = 0; a < 2; ++a) {
-                ptx::tma_load_3d(sR + r * TC_SQ + a * (TC_QT * 128), &tq, bar_q0k, col0 + a * 64, row0, 0);
                 ptx::tma_load_3d(sK + a * (TC_KEYS * 128), &tk, bar_q0k, col0 + a * 64, row0, 0);
+                ptx::tma_load_3d(sQ + a * (TC_QT * 128), &tq, bar_q0k, col0 + a * 64, row0, 0);
             }
         };
-        auto load_q1 = [&](int item, int r) {
+        auto load_q1 = [&](int item) {
             const int row0 = (item / p.H) * p.S, col0 = (item % p.H) * p.hd;
             ptx::mbar_expect_tx(bar_q1, TC_SQ);
 #pragma unroll
-            for (int a = 0; a < 2; ++a) ptx::tma_load_3d(sR + r * TC_SQ + a * (TC_QT * 128), &tq, bar_q1, col0 + a * 64, row0 + TC_QT, 0);
+            for (int a = 0; a < 2; ++a) ptx::tma_load_3d(sQ + a * (TC_QT * 128), &tq, bar_q1, col0 + a * 64, row0 + TC_QT, 0);
         };
         auto load_v = [&](int item) {
             const int row0 = (item / p.H) * p.S, col0 = (item % p.H) * p.hd;
@@ -147,9 +158,8 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant
                 for (int a = 0; a < 2; ++a)
                     ptx::tma_load_3d(sV + kb * 16384 + a * 8192, &tv, bar_v, col0 + a * 64, row0 + kb * 64, 0);
         };
-        if (lane == 0 && (int)blockIdx.x < p.items) {
-            load_q0k(blockIdx.x, ra);
-            if (ntiles == 2) load_q1(blockIdx.x, rb);
+        if (lane == 0) {
+            load_q0k(blockIdx.x);
             load_v(blockIdx.x);
         }
         int it = 0;
@@ -162,31 +172,34 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant
                 constexpr uint32_t idesc_qk = ptx::instr_desc_bf16(TC_QT, TC_KEYS, false, false);
                 TC_STAMP(0);
                 for (int t = 0; t < ntiles; ++t) {
+                    if (t == 1) {  // the query slot is free once S0 is complete: it takes the second query tile
+                        ptx::mbar_wait(&bar_s[0], ph);
+                        load_q1(item);
+                    }
                     ptx::mbar_wait(t == 0 ? bar_q0k : bar_q1, ph);
                     TC_STAMP(1 + 3 * t);
                     if (it > 0) ptx::mbar_wait(&bar_free[t], ph ^ 1u);  // the previous item's output tile t has left TMEM
                     TC_STAMP(2 + 3 * t);
                     ptx::tcgen05_fence_after();
-                    const uint32_t q_base = ptx::smem_u32(sR) + (uint32_t)(t == 0 ? ra : rb) * TC_SQ;
                     for (int k = 0; k < ksteps; ++k) {
                         const uint32_t off = (uint32_t)(k >> 2) * 128u, kin = (uint32_t)(k & 3) * 32u;  // atom, 16 columns = 32 B inside it
-                        const uint64_t ad = ptx::smem_desc_sw128(q_base + off * TC_QT + kin, 0, 1024);
+                        const uint64_t ad = ptx::smem_desc_sw128(ptx::smem_u32(sQ) + off * TC_QT + kin, 0, 1024);
                         const uint64_t bd = ptx::smem_desc_sw128(ptx::smem_u32(sK) + off * TC_KEYS + kin, 0, 1024);
                         ptx::umma_bf16(tmem_base + (uint32_t)t * 256u, ad, bd, idesc_qk, k > 0 ? 1u : 0u);
                     }
                     ptx::umma_commit(&bar_s[t]);
                     TC_STAMP(3 + 3 * t);
                 }
-                if (has_next) {  // K and the spare region are free once the score products are complete
+                if (has_next) {  // K and the query slot are free once the score products are complete
                     ptx::mbar_wait(&bar_s[ntiles - 1], ph);
                     TC_STAMP(7);
-                    load_q0k(next, rc);
+                    load_q0k(next);
                 }
             }
             __syncwarp();
             for (int t = 0; t < ntiles; ++t) {
                 // the probabilities of tile t are in shared memory once all softmax threads have passed this named barrier
-                ptx::named_bar_sync(2 + t, TC_THREADS);
+                ptx::named_bar_sync(2 + t, TC_BAR_THREADS);
                 if (lane == 0) {
                     // -------------------------------------------------------- O_t = P_t V
                     TC_STAMP(8 + 2 * t);
@@ -195,10 +208,9 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant
                     constexpr uint32_t idesc_pv = ptx::instr_desc_bf16(TC_QT, 128, false, true);
 #pragma unroll 1
                     for (int kb = 0; kb < 4; ++kb) {
-                        const uint32_t p_atom = ptx::smem_u32(sR) + (uint32_t)(kb < 2 ? ra : rb) * TC_SQ + (uint32_t)(kb & 1) * (TC_QT * 128);
 #pragma unroll
                         for (int k = 0; k < 4; ++k) {
-                            const uint64_t ad = ptx::smem_desc_sw128(p_atom + k * 32, 0, 1024);
+                            const uint64_t ad = ptx::smem_desc_sw128(ptx::smem_u32(sP) + kb * (TC_QT * 128) + k * 32, 0, 1024);
                             const uint64_t bd = ptx::smem_desc_sw128(ptx::smem_u32(sV) + kb * 16384 + k * 2048, 8192, 1024);
                             ptx::umma_bf16(tmem_base + (uint32_t)t * 256u, ad, bd, idesc_pv, (kb > 0 || k > 0) ? 1u : 0u);
                         }
@@ -208,26 +220,24 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant
                 }
                 __syncwarp();
             }
-            if (lane == 0 && has_next) {  // V and the probability regions are free once the last output product is complete
+            if (lane == 0 && has_next) {  // V is free once the last output product is complete
                 ptx::mbar_wait(&bar_o[ntiles - 1], ph);
                 TC_STAMP(12);
                 load_v(next);
-                if (ntiles == 2) load_q1(next, ra);
             }
             __syncwarp();
-            const int r0 = ra;
-            ra = rc; rc = rb; rb = r0;
         }
-    } else {
+    } else if (warp < TC_SOFTMAX_WARPS) {
         // -------------------------------------------------------------------- softmax: thread = (query row, quarter of the keys)
         const int lg = warp & 3, quarter = warp >> 2;
         const int row = lg * 32 + lane;
         const uint32_t sw = (uint32_t)(row & 7);
-        const int c_out = quarter * 32;  // output columns of this thread: 32 from c_out, if below hd
+        // keys quarter * 64 .. + 63 = atom `quarter` of the probability buffer
+        const uint32_t atom = ptx::smem_u32(sP) + (uint32_t)quarter * (TC_QT * 128) + (uint32_t)row * 128u;
         int it = 0;
         for (int item = blockIdx.x; item < p.items; item += gridDim.x, ++it) {
             const uint32_t ph = (uint32_t)(it & 1);
-            const int row0 = (item / p.H) * p.S, col0 = (item % p.H) * p.hd;
+            const int row0 = (item / p.H) * p.S;
             if (warp < 8) {  // usable keys: inside the dialogue and not padded; warp w covers keys 32 w .. 32 w + 31
                 const int j = threadIdx.x;
                 const bool ok = j < p.S && p.key_pad[(int64_t)row0 + j] == 0;
@@ -238,14 +248,14 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant
             if (threadIdx.x == 0) TC_STAMP(16);
             const uint32_t w0 = key_ok[quarter * 2], w1 = key_ok[quarter * 2 + 1];
             const bool all_ok = (w0 & w1) == 0xffffffffu;  // warp-uniform: no masking work for fully valid key blocks
-            float inv[2] = {0.f, 0.f};
 #pragma unroll
             for (int t = 0; t < 2; ++t) {
                 if (t < ntiles) {
                     ptx::mbar_wait(&bar_s[t], ph);
                     ptx::tcgen05_fence_after();
                     if (threadIdx.x == 0) TC_STAMP(17 + 5 * t);
-                    const uint32_t t_row = tmem_base + (uint32_t)t * 256u + ((uint32_t)(lg * 32) << 16) + (uint32_t)(quarter * 64);
+                    const uint32_t t_tile = tmem_base + (uint32_t)t * 256u + ((uint32_t)(lg * 32) << 16);
+                    const uint32_t t_row = t_tile + (uint32_t)(quarter * 64);
                     float mx = -INFINITY;
 #pragma unroll
                     for (int c = 0; c < 2; ++c) {
@@ -266,17 +276,13 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant
                     mx = fmaxf(fmaxf(red_max[row], red_max[TC_QT + row]), fmaxf(red_max[2 * TC_QT + row], red_max[3 * TC_QT + row]));
                     if (mx == -INFINITY) mx = 0.f;  // no usable key at all: every probability is 0 (such rows are never stored)
                     const float mscaled = mx * p.scale_log2;
-                    ptx::named_bar_sync(1, TC_SOFTMAX_THREADS);  // every partial maximum has been read: the array takes the sums next
+                    ptx::named_bar_sync(1, TC_SOFTMAX_THREADS);  // every partial maximum has been read: the array is free for the next tile
                     if (threadIdx.x == 0) TC_STAMP(18 + 5 * t);
-                    // the probabilities go where both query tiles were: tile 0 waits for the second score product, tile 1 for the
-                    // first output product (it reads P0 from the same place)
-                    if (t == 0 && ntiles == 2) ptx::mbar_wait(&bar_s[1], ph);
+                    // the probability buffer is free once the product that read it last is complete
                     if (t == 1) ptx::mbar_wait(&bar_o[0], ph);
+                    else if (it > 0) ptx::mbar_wait(&bar_o[ntiles - 1], ph ^ 1u);
                     if (threadIdx.x == 0) TC_STAMP(19 + 5 * t);
                     float sum = 0.f;
-                    // keys quarter * 64 .. + 63 = atom `quarter`: atoms 0, 1 live in region ra, atoms 2, 3 in region rb
-                    const uint32_t atom = ptx::smem_u32(sR) + (uint32_t)(quarter < 2 ? ra : rb) * TC_SQ + (uint32_t)(quarter & 1) * (TC_QT * 128) +
-                                          (uint32_t)row * 128u;
 #pragma unroll
                     for (int c = 0; c < 2; ++c) {
                         uint32_t r[32];
@@ -310,48 +316,59 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant
                                          : "memory");
                         }
                     }
-                    red_sum[quarter * TC_QT + row] = sum;
+                    // this thread's partial row sum -> column 128 + quarter of the tile (the output product writes columns 0..127 only);
+                    // those columns hold scores of the third quarter: every softmax thread must have finished reading first
+                    ptx::named_bar_sync(1, TC_SOFTMAX_THREADS);
+                    tmem_st_1(t_tile + 128u + (uint32_t)quarter, __float_as_uint(sum));
+                    tmem_st_wait();
                     if (threadIdx.x == 0) TC_STAMP(20 + 5 * t);
                     ptx::fence_proxy_async();      // the probabilities are read by the tensor core through the async proxy
                     ptx::tcgen05_fence_before();   // ... and this tile's score columns are about to be overwritten by its output
-                    ptx::named_bar_sync(2 + t, TC_THREADS);  // releases the MMA thread; also orders red_sum for the partner threads
-                    inv[t] = 1.f / ((red_sum[row] + red_sum[TC_QT + row]) + (red_sum[2 * TC_QT + row] + red_sum[3 * TC_QT + row]));
+                    ptx::named_bar_sync(2 + t, TC_BAR_THREADS);  // releases the MMA thread
                     if (threadIdx.x == 0) TC_STAMP(21 + 5 * t);
                 }
             }
+        }
+    } else {
+        // -------------------------------------------------------------------- output: thread = query row
+        const int lg = warp & 3;
+        const int row = lg * 32 + lane;
+        int it = 0;
+        for (int item = blockIdx.x; item < p.items; item += gridDim.x, ++it) {
+            const uint32_t ph = (uint32_t)(it & 1);
+            const int row0 = (item / p.H) * p.S, col0 = (item % p.H) * p.hd;
+            for (int t = 0; t < ntiles; ++t) {
+                ptx::mbar_wait(&bar_o[t], ph);
+                ptx::tcgen05_fence_after();
+                if (threadIdx.x == TC_SOFTMAX_THREADS) TC_STAMP(28 + 2 * t);
+                const uint32_t t_tile = tmem_base + (uint32_t)t * 256u + ((uint32_t)(lg * 32) << 16);
+                uint32_t sums[4];
+                tmem_ld_4(t_tile + 128u, sums);
+                ptx::tmem_ld_wait();
+                const float iv = 1.f / ((__uint_as_float(sums[0]) + __uint_as_float(sums[1])) + (__uint_as_float(sums[2]) + __uint_as_float(sums[3])));
+                const int qrow = t * TC_QT + row;
+                __nv_bfloat16* orow = p.o + ((int64_t)row0 + qrow) * p.o_ld + col0;
+                for (int cc = 0; cc < p.hd; cc += 32) {
+                    uint32_t r[32];
+                    ptx::tmem_ld_32x32(t_tile + (uint32_t)cc, r);
+                    ptx::tmem_ld_wait();
+                    if (qrow < p.S) {
 #pragma unroll
-            for (int t = 0; t < 2; ++t) {
-                if (t < ntiles) {
-                    ptx::mbar_wait(&bar_o[t], ph);
-                    ptx::tcgen05_fence_after();
-                    if (threadIdx.x == 0) TC_STAMP(26 + t);
-                    const int qrow = t * TC_QT + row;
-                    if (c_out < p.hd) {  // warp-uniform
-                        uint32_t r[32];
-                        ptx::tmem_ld_32x32(tmem_base + (uint32_t)t * 256u + ((uint32_t)(lg * 32) << 16) + (uint32_t)c_out, r);
-                        ptx::tmem_ld_wait();
-                        if (qrow < p.S) {
-                            __nv_bfloat16* orow = p.o + ((int64_t)row0 + qrow) * p.o_ld + col0 + c_out;
-                            const float iv = inv[t];
+                        for (int q = 0; q < 2; ++q) {  // 2 x 32 bytes: whole sectors (16-byte stores cost a transaction per half sector)
+                            uint32_t w[8];
 #pragma unroll
-                            for (int q = 0; q < 2; ++q) {  // 2 x 32 bytes: whole sectors (16-byte stores cost a transaction per half sector)
-                                uint32_t w[8];
-#pragma unroll
-                                for (int i = 0; i < 8; ++i)
-                                    w[i] = pack2(__uint_as_float(r[16 * q + 2 * i]) * iv, __uint_as_float(r[16 * q + 2 * i + 1]) * iv);
-                                asm volatile("st.global.v8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"l"(orow + 16 * q), "r"(w[0]), "r"(w[1]),
-                                             "r"(w[2]), "r"(w[3]), "r"(w[4]), "r"(w[5]), "r"(w[6]), "r"(w[7])
-                                             : "memory");
-                            }
+                            for (int i = 0; i < 8; ++i)
+                                w[i] = pack2(__uint_as_float(r[16 * q + 2 * i]) * iv, __uint_as_float(r[16 * q + 2 * i + 1]) * iv);
+                            asm volatile("st.global.v8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"l"(orow + cc + 16 * q), "r"(w[0]), "r"(w[1]),
+                                         "r"(w[2]), "r"(w[3]), "r"(w[4]), "r"(w[5]), "r"(w[6]), "r"(w[7])
+                                         : "memory");
                         }
                     }
-                    ptx::tcgen05_fence_before();
-                    ptx::mbar_arrive(&bar_free[t]);  // this thread has read its part of output tile t
-                    if (threadIdx.x == 0) TC_STAMP(28 + t);
                 }
+                ptx::tcgen05_fence_before();
+                ptx::mbar_arrive(&bar_free[t]);  // this thread has read its row of output tile t (and its sums)
+                if (threadIdx.x == TC_SOFTMAX_THREADS) TC_STAMP(29 + 2 * t);
             }
-            const int r0 = ra;
-            ra = rc; rc = rb; rb = r0;
         }
     }
     ptx::tcgen05_fence_before();
