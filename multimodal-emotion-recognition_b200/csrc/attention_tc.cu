@@ -36,14 +36,18 @@ constexpr int TC_OUT_THREADS = TC_OUT_WARPS * 32;
 constexpr int TC_MMA_WARP = TC_SOFTMAX_WARPS + TC_OUT_WARPS;
 constexpr int TC_THREADS = (TC_MMA_WARP + 1) * 32;
 constexpr int TC_BAR_THREADS = TC_SOFTMAX_THREADS + 32;  // named barriers "probabilities ready": softmax warps + the MMA warp
-constexpr int TC_SQ = 2 * TC_QT * 128;        // one query tile: two 64-column atoms of [128 rows][128 B]
-constexpr int TC_SK = 2 * TC_KEYS * 128;      // two atoms of [256 rows][128 B]
-constexpr int TC_SV = 4 * 2 * 64 * 128;       // four 64-key blocks x two 64-column atoms of [64 rows][128 B]
-constexpr int TC_SP = 4 * TC_QT * 128;        // probabilities of one query tile: four 64-key atoms of [128 rows][128 B]
-constexpr int TC_AUX = 16 * 8 + 16 + 8 * 4 + 4 * TC_QT * 4;  // barriers, TMEM slot, key mask, row-maximum exchange
-// K | V | P | one query tile.  No alignment slack: the base is checked at run time.
-constexpr int TC_SMEM = TC_SK + TC_SV + TC_SP + TC_SQ + TC_AUX;
-static_assert(TC_SMEM <= 227 * 1024, "shared memory budget");
+// Q, K and V tiles are made of 32-column atoms (64-byte rows, 64-byte swizzle), hd / 32 of them: exactly the head's columns, so that
+// hd = 96 costs 3/4 of what two 64-column atoms would -- the room that lets both query tiles of an item stay resident.
+constexpr int TC_QATOM = TC_QT * 64;          // [128 rows][64 B]
+constexpr int TC_KATOM = TC_KEYS * 64;        // [256 rows][64 B]
+constexpr int TC_VATOM = 64 * 64;             // [64 keys][64 B], per 64-key block
+constexpr int TC_SP = 4 * TC_QT * 128;        // probabilities of one query tile: four 64-key atoms of [128 rows][128 B], 128-byte swizzle
+constexpr int TC_AUX = 3072;                  // barriers, TMEM slot, key mask, row-maximum exchange (first, so that the tiles stay 1024-aligned)
+// aux | K | V | P | query tile 0 | query tile 1 (hd <= 96; with hd = 128 one slot is time-multiplexed).  The base is checked at run time.
+__host__ __device__ constexpr int tc_smem_bytes(int hd) {
+    return TC_AUX + (hd / 32) * (TC_KATOM + 4 * TC_VATOM) + TC_SP + (hd / 32) * TC_QATOM * (hd <= 96 ? 2 : 1);
+}
+static_assert(tc_smem_bytes(128) <= 227 * 1024 && tc_smem_bytes(96) <= 227 * 1024, "shared memory budget");
 constexpr uint32_t TC_TMEM_COLS = 512;        // two score tiles of 256 columns; O_t reuses columns 0..127 of S_t, the row sums 128..131
 
 struct TcParams {
@@ -93,18 +97,22 @@ __global__ void __launch_bounds__(TC_THREADS, 1)
 attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__ CUtensorMap tk, const __grid_constant__ CUtensorMap tv,
                    const TcParams p) {
     extern __shared__ __align__(1024) uint8_t smem[];
-    uint8_t* sK = smem;
-    uint8_t* sV = sK + TC_SK;
-    uint8_t* sP = sV + TC_SV;
+    const int natoms = p.hd / 32;
+    const bool two_q = p.hd <= 96;  // both query tiles resident; otherwise tile 1 takes tile 0's slot once S0 is complete
+    const int q_bytes = natoms * TC_QATOM, k_bytes = natoms * TC_KATOM, v_bytes = natoms * 4 * TC_VATOM;
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem);
+    uint8_t* sK = smem + TC_AUX;
+    uint8_t* sV = sK + k_bytes;
+    uint8_t* sP = sV + v_bytes;
     uint8_t* sQ = sP + TC_SP;
-    uint64_t* bars = reinterpret_cast<uint64_t*>(sQ + TC_SQ);
+    uint8_t* sQ1 = two_q ? sQ + q_bytes : sQ;
     uint64_t* bar_q0k = bars;      // Q tile 0 and K landed
     uint64_t* bar_q1 = bars + 1;   // Q tile 1 landed
     uint64_t* bar_v = bars + 2;    // V landed
     uint64_t* bar_s = bars + 3;    // [2] scores of tile t complete in TMEM
     uint64_t* bar_o = bars + 5;    // [2] output of tile t complete in TMEM
     uint64_t* bar_free = bars + 7; // [2] output of tile t has been read: its TMEM columns may take the next item's scores
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 16);
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 16);  // (aux: 128 + 16 + 32 + 2048 bytes <= TC_AUX)
     uint32_t* key_ok = tmem_slot + 4;                            // 8 words: bit j of word w = key 32 w + j is usable
     float* red_max = reinterpret_cast<float*>(key_ok + 8);       // [4][128] partial row maxima
 
@@ -134,29 +142,27 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant
     pdl_trigger();
 
     if (warp == TC_MMA_WARP) {
-        auto load_q0k = [&](int item) {
+        auto load_q0k = [&](int item) {  // K, query tile 0 and, where it has a slot of its own, query tile 1
             const int row0 = (item / p.H) * p.S, col0 = (item % p.H) * p.hd;
-            ptx::mbar_expect_tx(bar_q0k, TC_SQ + TC_SK);
-#pragma unroll
-            for (int a = 0; a < 2; ++a) {
-                ptx::tma_load_3d(sK + a * (TC_KEYS * 128), &tk, bar_q0k, col0 + a * 64, row0, 0);
-                ptx::tma_load_3d(sQ + a * (TC_QT * 128), &tq, bar_q0k, col0 + a * 64, row0, 0);
+            const bool with_q1 = two_q && ntiles == 2;
+            ptx::mbar_expect_tx(bar_q0k, (uint32_t)(k_bytes + q_bytes * (with_q1 ? 2 : 1)));
+            for (int a = 0; a < natoms; ++a) {
+                ptx::tma_load_3d(sK + a * TC_KATOM, &tk, bar_q0k, col0 + a * 32, row0, 0);
+                ptx::tma_load_3d(sQ + a * TC_QATOM, &tq, bar_q0k, col0 + a * 32, row0, 0);
+                if (with_q1) ptx::tma_load_3d(sQ1 + a * TC_QATOM, &tq, bar_q0k, col0 + a * 32, row0 + TC_QT, 0);
             }
         };
-        auto load_q1 = [&](int item) {
+        auto load_q1 = [&](int item) {  // only without a second slot
             const int row0 = (item / p.H) * p.S, col0 = (item % p.H) * p.hd;
-            ptx::mbar_expect_tx(bar_q1, TC_SQ);
-#pragma unroll
-            for (int a = 0; a < 2; ++a) ptx::tma_load_3d(sQ + a * (TC_QT * 128), &tq, bar_q1, col0 + a * 64, row0 + TC_QT, 0);
+            ptx::mbar_expect_tx(bar_q1, (uint32_t)q_bytes);
+            for (int a = 0; a < natoms; ++a) ptx::tma_load_3d(sQ1 + a * TC_QATOM, &tq, bar_q1, col0 + a * 32, row0 + TC_QT, 0);
         };
         auto load_v = [&](int item) {
             const int row0 = (item / p.H) * p.S, col0 = (item % p.H) * p.hd;
-            ptx::mbar_expect_tx(bar_v, TC_SV);
-#pragma unroll
+            ptx::mbar_expect_tx(bar_v, (uint32_t)v_bytes);
             for (int kb = 0; kb < 4; ++kb)
-#pragma unroll
-                for (int a = 0; a < 2; ++a)
-                    ptx::tma_load_3d(sV + kb * 16384 + a * 8192, &tv, bar_v, col0 + a * 64, row0 + kb * 64, 0);
+                for (int a = 0; a < natoms; ++a)
+                    ptx::tma_load_3d(sV + (kb * natoms + a) * TC_VATOM, &tv, bar_v, col0 + a * 32, row0 + kb * 64, 0);
         };
         if (lane == 0) {
             load_q0k(blockIdx.x);
@@ -172,19 +178,20 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant
                 constexpr uint32_t idesc_qk = ptx::instr_desc_bf16(TC_QT, TC_KEYS, false, false);
                 TC_STAMP(0);
                 for (int t = 0; t < ntiles; ++t) {
-                    if (t == 1) {  // the query slot is free once S0 is complete: it takes the second query tile
+                    if (t == 1 && !two_q) {  // the query slot is free once S0 is complete: it takes the second query tile
                         ptx::mbar_wait(&bar_s[0], ph);
                         load_q1(item);
                     }
-                    ptx::mbar_wait(t == 0 ? bar_q0k : bar_q1, ph);
+                    if (t == 0 || !two_q) ptx::mbar_wait(t == 0 ? bar_q0k : bar_q1, ph);
                     TC_STAMP(1 + 3 * t);
                     if (it > 0) ptx::mbar_wait(&bar_free[t], ph ^ 1u);  // the previous item's output tile t has left TMEM
                     TC_STAMP(2 + 3 * t);
                     ptx::tcgen05_fence_after();
+                    const uint32_t q_base = ptx::smem_u32(t == 0 ? sQ : sQ1);
                     for (int k = 0; k < ksteps; ++k) {
-                        const uint32_t off = (uint32_t)(k >> 2) * 128u, kin = (uint32_t)(k & 3) * 32u;  // atom, 16 columns = 32 B inside it
-                        const uint64_t ad = ptx::smem_desc_sw128(ptx::smem_u32(sQ) + off * TC_QT + kin, 0, 1024);
-                        const uint64_t bd = ptx::smem_desc_sw128(ptx::smem_u32(sK) + off * TC_KEYS + kin, 0, 1024);
+                        const uint32_t a = (uint32_t)(k >> 1), kin = (uint32_t)(k & 1) * 32u;  // 32-column atom, 16 columns = 32 B inside it
+                        const uint64_t ad = ptx::smem_desc_sw64(q_base + a * TC_QATOM + kin, 0, 512);
+                        const uint64_t bd = ptx::smem_desc_sw64(ptx::smem_u32(sK) + a * TC_KATOM + kin, 0, 512);
                         ptx::umma_bf16(tmem_base + (uint32_t)t * 256u, ad, bd, idesc_qk, k > 0 ? 1u : 0u);
                     }
                     ptx::umma_commit(&bar_s[t]);
@@ -205,13 +212,14 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant
                     TC_STAMP(8 + 2 * t);
                     if (t == 0) ptx::mbar_wait(bar_v, ph);
                     ptx::tcgen05_fence_after();
-                    constexpr uint32_t idesc_pv = ptx::instr_desc_bf16(TC_QT, 128, false, true);
+                    const uint32_t idesc_pv = ptx::instr_desc_bf16(TC_QT, p.hd, false, true);  // N = hd: hd / 32 MN-major atoms
 #pragma unroll 1
                     for (int kb = 0; kb < 4; ++kb) {
 #pragma unroll
                         for (int k = 0; k < 4; ++k) {
                             const uint64_t ad = ptx::smem_desc_sw128(ptx::smem_u32(sP) + kb * (TC_QT * 128) + k * 32, 0, 1024);
-                            const uint64_t bd = ptx::smem_desc_sw128(ptx::smem_u32(sV) + kb * 16384 + k * 2048, 8192, 1024);
+                            // 64-key block kb: atoms TC_VATOM apart (LBO), 8-key groups 512 B apart (SBO), 16 keys = 1024 B per k-step
+                            const uint64_t bd = ptx::smem_desc_sw64(ptx::smem_u32(sV) + kb * natoms * TC_VATOM + k * 1024, TC_VATOM, 512);
                             ptx::umma_bf16(tmem_base + (uint32_t)t * 256u, ad, bd, idesc_pv, (kb > 0 || k > 0) ? 1u : 0u);
                         }
                     }
@@ -392,12 +400,12 @@ bool tc_supported(int hd, int64_t S, int planes, int64_t rows) {
 int fwd_long_tc(int hd, const m2f_planes_t* q, const m2f_planes_t* k, const m2f_planes_t* v, const uint8_t* pad, int64_t B, int S, int H,
                 const OutView& o, cudaStream_t st) {
     CUtensorMap tq, tk, tv;
-    M2F_TRY(make_planes_tmap(&tq, q, TC_QT));
-    M2F_TRY(make_planes_tmap(&tk, k, TC_KEYS));
-    M2F_TRY(make_planes_tmap(&tv, v, 64));
+    M2F_TRY(make_planes_tmap_sw64(&tq, q, TC_QT));
+    M2F_TRY(make_planes_tmap_sw64(&tk, k, TC_KEYS));
+    M2F_TRY(make_planes_tmap_sw64(&tv, v, 64));
     static bool attr_set = false;
     if (!attr_set) {
-        M2F_CUDA(cudaFuncSetAttribute(attn_fwd_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM));
+        M2F_CUDA(cudaFuncSetAttribute(attn_fwd_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, tc_smem_bytes(128)));
         attr_set = true;
     }
     TcParams p;
@@ -417,7 +425,7 @@ int fwd_long_tc(int hd, const m2f_planes_t* q, const m2f_planes_t* k, const m2f_
         M2F_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
     }
     const unsigned grid = (unsigned)std::min<int64_t>(B * H, sms);  // persistent: one CTA per SM walks the (dialogue, head) items
-    M2F_CUDA(launch_chain(attn_fwd_tc_kernel, dim3(grid), dim3(TC_THREADS), (size_t)TC_SMEM, st, 1, tq, tk, tv, p));
+    M2F_CUDA(launch_chain(attn_fwd_tc_kernel, dim3(grid), dim3(TC_THREADS), (size_t)tc_smem_bytes(hd), st, 1, tq, tk, tv, p));
     M2F_LAUNCH_CHECK();
     return M2F_OK;
 }

@@ -58,6 +58,7 @@ constexpr int EPI2_WARP_BYTES = 23 * 1024;
 
 // host helpers (gemm_sm100.cu)
 int make_planes_tmap(CUtensorMap* map, const m2f_planes_t* t, int box_rows);
+int make_planes_tmap_sw64(CUtensorMap* map, const m2f_planes_t* t, int box_rows);  // 32-column boxes, 64-byte swizzle
 constexpr int GEMM_TILE_CTA2 = 0x1000;
 int gemm_block_n(int64_t M, int64_t N, int64_t K);   // tile code: BLOCK_N | GEMM_TILE_CTA2
 int gemm_b_box_rows(int tile);            // rows of B one CTA stages per k-block (K-major tensor-map box)

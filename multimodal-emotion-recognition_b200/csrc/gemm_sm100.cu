@@ -749,6 +749,24 @@ int make_planes_tmap(CUtensorMap* map, const m2f_planes_t* t, int box_rows) {
     return M2F_OK;
 }
 
+// the same view with 32-column boxes and the 64-byte swizzle (attention_tc.cu: head sizes that are multiples of 32, not of 64)
+int make_planes_tmap_sw64(CUtensorMap* map, const m2f_planes_t* t, int box_rows) {
+    EncodeTiledFn enc = get_encode_fn();
+    M2F_REQUIRE(enc != nullptr, M2F_ERR_CUDA, "cuTensorMapEncodeTiled entry point not available");
+    M2F_REQUIRE(t->ptr != nullptr && t->rows > 0 && t->cols > 0 && t->planes >= 1 && t->planes <= 3, M2F_ERR_ARG, "tensor map: bad planes view");
+    M2F_REQUIRE((reinterpret_cast<uintptr_t>(t->ptr) & 15) == 0 && (t->ld % 8) == 0 && t->ld >= t->cols, M2F_ERR_ALIGN,
+                "tensor map: base must be 16-byte aligned and ld a multiple of 8");
+    cuuint64_t dims[3] = {(cuuint64_t)t->cols, (cuuint64_t)t->rows, (cuuint64_t)t->planes};
+    const int64_t ps = t->planes > 1 ? t->plane_stride : t->rows * t->ld;
+    cuuint64_t strides[2] = {(cuuint64_t)t->ld * 2, (cuuint64_t)ps * 2};
+    cuuint32_t box[3] = {32, (cuuint32_t)box_rows, 1};
+    cuuint32_t estr[3] = {1, 1, 1};
+    CUresult r = enc(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, t->ptr, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                     CU_TENSOR_MAP_SWIZZLE_64B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    M2F_REQUIRE(r == CUDA_SUCCESS, M2F_ERR_CUDA, "cuTensorMapEncodeTiled (64-byte swizzle) failed with CUresult %d", (int)r);
+    return M2F_OK;
+}
+
 // 2-D / 3-D tensor map with a 32 x 32 box for the TMA epilogue
 static int make_epi_tmap(CUtensorMap* map, CUtensorMapDataType dt, int esize, void* ptr, int64_t rows, int64_t cols, int64_t ld, int planes,
                          int64_t plane_stride) {

@@ -224,6 +224,17 @@ __device__ __forceinline__ uint64_t smem_desc_sw128(uint32_t smem_addr, uint32_t
     return d;
 }
 
+// the same with a 64-byte swizzle (field value 4): 32-element bf16 atoms, 64-byte rows, 8-row groups 512 bytes apart
+__device__ __forceinline__ uint64_t smem_desc_sw64(uint32_t smem_addr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
+    uint64_t d = 0;
+    d |= (uint64_t)((smem_addr >> 4) & 0x3FFF);
+    d |= (uint64_t)((lbo_bytes >> 4) & 0x3FFF) << 16;
+    d |= (uint64_t)((sbo_bytes >> 4) & 0x3FFF) << 32;
+    d |= (uint64_t)1 << 46;
+    d |= (uint64_t)4 << 61;
+    return d;
+}
+
 // Instruction descriptor, kind::f16: [4,6) D format 1 = f32 | [7,10) A format 1 = bf16 | [10,13) B format
 // 1 = bf16 | [15] A major (1 = MN) | [16] B major | [17,23) N >> 3 | [24,29) M >> 4
 __host__ __device__ constexpr uint32_t instr_desc_bf16(int M, int N, bool a_mn, bool b_mn) {
