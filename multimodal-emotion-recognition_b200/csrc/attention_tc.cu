@@ -168,64 +168,94 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant
             load_q0k(blockIdx.x);
             load_v(blockIdx.x);
         }
+        constexpr uint32_t idesc_qk = ptx::instr_desc_bf16(TC_QT, TC_KEYS, false, false);
+        const uint32_t idesc_pv = ptx::instr_desc_bf16(TC_QT, p.hd, false, true);  // N = hd: hd / 32 MN-major atoms
+        auto issue_qk = [&](int t) {  // S_t = Q_t K^T
+            ptx::tcgen05_fence_after();
+            const uint32_t q_base = ptx::smem_u32(t == 0 ? sQ : sQ1);
+            for (int k = 0; k < ksteps; ++k) {
+                const uint32_t a = (uint32_t)(k >> 1), kin = (uint32_t)(k & 1) * 32u;  // 32-column atom, 16 columns = 32 B inside it
+                const uint64_t ad = ptx::smem_desc_sw64(q_base + a * TC_QATOM + kin, 0, 512);
+                const uint64_t bd = ptx::smem_desc_sw64(ptx::smem_u32(sK) + a * TC_KATOM + kin, 0, 512);
+                ptx::umma_bf16(tmem_base + (uint32_t)t * 256u, ad, bd, idesc_qk, k > 0 ? 1u : 0u);
+            }
+            ptx::umma_commit(&bar_s[t]);
+        };
+        auto issue_pv = [&](int t) {  // O_t = P_t V
+            ptx::tcgen05_fence_after();
+#pragma unroll 1
+            for (int kb = 0; kb < 4; ++kb) {
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                    const uint64_t ad = ptx::smem_desc_sw128(ptx::smem_u32(sP) + kb * (TC_QT * 128) + k * 32, 0, 1024);
+                    // 64-key block kb: atoms TC_VATOM apart (LBO), 8-key groups 512 B apart (SBO), 16 keys = 1024 B per k-step
+                    const uint64_t bd = ptx::smem_desc_sw64(ptx::smem_u32(sV) + kb * natoms * TC_VATOM + k * 1024, TC_VATOM, 512);
+                    ptx::umma_bf16(tmem_base + (uint32_t)t * 256u, ad, bd, idesc_pv, (kb > 0 || k > 0) ? 1u : 0u);
+                }
+            }
+            ptx::umma_commit(&bar_o[t]);
+        };
         int it = 0;
+        bool qk0_issued = false;  // S0 of the coming item was already issued ahead of the previous item's last output product
         for (int item = blockIdx.x; item < p.items; item += gridDim.x, ++it) {
             const uint32_t ph = (uint32_t)(it & 1);
             const int next = item + (int)gridDim.x;
             const bool has_next = next < p.items;
             if (lane == 0) {
-                // ------------------------------------------------------------ S_t = Q_t K^T
-                constexpr uint32_t idesc_qk = ptx::instr_desc_bf16(TC_QT, TC_KEYS, false, false);
                 TC_STAMP(0);
-                for (int t = 0; t < ntiles; ++t) {
-                    if (t == 1 && !two_q) {  // the query slot is free once S0 is complete: it takes the second query tile
+                if (!qk0_issued) {
+                    ptx::mbar_wait(bar_q0k, ph);
+                    TC_STAMP(1);
+                    if (it > 0) ptx::mbar_wait(&bar_free[0], ph ^ 1u);  // the previous item's output tile 0 has left TMEM
+                    TC_STAMP(2);
+                    issue_qk(0);
+                    TC_STAMP(3);
+                }
+                if (ntiles == 2) {
+                    if (!two_q) {  // the query slot is free once S0 is complete: it takes the second query tile
                         ptx::mbar_wait(&bar_s[0], ph);
                         load_q1(item);
+                        ptx::mbar_wait(bar_q1, ph);
                     }
-                    if (t == 0 || !two_q) ptx::mbar_wait(t == 0 ? bar_q0k : bar_q1, ph);
-                    TC_STAMP(1 + 3 * t);
-                    if (it > 0) ptx::mbar_wait(&bar_free[t], ph ^ 1u);  // the previous item's output tile t has left TMEM
-                    TC_STAMP(2 + 3 * t);
-                    ptx::tcgen05_fence_after();
-                    const uint32_t q_base = ptx::smem_u32(t == 0 ? sQ : sQ1);
-                    for (int k = 0; k < ksteps; ++k) {
-                        const uint32_t a = (uint32_t)(k >> 1), kin = (uint32_t)(k & 1) * 32u;  // 32-column atom, 16 columns = 32 B inside it
-                        const uint64_t ad = ptx::smem_desc_sw64(q_base + a * TC_QATOM + kin, 0, 512);
-                        const uint64_t bd = ptx::smem_desc_sw64(ptx::smem_u32(sK) + a * TC_KATOM + kin, 0, 512);
-                        ptx::umma_bf16(tmem_base + (uint32_t)t * 256u, ad, bd, idesc_qk, k > 0 ? 1u : 0u);
-                    }
-                    ptx::umma_commit(&bar_s[t]);
-                    TC_STAMP(3 + 3 * t);
+                    TC_STAMP(4);
+                    if (it > 0) ptx::mbar_wait(&bar_free[1], ph ^ 1u);  // the previous item's output tile 1 has left TMEM
+                    TC_STAMP(5);
+                    issue_qk(1);
+                    TC_STAMP(6);
                 }
-                if (has_next) {  // K and the query slot are free once the score products are complete
+                if (has_next) {  // K and the query slots are free once the score products are complete
                     ptx::mbar_wait(&bar_s[ntiles - 1], ph);
                     TC_STAMP(7);
                     load_q0k(next);
                 }
             }
             __syncwarp();
-            for (int t = 0; t < ntiles; ++t) {
-                // the probabilities of tile t are in shared memory once all softmax threads have passed this named barrier
-                ptx::named_bar_sync(2 + t, TC_BAR_THREADS);
+            // the probabilities of tile 0 are in shared memory once all softmax threads have passed this named barrier
+            ptx::named_bar_sync(2, TC_BAR_THREADS);
+            if (lane == 0) {
+                TC_STAMP(8);
+                ptx::mbar_wait(bar_v, ph);
+                issue_pv(0);
+                TC_STAMP(9);
+            }
+            __syncwarp();
+            qk0_issued = false;
+            if (ntiles == 2) {
+                ptx::named_bar_sync(3, TC_BAR_THREADS);
                 if (lane == 0) {
-                    // -------------------------------------------------------- O_t = P_t V
-                    TC_STAMP(8 + 2 * t);
-                    if (t == 0) ptx::mbar_wait(bar_v, ph);
-                    ptx::tcgen05_fence_after();
-                    const uint32_t idesc_pv = ptx::instr_desc_bf16(TC_QT, p.hd, false, true);  // N = hd: hd / 32 MN-major atoms
-#pragma unroll 1
-                    for (int kb = 0; kb < 4; ++kb) {
-#pragma unroll
-                        for (int k = 0; k < 4; ++k) {
-                            const uint64_t ad = ptx::smem_desc_sw128(ptx::smem_u32(sP) + kb * (TC_QT * 128) + k * 32, 0, 1024);
-                            // 64-key block kb: atoms TC_VATOM apart (LBO), 8-key groups 512 B apart (SBO), 16 keys = 1024 B per k-step
-                            const uint64_t bd = ptx::smem_desc_sw64(ptx::smem_u32(sV) + kb * natoms * TC_VATOM + k * 1024, TC_VATOM, 512);
-                            ptx::umma_bf16(tmem_base + (uint32_t)t * 256u, ad, bd, idesc_pv, (kb > 0 || k > 0) ? 1u : 0u);
-                        }
+                    TC_STAMP(10);
+                    if (has_next) {
+                        // the next item's first score product goes AHEAD of this item's second output product: the softmax warps are
+                        // about to wait for it, the output warps have no deadline.  Its operands were requested long ago and output
+                        // tile 0 of this item was stored while the softmax warps worked on tile 1.
+                        ptx::mbar_wait(bar_q0k, ph ^ 1u);
+                        ptx::mbar_wait(&bar_free[0], ph);
+                        issue_qk(0);
                     }
-                    ptx::umma_commit(&bar_o[t]);
-                    TC_STAMP(9 + 2 * t);
+                    issue_pv(1);
+                    TC_STAMP(11);
                 }
+                qk0_issued = has_next;
                 __syncwarp();
             }
             if (lane == 0 && has_next) {  // V is free once the last output product is complete
