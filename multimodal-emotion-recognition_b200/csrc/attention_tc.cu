@@ -258,12 +258,6 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant
                 qk0_issued = has_next;
                 __syncwarp();
             }
-            if (lane == 0 && has_next) {  // V is free once the last output product is complete
-                ptx::mbar_wait(&bar_o[ntiles - 1], ph);
-                TC_STAMP(12);
-                load_v(next);
-            }
-            __syncwarp();
         }
     } else if (warp < TC_SOFTMAX_WARPS) {
         // -------------------------------------------------------------------- softmax: thread = (query row, quarter of the keys)
@@ -362,7 +356,7 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant
                     if (threadIdx.x == 0) TC_STAMP(20 + 5 * t);
                     ptx::fence_proxy_async();      // the probabilities are read by the tensor core through the async proxy
                     ptx::tcgen05_fence_before();   // ... and this tile's score columns are about to be overwritten by its output
-                    ptx::named_bar_sync(2 + t, TC_BAR_THREADS);  // releases the MMA thread
+                    ptx::named_bar_arrive(2 + t, TC_BAR_THREADS);  // releases the MMA warp (which syncs on it); no waiting on this side
                     if (threadIdx.x == 0) TC_STAMP(21 + 5 * t);
                 }
             }
@@ -375,10 +369,21 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant
         for (int item = blockIdx.x; item < p.items; item += gridDim.x, ++it) {
             const uint32_t ph = (uint32_t)(it & 1);
             const int row0 = (item / p.H) * p.S, col0 = (item % p.H) * p.hd;
+            const int next = item + (int)gridDim.x;
             for (int t = 0; t < ntiles; ++t) {
                 ptx::mbar_wait(&bar_o[t], ph);
                 ptx::tcgen05_fence_after();
-                if (threadIdx.x == TC_SOFTMAX_THREADS) TC_STAMP(28 + 2 * t);
+                if (threadIdx.x == TC_SOFTMAX_THREADS) {
+                    TC_STAMP(28 + 2 * t);
+                    if (t == ntiles - 1 && next < p.items) {  // V is free once the item's last output product is complete: the first
+                        // output thread requests the next item's V (the MMA lane does not have to come back for it)
+                        const int nrow0 = (next / p.H) * p.S, ncol0 = (next % p.H) * p.hd;
+                        ptx::mbar_expect_tx(bar_v, (uint32_t)v_bytes);
+                        for (int kb = 0; kb < 4; ++kb)
+                            for (int a = 0; a < natoms; ++a)
+                                ptx::tma_load_3d(sV + (kb * natoms + a) * TC_VATOM, &tv, bar_v, ncol0 + a * 32, nrow0 + kb * 64, 0);
+                    }
+                }
                 const uint32_t t_tile = tmem_base + (uint32_t)t * 256u + ((uint32_t)(lg * 32) << 16);
                 uint32_t sums[4];
                 tmem_ld_4(t_tile + 128u, sums);
