@@ -31,7 +31,7 @@ constexpr int TC_QT = 128;     // query rows per tile (TMEM lanes)
 constexpr int TC_KEYS = 256;   // key tile = the whole (padded) dialogue
 constexpr int TC_SOFTMAX_WARPS = 16;          // four threads per query row, 64 keys each
 constexpr int TC_SOFTMAX_THREADS = TC_SOFTMAX_WARPS * 32;
-constexpr int TC_OUT_WARPS = 4;               // one thread per query row: output tile TMEM -> global
+constexpr int TC_OUT_WARPS = 8;               // two threads per query row (alternate 32-column chunks): output tile TMEM -> global
 constexpr int TC_OUT_THREADS = TC_OUT_WARPS * 32;
 constexpr int TC_MMA_WARP = TC_SOFTMAX_WARPS + TC_OUT_WARPS;
 constexpr int TC_THREADS = (TC_MMA_WARP + 1) * 32;
@@ -117,7 +117,6 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant
     float* red_max = reinterpret_cast<float*>(key_ok + 8);       // [4][128] partial row maxima
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int ksteps = p.hd / 16;      // k-steps of the first product (hd = 64 / 96 / 128)
     const int ntiles = p.S > TC_QT ? 2 : 1;
 
     if (threadIdx.x == 0 && (ptx::smem_u32(smem) & 1023u) != 0) {
@@ -170,28 +169,33 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant
         }
         constexpr uint32_t idesc_qk = ptx::instr_desc_bf16(TC_QT, TC_KEYS, false, false);
         const uint32_t idesc_pv = ptx::instr_desc_bf16(TC_QT, p.hd, false, true);  // N = hd: hd / 32 MN-major atoms
+        // The issuing thread is one lane: every instruction between two MMAs is latency on the tensor core's queue, so the descriptors
+        // are built once per atom and advanced by adding to their address field (bits 0..13, in 16-byte units).
         auto issue_qk = [&](int t) {  // S_t = Q_t K^T
             ptx::tcgen05_fence_after();
             const uint32_t q_base = ptx::smem_u32(t == 0 ? sQ : sQ1);
-            for (int k = 0; k < ksteps; ++k) {
-                const uint32_t a = (uint32_t)(k >> 1), kin = (uint32_t)(k & 1) * 32u;  // 32-column atom, 16 columns = 32 B inside it
-                const uint64_t ad = ptx::smem_desc_sw64(q_base + a * TC_QATOM + kin, 0, 512);
-                const uint64_t bd = ptx::smem_desc_sw64(ptx::smem_u32(sK) + a * TC_KATOM + kin, 0, 512);
-                ptx::umma_bf16(tmem_base + (uint32_t)t * 256u, ad, bd, idesc_qk, k > 0 ? 1u : 0u);
+            const uint32_t d_tmem = tmem_base + (uint32_t)t * 256u;
+            for (int a = 0; a < natoms; ++a) {  // 32-column atom = two k-steps of 16 columns (32 B apart)
+                const uint64_t ad = ptx::smem_desc_sw64(q_base + a * TC_QATOM, 0, 512);
+                const uint64_t bd = ptx::smem_desc_sw64(ptx::smem_u32(sK) + a * TC_KATOM, 0, 512);
+                ptx::umma_bf16(d_tmem, ad, bd, idesc_qk, a > 0 ? 1u : 0u);
+                ptx::umma_bf16(d_tmem, ad + 2, bd + 2, idesc_qk, 1u);
             }
             ptx::umma_commit(&bar_s[t]);
         };
         auto issue_pv = [&](int t) {  // O_t = P_t V
             ptx::tcgen05_fence_after();
-#pragma unroll 1
-            for (int kb = 0; kb < 4; ++kb) {
+            const uint32_t d_tmem = tmem_base + (uint32_t)t * 256u;
 #pragma unroll
-                for (int k = 0; k < 4; ++k) {
-                    const uint64_t ad = ptx::smem_desc_sw128(ptx::smem_u32(sP) + kb * (TC_QT * 128) + k * 32, 0, 1024);
-                    // 64-key block kb: atoms TC_VATOM apart (LBO), 8-key groups 512 B apart (SBO), 16 keys = 1024 B per k-step
-                    const uint64_t bd = ptx::smem_desc_sw64(ptx::smem_u32(sV) + kb * natoms * TC_VATOM + k * 1024, TC_VATOM, 512);
-                    ptx::umma_bf16(tmem_base + (uint32_t)t * 256u, ad, bd, idesc_pv, (kb > 0 || k > 0) ? 1u : 0u);
-                }
+            for (int kb = 0; kb < 4; ++kb) {
+                // P: 64-key atom kb, 16 keys = 32 B per k-step.  V: 64-key block kb, atoms TC_VATOM apart (LBO), 8-key groups 512 B
+                // apart (SBO), 16 keys = 1024 B per k-step
+                const uint64_t ad = ptx::smem_desc_sw128(ptx::smem_u32(sP) + kb * (TC_QT * 128), 0, 1024);
+                const uint64_t bd = ptx::smem_desc_sw64(ptx::smem_u32(sV) + kb * natoms * TC_VATOM, TC_VATOM, 512);
+                ptx::umma_bf16(d_tmem, ad, bd, idesc_pv, kb > 0 ? 1u : 0u);
+                ptx::umma_bf16(d_tmem, ad + 2, bd + 64, idesc_pv, 1u);
+                ptx::umma_bf16(d_tmem, ad + 4, bd + 128, idesc_pv, 1u);
+                ptx::umma_bf16(d_tmem, ad + 6, bd + 192, idesc_pv, 1u);
             }
             ptx::umma_commit(&bar_o[t]);
         };
@@ -359,7 +363,7 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant
         }
     } else {
         // -------------------------------------------------------------------- output: thread = query row
-        const int lg = warp & 3;
+        const int lg = warp & 3, part = (warp - TC_SOFTMAX_WARPS) >> 2;  // part 0: chunks 0, 2; part 1: chunks 1, 3
         const int row = lg * 32 + lane;
         int it = 0;
         for (int item = blockIdx.x; item < p.items; item += gridDim.x, ++it) {
@@ -402,7 +406,7 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant
                 const float iv = 1.f / ((__uint_as_float(sums[0]) + __uint_as_float(sums[1])) + (__uint_as_float(sums[2]) + __uint_as_float(sums[3])));
                 const int qrow = t * TC_QT + row;
                 __nv_bfloat16* orow = p.o + ((int64_t)row0 + qrow) * p.o_ld + col0;
-                for (int cc = 0; cc < p.hd; cc += 32) {
+                for (int cc = part * 32; cc < p.hd; cc += 64) {
                     uint32_t r[32];
                     ptx::tmem_ld_32x32(t_tile + (uint32_t)cc, r);
                     ptx::tmem_ld_wait();
