@@ -370,7 +370,7 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant
             const uint32_t ph = (uint32_t)(it & 1);
             const int row0 = (item / p.H) * p.S, col0 = (item % p.H) * p.hd;
             const int next = item + (int)gridDim.x;
-            if (threadIdx.x == TC_SOFTMAX_THREADS + 32 && next < p.items) {
+            if (threadIdx.x == TC_SOFTMAX_THREADS + 5 * 32 && next < p.items) {  // (a warp of the half with fewer chunks)
                 // K and the query slots are free once the item's score products are complete: the second output warp's first thread
                 // requests the next item's (nine TMA instructions that the MMA lane does not have to spend 0.8 us on)
                 ptx::mbar_wait(&bar_s[ntiles - 1], ph);
@@ -388,8 +388,8 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant
             for (int t = 0; t < ntiles; ++t) {
                 ptx::mbar_wait(&bar_o[t], ph);
                 ptx::tcgen05_fence_after();
-                if (threadIdx.x == TC_SOFTMAX_THREADS) {
-                    TC_STAMP(28 + 2 * t);
+                if (threadIdx.x == TC_SOFTMAX_THREADS) TC_STAMP(28 + 2 * t);
+                if (threadIdx.x == TC_SOFTMAX_THREADS + 4 * 32) {
                     if (t == ntiles - 1 && next < p.items) {  // V is free once the item's last output product is complete: the first
                         // output thread requests the next item's V (the MMA lane does not have to come back for it)
                         const int nrow0 = (next / p.H) * p.S, ncol0 = (next % p.H) * p.hd;
