@@ -805,9 +805,9 @@ def hbm_kernel_rooflines(pkg, torch, dev, cfg):
     flops = 4.0 * Sl * Dm * Ml
     add("attention forward, long dialogues (S=256, hd=96, inference; tcgen05 / TMEM / TMA kernel), 512 dialogues x 8 heads", 4 * Ml * Dm * 2 + Ml, us)
     out[-1]["tensor_tflops"] = flops / (us * 1e-6) / 1e12
-    out[-1]["note"] = ("103 GFLOP and 33.5 M exponentials per launch; one CTA per (dialogue, head) and SM: the loads of a CTA are not overlapped with "
-                       "the previous CTA's softmax (shared memory holds one dialogue-head: K, V, Q / P), and the softmax is bound by the 16 "
-                       "ex2 per clock of an SM (2 us of the ~12 us a CTA takes)")
+    out[-1]["note"] = ("103 GFLOP and 33.5 M exponentials per launch; persistent CTAs (one per SM) walk the (dialogue, head) items with the next item's "
+                       "K / Q / V in flight under the current item's softmax; what is left is the softmax itself (16 ex2 per clock per SM: 2.1 us of "
+                       "the ~6.5 us an item takes) and the two score tiles that have to leave TMEM before the next item's second product")
     del q, k, v, o
 
     # fused Adam + bf16 shadow refresh over the model arena
