@@ -95,6 +95,24 @@ struct OutView {
 template <int HD, int SP>
 __device__ __forceinline__ void load_tile(__nv_bfloat16* dst, const View& t, int P, int64_t row0, int col0, int S) {
     constexpr int LDS = HD + 8, CH = HD / 8;
+    if (blockDim.x % CH == 0) {
+        // thread = (row of the pass, 16-byte chunk of the row): one division up front, then pointer increments -- these kernels are
+        // instruction-bound and the index arithmetic of the general loop below was a fifth of their instructions
+        const int rpp = blockDim.x / CH;  // rows per pass
+        const int r0 = threadIdx.x / CH, c = (threadIdx.x - r0 * CH) * 8;
+        const __nv_bfloat16* base = t.ptr + row0 * t.ld + col0 + c;
+        for (int pl = 0; pl < P; ++pl) {
+            const __nv_bfloat16* src = base + pl * t.stride + (int64_t)r0 * t.ld;
+            uint32_t d = ptx::smem_u32(dst + (pl * SP + r0) * LDS + c);
+            for (int r = r0; r < SP; r += rpp) {
+                const bool live = r < S;
+                asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(d), "l"(live ? src : base), "r"(live ? 16 : 0) : "memory");
+                src += (int64_t)rpp * t.ld;
+                d += (uint32_t)(rpp * LDS * 2);
+            }
+        }
+        return;
+    }
     for (int i = threadIdx.x; i < P * SP * CH; i += blockDim.x) {
         const int pl = i / (SP * CH), rem = i - pl * (SP * CH);
         const int r = rem / CH, c = (rem - r * CH) * 8;
@@ -237,13 +255,29 @@ __device__ __forceinline__ uint32_t drop_bits(const Drop& d, uint64_t bh, int S,
     const int g = lane >> 2, q = lane & 3;
     const uint64_t s8o = (uint64_t)((S + 7) >> 3);  // S8 / 8
     uint32_t bits = 0;
+    // The four lanes of a quad own the four words of the same calls (same rows, same 8-key tiles): each lane makes one call out of
+    // four and a 4 x 4 transpose inside the quad (two butterfly stages, four shuffles) hands every lane its word of each call.
 #pragma unroll 1
-    for (int e = 0; e < 2 * (SP / 8); ++e) {
-        const int i = i0 + g + (e & 1) * 8, nt = e >> 1;
-        uint32_t r[4];
-        philox4(d.ph, (bh * S + i) * s8o + nt, r);
-        const uint32_t w = (q & 2) ? ((q & 1) ? r[3] : r[2]) : ((q & 1) ? r[1] : r[0]);
-        bits |= (((w & 0xFFFFu) >= d.thresh ? 1u : 0u) | ((w >> 16) >= d.thresh ? 2u : 0u)) << (2 * e);
+    for (int m = 0; m < (SP / 8) / 2; ++m) {
+        const int e_own = 4 * m + q;
+        uint32_t a[4];
+        philox4(d.ph, (bh * S + (i0 + g + (e_own & 1) * 8)) * s8o + (e_own >> 1), a);
+        {   // stage 1: partner lane ^ 1 -- even lanes hand over words 1, 3 and receive the partner's words 0, 2 into them
+            const bool odd = (q & 1) != 0;
+            const uint32_t x = __shfl_xor_sync(0xffffffffu, odd ? a[0] : a[1], 1), y = __shfl_xor_sync(0xffffffffu, odd ? a[2] : a[3], 1);
+            if (odd) { a[0] = x; a[2] = y; } else { a[1] = x; a[3] = y; }
+        }
+        {   // stage 2: partner lane ^ 2 -- lanes 0, 1 hand over words 2, 3 and receive the partner's words 0, 1 into them
+            const bool hi = (q & 2) != 0;
+            const uint32_t x = __shfl_xor_sync(0xffffffffu, hi ? a[0] : a[2], 2), y = __shfl_xor_sync(0xffffffffu, hi ? a[1] : a[3], 2);
+            if (hi) { a[0] = x; a[1] = y; } else { a[2] = x; a[3] = y; }
+        }
+        // a[j] is now word q of call 4 m + j
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const uint32_t w = a[j];
+            bits |= (((w & 0xFFFFu) >= d.thresh ? 1u : 0u) | ((w >> 16) >= d.thresh ? 2u : 0u)) << (2 * (4 * m + j));
+        }
     }
     return bits;
 }
