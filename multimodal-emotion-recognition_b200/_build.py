@@ -11,7 +11,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 BUILD = os.path.join(HERE, "build")
 LIB = os.path.join(HERE, "libm2f_b200.so")
-SOURCES = ["abi.cu", "gemm_sm100.cu", "layernorm.cu", "attention.cu", "attention_mma_p1.cu", "attention_mma_p2.cu", "attention_mma_p3.cu", "attention_mma_long.cu", "attention_tc.cu", "loss.cu", "loss_static.cu", "optim.cu", "pipeline.cu", "exchange.cu", "plan.cu"]
+SOURCES = ["abi.cu", "gemm_sm100.cu", "gemm_persist.cu", "layernorm.cu", "attention.cu", "attention_mma_p1.cu", "attention_mma_p2.cu", "attention_mma_p3.cu", "attention_mma_long.cu", "attention_tc.cu", "loss.cu", "loss_static.cu", "optim.cu", "pipeline.cu", "exchange.cu", "plan.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "-Xcompiler", "-fPIC", "--use_fast_math=false"]
 

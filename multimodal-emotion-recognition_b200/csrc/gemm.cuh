@@ -60,6 +60,9 @@ constexpr int EPI2_WARP_BYTES = 23 * 1024;
 int make_planes_tmap(CUtensorMap* map, const m2f_planes_t* t, int box_rows);
 int make_planes_tmap_sw64(CUtensorMap* map, const m2f_planes_t* t, int box_rows);  // 32-column boxes, 64-byte swizzle
 constexpr int GEMM_TILE_CTA2 = 0x1000;
+constexpr int GEMM_TILE_PERSIST = 0x2000;  // very many row tiles: the persistent pair kernel (gemm_persist.cu) where its epilogue applies
+bool gemm_persist_eligible(const GemmParams& p, int a_mn, int b_mn);
+int gemm_launch_persist(const CUtensorMap& ta, const CUtensorMap& tb, const EpiMaps& em, const GemmParams& p, cudaStream_t stream);
 int gemm_block_n(int64_t M, int64_t N, int64_t K);   // tile code: BLOCK_N | GEMM_TILE_CTA2
 int gemm_b_box_rows(int tile);            // rows of B one CTA stages per k-block (K-major tensor-map box)
 int gemm_fill_params(GemmParams& p, const m2f_planes_t* A, int a_mn, const m2f_planes_t* B, int b_mn, const m2f_kseg_t* segs,

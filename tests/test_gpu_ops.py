@@ -79,6 +79,36 @@ def test_gemm_wgrad_both_mn_major(ops, M, N, K, planes):
     assert rel(out, ref) < (1e-5 if planes == 1 else 5e-6)
 
 
+@pytest.mark.parametrize("M,N,K,planes,variant", [
+    (70000, 768, 256, 1, "planes"),     # bias + ReLU -> one bf16 plane (FFN1 / fusion linear at inference); M not a multiple of 256
+    (65600, 2304, 192, 1, "planes"),    # nine column tiles, K not a multiple of 64 rounded by the tail k-block
+    (66000, 768, 320, 1, "resid"),      # bias + fp32 residual -> fp32 (out-projection / FFN2 at inference)
+    (65792, 512, 128, 2, "both"),       # two operand planes (three plane products), fp32 and plane output together
+    (65536, 300, 128, 1, "planes"),     # ragged N: the second column tile is clipped
+])
+def test_gemm_persistent_many_row_tiles(ops, M, N, K, planes, variant):
+    """M >= 65 536 (>= 512 row tiles): the persistent pair kernel of gemm_persist.cu -- every pair walks several tiles, two TMEM
+    accumulators, epilogue staging of its own.  Compared with the fp64 product of the same bf16 planes."""
+    X, W = rnd(M, K, seed=31), rnd(N, K, seed=32, scale=K ** -0.5)
+    A, B = ops.PlanesTensor.from_float(X, planes), ops.PlanesTensor.from_float(W, planes)
+    bias = rnd(N, seed=33)
+    ref = A.float().double() @ B.float().double().T + bias.double()
+    if variant == "planes":
+        outp = ops.PlanesTensor.empty(M, N, 1, "cuda", zero=True)
+        ops.gemm(A, B, M, N, bias=bias, relu=True, out_planes=outp)
+        assert rel(outp.float(), torch.relu(ref)) < 4e-3
+    elif variant == "resid":
+        resid = rnd(M, N, seed=34)
+        out = torch.full((M, N), float("nan"), device="cuda")
+        ops.gemm(A, B, M, N, bias=bias, resid=resid, out_f32=out)
+        assert rel(out, ref + resid.double()) < 1e-5
+    else:
+        out = torch.full((M, N), float("nan"), device="cuda")
+        outp = ops.PlanesTensor.empty(M, N, 1, "cuda", zero=True)
+        ops.gemm(A, B, M, N, bias=bias, out_f32=out, out_planes=outp)
+        assert rel(out, ref) < 1e-5 and rel(outp.float(), ref) < 4e-3
+
+
 def test_gemm_a_mn_b_k_major(ops):
     M, N, K = 300, 200, 192
     At, W = rnd(K, M, seed=7), rnd(N, K, seed=8)
