@@ -839,11 +839,13 @@ int gemm_block_n(int64_t M, int64_t N, int64_t K) {
     // ... except with very many row tiles (M >= 65 536: the C5 inference batch has 1024): there every launch is many waves, and two
     // single CTAs per SM, one in its epilogue while the other is in its main loop, beat one pair per SM whose epilogue overlaps
     // nothing (C5 batch 43.5 -> 41.5 ms, tools/gpu_r2_c5_tiles.sh).
-    // With >= 512 row tiles and at least one full 256-wide column tile the launch goes to the persistent pair kernel (gemm_persist.cu:
-    // tile loop, two TMEM accumulators) when its epilogue applies, else to the plain pair kernel; M2F_GEMM_PERSIST=0 restores the
-    // single CTAs.
+    // Launches of two and more 256 x 256 tiles per pair of SMs (and everything with >= 512 row tiles) go to the persistent pair kernel
+    // (gemm_persist.cu: tile loop, two TMEM accumulators) when its epilogue applies, else to the plain pair kernel;
+    // M2F_GEMM_PERSIST=0 restores the previous policy.
     static const bool persist_off = [] { const char* e = std::getenv("M2F_GEMM_PERSIST"); return e && e[0] == '0'; }();
-    if (pairs == 1 && !forced && !persist_off && mt >= 512 && N >= 256) return 256 | GEMM_TILE_CTA2 | GEMM_TILE_PERSIST;
+    const int64_t pair_tiles = ((M + 2 * BLOCK_M - 1) / (2 * BLOCK_M)) * ((N + 255) / 256);
+    if (pairs == 1 && !forced && !persist_off && N >= 256 && (mt >= 512 || pair_tiles >= 148))  // two tiles and more per pair of SMs
+        return 256 | GEMM_TILE_CTA2 | GEMM_TILE_PERSIST;
     if (pairs == 1 && N > 64 && mt < 512) {
         const int bn = (forced == 128 || forced == 256) ? forced : 256;
         return ((N <= 128) ? 128 : bn) | GEMM_TILE_CTA2;
