@@ -7,8 +7,9 @@
 // therefore has shared memory of its own (10 KB per warp) instead of borrowing the ring, and the ring is four stages of 32 KB.
 // One launch = one wave of pairs: no prologue / tear-down / launch gap per tile, and the pair tile halves the L2 -> SM bytes
 // per flop of the two single CTAs per SM that these shapes used before.
-// Epilogue features: bias, ReLU, fp32 residual, fp32 output, one bf16 output plane (what inference launches); anything else
-// (dropout, gates, accumulation, column sums, 2 - 3 planes, MN-major operands) stays with gemm_sm100.cu.
+// Epilogue features: bias, ReLU, fp32 residual, fp32 output, 1 - 3 bf16 output planes as far as the 10 KB of staging per warp hold
+// them (what inference launches, in every precision mode); anything else (dropout, gates, accumulation, column sums, MN-major
+// operands) stays with gemm_sm100.cu.
 #include <cstdlib>
 
 #include "common.cuh"
@@ -26,7 +27,7 @@ constexpr int PS_B_BYTES = (PS_BN / 2) * BLOCK_K * 2;      // this CTA's half of
 constexpr int PS_STAGE_BYTES = PS_A_BYTES + PS_B_BYTES;
 constexpr int PS_EPI_WARPS = 8;
 constexpr int PS_THREADS = 64 + 32 * PS_EPI_WARPS;
-constexpr int PS_WARP_STG = 4096 + 2048 + 4096;            // fp32 output tile | bf16 plane tile | residual tile
+constexpr int PS_WARP_STG = 10240;                         // per epilogue warp: fp32 output tile 4 KB | bf16 plane tiles 2 KB each | residual tile 4 KB, whichever are present
 constexpr int PS_OFF_STG = PS_STAGES * PS_STAGE_BYTES;
 constexpr int PS_OFF_BIAS = PS_OFF_STG + PS_EPI_WARPS * PS_WARP_STG;  // 2 x 256 floats (one per accumulator)
 constexpr int PS_OFF_BAR = PS_OFF_BIAS + 2 * PS_BN * 4;
@@ -142,11 +143,13 @@ gemm_persist_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_cons
     } else {
         // ---------------------------------------------------------------------- epilogue warps
         const int ew = warp - 2, lg = warp & 3;
-        const uint32_t s_of = ptx::smem_u32(smem + PS_OFF_STG) + (uint32_t)(ew * PS_WARP_STG), s_pl = s_of + 4096u, s_res = s_pl + 2048u;
-        uint64_t* rbar = &res_bar[ew];
-        const uint32_t sw128 = (uint32_t)(lane & 7), sw64 = (uint32_t)((lane >> 1) & 3);
         const bool f_bias = p.bias != nullptr, f_relu = p.relu != 0, f_res = p.resid != nullptr, f_of32 = p.out_f32 != nullptr,
                    f_opl = p.out_pl != nullptr;
+        const int n_pl = f_opl ? p.out_pl_n : 0;
+        const uint32_t s_of = ptx::smem_u32(smem + PS_OFF_STG) + (uint32_t)(ew * PS_WARP_STG);
+        const uint32_t s_pl = s_of + (f_of32 ? 4096u : 0u), s_res = s_pl + (uint32_t)n_pl * 2048u;
+        uint64_t* rbar = &res_bar[ew];
+        const uint32_t sw128 = (uint32_t)(lane & 7), sw64 = (uint32_t)((lane >> 1) & 3);
         const uint32_t acc_empty_leader = ptx::mapa(ptx::smem_u32(&acc_empty[0]), 0);
         uint32_t rphase = 0;
         int i = 0;
@@ -209,22 +212,27 @@ gemm_persist_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_cons
                             ps_sts128(s_of + (uint32_t)lane * 128u + (((uint32_t)j ^ sw128) << 4), __float_as_uint(x[4 * j]), __float_as_uint(x[4 * j + 1]),
                                       __float_as_uint(x[4 * j + 2]), __float_as_uint(x[4 * j + 3]));
                     }
-                    if (f_opl) {
+                    for (int pl = 0; pl < n_pl; ++pl) {  // hi plane, then the rounded residuals
                         uint32_t h[16];
 #pragma unroll
                         for (int j = 0; j < 16; ++j) {
                             const __nv_bfloat162 b2 = __floats2bfloat162_rn(x[2 * j], x[2 * j + 1]);
                             h[j] = *reinterpret_cast<const uint32_t*>(&b2);
+                            if (pl + 1 < n_pl) {
+                                x[2 * j] -= __low2float(b2);
+                                x[2 * j + 1] -= __high2float(b2);
+                            }
                         }
 #pragma unroll
                         for (int j = 0; j < 4; ++j)
-                            ps_sts128(s_pl + (uint32_t)lane * 64u + (((uint32_t)j ^ sw64) << 4), h[4 * j], h[4 * j + 1], h[4 * j + 2], h[4 * j + 3]);
+                            ps_sts128(s_pl + (uint32_t)pl * 2048u + (uint32_t)lane * 64u + (((uint32_t)j ^ sw64) << 4), h[4 * j], h[4 * j + 1],
+                                      h[4 * j + 2], h[4 * j + 3]);
                     }
                     ptx::fence_proxy_async();
                     __syncwarp();
                     if (lane == 0) {
                         if (f_of32) ptx::tma_store_2d(&em.out_f32, s_of, n0, m0);
-                        if (f_opl) ptx::tma_store_3d(&em.out_pl, s_pl, n0, m0, 0);
+                        for (int pl = 0; pl < n_pl; ++pl) ptx::tma_store_3d(&em.out_pl, s_pl + (uint32_t)pl * 2048u, n0, m0, pl);
                         ptx::bulk_commit();
                         ptx::bulk_wait_read0();  // the tiles are re-used by the next chunk (single staging set)
                     }
@@ -249,7 +257,8 @@ gemm_persist_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_cons
 // M2F_GEMM_PERSIST=0 keeps these shapes on gemm_sm100.cu (A/B, debugging)
 bool gemm_persist_eligible(const GemmParams& p, int a_mn, int b_mn) {
     static const bool off = [] { const char* e = std::getenv("M2F_GEMM_PERSIST"); return e && e[0] == '0'; }();
-    return !off && !a_mn && !b_mn && p.epi_tma && !p.gate && !p.drop.enabled && !p.accumulate && !p.colsum && p.out_pl_n <= 1 &&
+    const int stg = (p.out_f32 ? 4096 : 0) + (p.out_pl ? p.out_pl_n * 2048 : 0) + (p.resid ? 4096 : 0);  // per epilogue warp
+    return !off && !a_mn && !b_mn && p.epi_tma && !p.gate && !p.drop.enabled && !p.accumulate && !p.colsum && stg <= PS_WARP_STG &&
            (p.out_f32 || p.out_pl);
 }
 

@@ -85,6 +85,7 @@ def test_gemm_wgrad_both_mn_major(ops, M, N, K, planes):
     (66000, 768, 320, 1, "resid"),      # bias + fp32 residual -> fp32 (out-projection / FFN2 at inference)
     (65792, 512, 128, 2, "both"),       # two operand planes (three plane products), fp32 and plane output together
     (65536, 300, 128, 1, "planes"),     # ragged N: the second column tile is clipped
+    (65700, 512, 192, 3, "planes3"),    # fp32-parity inference: three operand planes (six products), three output planes
 ])
 def test_gemm_persistent_many_row_tiles(ops, M, N, K, planes, variant):
     """M >= 65 536 (>= 512 row tiles): the persistent pair kernel of gemm_persist.cu -- every pair walks several tiles, two TMEM
@@ -93,7 +94,11 @@ def test_gemm_persistent_many_row_tiles(ops, M, N, K, planes, variant):
     A, B = ops.PlanesTensor.from_float(X, planes), ops.PlanesTensor.from_float(W, planes)
     bias = rnd(N, seed=33)
     ref = A.float().double() @ B.float().double().T + bias.double()
-    if variant == "planes":
+    if variant == "planes3":
+        outp = ops.PlanesTensor.empty(M, N, 3, "cuda", zero=True)
+        ops.gemm(A, B, M, N, bias=bias, relu=True, out_planes=outp)
+        assert rel(outp.float(), torch.relu(ref)) < 5e-6
+    elif variant == "planes":
         outp = ops.PlanesTensor.empty(M, N, 1, "cuda", zero=True)
         ops.gemm(A, B, M, N, bias=bias, relu=True, out_planes=outp)
         assert rel(outp.float(), torch.relu(ref)) < 4e-3
