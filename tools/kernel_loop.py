@@ -32,6 +32,15 @@ for _ in range(reps):
     ops.gemm(dH, X1, N, K, a_mn=True, b_mn=True, out_f32=dW)
 torch.cuda.synchronize()
 
+# the persistent two-accumulator GEMM at the C5 inference size (FFN1, one plane)
+Mi = 131072
+Ai = ops.PlanesTensor.from_float(torch.randn(Mi, K, generator=g, device=dev), 1)
+Yi = ops.PlanesTensor.empty(Mi, N, 1, dev)
+for _ in range(reps):
+    ops.gemm(Ai, W1, Mi, N, bias=bias, relu=True, out_planes=Yi)
+torch.cuda.synchronize()
+del Ai, Yi
+
 # LayerNorm, staged kernels (M = 131072)
 Ml, D = 131072, 768
 x = torch.randn(Ml, D, generator=g, device=dev)
