@@ -71,6 +71,27 @@ def test_c5_long_dialogues_inference(P, planes, tol):
         assert bool((out.cpu().argmax(-1)[valid] == ref.argmax(-1)[valid]).all())
 
 
+@pytest.mark.parametrize("precision,tol", [("fp32", 1e-4), ("bf16x2f", 2e-2), ("bf16", 2e-2)])
+def test_inference_batch_of_many_tiles(P, precision, tol):
+    """An inference batch large enough (52 dialogues x 256 utterances = 13 312 rows: 156 and more 256 x 256 tiles per GEMM) for the
+    whole-model forward to run on the persistent two-accumulator GEMM (gemm_persist.cu) and, for one plane, the persistent
+    tcgen05 attention with several (dialogue, head) items per CTA (416 items) -- against the fp64 oracle on the CPU, ragged lengths."""
+    cfg = O.default_model_cfg(dropout=0.4, TEXT=dict(n_encoder_layers=1), AUDIO=dict(n_encoder_layers=1), FAM=dict(n_layers=1))
+    B, S = 52, 256
+    params = O.synth_params(cfg)
+    model = P.M2FNet(cfg, precision=precision)
+    model.load_state_dict({k: v.float() for k, v in params.items()}, strict=True)
+    model = model.to("cuda").eval()
+    b = O.synth_inputs(B, S, 768, 768)
+    with torch.inference_mode():
+        out = model(b["text"].cuda(), b["audio"].cuda(), b["padding_mask"].cuda())
+        ref = O.forward(params, cfg, b["text"].double(), b["audio"].double(), b["padding_mask"])
+    valid = ~b["padding_mask"]
+    assert O.rel_l2(out.cpu()[valid], ref[valid]) < tol
+    if precision == "fp32":
+        assert bool((out.cpu().argmax(-1)[valid] == ref.argmax(-1)[valid]).all())
+
+
 def test_reference_train_loop_body_tracks_oracle(P):
     """Four iterations of the reference's step (zero_grad, forward, CE, backward, Adam; src/train.py:222-233) with the
     stock torch criterion and torch.optim.Adam on the product model, against the oracle trained by the same optimizer
