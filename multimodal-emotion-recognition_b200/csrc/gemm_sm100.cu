@@ -842,9 +842,11 @@ int gemm_block_n(int64_t M, int64_t N, int64_t K) {
     // Launches of two and more 256 x 256 tiles per pair of SMs (and everything with >= 512 row tiles) go to the persistent pair kernel
     // (gemm_persist.cu: tile loop, two TMEM accumulators) when its epilogue applies, else to the plain pair kernel;
     // M2F_GEMM_PERSIST=0 restores the previous policy.
-    static const bool persist_off = [] { const char* e = std::getenv("M2F_GEMM_PERSIST"); return e && e[0] == '0'; }();
+    static const int persist_mode = [] { const char* e = std::getenv("M2F_GEMM_PERSIST"); return e ? std::atoi(e) : 1; }();  // 2: tuning aid
+    const bool persist_off = persist_mode == 0;
     const int64_t pair_tiles = ((M + 2 * BLOCK_M - 1) / (2 * BLOCK_M)) * ((N + 255) / 256);
-    if (pairs == 1 && !forced && !persist_off && N >= 256 && (mt >= 512 || pair_tiles >= 148))  // two tiles and more per pair of SMs
+    if (pairs == 1 && !forced && !persist_off && N >= 256 &&
+        (mt >= 512 || pair_tiles >= 148 || (persist_mode == 2 && pair_tiles >= 2)))  // two tiles and more per pair of SMs
         return 256 | GEMM_TILE_CTA2 | GEMM_TILE_PERSIST;
     if (pairs == 1 && N > 64 && mt < 512) {
         const int bn = (forced == 128 || forced == 256) ? forced : 256;

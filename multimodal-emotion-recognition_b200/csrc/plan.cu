@@ -1437,16 +1437,38 @@ extern "C" int m2f_plan_create(m2f_model_t* m, int64_t B, int64_t S, int32_t tra
         p->ws_bytes += round_up(M, 256);
         p->key_pad = kb;
     }
+    // Inference plans recycle buffers (training plans keep every activation for the backward):
+    //  * the encoder layers of a stack share one set of per-layer buffers, and inside that set tensors with disjoint lifetimes
+    //    share storage (every kernel of a stack runs in stream order): h (FFN hidden) lies on qkv, x1_pl on o_pl, y2 on y1;
+    //  * layer outputs alternate between two slots; the fp32 copy of the last stack output is never written and not allocated;
+    //  * the fusion layers share one q|v, one attention-output and two alternating concat buffers, and these, the stacked K
+    //    projections and the classifier's hidden layers are laid over the audio stack's buffers: everything written after the
+    //    two stacks have joined, when no stack buffer is live any more (their last reader is the stack's projection GEMM).
+    // C5 (M = 131 072, default dims): 22 GB -> 7.4 GB in bf16 mode, 48 GB -> 16.6 GB with three planes.
+    auto overlay = [&](auto first, auto second) {  // second() is laid over first(): both start at the same offset
+        p->ws_bytes = round_up(p->ws_bytes, 256);
+        const int64_t mark = p->ws_bytes;
+        first();
+        const int64_t end_first = p->ws_bytes;
+        p->ws_bytes = mark;
+        second();
+        p->ws_bytes = std::max(p->ws_bytes, end_first);
+    };
+    int64_t stack_lo[2] = {0, 0}, stack_hi[2] = {0, 0};
     for (int i = 0; i < 2; ++i) {
         Modality& mo = p->mod[i];
         if (!mo.enabled) continue;
         const int D = mo.D;
         Dmax = std::max(Dmax, D);
+        p->ws_bytes = round_up(p->ws_bytes, 256);
+        stack_lo[i] = p->ws_bytes;
         mo.in_pl = p->alloc_pl(M, D, P);
         EncLayer shared;  // inference plans alias one set of per-layer buffers
         bool have_shared = false;
+        size_t li = 0;
+        Buf x2_slot[2], x2pl_slot[2];
         for (auto& e : mo.layers) {
-            if (training_plan || !have_shared) {
+            if (training_plan) {
                 e.qkv_pl = p->alloc_pl(M, 3 * D, P);
                 e.o_pl = p->alloc_pl(M, D, P);
                 e.y1 = p->alloc_f32(M, D);
@@ -1456,44 +1478,76 @@ extern "C" int m2f_plan_create(m2f_model_t* m, int64_t B, int64_t S, int32_t tra
                 e.h_pl = p->alloc_pl(M, FF, P);
                 e.y2 = p->alloc_f32(M, D);
                 e.st2 = p->alloc_f32(M, 2);
-                if (!training_plan) { shared = e; have_shared = true; }
+            } else if (!have_shared) {
+                overlay([&] { e.qkv_pl = p->alloc_pl(M, 3 * D, P); }, [&] { e.h_pl = p->alloc_pl(M, FF, P); });
+                overlay([&] { e.o_pl = p->alloc_pl(M, D, P); }, [&] { e.x1_pl = p->alloc_pl(M, D, P); });
+                overlay([&] { e.y1 = p->alloc_f32(M, D); }, [&] { e.y2 = p->alloc_f32(M, D); });
+                e.st1 = p->alloc_f32(M, 2);
+                e.x1 = p->alloc_f32(M, D);
+                e.st2 = p->alloc_f32(M, 2);
+                shared = e;
+                have_shared = true;
             } else {
                 e.qkv_pl = shared.qkv_pl; e.o_pl = shared.o_pl; e.y1 = shared.y1; e.st1 = shared.st1; e.x1 = shared.x1;
                 e.x1_pl = shared.x1_pl; e.h_pl = shared.h_pl; e.y2 = shared.y2; e.st2 = shared.st2;
             }
             // the layer output feeds the next layer while this layer's buffers are being reused: never aliased per layer pair
-            e.x2 = p->alloc_f32(M, D);
-            e.x2_pl = p->alloc_pl(M, D, P);
-        }
-        if (!training_plan) {  // two alternating output slots are enough for inference
-            Buf x2a = mo.layers[0].x2, x2pa = mo.layers[0].x2_pl;
-            Buf x2b = x2a, x2pb = x2pa;
-            if (mo.layers.size() > 1) { x2b = mo.layers[1].x2; x2pb = mo.layers[1].x2_pl; }
-            for (size_t j = 2; j < mo.layers.size(); ++j) {
-                mo.layers[j].x2 = (j & 1) ? x2b : x2a;
-                mo.layers[j].x2_pl = (j & 1) ? x2pb : x2pa;
+            if (training_plan || li < 2) {
+                e.x2 = p->alloc_f32(M, D);
+                e.x2_pl = p->alloc_pl(M, D, P);
+                if (li < 2) { x2_slot[li] = e.x2; x2pl_slot[li] = e.x2_pl; }
+            } else {  // two alternating output slots are enough for inference
+                e.x2 = x2_slot[li & 1];
+                e.x2_pl = x2pl_slot[li & 1];
             }
+            ++li;
         }
         mo.xout.resize(mo.T); mo.xout_pl.resize(mo.T); mo.stf.resize(mo.T);
         for (int t = 0; t < mo.T; ++t) {
-            mo.xout[t] = p->alloc_f32(M, D);
+            if (training_plan || t < mo.T - 1) mo.xout[t] = p->alloc_f32(M, D);
+            else { mo.xout[t] = Buf(); mo.xout[t].rows = M; mo.xout[t].cols = D; mo.xout[t].ld = round_up(D, 4); mo.xout[t].off = stack_lo[i]; }  // never written (forward_modality)
             mo.xout_pl[t] = p->alloc_pl(M, D, P);
             mo.stf[t] = p->alloc_f32(M, 2);
         }
+        p->ws_bytes = round_up(p->ws_bytes, 256);
+        stack_hi[i] = p->ws_bytes;
     }
     p->zc_pl = p->alloc_pl(M, m->cls_in, P);
-    if (!m->fam.empty()) {
-        const int F = (int)m->fam.size();
-        p->t0_pl = p->alloc_pl(M, Df, P);
-        p->kall_pl = p->alloc_pl(M, (int64_t)F * Df, P);
-        for (auto& fl : p->fam) {
-            fl.qv_pl = p->alloc_pl(M, 2 * Df, P);
-            fl.xo_pl = p->alloc_pl(M, Df, P);
-            fl.u_pl = p->alloc_pl(M, 2 * Df, P);
-        }
-    }
+    if (!m->fam.empty()) p->t0_pl = p->alloc_pl(M, Df, P);
     p->cls_h.resize(m->cls.size() - 1);
-    for (size_t j = 0; j + 1 < m->cls.size(); ++j) p->cls_h[j] = p->alloc_pl(M, m->cls[j].out, P);
+    auto after_join = [&] {  // buffers first written after the two stacks have joined
+        if (!m->fam.empty()) {
+            const int F = (int)m->fam.size();
+            p->kall_pl = p->alloc_pl(M, (int64_t)F * Df, P);
+            int fi = 0;
+            for (auto& fl : p->fam) {
+                if (training_plan || fi == 0) {
+                    fl.qv_pl = p->alloc_pl(M, 2 * Df, P);
+                    fl.xo_pl = p->alloc_pl(M, Df, P);
+                } else {
+                    fl.qv_pl = p->fam[0].qv_pl;
+                    fl.xo_pl = p->fam[0].xo_pl;
+                }
+                // layer f reads its concat operand u[f] and writes the text half of u[f + 1]
+                fl.u_pl = (training_plan || fi < 2) ? p->alloc_pl(M, 2 * Df, P) : p->fam[fi & 1].u_pl;
+                ++fi;
+            }
+        }
+        for (size_t j = 0; j + 1 < m->cls.size(); ++j) p->cls_h[j] = p->alloc_pl(M, m->cls[j].out, P);
+    };
+    if (!training_plan && !m->fam.empty() && p->mod[0].enabled && stack_hi[0] > stack_lo[0]) {
+        const int64_t save = p->ws_bytes;
+        p->ws_bytes = stack_lo[0];
+        after_join();
+        if (p->ws_bytes > stack_hi[1] && p->ws_bytes > stack_hi[0]) {  // larger than the stacks' region (tiny encoders): no overlay
+            p->ws_bytes = save;
+            after_join();
+        } else {
+            p->ws_bytes = save;
+        }
+    } else {
+        after_join();
+    }
     if (training_plan) {
         p->dl_pl = p->alloc_pl(M, 8 * ((m->cfg.cls_out + 7) / 8), Pb);
         // every backward scratch matrix gets ld = its own width; the two stacks run side by side, so each has its own

@@ -104,3 +104,23 @@ def test_state_dict_keys_survive_a_forward_setup(pkg):
     assert m._grad_anchor() is not None
     assert set(m.state_dict().keys()) == keys
     assert all(not k.startswith("_") for k in keys)
+
+
+def test_inference_workspace_is_recycled(pkg):
+    """Plan geometry is host arithmetic (no device needed): an inference plan shares per-layer buffers, alternates two output slots
+    and lays the fusion / classifier buffers over the finished audio stack (csrc/plan.cu, m2f_plan_create), so the C5 batch
+    (512 dialogues x 256 utterances, /root/reference/src/test.py:51-74 at BASELINE.json configs[4]) needs < 8 GB in bf16 mode --
+    and far less than the training plan of the same geometry, which keeps every activation for the backward."""
+    import ctypes as C
+    L = pkg._lib.lib()
+    sizes = {}
+    for prec in ("bf16", "fp32"):
+        m = pkg.M2FNet(O.default_model_cfg(dropout=0.4), precision=prec)
+        for B, S, training in ((512, 256, 0), (64, 33, 0), (64, 33, 1)):
+            h = C.c_void_p()
+            assert L.m2f_plan_create(m._handle, B, S, training, C.byref(h)) == 0
+            sizes[prec, B, S, training] = int(L.m2f_plan_workspace_bytes(h))
+            L.m2f_plan_destroy(h)
+    assert sizes["bf16", 512, 256, 0] < 8e9
+    assert sizes["fp32", 512, 256, 0] < 16e9
+    assert sizes["bf16", 64, 33, 0] * 6 < sizes["bf16", 64, 33, 1]
