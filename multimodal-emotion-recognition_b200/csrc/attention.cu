@@ -216,10 +216,13 @@ attn_bwd_kernel(PlanesView q, PlanesView k, PlanesView v, PlanesView d_o, const 
 namespace amma {
 int fwd_p1(AMMA_FWD_ARGS); int fwd_p2(AMMA_FWD_ARGS); int fwd_p3(AMMA_FWD_ARGS);
 int bwd_p1(AMMA_BWD_ARGS); int bwd_p2(AMMA_BWD_ARGS); int bwd_p3(AMMA_BWD_ARGS);
-// attention_mma_long.cu: forward only, no probability dropout, 64 < S <= 256 (online softmax over key tiles)
+// attention_mma_long.cu: 64 < S <= 256 on mma.sync -- forward (online softmax over key tiles; with or without probability dropout)
+// and backward (tiled, statistics recomputed on chip)
 bool long_supported(int hd, int64_t S);
 int fwd_long(int hd, int P, const View& q, const View& k, const View& v, const uint8_t* pad, int64_t BH, int S, int H, float scale,
-             const OutView& o, cudaStream_t st);
+             const Drop& drop, const OutView& o, cudaStream_t st);
+int bwd_long(int hd, int P, const View& q, const View& k, const View& v, const View& d_o, const uint8_t* pad, int64_t BH, int S, int H, float scale,
+             const Drop& drop, const OutView& dq, const OutView& dk, const OutView& dv, float* dbq, float* dbk, float* dbv, cudaStream_t st);
 // attention_tc.cu: the same on tcgen05 / TMEM / TMA for one plane and head sizes 64 / 96 / 128
 bool tc_supported(int hd, int64_t S, int planes, int64_t rows);
 int fwd_long_tc(int hd, const m2f_planes_t* q, const m2f_planes_t* k, const m2f_planes_t* v, const uint8_t* pad, int64_t B, int S, int H,
@@ -279,15 +282,15 @@ extern "C" int m2f_attn_fwd(const m2f_planes_t* q, const m2f_planes_t* k, const 
         auto fn = q->planes == 1 ? amma::fwd_p1 : (q->planes == 2 ? amma::fwd_p2 : amma::fwd_p3);
         return fn(hd, SPv, aq, ak, av, key_pad, B * H, (int)S, H, sc, dropm, ao, st);
     }
-    if (drop_p == 0.f && amma::long_supported(hd, S) && amma::aligned16(q) && amma::aligned16(k) && amma::aligned16(v) &&
-        amma::aligned16(o)) {
-        // long dialogues at inference: K/V tiles through shared memory, online softmax over 64-key tiles
+    if (amma::long_supported(hd, S) && amma::aligned16(q) && amma::aligned16(k) && amma::aligned16(v) && amma::aligned16(o)) {
+        // long dialogues: K/V tiles through shared memory, online softmax over 64-key tiles (inference: the tcgen05 kernel where it applies)
         const amma::View aq{vq.ptr, vq.ld, vq.stride}, ak{vk.ptr, vk.ld, vk.stride}, av{vv.ptr, vv.ld, vv.stride};
         const amma::OutView ao{const_cast<__nv_bfloat16*>(vo.ptr), vo.ld, vo.stride};
-        if (amma::tc_supported(hd, S, q->planes, std::min(std::min(q->rows, k->rows), v->rows)) &&
+        if (drop_p == 0.f && amma::tc_supported(hd, S, q->planes, std::min(std::min(q->rows, k->rows), v->rows)) &&
             (reinterpret_cast<uintptr_t>(o->ptr) % 32) == 0 && (o->ld % 16) == 0)  // 32-byte output stores
             return amma::fwd_long_tc(hd, q, k, v, key_pad, B, (int)S, H, ao, reinterpret_cast<cudaStream_t>(stream));
-        return amma::fwd_long(hd, q->planes, aq, ak, av, key_pad, B * H, (int)S, H, 1.f / sqrtf((float)hd), ao, reinterpret_cast<cudaStream_t>(stream));
+        return amma::fwd_long(hd, q->planes, aq, ak, av, key_pad, B * H, (int)S, H, 1.f / sqrtf((float)hd), drop_make(drop_p, seed, step, site), ao,
+                              reinterpret_cast<cudaStream_t>(stream));
     }
     const int hd_pad = hd | 1;
     const size_t smem = sizeof(float) * ((size_t)2 * S * hd_pad + ATT_WARPS * hd_pad + ATT_WARPS * S);
@@ -343,11 +346,20 @@ extern "C" int m2f_attn_bwd(const m2f_planes_t* q, const m2f_planes_t* k, const 
             return fn(hd, SPv, aq, ak, av, ado, key_pad, B * H, (int)S, H, sc, dropm, odq, odk, odv, dbq, dbk, dbv, st);
         }
     }
+    if (amma::long_supported(hd, S) && amma::aligned16(q) && amma::aligned16(k) && amma::aligned16(v) && amma::aligned16(d_o) && out_ok(dq) &&
+        out_ok(dk) && out_ok(dv)) {
+        // long dialogues: tiled backward, row statistics recomputed on chip (attention_mma_long.cu)
+        const amma::View aq{vq.ptr, vq.ld, vq.stride}, ak{vk.ptr, vk.ld, vk.stride}, av{vv.ptr, vv.ld, vv.stride}, ado{vdo.ptr, vdo.ld, vdo.stride};
+        const amma::OutView odq{const_cast<__nv_bfloat16*>(vdq.ptr), vdq.ld, vdq.stride}, odk{const_cast<__nv_bfloat16*>(vdk.ptr), vdk.ld, vdk.stride},
+            odv{const_cast<__nv_bfloat16*>(vdv.ptr), vdv.ld, vdv.stride};
+        return amma::bwd_long(hd, q->planes, aq, ak, av, ado, key_pad, B * H, (int)S, H, 1.f / sqrtf((float)hd), drop_make(drop_p, seed, step, site),
+                              odq, odk, odv, dbq, dbk, dbv, reinterpret_cast<cudaStream_t>(stream));
+    }
     const int hd_pad = hd | 1, s_pad = (int)S | 1;
     const size_t smem = sizeof(float) * ((size_t)4 * S * hd_pad + (size_t)2 * S * s_pad);
     M2F_REQUIRE(smem <= 227 * 1024, M2F_ERR_UNSUPPORTED,
-                "attn_bwd: S = %lld, head_dim = %d needs %zu bytes of shared memory (> 227 KB); training supports shorter dialogues only",
-                (long long)S, hd, smem);
+                "attn_bwd: S = %lld, head_dim = %d needs %zu bytes of shared memory (> 227 KB) in the generic kernel; head sizes 32 / 64 / 96 / 128 "
+                "train at any S <= 256", (long long)S, hd, smem);
     static size_t smem_set = 0;
     if (smem > 48 * 1024 && smem > smem_set) {
         M2F_CUDA(cudaFuncSetAttribute(attn_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));

@@ -250,8 +250,9 @@ __device__ __forceinline__ uint64_t key_valid_bits(const uint8_t* pad, int S, in
 // (bh*S + i)*S8 + j of the site (S8 = S rounded up to 8), so an 8-wide tile row is exactly one Philox call (eight 16-bit
 // lanes) and the two columns 2q, 2q+1 a thread owns are the two halves of word q.
 // Bit (nt*2 + rowsel)*2 + c  <->  accumulator element [nt][rowsel*2 + c].  Rolled: one Philox body.
+// `j8_0`: first 8-key tile of the strip (key tile offset / 8) for the kernels that walk the keys in tiles.
 template <int SP>
-__device__ __forceinline__ uint32_t drop_bits(const Drop& d, uint64_t bh, int S, int i0, int lane) {
+__device__ __forceinline__ uint32_t drop_bits(const Drop& d, uint64_t bh, int S, int i0, int lane, int j8_0 = 0) {
     const int g = lane >> 2, q = lane & 3;
     const uint64_t s8o = (uint64_t)((S + 7) >> 3);  // S8 / 8
     uint32_t bits = 0;
@@ -261,7 +262,7 @@ __device__ __forceinline__ uint32_t drop_bits(const Drop& d, uint64_t bh, int S,
     for (int m = 0; m < (SP / 8) / 2; ++m) {
         const int e_own = 4 * m + q;
         uint32_t a[4];
-        philox4(d.ph, (bh * S + (i0 + g + (e_own & 1) * 8)) * s8o + (e_own >> 1), a);
+        philox4(d.ph, (bh * S + (i0 + g + (e_own & 1) * 8)) * s8o + (uint64_t)(j8_0 + (e_own >> 1)), a);
         {   // stage 1: partner lane ^ 1 -- even lanes hand over words 1, 3 and receive the partner's words 0, 2 into them
             const bool odd = (q & 1) != 0;
             const uint32_t x = __shfl_xor_sync(0xffffffffu, odd ? a[0] : a[1], 1), y = __shfl_xor_sync(0xffffffffu, odd ? a[2] : a[3], 1);

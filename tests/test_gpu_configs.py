@@ -92,6 +92,36 @@ def test_inference_batch_of_many_tiles(P, precision, tol):
         assert bool((out.cpu().argmax(-1)[valid] == ref.argmax(-1)[valid]).all())
 
 
+@pytest.mark.parametrize("B,S", [(1, 1), (3, 1), (2, 2), (2, 16), (3, 17), (2, 32), (2, 48), (3, 49), (2, 64), (2, 65), (2, 130), (2, 256)])
+def test_sequence_length_edges(P, B, S):
+    """Dialogue lengths at the edges of every attention tile size (single-utterance dialogues, the 16 / 32 / 48 / 64-row tiles of
+    the short-dialogue kernels, the hand-over to the tiled long-dialogue kernels at 65, the library's limit of 256) with head sizes
+    64 / 96 / 128: training forward + backward and the inference forward against the fp64 oracle at the fp32-parity tolerance."""
+    cfg = O.default_model_cfg(dropout=0.0,
+                              TEXT=dict(embedding_size=128, n_head=2, n_encoder_layers=1),
+                              AUDIO=dict(embedding_size=96, n_head=1, n_encoder_layers=1),
+                              FAM=dict(embedding_size=128, n_head=1, n_layers=1),
+                              CLASSIFIER=dict(hidden_size=32, output_size=7, n_layers=2))
+    model, params = _build(P, cfg, planes=3)
+    model.train()
+    b = O.synth_inputs(B, S, 128, 96)
+    ref_logits, ref_loss, ref_grads = O.loss_and_grads(params, cfg, b["text"].double(), b["audio"].double(), b["padding_mask"], b["emotion"])
+    out = model(b["text"].cuda(), b["audio"].cuda(), b["padding_mask"].cuda())
+    loss = torch.nn.CrossEntropyLoss(ignore_index=-1, label_smoothing=0.1)(out.permute(0, 2, 1), b["emotion"].cuda())
+    loss.backward()
+    valid = ~b["padding_mask"]
+    assert O.rel_l2(out.detach().cpu()[valid], ref_logits[valid]) < 1e-4
+    assert abs(loss.item() - ref_loss.item()) / abs(ref_loss.item()) < 1e-4
+    got = {O.canonical_name(n): p.grad.detach().cpu() for n, p in model.named_parameters()}
+    num = sum(float(((got[n].double() - g) ** 2).sum()) for n, g in ref_grads.items())
+    den = sum(float((g ** 2).sum()) for g in ref_grads.values())
+    assert (num / den) ** 0.5 < 1e-4
+    model.eval()
+    with torch.inference_mode():
+        out_eval = model(b["text"].cuda(), b["audio"].cuda(), b["padding_mask"].cuda())
+    assert O.rel_l2(out_eval.cpu()[valid], ref_logits[valid]) < 1e-4
+
+
 def test_reference_train_loop_body_tracks_oracle(P):
     """Four iterations of the reference's step (zero_grad, forward, CE, backward, Adam; src/train.py:222-233) with the
     stock torch criterion and torch.optim.Adam on the product model, against the oracle trained by the same optimizer

@@ -133,6 +133,22 @@ def test_train_mode_parity_with_replayed_masks(P, name):
     assert O.rel_l2(r2["out"][v], r1["out"][v]) > 1e-2
 
 
+def test_train_mode_parity_long_dialogues(P):
+    """The same replay at 130 utterances per dialogue: the tiled long-dialogue attention kernels (forward with dropout, backward;
+    attention_mma_long.cu) index the probability-dropout elements by (row, 8-key tile) across key tiles."""
+    cfg = O.default_model_cfg(dropout=P_DROP,
+                              TEXT=dict(embedding_size=128, n_head=2, n_encoder_layers=1),
+                              AUDIO=dict(embedding_size=96, n_head=1, n_encoder_layers=1),
+                              FAM=dict(embedding_size=128, n_head=1, n_layers=1),
+                              CLASSIFIER=dict(hidden_size=32, output_size=7, n_layers=2))
+    (r,) = run_train_mode(P, cfg, 2, 130, False, steps=1, planes=3)
+    print(f"S = 130: logits {r['logits']:.2e} loss {r['loss']:.2e} grads {r['grads']:.2e} (gate allowance {r['grads_allow']:.1e}) "
+          f"worst beyond its allowance {r['worst']} worst raw {r['worst_raw']}")
+    assert len(r["sites"]) == expected_sites(cfg)
+    assert r["logits"] < 1e-4 and r["loss"] < 1e-4 and r["grads"] < 1e-4 + r["grads_allow"]
+    assert r["worst"][1] < 1e-3 + r["worst"][2], r["worst"]
+
+
 def test_masks_depend_on_step_and_site(P):
     a = P.ops.dropout_mask(P_DROP, 11, 5, 0x1001, 1 << 16, "cuda")
     b = P.ops.dropout_mask(P_DROP, 11, 6, 0x1001, 1 << 16, "cuda")

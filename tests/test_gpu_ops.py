@@ -323,6 +323,50 @@ def test_attention_forward_long_dialogues(ops, B, S, H, hd, planes):
     assert rel(o.float(), ref.reshape(B * S, E)) < (5e-3 if planes == 1 else 3e-6)
 
 
+@pytest.mark.parametrize("planes", [1, 2, 3])
+@pytest.mark.parametrize("B,S,H,hd,p", [(3, 130, 2, 64, 0.4), (2, 256, 2, 128, 0.4), (3, 200, 4, 96, 0.0), (4, 65, 3, 32, 0.4), (2, 129, 8, 96, 0.4)])
+def test_attention_long_dialogues_training(ops, B, S, H, hd, p, planes):
+    """64 < S <= 256 in training: forward with probability dropout (attn_fwd_long_kernel<.., DROP>) and the tiled backward
+    (attn_bwd_long_kernel: row statistics, dQ, then dK / dV, tile by tile) of attention_mma_long.cu against torch autograd in fp64
+    on the same operands with the library's own keep mask.  Ragged lengths, a fully masked key tile in the middle of one dialogue,
+    a leading masked tile in another, a single-utterance dialogue."""
+    E = H * hd
+    g = torch.Generator().manual_seed(60)
+    L = torch.randint(1, S + 1, (B,), generator=g)
+    L[0] = S
+    L[B - 1] = 1
+    padb = torch.arange(S)[None, :] >= L[:, None]
+    if S >= 128:
+        padb[0, 64:128] = True
+    padb[1, :64] = True
+    padb[1, S - 1] = False
+    pad = padb.to(torch.uint8).cuda().contiguous()
+    qkv = rnd(B * S, 3 * E, seed=61) * 1.5
+    packed = ops.PlanesTensor.from_float(qkv, planes)
+    q, k, v = packed.cview(0, E), packed.cview(E, E), packed.cview(2 * E, E)
+    o = ops.PlanesTensor.empty(B * S, E, planes, "cuda", zero=True)
+    ops.attn_fwd(q, k, v, pad, B, S, H, o, drop_p=p, seed=19, step=3, site=0x3100)
+    S8 = (S + 7) // 8 * 8
+    keep = ops.dropout_mask(p, 19, 3, 0x3100, B * H * S * S8, "cuda").reshape(B, H, S, S8)[..., :S].double() if p > 0 else None
+    qd, kd, vd = (t.float().double().reshape(B, S, E).requires_grad_(True) for t in (q, k, v))
+    ref = _attn_ref(qd, kd, vd, pad, H, keep, p)
+    tol = {1: 5e-3, 2: 5e-5, 3: 3e-6}[planes]
+    assert rel(o.float(), ref.reshape(B * S, E)) < tol
+    d_o = rnd(B * S, E, seed=62)
+    dop = ops.PlanesTensor.from_float(d_o, planes)
+    ref.backward(dop.float().double().reshape(B, S, E))
+    dqkv = ops.PlanesTensor.empty(B * S, 3 * E, planes, "cuda", zero=True)
+    db = torch.ones(3 * E, device="cuda")
+    ops.attn_bwd(q, k, v, dop, pad, B, S, H, dqkv.cview(0, E), dqkv.cview(E, E), dqkv.cview(2 * E, E), drop_p=p, seed=19, step=3, site=0x3100,
+                 dbq=db[:E], dbk=db[E:2 * E], dbv=db[2 * E:])
+    got = dqkv.float()
+    ref_db = torch.cat([t.grad.reshape(B * S, E).sum(0) for t in (qd, kd, vd)]) + 1.0
+    assert rel(db, ref_db) < (2e-2 if planes == 1 else 1e-4)
+    assert rel(got[:, :E], qd.grad.reshape(B * S, E)) < tol
+    assert rel(got[:, E:2 * E], kd.grad.reshape(B * S, E)) < tol
+    assert rel(got[:, 2 * E:], vd.grad.reshape(B * S, E)) < tol
+
+
 def test_attention_limits_are_errors(ops):
     q = ops.PlanesTensor.empty(300, 64, 1, "cuda", zero=True)
     pad = torch.zeros(1, 300, dtype=torch.uint8, device="cuda")
