@@ -139,10 +139,10 @@ int m2f_ln_bwd(const float* g, int64_t g_ld, const float* x, int64_t x_ld, const
  * q,k,v,o: planes views of [B*S, H*hd] (cols = H*hd; they may alias one packed buffer through
  * different base pointers and a common ld).  key_pad: uint8 [B,S], 1 = padded.
  * Dropout element of probability (b, h, query i, key j): ((b*H + h)*S + i) * S8 + j of `site`, S8 = S rounded up to 8.
- * Limits: S <= 256 (M2F_ERR_UNSUPPORTED beyond).  Head sizes 16 / 32 / 64 / 96 / 128 run on tensor cores (S <= 64: whole problem on
- * chip; 64 < S <= 256, head sizes 32 and up: tiled, forward and backward, with or without dropout; inference with one plane and
- * head sizes 64 / 96 / 128: tcgen05); any other head size runs a generic kernel whose shared-memory footprint bounds S
- * (forward 2 S hd, backward 4 S hd + 2 S^2 floats within 227 KB). */
+ * Limits (M2F_ERR_UNSUPPORTED beyond).  Head sizes 16 / 32 / 64 / 96 / 128 run on tensor cores: S <= 64 with the whole problem on
+ * chip; 64 < S <= 4096 (head sizes 32 and up) tiled, forward and backward, with or without dropout; inference with one plane, head
+ * sizes 64 / 96 / 128 and S <= 256 on tcgen05.  Any other head size runs a generic kernel: S <= 256 and a shared-memory footprint
+ * (forward 2 S hd, backward 4 S hd + 2 S^2 floats) within 227 KB. */
 int m2f_attn_fwd(const m2f_planes_t* q, const m2f_planes_t* k, const m2f_planes_t* v,
                  const uint8_t* key_pad, int64_t B, int64_t S, int32_t H,
                  float drop_p, uint64_t seed, uint64_t step, uint32_t site,

@@ -216,8 +216,9 @@ attn_bwd_kernel(PlanesView q, PlanesView k, PlanesView v, PlanesView d_o, const 
 namespace amma {
 int fwd_p1(AMMA_FWD_ARGS); int fwd_p2(AMMA_FWD_ARGS); int fwd_p3(AMMA_FWD_ARGS);
 int bwd_p1(AMMA_BWD_ARGS); int bwd_p2(AMMA_BWD_ARGS); int bwd_p3(AMMA_BWD_ARGS);
-// attention_mma_long.cu: 64 < S <= 256 on mma.sync -- forward (online softmax over key tiles; with or without probability dropout)
-// and backward (tiled, statistics recomputed on chip)
+// attention_mma_long.cu: 64 < S <= LONG_MAX_S on mma.sync -- forward (online softmax over key tiles; with or without probability
+// dropout) and backward (tiled, statistics recomputed on chip)
+constexpr int LONG_MAX_S = 4096;
 bool long_supported(int hd, int64_t S);
 int fwd_long(int hd, int P, const View& q, const View& k, const View& v, const uint8_t* pad, int64_t BH, int S, int H, float scale,
              const Drop& drop, const OutView& o, cudaStream_t st);
@@ -269,7 +270,6 @@ extern "C" int m2f_attn_fwd(const m2f_planes_t* q, const m2f_planes_t* k, const 
     M2F_TRY(att_view(v, "attn_fwd v", B * S, E, &vv));
     M2F_TRY(att_view(o, "attn_fwd o", B * S, E, &vo));
     M2F_REQUIRE(vec_ok(q) && vec_ok(k) && vec_ok(v), M2F_ERR_ALIGN, "attn_fwd: q/k/v need ld %% 4 == 0 and 8-byte aligned bases");
-    M2F_REQUIRE(S <= 32 * ATT_MAX_KPL, M2F_ERR_UNSUPPORTED, "attn_fwd: S = %lld exceeds the single-CTA limit %d", (long long)S, 32 * ATT_MAX_KPL);
     M2F_REQUIRE(q->planes == k->planes && q->planes == v->planes && q->planes == o->planes, M2F_ERR_ARG, "attn_fwd: plane counts differ");
     if (amma::supported(hd, S) && amma::aligned16(q) && amma::aligned16(k) && amma::aligned16(v) && amma::aligned16(o)) {
         // short dialogues: tensor-path kernel, whole (dialogue, head) problem on chip
@@ -292,6 +292,9 @@ extern "C" int m2f_attn_fwd(const m2f_planes_t* q, const m2f_planes_t* k, const 
         return amma::fwd_long(hd, q->planes, aq, ak, av, key_pad, B * H, (int)S, H, 1.f / sqrtf((float)hd), drop_make(drop_p, seed, step, site), ao,
                               reinterpret_cast<cudaStream_t>(stream));
     }
+    M2F_REQUIRE(S <= 32 * ATT_MAX_KPL, M2F_ERR_UNSUPPORTED,
+                "attn_fwd: S = %lld exceeds the single-CTA limit %d of the generic kernel (head sizes 32 / 64 / 96 / 128 take S <= %d)", (long long)S,
+                32 * ATT_MAX_KPL, amma::LONG_MAX_S);
     const int hd_pad = hd | 1;
     const size_t smem = sizeof(float) * ((size_t)2 * S * hd_pad + ATT_WARPS * hd_pad + ATT_WARPS * S);
     M2F_REQUIRE(smem <= 227 * 1024, M2F_ERR_UNSUPPORTED, "attn_fwd: S = %lld, head_dim = %d needs %zu bytes of shared memory (> 227 KB)",
@@ -327,7 +330,6 @@ extern "C" int m2f_attn_bwd(const m2f_planes_t* q, const m2f_planes_t* k, const 
     M2F_TRY(att_view(dv, "attn_bwd dv", B * S, E, &vdv));
     M2F_REQUIRE(vec_ok(q) && vec_ok(k) && vec_ok(v) && vec_ok(d_o), M2F_ERR_ALIGN,
                 "attn_bwd: q/k/v/d_o need ld %% 4 == 0 and 8-byte aligned bases");
-    M2F_REQUIRE(S <= 32 * ATT_MAX_KPL, M2F_ERR_UNSUPPORTED, "attn_bwd: S = %lld exceeds the single-CTA limit %d", (long long)S, 32 * ATT_MAX_KPL);
     M2F_REQUIRE(q->planes == k->planes && q->planes == v->planes && q->planes == d_o->planes && q->planes == dq->planes &&
                     q->planes == dk->planes && q->planes == dv->planes, M2F_ERR_ARG, "attn_bwd: plane counts differ");
     auto out_ok = [](const m2f_planes_t* t) { return amma::aligned16(t); };
@@ -355,11 +357,14 @@ extern "C" int m2f_attn_bwd(const m2f_planes_t* q, const m2f_planes_t* k, const 
         return amma::bwd_long(hd, q->planes, aq, ak, av, ado, key_pad, B * H, (int)S, H, 1.f / sqrtf((float)hd), drop_make(drop_p, seed, step, site),
                               odq, odk, odv, dbq, dbk, dbv, reinterpret_cast<cudaStream_t>(stream));
     }
+    M2F_REQUIRE(S <= 32 * ATT_MAX_KPL, M2F_ERR_UNSUPPORTED,
+                "attn_bwd: S = %lld exceeds the single-CTA limit %d of the generic kernel (head sizes 32 / 64 / 96 / 128 take S <= %d)", (long long)S,
+                32 * ATT_MAX_KPL, amma::LONG_MAX_S);
     const int hd_pad = hd | 1, s_pad = (int)S | 1;
     const size_t smem = sizeof(float) * ((size_t)4 * S * hd_pad + (size_t)2 * S * s_pad);
     M2F_REQUIRE(smem <= 227 * 1024, M2F_ERR_UNSUPPORTED,
                 "attn_bwd: S = %lld, head_dim = %d needs %zu bytes of shared memory (> 227 KB) in the generic kernel; head sizes 32 / 64 / 96 / 128 "
-                "train at any S <= 256", (long long)S, hd, smem);
+                "train at any S <= %d", (long long)S, hd, smem, amma::LONG_MAX_S);
     static size_t smem_set = 0;
     if (smem > 48 * 1024 && smem > smem_set) {
         M2F_CUDA(cudaFuncSetAttribute(attn_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));

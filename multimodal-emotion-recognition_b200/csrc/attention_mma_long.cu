@@ -1,4 +1,4 @@
-// Long-dialogue attention (64 < S <= 256) on mma.sync: the forward -- the inference shape of BASELINE.json's config 5 (test() body,
+// Long-dialogue attention (64 < S <= 4096) on mma.sync: the forward -- the inference shape of BASELINE.json's config 5 (test() body,
 // src/test.py:58-71; S = 256) in bf16 mode (1 plane) and fp32-parity mode (2 / 3 planes), and, with probability dropout
 // (template DROP), the training forward at these lengths -- and the backward (attn_bwd_long_kernel, below).
 // Same arithmetic as the short-dialogue fast path (torch/nn/functional.py:6607-6620: softmax(QK^T / sqrt(hd) + key
@@ -176,7 +176,7 @@ int launch_long_hd(const View& q, const View& k, const View& v, const uint8_t* p
                   : launch_long<HD, KT, 0, false>(q, k, v, pad, BH, S, H, P, scale, drop, o, st);
 }
 
-// ------------------------------------------------------------------------------------------------ backward, 64 < S <= 256
+// ------------------------------------------------------------------------------------------------ backward, 64 < S <= 4096
 // dQ, dK, dV of softmax(Q K^T c + mask) (dropout) V for dialogues that do not fit the single-tile kernel of attention_mma_impl.cuh
 // (torch autograd of torch/nn/functional.py:6607-6690 is what it has to match).  One CTA per (dialogue, head) walks T x T tiles of
 // the S x S probability matrix three times, with nothing but the tile operands on chip and no scratch memory:
@@ -405,7 +405,8 @@ int launch_bwd_long_hd(const View& q, const View& k, const View& v, const View& 
 
 }  // namespace
 
-bool long_supported(int hd, int64_t S) { return (hd == 32 || hd == 64 || hd == 96 || hd == 128) && S > 64 && S <= 256; }
+// tile loops: no structural bound on S; 4096 keeps the backward's row statistics (8 bytes per row) a small part of shared memory
+bool long_supported(int hd, int64_t S) { return (hd == 32 || hd == 64 || hd == 96 || hd == 128) && S > 64 && S <= 4096; }
 
 int fwd_long(int hd, int P, const View& q, const View& k, const View& v, const uint8_t* pad, int64_t BH, int S, int H, float scale,
              const Drop& drop, const OutView& o, cudaStream_t st) {

@@ -295,7 +295,8 @@ def test_attention_forward_backward(ops, B, S, H, hd, p, planes):
                                       # more (dialogue, head) items than SMs: the persistent tcgen05 kernel (attention_tc.cu, one plane)
                                       # walks several items per CTA -- prefetch, barrier phases, TMEM hand-over between items; one
                                       # and two query tiles, both query-slot layouts (hd <= 96 / hd = 128)
-                                      (56, 256, 8, 96), (90, 130, 4, 128), (170, 100, 4, 64), (75, 131, 8, 96)])
+                                      (56, 256, 8, 96), (90, 130, 4, 128), (170, 100, 4, 64), (75, 131, 8, 96),
+                                      (2, 300, 2, 64), (2, 513, 1, 128)])  # beyond the tcgen05 kernel's single key tile: mma.sync tiles
 def test_attention_forward_long_dialogues(ops, B, S, H, hd, planes):
     """64 < S <= 256, no dropout (inference at BASELINE.json config 5): the tcgen05 kernel of attention_tc.cu for one plane and
     head sizes 64 / 96 / 128, the online-softmax mma.sync kernel of attention_mma_long.cu otherwise.  Lengths are ragged; one
@@ -324,7 +325,8 @@ def test_attention_forward_long_dialogues(ops, B, S, H, hd, planes):
 
 
 @pytest.mark.parametrize("planes", [1, 2, 3])
-@pytest.mark.parametrize("B,S,H,hd,p", [(3, 130, 2, 64, 0.4), (2, 256, 2, 128, 0.4), (3, 200, 4, 96, 0.0), (4, 65, 3, 32, 0.4), (2, 129, 8, 96, 0.4)])
+@pytest.mark.parametrize("B,S,H,hd,p", [(3, 130, 2, 64, 0.4), (2, 256, 2, 128, 0.4), (3, 200, 4, 96, 0.0), (4, 65, 3, 32, 0.4), (2, 129, 8, 96, 0.4),
+                                        (2, 300, 2, 64, 0.4), (2, 520, 1, 96, 0.4)])  # beyond 256: no structural limit in the tiled kernels
 def test_attention_long_dialogues_training(ops, B, S, H, hd, p, planes):
     """64 < S <= 256 in training: forward with probability dropout (attn_fwd_long_kernel<.., DROP>) and the tiled backward
     (attn_bwd_long_kernel: row statistics, dQ, then dK / dV, tile by tile) of attention_mma_long.cu against torch autograd in fp64
@@ -350,7 +352,7 @@ def test_attention_long_dialogues_training(ops, B, S, H, hd, p, planes):
     keep = ops.dropout_mask(p, 19, 3, 0x3100, B * H * S * S8, "cuda").reshape(B, H, S, S8)[..., :S].double() if p > 0 else None
     qd, kd, vd = (t.float().double().reshape(B, S, E).requires_grad_(True) for t in (q, k, v))
     ref = _attn_ref(qd, kd, vd, pad, H, keep, p)
-    tol = {1: 5e-3, 2: 5e-5, 3: 3e-6}[planes]
+    tol = {1: 5e-3, 2: 5e-5, 3: 3e-6 if S <= 256 else 6e-6}[planes]  # fp32 sums over S terms: 3.7e-6 measured at S = 520
     assert rel(o.float(), ref.reshape(B * S, E)) < tol
     d_o = rnd(B * S, E, seed=62)
     dop = ops.PlanesTensor.from_float(d_o, planes)
@@ -368,10 +370,16 @@ def test_attention_long_dialogues_training(ops, B, S, H, hd, p, planes):
 
 
 def test_attention_limits_are_errors(ops):
-    q = ops.PlanesTensor.empty(300, 64, 1, "cuda", zero=True)
+    q = ops.PlanesTensor.empty(300, 60, 1, "cuda", zero=True)  # head size 30: the generic kernel, whose limit is S = 256
     pad = torch.zeros(1, 300, dtype=torch.uint8, device="cuda")
     with pytest.raises(RuntimeError, match="exceeds the single-CTA limit"):
         ops.attn_fwd(q, q, q, pad, 1, 300, 2, q)
+    with pytest.raises(RuntimeError, match="exceeds the single-CTA limit"):
+        ops.attn_bwd(q, q, q, q, pad, 1, 300, 2, q, q, q)
+    big = ops.PlanesTensor.empty(4100, 64, 1, "cuda", zero=True)  # head size 32: tiled kernels up to S = 4096
+    pad = torch.zeros(1, 4100, dtype=torch.uint8, device="cuda")
+    with pytest.raises(RuntimeError, match="exceeds the single-CTA limit"):
+        ops.attn_fwd(big, big, big, pad, 1, 4100, 2, big)
 
 
 @pytest.mark.parametrize("weighted", [False, True])
