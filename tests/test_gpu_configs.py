@@ -92,10 +92,11 @@ def test_inference_batch_of_many_tiles(P, precision, tol):
         assert bool((out.cpu().argmax(-1)[valid] == ref.argmax(-1)[valid]).all())
 
 
-@pytest.mark.parametrize("B,S", [(1, 1), (3, 1), (2, 2), (2, 16), (3, 17), (2, 32), (2, 48), (3, 49), (2, 64), (2, 65), (2, 130), (2, 256)])
+@pytest.mark.parametrize("B,S", [(1, 1), (3, 1), (2, 2), (2, 16), (3, 17), (2, 32), (2, 48), (3, 49), (2, 64), (2, 65), (2, 130), (2, 256), (1, 300)])
 def test_sequence_length_edges(P, B, S):
     """Dialogue lengths at the edges of every attention tile size (single-utterance dialogues, the 16 / 32 / 48 / 64-row tiles of
-    the short-dialogue kernels, the hand-over to the tiled long-dialogue kernels at 65, the library's limit of 256) with head sizes
+    the short-dialogue kernels, the hand-over to the tiled long-dialogue kernels at 65, the tcgen05 inference kernel's limit of 256
+    and beyond) with head sizes
     64 / 96 / 128: training forward + backward and the inference forward against the fp64 oracle at the fp32-parity tolerance."""
     cfg = O.default_model_cfg(dropout=0.0,
                               TEXT=dict(embedding_size=128, n_head=2, n_encoder_layers=1),
