@@ -62,11 +62,15 @@ struct GemmCfg {
     static constexpr int STAGES = ((CTA2 ? PAIR_RING_KB : 96) * 1024) / STAGE_BYTES;
     static constexpr int BAR_BYTES = (2 * STAGES + 1) * 8 + 16 + 8 * 8;  // ring, accumulator-ready, TMEM slot, 8 epilogue-load barriers
     static constexpr int BIAS_BYTES = BLOCK_N * 4;  // the tile's bias values, staged while the main loop runs (so not in the ring)
-    static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + BAR_BYTES + BIAS_BYTES + 16 + 1024;  // + alignment slack
-    static constexpr int TMEM_COLS = BLOCK_N < 32 ? 32 : BLOCK_N;
+    // the ring doubles as the epilogue's staging area: 6 stages of a 192-wide pair tile (168 KB) are less than the 8 x 23 KB the
+    // TMA epilogue stages, so the region is sized by the larger of the two
+    static constexpr int STG_BYTES = EPI_WARPS * (EPI2_WARP_BYTES > EPI_STG_FLOATS * 4 ? EPI2_WARP_BYTES : EPI_STG_FLOATS * 4);
+    static constexpr int RING_BYTES = STAGES * STAGE_BYTES > STG_BYTES ? STAGES * STAGE_BYTES : STG_BYTES;
+    static constexpr int SMEM_BYTES = RING_BYTES + BAR_BYTES + BIAS_BYTES + 16 + 1024;  // + alignment slack
+    static constexpr int TMEM_COLS = BLOCK_N < 32 ? 32 : (BLOCK_N == 192 ? 256 : BLOCK_N);  // allocations are powers of two
+    static_assert(BLOCK_N != 192 || CTA2, "192-wide tiles exist for CTA pairs only (K-major B: 96 rows per CTA)");
     static_assert(STAGES >= 2, "pipeline too shallow");
-    static_assert(EPI_WARPS * EPI_STG_FLOATS * 4 <= STAGES * STAGE_BYTES, "epilogue staging must fit in the operand ring");
-    static_assert(EPI_WARPS * EPI2_WARP_BYTES <= STAGES * STAGE_BYTES, "TMA epilogue staging must fit in the operand ring");
+    static_assert(STG_BYTES <= RING_BYTES && SMEM_BYTES <= 227 * 1024, "ring / epilogue staging must fit in shared memory");
 };
 
 __device__ __forceinline__ uint2 pack_bf16x4(const float v[4]) {
@@ -436,7 +440,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ C
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
     uint8_t* smem_a = smem;
     uint8_t* smem_b = smem + STAGES * Cfg::A_BYTES;
-    uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + STAGES * Cfg::STAGE_BYTES);
+    uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + Cfg::RING_BYTES);
     uint64_t* empty_bar = full_bar + STAGES;
     uint64_t* tmem_full_bar = empty_bar + STAGES;
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full_bar + 1);
@@ -825,12 +829,14 @@ static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const EpiMa
 }
 
 // Tile code: BLOCK_N, plus GEMM_TILE_CTA2 when the tile is computed by a CTA pair (256 x BLOCK_N per pair).
+static int g_force_bn = -1;
 int gemm_b_box_rows(int tile) { return (tile & GEMM_TILE_CTA2) ? (tile & 0xfff) / 2 : (tile & 0xfff); }
 
 int gemm_block_n(int64_t M, int64_t N, int64_t K) {
     // one 128 x BLOCK_N tile per CTA: prefer the widest tile that still yields >= 148 CTAs
     const int64_t mt = (M + BLOCK_M - 1) / BLOCK_M;
-    static const int forced = [] { const char* e = std::getenv("M2F_GEMM_BN"); return e ? std::atoi(e) : 0; }();  // tuning aid
+    static const int forced_env = [] { const char* e = std::getenv("M2F_GEMM_BN"); return e ? std::atoi(e) : 0; }();  // tuning aid
+    const int forced = g_force_bn >= 0 ? g_force_bn : forced_env;  // m2f_debug_force_gemm_bn: the tests' way to reach every tile shape
     // M2F_GEMM_CTA2: 0 never, 1 always (default), 2 by shape.  Timed alone, a short-K GEMM is as fast with two small CTAs per SM
     // as with CTA pairs (rule 2 below was tuned that way); inside the step four to six GEMMs share the GPU, latency hiding comes
     // from the neighbours, and what counts is the L2 -> SM operand traffic per flop, which pairs halve for B: the whole train
@@ -849,6 +855,7 @@ int gemm_block_n(int64_t M, int64_t N, int64_t K) {
         (mt >= 512 || pair_tiles >= 148 || (persist_mode == 2 && pair_tiles >= 2)))  // two tiles and more per pair of SMs
         return 256 | GEMM_TILE_CTA2 | GEMM_TILE_PERSIST;
     if (pairs == 1 && N > 64 && mt < 512) {
+        if (forced == 192 && N > 128) return 192 | GEMM_TILE_CTA2;  // K-major operands only: m2f_gemm falls back to 256 otherwise
         const int bn = (forced == 128 || forced == 256) ? forced : 256;
         return ((N <= 128) ? 128 : bn) | GEMM_TILE_CTA2;
     }
@@ -955,6 +962,8 @@ int gemm_launch(const CUtensorMap& ta, const CUtensorMap& tb, const EpiMaps& em,
     M2F_GEMM_CASE(128, true)
     M2F_GEMM_CASE(256, true)
 #undef M2F_GEMM_CASE
+    // 256 x 192 pair tiles, K-major operands only (an MN-major B tile is made of 64-column swizzle atoms: 96 columns per CTA are 1.5)
+    if (block_n == 192 && cta2 && !a_mn && !b_mn) return launch_gemm<192, false, false, true>(ta, tb, em, p, stream);
     set_error("gemm: unsupported tile code %d", tile);
     return M2F_ERR_UNSUPPORTED;
 }
@@ -963,6 +972,7 @@ int gemm_launch(const CUtensorMap& ta, const CUtensorMap& tb, const EpiMaps& em,
 
 // profiling aid (not part of the public header): 8 x uint64 globaltimer stamps per CTA are written to `buf`
 extern "C" void m2f_debug_set_gemm_flags(int f) { m2f::g_dbg = f; }
+extern "C" void m2f_debug_force_gemm_bn(int bn) { m2f::g_force_bn = bn; }  // -1: back to the policy
 extern "C" void m2f_debug_set_gemm_trace(void* buf) { m2f::g_trace = reinterpret_cast<unsigned long long*>(buf); }
 
 extern "C" int m2f_gemm(const m2f_planes_t* A, int a_mn_major, const m2f_planes_t* B, int b_mn_major,
@@ -973,7 +983,8 @@ extern "C" int m2f_gemm(const m2f_planes_t* A, int a_mn_major, const m2f_planes_
     M2F_TRY(gemm_fill_params(p, A, a_mn_major, B, b_mn_major, segs, nsegs, M, N, epi));
     int64_t ktot = 0;
     for (int i = 0; i < nsegs; ++i) ktot += segs[i].klen;
-    const int bn = gemm_block_n(M, N, ktot);
+    int bn = gemm_block_n(M, N, ktot);
+    if ((bn & 0xfff) == 192 && (a_mn_major || b_mn_major)) bn = 256 | GEMM_TILE_CTA2;
     CUtensorMap ta, tb;
     EpiMaps em;
     memset(&em, 0, sizeof(em));

@@ -876,6 +876,15 @@ struct Ctx {
         if (narrow && (bn & GEMM_TILE_CTA2) && (bn & 0xfff) == 256 && N > 128 &&
             ((M + 2 * BLOCK_M - 1) / (2 * BLOCK_M)) * 2 * ((N + 255) / 256) <= 74)
             bn = 128 | GEMM_TILE_CTA2;
+        // Forward GEMMs (both operands K-major) whose N is a multiple of 192 (768: out-proj, FFN2, projections; 2304: packed QKV):
+        // 256 x 192 pair tiles give 4 / 12 column tiles instead of 3 / 9 -- at M = 2112 the two stacks' 768-wide GEMMs together
+        // are 144 CTAs (one wave of the 148 SMs, each with 3/4 of the main loop) instead of 108, and the QKV pair 432 CTAs of 3/4
+        // (three waves, the last one full) instead of 324 (three waves, the last one a fifth full).  M2F_GEMM_BN192: 0 off,
+        // 1 (default) inside the modality stacks, 2 also instead of the half-width tiles of the serial sections.
+        static const int bn192 = [] { const char* e = std::getenv("M2F_GEMM_BN192"); return e ? std::atoi(e) : 1; }();
+        if (bn192 && !a_mn && !b_mn && (bn & GEMM_TILE_CTA2) && !(bn & GEMM_TILE_PERSIST) && N % 192 == 0 && N >= 384 &&
+            (((bn & 0xfff) == 256 && !narrow) || (bn192 >= 2 && narrow)))
+            bn = 192 | GEMM_TILE_CTA2;
         EpiKey ek;
         std::memset(&ek, 0, sizeof(ek));  // padding bytes take part in the comparison
         ek.out_f32 = gp.out_f32; ek.out_pl = gp.out_pl; ek.gate = gp.gate; ek.resid = gp.resid;
@@ -915,11 +924,34 @@ struct Epi {
 
 static inline float inv_keep(float p) { return 1.f / (1.f - p); }
 
+// Timing aid (results become garbage): M2F_DEBUG_SKIP=<prefix>[,<prefix>...] leaves out every op of the step whose call text starts
+// with one of the prefixes (e.g. "m2f_ln_fwd,m2f_attn_bwd") -- the step time without them bounds what a faster kernel could win.
+static bool debug_skip(const char* expr) {
+    static const std::vector<std::string> pats = [] {
+        std::vector<std::string> v;
+        const char* e = std::getenv("M2F_DEBUG_SKIP");
+        std::string cur;
+        for (const char* q = e ? e : ""; ; ++q) {
+            if (*q == ',' || *q == 0) {
+                if (!cur.empty()) v.push_back(cur);
+                cur.clear();
+                if (*q == 0) break;
+            } else {
+                cur.push_back(*q);
+            }
+        }
+        return v;
+    }();
+    for (const std::string& pat : pats)
+        if (std::strncmp(expr, pat.c_str(), pat.size()) == 0) return true;
+    return false;
+}
+
 // an op of the step: M2F_TRY + (debug) a timeline stamp behind it on the same stream
-#define OP(expr)          \
-    do {                  \
-        M2F_TRY(expr);    \
-        c.stamp(#expr);   \
+#define OP(expr)                               \
+    do {                                       \
+        if (!debug_skip(#expr)) M2F_TRY(expr); \
+        c.stamp(#expr);                        \
     } while (0)
 
 // ------------------------------------------------------------------------------------------ forward

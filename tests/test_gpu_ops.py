@@ -114,6 +114,51 @@ def test_gemm_persistent_many_row_tiles(ops, M, N, K, planes, variant):
         assert rel(out, ref) < 1e-5 and rel(outp.float(), ref) < 4e-3
 
 
+@pytest.mark.parametrize("M,N,K,planes,variant", [
+    (2112, 768, 768, 2, "drop_resid"),   # out-projection forward of the benched mode: bias + dropout + residual -> fp32
+    (2112, 2304, 768, 2, "planes"),      # packed QKV: twelve column tiles, two operand and two output planes
+    (2112, 768, 2048, 1, "relu_drop"),   # bias + ReLU + dropout -> plane (the FFN1 epilogue on an N = 768 shape)
+    (300, 500, 200, 3, "planes"),        # ragged: last column tile clipped (500 = 2 x 192 + 116), K tail, three planes
+    (2112, 1536, 768, 1, "two_segs"),    # two K segments (concat operand), fp32 out
+])
+def test_gemm_192_wide_pair_tiles(ops, M, N, K, planes, variant):
+    """256 x 192 CTA-pair tiles (the plan's choice for forward GEMMs whose N is a multiple of 192; forced here through the debug hook):
+    six 32-column epilogue chunks per tile, 96 B rows per CTA, ring sized by the epilogue staging."""
+    import ctypes as C
+    L = ops._lib.lib()
+    L.m2f_debug_force_gemm_bn.argtypes = [C.c_int]
+    L.m2f_debug_force_gemm_bn.restype = None
+    X, W = rnd(M, K, seed=35), rnd(N, K, seed=36, scale=K ** -0.5)
+    A, B = ops.PlanesTensor.from_float(X, planes), ops.PlanesTensor.from_float(W, planes)
+    bias = rnd(N, seed=37)
+    ref = A.float().double() @ B.float().double().T + bias.double()
+    tol_pl = {1: 4e-3, 2: 3e-5, 3: 5e-6}[planes]
+    L.m2f_debug_force_gemm_bn(192)
+    try:
+        if variant == "planes":
+            outp = ops.PlanesTensor.empty(M, N, planes, "cuda", zero=True)
+            ops.gemm(A, B, M, N, bias=bias, out_planes=outp)
+            assert rel(outp.float(), ref) < tol_pl
+        elif variant == "drop_resid":
+            resid = rnd(M, N, seed=38)
+            out = torch.full((M, N), float("nan"), device="cuda")
+            ops.gemm(A, B, M, N, bias=bias, resid=resid, out_f32=out, drop_p=0.4, seed=3, step=4, site=0x55)
+            keep = ops.dropout_mask(0.4, 3, 4, 0x55, M * N, "cuda").reshape(M, N).double()
+            assert rel(out, ref * keep / 0.6 + resid.double()) < 1e-5
+        elif variant == "relu_drop":
+            outp = ops.PlanesTensor.empty(M, N, 1, "cuda", zero=True)
+            ops.gemm(A, B, M, N, bias=bias, relu=True, out_planes=outp, drop_p=0.4, seed=3, step=4, site=0x56)
+            keep = ops.dropout_mask(0.4, 3, 4, 0x56, M * N, "cuda").reshape(M, N).double()
+            assert rel(outp.float(), torch.relu(ref) * keep / 0.6) < tol_pl
+        else:
+            out = torch.full((M, N), float("nan"), device="cuda")
+            h = K // 128 * 64
+            ops.gemm(A, B, M, N, bias=bias, segs=[(0, 0, h), (h, h, K - h)], out_f32=out)
+            assert rel(out, ref) < 1e-5
+    finally:
+        L.m2f_debug_force_gemm_bn(-1)
+
+
 def test_gemm_a_mn_b_k_major(ops):
     M, N, K = 300, 200, 192
     At, W = rnd(K, M, seed=7), rnd(N, K, seed=8)
