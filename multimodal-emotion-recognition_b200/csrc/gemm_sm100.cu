@@ -493,6 +493,11 @@ gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ C
                     const uint32_t fb = ptx::mapa(ptx::smem_u32(&full_bar[stage]), 0);
                     if (!B_MN) {
                         ptx::tma_load_3d_2cta(sb, &tma_b, fb, kbb, nb0, pb);
+                    } else if constexpr (BLOCK_N == 192) {
+                        // 96 MN-major columns per CTA: three 32-column atoms of the 64-byte swizzle (make_planes_tmap_sw64)
+#pragma unroll
+                        for (int j = 0; j < 3; ++j)
+                            ptx::tma_load_3d_2cta(sb + j * (32 * BLOCK_K * 2), &tma_b, fb, nb0 + j * 32, kbb, pb);
                     } else {
 #pragma unroll
                         for (int j = 0; j < Cfg::B_ROWS / 64; ++j)
@@ -579,8 +584,11 @@ gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ C
             //   advancing K by 16 elements = +32 B inside the swizzle atom.
             // MN-major SW128: 64-element MN atoms BLOCK_K*128 B apart (LBO), 8-k-row groups 1024 B apart (SBO);
             //   advancing K by 16 rows = +2048 B.
-            constexpr uint32_t A_LBO = A_MN ? BLOCK_K * 128 : 0, B_LBO = B_MN ? BLOCK_K * 128 : 0;
-            constexpr uint32_t A_KSTEP = A_MN ? UMMA_K * 128 : UMMA_K * 2, B_KSTEP = B_MN ? UMMA_K * 128 : UMMA_K * 2;
+            // MN-major SW64 (B of the 192-wide pair tiles: 96 columns per CTA): 32-element atoms BLOCK_K*64 B apart (LBO), 8-k-row
+            //   groups 512 B apart (SBO); advancing K by 16 rows = +1024 B.
+            constexpr bool B_SW64 = B_MN && BLOCK_N == 192;
+            constexpr uint32_t A_LBO = A_MN ? BLOCK_K * 128 : 0, B_LBO = B_SW64 ? BLOCK_K * 64 : (B_MN ? BLOCK_K * 128 : 0);
+            constexpr uint32_t A_KSTEP = A_MN ? UMMA_K * 128 : UMMA_K * 2, B_KSTEP = B_SW64 ? UMMA_K * 64 : (B_MN ? UMMA_K * 128 : UMMA_K * 2);
             for (int it = 0; it < p.total_kb; ++it) {
                 const int stage = it % STAGES;
                 const uint32_t phase = (it / STAGES) & 1;
@@ -592,7 +600,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ C
 #pragma unroll
                 for (int k = 0; k < BLOCK_K / UMMA_K; ++k) {
                     const uint64_t ad = ptx::smem_desc_sw128(sa + k * A_KSTEP, A_LBO, 1024);
-                    const uint64_t bd = ptx::smem_desc_sw128(sb + k * B_KSTEP, B_LBO, 1024);
+                    const uint64_t bd = B_SW64 ? ptx::smem_desc_sw64(sb + k * B_KSTEP, B_LBO, 512) : ptx::smem_desc_sw128(sb + k * B_KSTEP, B_LBO, 1024);
                     if constexpr (CTA2) ptx::umma_bf16_2cta(tmem_base, ad, bd, idesc, (it > 0 || k > 0) ? 1u : 0u);
                     else ptx::umma_bf16(tmem_base, ad, bd, idesc, (it > 0 || k > 0) ? 1u : 0u);
                 }
@@ -962,8 +970,11 @@ int gemm_launch(const CUtensorMap& ta, const CUtensorMap& tb, const EpiMaps& em,
     M2F_GEMM_CASE(128, true)
     M2F_GEMM_CASE(256, true)
 #undef M2F_GEMM_CASE
-    // 256 x 192 pair tiles, K-major operands only (an MN-major B tile is made of 64-column swizzle atoms: 96 columns per CTA are 1.5)
+    // 256 x 192 pair tiles: K-major A; B K-major, or MN-major through 32-column atoms of the 64-byte swizzle (the caller builds
+    // that tensor map with make_planes_tmap_sw64: 96 columns per CTA are 1.5 atoms of the 128-byte swizzle); MN-major A with both
     if (block_n == 192 && cta2 && !a_mn && !b_mn) return launch_gemm<192, false, false, true>(ta, tb, em, p, stream);
+    if (block_n == 192 && cta2 && !a_mn && b_mn) return launch_gemm<192, false, true, true>(ta, tb, em, p, stream);
+    if (block_n == 192 && cta2 && a_mn && b_mn) return launch_gemm<192, true, true, true>(ta, tb, em, p, stream);
     set_error("gemm: unsupported tile code %d", tile);
     return M2F_ERR_UNSUPPORTED;
 }
@@ -984,12 +995,13 @@ extern "C" int m2f_gemm(const m2f_planes_t* A, int a_mn_major, const m2f_planes_
     int64_t ktot = 0;
     for (int i = 0; i < nsegs; ++i) ktot += segs[i].klen;
     int bn = gemm_block_n(M, N, ktot);
-    if ((bn & 0xfff) == 192 && (a_mn_major || b_mn_major)) bn = 256 | GEMM_TILE_CTA2;
+    if ((bn & 0xfff) == 192 && a_mn_major && !b_mn_major) bn = 256 | GEMM_TILE_CTA2;
     CUtensorMap ta, tb;
     EpiMaps em;
     memset(&em, 0, sizeof(em));
     M2F_TRY(gemm_make_epi_maps(p, &em));
     M2F_TRY(make_planes_tmap(&ta, A, a_mn_major ? BLOCK_K : BLOCK_M));
-    M2F_TRY(make_planes_tmap(&tb, B, b_mn_major ? BLOCK_K : gemm_b_box_rows(bn)));
+    if (b_mn_major && (bn & 0xfff) == 192) M2F_TRY(make_planes_tmap_sw64(&tb, B, BLOCK_K));
+    else M2F_TRY(make_planes_tmap(&tb, B, b_mn_major ? BLOCK_K : gemm_b_box_rows(bn)));
     return gemm_launch(ta, tb, em, p, bn, a_mn_major, b_mn_major, reinterpret_cast<cudaStream_t>(stream));
 }

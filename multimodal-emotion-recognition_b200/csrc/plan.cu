@@ -840,12 +840,13 @@ struct Ctx {
     const float* prm(int64_t off) const { return params + off; }
     float* grd(int64_t off) const { return grads + off; }
 
-    int tmap(const m2f_planes_t& t, int box_rows, const CUtensorMap** out) {
-        TmapKey k{t.ptr, t.rows, t.cols, t.ld, t.plane_stride, t.planes, box_rows};
+    int tmap(const m2f_planes_t& t, int box_rows, const CUtensorMap** out, bool sw64 = false) {
+        TmapKey k{t.ptr, t.rows, t.cols, t.ld, t.plane_stride, t.planes, box_rows | (sw64 ? 0x10000 : 0)};
         auto it = p->tmaps.find(k);
         if (it == p->tmaps.end()) {
             CUtensorMap m;
-            M2F_TRY(make_planes_tmap(&m, &t, box_rows));
+            if (sw64) M2F_TRY(make_planes_tmap_sw64(&m, &t, box_rows));
+            else M2F_TRY(make_planes_tmap(&m, &t, box_rows));
             it = p->tmaps.emplace(k, m).first;
         }
         *out = &it->second;
@@ -881,9 +882,16 @@ struct Ctx {
         // are 144 CTAs (one wave of the 148 SMs, each with 3/4 of the main loop) instead of 108, and the QKV pair 432 CTAs of 3/4
         // (three waves, the last one full) instead of 324 (three waves, the last one a fifth full).  M2F_GEMM_BN192: 0 off,
         // 1 (default) inside the modality stacks, 2 also instead of the half-width tiles of the serial sections.
+        // The same tiles exist for the backward (M2F_GEMM_BN192_BWD: bit 1 data gradients -- B = W read MN-major, 96 columns per CTA
+        // through the 64-byte swizzle --, bit 2 weight gradients) and are OFF by default: measured 3.357 (off) / 3.366 (dgrad) /
+        // 3.418 ms (wgrad) per step -- the single-product backward GEMMs are bound by their fixed costs, not their main loops, and
+        // more weight-gradient CTAs take SMs from the data-gradient chain (profiles/r2_ab_tiles.txt).
         static const int bn192 = [] { const char* e = std::getenv("M2F_GEMM_BN192"); return e ? std::atoi(e) : 1; }();
-        if (bn192 && !a_mn && !b_mn && (bn & GEMM_TILE_CTA2) && !(bn & GEMM_TILE_PERSIST) && N % 192 == 0 && N >= 384 &&
-            (((bn & 0xfff) == 256 && !narrow) || (bn192 >= 2 && narrow)))
+        static const int bn192b = [] { const char* e = std::getenv("M2F_GEMM_BN192_BWD"); return e ? std::atoi(e) : 0; }();
+        const bool fwd_like = !a_mn && !b_mn, dgrad_like = !a_mn && b_mn, wgrad_like = a_mn && b_mn;
+        if ((bn & GEMM_TILE_CTA2) && !(bn & GEMM_TILE_PERSIST) && N % 192 == 0 && N >= 384 &&
+            ((bn192 && fwd_like && (((bn & 0xfff) == 256 && !narrow) || (bn192 == 2 && narrow)) && !(bn192 == 3 && N > 768) && !(bn192 == 4 && N <= 768)) ||
+             (bn192b && (bn & 0xfff) == 256 && ((dgrad_like && (bn192b & 1)) || (wgrad_like && (bn192b & 2))))))
             bn = 192 | GEMM_TILE_CTA2;
         EpiKey ek;
         std::memset(&ek, 0, sizeof(ek));  // padding bytes take part in the comparison
@@ -901,7 +909,7 @@ struct Ctx {
         gp.epi_tma = eit->second.epi_tma;
         const CUtensorMap *ta, *tb;
         M2F_TRY(tmap(A, a_mn ? BLOCK_K : BLOCK_M, &ta));
-        M2F_TRY(tmap(B, b_mn ? BLOCK_K : gemm_b_box_rows(bn), &tb));
+        M2F_TRY(tmap(B, b_mn ? BLOCK_K : gemm_b_box_rows(bn), &tb, b_mn && (bn & 0xfff) == 192));
         return gemm_launch(*ta, *tb, eit->second.maps, gp, bn, a_mn, b_mn, stream());
     }
 };

@@ -120,6 +120,10 @@ def test_gemm_persistent_many_row_tiles(ops, M, N, K, planes, variant):
     (2112, 768, 2048, 1, "relu_drop"),   # bias + ReLU + dropout -> plane (the FFN1 epilogue on an N = 768 shape)
     (300, 500, 200, 3, "planes"),        # ragged: last column tile clipped (500 = 2 x 192 + 116), K tail, three planes
     (2112, 1536, 768, 1, "two_segs"),    # two K segments (concat operand), fp32 out
+    (2112, 768, 2304, 1, "dgrad"),       # dX = dY W with W read MN-major: 96 columns per CTA as three atoms of the 64-byte swizzle
+    (300, 500, 200, 3, "dgrad"),         # ... ragged, three planes
+    (768, 768, 2112, 1, "wgrad"),        # dW = dY^T X, both operands MN-major
+    (520, 400, 300, 2, "wgrad"),         # ... ragged, two planes
 ])
 def test_gemm_192_wide_pair_tiles(ops, M, N, K, planes, variant):
     """256 x 192 CTA-pair tiles (the plan's choice for forward GEMMs whose N is a multiple of 192; forced here through the debug hook):
@@ -135,7 +139,19 @@ def test_gemm_192_wide_pair_tiles(ops, M, N, K, planes, variant):
     tol_pl = {1: 4e-3, 2: 3e-5, 3: 5e-6}[planes]
     L.m2f_debug_force_gemm_bn(192)
     try:
-        if variant == "planes":
+        if variant == "dgrad":  # out[M, N] = dY[M, K] . Wt[K, N]
+            Wt = ops.PlanesTensor.from_float(rnd(K, N, seed=39, scale=K ** -0.5), planes, ld=(N + 7) // 8 * 8)
+            resid = rnd(M, N, seed=38)
+            out = torch.full((M, N), float("nan"), device="cuda")
+            ops.gemm(A, Wt, M, N, b_mn=True, resid=resid, out_f32=out)
+            assert rel(out, A.float().double() @ Wt.float().double() + resid.double()) < 1e-5
+        elif variant == "wgrad":  # out[M, N] = dY[K, M]^T . X[K, N]
+            dY = ops.PlanesTensor.from_float(rnd(K, M, seed=40), planes, ld=(M + 7) // 8 * 8)
+            Xk = ops.PlanesTensor.from_float(rnd(K, N, seed=41), planes, ld=(N + 7) // 8 * 8)
+            out = torch.full((M, N), float("nan"), device="cuda")
+            ops.gemm(dY, Xk, M, N, a_mn=True, b_mn=True, out_f32=out)
+            assert rel(out, dY.float().double().T @ Xk.float().double()) < 1e-5
+        elif variant == "planes":
             outp = ops.PlanesTensor.empty(M, N, planes, "cuda", zero=True)
             ops.gemm(A, B, M, N, bias=bias, out_planes=outp)
             assert rel(outp.float(), ref) < tol_pl
