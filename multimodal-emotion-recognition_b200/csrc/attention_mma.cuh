@@ -151,6 +151,55 @@ __device__ __forceinline__ void strip_nt(float (&acc)[SP / 8][4], const __nv_bfl
     }
 }
 
+// A fragments (mma.sync m16n8k16, row-major A) of a 16-row strip read straight from global memory: qf[pl][kk] holds, for the 16 columns
+// of k-step kk, {row g cols 2q..2q+1, row g+8 same, row g cols 8+2q.., row g+8 same} of plane pl -- 4-byte loads, the four lanes of a
+// quad cover 16 contiguous bytes of a row.  Rows >= S read as zero.  Used where a tile is the A operand of one product only (Q in the
+// forward): it then never occupies shared memory.
+template <int HD, int PMAX>
+__device__ __forceinline__ void load_a_frags(uint32_t (&qf)[PMAX][HD / 16][4], const View& t, int P, int64_t row0, int col0, int i0, int S, int lane) {
+    const int g = lane >> 2, qd = lane & 3;
+    const bool live0 = i0 + g < S, live1 = i0 + g + 8 < S;
+#pragma unroll
+    for (int pl = 0; pl < PMAX; ++pl) {
+        if (pl < P) {
+            const __nv_bfloat16* r0 = t.ptr + pl * t.stride + (row0 + i0 + g) * t.ld + col0 + 2 * qd;
+            const __nv_bfloat16* r1 = r0 + 8 * t.ld;
+#pragma unroll
+            for (int kk = 0; kk < HD / 16; ++kk) {
+                qf[pl][kk][0] = live0 ? __ldg(reinterpret_cast<const uint32_t*>(r0 + kk * 16)) : 0u;
+                qf[pl][kk][1] = live1 ? __ldg(reinterpret_cast<const uint32_t*>(r1 + kk * 16)) : 0u;
+                qf[pl][kk][2] = live0 ? __ldg(reinterpret_cast<const uint32_t*>(r0 + kk * 16 + 8)) : 0u;
+                qf[pl][kk][3] = live1 ? __ldg(reinterpret_cast<const uint32_t*>(r1 + kk * 16 + 8)) : 0u;
+            }
+        }
+    }
+}
+
+// acc[nt][4] (16 x SP strip) += A (register fragments of load_a_frags) * B^T (sB planes stored [n][k], k contiguous)
+template <int HD, int SP, int PMAX>
+__device__ __forceinline__ void strip_nt_regA(float (&acc)[SP / 8][4], const uint32_t (&qf)[PMAX][HD / 16][4], const __nv_bfloat16* sB, int lane) {
+    constexpr int LDS = HD + 8;
+    const int b_row = (lane & 7) + (lane >> 4) * 8, b_col = ((lane >> 3) & 1) * 8;
+    constexpr int NP = PMAX == 1 ? 1 : (PMAX == 2 ? 3 : 6);
+#pragma unroll
+    for (int kk = 0; kk < HD / 16; ++kk) {
+#pragma unroll
+        for (int pi = 0; pi < NP; ++pi) {
+            // plane products, least significant first (prod())
+            constexpr int PA2[3] = {1, 0, 0}, PB2[3] = {0, 1, 0};
+            constexpr int PA3[6] = {2, 1, 0, 1, 0, 0}, PB3[6] = {0, 1, 2, 0, 1, 0};
+            const int pa = PMAX == 1 ? 0 : (PMAX == 2 ? PA2[pi % 3] : PA3[pi]), pb = PMAX == 1 ? 0 : (PMAX == 2 ? PB2[pi % 3] : PB3[pi]);
+#pragma unroll
+            for (int n2 = 0; n2 < SP / 16; ++n2) {
+                uint32_t b[4];
+                ldsm_x4(ptx::smem_u32(sB + (pb * SP + n2 * 16 + b_row) * LDS + kk * 16 + b_col), b);
+                mma16816(acc[2 * n2], qf[pa][kk], b[0], b[1]);
+                mma16816(acc[2 * n2 + 1], qf[pa][kk], b[2], b[3]);
+            }
+        }
+    }
+}
+
 // out[nt][4] (16 x HD strip) += A(16 x SP, fp32 values in accumulator layout `pv`, split into planes on the fly)
 //                               * B (sB planes stored [k][n], n contiguous: ldmatrix.trans)
 template <int HD, int SP>

@@ -17,7 +17,7 @@ constexpr int P = M2F_ATT_P;
 template <int HD, int SP>
 struct Smem {
     static constexpr int LDS = HD + 8, LDP = SP + 8;
-    static size_t fwd_bytes() { return (size_t)3 * P * SP * LDS * 2; }
+    static size_t fwd_bytes() { return (size_t)2 * P * SP * LDS * 2; }  // K and V; Q goes from global memory to A fragments
     static size_t bwd_bytes() { return (size_t)4 * P * SP * LDS * 2 + (size_t)2 * P * SP * LDP * 2; }
 };
 
@@ -66,42 +66,48 @@ attn_fwd_mma_kernel(View q, View k, View v, const uint8_t* __restrict__ key_pad,
     drop = drop_resolve(drop);
     extern __shared__ __align__(16) uint8_t smraw[];
     constexpr int LDS = HD + 8;
-    __nv_bfloat16* sQ = reinterpret_cast<__nv_bfloat16*>(smraw);
-    __nv_bfloat16* sK = sQ + P * SP * LDS;
+    __nv_bfloat16* sK = reinterpret_cast<__nv_bfloat16*>(smraw);
     __nv_bfloat16* sV = sK + P * SP * LDS;
     const int b = blockIdx.x / H, h = blockIdx.x - b * H;
     const int64_t row0 = (int64_t)b * S;
     const int col0 = h * HD;
-    load_tile<HD, SP>(sQ, q, P, row0, col0, S);
     load_tile<HD, SP>(sK, k, P, row0, col0, S);
     load_tile<HD, SP>(sV, v, P, row0, col0, S);
-    cp_async_wait_all();
-    __syncthreads();
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int i0 = warp * 16;
-    if (i0 >= S) return;
+    const bool active = i0 < S;  // idle strips (S <= 16 (warp - 1)) only take part in the barriers
+    // Q is the A operand of one product and nothing else: its fragments come straight from global memory (under the K / V copies)
+    // and the tile never occupies shared memory -- 60 -> 40 KB per CTA with two planes at hd 96, five CTAs per SM instead of three
+    uint32_t qf[P][HD / 16][4];
+    if (active) load_a_frags<HD, P>(qf, q, P, row0, col0, i0, S, lane);
+    cp_async_wait_all();
+    __syncthreads();
     const int g = lane >> 2, qd = lane & 3;
-    float s[SP / 8][4];
-#pragma unroll
-    for (int nt = 0; nt < SP / 8; ++nt) s[nt][0] = s[nt][1] = s[nt][2] = s[nt][3] = 0.f;
-    strip_nt<HD, SP>(s, sQ, sK, P, i0, lane);
-#pragma unroll
-    for (int nt = 0; nt < SP / 8; ++nt) { s[nt][0] *= scale; s[nt][1] *= scale; s[nt][2] *= scale; s[nt][3] *= scale; }
-    softmax_rows<SP>(s, key_valid_bits(key_pad + row0, S, lane), lane);
-    if (drop.enabled) {
-        const uint32_t bits = drop_bits<SP>(drop, blockIdx.x, S, i0, lane);
-#pragma unroll
-        for (int nt = 0; nt < SP / 8; ++nt)
-#pragma unroll
-            for (int c = 0; c < 4; ++c) s[nt][c] *= drop_mul(bits, nt, c, drop.scale);
-    }
+    (void)g; (void)qd;
     float acc[HD / 8][4];
+    if (active) {
+        float s[SP / 8][4];
 #pragma unroll
-    for (int nt = 0; nt < HD / 8; ++nt) acc[nt][0] = acc[nt][1] = acc[nt][2] = acc[nt][3] = 0.f;
-    strip_regA_nn<HD, SP>(acc, s, sV, P, lane);
-    // this warp's 16 rows of sQ are dead (only this warp read them): stage O there, then coalesced rows to global
-    stage_strip<HD, SP>(acc, 1.f, sQ, P, i0, lane);
-    copy_out_strip<HD, SP>(sQ, o, P, row0, col0, i0, S, lane, nullptr);
+        for (int nt = 0; nt < SP / 8; ++nt) s[nt][0] = s[nt][1] = s[nt][2] = s[nt][3] = 0.f;
+        strip_nt_regA<HD, SP, P>(s, qf, sK, lane);
+#pragma unroll
+        for (int nt = 0; nt < SP / 8; ++nt) { s[nt][0] *= scale; s[nt][1] *= scale; s[nt][2] *= scale; s[nt][3] *= scale; }
+        softmax_rows<SP>(s, key_valid_bits(key_pad + row0, S, lane), lane);
+        if (drop.enabled) {
+            const uint32_t bits = drop_bits<SP>(drop, blockIdx.x, S, i0, lane);
+#pragma unroll
+            for (int nt = 0; nt < SP / 8; ++nt)
+#pragma unroll
+                for (int c = 0; c < 4; ++c) s[nt][c] *= drop_mul(bits, nt, c, drop.scale);
+        }
+#pragma unroll
+        for (int nt = 0; nt < HD / 8; ++nt) acc[nt][0] = acc[nt][1] = acc[nt][2] = acc[nt][3] = 0.f;
+        strip_regA_nn<HD, SP>(acc, s, sV, P, lane);
+    }
+    __syncthreads();  // every warp is done with K: its rows stage O (this warp's 16 rows), then coalesced rows go to global
+    if (!active) return;
+    stage_strip<HD, SP>(acc, 1.f, sK, P, i0, lane);
+    copy_out_strip<HD, SP>(sK, o, P, row0, col0, i0, S, lane, nullptr);
 }
 
 // Backward.  Pd = P * M (M = dropout multiplier), dPd = dO V^T, dP = dPd * M, dS = P * (dP - rowsum(dP * P)),
