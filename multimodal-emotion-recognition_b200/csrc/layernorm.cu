@@ -79,10 +79,11 @@ ln_fwd_kernel(const float* __restrict__ x, int64_t x_ld, const float* __restrict
     }
 }
 
-// Backward.  A block owns groups of 8 rows.  Phase 1, one row per warp: dx (fp32 and / or dropout-masked planes); the
-// row's c1 = mean(g*gamma), c2 = mean(g*gamma*xhat) are parked in shared memory.  Phase 2, one float4 column per
-// thread: the block re-reads its 8 rows of g and x (L1 / L2 hits) and accumulates the dgamma / dbeta / dbias column
-// sums in 12 registers; they leave the block as vector atomics (red.global.add.v4.f32) once, at the end.
+// Backward.  A block owns groups of 8 rows.  Phase 1, one row per warp: dx (fp32 and / or dropout-masked planes); what the
+// column sums need of the row -- g * xhat (dgamma), g (dbeta), the masked dx (dbias) -- is parked in shared memory as it is
+// produced (3 x 8 rows x D floats).  Phase 2, one float4 column per thread: the block adds up its 8 parked rows in 12 registers;
+// the sums leave the block as vector atomics (red.global.add.v4.f32) once, at the end.  (Until late in round 2 phase 2 re-read the
+// rows from global memory and recomputed dx, Philox included: 11 -> 8 us per launch at the training size.)
 constexpr int LNB_ROWS = 8;
 constexpr int LNB_THREADS = LNB_ROWS * 32;
 
@@ -95,12 +96,14 @@ ln_bwd_kernel(const float* __restrict__ g, int64_t g_ld, const float* __restrict
     pdl_wait();
     pdl_trigger();
     drop = drop_resolve(drop);
-    __shared__ float rowc[LNB_ROWS][4];  // mean, rstd, c1, c2
+    extern __shared__ __align__(16) float lnb_park[];  // [3][LNB_ROWS][D]
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const float invD = 1.f / (float)D;
     const int ccol = threadIdx.x * 4;  // phase-2 column of this thread (D <= 1024 = 256 threads x 4)
-    float4 sg = make_float4(0.f, 0.f, 0.f, 0.f), sb = sg, sbias = sg, gmc = sg;
-    if (ccol < D) gmc = *reinterpret_cast<const float4*>(gamma + ccol);
+    float* park_gx = lnb_park + (size_t)warp * D;
+    float* park_g = lnb_park + (size_t)(LNB_ROWS + warp) * D;
+    float* park_m = lnb_park + (size_t)(2 * LNB_ROWS + warp) * D;
+    float4 sg = make_float4(0.f, 0.f, 0.f, 0.f), sb = sg, sbias = sg;
     for (int64_t m0 = (int64_t)blockIdx.x * LNB_ROWS; m0 < M; m0 += (int64_t)gridDim.x * LNB_ROWS) {
         const int64_t m = m0 + warp;
         if (m < M) {
@@ -123,13 +126,14 @@ ln_bwd_kernel(const float* __restrict__ g, int64_t g_ld, const float* __restrict
                 if (col < D) {
                     const float4 gm = *reinterpret_cast<const float4*>(gamma + col);
                     xv[c] = make_float4((xv[c].x - mean) * rstd, (xv[c].y - mean) * rstd, (xv[c].z - mean) * rstd, (xv[c].w - mean) * rstd);
+                    *reinterpret_cast<float4*>(park_gx + col) = make_float4(av[c].x * xv[c].x, av[c].y * xv[c].y, av[c].z * xv[c].z, av[c].w * xv[c].w);
+                    *reinterpret_cast<float4*>(park_g + col) = av[c];
                     av[c] = make_float4(av[c].x * gm.x, av[c].y * gm.y, av[c].z * gm.z, av[c].w * gm.w);
                     s1 += av[c].x + av[c].y + av[c].z + av[c].w;
                     s2 += av[c].x * xv[c].x + av[c].y * xv[c].y + av[c].z * xv[c].z + av[c].w * xv[c].w;
                 }
             }
             const float c1 = warp_sum(s1) * invD, c2 = warp_sum(s2) * invD;
-            if (lane == 0) { rowc[warp][0] = mean; rowc[warp][1] = rstd; rowc[warp][2] = c1; rowc[warp][3] = c2; }
 #pragma unroll
             for (int c = 0; c < NCH; ++c) {
                 const int col = (c * 32 + lane) * 4;
@@ -137,13 +141,14 @@ ln_bwd_kernel(const float* __restrict__ g, int64_t g_ld, const float* __restrict
                     float o[4] = {rstd * (av[c].x - c1 - xv[c].x * c2), rstd * (av[c].y - c1 - xv[c].y * c2),
                                   rstd * (av[c].z - c1 - xv[c].z * c2), rstd * (av[c].w - c1 - xv[c].w * c2)};
                     if (dx) *reinterpret_cast<float4*>(dx + m * dx_ld + col) = make_float4(o[0], o[1], o[2], o[3]);
-                    if (dxpl) {
+                    if (dxpl || dbias) {
                         if (drop.enabled) {
                             float dm[4];
                             drop_mult4(drop, (uint64_t)(m * D + col) >> 2, dm);
                             o[0] *= dm[0]; o[1] *= dm[1]; o[2] *= dm[2]; o[3] *= dm[3];
                         }
-                        store_planes4(dxpl, dxpl_stride, P, m * dxpl_ld + col, o);
+                        if (dxpl) store_planes4(dxpl, dxpl_stride, P, m * dxpl_ld + col, o);
+                        if (dbias) *reinterpret_cast<float4*>(park_m + col) = make_float4(o[0], o[1], o[2], o[3]);
                     }
                 }
             }
@@ -152,22 +157,13 @@ ln_bwd_kernel(const float* __restrict__ g, int64_t g_ld, const float* __restrict
         if (ccol < D) {
             const int nrow = (int)min((int64_t)LNB_ROWS, M - m0);
             for (int r = 0; r < nrow; ++r) {
-                const int64_t mm = m0 + r;
-                const float4 xr = *reinterpret_cast<const float4*>(x + mm * x_ld + ccol);
-                const float4 gr = *reinterpret_cast<const float4*>(g + mm * g_ld + ccol);
-                const float mean = rowc[r][0], rstd = rowc[r][1], c1 = rowc[r][2], c2 = rowc[r][3];
-                const float4 xh = make_float4((xr.x - mean) * rstd, (xr.y - mean) * rstd, (xr.z - mean) * rstd, (xr.w - mean) * rstd);
-                sg.x += gr.x * xh.x; sg.y += gr.y * xh.y; sg.z += gr.z * xh.z; sg.w += gr.w * xh.w;
-                sb.x += gr.x; sb.y += gr.y; sb.z += gr.z; sb.w += gr.w;
+                const float4 a = *reinterpret_cast<const float4*>(lnb_park + (size_t)r * D + ccol);
+                const float4 b = *reinterpret_cast<const float4*>(lnb_park + (size_t)(LNB_ROWS + r) * D + ccol);
+                sg.x += a.x; sg.y += a.y; sg.z += a.z; sg.w += a.w;
+                sb.x += b.x; sb.y += b.y; sb.z += b.z; sb.w += b.w;
                 if (dbias) {
-                    float o[4] = {rstd * (gr.x * gmc.x - c1 - xh.x * c2), rstd * (gr.y * gmc.y - c1 - xh.y * c2),
-                                  rstd * (gr.z * gmc.z - c1 - xh.z * c2), rstd * (gr.w * gmc.w - c1 - xh.w * c2)};
-                    if (drop.enabled) {
-                        float dm[4];
-                        drop_mult4(drop, (uint64_t)(mm * D + ccol) >> 2, dm);
-                        o[0] *= dm[0]; o[1] *= dm[1]; o[2] *= dm[2]; o[3] *= dm[3];
-                    }
-                    sbias.x += o[0]; sbias.y += o[1]; sbias.z += o[2]; sbias.w += o[3];
+                    const float4 cm = *reinterpret_cast<const float4*>(lnb_park + (size_t)(2 * LNB_ROWS + r) * D + ccol);
+                    sbias.x += cm.x; sbias.y += cm.y; sbias.z += cm.z; sbias.w += cm.w;
                 }
             }
         }
@@ -581,8 +577,16 @@ extern "C" int m2f_ln_bwd(const float* g, int64_t g_ld, const float* x, int64_t 
         return M2F_OK;
     }
     const int lnb_grid = (int)std::min<int64_t>((M + LNB_ROWS - 1) / LNB_ROWS, 148 * 4);
-    M2F_LN_DISPATCH(D, M2F_CUDA(launch_chain(ln_bwd_kernel<NCH>, dim3(lnb_grid), dim3(LNB_THREADS), 0, st, 1, g, g_ld, x, x_ld, gamma, stats, M,
-                                             (int)D, dx_f32, dx_ld, dpl, dpl_ld, dpl_stride, P, drop, dgamma, dbeta, dbias)));
+    const size_t lnb_smem = (size_t)3 * LNB_ROWS * D * sizeof(float);  // D <= 1024: <= 96 KB
+    M2F_LN_DISPATCH(D, {
+        static size_t set = 0;
+        if (lnb_smem > 48 * 1024 && lnb_smem > set) {
+            M2F_CUDA(cudaFuncSetAttribute(ln_bwd_kernel<NCH>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)lnb_smem));
+            set = lnb_smem;
+        }
+        M2F_CUDA(launch_chain(ln_bwd_kernel<NCH>, dim3(lnb_grid), dim3(LNB_THREADS), lnb_smem, st, 1, g, g_ld, x, x_ld, gamma, stats, M, (int)D,
+                              dx_f32, dx_ld, dpl, dpl_ld, dpl_stride, P, drop, dgamma, dbeta, dbias));
+    });
     M2F_LAUNCH_CHECK();
     return M2F_OK;
 }
