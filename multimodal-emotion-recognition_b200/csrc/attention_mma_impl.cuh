@@ -80,6 +80,9 @@ attn_fwd_mma_kernel(View q, View k, View v, const uint8_t* __restrict__ key_pad,
     // and the tile never occupies shared memory -- 60 -> 40 KB per CTA with two planes at hd 96, five CTAs per SM instead of three
     uint32_t qf[P][HD / 16][4];
     if (active) load_a_frags<HD, P>(qf, q, P, row0, col0, i0, S, lane);
+    // nothing below depends on the tiles: the key mask (a global load) and the Philox words run under the copies
+    const uint64_t kvalid = key_valid_bits(key_pad + row0, S, lane);
+    const uint32_t dbits = (drop.enabled && active) ? drop_bits<SP>(drop, blockIdx.x, S, i0, lane) : 0xffffffffu;
     cp_async_wait_all();
     __syncthreads();
     const int g = lane >> 2, qd = lane & 3;
@@ -92,13 +95,12 @@ attn_fwd_mma_kernel(View q, View k, View v, const uint8_t* __restrict__ key_pad,
         strip_nt_regA<HD, SP, P>(s, qf, sK, lane);
 #pragma unroll
         for (int nt = 0; nt < SP / 8; ++nt) { s[nt][0] *= scale; s[nt][1] *= scale; s[nt][2] *= scale; s[nt][3] *= scale; }
-        softmax_rows<SP>(s, key_valid_bits(key_pad + row0, S, lane), lane);
+        softmax_rows<SP>(s, kvalid, lane);
         if (drop.enabled) {
-            const uint32_t bits = drop_bits<SP>(drop, blockIdx.x, S, i0, lane);
 #pragma unroll
             for (int nt = 0; nt < SP / 8; ++nt)
 #pragma unroll
-                for (int c = 0; c < 4; ++c) s[nt][c] *= drop_mul(bits, nt, c, drop.scale);
+                for (int c = 0; c < 4; ++c) s[nt][c] *= drop_mul(dbits, nt, c, drop.scale);
         }
 #pragma unroll
         for (int nt = 0; nt < HD / 8; ++nt) acc[nt][0] = acc[nt][1] = acc[nt][2] = acc[nt][3] = 0.f;
@@ -134,11 +136,14 @@ attn_bwd_mma_kernel(View q, View k, View v, View d_o, const uint8_t* __restrict_
     load_tile<HD, SP>(sK, k, P, row0, col0, S);
     load_tile<HD, SP>(sV, v, P, row0, col0, S);
     load_tile<HD, SP>(sdO, d_o, P, row0, col0, S);
-    cp_async_wait_all();
-    __syncthreads();
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int i0 = warp * 16;  // blockDim = 32 * SP / 16: every warp owns one 16-row strip
     const int g = lane >> 2, qd = lane & 3;
+    // nothing here depends on the tiles: the key mask (a global load) and the Philox words run under the copies
+    const uint64_t kvalid = key_valid_bits(key_pad + row0, S, lane);
+    const uint32_t bits = drop.enabled ? drop_bits<SP>(drop, blockIdx.x, S, i0, lane) : 0xffffffffu;
+    cp_async_wait_all();
+    __syncthreads();
     {
         float s[SP / 8][4], dp[SP / 8][4];
 #pragma unroll
@@ -150,9 +155,8 @@ attn_bwd_mma_kernel(View q, View k, View v, View d_o, const uint8_t* __restrict_
         strip_nt<HD, SP>(dp, sdO, sV, P, i0, lane);
 #pragma unroll
         for (int nt = 0; nt < SP / 8; ++nt) { s[nt][0] *= scale; s[nt][1] *= scale; s[nt][2] *= scale; s[nt][3] *= scale; }
-        softmax_rows<SP>(s, key_valid_bits(key_pad + row0, S, lane), lane);
+        softmax_rows<SP>(s, kvalid, lane);
         // dp <- dP = dPd * M; s stays P; pd = P * M written to shared; then dS
-        const uint32_t bits = drop.enabled ? drop_bits<SP>(drop, blockIdx.x, S, i0, lane) : 0xffffffffu;
         const float mscale = drop.enabled ? drop.scale : 1.f;
         float del0 = 0.f, del1 = 0.f;
 #pragma unroll
