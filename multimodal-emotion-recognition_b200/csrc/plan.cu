@@ -1113,7 +1113,7 @@ static int lin_wgrad(Ctx& c, cudaStream_t wst, const m2f_planes_t& dY, const m2f
     c.cur = wst;
     const bool narrow = c.narrow;
     c.narrow = narrow_level() >= 3;  // weight gradients run beside the chain: full-width tiles
-    int rc = c.gemm(dY, true, X, true, out, in, Epi().f32(dW, dW_ld));
+    int rc = debug_skip("wgrad") ? M2F_OK : c.gemm(dY, true, X, true, out, in, Epi().f32(dW, dW_ld));
     c.narrow = narrow;
     if (rc == M2F_OK && db) rc = m2f_colsum_planes(&dY, db, wst);
     c.stamp("wgrad");
