@@ -224,7 +224,9 @@ def test_dp2_peer_exchange_equals_single_gpu(tmp_path, in_graph):
         assert e < 1e-5, (variant, r)
     assert r["same"] and r["buckets"] >= 3
     assert r["err"] < 2e-5, r
-    assert r["param_err_after_4_steps"] < 1e-5, r
+    # as in tests/test_gpu_dp.py: the 6e-8 of summation-order noise in the first gradients grows through four Adam steps (small
+    # entries move by lr whatever their size) to 0.9e-5 .. 1.2e-5; a range exchanged before its producers finished shows as >= 1e-2
+    assert r["param_err_after_4_steps"] < 5e-5, r
 
 
 def _train_steps(pkg, cfg, steps, exchange_world1, overlap, graph, bucket_floats=20000, B=5, S=9):
