@@ -32,6 +32,20 @@ for _ in range(reps):
     ops.gemm(dH, X1, N, K, a_mn=True, b_mn=True, out_f32=dW)
 torch.cuda.synchronize()
 
+# 256 x 192 pair tiles (the plan's choice for the 768- / 2304-wide forward GEMMs): out-projection forward, 2 planes, dropout + residual
+import ctypes as C
+Lh = pkg._lib.lib()
+Lh.m2f_debug_force_gemm_bn.argtypes = [C.c_int]
+Lh.m2f_debug_force_gemm_bn.restype = None
+Ao = ops.PlanesTensor.from_float(torch.randn(M, K, generator=g, device=dev), 2)
+Wo = ops.PlanesTensor.from_float(torch.randn(K, K, generator=g, device=dev) * K ** -0.5, 2)
+bo, ro, yo = torch.zeros(K, device=dev), torch.randn(M, K, generator=g, device=dev), torch.empty(M, K, device=dev)
+Lh.m2f_debug_force_gemm_bn(192)
+for _ in range(reps):
+    ops.gemm(Ao, Wo, M, K, bias=bo, resid=ro, out_f32=yo, drop_p=0.4, seed=1, step=1, site=8)
+Lh.m2f_debug_force_gemm_bn(-1)
+torch.cuda.synchronize()
+
 # the persistent two-accumulator GEMM at the C5 inference size (FFN1, one plane)
 Mi = 131072
 Ai = ops.PlanesTensor.from_float(torch.randn(Mi, K, generator=g, device=dev), 1)
@@ -55,6 +69,14 @@ for _ in range(reps):
     ops.ln_bwd(sk, x, gamma, stats, dx=y, dx_planes=ypl, drop_p=0.4, seed=4, step=5, site=6, dgamma=dgamma, dbeta=dbeta, dbias=dbias)
 torch.cuda.synchronize()
 del x, sk, y, ypl
+
+# LayerNorm at the training size (M = 2112): the register-resident kernels
+xs, gs = torch.randn(M, D, generator=g, device=dev), torch.randn(M, D, generator=g, device=dev)
+ys, yps, sts = torch.empty(M, D, device=dev), ops.PlanesTensor.empty(M, D, 1, dev), torch.empty(M, 2, device=dev)
+for _ in range(reps):
+    ops.ln_fwd(xs, gamma, beta, y=ys, y_planes=yps, stats=sts)
+    ops.ln_bwd(gs, xs, gamma, sts, dx=ys, dx_planes=yps, drop_p=0.4, seed=4, step=5, site=6, dgamma=dgamma, dbeta=dbeta, dbias=dbias)
+torch.cuda.synchronize()
 
 # attention: training kernels (S = 33, 2 planes forward / 1 plane backward) and the long-dialogue inference kernel
 Bq, Sq, H = 2048, 33, 8
