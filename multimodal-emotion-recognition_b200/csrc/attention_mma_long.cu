@@ -232,6 +232,12 @@ attn_bwd_long_kernel(View q, View k, View v, View d_o, const uint8_t* __restrict
                 s[nt][2 + c] = live ? s[nt][2 + c] * scale : -INFINITY;
             }
     };
+    // does key tile kt hold a usable key?  The same answer in every thread (all read the same mask bytes).
+    auto tile_live = [&](int kt) -> bool {
+        uint64_t kv = key_valid_bits(key_pad + row0 + kt * T, S - kt * T, lane);
+        if constexpr (T < 64) kv &= (1ull << T) - 1ull;
+        return kv != 0ull;
+    };
     auto load_q_do = [&](int qi) {
         load_tile<HD, T>(sQ, q, P, row0 + qi * T, col0, S - qi * T);
         load_tile<HD, T>(sdO, d_o, P, row0 + qi * T, col0, S - qi * T);
@@ -249,7 +255,8 @@ attn_bwd_long_kernel(View q, View k, View v, View d_o, const uint8_t* __restrict
         float m0 = -INFINITY, m1 = -INFINITY, l0 = 0.f, l1 = 0.f, a0 = 0.f, a1 = 0.f;
 #pragma unroll 1
         for (int kt = 0; kt < ntile; ++kt) {
-            if (kt) __syncthreads();
+            if (!tile_live(kt)) continue;  // no usable key in the tile: it adds nothing to any row (block-uniform)
+            __syncthreads();
             load_k_v(kt);
             cp_async_wait_all();
             __syncthreads();
@@ -304,7 +311,8 @@ attn_bwd_long_kernel(View q, View k, View v, View d_o, const uint8_t* __restrict
         const float lse0 = stats[2 * r], del0 = stats[2 * r + 1], lse1 = stats[2 * (r + 8)], del1 = stats[2 * (r + 8) + 1];
 #pragma unroll 1
         for (int kt = 0; kt < ntile; ++kt) {
-            if (kt) __syncthreads();
+            if (!tile_live(kt)) continue;
+            __syncthreads();
             load_k_v(kt);
             cp_async_wait_all();
             __syncthreads();
@@ -330,7 +338,8 @@ attn_bwd_long_kernel(View q, View k, View v, View d_o, const uint8_t* __restrict
 #pragma unroll 1
     for (int kt = 0; kt < ntile; ++kt) {
         __syncthreads();
-        load_k_v(kt);
+        const bool live = tile_live(kt);  // a tile without a usable key gets zero gradients: the query loop is left out
+        if (live) load_k_v(kt);
         float accv[HD / 8][4], acck[HD / 8][4];
 #pragma unroll
         for (int nt = 0; nt < HD / 8; ++nt) {
@@ -338,7 +347,7 @@ attn_bwd_long_kernel(View q, View k, View v, View d_o, const uint8_t* __restrict
             acck[nt][0] = acck[nt][1] = acck[nt][2] = acck[nt][3] = 0.f;
         }
 #pragma unroll 1
-        for (int qi = 0; qi < ntile; ++qi) {
+        for (int qi = 0; qi < (live ? ntile : 0); ++qi) {
             if (qi) __syncthreads();  // the previous query tile's dV / dK products have read sQ, sdO, sPd, sdS
             load_q_do(qi);
             cp_async_wait_all();
