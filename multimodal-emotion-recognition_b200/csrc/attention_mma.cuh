@@ -234,6 +234,36 @@ __device__ __forceinline__ void strip_regA_nn(float (&out)[HD / 8][4], const flo
     }
 }
 
+// The same with the plane count known at compile time: the product loop unrolls and the plane selects fold away.
+template <int HD, int SP, int PMAX>
+__device__ __forceinline__ void strip_regA_nn_ct(float (&out)[HD / 8][4], const float (&pv)[SP / 8][4], const __nv_bfloat16* sB, int lane) {
+    constexpr int LDS = HD + 8;
+    const int b_row = (lane & 7) + ((lane >> 3) & 1) * 8, b_col = (lane >> 4) * 8;
+    constexpr int NP = PMAX == 1 ? 1 : (PMAX == 2 ? 3 : 6);
+#pragma unroll
+    for (int kt = 0; kt < SP / 16; ++kt) {
+        uint32_t ap[4][3];
+        split2(pv[2 * kt][0], pv[2 * kt][1], PMAX, ap[0]);
+        split2(pv[2 * kt][2], pv[2 * kt][3], PMAX, ap[1]);
+        split2(pv[2 * kt + 1][0], pv[2 * kt + 1][1], PMAX, ap[2]);
+        split2(pv[2 * kt + 1][2], pv[2 * kt + 1][3], PMAX, ap[3]);
+#pragma unroll
+        for (int pi = 0; pi < NP; ++pi) {
+            constexpr int PA2[3] = {1, 0, 0}, PB2[3] = {0, 1, 0};
+            constexpr int PA3[6] = {2, 1, 0, 1, 0, 0}, PB3[6] = {0, 1, 2, 0, 1, 0};
+            const int pa = PMAX == 1 ? 0 : (PMAX == 2 ? PA2[pi % 3] : PA3[pi]), pb = PMAX == 1 ? 0 : (PMAX == 2 ? PB2[pi % 3] : PB3[pi]);
+            const uint32_t a[4] = {ap[0][pa], ap[1][pa], ap[2][pa], ap[3][pa]};
+#pragma unroll
+            for (int n2 = 0; n2 < HD / 16; ++n2) {
+                uint32_t b[4];
+                ldsm_x4_t(ptx::smem_u32(sB + (pb * SP + kt * 16 + b_row) * LDS + n2 * 16 + b_col), b);
+                mma16816(out[2 * n2], a, b[0], b[1]);
+                mma16816(out[2 * n2 + 1], a, b[2], b[3]);
+            }
+        }
+    }
+}
+
 // out[nt][4] (16 x HD strip, rows i0..) += A (sA planes stored [m][k], leading dim SP + 8) * B (sB planes stored [k][n])
 template <int HD, int SP>
 __device__ __forceinline__ void strip_smemA_nn(float (&out)[HD / 8][4], const __nv_bfloat16* sA, const __nv_bfloat16* sB, int P, int i0, int lane) {

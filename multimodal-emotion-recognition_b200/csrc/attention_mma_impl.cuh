@@ -104,7 +104,7 @@ attn_fwd_mma_kernel(View q, View k, View v, const uint8_t* __restrict__ key_pad,
         }
 #pragma unroll
         for (int nt = 0; nt < HD / 8; ++nt) acc[nt][0] = acc[nt][1] = acc[nt][2] = acc[nt][3] = 0.f;
-        strip_regA_nn<HD, SP>(acc, s, sV, P, lane);
+        strip_regA_nn_ct<HD, SP, P>(acc, s, sV, lane);
     }
     __syncthreads();  // every warp is done with K: its rows stage O (this warp's 16 rows), then coalesced rows go to global
     if (!active) return;
