@@ -13,11 +13,12 @@
 namespace m2f {
 
 constexpr float LN_EPS = 1e-5f;
-constexpr int LN_THREADS = 128;
+constexpr int LN_THREADS = 128;   // default block of the register-resident forward (M2F_LN_FWD_THREADS = 64 / 128 / 256: tuning aid)
 constexpr int LN_WARPS = LN_THREADS / 32;
+constexpr int LN_MAX_THREADS = 256;
 
 template <int NCH>
-__global__ void __launch_bounds__(LN_THREADS)
+__global__ void __launch_bounds__(LN_MAX_THREADS)
 ln_fwd_kernel(const float* __restrict__ x, int64_t x_ld, const float* __restrict__ gamma, const float* __restrict__ beta,
               const float* __restrict__ skip, int64_t skip_ld, int64_t M, int D, float* __restrict__ y, int64_t y_ld,
               __nv_bfloat16* __restrict__ ypl, int64_t ypl_ld, int64_t ypl_stride, int P, Drop drop, float* __restrict__ stats) {
@@ -25,8 +26,9 @@ ln_fwd_kernel(const float* __restrict__ x, int64_t x_ld, const float* __restrict
     pdl_trigger();
     drop = drop_resolve(drop);
     const int lane = threadIdx.x & 31;
-    const int64_t warp0 = (int64_t)blockIdx.x * LN_WARPS + (threadIdx.x >> 5);
-    const int64_t nwarps = (int64_t)gridDim.x * LN_WARPS;
+    const int wpb = (int)(blockDim.x >> 5);
+    const int64_t warp0 = (int64_t)blockIdx.x * wpb + (threadIdx.x >> 5);
+    const int64_t nwarps = (int64_t)gridDim.x * wpb;
     const float invD = 1.f / (float)D;
     for (int64_t m = warp0; m < M; m += nwarps) {
         float4 v[NCH];
@@ -534,7 +536,13 @@ extern "C" int m2f_ln_fwd(const float* x, int64_t x_ld, const float* gamma, cons
         M2F_LAUNCH_CHECK();
         return M2F_OK;
     }
-    M2F_LN_DISPATCH(D, M2F_CUDA(launch_chain(ln_fwd_kernel<NCH>, dim3(ln_grid(M, 1)), dim3(LN_THREADS), 0, st, 1, x, x_ld, gamma, beta, skip,
+    static const int fwd_threads = [] {
+        const char* e = std::getenv("M2F_LN_FWD_THREADS");
+        const int v = e ? std::atoi(e) : LN_THREADS;
+        return (v == 64 || v == 128 || v == 256) ? v : LN_THREADS;
+    }();
+    const int64_t fwd_blocks = std::min<int64_t>((M + fwd_threads / 32 - 1) / (fwd_threads / 32), 148 * 4 * (LN_THREADS / 32) / (fwd_threads / 32));
+    M2F_LN_DISPATCH(D, M2F_CUDA(launch_chain(ln_fwd_kernel<NCH>, dim3((unsigned)std::max<int64_t>(fwd_blocks, 1)), dim3(fwd_threads), 0, st, 1, x, x_ld, gamma, beta, skip,
                                              skip_ld, M, (int)D, y_f32, y_ld, ypl, ypl_ld, ypl_stride, P, drop, stats)));
     M2F_LAUNCH_CHECK();
     return M2F_OK;
