@@ -468,12 +468,6 @@ static int ln_v2_level(int64_t M, int64_t D) {
 }
 static bool ln_v2_enabled(int64_t M, int64_t D) { return ln_v2_level(M, D) >= 1; }
 
-static int ln_grid(int64_t M, int rows_per_warp) {
-    int64_t blocks = (M + LN_WARPS * rows_per_warp - 1) / (LN_WARPS * rows_per_warp);
-    if (blocks > 148 * 4) blocks = 148 * 4;
-    return blocks < 1 ? 1 : (int)blocks;
-}
-
 static int ln_check(const void* x, int64_t x_ld, int64_t M, int64_t D, const char* who) {
     M2F_REQUIRE(x != nullptr && M > 0 && D > 0, M2F_ERR_ARG, "%s: bad argument", who);
     M2F_REQUIRE(D <= 1024 && (D % 4) == 0, M2F_ERR_UNSUPPORTED, "%s: D = %lld unsupported (need D %% 4 == 0 and D <= 1024)", who, (long long)D);
