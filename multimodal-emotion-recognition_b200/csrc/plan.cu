@@ -1019,6 +1019,14 @@ static int forward_modality(Ctx& c, Modality& mo, const float* input, const uint
 
 enum { PH_HEAD = 1, PH_BODY = 2, PH_TAIL = 4, PH_ALL = 7 };
 
+// M2F_FUSION_FORK (default 1): inside the serial fusion section, GEMMs that do not depend on each other run on an idle side
+// stream beside the chain -- forward: the stacked K projections beside relu + the first layer's q|v projection; backward: the
+// text half of d u (needed only by the layer's last GEMM) beside out-proj data gradient + attention backward.  0: one chain.
+static bool fusion_fork() {
+    static const bool on = [] { const char* e = std::getenv("M2F_FUSION_FORK"); return !(e && e[0] == '0'); }();
+    return on;
+}
+
 // M2F_NARROW: 0 = full-width tiles everywhere; 1 (default) = half-width tiles for the under-filled GEMMs of the serial sections
 // (fusion layers, classifier; measured 3.85 -> 3.74 ms per step at C2, profiles/r2_ab_tiles.txt); 2 = also inside the two
 // modality stacks (measured slower: 4.05 vs 4.00 in the same run); 3 = also for the weight gradients (slower still).
@@ -1063,7 +1071,13 @@ static int forward_all(Ctx& c, const float* text, const float* audio, const uint
         m2f_planes_t a = Ctx::cols(zc, 0, Df);
         m2f_planes_t kall = c.pv(p->kall_pl);
         // K projections of every fusion layer read the same audio features: one GEMM
+        const bool kfork = body && fork && fusion_fork();  // the audio chain's stream is idle from the join on
+        if (kfork) {
+            M2F_TRY(c.dep(c.st, c.side(0)));
+            c.cur = c.side(0);
+        }
         OP(c.gemm(a, false, c.pv(md->wk_all.w), false, M, (int64_t)F * Df, Epi().bias(c.f32(md->bk_all)).pl(kall)));
+        c.cur = nullptr;
         m2f_planes_t t_cur = c.pv(p->t0_pl);
         {   // relu(text) half of the first concat operand (src/model.py:16-17); later layers' text is already >= 0
             m2f_planes_t u0r = Ctx::cols(c.pv(p->fam[0].u_pl), Df, Df);
@@ -1075,6 +1089,7 @@ static int forward_all(Ctx& c, const float* text, const float* audio, const uint
             OP(c.gemm(t_cur, false, c.pv(fl.qv.w), false, M, 2 * Df, Epi().bias(c.f32(fl.bqv)).pl(qv)));
             // query = text, key = audio, value = text  (src/model.py:14)
             m2f_planes_t q = Ctx::cols(qv, 0, Df), v = Ctx::cols(qv, Df, Df), k = Ctx::cols(kall, (int64_t)f * Df, Df);
+            if (f == 0 && kfork) M2F_TRY(c.dep(c.side(0), c.st));  // the K projections are needed from here on
             OP(m2f_attn_fwd(&q, &k, &v, key_pad, p->B, p->S, md->cfg.fam_heads, pd, seed, step, M2F_SITE_FAM(f, 0), &xo, c.stream()));
             OP(c.gemm(xo, false, c.pv(fl.wo.w), false, M, Df, Epi().bias(c.prm(fl.wo.b_off)).relu().pl(Ctx::cols(u, 0, Df))));
             m2f_planes_t t_next = (f < F - 1) ? Ctx::cols(c.pv(p->fam[f + 1].u_pl), Df, Df) : Ctx::cols(zc, Df, Df);
@@ -1288,12 +1303,19 @@ static int backward_all(Ctx& c, const uint8_t* key_pad, const float* dlogits, in
             // right half of d u -> first contribution to the gradient of this layer's text input, already in the
             // pre-activation space of its producer: previous fusion linear (relu + dropout: gate [t > 0] / (1-p))
             // or the text projection (cat-relu gate [t0 > 0], then the regenerated projection dropout mask)
+            // (needed only by the layer's last GEMM: it runs beside the chain on the audio stack's idle weight-gradient stream)
+            const bool gfork = p->use_streams && fusion_fork() && c.side(2) != c.st;
+            if (gfork) {
+                M2F_TRY(c.dep(c.st, c.side(2)));
+                c.cur = c.side(2);
+            }
             if (f > 0) {
                 OP(c.gemm(dz_cur, false, Ctx::cols(wl, Df, Df), true, M, Df, Epi().gate(t_in, inv_keep(pd)).f32(gt, gt_ld)));
             } else {
                 OP(c.gemm(dz_cur, false, Ctx::cols(wl, Df, Df), true, M, Df,
                                Epi().gate(t_in, 1.f).drop(pd, seed, step, M2F_SITE_MOD(1, 1), Df).f32(gt, gt_ld)));
             }
+            c.cur = nullptr;
             // attention out-proj
             M2F_TRY(lin_wgrad(c, ws1, dxo, xo, c.grd(fl.wo.w_off), fl.wo.in, nullptr, fl.wo.out, fl.wo.in));
             OP(c.gemm(dxo, false, c.pvb(fl.wo.w), true, M, Df, Epi().pl(dattn)));
@@ -1310,6 +1332,7 @@ static int backward_all(Ctx& c, const uint8_t* key_pad, const float* dlogits, in
             if (ws1 != c.st) M2F_CUDA(cudaEventRecord(p->wgf_ev[n & 1], ws1));
             M2F_TRY(c.done_down_to(fl.inw_off));
             // second + third contributions to the text-input gradient: [dq | dv] . [Wq; Wv], same gate, summed with gt
+            if (gfork) M2F_TRY(c.dep(c.side(2), c.st));
             if (f > 0) {
                 OP(c.gemm(dqv, false, c.pvb(fl.qv.w), true, M, Df,
                                Epi().gate(t_in, inv_keep(pd)).resid(gt, gt_ld).pl(dz_other).colsum(c.grd(p->fam[f - 1].lin.b_off))));
